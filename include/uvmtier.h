@@ -1,0 +1,195 @@
+/*
+ * uvmtier.h -- C ABI of libuvmtier: a B200-native (sm_100a) implementation of the data-parallel
+ * core of the nvidia-uvm tiering path of CXLMemUring/open-gpu-kernel-modules (575.57.08):
+ *
+ *   (1) replayable-fault batch preprocessing  (uvm_gpu_replayable_faults.c)
+ *   (2) the uvm_perf_prefetch bitmap-tree prefetch hint per 2 MB va_block
+ *   (3) va_block make_resident page-list migration between host DRAM, a CXL NUMA node, HBM and
+ *       peer GPUs
+ *
+ * Every entry point cites the reference interface it replaces (paths relative to the reference
+ * root; UVM = kernel-open/nvidia-uvm).  Plain C: pointers and sizes only.  Error convention is
+ * the reference's NV_STATUS (kernel-open/common/inc/nvstatuscodes.h).  There is no CPU fallback:
+ * every compute entry point launches CUDA kernels on the context's device and fails with
+ * NV_ERR_GPU_* / NV_ERR_GENERIC when that is impossible.
+ *
+ * Threading (mirrors UVM/uvm_gpu_isr.c:598-625): one servicing thread per GPU.  Calls on one
+ * uvmtier_ctx_t are not re-entrant; different contexts (GPUs) may be driven concurrently.
+ *
+ * Pointer naming: `d_` = device pointer (HBM of the context's GPU), `h_` = host pointer.
+ * Functions ending in _device take device pointers and only enqueue work on the context stream
+ * (call uvmtier_synchronize to wait); functions without the suffix take host buffers and include
+ * the host<->device copies.
+ */
+#ifndef UVMTIER_H
+#define UVMTIER_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* NV_STATUS subset (kernel-open/common/inc/nvstatuscodes.h:27,59,106,110,172,173)             */
+/* ------------------------------------------------------------------------------------------ */
+typedef uint32_t NV_STATUS;
+#ifndef NV_OK
+#define NV_OK                              0x00000000u
+#define NV_ERR_GENERIC                     0x0000FFFFu
+#define NV_ERR_INVALID_ADDRESS             0x0000001Eu
+#define NV_ERR_INVALID_ARGUMENT            0x0000001Fu
+#define NV_ERR_INVALID_STATE               0x00000040u
+#define NV_ERR_MORE_PROCESSING_REQUIRED    0x0000004Du
+#define NV_ERR_NO_MEMORY                   0x00000051u
+#define NV_ERR_NOT_SUPPORTED               0x00000056u
+#define NV_ERR_INVALID_CHANNEL             0x00000024u
+#define NV_ERR_GPU_NOT_FULL_POWER          0x0000001Au /* used for "no usable CUDA device" */
+#define NV_WARN_MISMATCHED_TARGET          0x00010004u
+#define NV_WARN_MORE_PROCESSING_REQUIRED   0x00010005u
+#endif
+
+/* ------------------------------------------------------------------------------------------ */
+/* Basic types                                                                                 */
+/* ------------------------------------------------------------------------------------------ */
+#define UVMTIER_PAGE_SIZE            4096u
+#define UVMTIER_VA_BLOCK_SIZE        (2u << 20)   /* UVM_VA_BLOCK_SIZE, UVM/uvm_va_block_types.h:42-45 */
+#define UVMTIER_PAGES_PER_VA_BLOCK   512u         /* PAGES_PER_UVM_VA_BLOCK, :50 */
+#define UVMTIER_ID_CPU               0u           /* UVM_ID_CPU_VALUE,  UVM/uvm_processors.h:280 */
+#define UVMTIER_ID_GPU0              1u           /* UVM_ID_GPU0_VALUE, :281 */
+#define UVMTIER_ID_INVALID           257u         /* UVM_ID_INVALID = UVM_ID_MAX_PROCESSORS, :294,300 */
+
+/* uvm_page_mask_t (UVM/uvm_va_block_types.h:77-80): 512 bits, bit p = page p of the va_block.
+ * Arrays of masks are dense: mask i occupies 64 bytes at offset 64*i. */
+typedef struct { uint64_t bitmap[8]; } uvmtier_page_mask_t;
+
+/* uvm_va_block_region_t (UVM/uvm_va_block_types.h:70-75): [first, outer) */
+typedef struct { uint16_t first, outer; } uvmtier_va_block_region_t;
+
+typedef struct uvmtier_ctx uvmtier_ctx_t;
+
+/* ------------------------------------------------------------------------------------------ */
+/* Context                                                                                     */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Tunables; names, defaults and validation are the reference's module parameters
+ * (UVM/uvm_perf_prefetch.c:39-61,504-535; UVM/uvm_gpu_replayable_faults.c:72-115,152-213). */
+typedef struct {
+    uint32_t uvm_perf_prefetch_enable;      /* default 1 */
+    uint32_t uvm_perf_prefetch_threshold;   /* default 51; >100 -> 51 */
+    uint32_t uvm_perf_prefetch_min_faults;  /* default 1; outside [1,20] -> 1 */
+    uint32_t uvm_perf_fault_batch_count;    /* default 256 */
+    uint32_t uvm_perf_fault_coalesce;       /* default 1 */
+    uint32_t reserved[11];
+} uvmtier_config_t;
+
+/* Fills *cfg with the reference defaults. */
+void uvmtier_config_default(uvmtier_config_t *cfg);
+
+/* Creates a context bound to CUDA device `device` (one per GPU, like the reference's per-parent-GPU
+ * batch_service_context, UVM/uvm_gpu.h:411).  Applies the reference's tunable validation
+ * (uvm_perf_prefetch_init, UVM/uvm_perf_prefetch.c:504-535).  cfg may be NULL (defaults). */
+NV_STATUS uvmtier_init(int device, const uvmtier_config_t *cfg, uvmtier_ctx_t **out_ctx);
+void      uvmtier_deinit(uvmtier_ctx_t *ctx);
+
+/* Effective (validated) tunables. */
+void      uvmtier_get_config(const uvmtier_ctx_t *ctx, uvmtier_config_t *out);
+
+/* The context's CUDA stream (cudaStream_t as void*), and wait for all enqueued work. */
+void     *uvmtier_stream(uvmtier_ctx_t *ctx);
+NV_STATUS uvmtier_synchronize(uvmtier_ctx_t *ctx);
+
+/* Library build info: returns a static string "uvmtier <version> sm_100a". */
+const char *uvmtier_version(void);
+/* Number of CUDA kernels this library has launched in this process (all contexts). */
+uint64_t  uvmtier_kernel_launch_count(void);
+/* Last CUDA error text seen by the library on this thread ("" if none). */
+const char *uvmtier_last_error(void);
+
+/* Device memory helpers for C callers without their own CUDA code (thin cudaMalloc/cudaMemcpy). */
+NV_STATUS uvmtier_mem_alloc_device(uvmtier_ctx_t *ctx, size_t bytes, void **out_d_ptr);
+NV_STATUS uvmtier_mem_free_device(uvmtier_ctx_t *ctx, void *d_ptr);
+NV_STATUS uvmtier_mem_alloc_host_pinned(uvmtier_ctx_t *ctx, size_t bytes, void **out_h_ptr);
+NV_STATUS uvmtier_mem_free_host_pinned(uvmtier_ctx_t *ctx, void *h_ptr);
+NV_STATUS uvmtier_memcpy_h2d(uvmtier_ctx_t *ctx, void *d_dst, const void *h_src, size_t bytes);
+NV_STATUS uvmtier_memcpy_d2h(uvmtier_ctx_t *ctx, void *h_dst, const void *d_src, size_t bytes);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Per-block inputs of uvm_perf_prefetch_get_hint_va_block that the reference reads out of
+ * uvm_va_block_t / uvm_va_policy_t / uvm_va_space_t (UVM/uvm_perf_prefetch.c:327-413,447-502). */
+#define UVMTIER_PF_HAS_RESIDENT_MASK       0x01u /* va_block->gpus[dst] != NULL (:357); always true for a CPU dst */
+#define UVMTIER_PF_BLOCK_RESIDENT_EMPTY    0x02u /* uvm_processor_mask_empty(&va_block->resident) (:363) */
+#define UVMTIER_PF_HAS_THRASHING           0x04u /* uvm_perf_thrashing_get_thrashing_pages(va_block) != NULL */
+#define UVMTIER_PF_GPU_VA_SPACE_REGISTERED 0x08u /* dst GPU is in va_space->registered_gpu_va_spaces (:261) */
+
+typedef struct {
+    uint64_t start;              /* va_block->start (page aligned; need not be 64K aligned)          */
+    uint32_t big_page_size;      /* uvm_va_block_gpu_big_page_size(): 65536 (or 131072)              */
+    uint16_t num_pages;          /* uvm_va_block_num_cpu_pages(va_block), 1..512                     */
+    uint16_t faulted_first;      /* faulted_region.first                                             */
+    uint16_t faulted_outer;      /* faulted_region.outer                                             */
+    uint16_t new_residency;      /* uvm_processor_id_t value                                         */
+    uint16_t preferred_location; /* policy->preferred_location value, UVMTIER_ID_INVALID if unset    */
+    uint16_t flags;              /* UVMTIER_PF_*                                                     */
+} uvmtier_prefetch_block_t;      /* 24 bytes */
+
+/* va_block->prefetch_info (UVM/uvm_va_block.h:478-483); in/out. */
+typedef struct {
+    uint16_t last_migration_proc_id;
+    uint16_t fault_migrations_to_last_proc;
+} uvmtier_prefetch_info_t;
+
+/* Batched uvm_perf_prefetch_compute_ats (UVM/uvm_perf_prefetch.h:76-82, .c:425-445): the pure
+ * masks-in / mask-out form.  For block i: faulted pages d_faulted_pages[i], faulted region
+ * d_faulted_region[i], window d_max_prefetch_region[i], residency d_residency_mask[i]
+ * (d_residency_mask may be NULL = no residency information, like the reference's NULL argument).
+ * Writes d_out_prefetch_mask[i].  The bitmap tree is scratch in the reference and lives in
+ * registers here. */
+NV_STATUS uvmtier_perf_prefetch_compute_ats_device(uvmtier_ctx_t *ctx, size_t n_blocks,
+                                                   const uvmtier_page_mask_t *d_faulted_pages,
+                                                   const uvmtier_va_block_region_t *d_faulted_region,
+                                                   const uvmtier_va_block_region_t *d_max_prefetch_region,
+                                                   const uvmtier_page_mask_t *d_residency_mask,
+                                                   uvmtier_page_mask_t *d_out_prefetch_mask);
+NV_STATUS uvmtier_perf_prefetch_compute_ats(uvmtier_ctx_t *ctx, size_t n_blocks,
+                                            const uvmtier_page_mask_t *h_faulted_pages,
+                                            const uvmtier_va_block_region_t *h_faulted_region,
+                                            const uvmtier_va_block_region_t *h_max_prefetch_region,
+                                            const uvmtier_page_mask_t *h_residency_mask,
+                                            uvmtier_page_mask_t *h_out_prefetch_mask);
+
+/* Batched uvm_perf_prefetch_get_hint_va_block (UVM/uvm_perf_prefetch.h:92-98, .c:447-502) for
+ * n independent managed va_blocks.  d_resident[i] = resident mask of new_residency on block i
+ * (uvm_va_block_resident_mask_get, ignored when UVMTIER_PF_HAS_RESIDENT_MASK is clear);
+ * d_thrashing may be NULL (no block has thrashing info); d_cpu_read_mapped =
+ * va_block->cpu.pte_bits[UVM_PTE_BITS_CPU_READ], only read for a CPU destination, may be NULL
+ * (treated as empty).  d_info is updated in place.  Outputs: uvm_perf_prefetch_hint_t
+ * {prefetch_pages_mask -> d_out_prefetch_mask[i], residency -> d_out_residency[i]}.
+ * Range-group clipping (.c:484-494) is not modelled: the harness has no range groups. */
+NV_STATUS uvmtier_perf_prefetch_get_hint_va_block_device(uvmtier_ctx_t *ctx, size_t n_blocks,
+                                                         const uvmtier_prefetch_block_t *d_blocks,
+                                                         const uvmtier_page_mask_t *d_resident,
+                                                         const uvmtier_page_mask_t *d_faulted_pages,
+                                                         const uvmtier_page_mask_t *d_thrashing,
+                                                         const uvmtier_page_mask_t *d_cpu_read_mapped,
+                                                         uvmtier_prefetch_info_t *d_info,
+                                                         uvmtier_page_mask_t *d_out_prefetch_mask,
+                                                         uint32_t *d_out_residency);
+NV_STATUS uvmtier_perf_prefetch_get_hint_va_block(uvmtier_ctx_t *ctx, size_t n_blocks,
+                                                  const uvmtier_prefetch_block_t *h_blocks,
+                                                  const uvmtier_page_mask_t *h_resident,
+                                                  const uvmtier_page_mask_t *h_faulted_pages,
+                                                  const uvmtier_page_mask_t *h_thrashing,
+                                                  const uvmtier_page_mask_t *h_cpu_read_mapped,
+                                                  uvmtier_prefetch_info_t *h_info,
+                                                  uvmtier_page_mask_t *h_out_prefetch_mask,
+                                                  uint32_t *h_out_residency);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* UVMTIER_H */

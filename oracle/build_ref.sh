@@ -1,0 +1,68 @@
+#!/usr/bin/env bash
+# build_ref.sh -- TEST INFRASTRUCTURE ONLY.
+# Compiles the reference's own C for the hot path, from the sources where they lie under
+# /root/reference, against the thin shims in oracle/shim/.  Outputs ONLY shared objects into
+# oracle/_ref/ (git-ignored, but shipped to the GPU box).  Line-range extracts of reference
+# headers are written to a temp dir and deleted; reference sources never enter the repo.
+#
+# Every extract is pinned by the sha256 of its source file: if the reference
+# changes, the build fails instead of silently extracting the wrong lines.
+set -euo pipefail
+
+REF="${UVMTIER_REFERENCE:-/root/reference}"
+HERE="$(cd "$(dirname "${BASH_SOURCE[0]}")" && pwd)"
+OUT="$HERE/_ref"
+UVM="$REF/kernel-open/nvidia-uvm"
+INC="$REF/kernel-open/common/inc"
+
+if [ ! -d "$UVM" ]; then
+    echo "build_ref: $REF not present; keeping prebuilt oracle/_ref/*.so" >&2
+    exit 0
+fi
+
+pin() { # file sha256-prefix
+    local got
+    got="$(sha256sum "$UVM/$1" | cut -c1-16)"
+    if [ "$got" != "$2" ]; then
+        echo "build_ref: $1 sha256 prefix $got != pinned $2" >&2
+        exit 1
+    fi
+}
+pin uvm_perf_prefetch.c fe3d4e338321cecb
+pin uvm_perf_prefetch.h cfc4f49f47d627ef
+pin uvm_perf_utils.h 975610edc6739fea
+pin uvm_va_block.c 085ac82080044437
+pin uvm_va_block.h f1d0ce29432b4487
+pin uvm_va_block_types.h 5c35bec1c234c184
+pin uvm_gpu_replayable_faults.c c7991f9a9e029ae1
+pin uvm_hal_types.h 5b01cb3403d43919
+pin uvm_volta_fault_buffer.c cb8333be2239b583
+pin clc369.h 755c9258db3cbce8
+
+TMP="$(mktemp -d /tmp/uvmtier_ref.XXXXXX)"
+trap 'rm -rf "$TMP"' EXIT
+mkdir -p "$OUT"
+
+CFLAGS="-std=gnu11 -O2 -fPIC -shared -Wall -Wno-unused-function -Wno-unused-variable -Wno-unused-but-set-variable"
+
+# ---------------- prefetch leg: uvm_perf_prefetch.c, whole file, unmodified ----------------
+sed -n '36,80p' "$UVM/uvm_va_block_types.h" > "$TMP/x_va_block_types.h"
+sed -n '1604,1704p;1706,1882p;1915,1995p;2008,2039p' "$UVM/uvm_va_block.h" > "$TMP/x_va_block_helpers.h"
+sed -n '2177,2189p;2202,2220p' "$UVM/uvm_va_block.c" > "$TMP/x_big_page_region.h"
+gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_prefetch_glue.c" -o "$OUT/libref_prefetch.so"
+echo "build_ref: built $OUT/libref_prefetch.so"
+
+# ---------------- fault leg ----------------
+if [ -f "$HERE/ref_faults_glue.c" ]; then
+    sed -n '33,51p;76,98p;201,305p;309,317p;319,325p;342,453p' "$UVM/uvm_hal_types.h" > "$TMP/x_hal_types.h"
+    sed -n '695,740p;742,986p;988,1020p;1118,1212p' "$UVM/uvm_gpu_replayable_faults.c" > "$TMP/x_faults.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_faults_glue.c" -o "$OUT/libref_faults.so"
+    echo "build_ref: built $OUT/libref_faults.so"
+fi
+
+# ---------------- residency / migration leg ----------------
+if [ -f "$HERE/ref_resident_glue.c" ]; then
+    sed -n '36,80p' "$UVM/uvm_va_block_types.h" > "$TMP/x_va_block_types.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" -o "$OUT/libref_resident.so"
+    echo "build_ref: built $OUT/libref_resident.so"
+fi

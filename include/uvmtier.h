@@ -107,6 +107,11 @@ uint64_t  uvmtier_kernel_launch_count(void);
 /* Last CUDA error text seen by the library on this thread ("" if none). */
 const char *uvmtier_last_error(void);
 
+/* uvm_test_rng_32 stream (UVM/uvm_test_rng.c:37-62, Marsaglia KISS with the reference's constants):
+ * fills out[0..n) with the first n outputs for `seed`.  Host-only; the synthetic-trace generators of
+ * the harness shape all their inputs from this stream. */
+void      uvmtier_test_rng_fill(uint32_t seed, size_t n, uint32_t *out);
+
 /* Device memory helpers for C callers without their own CUDA code (thin cudaMalloc/cudaMemcpy). */
 NV_STATUS uvmtier_mem_alloc_device(uvmtier_ctx_t *ctx, size_t bytes, void **out_d_ptr);
 NV_STATUS uvmtier_mem_free_device(uvmtier_ctx_t *ctx, void *d_ptr);
@@ -114,6 +119,152 @@ NV_STATUS uvmtier_mem_alloc_host_pinned(uvmtier_ctx_t *ctx, size_t bytes, void *
 NV_STATUS uvmtier_mem_free_host_pinned(uvmtier_ctx_t *ctx, void *h_ptr);
 NV_STATUS uvmtier_memcpy_h2d(uvmtier_ctx_t *ctx, void *d_dst, const void *h_src, size_t bytes);
 NV_STATUS uvmtier_memcpy_d2h(uvmtier_ctx_t *ctx, void *h_dst, const void *d_src, size_t bytes);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (1) Replayable-fault batch preprocessing -- UVM/uvm_gpu_replayable_faults.c                 */
+/* ------------------------------------------------------------------------------------------ */
+
+/* One HW fault packet: NVC369_BUF_ENTRY, 32 bytes (UVM/clc369.h:33-66). */
+typedef struct { uint32_t w[8]; } uvmtier_fault_packet_t;
+
+/* Flat view of uvm_fault_buffer_entry_t (UVM/uvm_hal_types.h:376-453) after
+ * parse_fault_entry_common (UVM/uvm_volta_fault_buffer.c:312-391) and the fetch-time coalescing of
+ * fetch_fault_buffer_entries (UVM/uvm_gpu_replayable_faults.c:844-986).  Enum values are the
+ * reference's (uvm_aperture_t, uvm_fault_type_t, uvm_fault_access_type_t, ...). */
+#define UVMTIER_FE_FATAL      0x01u  /* is_fatal: fault_type >= UVM_FAULT_TYPE_FATAL (:922) */
+#define UVMTIER_FE_REPLAYABLE 0x02u  /* is_replayable */
+#define UVMTIER_FE_VIRTUAL    0x04u  /* is_virtual */
+#define UVMTIER_FE_PROTECTED  0x08u  /* in_protected_mode */
+#define UVMTIER_FE_FILTERED   0x10u  /* filtered: merged into another entry at fetch time (:753-780) */
+typedef struct {
+    uint64_t fault_address;          /* canonical, page aligned */
+    uint64_t timestamp;
+    uint64_t instance_ptr_address;
+    uint16_t client_id;
+    uint16_t mmu_engine_id;
+    uint16_t utlb_id;
+    uint16_t num_instances;          /* defined for non-filtered entries only (as in the reference) */
+    uint8_t  instance_ptr_aperture;
+    uint8_t  fault_type;
+    uint8_t  fault_access_type;
+    uint8_t  client_type;
+    uint8_t  mmu_engine_type;
+    uint8_t  gpc_id;
+    uint8_t  ve_id;
+    uint8_t  flags;                  /* UVMTIER_FE_* */
+    uint8_t  access_type_mask;       /* defined for non-filtered entries only */
+    uint8_t  pad[7];
+} uvmtier_fault_buffer_entry_t;      /* 48 bytes */
+
+/* One row of the instance-pointer translation table.  Replaces the lookup
+ * uvm_parent_gpu_fault_entry_to_va_space (UVM/uvm_gpu.c:3491-3552): (instance_ptr, ve_id) ->
+ * (va_space, gpu).  First matching row wins.  sort_rank is the dense rank of (va_space, gpu_id) over
+ * the table -- the order cmp_va_space/cmp_gpu (UVM/uvm_gpu_replayable_faults.c:707-719) induce when
+ * va_spaces are allocated from one array (pointer order == index order). */
+#define UVMTIER_VE_ID_ANY 0xFFu
+typedef struct {
+    uint64_t instance_ptr;           /* instance_ptr.address */
+    uint8_t  aperture;               /* uvm_aperture_t value (UVM_APERTURE_VID = 10, _SYS = 9) */
+    uint8_t  ve_id;                  /* subcontext id or UVMTIER_VE_ID_ANY */
+    uint16_t va_space;               /* VA space index */
+    uint16_t gpu_id;                 /* uvm_gpu_id_t value */
+    uint16_t sort_rank;
+} uvmtier_instance_ptr_entry_t;      /* 16 bytes */
+
+/* The uvm_parent_gpu_t fields the fault path reads. */
+typedef struct {
+    uint32_t max_batch_size;         /* fault_buffer.max_batch_size = uvm_perf_fault_batch_count, 1..1024 */
+    uint32_t utlb_per_gpc_count;     /* Blackwell: 2 * maxTpcPerGpcCount + 1 (UVM/uvm_blackwell_fault_buffer.h:85-90) */
+    uint32_t gpc_count;              /* rm_info.maxGpcCount; utlb_count = gpc_count * utlb_per_gpc_count */
+    uint32_t va_bits;                /* canonical-address width (UVM/uvm_gpu.c:428-459): 57 on Hopper+ */
+    uint32_t coalesce;               /* uvm_perf_fault_coalesce */
+    uint32_t reserved[3];
+} uvmtier_fault_gpu_params_t;        /* 32 bytes */
+
+/* Per-batch results: the counters of uvm_fault_service_batch_context_t (UVM/uvm_gpu.h:286-339). */
+typedef struct {
+    uint32_t num_cached_faults;
+    uint32_t num_coalesced_faults;
+    uint32_t is_single_instance_ptr;
+    uint32_t max_utlb_id;
+    uint32_t status;                 /* NV_OK, or NV_WARN_MORE_PROCESSING_REQUIRED when an instance pointer
+                                        did not translate (stale channel: UVM/uvm_gpu_replayable_faults.c:1097-1107) */
+    uint32_t num_duplicate_faults;   /* filled by the service pass (:1200-1203) */
+    uint32_t num_invalid_prefetch_faults;
+    uint32_t num_block_groups;       /* va_block groups found in this batch */
+} uvmtier_fault_batch_t;             /* 32 bytes */
+
+/* One element of ordered_fault_cache[] (the sorted view, UVM/uvm_gpu_replayable_faults.c:1134-1178):
+ * instead of a pointer into fault_cache, the index plus the fields servicing needs. */
+#define UVMTIER_OF_FATAL     0x80u   /* in fault_access_type: entry is fatal (skipped by servicing, :2294) */
+typedef struct {
+    uint64_t fault_address;
+    uint16_t fault_index;            /* index into this batch's fault_cache (ring order) */
+    uint16_t ctx;                    /* row of the instance-pointer table -> va_space, gpu */
+    uint16_t num_instances;
+    uint8_t  access_type_mask;
+    uint8_t  fault_access_type;      /* low 3 bits: uvm_fault_access_type_t; UVMTIER_OF_FATAL */
+} uvmtier_ordered_fault_t;           /* 16 bytes */
+
+/* Per input entry: what fetch-time coalescing did with it. */
+#define UVMTIER_DISP_INDEX_MASK 0x0000FFFFu /* fault_cache index of the entry it was merged into (itself if it opened a new one) */
+#define UVMTIER_DISP_FILTERED   0x00010000u
+#define UVMTIER_DISP_FATAL      0x00020000u
+#define UVMTIER_DISP_VALID      0x00040000u /* entry was fetched (valid bit set, inside the batch) */
+#define UVMTIER_DISP_RULE_SHIFT 24          /* 0 new representative, 1 merged by the per-uTLB rule, 2 by the batch-wide rule */
+
+/* A run of sorted entries that service_fault_batch_block_locked (:1375-1597) handles in one call:
+ * same va_space, same gpu, same 2 MB va_block, no fatal entry. */
+typedef struct {
+    uint64_t block_start;            /* va_block->start (2 MB aligned VA) */
+    uint16_t ctx;                    /* instance-pointer table row of the first entry */
+    uint16_t first_fault_index;      /* position in this batch's ordered array */
+    uint16_t block_faults;           /* entries in the run */
+    uint16_t flags;                  /* bit0: run is a single fatal entry (not serviced) */
+} uvmtier_fault_group_t;             /* 16 bytes */
+
+/* Configures the context's replayable-fault state: the parent-GPU parameters and the instance-pointer
+ * table (copied to the device).  Mirrors fault_buffer_init_replayable_faults
+ * (UVM/uvm_gpu_replayable_faults.c:139-213): allocate-once, reused by every batch.
+ * NV_ERR_INVALID_ARGUMENT for max_batch_size outside 1..1024, va_bits outside 40..57, n_rows > 256 or
+ * sort ranks that do not fit the packed sort key (rank < 256 for batches <= 256, < 64 above). */
+NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_params_t *gpu_params,
+                                    const uvmtier_instance_ptr_entry_t *h_table, size_t n_rows);
+
+/* F1 only: parse n packets (uvm_hal_volta_fault_buffer_parse_replayable_entry without clearing the
+ * valid bit).  num_instances / access_type_mask are 0. */
+NV_STATUS uvmtier_fault_buffer_parse_entries_device(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *d_packets,
+                                                    size_t n, uvmtier_fault_buffer_entry_t *d_out);
+NV_STATUS uvmtier_fault_buffer_parse_entries(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_packets, size_t n,
+                                             uvmtier_fault_buffer_entry_t *h_out);
+
+/* fetch_fault_buffer_entries (:844-986, mode BATCH_READY) + preprocess_fault_batch (:1134-1178) + the
+ * va_block grouping of service_fault_batch (:2232-2377) for ALL batches between GET and PUT at once:
+ * batch b covers ring entries get + b*max_batch_size .. (modulo ring_entries), one CTA per batch.
+ * Inside a batch, entries after the first one whose VALID bit is clear are not fetched.
+ *
+ *   d_ring            the fault ring (ring_entries packets); VALID bits of fetched entries are cleared
+ *                     when clear_valid != 0 (entry_clear_valid, UVM/uvm_pascal_fault_buffer.c:304-318)
+ *   d_disposition     [n] one word per ring entry in fetch order (UVMTIER_DISP_*)
+ *   d_ordered         [n] batch b's sorted view starts at b*max_batch_size
+ *   d_groups          [n] batch b's va_block groups start at b*max_batch_size
+ *   d_batches         [n_batches]
+ *   d_entries         optional [n] full parsed entries (parity/debug view), may be NULL
+ * n = (put - get) mod ring_entries.  Returns the new GET in *out_get (the reference's write_get). */
+NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *d_ring,
+                                                        uint32_t ring_entries, uint32_t get, uint32_t put,
+                                                        int clear_valid, uint32_t *d_disposition,
+                                                        uvmtier_ordered_fault_t *d_ordered,
+                                                        uvmtier_fault_group_t *d_groups,
+                                                        uvmtier_fault_batch_t *d_batches,
+                                                        uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
+/* Host-buffer form of the above: h_ring is copied in, results are copied out (h_entries may be NULL).
+ * The caller's ring is updated (cleared VALID bits) when clear_valid != 0. */
+NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *h_ring,
+                                                 uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
+                                                 uint32_t *h_disposition, uvmtier_ordered_fault_t *h_ordered,
+                                                 uvmtier_fault_group_t *h_groups, uvmtier_fault_batch_t *h_batches,
+                                                 uvmtier_fault_buffer_entry_t *h_entries, uint32_t *out_get);
 
 /* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */

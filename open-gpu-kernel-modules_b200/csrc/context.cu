@@ -156,6 +156,23 @@ NV_STATUS uvmtier_memcpy_d2h(uvmtier_ctx_t *ctx, void *h, const void *d, size_t 
     return NV_OK;
 }
 
+// Marsaglia KISS generator with the reference's constants (UVM/uvm_test_rng.c:37-62): every
+// synthetic trace / page list of the harness is shaped from this stream so that inputs derive
+// from the reference's own test RNG.
+void uvmtier_test_rng_fill(uint32_t seed, size_t n, uint32_t *out)
+{
+    uint32_t z = 362436069u, w = 521288629u, jcong = 380116160u, jsr = seed;
+    for (size_t i = 0; i < n; i++) {
+        z = 36969u * (z & 65535u) + (z >> 16);
+        w = 18000u * (w & 65535u) + (w >> 16);
+        jcong = 69069u * jcong + 1234567u;
+        jsr ^= jsr << 17;
+        jsr ^= jsr >> 13;
+        jsr ^= jsr << 5;
+        out[i] = (((z << 16) + w) ^ jcong) + jsr;
+    }
+}
+
 } // extern "C"
 
 NV_STATUS uvmtier_stage_reserve(uvmtier_ctx_t *ctx, size_t d_bytes, size_t h_bytes)

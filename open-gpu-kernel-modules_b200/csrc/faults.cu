@@ -1,3 +1,212 @@
-// faults.cu -- K0/K1 fault-batch preprocessing (placeholder until the kernels land).
+// faults.cu -- C-ABI entry points of the fault-batch preprocessing leg (K0/K1).
+// Reference: UVM/uvm_gpu_replayable_faults.c (fault_buffer_init_replayable_faults :139-213,
+// fetch_fault_buffer_entries :844-986, preprocess_fault_batch :1134-1178).
+//
+// Layout in HBM.  The ring is the raw array of 32-byte NVC369 packets.  Batch b owns the slice
+// [b*B, (b+1)*B) of every per-entry output array, so CTAs never share an output line.
+// Algorithmic bytes per ring entry: 32 read + 4 disposition + 16 per coalesced entry
+// + 16 per va_block group (+ 32 per batch) written.
 #include "common.cuh"
-void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx) { (void)ctx; }
+
+#include <stdlib.h>
+
+#include "fault_kernels.cuh"
+
+using namespace uvmtier_k;
+
+struct uvmtier_fault_state {
+    uvmtier_fault_gpu_params_t gp;
+    uvmtier_instance_ptr_entry_t *d_table;
+    uint32_t n_rows;
+    uint32_t threads;      // CTA size = next power of two >= max_batch_size (>= 32)
+    uint32_t idx_bits;
+    size_t smem_bytes;
+};
+
+void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx)
+{
+    if (!ctx->faults)
+        return;
+    if (ctx->faults->d_table)
+        cudaFree(ctx->faults->d_table);
+    free(ctx->faults);
+    ctx->faults = NULL;
+}
+
+extern "C" {
+
+NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_params_t *gp,
+                                    const uvmtier_instance_ptr_entry_t *h_table, size_t n_rows)
+{
+    if (!ctx || !gp || (n_rows && !h_table))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (gp->max_batch_size < 1 || gp->max_batch_size > kFaultMaxThreads || gp->va_bits < 40 || gp->va_bits > 57 ||
+        n_rows > kFaultMaxTableRows || gp->utlb_per_gpc_count == 0 || gp->gpc_count == 0 ||
+        gp->utlb_per_gpc_count * gp->gpc_count > 4096)
+        return NV_ERR_INVALID_ARGUMENT;
+
+    uint32_t threads = 32, idx_bits = 5;
+    while (threads < gp->max_batch_size) {
+        threads <<= 1;
+        idx_bits++;
+    }
+    const uint32_t rank_bits = 64 - kPageBits - 3 - idx_bits;
+    for (size_t i = 0; i < n_rows; i++)
+        if (h_table[i].sort_rank >= (1u << rank_bits))
+            return NV_ERR_INVALID_ARGUMENT;
+
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    uvmtier_fault_state_destroy(ctx);
+    uvmtier_fault_state *fs = (uvmtier_fault_state *)calloc(1, sizeof(*fs));
+    if (!fs)
+        return NV_ERR_NO_MEMORY;
+    fs->gp = *gp;
+    fs->gp.coalesce = gp->coalesce != 0;
+    fs->n_rows = (uint32_t)n_rows;
+    fs->threads = threads;
+    fs->idx_bits = idx_bits;
+    fs->smem_bytes = fault_smem_bytes(threads, gp->utlb_per_gpc_count * gp->gpc_count, (uint32_t)n_rows);
+    ctx->faults = fs;
+    UVMTIER_CUDA(cudaMalloc(&fs->d_table, (n_rows ? n_rows : 1) * sizeof(*h_table)));
+    if (n_rows) {
+        UVMTIER_CUDA(cudaMemcpyAsync(fs->d_table, h_table, n_rows * sizeof(*h_table), cudaMemcpyHostToDevice, ctx->stream));
+        UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    }
+    if (fs->smem_bytes > 48 * 1024)
+        UVMTIER_CUDA(cudaFuncSetAttribute(k_fault_fetch_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)fs->smem_bytes));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_fault_buffer_parse_entries_device(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *d_packets, size_t n,
+                                                    uvmtier_fault_buffer_entry_t *d_out)
+{
+    if (!ctx || (n && (!d_packets || !d_out)))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n)
+        return NV_OK;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    size_t grid = (n + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_fault_parse, (int)grid, 256, 0, ctx->stream, d_packets, n, ctx->faults->gp.utlb_per_gpc_count,
+                   ctx->faults->gp.va_bits, d_out);
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_fault_buffer_parse_entries(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_packets, size_t n,
+                                             uvmtier_fault_buffer_entry_t *h_out)
+{
+    if (!ctx || (n && (!h_packets || !h_out)))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n)
+        return NV_OK;
+    const size_t pb = uvmtier_align_up(n * 32, 256);
+    NV_STATUS st = uvmtier_stage_reserve(ctx, pb + n * sizeof(*h_out), 0);
+    if (st != NV_OK)
+        return st;
+    char *d = (char *)ctx->d_stage;
+    UVMTIER_CUDA(cudaMemcpyAsync(d, h_packets, n * 32, cudaMemcpyHostToDevice, ctx->stream));
+    st = uvmtier_fault_buffer_parse_entries_device(ctx, (const uvmtier_fault_packet_t *)d, n,
+                                                   (uvmtier_fault_buffer_entry_t *)(d + pb));
+    if (st != NV_OK)
+        return st;
+    UVMTIER_CUDA(cudaMemcpyAsync(h_out, d + pb, n * sizeof(*h_out), cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *d_ring,
+                                                        uint32_t ring_entries, uint32_t get, uint32_t put,
+                                                        int clear_valid, uint32_t *d_disposition,
+                                                        uvmtier_ordered_fault_t *d_ordered, uvmtier_fault_group_t *d_groups,
+                                                        uvmtier_fault_batch_t *d_batches,
+                                                        uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get)
+{
+    if (!ctx || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    const uvmtier_fault_state *fs = ctx->faults;
+    const uint32_t n = put >= get ? put - get : ring_entries - get + put;
+    if (out_get)
+        *out_get = put;
+    if (!n)
+        return NV_OK;
+    if (!d_disposition || !d_ordered || !d_groups || !d_batches)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    fault_kparams prm;
+    prm.B = fs->gp.max_batch_size;
+    prm.utlb_per_gpc = fs->gp.utlb_per_gpc_count;
+    prm.utlb_count = fs->gp.utlb_per_gpc_count * fs->gp.gpc_count;
+    prm.va_bits = fs->gp.va_bits;
+    prm.coalesce = fs->gp.coalesce && ctx->cfg.uvm_perf_fault_coalesce;
+    prm.ring_entries = ring_entries;
+    prm.get = get;
+    prm.n_entries = n;
+    prm.tbl_n = fs->n_rows;
+    prm.idx_bits = fs->idx_bits;
+    prm.clear_valid = clear_valid != 0;
+    const uint32_t n_batches = (n + prm.B - 1) / prm.B;
+    UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, ctx->stream, prm, d_ring,
+                   fs->d_table, d_disposition, d_ordered, d_groups, d_batches, d_entries);
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *h_ring, uint32_t ring_entries,
+                                                 uint32_t get, uint32_t put, int clear_valid, uint32_t *h_disposition,
+                                                 uvmtier_ordered_fault_t *h_ordered, uvmtier_fault_group_t *h_groups,
+                                                 uvmtier_fault_batch_t *h_batches, uvmtier_fault_buffer_entry_t *h_entries,
+                                                 uint32_t *out_get)
+{
+    if (!ctx || !h_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    const uint32_t n = put >= get ? put - get : ring_entries - get + put;
+    if (!n) {
+        if (out_get)
+            *out_get = put;
+        return NV_OK;
+    }
+    const uint32_t B = ctx->faults->gp.max_batch_size, n_batches = (n + B - 1) / B;
+    const size_t rb = uvmtier_align_up((size_t)ring_entries * 32, 256), db = uvmtier_align_up((size_t)n * 4, 256),
+                 ob = uvmtier_align_up((size_t)n * 16, 256), gb = ob, bb = uvmtier_align_up((size_t)n_batches * 32, 256),
+                 eb = h_entries ? uvmtier_align_up((size_t)n * sizeof(*h_entries), 256) : 0;
+    NV_STATUS st = uvmtier_stage_reserve(ctx, rb + db + ob + gb + bb + eb, 0);
+    if (st != NV_OK)
+        return st;
+    char *d = (char *)ctx->d_stage;
+    uvmtier_fault_packet_t *d_ring = (uvmtier_fault_packet_t *)d;
+    uint32_t *d_disp = (uint32_t *)(d + rb);
+    uvmtier_ordered_fault_t *d_ord = (uvmtier_ordered_fault_t *)(d + rb + db);
+    uvmtier_fault_group_t *d_grp = (uvmtier_fault_group_t *)(d + rb + db + ob);
+    uvmtier_fault_batch_t *d_bat = (uvmtier_fault_batch_t *)(d + rb + db + ob + gb);
+    uvmtier_fault_buffer_entry_t *d_ent = h_entries ? (uvmtier_fault_buffer_entry_t *)(d + rb + db + ob + gb + bb) : NULL;
+    UVMTIER_CUDA(cudaMemcpyAsync(d_ring, h_ring, (size_t)ring_entries * 32, cudaMemcpyHostToDevice, ctx->stream));
+    // slots past num_coalesced / num_block_groups are not written by the kernel: give them a defined value
+    UVMTIER_CUDA(cudaMemsetAsync(d_ord, 0xff, ob + gb, ctx->stream));
+    if (d_ent)
+        UVMTIER_CUDA(cudaMemsetAsync(d_ent, 0, eb, ctx->stream));
+    st = uvmtier_fetch_preprocess_fault_batches_device(ctx, d_ring, ring_entries, get, put, clear_valid, d_disp, d_ord,
+                                                       d_grp, d_bat, d_ent, out_get);
+    if (st != NV_OK)
+        return st;
+    if (clear_valid)
+        UVMTIER_CUDA(cudaMemcpyAsync(h_ring, d_ring, (size_t)ring_entries * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_disposition, d_disp, (size_t)n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_ordered, d_ord, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_groups, d_grp, (size_t)n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_batches, d_bat, (size_t)n_batches * 32, cudaMemcpyDeviceToHost, ctx->stream));
+    if (h_entries)
+        UVMTIER_CUDA(cudaMemcpyAsync(h_entries, d_ent, (size_t)n * sizeof(*h_entries), cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+} // extern "C"

@@ -144,6 +144,41 @@ class Context:
         _check(lib().uvmtier_memcpy_d2h(self._h, P(out), ctypes.c_void_p(dptr), ctypes.c_size_t(out.nbytes)), "memcpy_d2h")
         return out
 
+    # ---- (1) fault batches ----
+    def fault_buffer_init(self, gpu_params, table):
+        """uvmtier_fault_buffer_init: parent-GPU parameters + instance-pointer table."""
+        _check(lib().uvmtier_fault_buffer_init(self._h, P(gpu_params), P(table), ctypes.c_size_t(len(table))),
+               "uvmtier_fault_buffer_init")
+        self._fault_B = int(gpu_params["max_batch_size"][0])
+
+    def fault_buffer_parse_entries(self, packets):
+        from .layouts import FAULT_ENTRY_DT
+        out = np.zeros(len(packets), FAULT_ENTRY_DT)
+        _check(lib().uvmtier_fault_buffer_parse_entries(self._h, P(packets), ctypes.c_size_t(len(packets)), P(out)),
+               "uvmtier_fault_buffer_parse_entries")
+        return out
+
+    def fetch_preprocess_fault_batches(self, ring, get, put, clear_valid=True, want_entries=True):
+        """Host-buffer form. ring: uint32[ring_entries, 8] (updated in place when clear_valid).
+        Returns dict(disp, ordered, groups, batch, entries, get)."""
+        from .layouts import BATCH_DT, FAULT_ENTRY_DT, GROUP_DT, ORDERED_DT
+        ring_entries = len(ring)
+        n = put - get if put >= get else ring_entries - get + put
+        B = self._fault_B
+        nb = (n + B - 1) // B
+        disp = np.zeros(n, "<u4")
+        ordered = np.zeros(n, ORDERED_DT)
+        groups = np.zeros(n, GROUP_DT)
+        batch = np.zeros(nb, BATCH_DT)
+        entries = np.zeros(n, FAULT_ENTRY_DT) if want_entries else None
+        new_get = ctypes.c_uint32(0)
+        _check(lib().uvmtier_fetch_preprocess_fault_batches(self._h, P(ring), ctypes.c_uint32(ring_entries),
+                                                            ctypes.c_uint32(get), ctypes.c_uint32(put),
+                                                            ctypes.c_int(1 if clear_valid else 0), P(disp), P(ordered),
+                                                            P(groups), P(batch), P(entries), ctypes.byref(new_get)),
+               "uvmtier_fetch_preprocess_fault_batches")
+        return dict(disp=disp, ordered=ordered, groups=groups, batch=batch, entries=entries, get=new_get.value)
+
     # ---- (2) prefetch ----
     def perf_prefetch_compute_ats(self, faulted, faulted_region, max_prefetch_region, residency=None):
         """uvm_perf_prefetch_compute_ats for n blocks; host arrays in, uint64[n,8] mask out."""

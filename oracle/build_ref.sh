@@ -55,8 +55,13 @@ echo "build_ref: built $OUT/libref_prefetch.so"
 # ---------------- fault leg ----------------
 if [ -f "$HERE/ref_faults_glue.c" ]; then
     sed -n '33,51p;76,98p;201,305p;309,317p;319,325p;342,453p' "$UVM/uvm_hal_types.h" > "$TMP/x_hal_types.h"
+    sed -n '58,78p' "$UVM/uvm_push_macros.h" > "$TMP/x_push_macros.h"
+    sed -n '105,152p;199,243p;312,391p' "$UVM/uvm_volta_fault_buffer.c" > "$TMP/x_volta_parse.h"
     sed -n '695,740p;742,986p;988,1020p;1118,1212p' "$UVM/uvm_gpu_replayable_faults.c" > "$TMP/x_faults.h"
-    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_faults_glue.c" -o "$OUT/libref_faults.so"
+    sed -n '57,83p' "$UVM/uvm_blackwell_fault_buffer.h" > "$TMP/x_blackwell_utlb_enum.h"
+    sed -n '128,201p' "$UVM/uvm_blackwell_mmu.c" > "$TMP/x_blackwell_client_to_utlb.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_faults_glue.c" "$HERE/ref_faults_blackwell.c" \
+        "$HERE/ref_faults_hopper.c" -o "$OUT/libref_faults.so"
     echo "build_ref: built $OUT/libref_faults.so"
 fi
 

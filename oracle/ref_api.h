@@ -33,4 +33,66 @@ typedef struct {
     uint16_t fault_migrations_to_last_proc; /* NvU16 in the reference: wraps at 65536           */
 } ref_prefetch_info_t;
 
+
+/* ---------------- fault leg ---------------- */
+
+/* parsed fault entry + fetch-time coalescing state (view of uvm_fault_buffer_entry_t,
+ * uvm_hal_types.h:376-453); same layout as uvmtier_fault_buffer_entry_t */
+#define REF_FE_FATAL      0x01
+#define REF_FE_REPLAYABLE 0x02
+#define REF_FE_VIRTUAL    0x04
+#define REF_FE_PROTECTED  0x08
+#define REF_FE_FILTERED   0x10
+typedef struct {
+    uint64_t fault_address;         /* canonical, page aligned                               */
+    uint64_t timestamp;
+    uint64_t instance_ptr_address;
+    uint16_t client_id;
+    uint16_t mmu_engine_id;
+    uint16_t utlb_id;
+    uint16_t num_instances;         /* valid for non-filtered entries                        */
+    uint8_t instance_ptr_aperture;  /* uvm_aperture_t                                        */
+    uint8_t fault_type;             /* uvm_fault_type_t                                      */
+    uint8_t fault_access_type;      /* uvm_fault_access_type_t                               */
+    uint8_t client_type;
+    uint8_t mmu_engine_type;
+    uint8_t gpc_id;
+    uint8_t ve_id;
+    uint8_t flags;                  /* REF_FE_*                                              */
+    uint8_t access_type_mask;       /* valid for non-filtered entries                        */
+    uint8_t pad[7];
+} ref_fault_entry_t;                /* 48 bytes */
+
+#define REF_VE_ID_ANY 0xFF
+/* one row of the instance-pointer translation table (stand-in for
+ * uvm_parent_gpu_fault_entry_to_va_space, uvm_gpu.c:3491-3552) */
+typedef struct {
+    uint64_t instance_ptr;          /* instance_ptr.address (4K aligned)                     */
+    uint8_t aperture;               /* uvm_aperture_t value                                  */
+    uint8_t ve_id;                  /* subcontext, REF_VE_ID_ANY = any                       */
+    uint16_t va_space;              /* index of the uvm_va_space_t (pointer order = index order) */
+    uint16_t gpu_id;                /* uvm_gpu_id_t value                                    */
+    uint16_t sort_rank;             /* dense rank of (va_space, gpu_id) over the table       */
+} ref_instance_ptr_entry_t;         /* 16 bytes */
+
+typedef struct {
+    uint32_t max_batch_size;        /* uvm_perf_fault_batch_count                            */
+    uint32_t utlb_per_gpc_count;    /* parent_gpu->utlb_per_gpc_count (Blackwell: 2*TPC/GPC+1) */
+    uint32_t gpc_count;             /* rm_info.maxGpcCount                                   */
+    uint32_t va_bits;               /* canonical address width: 57 (Hopper+), 49 before      */
+    uint32_t coalesce;              /* uvm_perf_fault_coalesce                               */
+    uint32_t reserved[3];
+} ref_fault_gpu_params_t;
+
+typedef struct {
+    uint32_t num_cached_faults;
+    uint32_t num_coalesced_faults;
+    uint32_t is_single_instance_ptr;
+    uint32_t max_utlb_id;
+    uint32_t status;                /* NV_OK or NV_WARN_MORE_PROCESSING_REQUIRED (0x10005)   */
+    uint32_t num_duplicate_faults;
+    uint32_t num_invalid_prefetch_faults;
+    uint32_t num_block_groups;
+} ref_fault_batch_t;                /* 32 bytes */
+
 #endif

@@ -74,7 +74,10 @@ static inline bool is_power_of_2(unsigned long n) { return n != 0 && (n & (n - 1
 
 static inline int ilog2(unsigned long v) { return 63 - __builtin_clzl(v); }
 static inline unsigned long roundup_pow_of_two(unsigned long v) { return v <= 1 ? 1UL : 1UL << (64 - __builtin_clzl(v - 1)); }
-static inline int order_base_2(unsigned long v) { return v <= 1 ? 0 : ilog2(v - 1) + 1; }
+/* must be an integer constant expression: the reference sizes bit-fields with it */
+#define order_base_2(n) ((n) <= 1 ? 0 : (n) <= 2 ? 1 : (n) <= 4 ? 2 : (n) <= 8 ? 3 : (n) <= 16 ? 4 : (n) <= 32 ? 5 : \
+                         (n) <= 64 ? 6 : (n) <= 128 ? 7 : (n) <= 256 ? 8 : (n) <= 512 ? 9 : (n) <= 1024 ? 10 : \
+                         (n) <= 2048 ? 11 : (n) <= 4096 ? 12 : (n) <= 8192 ? 13 : (n) <= 16384 ? 14 : (n) <= 32768 ? 15 : 16)
 static inline unsigned long __fls(unsigned long w) { return 63 - __builtin_clzl(w); }
 static inline unsigned long __ffs(unsigned long w) { return __builtin_ctzl(w); }
 static inline NvU64 uvm_div_pow2_64(NvU64 n, NvU64 d) { return n >> ilog2(d); }

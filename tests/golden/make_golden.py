@@ -56,5 +56,39 @@ def prefetch():
     print("wrote prefetch_golden.npz", sum(v.nbytes for v in cases.values()), "bytes raw")
 
 
+def faults():
+    import faultlib as F
+    from uvmtier import tracegen as TG
+    ref = T.load_ref("faults")
+    assert ref is not None, "build oracle/_ref first (needs /root/reference)"
+    cases = {}
+    k = 0
+    for dist, ns, B, n in (("uniform", 4, 256, 700), ("stream", 1, 256, 700), ("hotset", 4, 64, 500),
+                           ("adversarial", 2, 256, 900), ("adversarial", 4, 100, 600), ("stream", 16, 1000, 1500)):
+        pk, tbl, _ = TG.fault_trace(n, 77 + k, dist, ns)
+        gp = TG.gpu_params(B)
+        r = F.run_fetch_preprocess(ref, "ref", pk, gp, tbl)
+        pre = "c%d_" % k
+        cases[pre + "packets"] = pk
+        cases[pre + "table"] = tbl
+        cases[pre + "gpu_params"] = gp
+        for name in ("entries", "ordered", "va_space", "gpu", "batch", "ring_after"):
+            cases[pre + name] = r[name]
+        k += 1
+    pk, tbl = F.directed_quirk_trace()
+    gp = TG.gpu_params()
+    r = F.run_fetch_preprocess(ref, "ref", pk, gp, tbl)
+    pre = "c%d_" % k
+    cases[pre + "packets"] = pk; cases[pre + "table"] = tbl; cases[pre + "gpu_params"] = gp
+    for name in ("entries", "ordered", "va_space", "gpu", "batch", "ring_after"):
+        cases[pre + name] = r[name]
+    k += 1
+    cases["n_cases"] = np.array(k)
+    np.savez_compressed(os.path.join(HERE, "faults_golden.npz"), **cases)
+    print("wrote faults_golden.npz")
+
+
 if __name__ == "__main__":
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.dirname(HERE)), "open-gpu-kernel-modules_b200"))
     prefetch()
+    faults()

@@ -1,0 +1,125 @@
+"""GPU parity tests of the fault-preprocessing leg through the C ABI: vs the oracle, the reference-made
+golden vectors, and size-independent properties at the BASELINE size (1M entries)."""
+import numpy as np
+import pytest
+
+import faultlib as F
+import uvmtier_testlib as T
+from uvmtier import tracegen as TG
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_fetch(ctx, pk, gp, tbl, clear_valid=True):
+    ctx.fault_buffer_init(gp, tbl)
+    n = len(pk)
+    ring = np.zeros((n + 1, 8), np.uint32)
+    ring[:n] = pk
+    r = ctx.fetch_preprocess_fault_batches(ring, 0, n, clear_valid=clear_valid)
+    assert r["get"] == n
+    return F.product_to_checker_view(n, int(gp["max_batch_size"][0]), tbl, r["disp"], r["ordered"], r["groups"], r["batch"],
+                                     r["entries"], ring[:n].copy())
+
+
+def test_gpu_matches_golden_vectors(ctx):
+    import os
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "faults_golden.npz"))
+    for k in range(int(g["n_cases"])):
+        pre = "c%d_" % k
+        pk, tbl, gp = g[pre + "packets"], g[pre + "table"], g[pre + "gpu_params"]
+        want = dict(entries=g[pre + "entries"], ordered=g[pre + "ordered"], va_space=g[pre + "va_space"], gpu=g[pre + "gpu"],
+                    batch=g[pre + "batch"], ring_after=g[pre + "ring_after"])
+        got = gpu_fetch(ctx, pk, gp, tbl)
+        F.assert_fetch_equal(want, got, "golden %d" % k)
+        F.check_groups(got, tbl, int(gp["max_batch_size"][0]))
+
+
+@pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
+@pytest.mark.parametrize("B,n_spaces", [(256, 4), (32, 1), (100, 16), (1000, 4), (1024, 2)])
+def test_gpu_matches_oracle(ctx, dist, B, n_spaces):
+    orc = T.load_oracle()
+    pk, tbl, _ = TG.fault_trace(20011, 42, dist, n_spaces)      # ragged last batch
+    gp = TG.gpu_params(B)
+    want = F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl)
+    got = gpu_fetch(ctx, pk, gp, tbl)
+    F.assert_fetch_equal(want, got, "%s B=%d" % (dist, B))
+    F.check_groups(got, tbl, B)
+
+
+def test_gpu_parse_matches_oracle(ctx):
+    orc = T.load_oracle()
+    pk, tbl, _ = TG.fault_trace(10000, 1, "uniform", 4)
+    for va_bits in (57, 49):
+        gp = TG.gpu_params(va_bits=va_bits)
+        ctx.fault_buffer_init(gp, tbl)
+        got = ctx.fault_buffer_parse_entries(pk)
+        want = F.run_parse(orc, "oracle", pk, gp)
+        for f in F.DECODE_FIELDS + ("flags",):
+            assert np.array_equal(got[f], want[f]), f
+
+
+def test_gpu_edge_cases(ctx):
+    orc = T.load_oracle()
+    pk, tbl, _ = TG.fault_trace(512, 9, "uniform", 4)
+    gp = TG.gpu_params(256)
+    # stale channel in batch 1
+    bad = pk.copy(); bad[300, 1] ^= 0x5
+    want = F.run_fetch_preprocess(orc, "oracle", bad, gp, tbl)
+    got = gpu_fetch(ctx, bad, gp, tbl)
+    assert list(got["batch"]["status"]) == [0, F.NV_WARN_MORE_PROCESSING_REQUIRED]
+    F.assert_fetch_equal(want, got)
+    # coalescing off
+    gp0 = TG.gpu_params(256, coalesce=0)
+    pk2, tbl2, _ = TG.fault_trace(700, 3, "stream", 1)
+    F.assert_fetch_equal(F.run_fetch_preprocess(orc, "oracle", pk2, gp0, tbl2), gpu_fetch(ctx, pk2, gp0, tbl2))
+    # fatal fault types
+    pk3, tbl3, _ = TG.fault_trace(600, 5, "adversarial", 2)
+    fatal = np.arange(600) % 7 == 3
+    pk3[fatal, 7] = (pk3[fatal, 7] & ~np.uint32(0x1F)) | TG.HW_FAULT_TYPE_PDE_SIZE
+    pk3[fatal, 3] |= 0x100
+    got = gpu_fetch(ctx, pk3, gp, tbl3)
+    F.assert_fetch_equal(F.run_fetch_preprocess(orc, "oracle", pk3, gp, tbl3), got)
+    F.check_groups(got, tbl3, 256)
+    # empty ring (get == put) and ring wrap-around
+    ctx.fault_buffer_init(gp, tbl)
+    ring = np.zeros((1024, 8), np.uint32)
+    r = ctx.fetch_preprocess_fault_batches(ring, 5, 5)
+    assert r["get"] == 5 and len(r["disp"]) == 0
+    ring[900:] = pk[:124]; ring[:388] = pk[124:]
+    r = ctx.fetch_preprocess_fault_batches(ring, 900, 388)
+    lin = gpu_fetch(ctx, pk, gp, tbl)
+    assert np.array_equal(r["batch"], lin["batch"]) and np.array_equal(r["ordered"], lin["ordered_rec"][:512])
+    # valid bits of fetched entries are cleared, the rest of the ring is untouched
+    assert (ring[900:, 7] >> 31 == 0).all() and (ring[:388, 7] >> 31 == 0).all()
+    # bad arguments
+    import ctypes
+    import uvmtier
+    st = uvmtier.lib().uvmtier_fault_buffer_init(ctx.handle, T.P(TG.gpu_params(2000)), T.P(tbl), ctypes.c_size_t(len(tbl)))
+    assert st == 0x1F
+
+
+def test_gpu_baseline_size_1m_entries(ctx):
+    """Config B: 1,048,576 entries in 256-entry batches.  Full compare with the oracle on the sorted view
+    and counters, plus properties: every batch's sorted view is ordered by the reference comparator, the
+    multiset of fault_cache indices equals the non-filtered set, num_instances sums to num_cached."""
+    orc = T.load_oracle()
+    n = 1 << 20
+    for dist in ("uniform", "stream"):
+        pk, tbl, _ = TG.fault_trace(n, 1, dist, 4)
+        gp = TG.gpu_params(256)
+        got = gpu_fetch(ctx, pk, gp, tbl)
+        want = F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl)
+        F.assert_fetch_equal(want, got, dist)
+        bt = got["batch"]
+        assert int(bt["num_cached_faults"].sum()) == n
+        rec = got["ordered_rec"]
+        live = (got["entries"]["flags"] & F.FE_FILTERED) == 0
+        assert int(live.sum()) == int(bt["num_coalesced_faults"].sum())
+        # sortedness inside every batch: (va_space, gpu, address, access desc, index)
+        pos = np.arange(n) % 256
+        valid = pos < np.repeat(bt["num_coalesced_faults"], 256)[:n]
+        k1 = (tbl["sort_rank"][np.where(valid, rec["ctx"], 0)].astype(np.uint64) << np.uint64(48)) | (rec["fault_address"] >> np.uint64(12))
+        k2 = ((7 - (rec["fault_access_type"] & 7)).astype(np.uint64) << np.uint64(16)) | rec["fault_index"]
+        nxt_same_batch = valid[1:] & valid[:-1] & (pos[1:] != 0)
+        ok = (k1[1:] > k1[:-1]) | ((k1[1:] == k1[:-1]) & (k2[1:] > k2[:-1]))
+        assert ok[nxt_same_batch].all()

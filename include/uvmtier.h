@@ -107,6 +107,19 @@ uint64_t  uvmtier_kernel_launch_count(void);
 /* Last CUDA error text seen by the library on this thread ("" if none). */
 const char *uvmtier_last_error(void);
 
+/* Timing on the context's stream with CUDA events (the stream the kernels are launched on).
+ * uvmtier_event_record enqueues event `slot` (0..UVMTIER_MAX_EVENTS-1); uvmtier_event_elapsed_ms returns the
+ * device time between two recorded slots after synchronising on the later one. */
+#define UVMTIER_MAX_EVENTS 1024
+NV_STATUS uvmtier_event_record(uvmtier_ctx_t *ctx, uint32_t slot);
+NV_STATUS uvmtier_event_elapsed_ms(uvmtier_ctx_t *ctx, uint32_t slot_start, uint32_t slot_stop, float *out_ms);
+/* cudaMemsetAsync on the context's stream (used by the harness to flush L2 between timed iterations). */
+NV_STATUS uvmtier_memset_device(uvmtier_ctx_t *ctx, void *d_ptr, int value, size_t bytes);
+/* Asynchronous copies on the context's stream (host memory should be pinned for true asynchrony). */
+NV_STATUS uvmtier_memcpy_h2d_async(uvmtier_ctx_t *ctx, void *d_dst, const void *h_src, size_t bytes);
+NV_STATUS uvmtier_memcpy_d2h_async(uvmtier_ctx_t *ctx, void *h_dst, const void *d_src, size_t bytes);
+NV_STATUS uvmtier_memcpy_d2d_async(uvmtier_ctx_t *ctx, void *d_dst, const void *d_src, size_t bytes);
+
 /* uvm_test_rng_32 stream (UVM/uvm_test_rng.c:37-62, Marsaglia KISS with the reference's constants):
  * fills out[0..n) with the first n outputs for `seed`.  Host-only; the synthetic-trace generators of
  * the harness shape all their inputs from this stream. */

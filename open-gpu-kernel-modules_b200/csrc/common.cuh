@@ -24,6 +24,7 @@ struct uvmtier_ctx {
     size_t d_stage_bytes;
     void *h_stage;              // pinned
     size_t h_stage_bytes;
+    cudaEvent_t events[UVMTIER_MAX_EVENTS];   // lazily created timing events
     struct uvmtier_fault_state *faults;   // lazily created by the fault entry points
     struct uvmtier_tiers *tiers;          // lazily created by the migration entry points
 };

@@ -99,6 +99,9 @@ void uvmtier_deinit(uvmtier_ctx_t *ctx)
     cudaStreamSynchronize(ctx->stream);
     uvmtier_fault_state_destroy(ctx);
     uvmtier_tiers_destroy(ctx);
+    for (int i = 0; i < UVMTIER_MAX_EVENTS; i++)
+        if (ctx->events[i])
+            cudaEventDestroy(ctx->events[i]);
     if (ctx->d_stage)
         cudaFree(ctx->d_stage);
     if (ctx->h_stage)
@@ -153,6 +156,52 @@ NV_STATUS uvmtier_memcpy_d2h(uvmtier_ctx_t *ctx, void *h, const void *d, size_t 
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     UVMTIER_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_event_record(uvmtier_ctx_t *ctx, uint32_t slot)
+{
+    if (!ctx || slot >= UVMTIER_MAX_EVENTS)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    if (!ctx->events[slot])
+        UVMTIER_CUDA(cudaEventCreate(&ctx->events[slot]));
+    UVMTIER_CUDA(cudaEventRecord(ctx->events[slot], ctx->stream));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_event_elapsed_ms(uvmtier_ctx_t *ctx, uint32_t a, uint32_t b, float *out_ms)
+{
+    if (!ctx || a >= UVMTIER_MAX_EVENTS || b >= UVMTIER_MAX_EVENTS || !out_ms || !ctx->events[a] || !ctx->events[b])
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaEventSynchronize(ctx->events[b]));
+    UVMTIER_CUDA(cudaEventElapsedTime(out_ms, ctx->events[a], ctx->events[b]));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_memset_device(uvmtier_ctx_t *ctx, void *d, int value, size_t bytes)
+{
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaMemsetAsync(d, value, bytes, ctx->stream));
+    return NV_OK;
+}
+NV_STATUS uvmtier_memcpy_h2d_async(uvmtier_ctx_t *ctx, void *d, const void *h, size_t bytes)
+{
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaMemcpyAsync(d, h, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    return NV_OK;
+}
+NV_STATUS uvmtier_memcpy_d2d_async(uvmtier_ctx_t *ctx, void *d_dst, const void *d_src, size_t bytes)
+{
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaMemcpyAsync(d_dst, d_src, bytes, cudaMemcpyDeviceToDevice, ctx->stream));
+    return NV_OK;
+}
+NV_STATUS uvmtier_memcpy_d2h_async(uvmtier_ctx_t *ctx, void *h, const void *d, size_t bytes)
+{
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaMemcpyAsync(h, d, bytes, cudaMemcpyDeviceToHost, ctx->stream));
     return NV_OK;
 }
 

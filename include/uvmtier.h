@@ -67,6 +67,12 @@ typedef struct { uint64_t bitmap[8]; } uvmtier_page_mask_t;
 /* uvm_va_block_region_t (UVM/uvm_va_block_types.h:70-75): [first, outer) */
 typedef struct { uint16_t first, outer; } uvmtier_va_block_region_t;
 
+/* va_block->prefetch_info (UVM/uvm_va_block.h:478-483); in/out of the prefetch hint. */
+typedef struct {
+    uint16_t last_migration_proc_id;
+    uint16_t fault_migrations_to_last_proc;   /* NvU16 in the reference: wraps at 65536 */
+} uvmtier_prefetch_info_t;
+
 typedef struct uvmtier_ctx uvmtier_ctx_t;
 
 /* ------------------------------------------------------------------------------------------ */
@@ -280,6 +286,100 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fau
                                                  uvmtier_fault_buffer_entry_t *h_entries, uint32_t *out_get);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (1b) Servicing the sorted batches per va_block -- UVM/uvm_gpu_replayable_faults.c:1375-2377  */
+/* ------------------------------------------------------------------------------------------ */
+
+/* VA layout of the harness (stand-in for the va_range tree): va_space s owns
+ * [va_base, va_base + blocks_per_space * 2 MB); its va_block b has state slot s * blocks_per_space + b. */
+typedef struct {
+    uint64_t va_base;
+    uint32_t blocks_per_space;
+    uint32_t n_spaces;
+    uint32_t gpu_id;                 /* uvm_gpu_id_t value of the faulting GPU this context serves */
+    uint32_t reserved;
+} uvmtier_va_layout_t;
+
+/* Per-slot va_block state (the uvm_va_block_t fields the hot path reads and writes), SoA, device memory:
+ *   gpu_resident      gpu_state->resident                                    (UVM/uvm_va_block.h:101-230)
+ *   cpu_resident[n]   cpu node state resident, node 0 = host DRAM, 1 = CXL   (:232-266)
+ *   gpu_pte[k]        gpu_state->pte_bits[UVM_PTE_BITS_GPU_READ/WRITE/ATOMIC]
+ *   prefetch_info     va_block->prefetch_info                                 (:478-483)
+ *   logical_prot      compute_logical_prot() of the block's VMA: 0 NONE, 1 READ_ONLY, 3 READ_WRITE_ATOMIC
+ *   preferred_location policy->preferred_location (UVMTIER_ID_INVALID = none) */
+typedef struct {
+    uvmtier_page_mask_t *gpu_resident;
+    uvmtier_page_mask_t *cpu_resident[2];
+    uvmtier_page_mask_t *gpu_pte[3];
+    uvmtier_prefetch_info_t *prefetch_info;
+    uint8_t *logical_prot;
+    uint16_t *preferred_location;
+} uvmtier_block_state_t;
+
+#define UVMTIER_SF_SERVICED         0x0001u /* page added to new_residency (:1560-1579) */
+#define UVMTIER_SF_DUPLICATE        0x0002u /* check_fault_entry_duplicate (:1180-1191) */
+#define UVMTIER_SF_FATAL            0x0004u /* mark_fault_fatal (:1235-1255) */
+#define UVMTIER_SF_INVALID_PREFETCH 0x0008u /* mark_fault_invalid_prefetch (:1214-1228) */
+#define UVMTIER_SF_AUTHORIZED       0x0010u /* uvm_va_block_page_is_gpu_authorized: nothing to do (:1518) */
+#define UVMTIER_SF_ACCESS_SHIFT     5       /* 3 bits: service access type */
+#define UVMTIER_SF_REASON_SHIFT     8       /* 3 bits: UvmEventFatalReason */
+#define UVMTIER_SF_CANCEL_SHIFT     12      /* 1 bit: uvm_fault_cancel_va_mode_t */
+
+/* What servicing one va_block run did: the uvm_service_block_context_t fields that survive the call
+ * (UVM/uvm_va_block_types.h), plus the copy list. */
+typedef struct {
+    uint32_t slot;                   /* block state slot; 0xFFFFFFFF = address outside every va_range */
+    uint16_t region_first, region_outer;
+    uint16_t page_fault_count;
+    uint16_t prefetch_count;
+    uint16_t migrated[2];            /* pages copied from CPU node 0 / 1 */
+    uint16_t first_touch;            /* pages populated (zeroed) at the destination */
+    uint16_t hint_residency;
+    uint32_t run_offset;             /* first copy run of this record in the run array */
+    uint16_t run_count;
+    uint16_t batch;
+    uint32_t group;
+    uvmtier_page_mask_t new_residency; /* per_processor_masks[gpu].new_residency after the prefetch hint */
+} uvmtier_service_group_t;           /* 96 bytes */
+
+/* One contiguous page run to move into HBM (block_copy_resident_pages_between coalesces consecutive pages
+ * with the same cause when both sides are block-contiguous, UVM/uvm_va_block.c:4242-4335). */
+#define UVMTIER_RUN_SRC_ZERO 7u
+typedef struct {
+    uint32_t slot;
+    uint16_t first_page;
+    uint16_t num_pages : 10;
+    uint16_t src : 3;                /* CPU node (0 DRAM, 1 CXL) or UVMTIER_RUN_SRC_ZERO (first touch) */
+    uint16_t prefetch : 1;           /* cause is PREFETCH rather than the fault */
+    uint16_t pad : 2;
+} uvmtier_copy_run_t;                /* 8 bytes */
+
+/* Allocates (zeroed, logical_prot = READ_WRITE_ATOMIC, no preferred location, prefetch_info =
+ * {UVMTIER_ID_INVALID, 0}) / frees the state table of n_spaces * blocks_per_space slots. */
+NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uvmtier_block_state_t *out);
+NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *state);
+
+/* service_fault_batch (:2232-2377) for ALL batches of a preprocess call: every va_block run is serviced
+ * like service_fault_batch_block_locked (:1375-1597) -> uvm_va_block_service_locked
+ * (UVM/uvm_va_block.c:12307): duplicate / permission / already-authorised filtering, prefetch hint,
+ * make_resident residency algebra and copy list, mapping state.  Runs that touch the same va_block are
+ * applied in batch order (the order the reference services them); different va_blocks run in parallel.
+ *
+ *   d_ordered, d_groups, d_batches   outputs of uvmtier_fetch_preprocess_fault_batches_device
+ *                                    (d_batches: num_duplicate_faults / num_invalid_prefetch_faults accumulate)
+ *   d_entry_flags   [n_batches*max_batch_size] UVMTIER_SF_* per sorted entry
+ *   d_service       [n_batches*max_batch_size] record of run g of batch b at b*max_batch_size + g
+ *                   (page_fault_count == 0 and slot set: examined, nothing to service)
+ *   d_runs/run_cap  copy runs; d_counters[0] = runs needed (if > run_cap the list is truncated and the call
+ *                   must be repeated on a fresh state with a larger buffer), d_counters[1] = records written
+ * Scratch (per-slot counters and the per-block run lists) lives in the context and is reused. */
+NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                               const uvmtier_ordered_fault_t *d_ordered,
+                                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                               const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                               uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                               uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */
 
@@ -301,11 +401,6 @@ typedef struct {
     uint16_t flags;              /* UVMTIER_PF_*                                                     */
 } uvmtier_prefetch_block_t;      /* 24 bytes */
 
-/* va_block->prefetch_info (UVM/uvm_va_block.h:478-483); in/out. */
-typedef struct {
-    uint16_t last_migration_proc_id;
-    uint16_t fault_migrations_to_last_proc;
-} uvmtier_prefetch_info_t;
 
 /* Batched uvm_perf_prefetch_compute_ats (UVM/uvm_perf_prefetch.h:76-82, .c:425-445): the pure
  * masks-in / mask-out form.  For block i: faulted pages d_faulted_pages[i], faulted region

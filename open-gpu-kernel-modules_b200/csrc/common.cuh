@@ -13,6 +13,23 @@
 #define UVMTIER_FULL_MASK 0xffffffffu
 #define UVMTIER_NUM_SMS_B200 148
 
+// Replayable-fault state of a context (uvmtier_fault_buffer_init).
+struct uvmtier_fault_state {
+    uvmtier_fault_gpu_params_t gp;
+    uvmtier_instance_ptr_entry_t *d_table;
+    uint32_t n_rows;
+    uint32_t threads;      // CTA size = next power of two >= max_batch_size (>= 32)
+    uint32_t idx_bits;
+    size_t smem_bytes;
+};
+
+// Scratch of the servicing pass (service.cu), grown on demand and reused.
+struct uvmtier_service_scratch {
+    uint32_t *d_count, *d_offset, *d_cursor, *d_sums, *d_batch_unmapped, *d_list;
+    uint32_t n_slots_cap, n_batches_cap;
+    size_t list_cap;
+};
+
 struct uvmtier_ctx {
     int device;
     int sm_count;
@@ -26,6 +43,7 @@ struct uvmtier_ctx {
     size_t h_stage_bytes;
     cudaEvent_t events[UVMTIER_MAX_EVENTS];   // lazily created timing events
     struct uvmtier_fault_state *faults;   // lazily created by the fault entry points
+    struct uvmtier_service_scratch svc;   // scratch of the servicing pass
     struct uvmtier_tiers *tiers;          // lazily created by the migration entry points
 };
 

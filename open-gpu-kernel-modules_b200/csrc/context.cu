@@ -15,6 +15,7 @@ void uvmtier_set_error(const char *what, cudaError_t err, const char *file, int 
 
 void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx);
 void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx);
+void uvmtier_service_scratch_destroy(uvmtier_ctx_t *ctx);
 
 extern "C" {
 
@@ -99,6 +100,7 @@ void uvmtier_deinit(uvmtier_ctx_t *ctx)
     cudaStreamSynchronize(ctx->stream);
     uvmtier_fault_state_destroy(ctx);
     uvmtier_tiers_destroy(ctx);
+    uvmtier_service_scratch_destroy(ctx);
     for (int i = 0; i < UVMTIER_MAX_EVENTS; i++)
         if (ctx->events[i])
             cudaEventDestroy(ctx->events[i]);

@@ -14,14 +14,6 @@
 
 using namespace uvmtier_k;
 
-struct uvmtier_fault_state {
-    uvmtier_fault_gpu_params_t gp;
-    uvmtier_instance_ptr_entry_t *d_table;
-    uint32_t n_rows;
-    uint32_t threads;      // CTA size = next power of two >= max_batch_size (>= 32)
-    uint32_t idx_bits;
-    size_t smem_bytes;
-};
 
 void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx)
 {

@@ -14,6 +14,7 @@
 #pragma once
 
 #include "mask512.cuh"
+#include "uvmtier.h"
 
 // Union (in tree coordinates, one word per lane) of all nodes that pass `thr` and contain a bit
 // of `fw`.  `w` must have no bits at or beyond leaf_count.
@@ -159,4 +160,73 @@ __device__ __forceinline__ uint32_t pf_prefetch_mask(uint32_t pages_t, uint32_t 
     if (bq - offset > offset)                       // quirk nodes: [offset, outer - offset)
         fill |= hw_range(offset, bq - offset, l);
     return fill & hw_range(max_first, max_outer, l);
+}
+
+// uvm_perf_prefetch_prenotify_fault_migrations (:327-413) + the residency decision of
+// uvm_perf_prefetch_get_hint_va_block (:477-500) for one managed va_block per half-warp.
+//   f, res, thr, mapped : this lane's word of faulted / resident(dst) / thrashing / cpu read-mapped masks
+//   flags               : UVMTIER_PF_* ; big_pages: pages per big page of the destination (16 or 32)
+//   *pi                 : va_block->prefetch_info, updated;  *hint: hint residency (UVMTIER_ID_INVALID = none)
+// Returns this lane's word of prefetch_pages_mask.  Warp-synchronous: all 32 lanes must call it.
+__device__ __forceinline__ uint32_t pf_get_hint_block(uint32_t f, uint32_t res, uint32_t thr, uint32_t mapped, bool have_thr,
+                                                      uint64_t start, int num_pages, int ff, int fo, uint32_t dst,
+                                                      uint32_t pref, uint32_t flags, uint32_t big_pages, uint32_t threshold,
+                                                      uint32_t min_faults, uvmtier_prefetch_info_t *pi, uint32_t *hint, int lane)
+{
+    const int l = lane & 15;
+    if (pi->last_migration_proc_id != dst) {                               // :340-343
+        pi->last_migration_proc_id = (uint16_t)dst;
+        pi->fault_migrations_to_last_proc = 0;
+    }
+    const bool first_touch = (flags & UVMTIER_PF_BLOCK_RESIDENT_EMPTY) && dst == pref;   // :363-366
+
+    // ---- tree: init (:222-238), big-page alignment (:275-285), grow (:164-220) ----
+    // Block start inside its big page, in pages.  big_pages is a power of two (16 or 32).
+    const int spb = (int)((start / UVMTIER_PAGE_SIZE) & (big_pages - 1));
+    const int bf = spb ? (int)big_pages - spb : 0;                         // first whole big page
+    const int bo = num_pages - ((spb + num_pages) & ((int)big_pages - 1)); // end of the last whole one
+    const bool has_big = bo > bf;
+    const int offset = (has_big && bf > 0) ? spb : 0;
+    const int leaf_count = num_pages + offset;
+
+    const bool any_off = __any_sync(HW_FULL, offset != 0);
+    uint32_t pages_t = res | f, f_t = f, thr_t = thr;
+    if (any_off) {
+        pages_t = hw_shl(pages_t, offset, l);
+        f_t = hw_shl(f_t, offset, l);
+        thr_t = hw_shl(thr_t, offset, l);
+    }
+    const uint32_t valid_t = hw_range(offset, leaf_count, l);
+    uint32_t grow;
+    if (big_pages == 16) {
+        const uint32_t lo = ((f_t & 0xffffu) && !(thr_t & 0xffffu)) ? 0xffffu : 0u;
+        const uint32_t hi = ((f_t >> 16) && !(thr_t >> 16)) ? 0xffff0000u : 0u;
+        grow = lo | hi;
+    }
+    else {
+        grow = (f_t && !thr_t) ? 0xffffffffu : 0u;
+    }
+    // no whole big page in the block: the block is one region (:173-181)
+    const bool any_f = hw_any(f, lane), any_thr = hw_any(thr, lane);
+    if (!has_big)
+        grow = (any_f && !any_thr) ? 0xffffffffu : 0u;
+    pages_t |= grow & valid_t;
+
+    // ---- walk (:378-390) ----
+    const uint32_t fwork = f & ~thr & hw_range(ff, fo, l);
+    const uint32_t walked = pf_prefetch_mask(pages_t, fwork, 0, num_pages, offset, threshold, l);
+    uint32_t o = first_touch ? hw_range(0, num_pages, l) : walked;
+
+    // ---- post filters (:392-408) ----
+    o &= ~f;
+    if (dst == UVMTIER_ID_CPU)
+        o &= ~(res & mapped);
+    if (have_thr)
+        o &= ~thr;
+    const uint32_t weight = hw_weight(f & hw_range(ff, fo, l));
+    pi->fault_migrations_to_last_proc = (uint16_t)(pi->fault_migrations_to_last_proc + weight);   // :410
+    const uint32_t pending = hw_weight(o);
+    *hint = (pi->fault_migrations_to_last_proc >= min_faults && pending > 0) ? pi->last_migration_proc_id   // :477-500
+                                                                               : (uint32_t)UVMTIER_ID_INVALID;
+    return o;
 }

@@ -84,58 +84,9 @@ k_prefetch_get_hint(size_t n, const uvmtier_prefetch_block_t *__restrict__ block
 
         uint32_t o = 0;
         uint32_t hint = UVMTIER_ID_INVALID;
-        if (tun.enable) {   // uniform
-            if (pi.last_migration_proc_id != dst) {                               // :340-343
-                pi.last_migration_proc_id = (uint16_t)dst;
-                pi.fault_migrations_to_last_proc = 0;
-            }
-            const bool first_touch = (flags & UVMTIER_PF_BLOCK_RESIDENT_EMPTY) && dst == pref;   // :363-366
-
-            // ---- tree: init (:222-238), big-page alignment (:275-285), grow (:164-220) ----
-            // Block start inside its big page, in pages.  big_pages is a power of two (16 or 32).
-            const int spb = (int)((start / UVMTIER_PAGE_SIZE) & (big_pages - 1));
-            const int bf = spb ? (int)big_pages - spb : 0;                         // first whole big page
-            const int bo = num_pages - ((spb + num_pages) & ((int)big_pages - 1)); // end of the last whole one
-            const bool has_big = bo > bf;
-            const int offset = (has_big && bf > 0) ? spb : 0;
-            const int leaf_count = num_pages + offset;
-
-            uint32_t pages_t = hw_shl(res | f, offset, l);
-            const uint32_t f_t = hw_shl(f, offset, l);
-            const uint32_t thr_t = hw_shl(thr, offset, l);
-            const uint32_t valid_t = hw_range(offset, leaf_count, l);
-            uint32_t grow;
-            if (big_pages == 16) {
-                const uint32_t lo = ((f_t & 0xffffu) && !(thr_t & 0xffffu)) ? 0xffffu : 0u;
-                const uint32_t hi = ((f_t >> 16) && !(thr_t >> 16)) ? 0xffff0000u : 0u;
-                grow = lo | hi;
-            }
-            else {
-                grow = (f_t && !thr_t) ? 0xffffffffu : 0u;
-            }
-            // no whole big page in the block: the block is one region (:173-181)
-            const bool any_f = hw_any(f, lane), any_thr = hw_any(thr, lane);
-            if (!has_big)
-                grow = (any_f && !any_thr) ? 0xffffffffu : 0u;
-            pages_t |= grow & valid_t;
-
-            // ---- walk (:378-390) ----
-            const uint32_t fwork = f & ~thr & hw_range(ff, fo, l);
-            const uint32_t walked = pf_prefetch_mask(pages_t, fwork, 0, num_pages, offset, tun.threshold, l);
-            o = first_touch ? hw_range(0, num_pages, l) : walked;
-
-            // ---- post filters (:392-408) ----
-            o &= ~f;
-            if (dst == UVMTIER_ID_CPU)
-                o &= ~(res & mapped);
-            if (have_thr)
-                o &= ~thr;
-            const uint32_t weight = hw_weight(f & hw_range(ff, fo, l));
-            pi.fault_migrations_to_last_proc = (uint16_t)(pi.fault_migrations_to_last_proc + weight);   // :410
-            const uint32_t pending = hw_weight(o);
-            if (pi.fault_migrations_to_last_proc >= tun.min_faults && pending > 0)                      // :477-500
-                hint = pi.last_migration_proc_id;
-        }
+        if (tun.enable)   // uniform
+            o = pf_get_hint_block(f, res, thr, mapped, have_thr, start, num_pages, ff, fo, dst, pref, flags, big_pages,
+                                  tun.threshold, tun.min_faults, &pi, &hint, lane);
         if (live) {
             out[i * 16 + l] = o;
             if (l == 0) {

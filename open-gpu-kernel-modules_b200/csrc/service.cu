@@ -1,0 +1,180 @@
+// service.cu -- C-ABI entry points of the per-va_block servicing pass (stage C/D/E) and the block state table.
+// Reference: UVM/uvm_gpu_replayable_faults.c:2232-2377 (service_fault_batch) and callees; see service_kernels.cuh.
+//
+// Scratch in HBM (owned by the context, grown on demand, reused by every call): per-slot run counters, their
+// exclusive scan and fill cursors (3 x 4 B x n_slots), the per-block run lists (4 B per run) and one flag per
+// batch.  Algorithmic bytes per serviced va_block run: 16 (run) + 16 per entry + 2 per entry flag + 96 record
+// + the block's state (6 masks x 64 B + 8 B) read and written once per touched block, + 8 per copy run.
+#include "common.cuh"
+
+#include <stdlib.h>
+
+#include "service_kernels.cuh"
+
+using namespace uvmtier_k;
+
+static NV_STATUS scratch_reserve(uvmtier_ctx_t *ctx, uint32_t n_slots, uint32_t n_batches, size_t list_entries)
+{
+    uvmtier_service_scratch *s = &ctx->svc;
+    if (n_slots > s->n_slots_cap) {
+        if (s->d_count) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_count); s->d_count = NULL; s->n_slots_cap = 0; }
+        // count | offset | cursor | sums(1024)
+        UVMTIER_CUDA(cudaMalloc(&s->d_count, ((size_t)n_slots * 3 + 1024) * sizeof(uint32_t)));
+        s->d_offset = s->d_count + n_slots;
+        s->d_cursor = s->d_offset + n_slots;
+        s->d_sums = s->d_cursor + n_slots;
+        s->n_slots_cap = n_slots;
+    }
+    else if (s->d_count) {
+        s->d_offset = s->d_count + s->n_slots_cap;
+        s->d_cursor = s->d_offset + s->n_slots_cap;
+        s->d_sums = s->d_cursor + s->n_slots_cap;
+    }
+    if (n_batches > s->n_batches_cap) {
+        if (s->d_batch_unmapped) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_batch_unmapped); s->d_batch_unmapped = NULL; }
+        UVMTIER_CUDA(cudaMalloc(&s->d_batch_unmapped, (size_t)n_batches * sizeof(uint32_t)));
+        s->n_batches_cap = n_batches;
+    }
+    if (list_entries > s->list_cap) {
+        if (s->d_list) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_list); s->d_list = NULL; }
+        UVMTIER_CUDA(cudaMalloc(&s->d_list, list_entries * sizeof(uint32_t)));
+        s->list_cap = list_entries;
+    }
+    return NV_OK;
+}
+
+void uvmtier_service_scratch_destroy(uvmtier_ctx_t *ctx)
+{
+    uvmtier_service_scratch *s = &ctx->svc;
+    if (s->d_count) cudaFree(s->d_count);
+    if (s->d_batch_unmapped) cudaFree(s->d_batch_unmapped);
+    if (s->d_list) cudaFree(s->d_list);
+    memset(s, 0, sizeof(*s));
+}
+
+extern "C" {
+
+NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *lay, uvmtier_block_state_t *out)
+{
+    if (!ctx || !lay || !out || !lay->n_spaces || !lay->blocks_per_space)
+        return NV_ERR_INVALID_ARGUMENT;
+    const size_t n = (size_t)lay->n_spaces * lay->blocks_per_space;
+    if (n > (size_t)1024 * kScanItems)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    memset(out, 0, sizeof(*out));
+    // one allocation: 6 mask arrays, prefetch_info, preferred_location, logical_prot
+    const size_t mask_bytes = n * 64;
+    char *base = NULL;
+    UVMTIER_CUDA(cudaMalloc(&base, 6 * mask_bytes + n * 4 + n * 2 + n));
+    out->gpu_resident = (uvmtier_page_mask_t *)base;
+    out->cpu_resident[0] = (uvmtier_page_mask_t *)(base + mask_bytes);
+    out->cpu_resident[1] = (uvmtier_page_mask_t *)(base + 2 * mask_bytes);
+    out->gpu_pte[0] = (uvmtier_page_mask_t *)(base + 3 * mask_bytes);
+    out->gpu_pte[1] = (uvmtier_page_mask_t *)(base + 4 * mask_bytes);
+    out->gpu_pte[2] = (uvmtier_page_mask_t *)(base + 5 * mask_bytes);
+    out->prefetch_info = (uvmtier_prefetch_info_t *)(base + 6 * mask_bytes);
+    out->preferred_location = (uint16_t *)(base + 6 * mask_bytes + n * 4);
+    out->logical_prot = (uint8_t *)(base + 6 * mask_bytes + n * 4 + n * 2);
+    UVMTIER_CUDA(cudaMemsetAsync(base, 0, 6 * mask_bytes, ctx->stream));
+    // prefetch_info = {UVMTIER_ID_INVALID (0x0101), 0}; preferred_location = 0x0101; logical_prot = 3
+    UVMTIER_CUDA(cudaMemset2DAsync(out->prefetch_info, 4, 0x01, 2, n, ctx->stream));
+    UVMTIER_CUDA(cudaMemset2DAsync((char *)out->prefetch_info + 2, 4, 0x00, 2, n, ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(out->preferred_location, 0x01, n * 2, ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(out->logical_prot, 3, n, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *state)
+{
+    if (!ctx || !state)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    if (state->gpu_resident)
+        UVMTIER_CUDA(cudaFree(state->gpu_resident));
+    memset(state, 0, sizeof(*state));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                               const uvmtier_ordered_fault_t *d_ordered,
+                                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                               const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                               uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                               uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters)
+{
+    if (!ctx || !lay || !state)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n_batches)
+        return NV_OK;
+    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t B = ctx->faults->gp.max_batch_size;
+    const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
+    if (!B || n_slots64 == 0 || n_slots64 > (size_t)1024 * kScanItems)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t n_slots = (uint32_t)n_slots64;
+    const size_t total = (size_t)n_batches * B;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    NV_STATUS st = scratch_reserve(ctx, n_slots, n_batches, total);
+    if (st != NV_OK)
+        return st;
+    uvmtier_service_scratch *s = &ctx->svc;
+
+    service_kparams prm;
+    prm.va_base = lay->va_base;
+    prm.B = B;
+    prm.n_batches = n_batches;
+    prm.blocks_per_space = lay->blocks_per_space;
+    prm.n_spaces = lay->n_spaces;
+    prm.gpu_id = lay->gpu_id;
+    prm.n_slots = n_slots;
+    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable;
+    prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
+    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
+    prm.run_cap = run_cap;
+
+    block_state_ptrs bs;
+    bs.gpu_resident = (uint32_t *)state->gpu_resident;
+    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0];
+    bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
+    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0];
+    bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1];
+    bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
+    bs.prefetch_info = state->prefetch_info;
+    bs.logical_prot = state->logical_prot;
+    bs.preferred_location = state->preferred_location;
+
+    // count + cursor are zeroed together (offset lies between them and is fully rewritten by the scan)
+    UVMTIER_CUDA(cudaMemsetAsync(s->d_count, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(s->d_cursor, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(s->d_batch_unmapped, 0, (size_t)n_batches * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+
+    const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
+    size_t grid = (total + kSvcThreads - 1) / kSvcThreads, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, s->d_count,
+                   s->d_batch_unmapped, s->d_list, 0, s->d_offset, s->d_cursor);
+    const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
+    UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, s->d_count, n_slots, s->d_sums);
+    UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, s->d_sums, n_sums);
+    UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, s->d_count, n_slots, s->d_sums, s->d_offset);
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, s->d_count,
+                   s->d_batch_unmapped, s->d_list, 1, s->d_offset, s->d_cursor);
+    size_t bgrid = ((size_t)n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
+    if (bgrid > cap)
+        bgrid = cap;
+    UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
+                   s->d_count, s->d_offset, s->d_list, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_service_unmapped, (n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches,
+                   d_tbl, s->d_batch_unmapped, d_entry_flags, d_service);
+    return NV_OK;
+}
+
+} // extern "C"

@@ -1,0 +1,481 @@
+// service_kernels.cuh -- stage C/D/E: servicing the sorted fault batches per va_block.
+// Device code only (host side: service.cu); also compiled by tests/simt for the CPU emulator.
+//
+// Reference (UVM = kernel-open/nvidia-uvm): service_fault_batch (uvm_gpu_replayable_faults.c:2232-2377),
+// service_fault_batch_dispatch (:1946-2035), service_fault_batch_block_locked (:1375-1597),
+// check_fault_access_permissions (:1293-1360), uvm_va_block_service_locked (uvm_va_block.c:12307-12359) with
+// uvm_va_block_get_prefetch_hint (:11828-11881), block_copy_resident_pages (:4660-4847),
+// uvm_va_block_make_resident_finish (:5042-5084) and the mapping step of uvm_va_block_service_finish
+// (:12063-12302, compute_new_permission :11019-11066).
+//
+// The reference services batch after batch on one thread.  Different va_blocks never interact, so here
+// every va_block gets one warp that applies the block's runs in batch order:
+//   k_service_count   -> how many runs touch each state slot              (atomics on a per-slot counter)
+//   k_scan_*          -> exclusive scan = start of each slot's list
+//   k_service_fill    -> the slot's list of run ids (unordered)
+//   k_service_blocks  -> per slot: pick the runs in ascending (batch, run) order and service them
+//   k_service_unmapped-> runs whose address lies in no va_range (fatal / invalid prefetch, :2022-2031)
+// A va_block's masks stay in registers across all its runs: one 32-bit word per lane, lanes 16-31 mirror
+// lanes 0-15 (the mask helpers are half-warp wide) so that control flow is uniform across the warp.
+#pragma once
+
+#include "devio.cuh"
+#include "fault_decode.cuh"
+#include "prefetch.cuh"
+
+namespace uvmtier_k {
+
+constexpr int kSvcThreads = 256;
+constexpr uint32_t kScanItems = 4096;      // elements per CTA in the scan kernels (256 threads x 16)
+
+enum : uint32_t { PROT_NONE = 0, PROT_RO = 1, PROT_RW = 2, PROT_RWA = 3 };
+enum : uint32_t { REASON_INVALID_ADDRESS = 1, REASON_INVALID_PERMISSIONS = 2 };   // UvmEventFatalReason
+enum : uint32_t { CANCEL_ALL = 0, CANCEL_WRITE_AND_ATOMIC = 1 };                  // uvm_fault_cancel_va_mode_t
+
+struct service_kparams {
+    uint64_t va_base;
+    uint32_t B, n_batches;
+    uint32_t blocks_per_space, n_spaces, gpu_id, n_slots;
+    uint32_t pf_enable, pf_threshold, pf_min_faults;
+    uint32_t run_cap;
+};
+
+struct block_state_ptrs {
+    uint32_t *gpu_resident;
+    uint32_t *cpu_resident[2];
+    uint32_t *gpu_pte[3];
+    uvmtier_prefetch_info_t *prefetch_info;
+    uint8_t *logical_prot;
+    uint16_t *preferred_location;
+};
+
+// uvm_fault_access_type_to_prot, UVM/uvm_hal_types.h:522-537
+__device__ __forceinline__ uint32_t svc_prot_of(uint32_t acc)
+{
+    return acc == ACC_ATOMIC_STRONG ? PROT_RWA : ((acc == ACC_ATOMIC_WEAK || acc == ACC_WRITE) ? PROT_RW : PROT_RO);
+}
+
+// State slot of a run, or 0xFFFFFFFF when its va_block lies in no va_range of its VA space.
+__device__ __forceinline__ uint32_t svc_slot(const service_kparams &prm, uint32_t va_space, uint64_t block_start)
+{
+    const uint64_t off = block_start - prm.va_base;
+    if (block_start < prm.va_base || (off >> 21) >= prm.blocks_per_space || va_space >= prm.n_spaces)
+        return 0xffffffffu;
+    return va_space * prm.blocks_per_space + (uint32_t)(off >> 21);
+}
+
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(kSvcThreads)
+k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ groups,
+                const uvmtier_fault_batch_t *__restrict__ batches, const uvmtier_instance_ptr_entry_t *__restrict__ tbl,
+                uint32_t *__restrict__ count, uint32_t *__restrict__ batch_unmapped, uint32_t *__restrict__ list, int fill,
+                const uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
+{
+    const uint32_t total = prm.n_batches * prm.B;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const uint32_t b = t / prm.B, g = t - b * prm.B;
+        const uvmtier_fault_batch_t bt = batches[b];
+        if (bt.status != NV_OK || g >= bt.num_block_groups)
+            continue;
+        const uvmtier_fault_group_t grp = groups[t];
+        if (grp.flags & 1u)
+            continue;                                       // fatal fault type: service_fault_batch skips it (:2294-2303)
+        const uint32_t slot = svc_slot(prm, tbl[grp.ctx].va_space, grp.block_start);
+        if (slot == 0xffffffffu) {
+            if (!fill)
+                batch_unmapped[b] = 1u;
+            continue;
+        }
+        if (!fill)
+            atomicAdd(&count[slot], 1u);
+        else
+            list[offset[slot] + atomicAdd(&cursor[slot], 1u)] = t;
+    }
+}
+
+// ---- exclusive scan of count[0..n) into offset[0..n): per-CTA sums, scan of the sums, final pass ----
+__global__ void __launch_bounds__(256)
+k_scan_sums(const uint32_t *__restrict__ in, uint32_t n, uint32_t *__restrict__ sums)
+{
+    __shared__ uint32_t s_w[8];
+    const uint32_t base = blockIdx.x * kScanItems;
+    uint32_t v = 0;
+    for (uint32_t i = threadIdx.x; i < kScanItems; i += 256)
+        if (base + i < n) v += in[base + i];
+    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
+    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        uint32_t t = 0;
+        for (int w = 0; w < 8; w++) t += s_w[w];
+        sums[blockIdx.x] = t;
+    }
+}
+
+__global__ void __launch_bounds__(1024)
+k_scan_top(uint32_t *__restrict__ sums, uint32_t n_sums)
+{
+    // n_sums <= 1024: one element per thread, in-place exclusive scan
+    __shared__ uint32_t s_w[32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t v = tid < n_sums ? sums[tid] : 0u;
+    uint32_t x = v;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if ((int)lane >= d) x += y;
+    }
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = s_w[lane];
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, w, d);
+            if ((int)lane >= d) w += y;
+        }
+        s_w[lane] = w;
+    }
+    __syncthreads();
+    const uint32_t before = warp ? s_w[warp - 1] : 0u;
+    if (tid < n_sums)
+        sums[tid] = before + x - v;
+}
+
+__global__ void __launch_bounds__(256)
+k_scan_final(const uint32_t *__restrict__ in, uint32_t n, const uint32_t *__restrict__ sums, uint32_t *__restrict__ out)
+{
+    // thread t owns 16 consecutive elements
+    __shared__ uint32_t s_w[8];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t base = blockIdx.x * kScanItems + tid * 16;
+    uint32_t v[16], tot = 0;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        v[k] = base + k < n ? in[base + k] : 0u;
+        tot += v[k];
+    }
+    uint32_t x = tot;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if ((int)lane >= d) x += y;
+    }
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    uint32_t before = sums[blockIdx.x];
+    for (uint32_t w = 0; w < warp; w++) before += s_w[w];
+    uint32_t run = before + x - tot;
+#pragma unroll
+    for (int k = 0; k < 16; k++) {
+        if (base + k < n) out[base + k] = run;
+        run += v[k];
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Counts (and, with runs != NULL, writes) the copy runs of mask `m`: maximal sequences of consecutive pages
+// with the same cause (UVM/uvm_va_block.c:4242-4335).  Warp-synchronous; word per lane, half-warp wide.
+__device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint32_t slot, uint32_t src,
+                                                  uvmtier_copy_run_t *runs, uint32_t at, uint32_t run_cap, int lane)
+{
+    const int l = lane & 15;
+    uint32_t pm = __shfl_up_sync(HW_FULL, m >> 31, 1, 16);
+    uint32_t pp = __shfl_up_sync(HW_FULL, pf >> 31, 1, 16);
+    if (l == 0) { pm = 0; pp = 0; }
+    const uint32_t m_prev = (m << 1) | pm, pf_prev = (pf << 1) | pp;
+    uint32_t start = m & (~m_prev | (pf ^ pf_prev));
+    const uint32_t stop = ~m | start;                       // a run cannot extend through these positions
+    const uint32_t nstart = __popc(start);
+    // exclusive prefix of nstart over the 16 lanes, and the total
+    uint32_t incl = nstart;
+    for (int d = 1; d < 16; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(HW_FULL, incl, d, 16);
+        if (l >= d) incl += y;
+    }
+    const uint32_t total = __shfl_sync(HW_FULL, incl, 15, 16);
+    if (!runs)
+        return total;
+    // first stop at or after the start of each FOLLOWING word (suffix minimum), 512 if none
+    uint32_t mine = stop ? (uint32_t)(32 * l + __ffs((int)stop) - 1) : 512u;
+    uint32_t next_abs = __shfl_down_sync(HW_FULL, mine, 1, 16);
+    if (l == 15) next_abs = 512u;
+    for (int d = 1; d < 16; d <<= 1) {
+        const uint32_t y = __shfl_down_sync(HW_FULL, next_abs, d, 16);
+        if (l + d <= 15) next_abs = min(next_abs, y);
+    }
+    uint32_t k = at + incl - nstart;
+    while (start) {
+        const int s = __ffs((int)start) - 1;
+        start &= start - 1;
+        const uint32_t rest = s == 31 ? 0u : (stop >> (s + 1));
+        const uint32_t first = (uint32_t)(32 * l + s);
+        const uint32_t end = rest ? first + (uint32_t)__ffs((int)rest) : next_abs;
+        if (k < run_cap && lane < 16) {
+            uvmtier_copy_run_t r;
+            r.slot = slot;
+            r.first_page = (uint16_t)first;
+            r.num_pages = (uint16_t)(end - first);
+            r.src = (uint16_t)src;
+            r.prefetch = (uint16_t)((pf >> s) & 1u);
+            r.pad = 0;
+            runs[k] = r;
+        }
+        k++;
+    }
+    return total;
+}
+
+// One warp per state slot.
+__global__ void __launch_bounds__(kSvcThreads)
+k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
+                 const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
+                 block_state_ptrs st, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
+                 const uint32_t *__restrict__ list, uint16_t *__restrict__ entry_flags,
+                 uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
+                 uint32_t *__restrict__ counters)
+{
+    const int lane = threadIdx.x & 31, l = lane & 15;
+    const uint32_t n_warps = gridDim.x * (kSvcThreads / 32);
+    for (uint32_t slot = blockIdx.x * (kSvcThreads / 32) + (threadIdx.x >> 5); slot < prm.n_slots; slot += n_warps) {
+        const uint32_t cnt = count[slot];
+        if (!cnt)
+            continue;
+        const uint32_t off = offset[slot];
+        const size_t w = (size_t)slot * 16 + l;
+        uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
+        uint32_t pte0 = st.gpu_pte[0][w], pte1 = st.gpu_pte[1][w], pte2 = st.gpu_pte[2][w];
+        const uint32_t logical = st.logical_prot[slot], pref = st.preferred_location[slot];
+        uvmtier_prefetch_info_t pi = st.prefetch_info[slot];
+
+        const uint32_t mykey = (uint32_t)lane < cnt ? list[off + lane] : 0xffffffffu;
+        uint32_t last = 0;
+        for (uint32_t k = 0; k < cnt; k++) {
+            // ---- next run of this va_block in (batch, run) order ----
+            uint32_t best = (k == 0 || mykey > last) ? mykey : 0xffffffffu;
+            if (cnt > 32)
+                for (uint32_t j = lane + 32; j < cnt; j += 32) {
+                    const uint32_t v = list[off + j];
+                    if ((k == 0 || v > last) && v < best) best = v;
+                }
+            for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(HW_FULL, best, d));
+            const uint32_t t = best;
+            last = t;
+            const uint32_t b = t / prm.B, base = b * prm.B;
+            const uvmtier_fault_group_t grp = groups[t];
+            const uint32_t first = grp.first_fault_index, n = grp.block_faults;
+
+            // ---- service_fault_batch_block_locked :1433-1580 ----
+            uint32_t newres = 0, page_faults = 0, dup_sum = 0, ip_sum = 0, prev_page = 0xffffffffu;
+            int first_page = 512, last_page = 0;
+            bool prev_fatal = false, prev_ip = false;
+            for (uint32_t i = 0; i < n; i++) {
+                const uvmtier_ordered_fault_t e = ordered[base + first + i];
+                const uint32_t acc = e.fault_access_type & 7u;
+                const uint32_t page = (uint32_t)((e.fault_address - grp.block_start) >> 12);
+                const bool dup = i > 0 && page == prev_page;              // same va_space inside a run (:1180-1191)
+                uint32_t service_acc = acc, fl = 0;
+                bool entry_fatal = false, entry_ip = false, done = false;
+                dup_sum += dup ? e.num_instances : (uint32_t)e.num_instances - 1u;   // :1200-1203
+                if (dup) {
+                    fl |= UVMTIER_SF_DUPLICATE;
+                    if (prev_ip) {                                        // fault_entry_duplicate_flags :1257-1272
+                        entry_ip = true;
+                        ip_sum += e.num_instances;
+                    }
+                    if (!prev_fatal)
+                        done = true;                                      // page already serviced (:1481-1483)
+                }
+                if (!done && svc_prot_of(acc) > logical) {                // check_fault_access_permissions :1293-1360
+                    if (acc == ACC_PREFETCH) {
+                        entry_ip = true;
+                        ip_sum += e.num_instances;
+                        done = true;
+                    }
+                    else {
+                        uint32_t cancel = CANCEL_ALL;
+                        service_acc = ACC_COUNT;
+                        if (acc > ACC_READ) {
+                            cancel = CANCEL_WRITE_AND_ATOMIC;
+                            if (e.access_type_mask & (1u << ACC_READ)) {
+                                if (svc_prot_of(ACC_READ) <= logical)
+                                    service_acc = ACC_READ;
+                                else
+                                    cancel = CANCEL_ALL;
+                            }
+                        }
+                        entry_fatal = true;
+                        fl |= UVMTIER_SF_FATAL | (REASON_INVALID_PERMISSIONS << UVMTIER_SF_REASON_SHIFT) |
+                              (cancel << UVMTIER_SF_CANCEL_SHIFT);
+                        if (service_acc == ACC_COUNT)
+                            done = true;
+                    }
+                }
+                if (!done) {
+                    // already authorised: nothing to do (:1518-1522, uvm_va_block.c:2576-2615)
+                    const uint32_t prot = svc_prot_of(service_acc);
+                    const uint32_t ptw = prot == PROT_RWA ? pte2 : (prot == PROT_RW ? pte1 : pte0);
+                    const uint32_t word = __shfl_sync(HW_FULL, ptw, (int)(page >> 5), 16);
+                    if ((word >> (page & 31u)) & 1u) {
+                        fl |= UVMTIER_SF_AUTHORIZED;
+                    }
+                    else {
+                        // new residency: the faulting GPU (harness policy; block_select_processor_residency
+                        // falls through to the faulting processor, uvm_va_block.c:11560-11712)
+                        if ((uint32_t)l == (page >> 5))
+                            newres |= 1u << (page & 31u);
+                        page_faults++;
+                        fl |= UVMTIER_SF_SERVICED | (service_acc << UVMTIER_SF_ACCESS_SHIFT);
+                        first_page = min(first_page, (int)page);
+                        last_page = max(last_page, (int)page);
+                    }
+                }
+                if (entry_ip)
+                    fl |= UVMTIER_SF_INVALID_PREFETCH;
+                if (lane == 0)
+                    entry_flags[base + first + i] = (uint16_t)fl;
+                prev_fatal = entry_fatal;
+                prev_ip = entry_ip;
+                prev_page = page;
+            }
+            if (lane == 0) {
+                if (dup_sum) atomicAdd(&batches[b].num_duplicate_faults, dup_sum);
+                if (ip_sum) atomicAdd(&batches[b].num_invalid_prefetch_faults, ip_sum);
+            }
+
+            // ---- uvm_va_block_service_locked ----
+            uint32_t hint = UVMTIER_ID_INVALID, pf = 0, n_pf = 0, n0 = 0, n1 = 0, nt = 0, run_off = 0, run_cnt = 0;
+            int rf = 0, ro = 0;
+            if (page_faults) {                                            // uniform across the warp
+                rf = first_page;
+                ro = last_page + 1;
+                const bool block_empty = !hw_any(gres | c0 | c1, lane);
+                if (prm.pf_enable) {
+                    const uint32_t flags = UVMTIER_PF_HAS_RESIDENT_MASK | UVMTIER_PF_GPU_VA_SPACE_REGISTERED |
+                                           (block_empty ? UVMTIER_PF_BLOCK_RESIDENT_EMPTY : 0u);
+                    pf = pf_get_hint_block(newres, gres, 0u, 0u, false, grp.block_start, 512, rf, ro, prm.gpu_id, pref, flags,
+                                           16u, prm.pf_threshold, prm.pf_min_faults, &pi, &hint, lane);
+                }
+                if (hint != UVMTIER_ID_INVALID) {                         // uvm_va_block_get_prefetch_hint :11856-11876
+                    n_pf = hw_weight(pf);
+                    newres |= pf;
+                    rf = hw_first_bit(newres, lane);
+                    ro = hw_last_bit(newres, lane) + 1;
+                }
+                else {
+                    pf = 0;
+                }
+                // block_copy_resident_pages :4660-4847: GPU destination, CPU NUMA nodes in ascending order
+                uint32_t todo = newres & ~gres;
+                const uint32_t from0 = todo & c0;
+                todo &= ~from0;
+                const uint32_t from1 = todo & c1;
+                const uint32_t touch = todo & ~from1;                     // resident nowhere: populated + zeroed
+                n0 = hw_weight(from0); n1 = hw_weight(from1); nt = hw_weight(touch);
+                const uint32_t r0 = svc_emit_runs(from0, pf, slot, 0u, NULL, 0u, 0u, lane);
+                const uint32_t r1 = svc_emit_runs(from1, pf, slot, 1u, NULL, 0u, 0u, lane);
+                const uint32_t r2 = svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, NULL, 0u, 0u, lane);
+                run_cnt = r0 + r1 + r2;
+                if (lane == 0 && run_cnt)
+                    run_off = atomicAdd(&counters[0], run_cnt);
+                run_off = __shfl_sync(HW_FULL, run_off, 0);
+                svc_emit_runs(from0, pf, slot, 0u, runs, run_off, prm.run_cap, lane);
+                svc_emit_runs(from1, pf, slot, 1u, runs, run_off + r0, prm.run_cap, lane);
+                svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, runs, run_off + r0 + r1, prm.run_cap, lane);
+                // uvm_va_block_make_resident_finish :5042-5084
+                gres |= newres;
+                c0 &= ~newres;
+                c1 &= ~newres;
+                // service_finish: map the faulting GPU.  compute_new_permission (:11019-11066): the pages now live on
+                // the faulting GPU, which has native atomics on its own memory, and nobody else holds an atomic
+                // mapping of a page that just moved -> READ_WRITE_ATOMIC under a read-write VMA, READ_ONLY otherwise.
+                pte0 |= newres;
+                if (logical == PROT_RWA) {
+                    pte1 |= newres;
+                    pte2 |= newres;
+                }
+            }
+            // ---- record ----
+            if (lane < 16) {
+                uint32_t *rec = (uint32_t *)&service[t];
+                if (l < 8) {
+                    uint32_t v = 0;
+                    switch (l) {
+                        case 0: v = slot; break;
+                        case 1: v = (uint32_t)rf | ((uint32_t)ro << 16); break;
+                        case 2: v = page_faults | (n_pf << 16); break;
+                        case 3: v = n0 | (n1 << 16); break;
+                        case 4: v = nt | (hint << 16); break;
+                        case 5: v = run_off; break;
+                        case 6: v = run_cnt | (b << 16); break;
+                        case 7: v = t - base; break;
+                    }
+                    rec[l] = v;
+                }
+                rec[8 + l] = page_faults ? newres : 0u;
+            }
+        }
+        if (lane < 16) {
+            st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;
+            st.gpu_pte[0][w] = pte0; st.gpu_pte[1][w] = pte1; st.gpu_pte[2][w] = pte2;
+            if (l == 0)
+                st.prefetch_info[slot] = pi;
+        }
+    }
+}
+
+// Runs whose va_block lies in no va_range: service_fault_batch_fatal_notify, one entry at a time
+// (:1656-1698, :2022-2031).  One thread per batch that has such runs; sequential like the reference because an
+// entry inherits the invalid-prefetch flag of the sorted entry before it.
+__global__ void __launch_bounds__(128)
+k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
+                   const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
+                   const uvmtier_instance_ptr_entry_t *__restrict__ tbl, const uint32_t *__restrict__ batch_unmapped,
+                   uint16_t *__restrict__ entry_flags, uvmtier_service_group_t *__restrict__ service)
+{
+    const uint32_t b = blockIdx.x * blockDim.x + threadIdx.x;
+    if (b >= prm.n_batches || !batch_unmapped[b])
+        return;
+    const uint32_t base = b * prm.B, ng = batches[b].num_block_groups;
+    uint32_t ip_sum = 0;
+    for (uint32_t g = 0; g < ng; g++) {
+        const uvmtier_fault_group_t grp = groups[base + g];
+        if (grp.flags & 1u)
+            continue;
+        const uint32_t va_space = tbl[grp.ctx].va_space;
+        if (svc_slot(prm, va_space, grp.block_start) != 0xffffffffu)
+            continue;
+        for (uint32_t i = 0; i < grp.block_faults; i++) {
+            const uint32_t s = grp.first_fault_index + i;
+            const uvmtier_ordered_fault_t e = ordered[base + s];
+            const uint32_t acc = e.fault_access_type & 7u;
+            uint32_t fl = 0;
+            bool dup = false;
+            if (s > 0) {
+                const uvmtier_ordered_fault_t pe = ordered[base + s - 1];
+                dup = tbl[pe.ctx].va_space == va_space && pe.fault_address == e.fault_address;
+            }
+            if (dup && (entry_flags[base + s - 1] & UVMTIER_SF_INVALID_PREFETCH)) {
+                fl |= UVMTIER_SF_INVALID_PREFETCH;
+                ip_sum += e.num_instances;
+            }
+            if (dup)
+                fl |= UVMTIER_SF_DUPLICATE;
+            if (acc == ACC_PREFETCH) {
+                fl |= UVMTIER_SF_INVALID_PREFETCH;
+                ip_sum += e.num_instances;
+            }
+            else {
+                fl |= UVMTIER_SF_FATAL | (REASON_INVALID_ADDRESS << UVMTIER_SF_REASON_SHIFT) | (CANCEL_ALL << UVMTIER_SF_CANCEL_SHIFT);
+            }
+            entry_flags[base + s] = (uint16_t)fl;
+        }
+        uvmtier_service_group_t rec;
+        rec.slot = 0xffffffffu; rec.region_first = 0; rec.region_outer = 0; rec.page_fault_count = 0; rec.prefetch_count = 0;
+        rec.migrated[0] = 0; rec.migrated[1] = 0; rec.first_touch = 0; rec.hint_residency = UVMTIER_ID_INVALID;
+        rec.run_offset = 0; rec.run_count = 0; rec.batch = (uint16_t)b; rec.group = g;
+        for (int k = 0; k < 8; k++) rec.new_residency.bitmap[k] = 0;
+        service[base + g] = rec;
+    }
+    if (ip_sum)
+        atomicAdd(&batches[b].num_invalid_prefetch_faults, ip_sum);
+}
+
+} // namespace uvmtier_k

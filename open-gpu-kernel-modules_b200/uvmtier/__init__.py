@@ -179,6 +179,36 @@ class Context:
                "uvmtier_fetch_preprocess_fault_batches")
         return dict(disp=disp, ordered=ordered, groups=groups, batch=batch, entries=entries, get=new_get.value)
 
+    # ---- (1b) servicing ----
+    def block_state_alloc(self, layout):
+        """uvmtier_block_state_alloc -> DeviceBlockState (device pointers + upload/download helpers)."""
+        return DeviceBlockState(self, layout)
+
+    def service_fault_batches(self, k1, layout, dstate, run_cap=1 << 20):
+        """Full device path on the results of fetch_preprocess_fault_batches (dict k1, host arrays): uploads the
+        sorted view, runs uvmtier_service_fault_batches_device, downloads flags / records / runs / counters."""
+        from .blockstate import COPY_RUN_DT, SERVICE_GROUP_DT
+        from .layouts import BATCH_DT
+        nb = len(k1["batch"])
+        total = len(k1["ordered"])
+        d_ord = self.to_device(k1["ordered"]); d_grp = self.to_device(k1["groups"]); d_bat = self.to_device(k1["batch"])
+        d_flags = self.alloc(total * 2); d_svc = self.alloc(total * 96); d_runs = self.alloc(max(run_cap, 1) * 8)
+        d_cnt = self.alloc(8)
+        try:
+            _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(d_svc), 0, ctypes.c_size_t(total * 96)), "memset")
+            _check(lib().uvmtier_service_fault_batches_device(self._h, ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat),
+                                                              P(layout), ctypes.byref(dstate.ptrs), P(d_flags), P(d_svc),
+                                                              P(d_runs), ctypes.c_uint32(run_cap), P(d_cnt)),
+                   "uvmtier_service_fault_batches_device")
+            self.synchronize()
+            cnt = self.from_device(d_cnt, 2, "<u4")
+            return dict(flags=self.from_device(d_flags, total, "<u2"), service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
+                        runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT), n_runs=int(cnt[0]),
+                        batch=self.from_device(d_bat, nb, BATCH_DT), state=dstate.download())
+        finally:
+            for p in (d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt):
+                self.free(p)
+
     # ---- (2) prefetch ----
     def perf_prefetch_compute_ats(self, faulted, faulted_region, max_prefetch_region, residency=None):
         """uvm_perf_prefetch_compute_ats for n blocks; host arrays in, uint64[n,8] mask out."""
@@ -200,3 +230,39 @@ class Context:
                                                              P(out), P(res)),
                "uvmtier_perf_prefetch_get_hint_va_block")
         return out, res, info
+
+
+class DeviceBlockState:
+    """uvmtier_block_state_t in device memory (one table per context / GPU)."""
+
+    def __init__(self, ctx, layout):
+        from .blockstate import BlockStatePtrs
+        self.ctx = ctx
+        self.layout = layout
+        self.n = int(layout["n_spaces"][0]) * int(layout["blocks_per_space"][0])
+        self.ptrs = BlockStatePtrs()
+        _check(lib().uvmtier_block_state_alloc(ctx.handle, P(layout), ctypes.byref(self.ptrs)), "uvmtier_block_state_alloc")
+
+    def _fields(self):
+        p = self.ptrs
+        return (("gpu_resident", p.gpu_resident), ("cpu_resident0", p.cpu_resident[0]), ("cpu_resident1", p.cpu_resident[1]),
+                ("gpu_pte0", p.gpu_pte[0]), ("gpu_pte1", p.gpu_pte[1]), ("gpu_pte2", p.gpu_pte[2]),
+                ("prefetch_info", p.prefetch_info), ("logical_prot", p.logical_prot), ("preferred_location", p.preferred_location))
+
+    def upload(self, host_state):
+        assert host_state.n == self.n
+        for name, dptr in self._fields():
+            a = np.ascontiguousarray(getattr(host_state, name))
+            _check(lib().uvmtier_memcpy_h2d(self.ctx.handle, ctypes.c_void_p(dptr), P(a), ctypes.c_size_t(a.nbytes)), "h2d")
+
+    def download(self):
+        from .blockstate import HostBlockState
+        h = HostBlockState(self.n)
+        for name, dptr in self._fields():
+            a = getattr(h, name)
+            _check(lib().uvmtier_memcpy_d2h(self.ctx.handle, P(a), ctypes.c_void_p(dptr), ctypes.c_size_t(a.nbytes)), "d2h")
+        return h
+
+    def free(self):
+        if self.ptrs.gpu_resident:
+            lib().uvmtier_block_state_free(self.ctx.handle, ctypes.byref(self.ptrs))

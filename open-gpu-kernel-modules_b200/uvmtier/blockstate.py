@@ -1,0 +1,72 @@
+"""Host-side containers for the per-slot va_block state table and the servicing-pass records
+(numpy mirrors of uvmtier_va_layout_t / uvmtier_block_state_t / uvmtier_service_group_t / uvmtier_copy_run_t)."""
+import ctypes
+
+import numpy as np
+
+VA_LAYOUT_DT = np.dtype([("va_base", "<u8"), ("blocks_per_space", "<u4"), ("n_spaces", "<u4"), ("gpu_id", "<u4"),
+                         ("reserved", "<u4")])
+SERVICE_GROUP_DT = np.dtype([("slot", "<u4"), ("region_first", "<u2"), ("region_outer", "<u2"), ("page_fault_count", "<u2"),
+                             ("prefetch_count", "<u2"), ("migrated", "<u2", 2), ("first_touch", "<u2"), ("hint_residency", "<u2"),
+                             ("run_offset", "<u4"), ("run_count", "<u2"), ("batch", "<u2"), ("group", "<u4"),
+                             ("new_residency", "<u8", 8)])
+COPY_RUN_DT = np.dtype([("slot", "<u4"), ("first_page", "<u2"), ("bits", "<u2")])   # bits: num_pages:10 src:3 prefetch:1
+PREFETCH_INFO_DT = np.dtype([("last_migration_proc_id", "<u2"), ("fault_migrations_to_last_proc", "<u2")])
+assert (VA_LAYOUT_DT.itemsize, SERVICE_GROUP_DT.itemsize, COPY_RUN_DT.itemsize) == (24, 96, 8)
+
+STATE_FIELDS = ("gpu_resident", "cpu_resident0", "cpu_resident1", "gpu_pte0", "gpu_pte1", "gpu_pte2", "prefetch_info",
+                "logical_prot", "preferred_location")
+
+
+class BlockStatePtrs(ctypes.Structure):
+    _fields_ = [("gpu_resident", ctypes.c_void_p), ("cpu_resident", ctypes.c_void_p * 2), ("gpu_pte", ctypes.c_void_p * 3),
+                ("prefetch_info", ctypes.c_void_p), ("logical_prot", ctypes.c_void_p), ("preferred_location", ctypes.c_void_p)]
+
+
+class HostBlockState:
+    """Host copy of the per-slot va_block state (numpy)."""
+
+    def __init__(self, n_slots):
+        z = lambda: np.zeros((n_slots, 8), "<u8")
+        self.n = n_slots
+        self.gpu_resident, self.cpu_resident0, self.cpu_resident1 = z(), z(), z()
+        self.gpu_pte0, self.gpu_pte1, self.gpu_pte2 = z(), z(), z()
+        self.prefetch_info = np.zeros(n_slots, PREFETCH_INFO_DT)
+        self.prefetch_info["last_migration_proc_id"] = 257
+        self.logical_prot = np.full(n_slots, 3, "u1")
+        self.preferred_location = np.full(n_slots, 257, "<u2")
+
+    def copy(self):
+        c = HostBlockState(self.n)
+        for f in STATE_FIELDS:
+            setattr(c, f, getattr(self, f).copy())
+        return c
+
+    def ptrs(self):
+        s = BlockStatePtrs()
+        s.gpu_resident = self.gpu_resident.ctypes.data
+        s.cpu_resident[0] = self.cpu_resident0.ctypes.data
+        s.cpu_resident[1] = self.cpu_resident1.ctypes.data
+        s.gpu_pte[0] = self.gpu_pte0.ctypes.data
+        s.gpu_pte[1] = self.gpu_pte1.ctypes.data
+        s.gpu_pte[2] = self.gpu_pte2.ctypes.data
+        s.prefetch_info = self.prefetch_info.ctypes.data
+        s.logical_prot = self.logical_prot.ctypes.data
+        s.preferred_location = self.preferred_location.ctypes.data
+        return s
+
+    def assert_equal(self, other, what=""):
+        for f in STATE_FIELDS:
+            a, b = getattr(self, f), getattr(other, f)
+            if not np.array_equal(a, b):
+                bad = np.nonzero((a != b).reshape(self.n, -1).any(axis=1))[0] if a.dtype.names is None else np.nonzero(a != b)[0]
+                raise AssertionError("%s state.%s differs at slots %s" % (what, f, bad[:8]))
+
+
+def make_layout(lay, gpu_id=1):
+    v = np.zeros(1, VA_LAYOUT_DT)
+    v["va_base"] = lay["va_base"]
+    v["blocks_per_space"] = lay["blocks_per_space"]
+    v["n_spaces"] = lay["n_spaces"]
+    v["gpu_id"] = gpu_id
+    return v

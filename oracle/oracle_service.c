@@ -1,0 +1,297 @@
+/*
+ * oracle_service.c -- TEST INFRASTRUCTURE ONLY: CPU restatement of the per-va_block servicing of a
+ * sorted fault batch (UVM = kernel-open/nvidia-uvm):
+ *   F4  service_fault_batch / _dispatch / _block_locked      uvm_gpu_replayable_faults.c:1375-1597,1946-2035,2232-2377
+ *       check_fault_access_permissions                        :1293-1360
+ *   P4  uvm_va_block_get_prefetch_hint                        uvm_va_block.c:11828-11881 (calls oracle_prefetch.c)
+ *   M1-M4 make_resident mask algebra                          uvm_va_block.c:4660-4847 (copy lists), :4990-5084 (state)
+ *       mapping after service                                 uvm_va_block.c:11019-11066, 12063-12080
+ *
+ * Harness policy, stated once here and in DESIGN.md: one faulting GPU per state table,
+ * no read duplication, no thrashing, no accessed_by, every range migratable, no range groups; the
+ * destination of every serviced fault is the faulting GPU (block_select_processor_residency falls through
+ * to `return processor_id`, uvm_va_block.c:11560-11712, when the page is not resident on it); CPU memory
+ * has two NUMA nodes (0 = DRAM, 1 = CXL); both tiers and HBM back a va_block contiguously.
+ *
+ * Pinning: no known-answer vectors exist in the reference for this stage.  The batch-level loop and the
+ * permission logic are additionally pinned against the reference's own code where it compiles
+ * (oracle/_ref/libref_service.so, see ref_service_glue.c); the prefetch leg inside is the KAT-pinned one.
+ * Batches are applied in trace order, exactly like uvm_parent_gpu_service_replayable_faults (:2906-2960).
+ */
+#include "oracle_common.h"
+#include "ref_api.h"
+
+enum { ACC_PREFETCH = 0, ACC_READ, ACC_WRITE, ACC_ATOMIC_WEAK, ACC_ATOMIC_STRONG, ACC_COUNT };
+enum { PROT_NONE = 0, PROT_RO = 1, PROT_RW = 2, PROT_RWA = 3 };
+enum { REASON_INVALID_ADDRESS = 1, REASON_INVALID_PERMISSIONS = 2 };   /* UvmEventFatalReason, uvm_types.h:514-529 */
+enum { CANCEL_ALL = 0, CANCEL_WRITE_AND_ATOMIC = 1 };                  /* uvm_hal_types.h:262-271 */
+
+void oracle_prefetch_get_hint_va_block(size_t n, const ref_prefetch_block_t *blk, const uint64_t *resident,
+                                       const uint64_t *faulted, const uint64_t *thrashing,
+                                       const uint64_t *cpu_read_mapped, ref_prefetch_info_t *info,
+                                       uint64_t *out_mask, uint32_t *out_residency);
+
+/* uvm_fault_access_type_to_prot, uvm_hal_types.h:522-537 */
+static unsigned prot_of(unsigned acc)
+{
+    if (acc == ACC_ATOMIC_STRONG) return PROT_RWA;
+    if (acc == ACC_ATOMIC_WEAK || acc == ACC_WRITE) return PROT_RW;
+    return PROT_RO;
+}
+
+/* uvm_va_block_check_logical_permissions for a GPU fault on a migratable managed range
+ * (uvm_va_block.c:12361-12416 with uvm_enable_builtin_tests set, as in the reference's own test runs) */
+static bool logical_ok(unsigned logical_prot, unsigned acc) { return prot_of(acc) <= logical_prot; }
+
+static void mask_ptr_load(or_mask_t *m, uint64_t *base, uint32_t slot) { or_load(m, base + 8 * (size_t)slot); }
+static void mask_ptr_store(uint64_t *base, uint32_t slot, const or_mask_t *m) { or_store(base + 8 * (size_t)slot, m); }
+
+/* Emits the copy runs of `pages` from source `src`: consecutive pages with the same cause form one run
+ * (block_copy_resident_pages_between, uvm_va_block.c:4143-4335, both sides block-contiguous). */
+static uint32_t emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uint32_t slot, unsigned src,
+                          ref_copy_run_t *runs, uint32_t at, uint32_t cap)
+{
+    unsigned p = 0;
+    uint32_t n = 0;
+    while (p < OR_PAGES) {
+        unsigned q, cause;
+        if (!or_test(pages, p)) { p++; continue; }
+        cause = or_test(prefetch, p);
+        for (q = p + 1; q < OR_PAGES && or_test(pages, q) && (unsigned)or_test(prefetch, q) == cause; q++) {}
+        if (at + n < cap) {
+            ref_copy_run_t *r = &runs[at + n];
+            r->slot = slot; r->first_page = (uint16_t)p; r->num_pages = q - p; r->src = src; r->prefetch = cause; r->pad = 0;
+        }
+        n++;
+        p = q;
+    }
+    return n;
+}
+
+/*
+ * Services every batch in order.  ordered/groups/batch: the product-layout outputs of the preprocess
+ * stage, batch b at offset b * max_batch_size.  Outputs:
+ *   entry_flags[b*B + s]  REF_SF_* of sorted entry s
+ *   svc[]                 one record per serviced-or-examined run, in (batch, group) order; returns count
+ *   runs[]                copy runs, in record order (run_offset/run_count index into it)
+ *   batch[].num_duplicate_faults / num_invalid_prefetch_faults are accumulated
+ * *n_runs receives the number of runs needed (may exceed run_cap: then only run_cap were written).
+ */
+uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_size, const ref_ordered_fault_t *ordered,
+                                      const ref_fault_group_t *groups, ref_fault_batch_t *batch,
+                                      const ref_instance_ptr_entry_t *tbl, const ref_va_layout_t *lay,
+                                      const ref_block_state_t *st, unsigned pf_enable, unsigned pf_threshold,
+                                      unsigned pf_min_faults, uint16_t *entry_flags, ref_service_group_t *svc,
+                                      ref_copy_run_t *runs, uint32_t run_cap, uint32_t *n_runs)
+{
+    uint32_t b, nsvc = 0, nrun = 0;
+    extern int oracle_prefetch_init(unsigned, unsigned, unsigned);
+    oracle_prefetch_init(pf_enable, pf_threshold, pf_min_faults);
+
+    for (b = 0; b < n_batches; b++) {
+        const size_t base = (size_t)b * max_batch_size;
+        uint32_t g;
+        if (batch[b].status != 0)
+            continue;                                   /* batch is refetched, nothing serviced (:2946) */
+        for (g = 0; g < batch[b].num_block_groups; g++) {
+            const ref_fault_group_t *grp = &groups[base + g];
+            const uint32_t first = grp->first_fault_index, count = grp->block_faults;
+            const uint32_t va_space = tbl[grp->ctx].va_space;
+            ref_service_group_t *rec;
+            uint64_t off;
+            uint32_t slot = 0xFFFFFFFFu, i, page_faults = 0;
+            unsigned first_page = OR_PAGES, last_page = 0, logical;
+            or_mask_t newres, gpu_res, pte[3];
+            bool prev_fatal = false, prev_invalid_prefetch = false;
+
+            for (i = 0; i < count; i++)
+                entry_flags[base + first + i] = 0;
+            if (grp->flags & 1)
+                continue;                               /* fatal fault type: skipped by service_fault_batch (:2294-2303) */
+
+            rec = &svc[nsvc++];
+            memset(rec, 0, sizeof(*rec));
+            rec->batch = (uint16_t)b; rec->group = g; rec->hint_residency = 257; rec->run_offset = nrun;
+            off = grp->block_start - lay->va_base;
+            if (grp->block_start >= lay->va_base && (off >> 21) < lay->blocks_per_space && va_space < lay->n_spaces)
+                slot = va_space * lay->blocks_per_space + (uint32_t)(off >> 21);
+            rec->slot = slot;
+
+            if (slot == 0xFFFFFFFFu) {
+                /* no va_range: service_fault_batch_fatal_notify one entry at a time (:1656-1698, :2022-2031) */
+                for (i = 0; i < count; i++) {
+                    const ref_ordered_fault_t *e = &ordered[base + first + i];
+                    const unsigned acc = e->fault_access_type & 7;
+                    uint16_t fl = 0;
+                    bool dup = false;
+                    if (first + i > 0) {
+                        const ref_ordered_fault_t *pe = &ordered[base + first + i - 1];
+                        dup = tbl[pe->ctx].va_space == va_space && pe->fault_address == e->fault_address;
+                    }
+                    if (dup && (entry_flags[base + first + i - 1] & REF_SF_INVALID_PREFETCH)) {
+                        fl |= REF_SF_INVALID_PREFETCH;                   /* fault_entry_duplicate_flags :1257-1272 */
+                        batch[b].num_invalid_prefetch_faults += e->num_instances;
+                    }
+                    if (dup)
+                        fl |= REF_SF_DUPLICATE;
+                    if (acc == ACC_PREFETCH) {
+                        fl |= REF_SF_INVALID_PREFETCH;
+                        batch[b].num_invalid_prefetch_faults += e->num_instances;
+                    }
+                    else {
+                        fl |= REF_SF_FATAL | (REASON_INVALID_ADDRESS << REF_SF_REASON_SHIFT) | (CANCEL_ALL << REF_SF_CANCEL_SHIFT);
+                    }
+                    entry_flags[base + first + i] = fl;
+                }
+                continue;
+            }
+
+            logical = st->logical_prot[slot];
+            mask_ptr_load(&gpu_res, st->gpu_resident, slot);
+            for (i = 0; i < 3; i++) mask_ptr_load(&pte[i], st->gpu_pte[i], slot);
+            or_zero(&newres);
+
+            /* ---- service_fault_batch_block_locked :1433-1580 ---- */
+            for (i = 0; i < count; i++) {
+                const ref_ordered_fault_t *e = &ordered[base + first + i];
+                const unsigned acc = e->fault_access_type & 7;
+                const unsigned page = (unsigned)((e->fault_address - grp->block_start) >> 12);
+                unsigned service_acc = acc;
+                uint16_t fl = 0;
+                bool dup = false, entry_fatal = false, entry_invalid_prefetch = false;
+
+                if (i > 0)
+                    dup = ordered[base + first + i - 1].fault_address == e->fault_address;   /* same va_space inside a run */
+                batch[b].num_duplicate_faults += dup ? e->num_instances : (uint32_t)e->num_instances - 1;  /* :1200-1203 */
+                if (dup) {
+                    fl |= REF_SF_DUPLICATE;
+                    if (prev_invalid_prefetch) {                                             /* :1264-1267 */
+                        entry_invalid_prefetch = true;
+                        batch[b].num_invalid_prefetch_faults += e->num_instances;
+                    }
+                    if (!prev_fatal)
+                        goto next;                                                           /* :1481-1483 */
+                }
+
+                /* check_fault_access_permissions :1293-1360 */
+                if (!logical_ok(logical, acc)) {
+                    if (acc == ACC_PREFETCH) {
+                        entry_invalid_prefetch = true;
+                        batch[b].num_invalid_prefetch_faults += e->num_instances;
+                        goto next;
+                    }
+                    else {
+                        unsigned cancel = CANCEL_ALL;
+                        service_acc = ACC_COUNT;
+                        if (acc > ACC_READ) {
+                            cancel = CANCEL_WRITE_AND_ATOMIC;
+                            if (e->access_type_mask & (1u << ACC_READ)) {
+                                if (logical_ok(logical, ACC_READ))
+                                    service_acc = ACC_READ;
+                                else
+                                    cancel = CANCEL_ALL;
+                            }
+                        }
+                        entry_fatal = true;
+                        fl |= REF_SF_FATAL | (REASON_INVALID_PERMISSIONS << REF_SF_REASON_SHIFT) | (cancel << REF_SF_CANCEL_SHIFT);
+                        if (service_acc == ACC_COUNT)
+                            goto next;
+                    }
+                }
+                /* already authorised -> nothing to do (:1518-1522; uvm_va_block.c:2576-2615) */
+                if (or_test(&pte[prot_of(service_acc) - 1], page)) {
+                    fl |= REF_SF_AUTHORIZED;
+                    goto next;
+                }
+                /* new residency = the faulting GPU (harness policy); :1560-1579 */
+                or_set(&newres, page);
+                page_faults++;
+                fl |= REF_SF_SERVICED | (service_acc << REF_SF_ACCESS_SHIFT);
+                if (page < first_page) first_page = page;
+                if (page > last_page) last_page = page;
+            next:
+                if (entry_invalid_prefetch) fl |= REF_SF_INVALID_PREFETCH;
+                entry_flags[base + first + i] = fl;
+                prev_fatal = entry_fatal;
+                prev_invalid_prefetch = entry_invalid_prefetch;
+            }
+
+            rec->page_fault_count = (uint16_t)page_faults;
+            if (!page_faults)
+                continue;
+
+            /* ---- uvm_va_block_service_locked, uvm_va_block.c:12307-12359 ---- */
+            {
+                or_mask_t pf_mask, cpu0, cpu1, todo, from0, from1, touch, any_cpu;
+                ref_prefetch_block_t pb;
+                uint32_t hint;
+                unsigned rf = first_page, ro = last_page + 1, p;
+
+                /* get_prefetch_hint :11828-11881: exactly one destination processor */
+                memset(&pb, 0, sizeof(pb));
+                pb.start = grp->block_start; pb.big_page_size = 65536; pb.num_pages = 512;
+                pb.faulted_first = (uint16_t)rf; pb.faulted_outer = (uint16_t)ro;
+                pb.new_residency = (uint16_t)lay->gpu_id; pb.preferred_location = st->preferred_location[slot];
+                mask_ptr_load(&cpu0, st->cpu_resident[0], slot);
+                mask_ptr_load(&cpu1, st->cpu_resident[1], slot);
+                or_or(&any_cpu, &cpu0, &cpu1);
+                pb.flags = REF_PF_HAS_RESIDENT_MASK | REF_PF_GPU_VA_SPACE_REGISTERED |
+                           ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0);
+                oracle_prefetch_get_hint_va_block(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot],
+                                                  pf_mask.w, &hint);
+                rec->hint_residency = (uint16_t)hint;
+                if (hint != 257) {
+                    or_or(&newres, &newres, &pf_mask);
+                    for (p = 0; p < OR_PAGES; p++) if (or_test(&newres, p)) { rf = p; break; }
+                    for (p = OR_PAGES; p-- > 0;) if (or_test(&newres, p)) { ro = p + 1; break; }
+                    rec->prefetch_count = (uint16_t)or_weight(&pf_mask);
+                }
+                else {
+                    or_zero(&pf_mask);
+                }
+                rec->region_first = (uint16_t)rf; rec->region_outer = (uint16_t)ro;
+                or_store(rec->new_residency, &newres);
+
+                /* make_resident_copy: block_copy_resident_pages :4660-4847, GPU destination, CPU nodes as sources */
+                or_andnot(&todo, &newres, &gpu_res);                 /* :4687-4690 */
+                or_and(&from0, &todo, &cpu0);                        /* node 0 first (for_each_possible_uvm_node) */
+                or_andnot(&todo, &todo, &from0);
+                or_and(&from1, &todo, &cpu1);
+                or_andnot(&touch, &todo, &from1);                    /* resident nowhere: populated + zeroed at the destination */
+                rec->migrated[0] = (uint16_t)or_weight(&from0);
+                rec->migrated[1] = (uint16_t)or_weight(&from1);
+                rec->first_touch = (uint16_t)or_weight(&touch);
+                {
+                    uint32_t k = 0;
+                    k += emit_runs(&from0, &pf_mask, slot, 0, runs, nrun + k, run_cap);
+                    k += emit_runs(&from1, &pf_mask, slot, 1, runs, nrun + k, run_cap);
+                    k += emit_runs(&touch, &pf_mask, slot, 7, runs, nrun + k, run_cap);
+                    rec->run_count = (uint16_t)k;
+                    nrun += k;
+                }
+                /* make_resident_finish :5042-5084: dst |= migrated | first touch; everyone else loses the region's pages */
+                or_or(&gpu_res, &gpu_res, &newres);
+                or_andnot(&cpu0, &cpu0, &newres);
+                or_andnot(&cpu1, &cpu1, &newres);
+                mask_ptr_store(st->gpu_resident, slot, &gpu_res);
+                mask_ptr_store(st->cpu_resident[0], slot, &cpu0);
+                mask_ptr_store(st->cpu_resident[1], slot, &cpu1);
+
+                /* service_finish :12063-12302: map the faulting GPU.  compute_new_permission (:11019-11066): the
+                 * page is now resident on the faulting GPU, which has native atomics on its own memory, and no
+                 * other faultable processor holds an atomic mapping of a page that just moved, so a read-write
+                 * VMA maps READ_WRITE_ATOMIC whatever the access type; a read-only VMA maps READ_ONLY. */
+                {
+                    const unsigned new_prot = logical == PROT_RWA ? PROT_RWA : PROT_RO;
+                    for (i = 0; i < new_prot; i++) {
+                        or_or(&pte[i], &pte[i], &newres);
+                        mask_ptr_store(st->gpu_pte[i], slot, &pte[i]);
+                    }
+                }
+            }
+        }
+    }
+    if (n_runs)
+        *n_runs = nrun;
+    return nsvc;
+}

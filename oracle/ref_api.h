@@ -95,4 +95,80 @@ typedef struct {
     uint32_t num_block_groups;
 } ref_fault_batch_t;                /* 32 bytes */
 
+/* ---------------- service pass (stage C/D/E) ---------------- */
+
+/* one element of the sorted view and one va_block run, same layout as the product's
+ * uvmtier_ordered_fault_t / uvmtier_fault_group_t */
+typedef struct {
+    uint64_t fault_address;
+    uint16_t fault_index;
+    uint16_t ctx;
+    uint16_t num_instances;
+    uint8_t access_type_mask;
+    uint8_t fault_access_type;      /* low 3 bits; 0x80 = fatal */
+} ref_ordered_fault_t;
+typedef struct {
+    uint64_t block_start;
+    uint16_t ctx;
+    uint16_t first_fault_index;
+    uint16_t block_faults;
+    uint16_t flags;
+} ref_fault_group_t;
+
+/* VA layout of the harness: va_space s owns [va_base, va_base + blocks_per_space * 2MB); its va_block
+ * b has state slot s * blocks_per_space + b (stand-in for the va_range tree) */
+typedef struct {
+    uint64_t va_base;
+    uint32_t blocks_per_space;
+    uint32_t n_spaces;
+    uint32_t gpu_id;                /* uvm_gpu_id_t value of the faulting GPU (this context) */
+    uint32_t reserved;
+} ref_va_layout_t;
+
+/* per-slot va_block state, SoA (host pointers here; device pointers in the product) */
+typedef struct {
+    uint64_t *gpu_resident;         /* gpu_state->resident                 [n_slots][8] */
+    uint64_t *cpu_resident[2];      /* cpu node_state->resident, node 0 = DRAM, 1 = CXL */
+    uint64_t *gpu_pte[3];           /* gpu_state->pte_bits[READ, WRITE, ATOMIC] */
+    ref_prefetch_info_t *prefetch_info;
+    uint8_t *logical_prot;          /* compute_logical_prot(): 0 NONE, 1 READ_ONLY, 3 READ_WRITE_ATOMIC */
+    uint16_t *preferred_location;   /* policy->preferred_location, 257 = none */
+} ref_block_state_t;
+
+#define REF_SF_SERVICED         0x0001
+#define REF_SF_DUPLICATE        0x0002
+#define REF_SF_FATAL            0x0004
+#define REF_SF_INVALID_PREFETCH 0x0008
+#define REF_SF_AUTHORIZED       0x0010
+#define REF_SF_ACCESS_SHIFT     5       /* 3 bits: service access type */
+#define REF_SF_REASON_SHIFT     8       /* 3 bits: UvmEventFatalReason */
+#define REF_SF_CANCEL_SHIFT     12      /* 1 bit: uvm_fault_cancel_va_mode_t */
+
+/* what servicing one va_block run did (service_fault_batch_block_locked + uvm_va_block_service_locked) */
+typedef struct {
+    uint32_t slot;                  /* block state slot, 0xFFFFFFFF = address outside every va_range */
+    uint16_t region_first, region_outer;   /* service region after the prefetch hint (:11875) */
+    uint16_t page_fault_count;      /* pages set by faults */
+    uint16_t prefetch_count;        /* pages added by the hint */
+    uint16_t migrated[2];           /* pages copied from CPU node 0 / 1 */
+    uint16_t first_touch;           /* pages populated (zeroed) at the destination */
+    uint16_t hint_residency;
+    uint32_t run_offset;            /* first copy run of this group in the run array */
+    uint16_t run_count;
+    uint16_t batch;
+    uint32_t group;                 /* index of the run inside its batch */
+    uint64_t new_residency[8];      /* per_processor_masks[gpu].new_residency after the hint */
+} ref_service_group_t;              /* 96 bytes */
+
+/* one contiguous page run to move: block_copy_resident_pages_between coalesces consecutive pages
+ * when both sides are block-contiguous (uvm_va_block.c:4278-4288) */
+typedef struct {
+    uint32_t slot;
+    uint16_t first_page;
+    uint16_t num_pages : 10;
+    uint16_t src : 3;               /* 0 CPU node 0, 1 CPU node 1, 7 = zero-fill (first touch) */
+    uint16_t prefetch : 1;          /* run cause is PREFETCH (runs also split where the cause changes) */
+    uint16_t pad : 2;
+} ref_copy_run_t;                   /* 8 bytes */
+
 #endif

@@ -1,0 +1,138 @@
+"""CPU tests of the servicing pass (stage C/D/E): the product's kernels under the SIMT emulator vs the oracle,
+plus directed cases for the reference's rules (duplicates, permissions, already-authorised, unmapped addresses,
+first touch, batch order across runs of the same va_block)."""
+import numpy as np
+import pytest
+
+import faultlib as F
+import servicelib as S
+import uvmtier_testlib as T
+from uvmtier import tracegen as TG
+
+SMALL_VA = 64 << 21      # 64 va_blocks in total: many batches hit the same block
+
+
+def _k1(pk, gp, tbl):
+    return F.run_fetch_preprocess_simt(T.load_simt(), pk, gp, tbl)
+
+
+def _both(pk, gp, tbl, lay, st0, pf=(1, 51, 1)):
+    k1 = _k1(pk, gp, tbl)
+    layout = S.make_layout(lay)
+    want = S.run_service_oracle(T.load_oracle(), k1, gp, tbl, layout, st0, pf)
+    got = S.run_service_simt(T.load_simt(), k1, gp, tbl, layout, st0, pf)
+    return k1, want, got
+
+
+@pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
+@pytest.mark.parametrize("B", [256, 48])
+def test_simt_service_matches_oracle(dist, B):
+    pk, tbl, lay = TG.fault_trace(1200, 21, dist, 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(B)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 4)
+    _, want, got = _both(pk, gp, tbl, lay, st0)
+    S.assert_service_equal(want, got, B, "%s %d" % (dist, B))
+    S.check_service_invariants(got, st0)
+
+
+def test_block_touched_by_more_than_32_batches_is_applied_in_batch_order():
+    pk, tbl, lay = TG.fault_trace(1600, 3, "hotset", 1, total_va_bytes=8 << 21)
+    gp = TG.gpu_params(32)                                   # 50 batches over 8 blocks
+    st0 = S.random_state(8, 9, populated=0.5, ro_frac=0, none_frac=0)
+    _, want, got = _both(pk, gp, tbl, lay, st0)
+    per_slot = np.bincount(want["records"]["slot"], minlength=8)
+    assert per_slot.max() > 32
+    S.assert_service_equal(want, got, 32)
+
+
+def test_directed_rules():
+    """One va_block, hand-built faults: duplicate counting, read-only VMA, already mapped page, first touch."""
+    tbl = TG.instance_ptr_table(1)
+    lay = dict(va_base=TG.VA_BASE, blocks_per_space=2, n_spaces=1)
+    A = lambda page, blk=0: TG.VA_BASE + (blk << 21) + (page << 12)
+    R, W, AT, PF = TG.HW_VIRT_READ, TG.HW_VIRT_WRITE, TG.HW_VIRT_ATOMIC_STRONG, TG.HW_VIRT_PREFETCH
+    #            page  access  gpc client
+    rows = [(5, R, 0, 0), (5, W, 1, 0),          # same page, different uTLBs, W first in sort order; R is the duplicate
+            (9, W, 0, 1),                        # already mapped RW -> authorised
+            (40, R, 0, 2),                       # resident on CPU node 1 -> copy run from CXL
+            (41, R, 0, 3),                       # resident on CPU node 0 -> copy run from DRAM
+            (100, PF, 0, 4),                     # prefetch access, page resident nowhere -> first touch
+            (3, W, 0, 5, 1), (3, R, 1, 5, 1), (7, PF, 0, 6, 1), (8, AT, 0, 7, 1)]   # block 1 is read-only
+    addr = np.array([A(r[0], r[4] if len(r) > 4 else 0) for r in rows], np.uint64)
+    pk = TG.encode_packets(np.full(len(rows), tbl["instance_ptr"][0]), addr, [r[1] for r in rows], [r[2] for r in rows],
+                           [TG.T1_CLIENTS[r[3]] for r in rows], np.arange(len(rows)) + 100)
+    gp = TG.gpu_params(256)
+    st0 = S.HostBlockState(2)
+    bit = lambda m, s, p: m.__setitem__((s, p // 64), m[s, p // 64] | np.uint64(1 << (p % 64)))
+    for m in (st0.gpu_resident, st0.gpu_pte0, st0.gpu_pte1):
+        bit(m, 0, 9)
+    bit(st0.cpu_resident1, 0, 40); bit(st0.cpu_resident0, 0, 41)
+    st0.logical_prot[1] = 1
+    k1, want, got = _both(pk, gp, tbl, lay, st0, pf=(0, 51, 1))     # prefetch heuristic off: isolate stage C/E
+    S.assert_service_equal(want, got, 256)
+    o, fl = k1["ordered_rec"], want["flags"]
+    page_of = lambda i: int((int(o["fault_address"][i]) - TG.VA_BASE) >> 12)
+    byp = {page_of(i): [] for i in range(len(rows))}
+    for i in range(len(rows)):
+        byp[page_of(i)].append(int(fl[i]))
+    assert byp[5] == [S_FL(serviced=1, acc=2), S_FL(dup=1)]
+    assert byp[9] == [S_FL(auth=1)]
+    assert byp[40] == [S_FL(serviced=1, acc=1)] and byp[41] == [S_FL(serviced=1, acc=1)]
+    assert byp[100] == [S_FL(serviced=1, acc=0)]
+    # read-only block 1, page 3: the READ was coalesced into the WRITE at fetch time (batch-wide rule), so ONE entry
+    # with access_type_mask {READ, WRITE}: the write is fatal (cancel WRITE_AND_ATOMIC, reason permissions) but the
+    # pending read instance is still serviced as a READ (check_fault_access_permissions :1326-1349)
+    assert byp[512 + 3] == [S_FL(serviced=1, fatal=1, acc=1, reason=2, cancel=1)]
+    assert byp[512 + 7] == [S_FL(serviced=1, acc=0)]
+    assert byp[512 + 8] == [S_FL(fatal=1, reason=2, cancel=1)]
+    assert int(want["batch"]["num_duplicate_faults"][0]) == 2
+    rec = want["records"]
+    assert len(rec) == 2 and list(rec["page_fault_count"]) == [4, 2]
+    assert list(rec["migrated"][0]) == [1, 1] and rec["first_touch"][0] == 2 and rec["first_touch"][1] == 2
+    st = want["state"]
+    assert T.bool_from_masks(st.gpu_pte2)[0, [5, 40, 41, 100]].all()          # read-write VMA -> READ_WRITE_ATOMIC
+    assert T.bool_from_masks(st.gpu_pte0)[1, [3, 7]].all() and not T.bool_from_masks(st.gpu_pte1)[1].any()
+    assert not T.bool_from_masks(st.cpu_resident0)[0, 41] and not T.bool_from_masks(st.cpu_resident1)[0, 40]
+
+
+def S_FL(serviced=0, dup=0, fatal=0, ip=0, auth=0, acc=0, reason=0, cancel=0):
+    return serviced | dup << 1 | fatal << 2 | ip << 3 | auth << 4 | (acc << 5 if serviced else 0) | reason << 8 | cancel << 12
+
+
+def test_addresses_outside_every_va_range():
+    """service_fault_batch_dispatch -> service_fault_batch_fatal_notify: fatal (invalid address) or, for a
+    prefetch access, invalid prefetch; nothing is serviced and no state changes."""
+    pk, tbl, lay = TG.fault_trace(700, 8, "uniform", 2, total_va_bytes=SMALL_VA)
+    out = np.arange(700) % 5 == 2
+    pk[out, 3] |= 0x40                       # far above the managed range
+    gp = TG.gpu_params(128)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 6)
+    k1, want, got = _both(pk, gp, tbl, lay, st0)
+    S.assert_service_equal(want, got, 128)
+    fl = want["flags"]
+    assert ((fl >> 8) & 7 == 1).sum() > 50                     # UvmEventFatalReasonInvalidAddress
+    assert int(want["batch"]["num_invalid_prefetch_faults"].sum()) > 0
+    assert (want["records"]["slot"] == 0xFFFFFFFF).sum() > 50
+
+
+def test_fatal_fault_types_are_skipped_and_failed_batches_not_serviced():
+    pk, tbl, lay = TG.fault_trace(600, 5, "adversarial", 2, total_va_bytes=SMALL_VA)
+    fatal = np.arange(600) % 7 == 3
+    pk[fatal, 7] = (pk[fatal, 7] & ~np.uint32(0x1F)) | TG.HW_FAULT_TYPE_PDE_SIZE
+    pk[fatal, 3] |= 0x100
+    pk[400, 1] ^= 0x5                        # stale channel in the second batch -> whole batch refetched
+    gp = TG.gpu_params(256)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 2)
+    k1, want, got = _both(pk, gp, tbl, lay, st0)
+    assert list(k1["batch"]["status"]) == [0, F.NV_WARN_MORE_PROCESSING_REQUIRED, 0]
+    S.assert_service_equal(want, got, 256)
+    assert (want["records"]["batch"] != 1).all()
+
+
+@pytest.mark.parametrize("thr", [1, 75, 100])
+def test_prefetch_threshold_flows_into_service(thr):
+    pk, tbl, lay = TG.fault_trace(800, 13, "stream", 1, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(256)
+    st0 = S.random_state(lay["blocks_per_space"], 8, ro_frac=0, none_frac=0)
+    _, want, got = _both(pk, gp, tbl, lay, st0, pf=(1, thr, 1))
+    S.assert_service_equal(want, got, 256, "thr %d" % thr)

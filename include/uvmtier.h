@@ -448,6 +448,78 @@ NV_STATUS uvmtier_perf_prefetch_get_hint_va_block(uvmtier_ctx_t *ctx, size_t n_b
                                                   uvmtier_page_mask_t *h_out_prefetch_mask,
                                                   uint32_t *h_out_residency);
 
+/* ------------------------------------------------------------------------------------------ */
+/* (3) Page-list migration between tiers -- UVM/uvm_va_block.c block_copy_* / make_resident    */
+/* ------------------------------------------------------------------------------------------ */
+
+/* Memory tiers of one context.  A tier is a contiguous arena; a va_block slot s is backed in every tier at
+ * byte offset s * 2 MB (block-contiguous backing: is_block_phys_contig() true on both sides, so consecutive
+ * pages coalesce into one copy, UVM/uvm_va_block.c:4278-4288). */
+#define UVMTIER_TIER_HBM    0u   /* this context's GPU memory                                              */
+#define UVMTIER_TIER_DRAM   1u   /* host DRAM (CPU NUMA node with CPUs), pinned + mapped                    */
+#define UVMTIER_TIER_CXL    2u   /* CXL memory = CPU-less NUMA node; emulated on a DRAM node when absent    */
+#define UVMTIER_TIER_PEER0  8u   /* UVMTIER_TIER_PEER0 + i: HBM of another GPU, mapped through NVLink/NVSwitch */
+#define UVMTIER_MAX_TIERS   24u
+
+typedef struct {
+    uint64_t bytes;
+    void    *device_ptr;         /* address the kernels use                                                */
+    void    *host_ptr;           /* CPU address (host tiers), NULL for HBM / peer                          */
+    int32_t  numa_node;          /* node the pages were bound to, -1 = not bound                           */
+    uint32_t flags;              /* UVMTIER_TIERF_*                                                        */
+} uvmtier_tier_info_t;
+#define UVMTIER_TIERF_CXL_EMULATED 0x1u  /* no CPU-less NUMA node on this machine: a DRAM node stands in   */
+#define UVMTIER_TIERF_HUGEPAGES    0x2u
+#define UVMTIER_TIERF_EXTERNAL     0x4u  /* memory owned by the caller (uvmtier_tier_register)             */
+
+/* NUMA probe of /sys/devices/system/node: out_dram_node = a node with CPUs and memory, out_cxl_node = a
+ * node with memory and no CPUs (-1 if none).  Returns the number of online nodes. */
+int uvmtier_numa_probe(int *out_dram_node, int *out_cxl_node);
+
+/* Creates tier `tier` with `bytes` of backing store.  HBM: cudaMalloc.  DRAM/CXL: anonymous mmap bound to
+ * `numa_node` (-1: probe; the reference allocates with alloc_pages_node(nid, __GFP_THISNODE),
+ * UVM/uvm_pmm_sysmem.c:829-853) and registered with CUDA as mapped pinned memory so that SMs can address it. */
+NV_STATUS uvmtier_tier_create(uvmtier_ctx_t *ctx, uint32_t tier, uint64_t bytes, int numa_node, uvmtier_tier_info_t *out);
+/* Registers caller-owned memory as a tier: device_ptr must be addressable by this context's GPU (peer HBM
+ * after cudaDeviceEnablePeerAccess, or host memory already registered as mapped). */
+NV_STATUS uvmtier_tier_register(uvmtier_ctx_t *ctx, uint32_t tier, void *device_ptr, void *host_ptr, uint64_t bytes);
+/* Maps the HBM tier of `peer_ctx` (another GPU of this process) as tier UVMTIER_TIER_PEER0 + peer_index of
+ * `ctx`, enabling peer access both ways (the reference: UVM_GPU_LINK_NVLINK_5 peer apertures, UVM/uvm_gpu.h:611-640). */
+NV_STATUS uvmtier_tier_map_peer(uvmtier_ctx_t *ctx, uint32_t peer_index, uvmtier_ctx_t *peer_ctx);
+NV_STATUS uvmtier_tier_info(uvmtier_ctx_t *ctx, uint32_t tier, uvmtier_tier_info_t *out);
+NV_STATUS uvmtier_tier_destroy(uvmtier_ctx_t *ctx, uint32_t tier);
+
+/* The copy primitive: replaces block_copy_pages -> block_copy_push -> ce_hal->memcopy
+ * (UVM/uvm_va_block.c:3863-3991, UVM/uvm_volta_ce.c:119-183) and, for CPU<->CPU, the kmap+memcpy page loop
+ * (:3972-3984).  Copies n pages of page_size bytes (4096, 65536 or 2097152): page i from
+ * src_tier + d_src_off[i] to dst_tier + d_dst_off[i].  Offsets are bytes, page_size aligned.  SM-driven:
+ * persistent CTAs stage 4 KB pieces through shared memory with 1-D TMA bulk copies.
+ * method: 0 = TMA bulk pipeline (default), 1 = plain 16-byte ld/st (for comparison). */
+NV_STATUS uvmtier_copy_page_list_device(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, size_t n,
+                                        const uint64_t *d_dst_off, const uint64_t *d_src_off, uint32_t page_size,
+                                        int method);
+/* Host-list form (lists are copied to the device first). */
+NV_STATUS uvmtier_copy_page_list(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, size_t n,
+                                 const uint64_t *h_dst_off, const uint64_t *h_src_off, uint32_t page_size, int method);
+
+/* Executes the copy runs produced by the servicing / make_resident passes: run r moves pages
+ * [first_page, first_page + num_pages) of slot r.slot from tier (DRAM for src 0, CXL for src 1) into the HBM
+ * tier at the same block offset; UVMTIER_RUN_SRC_ZERO runs zero-fill (block_populate_gpu_chunk zeroes new
+ * chunks, UVM/uvm_va_block.c:3011).  n_runs is read from the device counter d_n_runs (clamped to run_cap). */
+NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs,
+                                   uint32_t run_cap, int method);
+
+/* 64-bit checksum of n pages of a tier (order-sensitive FNV-style mix per page, one value per page):
+ * lets the harness verify migrated contents without copying them back. */
+NV_STATUS uvmtier_checksum_pages_device(uvmtier_ctx_t *ctx, uint32_t tier, size_t n, const uint64_t *d_off,
+                                        uint32_t page_size, uint64_t *d_out);
+
+/* Link-peak probe: best-of-`reps` time of one cudaMemcpyAsync (the copy engine, i.e. what the reference's
+ * ce_hal->memcopy does) of `bytes` from the start of src_tier to the start of dst_tier.  Defines the
+ * "measured link peak" the copy kernels are compared with. */
+NV_STATUS uvmtier_tier_memcpy_peak(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, uint64_t bytes, int reps,
+                                   float *out_best_ms);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,3 +1,419 @@
-// migrate.cu -- K3 page-list migration (placeholder until the kernels land).
+// migrate.cu -- K3: memory tiers (HBM, host DRAM, CXL NUMA node, peer HBM) and the page-list copy entry points.
+// Reference: the copy leg of uvm_va_block_make_resident (UVM/uvm_va_block.c:3863-3991, 4069-4377), CPU chunks
+// allocated per NUMA node (UVM/uvm_pmm_sysmem.c:829-853), peer apertures (UVM/uvm_gpu.h:611-640).
+//
+// Layout.  Every tier is one contiguous arena; va_block slot s lives at byte offset s * 2 MB in each of them.
+// Host tiers are anonymous mappings bound to a NUMA node with mbind(2) (raw syscall, no libnuma) and
+// registered with CUDA as portable mapped memory, so the SMs read/write them in place over PCIe.
+// Bound: the host link (PCIe Gen5 x16) for DRAM/CXL <-> HBM, NVLink for peer; payload bytes = pages * page_size.
 #include "common.cuh"
-void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx) { (void)ctx; }
+
+#include <dirent.h>
+#include <errno.h>
+#include <stdlib.h>
+#include <sys/mman.h>
+#include <sys/syscall.h>
+#include <unistd.h>
+
+#include "migrate_kernels.cuh"
+
+using namespace uvmtier_k;
+
+struct uvmtier_tier {
+    uvmtier_tier_info_t info;
+    bool used;
+    bool registered;      // cudaHostRegister done by us
+    bool mmapped;         // mmap done by us
+    bool cuda_alloc;      // cudaMalloc done by us
+};
+
+struct uvmtier_tiers {
+    uvmtier_tier t[UVMTIER_MAX_TIERS];
+    uint64_t *d_lists;    // scratch for uvmtier_copy_runs_device: 3 page lists + counters
+    uint32_t *d_list_count;
+    uint32_t list_cap;
+    uint32_t *h_list_count;   // pinned
+    bool smem_attr_set;
+};
+
+static uvmtier_tiers *tiers_get(uvmtier_ctx_t *ctx)
+{
+    if (!ctx->tiers)
+        ctx->tiers = (uvmtier_tiers *)calloc(1, sizeof(uvmtier_tiers));
+    return ctx->tiers;
+}
+
+static void tier_release(uvmtier_ctx_t *ctx, uvmtier_tier *t)
+{
+    if (!t->used)
+        return;
+    cudaSetDevice(ctx->device);
+    if (t->registered)
+        cudaHostUnregister(t->info.host_ptr);
+    if (t->mmapped)
+        munmap(t->info.host_ptr, t->info.bytes);
+    if (t->cuda_alloc)
+        cudaFree(t->info.device_ptr);
+    memset(t, 0, sizeof(*t));
+}
+
+void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx)
+{
+    if (!ctx->tiers)
+        return;
+    for (uint32_t i = 0; i < UVMTIER_MAX_TIERS; i++)
+        tier_release(ctx, &ctx->tiers->t[i]);
+    if (ctx->tiers->d_lists)
+        cudaFree(ctx->tiers->d_lists);
+    if (ctx->tiers->h_list_count)
+        cudaFreeHost(ctx->tiers->h_list_count);
+    free(ctx->tiers);
+    ctx->tiers = NULL;
+}
+
+static int read_small_file(const char *path, char *buf, size_t cap)
+{
+    FILE *f = fopen(path, "r");
+    if (!f)
+        return -1;
+    size_t n = fread(buf, 1, cap - 1, f);
+    fclose(f);
+    buf[n] = 0;
+    while (n && (buf[n - 1] == '\n' || buf[n - 1] == ' '))
+        buf[--n] = 0;
+    return (int)n;
+}
+
+extern "C" {
+
+int uvmtier_numa_probe(int *out_dram_node, int *out_cxl_node)
+{
+    int dram = -1, cxl = -1, count = 0;
+    DIR *d = opendir("/sys/devices/system/node");
+    if (d) {
+        struct dirent *e;
+        while ((e = readdir(d))) {
+            int id;
+            if (sscanf(e->d_name, "node%d", &id) != 1)
+                continue;
+            char path[256], buf[4096];
+            count++;
+            snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/meminfo", id);
+            unsigned long long kb = 0;
+            if (read_small_file(path, buf, sizeof(buf)) > 0) {
+                const char *p = strstr(buf, "MemTotal:");
+                if (p)
+                    sscanf(p, "MemTotal: %llu", &kb);
+            }
+            snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/cpulist", id);
+            const int n = read_small_file(path, buf, sizeof(buf));
+            const bool has_cpu = n > 0;
+            if (kb > 0 && has_cpu && (dram < 0 || id < dram))
+                dram = id;
+            if (kb > 0 && !has_cpu && (cxl < 0 || id < cxl))
+                cxl = id;            // memory-only node: how a CXL type-3 expander shows up
+        }
+        closedir(d);
+    }
+    if (out_dram_node)
+        *out_dram_node = dram;
+    if (out_cxl_node)
+        *out_cxl_node = cxl;
+    return count;
+}
+
+NV_STATUS uvmtier_tier_create(uvmtier_ctx_t *ctx, uint32_t tier, uint64_t bytes, int numa_node, uvmtier_tier_info_t *out)
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !bytes || tier >= UVMTIER_TIER_PEER0)
+        return NV_ERR_INVALID_ARGUMENT;
+    uvmtier_tiers *ts = tiers_get(ctx);
+    if (!ts)
+        return NV_ERR_NO_MEMORY;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    uvmtier_tier *t = &ts->t[tier];
+    tier_release(ctx, t);
+    bytes = uvmtier_align_up(bytes, UVMTIER_VA_BLOCK_SIZE);
+    t->info.bytes = bytes;
+    t->info.numa_node = -1;
+    if (tier == UVMTIER_TIER_HBM) {
+        UVMTIER_CUDA(cudaMalloc(&t->info.device_ptr, bytes));
+        t->cuda_alloc = true;
+    }
+    else {
+        int dram = -1, cxl = -1;
+        uvmtier_numa_probe(&dram, &cxl);
+        if (numa_node < 0) {
+            if (tier == UVMTIER_TIER_CXL) {
+                numa_node = cxl >= 0 ? cxl : dram;
+                if (cxl < 0)
+                    t->info.flags |= UVMTIER_TIERF_CXL_EMULATED;     // said loudly, never silently
+            }
+            else {
+                numa_node = dram;
+            }
+        }
+        else if (tier == UVMTIER_TIER_CXL && numa_node != cxl) {
+            t->info.flags |= UVMTIER_TIERF_CXL_EMULATED;
+        }
+        void *p = mmap(NULL, bytes, PROT_READ | PROT_WRITE, MAP_PRIVATE | MAP_ANONYMOUS, -1, 0);
+        if (p == MAP_FAILED)
+            return NV_ERR_NO_MEMORY;
+        t->mmapped = true;
+        t->info.host_ptr = p;
+        madvise(p, bytes, MADV_HUGEPAGE);
+        if (numa_node >= 0 && numa_node < 64) {
+            unsigned long mask = 1ul << numa_node;
+            // MPOL_BIND = 2; strict node binding like alloc_pages_node(nid, __GFP_THISNODE)
+            if (syscall(SYS_mbind, p, bytes, 2, &mask, sizeof(mask) * 8 + 1, 0) == 0)
+                t->info.numa_node = numa_node;
+        }
+        cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable | cudaHostRegisterMapped);
+        if (e != cudaSuccess) {
+            uvmtier_set_error("cudaHostRegister", e, __FILE__, __LINE__);
+            tier_release(ctx, t);
+            return uvmtier_status_from_cuda(e);
+        }
+        t->registered = true;
+        UVMTIER_CUDA(cudaHostGetDevicePointer(&t->info.device_ptr, p, 0));
+    }
+    t->used = true;
+    if (out)
+        *out = t->info;
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_tier_register(uvmtier_ctx_t *ctx, uint32_t tier, void *device_ptr, void *host_ptr, uint64_t bytes)
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !device_ptr || !bytes)
+        return NV_ERR_INVALID_ARGUMENT;
+    uvmtier_tiers *ts = tiers_get(ctx);
+    if (!ts)
+        return NV_ERR_NO_MEMORY;
+    uvmtier_tier *t = &ts->t[tier];
+    tier_release(ctx, t);
+    t->info.bytes = bytes;
+    t->info.device_ptr = device_ptr;
+    t->info.host_ptr = host_ptr;
+    t->info.numa_node = -1;
+    t->info.flags = UVMTIER_TIERF_EXTERNAL;
+    t->used = true;
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_tier_map_peer(uvmtier_ctx_t *ctx, uint32_t peer_index, uvmtier_ctx_t *peer)
+{
+    if (!ctx || !peer || UVMTIER_TIER_PEER0 + peer_index >= UVMTIER_MAX_TIERS || !peer->tiers ||
+        !peer->tiers->t[UVMTIER_TIER_HBM].used || ctx->device == peer->device)
+        return NV_ERR_INVALID_ARGUMENT;
+    int can = 0;
+    UVMTIER_CUDA(cudaDeviceCanAccessPeer(&can, ctx->device, peer->device));
+    if (!can)
+        return NV_ERR_NOT_SUPPORTED;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0);
+    if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) {
+        uvmtier_set_error("cudaDeviceEnablePeerAccess", e, __FILE__, __LINE__);
+        return uvmtier_status_from_cuda(e);
+    }
+    cudaGetLastError();
+    const uvmtier_tier_info_t *pi = &peer->tiers->t[UVMTIER_TIER_HBM].info;
+    return uvmtier_tier_register(ctx, UVMTIER_TIER_PEER0 + peer_index, pi->device_ptr, NULL, pi->bytes);
+}
+
+NV_STATUS uvmtier_tier_info(uvmtier_ctx_t *ctx, uint32_t tier, uvmtier_tier_info_t *out)
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !out || !ctx->tiers || !ctx->tiers->t[tier].used)
+        return NV_ERR_INVALID_ARGUMENT;
+    *out = ctx->tiers->t[tier].info;
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_tier_destroy(uvmtier_ctx_t *ctx, uint32_t tier)
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !ctx->tiers)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    tier_release(ctx, &ctx->tiers->t[tier]);
+    return NV_OK;
+}
+
+static NV_STATUS launch_copy(uvmtier_ctx_t *ctx, const copy_list_params &p, int method)
+{
+    const uint64_t n_pieces = p.n_pages * p.pieces_per_page;
+    if (!n_pieces)
+        return NV_OK;
+    if (method == 1) {
+        uint64_t grid = n_pieces < (uint64_t)ctx->sm_count * 16 ? n_pieces : (uint64_t)ctx->sm_count * 16;
+        UVMTIER_LAUNCH(k_copy_pages_ldst, (int)grid, 256, 0, ctx->stream, p);
+        return NV_OK;
+    }
+    const size_t smem = (size_t)kStages * kStageBytes;
+    if (!ctx->tiers->smem_attr_set) {
+        UVMTIER_CUDA(cudaFuncSetAttribute(k_copy_pages_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ctx->tiers->smem_attr_set = true;
+    }
+    const uint64_t items = (n_pieces + kPiecesPerStage - 1) / kPiecesPerStage;
+    const uint64_t grid = items < (uint64_t)ctx->sm_count ? items : (uint64_t)ctx->sm_count;   // one CTA per SM
+    UVMTIER_LAUNCH(k_copy_pages_tma, (int)grid, kCopyThreads, smem, ctx->stream, p);
+    return NV_OK;
+}
+
+static bool page_size_ok(uint32_t ps) { return ps == 4096u || ps == 65536u || ps == (2u << 20); }
+
+NV_STATUS uvmtier_copy_page_list_device(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, size_t n,
+                                        const uint64_t *d_dst_off, const uint64_t *d_src_off, uint32_t page_size, int method)
+{
+    if (!ctx || dst_tier >= UVMTIER_MAX_TIERS || src_tier >= UVMTIER_MAX_TIERS || !page_size_ok(page_size))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers || !ctx->tiers->t[dst_tier].used || !ctx->tiers->t[src_tier].used)
+        return NV_ERR_INVALID_STATE;
+    if (!n)
+        return NV_OK;
+    if (!d_dst_off || !d_src_off)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    copy_list_params p;
+    p.src_base = (const uint8_t *)ctx->tiers->t[src_tier].info.device_ptr;
+    p.dst_base = (uint8_t *)ctx->tiers->t[dst_tier].info.device_ptr;
+    p.src_off = d_src_off;
+    p.dst_off = d_dst_off;
+    p.n_pages = n;
+    p.pieces_per_page = page_size / kPiece;
+    return launch_copy(ctx, p, method);
+}
+
+NV_STATUS uvmtier_copy_page_list(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, size_t n, const uint64_t *h_dst_off,
+                                 const uint64_t *h_src_off, uint32_t page_size, int method)
+{
+    if (!ctx || (n && (!h_dst_off || !h_src_off)))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!n)
+        return NV_OK;
+    const size_t lb = uvmtier_align_up(n * 8, 256);
+    NV_STATUS st = uvmtier_stage_reserve(ctx, 2 * lb, 0);
+    if (st != NV_OK)
+        return st;
+    uint64_t *d_dst = (uint64_t *)ctx->d_stage, *d_src = (uint64_t *)((char *)ctx->d_stage + lb);
+    UVMTIER_CUDA(cudaMemcpyAsync(d_dst, h_dst_off, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(d_src, h_src_off, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    st = uvmtier_copy_page_list_device(ctx, dst_tier, src_tier, n, d_dst, d_src, page_size, method);
+    if (st != NV_OK)
+        return st;
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs,
+                                   uint32_t run_cap, int method)
+{
+    if (!ctx || !d_runs || !d_n_runs)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers || !ctx->tiers->t[UVMTIER_TIER_HBM].used)
+        return NV_ERR_INVALID_STATE;
+    if (!run_cap)
+        return NV_OK;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    uvmtier_tiers *ts = ctx->tiers;
+    // a run has at most 512 pages, but the lists are sized from the HBM arena: no more pages than it holds
+    const uint64_t hbm_pages = ts->t[UVMTIER_TIER_HBM].info.bytes / UVMTIER_PAGE_SIZE;
+    const uint32_t want = (uint32_t)(hbm_pages < 0x7fffffffull ? hbm_pages : 0x7fffffffull);
+    if (want > ts->list_cap) {
+        if (ts->d_lists) {
+            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+            UVMTIER_CUDA(cudaFree(ts->d_lists));
+            ts->d_lists = NULL;
+        }
+        UVMTIER_CUDA(cudaMalloc(&ts->d_lists, (size_t)want * 3 * sizeof(uint64_t) + 64));
+        ts->d_list_count = (uint32_t *)(ts->d_lists + (size_t)want * 3);
+        ts->list_cap = want;
+    }
+    if (!ts->h_list_count)
+        UVMTIER_CUDA(cudaHostAlloc(&ts->h_list_count, 64, cudaHostAllocPortable));
+    uint64_t *l0 = ts->d_lists, *l1 = l0 + ts->list_cap, *lz = l1 + ts->list_cap;
+    UVMTIER_CUDA(cudaMemsetAsync(ts->d_list_count, 0, 16, ctx->stream));
+    size_t grid = ((size_t)run_cap + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, l0, l1, lz, ts->d_list_count,
+                   ts->list_cap);
+    // the list lengths size the copy grids: one small D2H read (the reference also walks its masks on the CPU)
+    UVMTIER_CUDA(cudaMemcpyAsync(ts->h_list_count, ts->d_list_count, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    uint8_t *hbm = (uint8_t *)ts->t[UVMTIER_TIER_HBM].info.device_ptr;
+    for (int which = 0; which < 2; which++) {
+        const uint32_t n = ts->h_list_count[which] < ts->list_cap ? ts->h_list_count[which] : ts->list_cap;
+        if (!n)
+            continue;
+        const uint32_t tier = which == 0 ? UVMTIER_TIER_DRAM : UVMTIER_TIER_CXL;
+        if (!ts->t[tier].used)
+            return NV_ERR_INVALID_STATE;
+        copy_list_params p;
+        p.src_base = (const uint8_t *)ts->t[tier].info.device_ptr;
+        p.dst_base = hbm;
+        p.src_off = which == 0 ? l0 : l1;
+        p.dst_off = p.src_off;
+        p.n_pages = n;
+        p.pieces_per_page = 1;
+        NV_STATUS st = launch_copy(ctx, p, method);
+        if (st != NV_OK)
+            return st;
+    }
+    const uint32_t nz = ts->h_list_count[2] < ts->list_cap ? ts->h_list_count[2] : ts->list_cap;
+    if (nz) {
+        const uint32_t zg = nz < (uint32_t)ctx->sm_count * 16 ? nz : (uint32_t)ctx->sm_count * 16;
+        UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, hbm, lz, (uint64_t)nz, 1u);
+    }
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_checksum_pages_device(uvmtier_ctx_t *ctx, uint32_t tier, size_t n, const uint64_t *d_off, uint32_t page_size,
+                                        uint64_t *d_out)
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !page_size_ok(page_size))
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers || !ctx->tiers->t[tier].used)
+        return NV_ERR_INVALID_STATE;
+    if (!n)
+        return NV_OK;
+    if (!d_off || !d_out)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    const size_t grid = n < (size_t)ctx->sm_count * 8 ? n : (size_t)ctx->sm_count * 8;
+    UVMTIER_LAUNCH(k_checksum_pages, (int)grid, 256, 0, ctx->stream, (const uint8_t *)ctx->tiers->t[tier].info.device_ptr, d_off,
+                   (uint64_t)n, page_size, d_out);
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_tier_memcpy_peak(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, uint64_t bytes, int reps,
+                                   float *out_best_ms)
+{
+    if (!ctx || dst_tier >= UVMTIER_MAX_TIERS || src_tier >= UVMTIER_MAX_TIERS || !out_best_ms || reps < 1)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers || !ctx->tiers->t[dst_tier].used || !ctx->tiers->t[src_tier].used)
+        return NV_ERR_INVALID_STATE;
+    const uvmtier_tier_info_t *d = &ctx->tiers->t[dst_tier].info, *s = &ctx->tiers->t[src_tier].info;
+    if (bytes > d->bytes || bytes > s->bytes)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    cudaEvent_t a, b;
+    UVMTIER_CUDA(cudaEventCreate(&a));
+    UVMTIER_CUDA(cudaEventCreate(&b));
+    float best = 1e30f;
+    for (int r = 0; r < reps + 1; r++) {        // first one is a warm-up
+        UVMTIER_CUDA(cudaEventRecord(a, ctx->stream));
+        UVMTIER_CUDA(cudaMemcpyAsync(d->device_ptr, s->device_ptr, bytes, cudaMemcpyDefault, ctx->stream));
+        UVMTIER_CUDA(cudaEventRecord(b, ctx->stream));
+        UVMTIER_CUDA(cudaEventSynchronize(b));
+        float ms = 0;
+        UVMTIER_CUDA(cudaEventElapsedTime(&ms, a, b));
+        if (r > 0 && ms < best)
+            best = ms;
+    }
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+    *out_best_ms = best;
+    return NV_OK;
+}
+
+} // extern "C"

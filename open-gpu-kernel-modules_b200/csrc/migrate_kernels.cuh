@@ -1,0 +1,215 @@
+// migrate_kernels.cuh -- K3: SM-driven page gather/scatter copies between tiers (sm_100a).
+// Replaces the copy primitive of block_copy_pages / ce_hal->memcopy (UVM/uvm_va_block.c:3863-3991,
+// UVM/uvm_volta_ce.c:119-183) and the CPU kmap+memcpy page loop (:3972-3984).
+//
+// Work unit = one 4 KB piece (a 4 KB page, or 1/16 of a 64 KB page, or 1/512 of a 2 MB page).  A persistent
+// CTA owns a ring of kStages shared-memory stages of kPiecesPerStage pieces.  ONE elected thread drives the
+// whole pipeline with the TMA engine:
+//   global(src tier) --cp.async.bulk--> shared  (completion: mbarrier complete_tx)
+//   shared --cp.async.bulk--> global(dst tier)   (completion: bulk async-group)
+// so loads of later stages are in flight while earlier stages drain; no thread touches the payload.  The src /
+// dst pointers may be HBM, host-mapped (DRAM / CXL, zero-copy over PCIe) or peer HBM over NVLink: the access
+// path is picked by the address, the kernel is the same.
+#pragma once
+
+#include <stdint.h>
+
+#include "uvmtier.h"
+
+namespace uvmtier_k {
+
+constexpr uint32_t kPiece = 4096;            // bytes per TMA bulk op
+constexpr uint32_t kPiecesPerStage = 4;      // 16 KB per stage
+constexpr uint32_t kStages = 12;             // 192 KB of shared memory per CTA, 1 CTA per SM
+constexpr uint32_t kStageBytes = kPiece * kPiecesPerStage;
+constexpr uint32_t kCopyThreads = 32;
+
+struct copy_list_params {
+    const uint8_t *src_base;
+    uint8_t *dst_base;
+    const uint64_t *src_off;     // per page
+    const uint64_t *dst_off;
+    uint64_t n_pages;
+    uint32_t pieces_per_page;    // page_size / 4096
+};
+
+// ---- thin PTX wrappers ----
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra DONE;\n"
+        "bra WAIT_LOOP;\n"
+        "DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity) : "memory");
+}
+__device__ __forceinline__ void tma_load_1d(void *smem_dst, const void *gmem_src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gmem_src), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
+__device__ __forceinline__ void tma_store_1d(void *gmem_dst, const void *smem_src, uint32_t bytes)
+{
+    asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(gmem_dst), "r"(smem_u32(smem_src)), "r"(bytes)
+                 : "memory");
+}
+__device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
+template <int N> __device__ __forceinline__ void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read %0;" ::"n"(N) : "memory"); }
+template <int N> __device__ __forceinline__ void tma_wait_all() { asm volatile("cp.async.bulk.wait_group %0;" ::"n"(N) : "memory"); }
+
+// Source / destination address of 4 KB piece u of the page list.
+__device__ __forceinline__ void piece_addr(const copy_list_params &p, uint64_t u, const uint8_t **src, uint8_t **dst)
+{
+    const uint64_t page = u / p.pieces_per_page;
+    const uint64_t within = (u - page * p.pieces_per_page) * kPiece;
+    *src = p.src_base + p.src_off[page] + within;
+    *dst = p.dst_base + p.dst_off[page] + within;
+}
+
+// Persistent TMA pipeline.  grid = a multiple of the SM count; CTA c takes stages c, c + grid, ... (a stage =
+// kPiecesPerStage consecutive pieces), so neighbouring CTAs stream neighbouring memory.
+__global__ void __launch_bounds__(kCopyThreads, 1) k_copy_pages_tma(copy_list_params p)
+{
+    extern __shared__ __align__(128) uint8_t smem[];
+    __shared__ __align__(8) uint64_t full[kStages];
+    const uint64_t n_pieces = p.n_pages * p.pieces_per_page;
+    const uint64_t n_stage_items = (n_pieces + kPiecesPerStage - 1) / kPiecesPerStage;
+    if (threadIdx.x != 0)
+        return;                                        // one thread drives the TMA engine
+    for (uint32_t s = 0; s < kStages; s++)
+        mbar_init(&full[s], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+
+    // items of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
+    const uint64_t first = blockIdx.x, step = gridDim.x;
+    if (first >= n_stage_items)
+        return;
+    const uint64_t my_items = (n_stage_items - first + step - 1) / step;
+
+    auto issue_load = [&](uint64_t k) {                // k-th item of this CTA -> stage k % kStages
+        const uint32_t s = (uint32_t)(k % kStages);
+        const uint64_t u0 = (first + k * step) * kPiecesPerStage;
+        const uint32_t cnt = (uint32_t)min((uint64_t)kPiecesPerStage, n_pieces - u0);
+        mbar_expect_tx(&full[s], cnt * kPiece);
+        for (uint32_t j = 0; j < cnt; j++) {
+            const uint8_t *src;
+            uint8_t *dst;
+            piece_addr(p, u0 + j, &src, &dst);
+            tma_load_1d(smem + (size_t)s * kStageBytes + j * kPiece, src, kPiece, &full[s]);
+        }
+    };
+    auto issue_store = [&](uint64_t k) {
+        const uint32_t s = (uint32_t)(k % kStages);
+        const uint64_t u0 = (first + k * step) * kPiecesPerStage;
+        const uint32_t cnt = (uint32_t)min((uint64_t)kPiecesPerStage, n_pieces - u0);
+        mbar_wait(&full[s], (uint32_t)((k / kStages) & 1));
+        for (uint32_t j = 0; j < cnt; j++) {
+            const uint8_t *src;
+            uint8_t *dst;
+            piece_addr(p, u0 + j, &src, &dst);
+            tma_store_1d(dst, smem + (size_t)s * kStageBytes + j * kPiece, kPiece);
+        }
+        tma_commit();
+    };
+
+    const uint64_t prologue = min(my_items, (uint64_t)(kStages - 1));
+    for (uint64_t k = 0; k < prologue; k++)
+        issue_load(k);
+    for (uint64_t k = 0; k < my_items; k++) {
+        issue_store(k);
+        const uint64_t nxt = k + kStages - 1;          // reuses the stage whose stores were committed at k - 1
+        if (nxt < my_items) {
+            tma_wait_read<1>();                        // all but the newest store group have left shared memory
+            issue_load(nxt);
+        }
+    }
+    tma_wait_all<0>();                                 // writes performed before the kernel ends
+}
+
+// Comparison kernel: every thread moves 16-byte vectors with plain loads/stores (the pre-TMA way).
+__global__ void __launch_bounds__(256) k_copy_pages_ldst(copy_list_params p)
+{
+    const uint64_t n_pieces = p.n_pages * p.pieces_per_page;
+    for (uint64_t u = blockIdx.x; u < n_pieces; u += gridDim.x) {
+        const uint8_t *src;
+        uint8_t *dst;
+        piece_addr(p, u, &src, &dst);
+        const uint4 v = *((const uint4 *)src + threadIdx.x);    // 256 threads x 16 B = 4 KB
+        *((uint4 *)dst + threadIdx.x) = v;
+    }
+}
+
+// Zero-fill of 4 KB pieces (first-touch population, UVM/uvm_va_block.c:3011).
+__global__ void __launch_bounds__(256) k_zero_pages(uint8_t *base, const uint64_t *off, uint64_t n_pages, uint32_t pieces_per_page)
+{
+    const uint64_t n_pieces = n_pages * pieces_per_page;
+    for (uint64_t u = blockIdx.x; u < n_pieces; u += gridDim.x) {
+        const uint64_t page = u / pieces_per_page;
+        uint8_t *dst = base + off[page] + (u - page * pieces_per_page) * kPiece;
+        *((uint4 *)dst + threadIdx.x) = make_uint4(0, 0, 0, 0);
+    }
+}
+
+// Expands copy runs into per-page offset lists: for run r, page j: offset = slot * 2 MB + (first_page + j) * 4 KB
+// (the same offset in the source tier and in HBM).  Three lists: from DRAM, from CXL, zero-fill.  Counters:
+// list_count[3].  One thread per run; pages are appended with one atomicAdd per run.
+__global__ void __launch_bounds__(256) k_expand_runs(const uvmtier_copy_run_t *runs, const uint32_t *n_runs_dev, uint32_t run_cap,
+                                                     uint64_t *list0, uint64_t *list1, uint64_t *listz, uint32_t *list_count,
+                                                     uint32_t list_cap)
+{
+    const uint32_t n_runs = min(*n_runs_dev, run_cap);
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
+        const uvmtier_copy_run_t run = runs[r];
+        const uint32_t which = run.src == 0 ? 0u : (run.src == 1 ? 1u : 2u);
+        uint64_t *list = which == 0 ? list0 : (which == 1 ? list1 : listz);
+        const uint32_t at = atomicAdd(&list_count[which], (uint32_t)run.num_pages);
+        const uint64_t base = (uint64_t)run.slot * UVMTIER_VA_BLOCK_SIZE + (uint64_t)run.first_page * UVMTIER_PAGE_SIZE;
+        for (uint32_t j = 0; j < run.num_pages; j++)
+            if (at + j < list_cap)
+                list[at + j] = base + (uint64_t)j * UVMTIER_PAGE_SIZE;
+    }
+}
+
+// One 64-bit value per page: xor-rotate-multiply over the page's 64-bit words in order.
+__global__ void __launch_bounds__(256) k_checksum_pages(const uint8_t *base, const uint64_t *off, uint64_t n_pages, uint32_t page_size,
+                                                        uint64_t *out)
+{
+    __shared__ uint64_t s_part[8];
+    for (uint64_t pg = blockIdx.x; pg < n_pages; pg += gridDim.x) {
+        const uint64_t *src = (const uint64_t *)(base + off[pg]);
+        const uint32_t words = page_size / 8;
+        uint64_t h = 0;
+        for (uint32_t i = threadIdx.x; i < words; i += 256) {
+            uint64_t v = src[i] + 0x9E3779B97F4A7C15ull * (uint64_t)(i + 1);
+            v ^= v >> 29;
+            v *= 0xBF58476D1CE4E5B9ull;
+            v ^= v >> 32;
+            h += v;                                    // commutative combine of position-salted words
+        }
+        for (int d = 16; d > 0; d >>= 1) h += __shfl_xor_sync(0xffffffffu, h, d);
+        if ((threadIdx.x & 31) == 0) s_part[threadIdx.x >> 5] = h;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            uint64_t t = 0;
+            for (int w = 0; w < 8; w++) t += s_part[w];
+            out[pg] = t;
+        }
+        __syncthreads();
+    }
+}
+
+} // namespace uvmtier_k

@@ -68,6 +68,28 @@ class Config(ctypes.Structure):
     ]
 
 
+TIER_HBM, TIER_DRAM, TIER_CXL, TIER_PEER0 = 0, 1, 2, 8
+TIERF_CXL_EMULATED = 0x1
+
+
+class TierInfo(ctypes.Structure):
+    """uvmtier_tier_info_t"""
+    _fields_ = [("bytes", ctypes.c_uint64), ("device_ptr", ctypes.c_void_p), ("host_ptr", ctypes.c_void_p),
+                ("numa_node", ctypes.c_int32), ("flags", ctypes.c_uint32)]
+
+    def host_view(self):
+        """numpy uint8 view of a host tier's arena."""
+        assert self.host_ptr, "not a host tier"
+        return np.frombuffer((ctypes.c_uint8 * self.bytes).from_address(self.host_ptr), dtype=np.uint8)
+
+
+def numa_probe():
+    """(online nodes, dram node, cxl node or -1)"""
+    d, c = ctypes.c_int(-1), ctypes.c_int(-1)
+    n = lib().uvmtier_numa_probe(ctypes.byref(d), ctypes.byref(c))
+    return n, d.value, c.value
+
+
 def default_config():
     cfg = Config()
     lib().uvmtier_config_default(ctypes.byref(cfg))
@@ -208,6 +230,44 @@ class Context:
         finally:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt):
                 self.free(p)
+
+    # ---- (3) tiers + page-list migration ----
+    def tier_create(self, tier, nbytes, numa_node=-1):
+        """uvmtier_tier_create -> TierInfo (device_ptr, host view as numpy uint8 for host tiers)."""
+        info = TierInfo()
+        _check(lib().uvmtier_tier_create(self._h, ctypes.c_uint32(tier), ctypes.c_uint64(nbytes), ctypes.c_int(numa_node),
+                                         ctypes.byref(info)), "uvmtier_tier_create")
+        return info
+
+    def tier_map_peer(self, peer_index, peer_ctx):
+        _check(lib().uvmtier_tier_map_peer(self._h, ctypes.c_uint32(peer_index), peer_ctx.handle), "uvmtier_tier_map_peer")
+
+    def tier_destroy(self, tier):
+        _check(lib().uvmtier_tier_destroy(self._h, ctypes.c_uint32(tier)), "uvmtier_tier_destroy")
+
+    def copy_page_list(self, dst_tier, src_tier, dst_off, src_off, page_size, method=0):
+        """uvmtier_copy_page_list (host lists of byte offsets, uint64)."""
+        dst_off = np.ascontiguousarray(dst_off, "<u8"); src_off = np.ascontiguousarray(src_off, "<u8")
+        _check(lib().uvmtier_copy_page_list(self._h, ctypes.c_uint32(dst_tier), ctypes.c_uint32(src_tier),
+                                            ctypes.c_size_t(len(dst_off)), P(dst_off), P(src_off), ctypes.c_uint32(page_size),
+                                            ctypes.c_int(method)), "uvmtier_copy_page_list")
+
+    def checksum_pages(self, tier, off, page_size):
+        off = np.ascontiguousarray(off, "<u8")
+        d_off = self.to_device(off); d_out = self.alloc(len(off) * 8)
+        try:
+            _check(lib().uvmtier_checksum_pages_device(self._h, ctypes.c_uint32(tier), ctypes.c_size_t(len(off)), P(d_off),
+                                                       ctypes.c_uint32(page_size), P(d_out)), "uvmtier_checksum_pages_device")
+            self.synchronize()
+            return self.from_device(d_out, len(off), "<u8")
+        finally:
+            self.free(d_off); self.free(d_out)
+
+    def tier_memcpy_peak_gbs(self, dst_tier, src_tier, nbytes, reps=5):
+        ms = ctypes.c_float(0)
+        _check(lib().uvmtier_tier_memcpy_peak(self._h, ctypes.c_uint32(dst_tier), ctypes.c_uint32(src_tier),
+                                              ctypes.c_uint64(nbytes), ctypes.c_int(reps), ctypes.byref(ms)), "tier_memcpy_peak")
+        return nbytes / (ms.value * 1e-3) / 1e9
 
     # ---- (2) prefetch ----
     def perf_prefetch_compute_ats(self, faulted, faulted_region, max_prefetch_region, residency=None):

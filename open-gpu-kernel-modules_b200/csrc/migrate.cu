@@ -254,7 +254,8 @@ static NV_STATUS launch_copy(uvmtier_ctx_t *ctx, const copy_list_params &p, int 
         ctx->tiers->smem_attr_set = true;
     }
     const uint64_t items = (n_pieces + kPiecesPerStage - 1) / kPiecesPerStage;
-    const uint64_t grid = items < (uint64_t)ctx->sm_count ? items : (uint64_t)ctx->sm_count;   // one CTA per SM
+    const uint64_t full = (uint64_t)ctx->sm_count * kCtasPerSm;        // persistent: every SM holds kCtasPerSm CTAs
+    const uint64_t grid = items < full ? items : full;
     UVMTIER_LAUNCH(k_copy_pages_tma, (int)grid, kCopyThreads, smem, ctx->stream, p);
     return NV_OK;
 }

@@ -3,8 +3,8 @@
 // UVM/uvm_volta_ce.c:119-183) and the CPU kmap+memcpy page loop (:3972-3984).
 //
 // Work unit = one 4 KB piece (a 4 KB page, or 1/16 of a 64 KB page, or 1/512 of a 2 MB page).  A persistent
-// CTA owns a ring of kStages shared-memory stages of kPiecesPerStage pieces.  ONE elected thread drives the
-// whole pipeline with the TMA engine:
+// one-warp CTA owns a ring of kStages shared-memory stages of kPiecesPerStage pieces (several CTAs per SM).
+// ONE elected thread per CTA drives its pipeline with the TMA engine:
 //   global(src tier) --cp.async.bulk--> shared  (completion: mbarrier complete_tx)
 //   shared --cp.async.bulk--> global(dst tier)   (completion: bulk async-group)
 // so loads of later stages are in flight while earlier stages drain; no thread touches the payload.  The src /
@@ -20,7 +20,8 @@ namespace uvmtier_k {
 
 constexpr uint32_t kPiece = 4096;            // bytes per TMA bulk op
 constexpr uint32_t kPiecesPerStage = 4;      // 16 KB per stage
-constexpr uint32_t kStages = 12;             // 192 KB of shared memory per CTA, 1 CTA per SM
+constexpr uint32_t kStages = 4;              // 64 KB of shared memory per CTA
+constexpr uint32_t kCtasPerSm = 3;           // three independent pipelines (issuing threads) per SM
 constexpr uint32_t kStageBytes = kPiece * kPiecesPerStage;
 constexpr uint32_t kCopyThreads = 32;
 
@@ -79,65 +80,104 @@ __device__ __forceinline__ void piece_addr(const copy_list_params &p, uint64_t u
     *dst = p.dst_base + p.dst_off[page] + within;
 }
 
-// Persistent TMA pipeline.  grid = a multiple of the SM count; CTA c takes stages c, c + grid, ... (a stage =
-// kPiecesPerStage consecutive pieces), so neighbouring CTAs stream neighbouring memory.
-__global__ void __launch_bounds__(kCopyThreads, 1) k_copy_pages_tma(copy_list_params p)
+// Persistent TMA pipeline.  kCtasPerSm CTAs of one warp per SM; CTA c takes items c, c + grid, ... (an item =
+// kPiecesPerStage consecutive pieces = one shared-memory stage), so neighbouring CTAs stream neighbouring memory.
+// All 32 lanes fetch page offsets (one piece each, 8 items at a time) so that the list reads cost one memory
+// latency per 32 pieces; lane 0 alone talks to the TMA engine.
+__global__ void __launch_bounds__(kCopyThreads, kCtasPerSm) k_copy_pages_tma(copy_list_params p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
     __shared__ __align__(8) uint64_t full[kStages];
-    const uint64_t n_pieces = p.n_pages * p.pieces_per_page;
-    const uint64_t n_stage_items = (n_pieces + kPiecesPerStage - 1) / kPiecesPerStage;
-    if (threadIdx.x != 0)
-        return;                                        // one thread drives the TMA engine
-    for (uint32_t s = 0; s < kStages; s++)
-        mbar_init(&full[s], 1);
-    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-
-    // items of this CTA: blockIdx.x, blockIdx.x + gridDim.x, ...
+    __shared__ uint8_t *s_dst[kStages][kPiecesPerStage];
+    const int lane = threadIdx.x;
+    const uint32_t ppp_shift = 31 - __clz((int)p.pieces_per_page);        // pieces_per_page is 1, 16 or 512
+    const uint64_t n_pieces = p.n_pages << ppp_shift;
+    const uint64_t n_items = (n_pieces + kPiecesPerStage - 1) / kPiecesPerStage;
     const uint64_t first = blockIdx.x, step = gridDim.x;
-    if (first >= n_stage_items)
+    if (first >= n_items)
         return;
-    const uint64_t my_items = (n_stage_items - first + step - 1) / step;
+    const uint64_t my_items = (n_items - first + step - 1) / step;
+    const bool big = p.pieces_per_page >= kPiecesPerStage;               // a stage never straddles two pages
 
-    auto issue_load = [&](uint64_t k) {                // k-th item of this CTA -> stage k % kStages
+    if (lane == 0) {
+        for (uint32_t s = 0; s < kStages; s++)
+            mbar_init(&full[s], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    }
+    __syncwarp();
+
+    const uint8_t *my_src = NULL;
+    uint8_t *my_dst = NULL;
+    auto fetch = [&](uint64_t k0) {                    // lanes: piece (lane & 3) of item k0 + (lane >> 2)
+        const uint64_t k = k0 + (uint64_t)(lane >> 2);
+        const uint64_t u = ((first + k * step) * kPiecesPerStage) + (uint64_t)(lane & 3);
+        if (k < my_items && u < n_pieces) {
+            const uint64_t page = u >> ppp_shift;
+            const uint64_t within = (u & (p.pieces_per_page - 1)) * kPiece;
+            my_src = p.src_base + p.src_off[page] + within;
+            my_dst = p.dst_base + p.dst_off[page] + within;
+        }
+    };
+    auto load = [&](uint64_t k) {                      // all lanes call; lane 0 issues
+        if ((k & 7) == 0)
+            fetch(k);
         const uint32_t s = (uint32_t)(k % kStages);
         const uint64_t u0 = (first + k * step) * kPiecesPerStage;
         const uint32_t cnt = (uint32_t)min((uint64_t)kPiecesPerStage, n_pieces - u0);
-        mbar_expect_tx(&full[s], cnt * kPiece);
-        for (uint32_t j = 0; j < cnt; j++) {
-            const uint8_t *src;
-            uint8_t *dst;
-            piece_addr(p, u0 + j, &src, &dst);
-            tma_load_1d(smem + (size_t)s * kStageBytes + j * kPiece, src, kPiece, &full[s]);
+        const uint8_t *src[kPiecesPerStage];
+        uint8_t *dst[kPiecesPerStage];
+#pragma unroll
+        for (uint32_t j = 0; j < kPiecesPerStage; j++) {
+            src[j] = (const uint8_t *)__shfl_sync(0xffffffffu, (unsigned long long)my_src, (int)((k & 7) * 4 + j));
+            dst[j] = (uint8_t *)__shfl_sync(0xffffffffu, (unsigned long long)my_dst, (int)((k & 7) * 4 + j));
+        }
+        if (lane == 0) {
+            mbar_expect_tx(&full[s], cnt * kPiece);
+            if (big) {
+                tma_load_1d(smem + (size_t)s * kStageBytes, src[0], cnt * kPiece, &full[s]);
+                s_dst[s][0] = dst[0];
+            }
+            else {
+#pragma unroll
+                for (uint32_t j = 0; j < kPiecesPerStage; j++)
+                    if (j < cnt) {
+                        tma_load_1d(smem + (size_t)s * kStageBytes + j * kPiece, src[j], kPiece, &full[s]);
+                        s_dst[s][j] = dst[j];
+                    }
+            }
         }
     };
-    auto issue_store = [&](uint64_t k) {
+    auto store = [&](uint64_t k) {                     // lane 0 only
         const uint32_t s = (uint32_t)(k % kStages);
         const uint64_t u0 = (first + k * step) * kPiecesPerStage;
         const uint32_t cnt = (uint32_t)min((uint64_t)kPiecesPerStage, n_pieces - u0);
         mbar_wait(&full[s], (uint32_t)((k / kStages) & 1));
-        for (uint32_t j = 0; j < cnt; j++) {
-            const uint8_t *src;
-            uint8_t *dst;
-            piece_addr(p, u0 + j, &src, &dst);
-            tma_store_1d(dst, smem + (size_t)s * kStageBytes + j * kPiece, kPiece);
+        if (big) {
+            tma_store_1d(s_dst[s][0], smem + (size_t)s * kStageBytes, cnt * kPiece);
+        }
+        else {
+            for (uint32_t j = 0; j < cnt; j++)
+                tma_store_1d(s_dst[s][j], smem + (size_t)s * kStageBytes + j * kPiece, kPiece);
         }
         tma_commit();
     };
 
     const uint64_t prologue = min(my_items, (uint64_t)(kStages - 1));
     for (uint64_t k = 0; k < prologue; k++)
-        issue_load(k);
+        load(k);
     for (uint64_t k = 0; k < my_items; k++) {
-        issue_store(k);
+        if (lane == 0)
+            store(k);
         const uint64_t nxt = k + kStages - 1;          // reuses the stage whose stores were committed at k - 1
         if (nxt < my_items) {
-            tma_wait_read<1>();                        // all but the newest store group have left shared memory
-            issue_load(nxt);
+            if (lane == 0)
+                tma_wait_read<1>();                    // all but the newest store group have left shared memory
+            load(nxt);
         }
     }
-    tma_wait_all<0>();                                 // writes performed before the kernel ends
+    if (lane == 0)
+        tma_wait_all<0>();                             // writes performed before the kernel ends
 }
 
 // Comparison kernel: every thread moves 16-byte vectors with plain loads/stores (the pre-TMA way).

@@ -44,6 +44,13 @@ def fill(info, tier, seed, pattern="rng"):
     return v
 
 
+def hbm_fill(c, info, value, nbytes):
+    import ctypes
+    uvmtier._check(uvmtier.lib().uvmtier_memset_device(c.handle, ctypes.c_void_p(info[TIER_HBM].device_ptr), ctypes.c_int(value),
+                                                       ctypes.c_size_t(nbytes)), "memset")
+    c.synchronize()
+
+
 def hbm_read(c, info, nbytes=ARENA):
     return c.from_device(info[TIER_HBM].device_ptr, nbytes, np.uint8)
 
@@ -76,7 +83,7 @@ def test_host_to_hbm_and_back_byte_exact(tiers, page_size, order, method):
     dst_off = dst_pages.astype(np.uint64) * np.uint64(page_size)
     for src_tier, pat in ((TIER_DRAM, "rng"), (TIER_CXL, "fork")):
         src = fill(info, src_tier, 42 + page_size, pat)
-        uvmtier._check(uvmtier.lib().uvmtier_memset_device(c.handle, info[TIER_HBM].device_ptr, 0xEE, ARENA), "memset")
+        hbm_fill(c, info, 0xEE, ARENA)
         c.copy_page_list(TIER_HBM, src_tier, dst_off, src_off, page_size, method)
         got = hbm_read(c, info)
         want = np.full(ARENA, 0xEE, np.uint8)
@@ -117,7 +124,7 @@ def test_edge_cases(tiers):
     src = fill(info, TIER_DRAM, 3)
     for n in (1, 5, 4 * 12 * 148 + 3):
         off = np.arange(n, dtype=np.uint64) * np.uint64(4096)
-        uvmtier._check(uvmtier.lib().uvmtier_memset_device(c.handle, info[TIER_HBM].device_ptr, 0, ARENA), "memset")
+        hbm_fill(c, info, 0, ARENA)
         c.copy_page_list(TIER_HBM, TIER_DRAM, off, off, 4096)
         got = hbm_read(c, info, (n + 1) * 4096)
         assert np.array_equal(got[:n * 4096], src[:n * 4096]) and not got[n * 4096:].any()
@@ -139,7 +146,7 @@ def test_copy_runs_from_the_service_pass_move_the_right_bytes():
     with uvmtier.Context(0) as c:
         info = {t: c.tier_create(t, n_blocks << 21) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
         dram = fill(info, TIER_DRAM, 11); cxl = fill(info, TIER_CXL, 12, "fork")
-        uvmtier._check(uvmtier.lib().uvmtier_memset_device(c.handle, info[TIER_HBM].device_ptr, 0xAB, n_blocks << 21), "memset")
+        hbm_fill(c, info, 0xAB, n_blocks << 21)
         pk, tbl, lay = TG.fault_trace(6000, 31, "uniform", 1, total_va_bytes=n_blocks << 21)
         gp = TG.gpu_params(256)
         st0 = S.random_state(n_blocks, 2, populated=0.8, ro_frac=0, none_frac=0)
@@ -156,7 +163,8 @@ def test_copy_runs_from_the_service_pass_move_the_right_bytes():
         got = c.service_fault_batches(r, layout, ds, run_cap)
         assert got["n_runs"] <= run_cap
         d_runs = c.to_device(got["runs"]); d_n = c.to_device(np.array([got["n_runs"]], "<u4"))
-        uvmtier._check(uvmtier.lib().uvmtier_copy_runs_device(c.handle, uvmtier.P(d_runs), uvmtier.P(d_n), run_cap, 0), "copy_runs")
+        import ctypes
+        uvmtier._check(uvmtier.lib().uvmtier_copy_runs_device(c.handle, uvmtier.P(d_runs), uvmtier.P(d_n), ctypes.c_uint32(run_cap), ctypes.c_int(0)), "copy_runs")
         c.synchronize()
         hbm = c.from_device(info[TIER_HBM].device_ptr, n_blocks << 21, np.uint8).reshape(n_blocks * 512, 4096)
         from0 = T.bool_from_masks(st0.cpu_resident0) & T.bool_from_masks(got["state"].gpu_resident)

@@ -471,6 +471,7 @@ typedef struct {
 #define UVMTIER_TIERF_CXL_EMULATED 0x1u  /* no CPU-less NUMA node on this machine: a DRAM node stands in   */
 #define UVMTIER_TIERF_HUGEPAGES    0x2u
 #define UVMTIER_TIERF_EXTERNAL     0x4u  /* memory owned by the caller (uvmtier_tier_register)             */
+#define UVMTIER_TIERF_IPC          0x8u  /* peer HBM of another process, opened from a CUDA IPC handle      */
 
 /* NUMA probe of /sys/devices/system/node: out_dram_node = a node with CPUs and memory, out_cxl_node = a
  * node with memory and no CPUs (-1 if none).  Returns the number of online nodes. */
@@ -486,6 +487,10 @@ NV_STATUS uvmtier_tier_register(uvmtier_ctx_t *ctx, uint32_t tier, void *device_
 /* Maps the HBM tier of `peer_ctx` (another GPU of this process) as tier UVMTIER_TIER_PEER0 + peer_index of
  * `ctx`, enabling peer access both ways (the reference: UVM_GPU_LINK_NVLINK_5 peer apertures, UVM/uvm_gpu.h:611-640). */
 NV_STATUS uvmtier_tier_map_peer(uvmtier_ctx_t *ctx, uint32_t peer_index, uvmtier_ctx_t *peer_ctx);
+/* Same across processes (one process per GPU): export this context's HBM tier as a 64-byte CUDA IPC handle,
+ * import a peer's handle as tier UVMTIER_TIER_PEER0 + i (bytes = size of the peer's arena). */
+NV_STATUS uvmtier_tier_ipc_export(uvmtier_ctx_t *ctx, uint32_t tier, uint8_t handle[64]);
+NV_STATUS uvmtier_tier_ipc_import(uvmtier_ctx_t *ctx, uint32_t tier, const uint8_t handle[64], uint64_t bytes);
 NV_STATUS uvmtier_tier_info(uvmtier_ctx_t *ctx, uint32_t tier, uvmtier_tier_info_t *out);
 NV_STATUS uvmtier_tier_destroy(uvmtier_ctx_t *ctx, uint32_t tier);
 

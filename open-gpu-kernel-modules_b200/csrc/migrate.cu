@@ -54,6 +54,8 @@ static void tier_release(uvmtier_ctx_t *ctx, uvmtier_tier *t)
         munmap(t->info.host_ptr, t->info.bytes);
     if (t->cuda_alloc)
         cudaFree(t->info.device_ptr);
+    if (t->info.flags & UVMTIER_TIERF_IPC)
+        cudaIpcCloseMemHandle(t->info.device_ptr);
     memset(t, 0, sizeof(*t));
 }
 
@@ -218,6 +220,37 @@ NV_STATUS uvmtier_tier_map_peer(uvmtier_ctx_t *ctx, uint32_t peer_index, uvmtier
     cudaGetLastError();
     const uvmtier_tier_info_t *pi = &peer->tiers->t[UVMTIER_TIER_HBM].info;
     return uvmtier_tier_register(ctx, UVMTIER_TIER_PEER0 + peer_index, pi->device_ptr, NULL, pi->bytes);
+}
+
+// One process per GPU (torchrun): the peer's HBM arena arrives as a CUDA IPC handle.
+NV_STATUS uvmtier_tier_ipc_export(uvmtier_ctx_t *ctx, uint32_t tier, uint8_t handle[64])
+{
+    if (!ctx || tier >= UVMTIER_MAX_TIERS || !handle || !ctx->tiers || !ctx->tiers->t[tier].used || !ctx->tiers->t[tier].cuda_alloc)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    UVMTIER_CUDA(cudaIpcGetMemHandle(&h, ctx->tiers->t[tier].info.device_ptr));
+    static_assert(sizeof(h) == 64, "cudaIpcMemHandle_t is 64 bytes");
+    memcpy(handle, &h, 64);
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_tier_ipc_import(uvmtier_ctx_t *ctx, uint32_t tier, const uint8_t handle[64], uint64_t bytes)
+{
+    if (!ctx || tier < UVMTIER_TIER_PEER0 || tier >= UVMTIER_MAX_TIERS || !handle || !bytes)
+        return NV_ERR_INVALID_ARGUMENT;
+    uvmtier_tiers *ts = tiers_get(ctx);
+    if (!ts)
+        return NV_ERR_NO_MEMORY;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handle, 64);
+    void *p = NULL;
+    UVMTIER_CUDA(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    NV_STATUS st = uvmtier_tier_register(ctx, tier, p, NULL, bytes);
+    if (st == NV_OK)
+        ts->t[tier].info.flags |= UVMTIER_TIERF_IPC;
+    return st;
 }
 
 NV_STATUS uvmtier_tier_info(uvmtier_ctx_t *ctx, uint32_t tier, uvmtier_tier_info_t *out)

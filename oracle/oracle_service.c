@@ -242,8 +242,8 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                 rec->hint_residency = (uint16_t)hint;
                 if (hint != 257) {
                     or_or(&newres, &newres, &pf_mask);
-                    for (p = 0; p < OR_PAGES; p++) if (or_test(&newres, p)) { rf = p; break; }
-                    for (p = OR_PAGES; p-- > 0;) if (or_test(&newres, p)) { ro = p + 1; break; }
+                    for (p = 0; p < OR_WORDS; p++) if (newres.w[p]) { rf = 64 * p + (unsigned)__builtin_ctzll(newres.w[p]); break; }
+                    for (p = OR_WORDS; p-- > 0;) if (newres.w[p]) { ro = 64 * p + 64 - (unsigned)__builtin_clzll(newres.w[p]); break; }
                     rec->prefetch_count = (uint16_t)or_weight(&pf_mask);
                 }
                 else {

@@ -91,15 +91,30 @@ static inline bool __test_and_clear_bit(unsigned nr, unsigned long *m) { bool o 
 #define set_bit __set_bit
 #define clear_bit __clear_bit
 
-/* ---- bitmap API (bit-at-a-time: obviously correct beats fast in an oracle) ---- */
+/* ---- bitmap API: word-wise like Linux lib/bitmap.c, so that timing the reference through this shim is a fair
+ * CPU baseline (the semantics are exact bit math either way) ---- */
+static inline unsigned long kshim_range_word(unsigned i, long first, long outer)
+{
+    long lo = first - 64 * (long)i, hi = outer - 64 * (long)i;
+    unsigned long a, b;
+    if (lo < 0) lo = 0;
+    if (hi > 64) hi = 64;
+    if (hi <= lo) return 0;
+    a = hi == 64 ? ~0UL : ((1UL << hi) - 1);
+    b = lo == 0 ? 0 : ((1UL << lo) - 1);
+    return a & ~b;
+}
 static inline void bitmap_zero(unsigned long *d, unsigned n) { memset(d, 0, BITS_TO_LONGS(n) * sizeof(long)); }
-static inline void bitmap_fill(unsigned long *d, unsigned n) { unsigned i; bitmap_zero(d, n); for (i = 0; i < n; i++) __set_bit(i, d); }
+static inline void bitmap_fill(unsigned long *d, unsigned n) { unsigned i; for (i = 0; i < BITS_TO_LONGS(n); i++) d[i] = kshim_range_word(i, 0, n); }
 static inline void bitmap_copy(unsigned long *d, const unsigned long *s, unsigned n) { memcpy(d, s, BITS_TO_LONGS(n) * sizeof(long)); }
-static inline unsigned bitmap_weight(const unsigned long *s, unsigned n) { unsigned i, w = 0; for (i = 0; i < n; i++) w += test_bit(i, s); return w; }
+static inline unsigned bitmap_weight(const unsigned long *s, unsigned n)
+{ unsigned i, w = 0; for (i = 0; i < BITS_TO_LONGS(n); i++) w += (unsigned)__builtin_popcountl(s[i] & kshim_range_word(i, 0, n)); return w; }
 static inline bool bitmap_empty(const unsigned long *s, unsigned n) { return bitmap_weight(s, n) == 0; }
 static inline bool bitmap_full(const unsigned long *s, unsigned n) { return bitmap_weight(s, n) == n; }
-static inline void bitmap_set(unsigned long *m, unsigned start, int len) { int i; for (i = 0; i < len; i++) __set_bit(start + i, m); }
-static inline void bitmap_clear(unsigned long *m, unsigned start, int len) { int i; for (i = 0; i < len; i++) __clear_bit(start + i, m); }
+static inline void bitmap_set(unsigned long *m, unsigned start, int len)
+{ unsigned i; if (len <= 0) return; for (i = start / 64; 64 * i < start + (unsigned)len; i++) m[i] |= kshim_range_word(i, start, (long)start + len); }
+static inline void bitmap_clear(unsigned long *m, unsigned start, int len)
+{ unsigned i; if (len <= 0) return; for (i = start / 64; 64 * i < start + (unsigned)len; i++) m[i] &= ~kshim_range_word(i, start, (long)start + len); }
 static inline bool bitmap_and(unsigned long *d, const unsigned long *a, const unsigned long *b, unsigned n)
 { unsigned i; unsigned long r = 0; for (i = 0; i < BITS_TO_LONGS(n); i++) r |= (d[i] = a[i] & b[i]); return r != 0; }
 static inline bool bitmap_andnot(unsigned long *d, const unsigned long *a, const unsigned long *b, unsigned n)
@@ -116,18 +131,58 @@ static inline bool bitmap_intersects(const unsigned long *a, const unsigned long
 { unsigned i; for (i = 0; i < n; i++) if (test_bit(i, a) && test_bit(i, b)) return true; return false; }
 /* dst may alias src, as the callers in uvm_perf_prefetch.c do */
 static inline void bitmap_shift_right(unsigned long *d, const unsigned long *s, unsigned shift, unsigned n)
-{ unsigned long t[BITS_TO_LONGS(n)]; unsigned i; memset(t, 0, sizeof(t)); for (i = 0; i + shift < n; i++) if (test_bit(i + shift, s)) __set_bit(i, t); memcpy(d, t, sizeof(t)); }
+{
+    const unsigned W = BITS_TO_LONGS(n), q = shift / 64, r = shift % 64;
+    unsigned long t[BITS_TO_LONGS(n)];
+    unsigned i;
+    for (i = 0; i < W; i++) {
+        unsigned long lo = i + q < W ? s[i + q] & kshim_range_word(i + q, 0, n) : 0;
+        unsigned long hi = i + q + 1 < W ? s[i + q + 1] & kshim_range_word(i + q + 1, 0, n) : 0;
+        t[i] = r ? (lo >> r) | (hi << (64 - r)) : lo;
+    }
+    memcpy(d, t, sizeof(t));
+}
 static inline void bitmap_shift_left(unsigned long *d, const unsigned long *s, unsigned shift, unsigned n)
-{ unsigned long t[BITS_TO_LONGS(n)]; unsigned i; memset(t, 0, sizeof(t)); for (i = 0; i + shift < n; i++) if (test_bit(i, s)) __set_bit(i + shift, t); memcpy(d, t, sizeof(t)); }
+{
+    const unsigned W = BITS_TO_LONGS(n), q = shift / 64, r = shift % 64;
+    unsigned long t[BITS_TO_LONGS(n)];
+    unsigned i;
+    for (i = 0; i < W; i++) {
+        unsigned long hi = i >= q ? s[i - q] : 0, lo = i >= q + 1 ? s[i - q - 1] : 0;
+        t[i] = (r ? (hi << r) | (lo >> (64 - r)) : hi) & kshim_range_word(i, 0, n);
+    }
+    memcpy(d, t, sizeof(t));
+}
 
 static inline unsigned long find_next_bit(const unsigned long *m, unsigned long size, unsigned long off)
-{ for (; off < size; off++) if (test_bit(off, m)) return off; return size; }
+{
+    unsigned long i;
+    for (i = off / 64; 64 * i < size; i++) {
+        unsigned long w = m[i] & kshim_range_word((unsigned)i, (long)off, (long)size);
+        if (w) return 64 * i + (unsigned long)__builtin_ctzl(w);
+    }
+    return size;
+}
 static inline unsigned long find_next_zero_bit(const unsigned long *m, unsigned long size, unsigned long off)
-{ for (; off < size; off++) if (!test_bit(off, m)) return off; return size; }
+{
+    unsigned long i;
+    for (i = off / 64; 64 * i < size; i++) {
+        unsigned long w = ~m[i] & kshim_range_word((unsigned)i, (long)off, (long)size);
+        if (w) return 64 * i + (unsigned long)__builtin_ctzl(w);
+    }
+    return size;
+}
 static inline unsigned long find_first_bit(const unsigned long *m, unsigned long size) { return find_next_bit(m, size, 0); }
 static inline unsigned long find_first_zero_bit(const unsigned long *m, unsigned long size) { return find_next_zero_bit(m, size, 0); }
 static inline unsigned long find_last_bit(const unsigned long *m, unsigned long size)
-{ unsigned long i = size; while (i-- > 0) if (test_bit(i, m)) return i; return size; }
+{
+    unsigned long i = BITS_TO_LONGS(size);
+    while (i-- > 0) {
+        unsigned long w = m[i] & kshim_range_word((unsigned)i, 0, (long)size);
+        if (w) return 64 * i + 63 - (unsigned long)__builtin_clzl(w);
+    }
+    return size;
+}
 
 /* ---- list_head ---- */
 struct list_head { struct list_head *next, *prev; };

@@ -37,7 +37,7 @@ N_SPACES = 4
 VA_BYTES = 64 << 30
 N_BLOCKS = VA_BYTES >> 21
 L2_FLUSH_BYTES = 256 << 20
-RUN_CAP = 1 << 22
+RUN_CAP = 1 << 23
 METRIC = "fault entries/s preprocessed (1M-entry trace: decode+coalesce+sort+group by va_block, serviced with prefetch trees over 64 GB VA)"
 UNIT = "entries/s"
 
@@ -113,12 +113,14 @@ def build_workload(seed, trace):
     gp = TG.gpu_params(BATCH)
     n_slots = lay["blocks_per_space"] * N_SPACES
     st = HostBlockState(n_slots)
-    rs = TG.Stream(seed ^ 0x5EED, n_slots * 16 * 2)
-    a = rs.take(n_slots * 16).reshape(n_slots, 16)
-    b = rs.take(n_slots * 16).reshape(n_slots, 16)
-    cxl = (a & b).astype("<u4")                                # ~25 % of the pages live on the CXL node
-    st.cpu_resident1 = np.ascontiguousarray(cxl).view("<u8").reshape(n_slots, 8).copy()
-    st.cpu_resident0 = (~st.cpu_resident1).copy()              # the rest on host DRAM
+    # ~25 % of every va_block's 64 KB chunks live on the CXL node, the rest on host DRAM (tiering works on
+    # multi-page extents, not single pages)
+    rs = TG.Stream(seed ^ 0x5EED, n_slots * 2)
+    chunk_bits = (rs.take(n_slots) & rs.take(n_slots)).astype("<u4")                  # 32 chunks of 16 pages per block
+    chunks = np.unpackbits(chunk_bits.view(np.uint8).reshape(n_slots, 4), axis=1, bitorder="little")
+    pages = np.repeat(chunks, 16, axis=1)
+    st.cpu_resident1 = np.ascontiguousarray(np.packbits(pages, axis=1, bitorder="little")).view("<u8").reshape(n_slots, 8).copy()
+    st.cpu_resident0 = (~st.cpu_resident1).copy()
     return dict(packets=pk, table=tbl, gpu_params=gp, layout=make_layout(lay), lay=lay, state=st, n_slots=n_slots)
 
 

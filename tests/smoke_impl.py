@@ -1,7 +1,12 @@
 """smoke(): one small call per hot-path leg on cuda:0, compared with the CPU oracle."""
+import ctypes
+
 import numpy as np
 
+import faultlib as F
+import servicelib as S
 import uvmtier
+from uvmtier import TIER_DRAM, TIER_HBM, tracegen as TG
 from uvmtier_testlib import gen_prefetch_blocks, load_oracle, run_prefetch_get_hint
 
 
@@ -9,11 +14,51 @@ def run():
     orc = load_oracle()
     with uvmtier.Context(0) as ctx:
         before = uvmtier.kernel_launch_count()
+
+        # (2) prefetch hints, standalone
         inp = gen_prefetch_blocks(256, 3, full_blocks=False, aligned=False, thrashing=True)
         got = ctx.perf_prefetch_get_hint_va_block(inp["blocks"], inp["resident"], inp["faulted"], inp["thrashing"],
                                                   inp["cpu_read"], inp["info"])
         want = run_prefetch_get_hint(orc, "oracle", inp)
         for g, w, name in zip(got, want, ("prefetch mask", "hint residency", "prefetch_info")):
             assert np.array_equal(g, w), "smoke: %s differs from the oracle" % name
-        assert uvmtier.kernel_launch_count() > before, "smoke: no CUDA kernel was launched"
-    print("smoke ok: %s, %d kernel launches" % (uvmtier.lib().uvmtier_version().decode(), uvmtier.kernel_launch_count() - before))
+
+        # (1) fault batches: decode + coalesce + sort + va_block runs, then the per-block service pass
+        n_blocks = 64
+        pk, tbl, lay = TG.fault_trace(2000, 5, "stream", 2, total_va_bytes=n_blocks << 21)
+        gp = TG.gpu_params(256)
+        ctx.fault_buffer_init(gp, tbl)
+        ring = np.zeros((len(pk) + 1, 8), np.uint32)
+        ring[:len(pk)] = pk
+        r = ctx.fetch_preprocess_fault_batches(ring, 0, len(pk))
+        k1 = F.product_to_checker_view(len(pk), 256, tbl, r["disp"], r["ordered"], r["groups"], r["batch"], r["entries"],
+                                       ring[:len(pk)].copy())
+        F.assert_fetch_equal(F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl), k1, "smoke fetch/preprocess")
+        nb = len(r["batch"])
+        pad = nb * 256 - len(pk)
+        r["ordered"] = np.concatenate([r["ordered"], np.zeros(pad, r["ordered"].dtype)])
+        r["groups"] = np.concatenate([r["groups"], np.zeros(pad, r["groups"].dtype)])
+        k1["ordered_rec"], k1["groups"] = r["ordered"], r["groups"]
+        layout = S.make_layout(lay)
+        st0 = S.random_state(n_blocks, 4)
+        ds = ctx.block_state_alloc(layout)
+        ds.upload(st0)
+        svc = ctx.service_fault_batches(r, layout, ds)
+        S.assert_service_equal(S.run_service_oracle(orc, k1, gp, tbl, layout, st0), svc, 256, "smoke service")
+        ds.free()
+
+        # (3) migration: 4 KB pages DRAM -> HBM in random order, byte exact
+        nbytes = 8 << 20
+        info = {t: ctx.tier_create(t, nbytes) for t in (TIER_HBM, TIER_DRAM)}
+        src = info[TIER_DRAM].host_view()
+        src[:] = TG.rng_stream(9, nbytes // 4).view(np.uint8)
+        perm = np.random.default_rng(1).permutation(nbytes // 4096)
+        off = np.arange(nbytes // 4096, dtype=np.uint64) * np.uint64(4096)
+        ctx.copy_page_list(TIER_HBM, TIER_DRAM, perm.astype(np.uint64) * np.uint64(4096), off, 4096)
+        hbm = ctx.from_device(info[TIER_HBM].device_ptr, nbytes, np.uint8).reshape(-1, 4096)
+        assert np.array_equal(hbm[perm], src.reshape(-1, 4096)), "smoke: migrated pages differ"
+
+        launches = uvmtier.kernel_launch_count() - before
+        assert launches >= 10, "smoke: CUDA kernels were not launched"
+    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, migration)" %
+          (uvmtier.lib().uvmtier_version().decode(), launches))

@@ -379,6 +379,33 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
                                                uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
                                                uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters);
 
+/* The same servicing pass for callers that are not allowed to allocate.  (This entry point has no counterpart
+ * in the reference; it exists for the user-space setting.)
+ *
+ * A fault-servicing thread is the code that runs when GPU memory is exhausted -- servicing is what evicts and
+ * frees it -- so it cannot depend on cudaMalloc succeeding, or returning promptly, for its own working space;
+ * integrations that fix their memory budget at start-up and forbid allocator calls afterwards are in the same
+ * position.  uvmtier_service_fault_batches_device grows its working space with cudaMalloc; this variant uses a
+ * fixed array that is part of the library image instead and calls no cudaMalloc / cudaFree or any other
+ * allocating routine.  Arguments, results and semantics are those of uvmtier_service_fault_batches_device.
+ *
+ * Limits (NV_ERR_INVALID_ARGUMENT beyond them, uvmtier_last_error() says which):
+ *   n_spaces * blocks_per_space <= 65536 va_block slots (128 GB of VA),
+ *   n_batches * max_batch_size  <= 262144 entries,  n_batches <= 4096.
+ * The array is about 1.8 MB and every GPU that loads the library holds it until the process exits.
+ * The first call on a GPU looks up the array's device address (with that GPU current); make that first call
+ * before any stream capture is begun.  All calls on a GPU share the one array, which keeps the previous call's
+ * contents: the function clears the parts that have to start at zero itself, but two calls whose GPU work
+ * overlaps (different streams or contexts on the same GPU) race on it -- serialise them. */
+NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                       const uvmtier_ordered_fault_t *d_ordered,
+                                                       const uvmtier_fault_group_t *d_groups,
+                                                       uvmtier_fault_batch_t *d_batches,
+                                                       const uvmtier_va_layout_t *layout,
+                                                       const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
+                                                       uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
+                                                       uint32_t run_cap, uint32_t *d_counters);
+
 /* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */

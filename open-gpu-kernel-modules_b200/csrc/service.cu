@@ -178,3 +178,126 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Servicing pass for callers that must not allocate.
+//
+// Who: a fault handler is the one piece of code that still has to run when the GPU's memory is exhausted -- it is
+// what frees memory, by evicting.  A servicing thread in that position cannot ask cudaMalloc for working space:
+// the request may fail, or block behind the very allocator state the faults are waiting on.  The same holds for
+// a host integration that pins its memory budget up front and forbids allocator calls afterwards.
+//
+// What: the pass above keeps its working space (per-slot run counters, their scan, fill cursors, the per-block
+// run lists, one flag per batch) in buffers it grows with cudaMalloc.  This variant keeps the same working space
+// in one fixed array that is part of the library image.  Every GPU that loads the library carries the array
+// (about 1.8 MB) until the process exits; the price of never allocating is a hard ceiling on the problem size.
+constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of VA
+constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size
+constexpr uint32_t kNoAllocMaxBatches = 4096;
+constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 3 + 1024 + kNoAllocMaxBatches + kNoAllocMaxEntries;
+
+static __device__ __align__(256) uint32_t g_service_scratch[kNoAllocWords];
+
+// In host code `g_service_scratch` is only a handle for the symbol, not memory a kernel could use.  The device
+// address is looked up once per GPU, with that GPU current, and kept here.
+static uint32_t *g_service_scratch_addr[64];
+
+extern "C" NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                                  const uvmtier_ordered_fault_t *d_ordered,
+                                                                  const uvmtier_fault_group_t *d_groups,
+                                                                  uvmtier_fault_batch_t *d_batches,
+                                                                  const uvmtier_va_layout_t *lay,
+                                                                  const uvmtier_block_state_t *state,
+                                                                  uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                                  uvmtier_copy_run_t *d_runs, uint32_t run_cap,
+                                                                  uint32_t *d_counters)
+{
+    if (!ctx || !lay || !state)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n_batches)
+        return NV_OK;
+    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t B = ctx->faults->gp.max_batch_size;
+    const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * B;
+    if (!B || !n_slots64 || ctx->device < 0 || ctx->device >= 64)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (n_slots64 > kNoAllocMaxSlots || total > kNoAllocMaxEntries || n_batches > kNoAllocMaxBatches) {
+        char msg[256];
+        snprintf(msg, sizeof(msg),
+                 "uvmtier_service_fault_batches_noalloc_device: %zu va_block slots / %zu entries / %u batches exceed the "
+                 "fixed scratch (%u slots, %u entries, %u batches); use uvmtier_service_fault_batches_device",
+                 n_slots64, total, n_batches, kNoAllocMaxSlots, kNoAllocMaxEntries, kNoAllocMaxBatches);
+        uvmtier_set_error(msg, cudaErrorInvalidValue, __FILE__, __LINE__);
+        return NV_ERR_INVALID_ARGUMENT;
+    }
+    const uint32_t n_slots = (uint32_t)n_slots64;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    if (!g_service_scratch_addr[ctx->device]) {
+        uint32_t *p = NULL;
+        UVMTIER_CUDA(cudaGetSymbolAddress((void **)&p, g_service_scratch));
+        g_service_scratch_addr[ctx->device] = p;
+    }
+    uint32_t *d_count = g_service_scratch_addr[ctx->device];
+    uint32_t *d_offset = d_count + kNoAllocMaxSlots;
+    uint32_t *d_cursor = d_offset + kNoAllocMaxSlots;
+    uint32_t *d_sums = d_cursor + kNoAllocMaxSlots;
+    uint32_t *d_batch_unmapped = d_sums + 1024;
+    uint32_t *d_list = d_batch_unmapped + kNoAllocMaxBatches;
+
+    service_kparams prm;
+    prm.va_base = lay->va_base;
+    prm.B = B;
+    prm.n_batches = n_batches;
+    prm.blocks_per_space = lay->blocks_per_space;
+    prm.n_spaces = lay->n_spaces;
+    prm.gpu_id = lay->gpu_id;
+    prm.n_slots = n_slots;
+    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable;
+    prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
+    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
+    prm.run_cap = run_cap;
+
+    block_state_ptrs bs;
+    bs.gpu_resident = (uint32_t *)state->gpu_resident;
+    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0];
+    bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
+    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0];
+    bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1];
+    bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
+    bs.prefetch_info = state->prefetch_info;
+    bs.logical_prot = state->logical_prot;
+    bs.preferred_location = state->preferred_location;
+
+    // The array still holds the previous call's numbers: the counters, the cursors and the per-batch flags are
+    // accumulated into and must start at zero; offsets, partial sums and lists are fully rewritten before use.
+    UVMTIER_CUDA(cudaMemsetAsync(d_count, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_cursor, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_batch_unmapped, 0, (size_t)n_batches * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+
+    const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
+    size_t grid = (total + kSvcThreads - 1) / kSvcThreads, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, d_count,
+                   d_batch_unmapped, d_list, 0, d_offset, d_cursor);
+    const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
+    UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, d_count, n_slots, d_sums);
+    UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, d_sums, n_sums);
+    UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, d_count, n_slots, d_sums, d_offset);
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, d_count,
+                   d_batch_unmapped, d_list, 1, d_offset, d_cursor);
+    size_t bgrid = ((size_t)n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
+    if (bgrid > cap)
+        bgrid = cap;
+    UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
+                   d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_service_unmapped, (n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
+                   d_batch_unmapped, d_entry_flags, d_service);
+    return NV_OK;
+}

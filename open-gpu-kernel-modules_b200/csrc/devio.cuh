@@ -5,6 +5,13 @@
 
 #include <stdint.h>
 
+// Dynamic shared memory of the running CTA (the emulator gives every CTA the same static buffer).
+#ifdef UVMTIER_SIMT_EMU
+#define UVMTIER_DYN_SMEM(name) unsigned char *name = (unsigned char *)simt::g_dynamic_smem
+#else
+#define UVMTIER_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
+#endif
+
 #ifdef UVMTIER_SIMT_EMU
 
 static inline uint32_t ld_stream(const uint32_t *p) { return *p; }

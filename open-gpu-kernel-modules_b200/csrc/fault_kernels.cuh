@@ -57,12 +57,6 @@ __host__ __device__ inline size_t fault_smem_bytes(uint32_t T, uint32_t utlb_cou
     return sizeof(fault_smem_scalars) + (size_t)T * per_entry + tbl + (size_t)tbl_n * 16 + 64;
 }
 
-#ifdef UVMTIER_SIMT_EMU
-#define UVMTIER_DYN_SMEM(name) unsigned char *name = (unsigned char *)simt::g_dynamic_smem
-#else
-#define UVMTIER_DYN_SMEM(name) extern __shared__ __align__(16) unsigned char name[]
-#endif
-
 __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m)
 {
     uint32_t lo = __shfl_xor_sync(0xffffffffu, (uint32_t)v, m);

@@ -10,8 +10,47 @@
 #include <stdlib.h>
 
 #include "service_kernels.cuh"
+#include "service_tpb.cuh"
 
 using namespace uvmtier_k;
+
+// Tail of the pass, shared by the two entry points: sort every slot's run list, service the va_blocks (one thread
+// per block), then the runs that belong to no va_range.  UVMTIER_SERVICE_WARP_PER_BLOCK=1 selects the older
+// warp-per-block kernel (kept for comparison; same results).
+static NV_STATUS launch_block_service(uvmtier_ctx_t *ctx, const service_kparams &prm, const uvmtier_ordered_fault_t *d_ordered,
+                                      const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                      const uvmtier_instance_ptr_entry_t *d_tbl, const block_state_ptrs &bs, uint32_t *d_count,
+                                      uint32_t *d_offset, uint32_t *d_list, uint32_t *d_batch_unmapped, uint16_t *d_entry_flags,
+                                      uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t *d_counters)
+{
+    static const bool warp_per_block = getenv("UVMTIER_SERVICE_WARP_PER_BLOCK") != NULL;
+    const size_t cap = (size_t)ctx->sm_count * 8;
+    if (warp_per_block) {
+        size_t bgrid = ((size_t)prm.n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
+        if (bgrid > cap)
+            bgrid = cap;
+        UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
+                       d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
+    }
+    else {
+        static bool attr_set[64];
+        if (!attr_set[ctx->device & 63]) {
+            // opt in to the 16 KB of dynamic shared memory of the list sorter (below the 48 KB default: no-op, kept explicit)
+            UVMTIER_CUDA(cudaFuncSetAttribute(k_service_sort_lists, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                              (int)(kSortSmemKeys * sizeof(uint32_t))));
+            attr_set[ctx->device & 63] = true;
+        }
+        size_t sgrid = prm.n_slots < (size_t)ctx->sm_count * 32 ? prm.n_slots : (size_t)ctx->sm_count * 32;
+        UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, 32, kSortSmemKeys * sizeof(uint32_t), ctx->stream, prm.n_slots, d_count,
+                       d_offset, d_list);
+        const uint32_t tgrid = (prm.n_slots + kTpbThreads - 1) / kTpbThreads;
+        UVMTIER_LAUNCH(k_service_blocks_tpb, tgrid, kTpbThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
+                       d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
+    }
+    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
+                   d_batch_unmapped, d_entry_flags, d_service);
+    return NV_OK;
+}
 
 static NV_STATUS scratch_reserve(uvmtier_ctx_t *ctx, uint32_t n_slots, uint32_t n_batches, size_t list_entries)
 {
@@ -167,14 +206,8 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
     UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, s->d_count, n_slots, s->d_sums, s->d_offset);
     UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, s->d_count,
                    s->d_batch_unmapped, s->d_list, 1, s->d_offset, s->d_cursor);
-    size_t bgrid = ((size_t)n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
-    if (bgrid > cap)
-        bgrid = cap;
-    UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
-                   s->d_count, s->d_offset, s->d_list, d_entry_flags, d_service, d_runs, d_counters);
-    UVMTIER_LAUNCH(k_service_unmapped, (n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches,
-                   d_tbl, s->d_batch_unmapped, d_entry_flags, d_service);
-    return NV_OK;
+    return launch_block_service(ctx, prm, d_ordered, d_groups, d_batches, d_tbl, bs, s->d_count, s->d_offset, s->d_list,
+                                s->d_batch_unmapped, d_entry_flags, d_service, d_runs, d_counters);
 }
 
 } // extern "C"
@@ -292,12 +325,6 @@ extern "C" NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t 
     UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, d_count, n_slots, d_sums, d_offset);
     UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, d_count,
                    d_batch_unmapped, d_list, 1, d_offset, d_cursor);
-    size_t bgrid = ((size_t)n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
-    if (bgrid > cap)
-        bgrid = cap;
-    UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
-                   d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
-    UVMTIER_LAUNCH(k_service_unmapped, (n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
-                   d_batch_unmapped, d_entry_flags, d_service);
-    return NV_OK;
+    return launch_block_service(ctx, prm, d_ordered, d_groups, d_batches, d_tbl, bs, d_count, d_offset, d_list, d_batch_unmapped,
+                                d_entry_flags, d_service, d_runs, d_counters);
 }

@@ -66,7 +66,7 @@ def run_service_oracle(orc, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap
     return dict(flags=flags, records=svc[:nsvc], runs=runs, n_runs=n_runs.value, batch=batch, state=st)
 
 
-def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20):
+def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, warp_per_block=0):
     B = int(gp["max_batch_size"][0])
     nb = len(k1["batch"])
     flags, svc, runs, counters = _alloc_outputs(nb, B, run_cap)
@@ -75,7 +75,8 @@ def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1
     ptrs = st.ptrs()
     sim.simt_service_fault_batches(ctypes.c_uint32(nb), ctypes.c_uint32(B), P(k1["ordered_rec"]), P(k1["groups"]), P(batch),
                                    P(table), P(layout), ctypes.byref(ptrs), ctypes.c_uint32(pf[0]), ctypes.c_uint32(pf[1]),
-                                   ctypes.c_uint32(pf[2]), P(flags), P(svc), P(runs), ctypes.c_uint32(run_cap), P(counters))
+                                   ctypes.c_uint32(pf[2]), P(flags), P(svc), P(runs), ctypes.c_uint32(run_cap), P(counters),
+                                   ctypes.c_int(warp_per_block))
     return dict(flags=flags, service=svc, runs=runs, n_runs=int(counters[0]), batch=batch, state=st)
 
 

@@ -5,6 +5,7 @@
 #include <vector>
 
 #include "service_kernels.cuh"
+#include "service_tpb.cuh"
 
 using namespace uvmtier_k;
 
@@ -13,7 +14,7 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
                                           const uvmtier_instance_ptr_entry_t *tbl, const uvmtier_va_layout_t *lay,
                                           const uvmtier_block_state_t *state, uint32_t pf_enable, uint32_t pf_threshold,
                                           uint32_t pf_min_faults, uint16_t *entry_flags, uvmtier_service_group_t *service,
-                                          uvmtier_copy_run_t *runs, uint32_t run_cap, uint32_t *counters)
+                                          uvmtier_copy_run_t *runs, uint32_t run_cap, uint32_t *counters, int warp_per_block)
 {
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
     const size_t total = (size_t)n_batches * B;
@@ -36,7 +37,14 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
     simt::launch(dim3(1), dim3(1024), [&] { k_scan_top(sums.data(), n_sums); });
     simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_final(count.data(), n_slots, sums.data(), offset.data()); });
     simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count.data(), unmapped.data(), list.data(), 1, offset.data(), cursor.data()); });
-    simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, count.data(), offset.data(), list.data(), entry_flags, service, runs, counters); });
+    if (warp_per_block) {
+        simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, count.data(), offset.data(), list.data(), entry_flags, service, runs, counters); });
+    }
+    else {
+        simt::launch(dim3(5), dim3(32), [&] { k_service_sort_lists(n_slots, count.data(), offset.data(), list.data()); });
+        simt::launch(dim3((n_slots + kTpbThreads - 1) / kTpbThreads), dim3(kTpbThreads),
+                     [&] { k_service_blocks_tpb(prm, ordered, groups, batches, bs, count.data(), offset.data(), list.data(), entry_flags, service, runs, counters); });
+    }
     simt::launch(dim3((n_batches + 127) / 128), dim3(128), [&] { k_service_unmapped(prm, ordered, groups, batches, tbl, unmapped.data(), entry_flags, service); });
     return 0;
 }

@@ -25,9 +25,8 @@ struct uvmtier_fault_state {
 
 // Scratch of the servicing pass (service.cu), grown on demand and reused.
 struct uvmtier_service_scratch {
-    uint32_t *d_count, *d_offset, *d_cursor, *d_sums, *d_batch_unmapped, *d_list;
-    uint32_t n_slots_cap, n_batches_cap;
-    size_t list_cap;
+    uint32_t *d_base;
+    size_t cap_words;
 };
 
 struct uvmtier_ctx {

@@ -1,93 +1,190 @@
 // service.cu -- C-ABI entry points of the per-va_block servicing pass (stage C/D/E) and the block state table.
 // Reference: UVM/uvm_gpu_replayable_faults.c:2232-2377 (service_fault_batch) and callees; see service_kernels.cuh.
 //
-// Scratch in HBM (owned by the context, grown on demand, reused by every call): per-slot run counters, their
-// exclusive scan and fill cursors (3 x 4 B x n_slots), the per-block run lists (4 B per run) and one flag per
-// batch.  Algorithmic bytes per serviced va_block run: 16 (run) + 16 per entry + 2 per entry flag + 96 record
+// Working space in HBM (one buffer owned by the context, grown on demand and reused; or the fixed array of the
+// no-alloc entry point): per slot the number of runs, a fill cursor, the number of entries and the start of its
+// run list (4 x 4 B x n_slots), the run lists (4 B per run), one flag per batch and two short work lists.
+// Algorithmic bytes per serviced va_block run: 16 (run) + 16 per entry + 2 per entry flag + 96 record
 // + the block's state (6 masks x 64 B + 8 B) read and written once per touched block, + 8 per copy run.
 #include "common.cuh"
 
 #include <stdlib.h>
 
 #include "service_kernels.cuh"
-#include "service_tpb.cuh"
+#include "service_grp.cuh"
 
 using namespace uvmtier_k;
 
-// Tail of the pass, shared by the two entry points: sort every slot's run list, service the va_blocks (one thread
-// per block), then the runs that belong to no va_range.  UVMTIER_SERVICE_WARP_PER_BLOCK=1 selects the older
-// warp-per-block kernel (kept for comparison; same results).
-static NV_STATUS launch_block_service(uvmtier_ctx_t *ctx, const service_kparams &prm, const uvmtier_ordered_fault_t *d_ordered,
-                                      const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
-                                      const uvmtier_instance_ptr_entry_t *d_tbl, const block_state_ptrs &bs, uint32_t *d_count,
-                                      uint32_t *d_offset, uint32_t *d_list, uint32_t *d_batch_unmapped, uint16_t *d_entry_flags,
-                                      uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t *d_counters)
+// A slot whose runs hold this many entries or more is serviced by a whole warp (entries filtered 32 at a time)
+// instead of a small group of lanes (entries one after the other).
+constexpr uint32_t kHeavyMinEntries = 96;
+
+// Carves the working space for one call out of `base`.
+struct service_scratch_view {
+    uint32_t *count, *cursor, *weight, *big, *heavy, *batch_unmapped;    // zeroed at the start of every call
+    uint32_t *offset, *sums, *list;                                      // fully rewritten before use
+    size_t zero_words, words;
+};
+static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint32_t n_batches, size_t total)
 {
-    static const bool warp_per_block = getenv("UVMTIER_SERVICE_WARP_PER_BLOCK") != NULL;
-    const size_t cap = (size_t)ctx->sm_count * 8;
-    if (warp_per_block) {
-        size_t bgrid = ((size_t)prm.n_slots + (kSvcThreads / 32) - 1) / (kSvcThreads / 32);
-        if (bgrid > cap)
-            bgrid = cap;
-        UVMTIER_LAUNCH(k_service_blocks, (int)bgrid, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
-                       d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
+    service_scratch_view v;
+    const size_t slots4 = ((size_t)n_slots + 3) & ~(size_t)3;            // keeps every array 16-byte aligned
+    const size_t big_cap = ((total / kSortWarpKeys + 2) + 3) & ~(size_t)3;
+    const size_t heavy_cap = ((total / kHeavyMinEntries + 2) + 3) & ~(size_t)3;
+    const size_t batches4 = ((size_t)n_batches + 3) & ~(size_t)3;
+    uint32_t *p = base;
+    v.count = p; p += slots4;
+    v.cursor = p; p += slots4;
+    v.weight = p; p += slots4;
+    v.big = p; p += big_cap;
+    v.heavy = p; p += heavy_cap;
+    v.batch_unmapped = p; p += batches4;
+    v.zero_words = (size_t)(p - base);
+    v.offset = p; p += slots4;
+    v.sums = p; p += 1024;
+    v.list = p; p += (total + 3) & ~(size_t)3;
+    v.words = (size_t)(p - base);
+    return v;
+}
+
+static uint32_t service_lanes_per_block()
+{
+    static int lanes = -1;
+    if (lanes < 0) {
+        const char *e = getenv("UVMTIER_SERVICE_LANES");
+        const int v = e ? atoi(e) : 4;
+        lanes = (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 4;
     }
-    else {
-        static bool attr_set[64];
-        if (!attr_set[ctx->device & 63]) {
-            // opt in to the 16 KB of dynamic shared memory of the list sorter (below the 48 KB default: no-op, kept explicit)
-            UVMTIER_CUDA(cudaFuncSetAttribute(k_service_sort_lists, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                              (int)(kSortSmemKeys * sizeof(uint32_t))));
-            attr_set[ctx->device & 63] = true;
-        }
-        size_t sgrid = prm.n_slots < (size_t)ctx->sm_count * 32 ? prm.n_slots : (size_t)ctx->sm_count * 32;
-        UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, 32, kSortSmemKeys * sizeof(uint32_t), ctx->stream, prm.n_slots, d_count,
-                       d_offset, d_list);
-        const uint32_t tgrid = (prm.n_slots + kTpbThreads - 1) / kTpbThreads;
-        UVMTIER_LAUNCH(k_service_blocks_tpb, tgrid, kTpbThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, d_count,
-                       d_offset, d_list, d_entry_flags, d_service, d_runs, d_counters);
-    }
-    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
-                   d_batch_unmapped, d_entry_flags, d_service);
+    return (uint32_t)lanes;
+}
+
+template <int G>
+static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, const uvmtier_ordered_fault_t *d_ordered,
+                            const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const block_state_ptrs &bs,
+                            const service_scratch_view &v, uint32_t heavy_min, uint16_t *d_entry_flags,
+                            uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t *d_counters)
+{
+    const size_t threads = (size_t)prm.n_slots * G;
+    const uint32_t grid = (uint32_t)((threads + kGrpThreads - 1) / kGrpThreads);
+    UVMTIER_LAUNCH(k_service_blocks_grp<G>, grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, v.count,
+                   v.offset, v.list, v.weight, heavy_min, d_entry_flags, d_service, d_runs, d_counters);
     return NV_OK;
 }
 
-static NV_STATUS scratch_reserve(uvmtier_ctx_t *ctx, uint32_t n_slots, uint32_t n_batches, size_t list_entries)
+// The whole pass on the context's stream, working space at `base` (v.words words).
+static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,
+                              const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const uvmtier_va_layout_t *lay,
+                              const uvmtier_block_state_t *state, uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                              uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters)
 {
-    uvmtier_service_scratch *s = &ctx->svc;
-    if (n_slots > s->n_slots_cap) {
-        if (s->d_count) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_count); s->d_count = NULL; s->n_slots_cap = 0; }
-        // count | offset | cursor | sums(1024)
-        UVMTIER_CUDA(cudaMalloc(&s->d_count, ((size_t)n_slots * 3 + 1024) * sizeof(uint32_t)));
-        s->d_offset = s->d_count + n_slots;
-        s->d_cursor = s->d_offset + n_slots;
-        s->d_sums = s->d_cursor + n_slots;
-        s->n_slots_cap = n_slots;
+    const uint32_t B = ctx->faults->gp.max_batch_size;
+    const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * B;
+    const service_scratch_view v = scratch_view(base, n_slots, n_batches, total);
+
+    service_kparams prm;
+    prm.va_base = lay->va_base;
+    prm.B = B;
+    prm.n_batches = n_batches;
+    prm.blocks_per_space = lay->blocks_per_space;
+    prm.n_spaces = lay->n_spaces;
+    prm.gpu_id = lay->gpu_id;
+    prm.n_slots = n_slots;
+    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable;
+    prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
+    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
+    prm.run_cap = run_cap;
+    prm.B_shift = svc_log2_or_none(B);
+
+    block_state_ptrs bs;
+    bs.gpu_resident = (uint32_t *)state->gpu_resident;
+    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0];
+    bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
+    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0];
+    bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1];
+    bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
+    bs.prefetch_info = state->prefetch_info;
+    bs.logical_prot = state->logical_prot;
+    bs.preferred_location = state->preferred_location;
+
+    // The working space still holds the previous call's numbers.  Counters, cursors, entry totals, the two work
+    // lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset: they are
+    // adjacent); offsets, partial sums and run lists are fully rewritten before they are read.
+    UVMTIER_CUDA(cudaMemsetAsync(base, 0, v.zero_words * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+
+    const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
+    const size_t cap = (size_t)ctx->sm_count * 8;
+    size_t grid = (total + kSvcThreads - 1) / kSvcThreads;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, v.count, v.weight,
+                   v.batch_unmapped, v.list, 0, v.offset, v.cursor);
+    if (n_slots <= kScanSingleMax) {
+        UVMTIER_LAUNCH(k_scan_single, 1, 1024, 0, ctx->stream, v.count, n_slots, v.offset);
     }
-    else if (s->d_count) {
-        s->d_offset = s->d_count + s->n_slots_cap;
-        s->d_cursor = s->d_offset + s->n_slots_cap;
-        s->d_sums = s->d_cursor + s->n_slots_cap;
+    else {
+        const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
+        UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, v.count, n_slots, v.sums);
+        UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, v.sums, n_sums);
+        UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, v.count, n_slots, v.sums, v.offset);
     }
-    if (n_batches > s->n_batches_cap) {
-        if (s->d_batch_unmapped) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_batch_unmapped); s->d_batch_unmapped = NULL; }
-        UVMTIER_CUDA(cudaMalloc(&s->d_batch_unmapped, (size_t)n_batches * sizeof(uint32_t)));
-        s->n_batches_cap = n_batches;
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, v.count, v.weight,
+                   v.batch_unmapped, v.list, 1, v.offset, v.cursor);
+
+    // UVMTIER_SERVICE_HEAVY_MIN moves the group / warp split up (for experiments; 0xffffffff = no block on a warp).
+    // It cannot go below kHeavyMinEntries: that is what bounds the length of the heavy list.
+    static const char *heavy_env = getenv("UVMTIER_SERVICE_HEAVY_MIN");
+    const uint32_t heavy_min = heavy_env ? (uint32_t)strtoul(heavy_env, NULL, 0) : kHeavyMinEntries;
+    const uint32_t list_heavy_min = heavy_min < kHeavyMinEntries ? kHeavyMinEntries : heavy_min;
+    size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
+    if (sgrid > cap)
+        sgrid = cap;
+    UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, v.count, v.offset, v.list, v.weight,
+                   list_heavy_min, v.big, v.heavy);
+    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, v.count, v.offset, v.list, v.big);
+
+    NV_STATUS st = NV_OK;
+    switch (service_lanes_per_block()) {
+        case 1: st = launch_grp<1>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
+        case 2: st = launch_grp<2>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
+        case 8: st = launch_grp<8>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
+        case 16: st = launch_grp<16>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
+        default: st = launch_grp<4>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
     }
-    if (list_entries > s->list_cap) {
-        if (s->d_list) { cudaStreamSynchronize(ctx->stream); cudaFree(s->d_list); s->d_list = NULL; }
-        UVMTIER_CUDA(cudaMalloc(&s->d_list, list_entries * sizeof(uint32_t)));
-        s->list_cap = list_entries;
-    }
+    if (st != NV_OK)
+        return st;
+    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, v.count,
+                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
+                   v.batch_unmapped, d_entry_flags, d_service);
+    return NV_OK;
+}
+
+static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, const void *d_ordered, const void *d_groups,
+                                    const void *d_batches, const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                    const void *d_entry_flags, const void *d_service, const void *d_runs, uint32_t run_cap,
+                                    const void *d_counters)
+{
+    if (!ctx || !lay || !state)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n_batches)
+        return NV_OK;
+    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
+        return NV_ERR_INVALID_ARGUMENT;
+    const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
+    if (!ctx->faults->gp.max_batch_size || n_slots64 == 0 || n_slots64 > (size_t)1024 * kScanItems)
+        return NV_ERR_INVALID_ARGUMENT;
     return NV_OK;
 }
 
 void uvmtier_service_scratch_destroy(uvmtier_ctx_t *ctx)
 {
     uvmtier_service_scratch *s = &ctx->svc;
-    if (s->d_count) cudaFree(s->d_count);
-    if (s->d_batch_unmapped) cudaFree(s->d_batch_unmapped);
-    if (s->d_list) cudaFree(s->d_list);
+    if (s->d_base) cudaFree(s->d_base);
     memset(s, 0, sizeof(*s));
 }
 
@@ -143,71 +240,27 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
                                                uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
                                                uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters)
 {
-    if (!ctx || !lay || !state)
-        return NV_ERR_INVALID_ARGUMENT;
-    if (!ctx->faults)
-        return NV_ERR_INVALID_STATE;
-    if (!n_batches)
-        return NV_OK;
-    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
-        return NV_ERR_INVALID_ARGUMENT;
-    const uint32_t B = ctx->faults->gp.max_batch_size;
-    const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
-    if (!B || n_slots64 == 0 || n_slots64 > (size_t)1024 * kScanItems)
-        return NV_ERR_INVALID_ARGUMENT;
-    const uint32_t n_slots = (uint32_t)n_slots64;
-    const size_t total = (size_t)n_batches * B;
+    const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                                            d_runs, run_cap, d_counters);
+    if (ok != NV_OK || !n_batches)
+        return ok;
+    const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * ctx->faults->gp.max_batch_size;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
-    NV_STATUS st = scratch_reserve(ctx, n_slots, n_batches, total);
-    if (st != NV_OK)
-        return st;
     uvmtier_service_scratch *s = &ctx->svc;
-
-    service_kparams prm;
-    prm.va_base = lay->va_base;
-    prm.B = B;
-    prm.n_batches = n_batches;
-    prm.blocks_per_space = lay->blocks_per_space;
-    prm.n_spaces = lay->n_spaces;
-    prm.gpu_id = lay->gpu_id;
-    prm.n_slots = n_slots;
-    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable;
-    prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
-    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
-    prm.run_cap = run_cap;
-
-    block_state_ptrs bs;
-    bs.gpu_resident = (uint32_t *)state->gpu_resident;
-    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0];
-    bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
-    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0];
-    bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1];
-    bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
-    bs.prefetch_info = state->prefetch_info;
-    bs.logical_prot = state->logical_prot;
-    bs.preferred_location = state->preferred_location;
-
-    // count + cursor are zeroed together (offset lies between them and is fully rewritten by the scan)
-    UVMTIER_CUDA(cudaMemsetAsync(s->d_count, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(s->d_cursor, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(s->d_batch_unmapped, 0, (size_t)n_batches * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
-
-    const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
-    size_t grid = (total + kSvcThreads - 1) / kSvcThreads, cap = (size_t)ctx->sm_count * 8;
-    if (grid > cap)
-        grid = cap;
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, s->d_count,
-                   s->d_batch_unmapped, s->d_list, 0, s->d_offset, s->d_cursor);
-    const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
-    UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, s->d_count, n_slots, s->d_sums);
-    UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, s->d_sums, n_sums);
-    UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, s->d_count, n_slots, s->d_sums, s->d_offset);
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, s->d_count,
-                   s->d_batch_unmapped, s->d_list, 1, s->d_offset, s->d_cursor);
-    return launch_block_service(ctx, prm, d_ordered, d_groups, d_batches, d_tbl, bs, s->d_count, s->d_offset, s->d_list,
-                                s->d_batch_unmapped, d_entry_flags, d_service, d_runs, d_counters);
+    const size_t words = scratch_view(NULL, n_slots, n_batches, total).words;
+    if (words > s->cap_words) {
+        if (s->d_base) {
+            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+            UVMTIER_CUDA(cudaFree(s->d_base));
+            s->d_base = NULL;
+            s->cap_words = 0;
+        }
+        UVMTIER_CUDA(cudaMalloc(&s->d_base, words * sizeof(uint32_t)));
+        s->cap_words = words;
+    }
+    return service_pass(ctx, s->d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service, d_runs,
+                        run_cap, d_counters);
 }
 
 } // extern "C"
@@ -220,14 +273,16 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
 // the request may fail, or block behind the very allocator state the faults are waiting on.  The same holds for
 // a host integration that pins its memory budget up front and forbids allocator calls afterwards.
 //
-// What: the pass above keeps its working space (per-slot run counters, their scan, fill cursors, the per-block
-// run lists, one flag per batch) in buffers it grows with cudaMalloc.  This variant keeps the same working space
-// in one fixed array that is part of the library image.  Every GPU that loads the library carries the array
-// (about 1.8 MB) until the process exits; the price of never allocating is a hard ceiling on the problem size.
+// What: the pass above keeps its working space in a buffer it grows with cudaMalloc.  This variant keeps the same
+// working space in one fixed array that is part of the library image.  Every GPU that loads the library carries
+// the array (about 2.1 MB) until the process exits; the price of never allocating is a hard ceiling on the
+// problem size.
 constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of VA
 constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size
 constexpr uint32_t kNoAllocMaxBatches = 4096;
-constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 3 + 1024 + kNoAllocMaxBatches + kNoAllocMaxEntries;
+// scratch_view() of the largest problem, with room for its alignment padding
+constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 4 + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
+                                 (kNoAllocMaxEntries / kHeavyMinEntries + 8) + kNoAllocMaxBatches + 1024 + kNoAllocMaxEntries + 64;
 
 static __device__ __align__(256) uint32_t g_service_scratch[kNoAllocWords];
 
@@ -245,86 +300,36 @@ extern "C" NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t 
                                                                   uvmtier_copy_run_t *d_runs, uint32_t run_cap,
                                                                   uint32_t *d_counters)
 {
-    if (!ctx || !lay || !state)
-        return NV_ERR_INVALID_ARGUMENT;
-    if (!ctx->faults)
-        return NV_ERR_INVALID_STATE;
-    if (!n_batches)
-        return NV_OK;
-    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
-        return NV_ERR_INVALID_ARGUMENT;
-    const uint32_t B = ctx->faults->gp.max_batch_size;
-    const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
-    const size_t total = (size_t)n_batches * B;
-    if (!B || !n_slots64 || ctx->device < 0 || ctx->device >= 64)
-        return NV_ERR_INVALID_ARGUMENT;
-    if (n_slots64 > kNoAllocMaxSlots || total > kNoAllocMaxEntries || n_batches > kNoAllocMaxBatches) {
-        char msg[256];
-        snprintf(msg, sizeof(msg),
-                 "uvmtier_service_fault_batches_noalloc_device: %zu va_block slots / %zu entries / %u batches exceed the "
-                 "fixed scratch (%u slots, %u entries, %u batches); use uvmtier_service_fault_batches_device",
-                 n_slots64, total, n_batches, kNoAllocMaxSlots, kNoAllocMaxEntries, kNoAllocMaxBatches);
-        uvmtier_set_error(msg, cudaErrorInvalidValue, __FILE__, __LINE__);
-        return NV_ERR_INVALID_ARGUMENT;
+    if (ctx && lay && ctx->faults) {
+        // the size ceiling is checked before anything else so that an oversized request is reported as such
+        const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
+        const size_t total = (size_t)n_batches * ctx->faults->gp.max_batch_size;
+        if (n_slots64 > kNoAllocMaxSlots || total > kNoAllocMaxEntries || n_batches > kNoAllocMaxBatches) {
+            char msg[256];
+            snprintf(msg, sizeof(msg),
+                     "uvmtier_service_fault_batches_noalloc_device: %zu va_block slots / %zu entries / %u batches exceed the "
+                     "fixed scratch (%u slots, %u entries, %u batches); use uvmtier_service_fault_batches_device",
+                     n_slots64, total, n_batches, kNoAllocMaxSlots, kNoAllocMaxEntries, kNoAllocMaxBatches);
+            uvmtier_set_error(msg, cudaErrorInvalidValue, __FILE__, __LINE__);
+            return NV_ERR_INVALID_ARGUMENT;
+        }
     }
-    const uint32_t n_slots = (uint32_t)n_slots64;
+    const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                                            d_runs, run_cap, d_counters);
+    if (ok != NV_OK || !n_batches)
+        return ok;
+    if (ctx->device < 0 || ctx->device >= 64)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * ctx->faults->gp.max_batch_size;
+    if (scratch_view(NULL, n_slots, n_batches, total).words > kNoAllocWords)
+        return NV_ERR_INVALID_ARGUMENT;                                   // cannot happen within the three limits above
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     if (!g_service_scratch_addr[ctx->device]) {
         uint32_t *p = NULL;
         UVMTIER_CUDA(cudaGetSymbolAddress((void **)&p, g_service_scratch));
         g_service_scratch_addr[ctx->device] = p;
     }
-    uint32_t *d_count = g_service_scratch_addr[ctx->device];
-    uint32_t *d_offset = d_count + kNoAllocMaxSlots;
-    uint32_t *d_cursor = d_offset + kNoAllocMaxSlots;
-    uint32_t *d_sums = d_cursor + kNoAllocMaxSlots;
-    uint32_t *d_batch_unmapped = d_sums + 1024;
-    uint32_t *d_list = d_batch_unmapped + kNoAllocMaxBatches;
-
-    service_kparams prm;
-    prm.va_base = lay->va_base;
-    prm.B = B;
-    prm.n_batches = n_batches;
-    prm.blocks_per_space = lay->blocks_per_space;
-    prm.n_spaces = lay->n_spaces;
-    prm.gpu_id = lay->gpu_id;
-    prm.n_slots = n_slots;
-    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable;
-    prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
-    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
-    prm.run_cap = run_cap;
-
-    block_state_ptrs bs;
-    bs.gpu_resident = (uint32_t *)state->gpu_resident;
-    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0];
-    bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
-    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0];
-    bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1];
-    bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
-    bs.prefetch_info = state->prefetch_info;
-    bs.logical_prot = state->logical_prot;
-    bs.preferred_location = state->preferred_location;
-
-    // The array still holds the previous call's numbers: the counters, the cursors and the per-batch flags are
-    // accumulated into and must start at zero; offsets, partial sums and lists are fully rewritten before use.
-    UVMTIER_CUDA(cudaMemsetAsync(d_count, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_cursor, 0, (size_t)n_slots * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_batch_unmapped, 0, (size_t)n_batches * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
-
-    const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
-    size_t grid = (total + kSvcThreads - 1) / kSvcThreads, cap = (size_t)ctx->sm_count * 8;
-    if (grid > cap)
-        grid = cap;
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, d_count,
-                   d_batch_unmapped, d_list, 0, d_offset, d_cursor);
-    const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
-    UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, d_count, n_slots, d_sums);
-    UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, d_sums, n_sums);
-    UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, d_count, n_slots, d_sums, d_offset);
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, d_count,
-                   d_batch_unmapped, d_list, 1, d_offset, d_cursor);
-    return launch_block_service(ctx, prm, d_ordered, d_groups, d_batches, d_tbl, bs, d_count, d_offset, d_list, d_batch_unmapped,
-                                d_entry_flags, d_service, d_runs, d_counters);
+    return service_pass(ctx, g_service_scratch_addr[ctx->device], n_batches, d_ordered, d_groups, d_batches, lay, state,
+                        d_entry_flags, d_service, d_runs, run_cap, d_counters);
 }

@@ -38,7 +38,22 @@ struct service_kparams {
     uint32_t blocks_per_space, n_spaces, gpu_id, n_slots;
     uint32_t pf_enable, pf_threshold, pf_min_faults;
     uint32_t run_cap;
+    uint32_t B_shift;                          // log2(B) when B is a power of two, else 0xffffffff
 };
+
+__host__ __device__ __forceinline__ uint32_t svc_log2_or_none(uint32_t B)
+{
+    for (uint32_t s = 0; s < 32; s++)
+        if ((1u << s) == B)
+            return s;
+    return 0xffffffffu;
+}
+
+// Batch of ordered-array / group position t (B entries per batch).
+__device__ __forceinline__ uint32_t svc_batch_of(const service_kparams &prm, uint32_t t)
+{
+    return prm.B_shift != 0xffffffffu ? t >> prm.B_shift : t / prm.B;
+}
 
 struct block_state_ptrs {
     uint32_t *gpu_resident;
@@ -68,8 +83,8 @@ __device__ __forceinline__ uint32_t svc_slot(const service_kparams &prm, uint32_
 __global__ void __launch_bounds__(kSvcThreads)
 k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ groups,
                 const uvmtier_fault_batch_t *__restrict__ batches, const uvmtier_instance_ptr_entry_t *__restrict__ tbl,
-                uint32_t *__restrict__ count, uint32_t *__restrict__ batch_unmapped, uint32_t *__restrict__ list, int fill,
-                const uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
+                uint32_t *__restrict__ count, uint32_t *__restrict__ weight, uint32_t *__restrict__ batch_unmapped,
+                uint32_t *__restrict__ list, int fill, const uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
 {
     const uint32_t total = prm.n_batches * prm.B;
     for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
@@ -86,8 +101,10 @@ k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ g
                 batch_unmapped[b] = 1u;
             continue;
         }
-        if (!fill)
+        if (!fill) {
             atomicAdd(&count[slot], 1u);
+            atomicAdd(&weight[slot], (uint32_t)grp.block_faults);
+        }
         else
             list[offset[slot] + atomicAdd(&cursor[slot], 1u)] = t;
     }
@@ -170,6 +187,165 @@ k_scan_final(const uint32_t *__restrict__ in, uint32_t n, const uint32_t *__rest
     }
 }
 
+// The same scan in one launch for tables of up to kScanSingleMax slots (three launches cost more than the work):
+// one CTA, thread t owns `per` consecutive elements (per is a multiple of 4, the arrays are 16-byte aligned).
+constexpr uint32_t kScanSingleMax = 1u << 17;
+__global__ void __launch_bounds__(1024)
+k_scan_single(const uint32_t *__restrict__ in, uint32_t n, uint32_t *__restrict__ out)
+{
+    __shared__ uint32_t s_w[32];
+    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const uint32_t per = (((n + 1023u) / 1024u) + 3u) & ~3u;
+    const uint32_t base = tid * per;
+    uint32_t tot = 0;
+    for (uint32_t k = 0; k < per; k += 4) {
+        if (base + k + 4 <= n) {
+            const uint4 v = *(const uint4 *)(in + base + k);
+            tot += v.x + v.y + v.z + v.w;
+        }
+        else {
+            for (uint32_t j = base + k; j < n && j < base + k + 4; j++) tot += in[j];
+        }
+    }
+    uint32_t x = tot;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+        if ((int)lane >= d) x += y;
+    }
+    if (lane == 31) s_w[warp] = x;
+    __syncthreads();
+    if (warp == 0) {
+        uint32_t w = s_w[lane];
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, w, d);
+            if ((int)lane >= d) w += y;
+        }
+        s_w[lane] = w;
+    }
+    __syncthreads();
+    uint32_t run = (warp ? s_w[warp - 1] : 0u) + x - tot;
+    for (uint32_t k = 0; k < per; k += 4) {
+        if (base + k + 4 <= n) {
+            const uint4 v = *(const uint4 *)(in + base + k);
+            *(uint4 *)(out + base + k) = make_uint4(run, run + v.x, run + v.x + v.y, run + v.x + v.y + v.z);
+            run += v.x + v.y + v.z + v.w;
+        }
+        else {
+            for (uint32_t j = base + k; j < n && j < base + k + 4; j++) {
+                out[j] = run;
+                run += in[j];
+            }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sorts every slot's run list ascending (the fill pass appends in whatever order its atomics land) and sorts the
+// slots themselves into three classes for the kernels that follow:
+//   lists of more than kSortWarpKeys runs are left to k_service_sort_big   -> big[0] = how many, big[1..] = slots
+//   slots whose runs hold heavy_min or more entries go to k_service_blocks -> heavy[0] = how many, heavy[1..]
+//   everything else is serviced by k_service_blocks_grp.
+// One warp per slot: up to 32 runs in registers, up to kSortWarpKeys in the warp's slice of shared memory.
+constexpr uint32_t kSortWarpKeys = 512;
+constexpr int kSortThreads = 256;
+__global__ void __launch_bounds__(kSortThreads)
+k_service_sort_lists(uint32_t n_slots, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
+                     uint32_t *__restrict__ list, const uint32_t *__restrict__ weight, uint32_t heavy_min,
+                     uint32_t *__restrict__ big, uint32_t *__restrict__ heavy)
+{
+    __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
+    const int lane = threadIdx.x & 31;
+    uint32_t *s_keys = s_all + (threadIdx.x >> 5) * kSortWarpKeys;
+    const uint32_t n_warps = gridDim.x * (kSortThreads / 32);
+    for (uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += n_warps) {
+        const uint32_t cnt = count[slot];
+        if (!cnt)
+            continue;
+        if (lane == 0 && weight[slot] >= heavy_min)
+            heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
+        if (cnt < 2)
+            continue;
+        uint32_t *l = list + offset[slot];
+        if (cnt <= 32) {
+            uint32_t key = (uint32_t)lane < cnt ? l[lane] : 0xffffffffu;
+            for (int k = 2; k <= 32; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    const uint32_t other = __shfl_xor_sync(0xffffffffu, key, j);
+                    const bool up = (lane & k) == 0, keep_min = ((lane & j) == 0) == up;
+                    key = (keep_min == (key < other)) ? key : other;
+                }
+            if ((uint32_t)lane < cnt)
+                l[lane] = key;
+        }
+        else if (cnt <= kSortWarpKeys) {
+            uint32_t P = 64;
+            while (P < cnt) P <<= 1;
+            for (uint32_t i = lane; i < P; i += 32) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
+            __syncwarp();
+            for (uint32_t k = 2; k <= P; k <<= 1)
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    for (uint32_t i = lane; i < P / 2; i += 32) {
+                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;     // pair (a, a + j), bit j of a clear
+                        const uint32_t x = s_keys[a], y = s_keys[b];
+                        const bool up = (a & k) == 0;
+                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
+                    }
+                    __syncwarp();
+                }
+            for (uint32_t i = lane; i < cnt; i += 32) l[i] = s_keys[i];
+            __syncwarp();
+        }
+        else if (lane == 0) {
+            big[1u + atomicAdd(&big[0], 1u)] = slot;
+        }
+    }
+}
+
+// Long lists (a va_block that many batches touch): one CTA per list, bitonic sort in shared memory up to
+// kSortBigKeys runs; beyond that an odd-even transposition sort in place (slow, but such a list needs more than
+// kSortBigKeys batches that all fault on the same 2 MB).
+constexpr uint32_t kSortBigKeys = 8192;
+constexpr int kSortBigThreads = 512;
+__global__ void __launch_bounds__(kSortBigThreads)
+k_service_sort_big(const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset, uint32_t *__restrict__ list,
+                   const uint32_t *__restrict__ big)
+{
+    __shared__ uint32_t s_keys[kSortBigKeys];
+    const uint32_t n_big = big[0];
+    for (uint32_t q = blockIdx.x; q < n_big; q += gridDim.x) {
+        const uint32_t slot = big[1u + q], cnt = count[slot];
+        uint32_t *l = list + offset[slot];
+        if (cnt <= kSortBigKeys) {
+            uint32_t P = 1024;
+            while (P < cnt) P <<= 1;
+            for (uint32_t i = threadIdx.x; i < P; i += kSortBigThreads) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
+            __syncthreads();
+            for (uint32_t k = 2; k <= P; k <<= 1)
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    for (uint32_t i = threadIdx.x; i < P / 2; i += kSortBigThreads) {
+                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;
+                        const uint32_t x = s_keys[a], y = s_keys[b];
+                        const bool up = (a & k) == 0;
+                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
+                    }
+                    __syncthreads();
+                }
+            for (uint32_t i = threadIdx.x; i < cnt; i += kSortBigThreads) l[i] = s_keys[i];
+            __syncthreads();
+        }
+        else {
+            for (uint32_t pass = 0; pass < cnt; pass++) {
+                for (uint32_t i = (pass & 1) + 2 * threadIdx.x; i + 1 < cnt; i += 2 * kSortBigThreads) {
+                    const uint32_t x = l[i], y = l[i + 1];
+                    if (x > y) { l[i] = y; l[i + 1] = x; }
+                }
+                __threadfence_block();
+                __syncthreads();
+            }
+        }
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // Counts (and, with runs != NULL, writes) the copy runs of mask `m`: maximal sequences of consecutive pages
 // with the same cause (UVM/uvm_va_block.c:4242-4335).  Warp-synchronous; word per lane, half-warp wide.
@@ -223,21 +399,98 @@ __device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint3
     return total;
 }
 
-// One warp per state slot.
+// What one entry of a run does, as a function of what the sorted entry before it did (service_fault_batch_block_locked
+// :1433-1580 with fault_entry_duplicate_flags :1257-1272 and check_fault_access_permissions :1293-1360).
+// state bit 0 = that entry was fatal, bit 1 = it was an invalid prefetch; `auth` = the page is already mapped with
+// READ (bit 0) / WRITE (bit 1) / ATOMIC (bit 2) permission.
+struct svc_entry_eval {
+    uint32_t flags;        // UVMTIER_SF_*
+    uint32_t state;        // handed to the next entry
+    uint32_t ip_add;       // added to the batch's num_invalid_prefetch_faults
+    bool serviced;         // the page joins new_residency
+};
+__device__ __forceinline__ svc_entry_eval svc_eval_entry(uint32_t acc, uint32_t num_instances, uint32_t access_type_mask, bool dup,
+                                                         uint32_t state_in, uint32_t logical, uint32_t auth)
+{
+    svc_entry_eval r;
+    const bool prev_fatal = state_in & 1u, prev_ip = state_in & 2u;
+    uint32_t service_acc = acc, fl = 0, ip_add = 0;
+    bool entry_fatal = false, entry_ip = false, done = false, serviced = false;
+    if (dup) {
+        fl |= UVMTIER_SF_DUPLICATE;
+        if (prev_ip) {                                        // fault_entry_duplicate_flags :1257-1272
+            entry_ip = true;
+            ip_add += num_instances;
+        }
+        if (!prev_fatal)
+            done = true;                                      // page already serviced (:1481-1483)
+    }
+    if (!done && svc_prot_of(acc) > logical) {                // check_fault_access_permissions :1293-1360
+        if (acc == ACC_PREFETCH) {
+            entry_ip = true;
+            ip_add += num_instances;
+            done = true;
+        }
+        else {
+            uint32_t cancel = CANCEL_ALL;
+            service_acc = ACC_COUNT;
+            if (acc > ACC_READ) {
+                cancel = CANCEL_WRITE_AND_ATOMIC;
+                if (access_type_mask & (1u << ACC_READ)) {
+                    if (svc_prot_of(ACC_READ) <= logical)
+                        service_acc = ACC_READ;
+                    else
+                        cancel = CANCEL_ALL;
+                }
+            }
+            entry_fatal = true;
+            fl |= UVMTIER_SF_FATAL | (REASON_INVALID_PERMISSIONS << UVMTIER_SF_REASON_SHIFT) | (cancel << UVMTIER_SF_CANCEL_SHIFT);
+            if (service_acc == ACC_COUNT)
+                done = true;
+        }
+    }
+    if (!done) {
+        // already authorised: nothing to do (:1518-1522, uvm_va_block.c:2576-2615); otherwise the page moves to the
+        // faulting GPU (harness policy; block_select_processor_residency falls through to the faulting processor,
+        // uvm_va_block.c:11560-11712)
+        if ((auth >> (svc_prot_of(service_acc) - 1u)) & 1u) {
+            fl |= UVMTIER_SF_AUTHORIZED;
+        }
+        else {
+            serviced = true;
+            fl |= UVMTIER_SF_SERVICED | (service_acc << UVMTIER_SF_ACCESS_SHIFT);
+        }
+    }
+    if (entry_ip)
+        fl |= UVMTIER_SF_INVALID_PREFETCH;
+    r.flags = fl;
+    r.state = (entry_fatal ? 1u : 0u) | (entry_ip ? 2u : 0u);
+    r.ip_add = ip_add;
+    r.serviced = serviced;
+    return r;
+}
+
+// One warp per slot, for the slots the sorter put on the `heavy` list: runs with many entries.  The entries of a
+// run are filtered 32 at a time.  An entry depends on the one before it only when both fault on the same page
+// (a duplicate inherits "fatal" / "invalid prefetch"), so every lane evaluates its entry from its neighbour's last
+// result and the warp repeats until nothing changes: as many rounds as the longest chain of duplicates, and the
+// result of the sequential scan.
 __global__ void __launch_bounds__(kSvcThreads)
 k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                  const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
                  block_state_ptrs st, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
-                 const uint32_t *__restrict__ list, uint16_t *__restrict__ entry_flags,
+                 const uint32_t *__restrict__ list, const uint32_t *__restrict__ heavy, uint16_t *__restrict__ entry_flags,
                  uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
                  uint32_t *__restrict__ counters)
 {
-    const int lane = threadIdx.x & 31, l = lane & 15;
+    __shared__ uint32_t s_newres[kSvcThreads / 32][16];
+    const int lane = threadIdx.x & 31, l = lane & 15, warp = threadIdx.x >> 5;
     const uint32_t n_warps = gridDim.x * (kSvcThreads / 32);
-    for (uint32_t slot = blockIdx.x * (kSvcThreads / 32) + (threadIdx.x >> 5); slot < prm.n_slots; slot += n_warps) {
+    const uint32_t n_heavy = heavy[0];
+    const uint4 *oraw = (const uint4 *)ordered;
+    for (uint32_t q = blockIdx.x * (kSvcThreads / 32) + warp; q < n_heavy; q += n_warps) {
+        const uint32_t slot = heavy[1u + q];
         const uint32_t cnt = count[slot];
-        if (!cnt)
-            continue;
         const uint32_t off = offset[slot];
         const size_t w = (size_t)slot * 16 + l;
         uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
@@ -245,96 +498,62 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
         const uint32_t logical = st.logical_prot[slot], pref = st.preferred_location[slot];
         uvmtier_prefetch_info_t pi = st.prefetch_info[slot];
 
-        const uint32_t mykey = (uint32_t)lane < cnt ? list[off + lane] : 0xffffffffu;
-        uint32_t last = 0;
         for (uint32_t k = 0; k < cnt; k++) {
-            // ---- next run of this va_block in (batch, run) order ----
-            uint32_t best = (k == 0 || mykey > last) ? mykey : 0xffffffffu;
-            if (cnt > 32)
-                for (uint32_t j = lane + 32; j < cnt; j += 32) {
-                    const uint32_t v = list[off + j];
-                    if ((k == 0 || v > last) && v < best) best = v;
-                }
-            for (int d = 16; d > 0; d >>= 1) best = min(best, __shfl_xor_sync(HW_FULL, best, d));
-            const uint32_t t = best;
-            last = t;
+            const uint32_t t = list[off + k];                             // ascending (batch, run): the list is sorted
             const uint32_t b = t / prm.B, base = b * prm.B;
             const uvmtier_fault_group_t grp = groups[t];
             const uint32_t first = grp.first_fault_index, n = grp.block_faults;
 
-            // ---- service_fault_batch_block_locked :1433-1580 ----
-            uint32_t newres = 0, page_faults = 0, dup_sum = 0, ip_sum = 0, prev_page = 0xffffffffu;
-            int first_page = 512, last_page = 0;
-            bool prev_fatal = false, prev_ip = false;
-            for (uint32_t i = 0; i < n; i++) {
-                const uvmtier_ordered_fault_t e = ordered[base + first + i];
-                const uint32_t acc = e.fault_access_type & 7u;
-                const uint32_t page = (uint32_t)((e.fault_address - grp.block_start) >> 12);
-                const bool dup = i > 0 && page == prev_page;              // same va_space inside a run (:1180-1191)
-                uint32_t service_acc = acc, fl = 0;
-                bool entry_fatal = false, entry_ip = false, done = false;
-                dup_sum += dup ? e.num_instances : (uint32_t)e.num_instances - 1u;   // :1200-1203
-                if (dup) {
-                    fl |= UVMTIER_SF_DUPLICATE;
-                    if (prev_ip) {                                        // fault_entry_duplicate_flags :1257-1272
-                        entry_ip = true;
-                        ip_sum += e.num_instances;
-                    }
-                    if (!prev_fatal)
-                        done = true;                                      // page already serviced (:1481-1483)
-                }
-                if (!done && svc_prot_of(acc) > logical) {                // check_fault_access_permissions :1293-1360
-                    if (acc == ACC_PREFETCH) {
-                        entry_ip = true;
-                        ip_sum += e.num_instances;
-                        done = true;
-                    }
-                    else {
-                        uint32_t cancel = CANCEL_ALL;
-                        service_acc = ACC_COUNT;
-                        if (acc > ACC_READ) {
-                            cancel = CANCEL_WRITE_AND_ATOMIC;
-                            if (e.access_type_mask & (1u << ACC_READ)) {
-                                if (svc_prot_of(ACC_READ) <= logical)
-                                    service_acc = ACC_READ;
-                                else
-                                    cancel = CANCEL_ALL;
-                            }
-                        }
-                        entry_fatal = true;
-                        fl |= UVMTIER_SF_FATAL | (REASON_INVALID_PERMISSIONS << UVMTIER_SF_REASON_SHIFT) |
-                              (cancel << UVMTIER_SF_CANCEL_SHIFT);
-                        if (service_acc == ACC_COUNT)
-                            done = true;
-                    }
-                }
-                if (!done) {
-                    // already authorised: nothing to do (:1518-1522, uvm_va_block.c:2576-2615)
-                    const uint32_t prot = svc_prot_of(service_acc);
-                    const uint32_t ptw = prot == PROT_RWA ? pte2 : (prot == PROT_RW ? pte1 : pte0);
-                    const uint32_t word = __shfl_sync(HW_FULL, ptw, (int)(page >> 5), 16);
-                    if ((word >> (page & 31u)) & 1u) {
-                        fl |= UVMTIER_SF_AUTHORIZED;
-                    }
-                    else {
-                        // new residency: the faulting GPU (harness policy; block_select_processor_residency
-                        // falls through to the faulting processor, uvm_va_block.c:11560-11712)
-                        if ((uint32_t)l == (page >> 5))
-                            newres |= 1u << (page & 31u);
-                        page_faults++;
-                        fl |= UVMTIER_SF_SERVICED | (service_acc << UVMTIER_SF_ACCESS_SHIFT);
-                        first_page = min(first_page, (int)page);
-                        last_page = max(last_page, (int)page);
-                    }
-                }
-                if (entry_ip)
-                    fl |= UVMTIER_SF_INVALID_PREFETCH;
+            // ---- service_fault_batch_block_locked :1433-1580, 32 entries at a time ----
+            if (lane < 16)
+                s_newres[warp][lane] = 0;
+            __syncwarp();
+            uint32_t page_faults = 0, dup_sum = 0, ip_sum = 0, carry_page = 0xffffffffu, carry_state = 0;
+            for (uint32_t c = 0; c < n; c += 32) {
+                const uint32_t i = c + lane;
+                const bool valid = i < n;
+                uint4 e = make_uint4(0, 0, 0, 0);
+                if (valid)
+                    e = oraw[base + first + i];
+                const uint32_t acc = (e.w >> 24) & 7u, num_instances = e.w & 0xffffu, access_type_mask = (e.w >> 16) & 0xffu;
+                const uint32_t page = valid ? (e.x - (uint32_t)grp.block_start) >> 12 : 0x80000000u + lane;
+                uint32_t prev_page = __shfl_up_sync(HW_FULL, page, 1);
                 if (lane == 0)
-                    entry_flags[base + first + i] = (uint16_t)fl;
-                prev_fatal = entry_fatal;
-                prev_ip = entry_ip;
-                prev_page = page;
+                    prev_page = carry_page;
+                const bool dup = valid && i > 0 && page == prev_page;     // same va_space inside a run (:1180-1191)
+                // is the page already mapped for READ / WRITE / ATOMIC?  (the masks do not change inside a run)
+                const int wl = (int)((page >> 5) & 15u);
+                const uint32_t w0 = __shfl_sync(HW_FULL, pte0, wl), w1 = __shfl_sync(HW_FULL, pte1, wl), w2 = __shfl_sync(HW_FULL, pte2, wl);
+                const uint32_t sh = page & 31u;
+                const uint32_t auth = ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
+                svc_entry_eval ev;
+                uint32_t state = 0;
+                for (;;) {
+                    uint32_t state_in = __shfl_up_sync(HW_FULL, state, 1);
+                    if (lane == 0)
+                        state_in = carry_state;
+                    ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, dup ? state_in : 0u, logical, auth);
+                    const bool changed = valid && ev.state != state;
+                    if (valid)
+                        state = ev.state;
+                    if (!__any_sync(HW_FULL, changed))
+                        break;
+                }
+                if (valid) {
+                    entry_flags[base + first + i] = (uint16_t)ev.flags;
+                    if (ev.serviced)
+                        atomicOr(&s_newres[warp][page >> 5], 1u << sh);
+                }
+                const uint32_t dup_add = valid ? (dup ? num_instances : num_instances - 1u) : 0u;   // :1200-1203
+                dup_sum += __reduce_add_sync(HW_FULL, dup_add);
+                ip_sum += __reduce_add_sync(HW_FULL, valid ? ev.ip_add : 0u);
+                page_faults += (uint32_t)__popc(__ballot_sync(HW_FULL, valid && ev.serviced));
+                carry_page = __shfl_sync(HW_FULL, page, 31);
+                carry_state = __shfl_sync(HW_FULL, state, 31);
             }
+            __syncwarp();
+            uint32_t newres = s_newres[warp][l];
+            __syncwarp();
             if (lane == 0) {
                 if (dup_sum) atomicAdd(&batches[b].num_duplicate_faults, dup_sum);
                 if (ip_sum) atomicAdd(&batches[b].num_invalid_prefetch_faults, ip_sum);
@@ -344,8 +563,8 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
             uint32_t hint = UVMTIER_ID_INVALID, pf = 0, n_pf = 0, n0 = 0, n1 = 0, nt = 0, run_off = 0, run_cnt = 0;
             int rf = 0, ro = 0;
             if (page_faults) {                                            // uniform across the warp
-                rf = first_page;
-                ro = last_page + 1;
+                rf = hw_first_bit(newres, lane);
+                ro = hw_last_bit(newres, lane) + 1;
                 const bool block_empty = !hw_any(gres | c0 | c1, lane);
                 if (prm.pf_enable) {
                     const uint32_t flags = UVMTIER_PF_HAS_RESIDENT_MASK | UVMTIER_PF_GPU_VA_SPACE_REGISTERED |

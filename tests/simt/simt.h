@@ -7,12 +7,13 @@
 // against the oracle before a B200 run.  It is test infrastructure: it is never linked into
 // libuvmtier.so and is no fallback -- the product fails loudly without a GPU.
 //
-// Limits: kernels must not wait on other CTAs (they are serialised); all 32 lanes of a warp must
-// reach every *_sync intrinsic (full masks), as the product code guarantees.
+// Limits: kernels must not wait on other CTAs (they are serialised); every lane named in the mask of a
+// *_sync intrinsic must reach it, as the product code guarantees.
 #pragma once
 #define UVMTIER_SIMT_EMU 1
 
 #include <pthread.h>
+#include <sched.h>
 #include <stdint.h>
 #include <stdio.h>
 #include <stdlib.h>
@@ -46,6 +47,7 @@ namespace simt {
 struct Warp {
     uint64_t slot[32];
     pthread_barrier_t bar;
+    uint32_t m_arrive[32], m_gen[32];    // partial-mask barriers, indexed by the lowest lane of the mask
 };
 struct Cta {
     pthread_barrier_t bar;
@@ -65,68 +67,112 @@ extern dim3 blockDim, gridDim;
 static const int warpSize = 32;
 
 // ---------------------------------------------------------------- warp intrinsics
+// Every *_sync intrinsic takes its member mask seriously: the lanes named in the mask (and only they) meet at the
+// call.  Full masks use the warp's pthread barrier; partial masks (sub-warp groups that have diverged from the rest
+// of the warp) use a small spinning barrier keyed by the lowest lane of the mask, so a warp must always be split
+// into the same groups while it uses partial masks.
 namespace simt {
 template <class T> static inline uint64_t pack(T v) { uint64_t u = 0; memcpy(&u, &v, sizeof(T)); return u; }
 template <class T> static inline T unpack(uint64_t u) { T v; memcpy(&v, &u, sizeof(T)); return v; }
 static inline void wbar() { pthread_barrier_wait(&tl_warp->bar); }
-template <class T> static inline T exchange(T v, int src_lane)
+static inline void mbar(unsigned mask)
+{
+    if (mask == 0xffffffffu) {
+        wbar();
+        return;
+    }
+    const int leader = __builtin_ctz(mask), n = __builtin_popcount(mask);
+    if (n <= 1)
+        return;
+    Warp *w = tl_warp;
+    const uint32_t g = __atomic_load_n(&w->m_gen[leader], __ATOMIC_ACQUIRE);
+    if (__atomic_add_fetch(&w->m_arrive[leader], 1u, __ATOMIC_ACQ_REL) == (uint32_t)n) {
+        __atomic_store_n(&w->m_arrive[leader], 0u, __ATOMIC_RELAXED);
+        __atomic_add_fetch(&w->m_gen[leader], 1u, __ATOMIC_RELEASE);
+    }
+    else {
+        while (__atomic_load_n(&w->m_gen[leader], __ATOMIC_ACQUIRE) == g)
+            sched_yield();
+    }
+}
+template <class T> static inline T exchange(unsigned mask, T v, int src_lane)
 {
     static_assert(sizeof(T) <= 8, "shuffle payload");
     tl_warp->slot[tl_lane] = pack(v);
-    wbar();
+    mbar(mask);
     T r = unpack<T>(tl_warp->slot[src_lane]);
-    wbar();
+    mbar(mask);
+    return r;
+}
+template <class F> static inline unsigned reduce(unsigned mask, unsigned v, F f)
+{
+    tl_warp->slot[tl_lane] = v;
+    mbar(mask);
+    unsigned r = 0;
+    bool first = true;
+    for (int i = 0; i < 32; i++)
+        if ((mask >> i) & 1u) {
+            r = first ? (unsigned)tl_warp->slot[i] : f(r, (unsigned)tl_warp->slot[i]);
+            first = false;
+        }
+    mbar(mask);
     return r;
 }
 } // namespace simt
 
-template <class T> static inline T __shfl_sync(unsigned, T v, int src, int width = 32)
+template <class T> static inline T __shfl_sync(unsigned mask, T v, int src, int width = 32)
 {
     int base = simt::tl_lane & ~(width - 1);
-    return simt::exchange(v, base | (src & (width - 1)));
+    return simt::exchange(mask, v, base | (src & (width - 1)));
 }
-template <class T> static inline T __shfl_up_sync(unsigned, T v, unsigned delta, int width = 32)
+template <class T> static inline T __shfl_up_sync(unsigned mask, T v, unsigned delta, int width = 32)
 {
     int base = simt::tl_lane & ~(width - 1);
     int src = simt::tl_lane - (int)delta;
-    return simt::exchange(v, src < base ? simt::tl_lane : src);
+    return simt::exchange(mask, v, src < base ? simt::tl_lane : src);
 }
-template <class T> static inline T __shfl_down_sync(unsigned, T v, unsigned delta, int width = 32)
+template <class T> static inline T __shfl_down_sync(unsigned mask, T v, unsigned delta, int width = 32)
 {
     int base = simt::tl_lane & ~(width - 1);
     int src = simt::tl_lane + (int)delta;
-    return simt::exchange(v, src >= base + width ? simt::tl_lane : src);
+    return simt::exchange(mask, v, src >= base + width ? simt::tl_lane : src);
 }
-template <class T> static inline T __shfl_xor_sync(unsigned, T v, int m, int width = 32)
+template <class T> static inline T __shfl_xor_sync(unsigned mask, T v, int m, int width = 32)
 {
     int base = simt::tl_lane & ~(width - 1);
     int src = simt::tl_lane ^ m;
-    return simt::exchange(v, src >= base + width ? simt::tl_lane : src);
+    return simt::exchange(mask, v, src >= base + width ? simt::tl_lane : src);
 }
-static inline unsigned __ballot_sync(unsigned, int pred)
+static inline unsigned __ballot_sync(unsigned mask, int pred)
 {
     simt::tl_warp->slot[simt::tl_lane] = pred ? 1 : 0;
-    simt::wbar();
+    simt::mbar(mask);
     unsigned b = 0;
     for (int i = 0; i < 32; i++)
-        b |= (unsigned)(simt::tl_warp->slot[i] & 1) << i;
-    simt::wbar();
+        if ((mask >> i) & 1u)
+            b |= (unsigned)(simt::tl_warp->slot[i] & 1) << i;
+    simt::mbar(mask);
     return b;
 }
 static inline int __any_sync(unsigned m, int pred) { return __ballot_sync(m, pred) != 0; }
-static inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, pred) == 0xffffffffu; }
-template <class T> static inline unsigned __match_any_sync(unsigned, T v)
+static inline int __all_sync(unsigned m, int pred) { return __ballot_sync(m, pred) == m; }
+template <class T> static inline unsigned __match_any_sync(unsigned mask, T v)
 {
     simt::tl_warp->slot[simt::tl_lane] = simt::pack(v);
-    simt::wbar();
+    simt::mbar(mask);
     unsigned b = 0;
     for (int i = 0; i < 32; i++)
-        if (simt::tl_warp->slot[i] == simt::pack(v))
+        if (((mask >> i) & 1u) && simt::tl_warp->slot[i] == simt::pack(v))
             b |= 1u << i;
-    simt::wbar();
+    simt::mbar(mask);
     return b;
 }
-static inline void __syncwarp(unsigned = 0xffffffffu) { simt::wbar(); }
+static inline unsigned __reduce_add_sync(unsigned m, unsigned v) { return simt::reduce(m, v, [](unsigned a, unsigned b) { return a + b; }); }
+static inline unsigned __reduce_or_sync(unsigned m, unsigned v) { return simt::reduce(m, v, [](unsigned a, unsigned b) { return a | b; }); }
+static inline unsigned __reduce_and_sync(unsigned m, unsigned v) { return simt::reduce(m, v, [](unsigned a, unsigned b) { return a & b; }); }
+static inline unsigned __reduce_min_sync(unsigned m, unsigned v) { return simt::reduce(m, v, [](unsigned a, unsigned b) { return a < b ? a : b; }); }
+static inline unsigned __reduce_max_sync(unsigned m, unsigned v) { return simt::reduce(m, v, [](unsigned a, unsigned b) { return a > b ? a : b; }); }
+static inline void __syncwarp(unsigned m = 0xffffffffu) { simt::mbar(m); }
 static inline unsigned __activemask() { return 0xffffffffu; }
 
 // ---------------------------------------------------------------- CTA barriers

@@ -1,11 +1,14 @@
-// simt_service.cpp -- runs the servicing-pass kernels (service_kernels.cuh) under the CPU SIMT emulator with
-// the same launch sequence as uvmtier_service_fault_batches_device.  TEST INFRASTRUCTURE ONLY.
+// simt_service.cpp -- runs the servicing-pass kernels (service_kernels.cuh, service_grp.cuh) under the CPU SIMT
+// emulator with the same launch sequence as service_pass() in service.cu.  TEST INFRASTRUCTURE ONLY.
+//
+// lanes_per_block: 1, 2, 4, 8 or 16 (the group kernel's template parameter).  heavy_min: slots whose runs hold at
+// least this many entries are serviced by the warp-per-block kernel (0xffffffff = none, 0 = all).
 #include "simt.h"
 
 #include <vector>
 
 #include "service_kernels.cuh"
-#include "service_tpb.cuh"
+#include "service_grp.cuh"
 
 using namespace uvmtier_k;
 
@@ -14,37 +17,53 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
                                           const uvmtier_instance_ptr_entry_t *tbl, const uvmtier_va_layout_t *lay,
                                           const uvmtier_block_state_t *state, uint32_t pf_enable, uint32_t pf_threshold,
                                           uint32_t pf_min_faults, uint16_t *entry_flags, uvmtier_service_group_t *service,
-                                          uvmtier_copy_run_t *runs, uint32_t run_cap, uint32_t *counters, int warp_per_block)
+                                          uvmtier_copy_run_t *runs, uint32_t run_cap, uint32_t *counters, int lanes_per_block,
+                                          uint32_t heavy_min, int three_kernel_scan)
 {
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
     const size_t total = (size_t)n_batches * B;
     service_kparams prm;
     prm.va_base = lay->va_base; prm.B = B; prm.n_batches = n_batches; prm.blocks_per_space = lay->blocks_per_space;
     prm.n_spaces = lay->n_spaces; prm.gpu_id = lay->gpu_id; prm.n_slots = n_slots; prm.pf_enable = pf_enable;
-    prm.pf_threshold = pf_threshold; prm.pf_min_faults = pf_min_faults; prm.run_cap = run_cap;
+    prm.pf_threshold = pf_threshold; prm.pf_min_faults = pf_min_faults; prm.run_cap = run_cap; prm.B_shift = svc_log2_or_none(B);
     block_state_ptrs bs;
     bs.gpu_resident = (uint32_t *)state->gpu_resident;
     bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0]; bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
     bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0]; bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1]; bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
     bs.prefetch_info = state->prefetch_info; bs.logical_prot = state->logical_prot; bs.preferred_location = state->preferred_location;
 
-    std::vector<uint32_t> count(n_slots, 0), offset(n_slots, 0), cursor(n_slots, 0), sums(1024, 0), unmapped(n_batches, 0), list(total + 1, 0);
+    // 16-byte aligned like the device arrays (k_scan_single reads and writes uint4)
+    std::vector<uint4> count4(n_slots / 4 + 2), offset4(n_slots / 4 + 2);
+    uint32_t *count = (uint32_t *)count4.data(), *offset = (uint32_t *)offset4.data();
+    memset(count, 0, (n_slots + 4) * sizeof(uint32_t));
+    std::vector<uint32_t> cursor(n_slots, 0), weight(n_slots, 0), sums(1024, 0), unmapped(n_batches, 0), list(total + 1, 0),
+        big(n_slots + 2, 0), heavy(n_slots + 2, 0);
     counters[0] = counters[1] = 0;
     memset(entry_flags, 0, total * sizeof(uint16_t));
-    const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
-    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count.data(), unmapped.data(), list.data(), 0, offset.data(), cursor.data()); });
-    simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_sums(count.data(), n_slots, sums.data()); });
-    simt::launch(dim3(1), dim3(1024), [&] { k_scan_top(sums.data(), n_sums); });
-    simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_final(count.data(), n_slots, sums.data(), offset.data()); });
-    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count.data(), unmapped.data(), list.data(), 1, offset.data(), cursor.data()); });
-    if (warp_per_block) {
-        simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, count.data(), offset.data(), list.data(), entry_flags, service, runs, counters); });
+    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count, weight.data(), unmapped.data(), list.data(), 0, offset, cursor.data()); });
+    if (!three_kernel_scan && n_slots <= kScanSingleMax) {
+        simt::launch(dim3(1), dim3(1024), [&] { k_scan_single(count, n_slots, offset); });
     }
     else {
-        simt::launch(dim3(5), dim3(32), [&] { k_service_sort_lists(n_slots, count.data(), offset.data(), list.data()); });
-        simt::launch(dim3((n_slots + kTpbThreads - 1) / kTpbThreads), dim3(kTpbThreads),
-                     [&] { k_service_blocks_tpb(prm, ordered, groups, batches, bs, count.data(), offset.data(), list.data(), entry_flags, service, runs, counters); });
+        const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
+        simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_sums(count, n_slots, sums.data()); });
+        simt::launch(dim3(1), dim3(1024), [&] { k_scan_top(sums.data(), n_sums); });
+        simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_final(count, n_slots, sums.data(), offset); });
     }
+    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count, weight.data(), unmapped.data(), list.data(), 1, offset, cursor.data()); });
+    simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, count, offset, list.data(), weight.data(), heavy_min, big.data(), heavy.data()); });
+    simt::launch(dim3(2), dim3(kSortBigThreads), [&] { k_service_sort_big(count, offset, list.data(), big.data()); });
+    const uint32_t ggrid = (uint32_t)(((size_t)n_slots * lanes_per_block + kGrpThreads - 1) / kGrpThreads);
+#define GRP(G) simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<G>(prm, ordered, groups, batches, bs, count, offset, list.data(), weight.data(), heavy_min, entry_flags, service, runs, counters); })
+    switch (lanes_per_block) {
+        case 1: GRP(1); break;
+        case 2: GRP(2); break;
+        case 8: GRP(8); break;
+        case 16: GRP(16); break;
+        default: GRP(4); break;
+    }
+#undef GRP
+    simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, count, offset, list.data(), heavy.data(), entry_flags, service, runs, counters); });
     simt::launch(dim3((n_batches + 127) / 128), dim3(128), [&] { k_service_unmapped(prm, ordered, groups, batches, tbl, unmapped.data(), entry_flags, service); });
     return 0;
 }

@@ -16,23 +16,65 @@ def _k1(pk, gp, tbl):
     return F.run_fetch_preprocess_simt(T.load_simt(), pk, gp, tbl)
 
 
-def _both(pk, gp, tbl, lay, st0, pf=(1, 51, 1)):
+NONE_HEAVY, ALL_HEAVY = 0xFFFFFFFF, 0
+
+
+def _both(pk, gp, tbl, lay, st0, pf=(1, 51, 1), **simt_args):
     k1 = _k1(pk, gp, tbl)
     layout = S.make_layout(lay)
     want = S.run_service_oracle(T.load_oracle(), k1, gp, tbl, layout, st0, pf)
-    got = S.run_service_simt(T.load_simt(), k1, gp, tbl, layout, st0, pf)
+    got = S.run_service_simt(T.load_simt(), k1, gp, tbl, layout, st0, pf, **simt_args)
     return k1, want, got
 
 
 @pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
 @pytest.mark.parametrize("B", [256, 48])
 def test_simt_service_matches_oracle(dist, B):
+    """Default split: va_blocks with few entries on 4-lane groups, the others on a warp each."""
     pk, tbl, lay = TG.fault_trace(1200, 21, dist, 2, total_va_bytes=SMALL_VA)
     gp = TG.gpu_params(B)
     st0 = S.random_state(lay["blocks_per_space"] * 2, 4)
     _, want, got = _both(pk, gp, tbl, lay, st0)
     S.assert_service_equal(want, got, B, "%s %d" % (dist, B))
     S.check_service_invariants(got, st0)
+
+
+@pytest.mark.parametrize("dist", ["uniform", "hotset", "adversarial"])
+@pytest.mark.parametrize("lanes,heavy_min", [(1, NONE_HEAVY), (2, NONE_HEAVY), (4, NONE_HEAVY), (8, NONE_HEAVY), (16, NONE_HEAVY),
+                                             (4, ALL_HEAVY), (4, 24)])
+def test_every_kernel_variant_matches_oracle(dist, lanes, heavy_min):
+    """Each lanes-per-block instantiation of the group kernel on its own, the warp-per-block kernel on its own
+    (entries filtered 32 at a time), and a split in the middle of this trace's weights."""
+    pk, tbl, lay = TG.fault_trace(900, 33, dist, 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(128)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 5)
+    _, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min, three_kernel_scan=lanes == 2)
+    S.assert_service_equal(want, got, 128, "%s lanes %d heavy_min %d" % (dist, lanes, heavy_min))
+
+
+def test_long_chains_of_duplicates_in_the_entry_parallel_filter():
+    """Many uTLBs faulting on the same few pages, read-only VMAs and prefetch accesses mixed in: duplicates inherit
+    'fatal' and 'invalid prefetch' along chains that cross the 32-entry chunks of the warp kernel."""
+    rng = np.random.default_rng(77)
+    n = 700
+    tbl = TG.instance_ptr_table(1)
+    lay = dict(va_base=TG.VA_BASE, blocks_per_space=4, n_spaces=1)
+    page = rng.integers(0, 6, n) * 37
+    blk = rng.integers(0, 4, n)
+    addr = (TG.VA_BASE + (blk.astype(np.uint64) << np.uint64(21)) + (page.astype(np.uint64) << np.uint64(12))).astype(np.uint64)
+    acc = rng.choice([TG.HW_VIRT_READ, TG.HW_VIRT_WRITE, TG.HW_VIRT_ATOMIC_STRONG, TG.HW_VIRT_PREFETCH], n)
+    pk = TG.encode_packets(np.full(n, tbl["instance_ptr"][0]), addr, acc, rng.integers(0, 8, n),
+                           [TG.T1_CLIENTS[i] for i in rng.integers(0, 8, n)], np.arange(n) + 1)
+    gp = TG.gpu_params(512)
+    st0 = S.random_state(4, 3, populated=0.4)
+    st0.logical_prot[:] = [3, 1, 1, 0]
+    st0.gpu_pte1[1:] = 0
+    st0.gpu_pte2[1:] = 0
+    st0.gpu_pte0[3] = 0
+    for lanes, heavy_min in ((4, ALL_HEAVY), (4, NONE_HEAVY)):
+        k1, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
+        S.assert_service_equal(want, got, 512, "heavy_min %d" % heavy_min)
+    assert int((want["flags"] & 2 != 0).sum()) > 200 and int((want["flags"] & 4 != 0).sum()) > 20
 
 
 def test_block_touched_by_more_than_32_batches_is_applied_in_batch_order():

@@ -2,8 +2,9 @@
 // Reference: UVM/uvm_gpu_replayable_faults.c:2232-2377 (service_fault_batch) and callees; see service_kernels.cuh.
 //
 // Working space in HBM (one buffer owned by the context, grown on demand and reused; or the fixed array of the
-// no-alloc entry point): per slot the number of runs, a fill cursor, the number of entries and the start of its
-// run list (4 x 4 B x n_slots), the run lists (4 B per run), one flag per batch and two short work lists.
+// no-alloc entry point): per slot the packed (runs, entries) counter and the start of its run list (12 B x
+// n_slots), per run its (slot, position) pair and its place in a list (12 B per run), one flag per batch and two
+// short work lists.
 // Algorithmic bytes per serviced va_block run: 16 (run) + 16 per entry + 2 per entry flag + 96 record
 // + the block's state (6 masks x 64 B + 8 B) read and written once per touched block, + 8 per copy run.
 #include "common.cuh"
@@ -11,6 +12,7 @@
 #include <stdlib.h>
 
 #include "service_kernels.cuh"
+#include "service_lists.cuh"
 #include "service_grp.cuh"
 
 using namespace uvmtier_k;
@@ -21,28 +23,28 @@ constexpr uint32_t kHeavyMinEntries = 96;
 
 // Carves the working space for one call out of `base`.
 struct service_scratch_view {
-    uint32_t *count, *cursor, *weight, *big, *heavy, *batch_unmapped;    // zeroed at the start of every call
-    uint32_t *offset, *sums, *list;                                      // fully rewritten before use
+    uint32_t *cw, *cursor, *big, *heavy, *batch_unmapped;                // zeroed at the start of every call
+    uint32_t *offset, *slotpos, *list;                                   // fully rewritten before use
     size_t zero_words, words;
 };
 static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint32_t n_batches, size_t total)
 {
     service_scratch_view v;
     const size_t slots4 = ((size_t)n_slots + 3) & ~(size_t)3;            // keeps every array 16-byte aligned
+    const size_t total4 = (total + 3) & ~(size_t)3;
     const size_t big_cap = ((total / kSortWarpKeys + 2) + 3) & ~(size_t)3;
     const size_t heavy_cap = ((total / kHeavyMinEntries + 2) + 3) & ~(size_t)3;
     const size_t batches4 = ((size_t)n_batches + 3) & ~(size_t)3;
     uint32_t *p = base;
-    v.count = p; p += slots4;
-    v.cursor = p; p += slots4;
-    v.weight = p; p += slots4;
+    v.cw = p; p += 2 * slots4;
+    v.cursor = p; p += 4;
     v.big = p; p += big_cap;
     v.heavy = p; p += heavy_cap;
     v.batch_unmapped = p; p += batches4;
     v.zero_words = (size_t)(p - base);
     v.offset = p; p += slots4;
-    v.sums = p; p += 1024;
-    v.list = p; p += (total + 3) & ~(size_t)3;
+    v.slotpos = p; p += 2 * total4;
+    v.list = p; p += total4;
     v.words = (size_t)(p - base);
     return v;
 }
@@ -66,8 +68,8 @@ static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, cons
 {
     const size_t threads = (size_t)prm.n_slots * G;
     const uint32_t grid = (uint32_t)((threads + kGrpThreads - 1) / kGrpThreads);
-    UVMTIER_LAUNCH(k_service_blocks_grp<G>, grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, v.count,
-                   v.offset, v.list, v.weight, heavy_min, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_service_blocks_grp<G>, grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
+                   (const uint2 *)v.cw, v.offset, v.list, heavy_min, d_entry_flags, d_service, d_runs, d_counters);
     return NV_OK;
 }
 
@@ -107,31 +109,23 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     bs.logical_prot = state->logical_prot;
     bs.preferred_location = state->preferred_location;
 
-    // The working space still holds the previous call's numbers.  Counters, cursors, entry totals, the two work
-    // lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset: they are
-    // adjacent); offsets, partial sums and run lists are fully rewritten before they are read.
+    // The working space still holds the previous call's numbers.  The packed per-slot counters, the list cursor,
+    // the two work lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset:
+    // they are adjacent); offsets, (slot, position) pairs and run lists are fully rewritten before they are read.
     UVMTIER_CUDA(cudaMemsetAsync(base, 0, v.zero_words * sizeof(uint32_t), ctx->stream));
     UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
     UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
 
     const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
+    const uint2 *cw = (const uint2 *)v.cw;
     const size_t cap = (size_t)ctx->sm_count * 8;
     size_t grid = (total + kSvcThreads - 1) / kSvcThreads;
     if (grid > cap)
         grid = cap;
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, v.count, v.weight,
-                   v.batch_unmapped, v.list, 0, v.offset, v.cursor);
-    if (n_slots <= kScanSingleMax) {
-        UVMTIER_LAUNCH(k_scan_single, 1, 1024, 0, ctx->stream, v.count, n_slots, v.offset);
-    }
-    else {
-        const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
-        UVMTIER_LAUNCH(k_scan_sums, n_sums, 256, 0, ctx->stream, v.count, n_slots, v.sums);
-        UVMTIER_LAUNCH(k_scan_top, 1, 1024, 0, ctx->stream, v.sums, n_sums);
-        UVMTIER_LAUNCH(k_scan_final, n_sums, 256, 0, ctx->stream, v.count, n_slots, v.sums, v.offset);
-    }
-    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl, v.count, v.weight,
-                   v.batch_unmapped, v.list, 1, v.offset, v.cursor);
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl,
+                   (unsigned long long *)v.cw, v.batch_unmapped, (uint2 *)v.slotpos);
+    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, v.offset, v.cursor);
+    UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
 
     // UVMTIER_SERVICE_HEAVY_MIN moves the group / warp split up (for experiments; 0xffffffff = no block on a warp).
     // It cannot go below kHeavyMinEntries: that is what bounds the length of the heavy list.
@@ -141,9 +135,9 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
     if (sgrid > cap)
         sgrid = cap;
-    UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, v.count, v.offset, v.list, v.weight,
-                   list_heavy_min, v.big, v.heavy);
-    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, v.count, v.offset, v.list, v.big);
+    UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
+                   v.big, v.heavy);
+    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, cw, v.offset, v.list, v.big);
 
     NV_STATUS st = NV_OK;
     switch (service_lanes_per_block()) {
@@ -155,7 +149,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     }
     if (st != NV_OK)
         return st;
-    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, v.count,
+    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, cw,
                    v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
     UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
                    v.batch_unmapped, d_entry_flags, d_service);
@@ -176,7 +170,8 @@ static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, cons
     if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
         return NV_ERR_INVALID_ARGUMENT;
     const size_t n_slots64 = (size_t)lay->n_spaces * lay->blocks_per_space;
-    if (!ctx->faults->gp.max_batch_size || n_slots64 == 0 || n_slots64 > (size_t)1024 * kScanItems)
+    if (!ctx->faults->gp.max_batch_size || n_slots64 == 0 || n_slots64 > kMaxSlots ||
+        (size_t)n_batches * ctx->faults->gp.max_batch_size > 0xffffffffu)
         return NV_ERR_INVALID_ARGUMENT;
     return NV_OK;
 }
@@ -195,7 +190,7 @@ NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_
     if (!ctx || !lay || !out || !lay->n_spaces || !lay->blocks_per_space)
         return NV_ERR_INVALID_ARGUMENT;
     const size_t n = (size_t)lay->n_spaces * lay->blocks_per_space;
-    if (n > (size_t)1024 * kScanItems)
+    if (n > kMaxSlots)
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     memset(out, 0, sizeof(*out));
@@ -275,14 +270,15 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
 //
 // What: the pass above keeps its working space in a buffer it grows with cudaMalloc.  This variant keeps the same
 // working space in one fixed array that is part of the library image.  Every GPU that loads the library carries
-// the array (about 2.1 MB) until the process exits; the price of never allocating is a hard ceiling on the
+// the array (about 3.9 MB) until the process exits; the price of never allocating is a hard ceiling on the
 // problem size.
 constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of VA
 constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size
 constexpr uint32_t kNoAllocMaxBatches = 4096;
 // scratch_view() of the largest problem, with room for its alignment padding
-constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 4 + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
-                                 (kNoAllocMaxEntries / kHeavyMinEntries + 8) + kNoAllocMaxBatches + 1024 + kNoAllocMaxEntries + 64;
+constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 3 + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
+                                 (kNoAllocMaxEntries / kHeavyMinEntries + 8) + kNoAllocMaxBatches +
+                                 (size_t)kNoAllocMaxEntries * 3 + 64;
 
 static __device__ __align__(256) uint32_t g_service_scratch[kNoAllocWords];
 

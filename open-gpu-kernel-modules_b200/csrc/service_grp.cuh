@@ -235,17 +235,20 @@ template <int G>
 __global__ void __launch_bounds__(kGrpThreads)
 k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                      const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
-                     block_state_ptrs st, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
-                     const uint32_t *__restrict__ list, const uint32_t *__restrict__ weight, uint32_t heavy_min,
-                     uint16_t *__restrict__ entry_flags, uvmtier_service_group_t *__restrict__ service,
-                     uvmtier_copy_run_t *__restrict__ runs, uint32_t *__restrict__ counters)
+                     block_state_ptrs st, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
+                     const uint32_t *__restrict__ list, uint32_t heavy_min, uint16_t *__restrict__ entry_flags,
+                     uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
+                     uint32_t *__restrict__ counters)
 {
     constexpr int W = 16 / G;
     const uint32_t slot = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const int lane = threadIdx.x & 31, gl = lane & (G - 1), gb = lane & ~(G - 1);
     uint32_t cnt = 0;
-    if (slot < prm.n_slots && weight[slot] < heavy_min)
-        cnt = count[slot];
+    if (slot < prm.n_slots) {
+        const uint2 c = cw[slot];                                         // (runs, entries) of the slot
+        if (c.y < heavy_min)
+            cnt = c.x;
+    }
     const uint32_t cnt_max = __reduce_max_sync(kFullWarp, cnt);
     if (!cnt_max)
         return;                                                           // the whole warp

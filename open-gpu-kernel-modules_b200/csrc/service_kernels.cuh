@@ -8,15 +8,16 @@
 // uvm_va_block_make_resident_finish (:5042-5084) and the mapping step of uvm_va_block_service_finish
 // (:12063-12302, compute_new_permission :11019-11066).
 //
-// The reference services batch after batch on one thread.  Different va_blocks never interact, so here
-// every va_block gets one warp that applies the block's runs in batch order:
-//   k_service_count   -> how many runs touch each state slot              (atomics on a per-slot counter)
-//   k_scan_*          -> exclusive scan = start of each slot's list
-//   k_service_fill    -> the slot's list of run ids (unordered)
-//   k_service_blocks  -> per slot: pick the runs in ascending (batch, run) order and service them
-//   k_service_unmapped-> runs whose address lies in no va_range (fatal / invalid prefetch, :2022-2031)
-// A va_block's masks stay in registers across all its runs: one 32-bit word per lane, lanes 16-31 mirror
-// lanes 0-15 (the mask helpers are half-warp wide) so that control flow is uniform across the warp.
+// The reference services batch after batch on one thread.  Different va_blocks never interact, so here the
+// runs (one va_block's faults of one batch) are first regrouped by va_block, then every va_block's runs are
+// applied in batch order by a small group of lanes or by a warp:
+//   service_lists.cuh   k_service_count / _alloc / _fill / _sort_* -> per state slot the sorted list of its runs
+//   service_grp.cuh     k_service_blocks_grp                         -> va_blocks with few entries, G lanes each
+//   this file           k_service_blocks                             -> va_blocks with many entries, a warp each
+//                       k_service_unmapped -> runs whose address lies in no va_range (fatal / invalid prefetch,
+//                                             :2022-2031)
+// In k_service_blocks a va_block's masks stay in registers across all its runs: one 32-bit word per lane, lanes
+// 16-31 mirror lanes 0-15 (the mask helpers are half-warp wide) so that control flow is uniform across the warp.
 #pragma once
 
 #include "devio.cuh"
@@ -26,7 +27,7 @@
 namespace uvmtier_k {
 
 constexpr int kSvcThreads = 256;
-constexpr uint32_t kScanItems = 4096;      // elements per CTA in the scan kernels (256 threads x 16)
+constexpr uint32_t kMaxSlots = 1u << 26;    // va_block slots of one state table (128 TB of VA)
 
 enum : uint32_t { PROT_NONE = 0, PROT_RO = 1, PROT_RW = 2, PROT_RWA = 3 };
 enum : uint32_t { REASON_INVALID_ADDRESS = 1, REASON_INVALID_PERMISSIONS = 2 };   // UvmEventFatalReason
@@ -77,273 +78,6 @@ __device__ __forceinline__ uint32_t svc_slot(const service_kparams &prm, uint32_
     if (block_start < prm.va_base || (off >> 21) >= prm.blocks_per_space || va_space >= prm.n_spaces)
         return 0xffffffffu;
     return va_space * prm.blocks_per_space + (uint32_t)(off >> 21);
-}
-
-// ------------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(kSvcThreads)
-k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ groups,
-                const uvmtier_fault_batch_t *__restrict__ batches, const uvmtier_instance_ptr_entry_t *__restrict__ tbl,
-                uint32_t *__restrict__ count, uint32_t *__restrict__ weight, uint32_t *__restrict__ batch_unmapped,
-                uint32_t *__restrict__ list, int fill, const uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
-{
-    const uint32_t total = prm.n_batches * prm.B;
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-        const uint32_t b = t / prm.B, g = t - b * prm.B;
-        const uvmtier_fault_batch_t bt = batches[b];
-        if (bt.status != NV_OK || g >= bt.num_block_groups)
-            continue;
-        const uvmtier_fault_group_t grp = groups[t];
-        if (grp.flags & 1u)
-            continue;                                       // fatal fault type: service_fault_batch skips it (:2294-2303)
-        const uint32_t slot = svc_slot(prm, tbl[grp.ctx].va_space, grp.block_start);
-        if (slot == 0xffffffffu) {
-            if (!fill)
-                batch_unmapped[b] = 1u;
-            continue;
-        }
-        if (!fill) {
-            atomicAdd(&count[slot], 1u);
-            atomicAdd(&weight[slot], (uint32_t)grp.block_faults);
-        }
-        else
-            list[offset[slot] + atomicAdd(&cursor[slot], 1u)] = t;
-    }
-}
-
-// ---- exclusive scan of count[0..n) into offset[0..n): per-CTA sums, scan of the sums, final pass ----
-__global__ void __launch_bounds__(256)
-k_scan_sums(const uint32_t *__restrict__ in, uint32_t n, uint32_t *__restrict__ sums)
-{
-    __shared__ uint32_t s_w[8];
-    const uint32_t base = blockIdx.x * kScanItems;
-    uint32_t v = 0;
-    for (uint32_t i = threadIdx.x; i < kScanItems; i += 256)
-        if (base + i < n) v += in[base + i];
-    for (int d = 16; d > 0; d >>= 1) v += __shfl_xor_sync(0xffffffffu, v, d);
-    if ((threadIdx.x & 31) == 0) s_w[threadIdx.x >> 5] = v;
-    __syncthreads();
-    if (threadIdx.x == 0) {
-        uint32_t t = 0;
-        for (int w = 0; w < 8; w++) t += s_w[w];
-        sums[blockIdx.x] = t;
-    }
-}
-
-__global__ void __launch_bounds__(1024)
-k_scan_top(uint32_t *__restrict__ sums, uint32_t n_sums)
-{
-    // n_sums <= 1024: one element per thread, in-place exclusive scan
-    __shared__ uint32_t s_w[32];
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t v = tid < n_sums ? sums[tid] : 0u;
-    uint32_t x = v;
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
-        if ((int)lane >= d) x += y;
-    }
-    if (lane == 31) s_w[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = s_w[lane];
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, w, d);
-            if ((int)lane >= d) w += y;
-        }
-        s_w[lane] = w;
-    }
-    __syncthreads();
-    const uint32_t before = warp ? s_w[warp - 1] : 0u;
-    if (tid < n_sums)
-        sums[tid] = before + x - v;
-}
-
-__global__ void __launch_bounds__(256)
-k_scan_final(const uint32_t *__restrict__ in, uint32_t n, const uint32_t *__restrict__ sums, uint32_t *__restrict__ out)
-{
-    // thread t owns 16 consecutive elements
-    __shared__ uint32_t s_w[8];
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t base = blockIdx.x * kScanItems + tid * 16;
-    uint32_t v[16], tot = 0;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        v[k] = base + k < n ? in[base + k] : 0u;
-        tot += v[k];
-    }
-    uint32_t x = tot;
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
-        if ((int)lane >= d) x += y;
-    }
-    if (lane == 31) s_w[warp] = x;
-    __syncthreads();
-    uint32_t before = sums[blockIdx.x];
-    for (uint32_t w = 0; w < warp; w++) before += s_w[w];
-    uint32_t run = before + x - tot;
-#pragma unroll
-    for (int k = 0; k < 16; k++) {
-        if (base + k < n) out[base + k] = run;
-        run += v[k];
-    }
-}
-
-// The same scan in one launch for tables of up to kScanSingleMax slots (three launches cost more than the work):
-// one CTA, thread t owns `per` consecutive elements (per is a multiple of 4, the arrays are 16-byte aligned).
-constexpr uint32_t kScanSingleMax = 1u << 17;
-__global__ void __launch_bounds__(1024)
-k_scan_single(const uint32_t *__restrict__ in, uint32_t n, uint32_t *__restrict__ out)
-{
-    __shared__ uint32_t s_w[32];
-    const uint32_t tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const uint32_t per = (((n + 1023u) / 1024u) + 3u) & ~3u;
-    const uint32_t base = tid * per;
-    uint32_t tot = 0;
-    for (uint32_t k = 0; k < per; k += 4) {
-        if (base + k + 4 <= n) {
-            const uint4 v = *(const uint4 *)(in + base + k);
-            tot += v.x + v.y + v.z + v.w;
-        }
-        else {
-            for (uint32_t j = base + k; j < n && j < base + k + 4; j++) tot += in[j];
-        }
-    }
-    uint32_t x = tot;
-    for (int d = 1; d < 32; d <<= 1) {
-        const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
-        if ((int)lane >= d) x += y;
-    }
-    if (lane == 31) s_w[warp] = x;
-    __syncthreads();
-    if (warp == 0) {
-        uint32_t w = s_w[lane];
-        for (int d = 1; d < 32; d <<= 1) {
-            const uint32_t y = __shfl_up_sync(0xffffffffu, w, d);
-            if ((int)lane >= d) w += y;
-        }
-        s_w[lane] = w;
-    }
-    __syncthreads();
-    uint32_t run = (warp ? s_w[warp - 1] : 0u) + x - tot;
-    for (uint32_t k = 0; k < per; k += 4) {
-        if (base + k + 4 <= n) {
-            const uint4 v = *(const uint4 *)(in + base + k);
-            *(uint4 *)(out + base + k) = make_uint4(run, run + v.x, run + v.x + v.y, run + v.x + v.y + v.z);
-            run += v.x + v.y + v.z + v.w;
-        }
-        else {
-            for (uint32_t j = base + k; j < n && j < base + k + 4; j++) {
-                out[j] = run;
-                run += in[j];
-            }
-        }
-    }
-}
-
-// ------------------------------------------------------------------------------------------------
-// Sorts every slot's run list ascending (the fill pass appends in whatever order its atomics land) and sorts the
-// slots themselves into three classes for the kernels that follow:
-//   lists of more than kSortWarpKeys runs are left to k_service_sort_big   -> big[0] = how many, big[1..] = slots
-//   slots whose runs hold heavy_min or more entries go to k_service_blocks -> heavy[0] = how many, heavy[1..]
-//   everything else is serviced by k_service_blocks_grp.
-// One warp per slot: up to 32 runs in registers, up to kSortWarpKeys in the warp's slice of shared memory.
-constexpr uint32_t kSortWarpKeys = 512;
-constexpr int kSortThreads = 256;
-__global__ void __launch_bounds__(kSortThreads)
-k_service_sort_lists(uint32_t n_slots, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
-                     uint32_t *__restrict__ list, const uint32_t *__restrict__ weight, uint32_t heavy_min,
-                     uint32_t *__restrict__ big, uint32_t *__restrict__ heavy)
-{
-    __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
-    const int lane = threadIdx.x & 31;
-    uint32_t *s_keys = s_all + (threadIdx.x >> 5) * kSortWarpKeys;
-    const uint32_t n_warps = gridDim.x * (kSortThreads / 32);
-    for (uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += n_warps) {
-        const uint32_t cnt = count[slot];
-        if (!cnt)
-            continue;
-        if (lane == 0 && weight[slot] >= heavy_min)
-            heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
-        if (cnt < 2)
-            continue;
-        uint32_t *l = list + offset[slot];
-        if (cnt <= 32) {
-            uint32_t key = (uint32_t)lane < cnt ? l[lane] : 0xffffffffu;
-            for (int k = 2; k <= 32; k <<= 1)
-                for (int j = k >> 1; j > 0; j >>= 1) {
-                    const uint32_t other = __shfl_xor_sync(0xffffffffu, key, j);
-                    const bool up = (lane & k) == 0, keep_min = ((lane & j) == 0) == up;
-                    key = (keep_min == (key < other)) ? key : other;
-                }
-            if ((uint32_t)lane < cnt)
-                l[lane] = key;
-        }
-        else if (cnt <= kSortWarpKeys) {
-            uint32_t P = 64;
-            while (P < cnt) P <<= 1;
-            for (uint32_t i = lane; i < P; i += 32) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
-            __syncwarp();
-            for (uint32_t k = 2; k <= P; k <<= 1)
-                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-                    for (uint32_t i = lane; i < P / 2; i += 32) {
-                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;     // pair (a, a + j), bit j of a clear
-                        const uint32_t x = s_keys[a], y = s_keys[b];
-                        const bool up = (a & k) == 0;
-                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
-                    }
-                    __syncwarp();
-                }
-            for (uint32_t i = lane; i < cnt; i += 32) l[i] = s_keys[i];
-            __syncwarp();
-        }
-        else if (lane == 0) {
-            big[1u + atomicAdd(&big[0], 1u)] = slot;
-        }
-    }
-}
-
-// Long lists (a va_block that many batches touch): one CTA per list, bitonic sort in shared memory up to
-// kSortBigKeys runs; beyond that an odd-even transposition sort in place (slow, but such a list needs more than
-// kSortBigKeys batches that all fault on the same 2 MB).
-constexpr uint32_t kSortBigKeys = 8192;
-constexpr int kSortBigThreads = 512;
-__global__ void __launch_bounds__(kSortBigThreads)
-k_service_sort_big(const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset, uint32_t *__restrict__ list,
-                   const uint32_t *__restrict__ big)
-{
-    __shared__ uint32_t s_keys[kSortBigKeys];
-    const uint32_t n_big = big[0];
-    for (uint32_t q = blockIdx.x; q < n_big; q += gridDim.x) {
-        const uint32_t slot = big[1u + q], cnt = count[slot];
-        uint32_t *l = list + offset[slot];
-        if (cnt <= kSortBigKeys) {
-            uint32_t P = 1024;
-            while (P < cnt) P <<= 1;
-            for (uint32_t i = threadIdx.x; i < P; i += kSortBigThreads) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
-            __syncthreads();
-            for (uint32_t k = 2; k <= P; k <<= 1)
-                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
-                    for (uint32_t i = threadIdx.x; i < P / 2; i += kSortBigThreads) {
-                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;
-                        const uint32_t x = s_keys[a], y = s_keys[b];
-                        const bool up = (a & k) == 0;
-                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
-                    }
-                    __syncthreads();
-                }
-            for (uint32_t i = threadIdx.x; i < cnt; i += kSortBigThreads) l[i] = s_keys[i];
-            __syncthreads();
-        }
-        else {
-            for (uint32_t pass = 0; pass < cnt; pass++) {
-                for (uint32_t i = (pass & 1) + 2 * threadIdx.x; i + 1 < cnt; i += 2 * kSortBigThreads) {
-                    const uint32_t x = l[i], y = l[i + 1];
-                    if (x > y) { l[i] = y; l[i + 1] = x; }
-                }
-                __threadfence_block();
-                __syncthreads();
-            }
-        }
-    }
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -478,7 +212,7 @@ __device__ __forceinline__ svc_entry_eval svc_eval_entry(uint32_t acc, uint32_t 
 __global__ void __launch_bounds__(kSvcThreads)
 k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                  const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
-                 block_state_ptrs st, const uint32_t *__restrict__ count, const uint32_t *__restrict__ offset,
+                 block_state_ptrs st, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
                  const uint32_t *__restrict__ list, const uint32_t *__restrict__ heavy, uint16_t *__restrict__ entry_flags,
                  uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
                  uint32_t *__restrict__ counters)
@@ -487,10 +221,10 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
     const int lane = threadIdx.x & 31, l = lane & 15, warp = threadIdx.x >> 5;
     const uint32_t n_warps = gridDim.x * (kSvcThreads / 32);
     const uint32_t n_heavy = heavy[0];
-    const uint4 *oraw = (const uint4 *)ordered;
+    const uint4 *oraw = (const uint4 *)ordered, *graw = (const uint4 *)groups;
     for (uint32_t q = blockIdx.x * (kSvcThreads / 32) + warp; q < n_heavy; q += n_warps) {
         const uint32_t slot = heavy[1u + q];
-        const uint32_t cnt = count[slot];
+        const uint32_t cnt = cw[slot].x;
         const uint32_t off = offset[slot];
         const size_t w = (size_t)slot * 16 + l;
         uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
@@ -498,11 +232,25 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
         const uint32_t logical = st.logical_prot[slot], pref = st.preferred_location[slot];
         uvmtier_prefetch_info_t pi = st.prefetch_info[slot];
 
+        // Three runs in flight (as in k_service_blocks_grp): run k+1's first 32 entries, run k+2's group and run
+        // k+3's id are loaded while run k is worked on -- a hot va_block is one long chain of dependent steps.
+        uint32_t t0 = list[off];
+        uint32_t t1 = cnt > 1 ? list[off + 1] : t0;
+        uint32_t t2 = cnt > 2 ? list[off + 2] : t0;
+        uint4 g0 = graw[t0], g1 = graw[t1];
+        uint4 e0 = make_uint4(0, 0, 0, 0);
+        if ((uint32_t)lane < (g0.w & 0xffffu))
+            e0 = oraw[svc_batch_of(prm, t0) * prm.B + (g0.z >> 16) + lane];
+
         for (uint32_t k = 0; k < cnt; k++) {
-            const uint32_t t = list[off + k];                             // ascending (batch, run): the list is sorted
-            const uint32_t b = t / prm.B, base = b * prm.B;
-            const uvmtier_fault_group_t grp = groups[t];
-            const uint32_t first = grp.first_fault_index, n = grp.block_faults;
+            const uint32_t t3 = k + 3 < cnt ? list[off + k + 3] : t0;
+            const uint4 g2 = graw[t2];
+            uint4 e1 = make_uint4(0, 0, 0, 0);
+            if ((uint32_t)lane < (g1.w & 0xffffu))
+                e1 = oraw[svc_batch_of(prm, t1) * prm.B + (g1.z >> 16) + lane];
+            const uint32_t t = t0;                                        // ascending (batch, run): the list is sorted
+            const uint32_t b = svc_batch_of(prm, t), base = b * prm.B;
+            const uint32_t first = g0.z >> 16, n = g0.w & 0xffffu;
 
             // ---- service_fault_batch_block_locked :1433-1580, 32 entries at a time ----
             if (lane < 16)
@@ -512,11 +260,11 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
             for (uint32_t c = 0; c < n; c += 32) {
                 const uint32_t i = c + lane;
                 const bool valid = i < n;
-                uint4 e = make_uint4(0, 0, 0, 0);
-                if (valid)
+                uint4 e = e0;
+                if (c && valid)
                     e = oraw[base + first + i];
                 const uint32_t acc = (e.w >> 24) & 7u, num_instances = e.w & 0xffffu, access_type_mask = (e.w >> 16) & 0xffu;
-                const uint32_t page = valid ? (e.x - (uint32_t)grp.block_start) >> 12 : 0x80000000u + lane;
+                const uint32_t page = valid ? (e.x - g0.x) >> 12 : 0x80000000u + lane;
                 uint32_t prev_page = __shfl_up_sync(HW_FULL, page, 1);
                 if (lane == 0)
                     prev_page = carry_page;
@@ -569,7 +317,8 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 if (prm.pf_enable) {
                     const uint32_t flags = UVMTIER_PF_HAS_RESIDENT_MASK | UVMTIER_PF_GPU_VA_SPACE_REGISTERED |
                                            (block_empty ? UVMTIER_PF_BLOCK_RESIDENT_EMPTY : 0u);
-                    pf = pf_get_hint_block(newres, gres, 0u, 0u, false, grp.block_start, 512, rf, ro, prm.gpu_id, pref, flags,
+                    const uint64_t block_start = ((uint64_t)g0.y << 32) | g0.x;
+                    pf = pf_get_hint_block(newres, gres, 0u, 0u, false, block_start, 512, rf, ro, prm.gpu_id, pref, flags,
                                            16u, prm.pf_threshold, prm.pf_min_faults, &pi, &hint, lane);
                 }
                 if (hint != UVMTIER_ID_INVALID) {                         // uvm_va_block_get_prefetch_hint :11856-11876
@@ -630,6 +379,9 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 }
                 rec[8 + l] = page_faults ? newres : 0u;
             }
+            t0 = t1; t1 = t2; t2 = t3;
+            g0 = g1; g1 = g2;
+            e0 = e1;
         }
         if (lane < 16) {
             st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;

@@ -1,0 +1,183 @@
+// service_lists.cuh -- front half of the servicing pass: regroup the va_block runs of all batches by va_block.
+//
+// The reference walks the batches one after the other, so a va_block sees its runs in batch order.  Here every
+// state slot gets the list of its runs (position t = batch * B + run of the group array), ascending:
+//   k_service_count     one thread per run: slot of the run; ONE 64-bit atomic per run adds (1, entries) to the
+//                       slot's packed (run count, entry count) and returns the run's position in the slot's list
+//   k_service_alloc     one thread per slot: list space with one atomic per warp -- lists need not be in slot
+//                       order, so no prefix scan over the table is needed
+//   k_service_fill      one thread per run: list[offset[slot] + position] = t (no atomics)
+//   k_service_sort_*    positions were handed out in arrival order: sort each list, and sort the slots into
+//                       classes for the servicing kernels (see k_service_sort_lists)
+#pragma once
+
+#include "service_kernels.cuh"
+
+namespace uvmtier_k {
+
+// cw[slot] = (number of runs, number of entries) of the slot, packed little-endian in one 64-bit word.
+__global__ void __launch_bounds__(kSvcThreads)
+k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ groups,
+                const uvmtier_fault_batch_t *__restrict__ batches, const uvmtier_instance_ptr_entry_t *__restrict__ tbl,
+                unsigned long long *__restrict__ cw, uint32_t *__restrict__ batch_unmapped, uint2 *__restrict__ slotpos)
+{
+    const uint32_t total = prm.n_batches * prm.B;
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const uint32_t b = svc_batch_of(prm, t), g = t - b * prm.B;
+        const uvmtier_fault_batch_t bt = batches[b];
+        uint2 sp = make_uint2(0xffffffffu, 0u);
+        if (bt.status == NV_OK && g < bt.num_block_groups) {
+            const uvmtier_fault_group_t grp = groups[t];
+            if (!(grp.flags & 1u)) {                        // fatal fault type: service_fault_batch skips it (:2294-2303)
+                const uint32_t slot = svc_slot(prm, tbl[grp.ctx].va_space, grp.block_start);
+                if (slot == 0xffffffffu) {
+                    batch_unmapped[b] = 1u;
+                }
+                else {
+                    const unsigned long long old = atomicAdd(&cw[slot], ((unsigned long long)grp.block_faults << 32) | 1ull);
+                    sp = make_uint2(slot, (uint32_t)old);
+                }
+            }
+        }
+        slotpos[t] = sp;
+    }
+}
+
+__global__ void __launch_bounds__(256)
+k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
+{
+    const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
+    const int lane = threadIdx.x & 31;
+    const uint32_t c = slot < n_slots ? cw[slot].x : 0u;
+    uint32_t incl = c;
+    for (int d = 1; d < 32; d <<= 1) {
+        const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
+        if (lane >= d) incl += y;
+    }
+    const uint32_t tot = __shfl_sync(0xffffffffu, incl, 31);
+    uint32_t base = 0;
+    if (lane == 31 && tot)
+        base = atomicAdd(cursor, tot);
+    base = __shfl_sync(0xffffffffu, base, 31);
+    if (slot < n_slots)
+        offset[slot] = base + incl - c;
+}
+
+__global__ void __launch_bounds__(kSvcThreads)
+k_service_fill(uint32_t total, const uint2 *__restrict__ slotpos, const uint32_t *__restrict__ offset, uint32_t *__restrict__ list)
+{
+    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const uint2 sp = slotpos[t];
+        if (sp.x != 0xffffffffu)
+            list[offset[sp.x] + sp.y] = t;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// Sorts every slot's run list ascending and sorts the slots themselves into three classes for the kernels that
+// follow:
+//   lists of more than kSortWarpKeys runs are left to k_service_sort_big   -> big[0] = how many, big[1..] = slots
+//   slots whose runs hold heavy_min or more entries go to k_service_blocks -> heavy[0] = how many, heavy[1..]
+//   everything else is serviced by k_service_blocks_grp.
+// One warp per slot: up to 32 runs in registers, up to kSortWarpKeys in the warp's slice of shared memory.
+constexpr uint32_t kSortWarpKeys = 512;
+constexpr int kSortThreads = 256;
+__global__ void __launch_bounds__(kSortThreads)
+k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
+                     uint32_t *__restrict__ list, uint32_t heavy_min, uint32_t *__restrict__ big, uint32_t *__restrict__ heavy)
+{
+    __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
+    const int lane = threadIdx.x & 31;
+    uint32_t *s_keys = s_all + (threadIdx.x >> 5) * kSortWarpKeys;
+    const uint32_t n_warps = gridDim.x * (kSortThreads / 32);
+    for (uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += n_warps) {
+        const uint2 c = cw[slot];
+        const uint32_t cnt = c.x;
+        if (!cnt)
+            continue;
+        if (lane == 0 && c.y >= heavy_min)
+            heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
+        if (cnt < 2)
+            continue;
+        uint32_t *l = list + offset[slot];
+        if (cnt <= 32) {
+            uint32_t key = (uint32_t)lane < cnt ? l[lane] : 0xffffffffu;
+            for (int k = 2; k <= 32; k <<= 1)
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    const uint32_t other = __shfl_xor_sync(0xffffffffu, key, j);
+                    const bool up = (lane & k) == 0, keep_min = ((lane & j) == 0) == up;
+                    key = (keep_min == (key < other)) ? key : other;
+                }
+            if ((uint32_t)lane < cnt)
+                l[lane] = key;
+        }
+        else if (cnt <= kSortWarpKeys) {
+            uint32_t P = 64;
+            while (P < cnt) P <<= 1;
+            for (uint32_t i = lane; i < P; i += 32) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
+            __syncwarp();
+            for (uint32_t k = 2; k <= P; k <<= 1)
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    for (uint32_t i = lane; i < P / 2; i += 32) {
+                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;     // pair (a, a + j), bit j of a clear
+                        const uint32_t x = s_keys[a], y = s_keys[b];
+                        const bool up = (a & k) == 0;
+                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
+                    }
+                    __syncwarp();
+                }
+            for (uint32_t i = lane; i < cnt; i += 32) l[i] = s_keys[i];
+            __syncwarp();
+        }
+        else if (lane == 0) {
+            big[1u + atomicAdd(&big[0], 1u)] = slot;
+        }
+    }
+}
+
+// Long lists (a va_block that many batches touch): one CTA per list, bitonic sort in shared memory up to
+// kSortBigKeys runs; beyond that an odd-even transposition sort in place (slow, but such a list needs more than
+// kSortBigKeys batches that all fault on the same 2 MB).
+constexpr uint32_t kSortBigKeys = 8192;
+constexpr int kSortBigThreads = 512;
+__global__ void __launch_bounds__(kSortBigThreads)
+k_service_sort_big(const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset, uint32_t *__restrict__ list,
+                   const uint32_t *__restrict__ big)
+{
+    __shared__ uint32_t s_keys[kSortBigKeys];
+    const uint32_t n_big = big[0];
+    for (uint32_t q = blockIdx.x; q < n_big; q += gridDim.x) {
+        const uint32_t slot = big[1u + q], cnt = cw[slot].x;
+        uint32_t *l = list + offset[slot];
+        if (cnt <= kSortBigKeys) {
+            uint32_t P = 1024;
+            while (P < cnt) P <<= 1;
+            for (uint32_t i = threadIdx.x; i < P; i += kSortBigThreads) s_keys[i] = i < cnt ? l[i] : 0xffffffffu;
+            __syncthreads();
+            for (uint32_t k = 2; k <= P; k <<= 1)
+                for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+                    for (uint32_t i = threadIdx.x; i < P / 2; i += kSortBigThreads) {
+                        const uint32_t a = 2 * i - (i & (j - 1)), b = a + j;
+                        const uint32_t x = s_keys[a], y = s_keys[b];
+                        const bool up = (a & k) == 0;
+                        if ((x > y) == up) { s_keys[a] = y; s_keys[b] = x; }
+                    }
+                    __syncthreads();
+                }
+            for (uint32_t i = threadIdx.x; i < cnt; i += kSortBigThreads) l[i] = s_keys[i];
+            __syncthreads();
+        }
+        else {
+            for (uint32_t pass = 0; pass < cnt; pass++) {
+                for (uint32_t i = (pass & 1) + 2 * threadIdx.x; i + 1 < cnt; i += 2 * kSortBigThreads) {
+                    const uint32_t x = l[i], y = l[i + 1];
+                    if (x > y) { l[i] = y; l[i + 1] = x; }
+                }
+                __threadfence_block();
+                __syncthreads();
+            }
+        }
+    }
+}
+
+} // namespace uvmtier_k

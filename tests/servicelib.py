@@ -66,7 +66,7 @@ def run_service_oracle(orc, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap
     return dict(flags=flags, records=svc[:nsvc], runs=runs, n_runs=n_runs.value, batch=batch, state=st)
 
 
-def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, lanes=4, heavy_min=96, three_kernel_scan=0):
+def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, lanes=4, heavy_min=96):
     """The product's servicing kernels under the CPU SIMT emulator.  lanes = lanes per va_block of the group kernel;
     slots holding heavy_min entries or more go to the warp-per-block kernel (0 = all of them, 0xffffffff = none)."""
     B = int(gp["max_batch_size"][0])
@@ -78,7 +78,7 @@ def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1
     sim.simt_service_fault_batches(ctypes.c_uint32(nb), ctypes.c_uint32(B), P(k1["ordered_rec"]), P(k1["groups"]), P(batch),
                                    P(table), P(layout), ctypes.byref(ptrs), ctypes.c_uint32(pf[0]), ctypes.c_uint32(pf[1]),
                                    ctypes.c_uint32(pf[2]), P(flags), P(svc), P(runs), ctypes.c_uint32(run_cap), P(counters),
-                                   ctypes.c_int(lanes), ctypes.c_uint32(heavy_min), ctypes.c_int(three_kernel_scan))
+                                   ctypes.c_int(lanes), ctypes.c_uint32(heavy_min))
     return dict(flags=flags, service=svc, runs=runs, n_runs=int(counters[0]), batch=batch, state=st)
 
 

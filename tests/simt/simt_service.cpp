@@ -8,6 +8,7 @@
 #include <vector>
 
 #include "service_kernels.cuh"
+#include "service_lists.cuh"
 #include "service_grp.cuh"
 
 using namespace uvmtier_k;
@@ -18,7 +19,7 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
                                           const uvmtier_block_state_t *state, uint32_t pf_enable, uint32_t pf_threshold,
                                           uint32_t pf_min_faults, uint16_t *entry_flags, uvmtier_service_group_t *service,
                                           uvmtier_copy_run_t *runs, uint32_t run_cap, uint32_t *counters, int lanes_per_block,
-                                          uint32_t heavy_min, int three_kernel_scan)
+                                          uint32_t heavy_min)
 {
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
     const size_t total = (size_t)n_batches * B;
@@ -32,29 +33,21 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
     bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0]; bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1]; bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
     bs.prefetch_info = state->prefetch_info; bs.logical_prot = state->logical_prot; bs.preferred_location = state->preferred_location;
 
-    // 16-byte aligned like the device arrays (k_scan_single reads and writes uint4)
-    std::vector<uint4> count4(n_slots / 4 + 2), offset4(n_slots / 4 + 2);
-    uint32_t *count = (uint32_t *)count4.data(), *offset = (uint32_t *)offset4.data();
-    memset(count, 0, (n_slots + 4) * sizeof(uint32_t));
-    std::vector<uint32_t> cursor(n_slots, 0), weight(n_slots, 0), sums(1024, 0), unmapped(n_batches, 0), list(total + 1, 0),
-        big(n_slots + 2, 0), heavy(n_slots + 2, 0);
+    // (runs, entries) per slot packed in 64 bits, like the device array
+    std::vector<unsigned long long> cw64(n_slots + 1, 0);
+    const uint2 *cw = (const uint2 *)cw64.data();
+    std::vector<uint32_t> offset(n_slots + 1, 0), cursor(4, 0), unmapped(n_batches, 0), list(total + 1, 0), big(n_slots + 2, 0),
+        heavy(n_slots + 2, 0);
+    std::vector<uint2> slotpos(total + 1);
     counters[0] = counters[1] = 0;
     memset(entry_flags, 0, total * sizeof(uint16_t));
-    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count, weight.data(), unmapped.data(), list.data(), 0, offset, cursor.data()); });
-    if (!three_kernel_scan && n_slots <= kScanSingleMax) {
-        simt::launch(dim3(1), dim3(1024), [&] { k_scan_single(count, n_slots, offset); });
-    }
-    else {
-        const uint32_t n_sums = (n_slots + kScanItems - 1) / kScanItems;
-        simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_sums(count, n_slots, sums.data()); });
-        simt::launch(dim3(1), dim3(1024), [&] { k_scan_top(sums.data(), n_sums); });
-        simt::launch(dim3(n_sums), dim3(256), [&] { k_scan_final(count, n_slots, sums.data(), offset); });
-    }
-    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, count, weight.data(), unmapped.data(), list.data(), 1, offset, cursor.data()); });
-    simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, count, offset, list.data(), weight.data(), heavy_min, big.data(), heavy.data()); });
-    simt::launch(dim3(2), dim3(kSortBigThreads), [&] { k_service_sort_big(count, offset, list.data(), big.data()); });
+    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, cw64.data(), unmapped.data(), slotpos.data()); });
+    simt::launch(dim3((n_slots + 255) / 256), dim3(256), [&] { k_service_alloc(n_slots, cw, offset.data(), cursor.data()); });
+    simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_fill((uint32_t)total, slotpos.data(), offset.data(), list.data()); });
+    simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, cw, offset.data(), list.data(), heavy_min, big.data(), heavy.data()); });
+    simt::launch(dim3(2), dim3(kSortBigThreads), [&] { k_service_sort_big(cw, offset.data(), list.data(), big.data()); });
     const uint32_t ggrid = (uint32_t)(((size_t)n_slots * lanes_per_block + kGrpThreads - 1) / kGrpThreads);
-#define GRP(G) simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<G>(prm, ordered, groups, batches, bs, count, offset, list.data(), weight.data(), heavy_min, entry_flags, service, runs, counters); })
+#define GRP(G) simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<G>(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), heavy_min, entry_flags, service, runs, counters); })
     switch (lanes_per_block) {
         case 1: GRP(1); break;
         case 2: GRP(2); break;
@@ -63,7 +56,7 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
         default: GRP(4); break;
     }
 #undef GRP
-    simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, count, offset, list.data(), heavy.data(), entry_flags, service, runs, counters); });
+    simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), heavy.data(), entry_flags, service, runs, counters); });
     simt::launch(dim3((n_batches + 127) / 128), dim3(128), [&] { k_service_unmapped(prm, ordered, groups, batches, tbl, unmapped.data(), entry_flags, service); });
     return 0;
 }

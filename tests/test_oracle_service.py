@@ -48,7 +48,7 @@ def test_every_kernel_variant_matches_oracle(dist, lanes, heavy_min):
     pk, tbl, lay = TG.fault_trace(900, 33, dist, 2, total_va_bytes=SMALL_VA)
     gp = TG.gpu_params(128)
     st0 = S.random_state(lay["blocks_per_space"] * 2, 5)
-    _, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min, three_kernel_scan=lanes == 2)
+    _, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
     S.assert_service_equal(want, got, 128, "%s lanes %d heavy_min %d" % (dist, lanes, heavy_min))
 
 

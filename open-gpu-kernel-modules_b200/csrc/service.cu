@@ -23,8 +23,8 @@ constexpr uint32_t kHeavyMinEntries = 96;
 
 // Carves the working space for one call out of `base`.
 struct service_scratch_view {
-    uint32_t *cw, *cursor, *big, *heavy, *batch_unmapped;                // zeroed at the start of every call
-    uint32_t *offset, *slotpos, *list;                                   // fully rewritten before use
+    uint32_t *cw, *cursor, *hist, *bin_cursor, *big, *heavy, *batch_unmapped;   // zeroed at the start of every call
+    uint32_t *offset, *light, *slotpos, *list;                           // fully rewritten before use
     size_t zero_words, words;
 };
 static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint32_t n_batches, size_t total)
@@ -38,11 +38,14 @@ static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint3
     uint32_t *p = base;
     v.cw = p; p += 2 * slots4;
     v.cursor = p; p += 4;
+    v.hist = p; p += kLightBins;
+    v.bin_cursor = p; p += kLightBins;
     v.big = p; p += big_cap;
     v.heavy = p; p += heavy_cap;
     v.batch_unmapped = p; p += batches4;
     v.zero_words = (size_t)(p - base);
     v.offset = p; p += slots4;
+    v.light = p; p += slots4;
     v.slotpos = p; p += 2 * total4;
     v.list = p; p += total4;
     v.words = (size_t)(p - base);
@@ -60,7 +63,7 @@ static uint32_t service_lanes_per_block()
     return (uint32_t)lanes;
 }
 
-template <int G>
+template <int G, int M>
 static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, const uvmtier_ordered_fault_t *d_ordered,
                             const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const block_state_ptrs &bs,
                             const service_scratch_view &v, uint32_t heavy_min, uint16_t *d_entry_flags,
@@ -68,8 +71,8 @@ static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, cons
 {
     const size_t threads = (size_t)prm.n_slots * G;
     const uint32_t grid = (uint32_t)((threads + kGrpThreads - 1) / kGrpThreads);
-    UVMTIER_LAUNCH(k_service_blocks_grp<G>, grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
-                   (const uint2 *)v.cw, v.offset, v.list, heavy_min, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH((k_service_blocks_grp<G, M>), grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
+                   (const uint2 *)v.cw, v.offset, v.list, v.light, v.cursor + 1, d_entry_flags, d_service, d_runs, d_counters);
     return NV_OK;
 }
 
@@ -124,29 +127,34 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
         grid = cap;
     UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl,
                    (unsigned long long *)v.cw, v.batch_unmapped, (uint2 *)v.slotpos);
-    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, v.offset, v.cursor);
-    UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
-
     // UVMTIER_SERVICE_HEAVY_MIN moves the group / warp split up (for experiments; 0xffffffff = no block on a warp).
     // It cannot go below kHeavyMinEntries: that is what bounds the length of the heavy list.
     static const char *heavy_env = getenv("UVMTIER_SERVICE_HEAVY_MIN");
     const uint32_t heavy_min = heavy_env ? (uint32_t)strtoul(heavy_env, NULL, 0) : kHeavyMinEntries;
     const uint32_t list_heavy_min = heavy_min < kHeavyMinEntries ? kHeavyMinEntries : heavy_min;
+    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, list_heavy_min, v.offset, v.cursor, v.hist);
+    UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
     size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
     if (sgrid > cap)
         sgrid = cap;
     UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
-                   v.big, v.heavy);
+                   v.big, v.heavy, v.hist, v.bin_cursor, v.light);
     UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, cw, v.offset, v.list, v.big);
 
+    // lanes per va_block x CTAs per SM the kernel is compiled for; UVMTIER_SERVICE_LANES / UVMTIER_SERVICE_MINCTAS
+    // pick another instantiation (for experiments)
+    static const char *minctas_env = getenv("UVMTIER_SERVICE_MINCTAS");
+    const int minctas = minctas_env ? atoi(minctas_env) : 0;
+#define GRP_ARGS ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters
     NV_STATUS st = NV_OK;
     switch (service_lanes_per_block()) {
-        case 1: st = launch_grp<1>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
-        case 2: st = launch_grp<2>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
-        case 8: st = launch_grp<8>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
-        case 16: st = launch_grp<16>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
-        default: st = launch_grp<4>(ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters); break;
+        case 1: st = launch_grp<1, 1>(GRP_ARGS); break;
+        case 2: st = minctas == 4 ? launch_grp<2, 4>(GRP_ARGS) : (minctas == 3 ? launch_grp<2, 3>(GRP_ARGS) : launch_grp<2, 2>(GRP_ARGS)); break;
+        case 8: st = minctas == 8 ? launch_grp<8, 8>(GRP_ARGS) : (minctas == 6 ? launch_grp<8, 6>(GRP_ARGS) : launch_grp<8, 5>(GRP_ARGS)); break;
+        case 16: st = launch_grp<16, 8>(GRP_ARGS); break;
+        default: st = minctas == 7 ? launch_grp<4, 7>(GRP_ARGS) : minctas == 6 ? launch_grp<4, 6>(GRP_ARGS) : (minctas == 5 ? launch_grp<4, 5>(GRP_ARGS) : launch_grp<4, 4>(GRP_ARGS)); break;
     }
+#undef GRP_ARGS
     if (st != NV_OK)
         return st;
     UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, cw,
@@ -276,7 +284,7 @@ constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of
 constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size
 constexpr uint32_t kNoAllocMaxBatches = 4096;
 // scratch_view() of the largest problem, with room for its alignment padding
-constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 3 + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
+constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 4 + 2 * kLightBins + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
                                  (kNoAllocMaxEntries / kHeavyMinEntries + 8) + kNoAllocMaxBatches +
                                  (size_t)kNoAllocMaxEntries * 3 + 64;
 

@@ -22,6 +22,9 @@ namespace uvmtier_k {
 
 constexpr int kGrpThreads = 128;
 constexpr uint32_t kFullWarp = 0xffffffffu;
+#ifdef UVMTIER_EXPERIMENT_SPREAD
+static __device__ uint32_t g_dbg_counters[1024 * 32];
+#endif
 
 // ---- levels of <= 32 leaves inside one word (same arithmetic as pf_tree_select, offset 0) ----
 __device__ __forceinline__ uint32_t pf_word_levels(uint32_t w, uint32_t fw, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3,
@@ -231,23 +234,26 @@ __device__ __forceinline__ uint32_t svc_claim_runs(uint32_t *counter, uint32_t n
 // ------------------------------------------------------------------------------------------------
 // G lanes per state slot; the slot's run list is sorted.  Slots whose runs hold heavy_min or more entries in
 // total are left to the entry-parallel kernel (k_service_blocks).
-template <int G>
-__global__ void __launch_bounds__(kGrpThreads)
+// M = CTAs per SM the register allocation has to leave room for (occupancy against spills; measured, see service.cu).
+template <int G, int M>
+__global__ void __launch_bounds__(kGrpThreads, M)
 k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                      const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
                      block_state_ptrs st, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
-                     const uint32_t *__restrict__ list, uint32_t heavy_min, uint16_t *__restrict__ entry_flags,
+                     const uint32_t *__restrict__ list, const uint32_t *__restrict__ light,
+                     const uint32_t *__restrict__ n_light, uint16_t *__restrict__ entry_flags,
                      uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
                      uint32_t *__restrict__ counters)
 {
     constexpr int W = 16 / G;
-    const uint32_t slot = (blockIdx.x * blockDim.x + threadIdx.x) / G;
+    // light[] holds the slots this kernel services, longest run list first: the groups of a warp then have about
+    // the same number of steps (a warp takes as many as its longest list) and the long warps start first
+    const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const int lane = threadIdx.x & 31, gl = lane & (G - 1), gb = lane & ~(G - 1);
-    uint32_t cnt = 0;
-    if (slot < prm.n_slots) {
-        const uint2 c = cw[slot];                                         // (runs, entries) of the slot
-        if (c.y < heavy_min)
-            cnt = c.x;
+    uint32_t slot = 0, cnt = 0;
+    if (gid < *n_light) {
+        slot = light[gid];
+        cnt = cw[slot].x;
     }
     const uint32_t cnt_max = __reduce_max_sync(kFullWarp, cnt);
     if (!cnt_max)
@@ -265,7 +271,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
     // Three runs in flight: the loads of run k+1's first entry, run k+2's group and run k+3's id are issued before
     // run k is worked on, so the list -> group -> entry chain is off the critical path.
     const uint4 *graw = (const uint4 *)groups, *oraw = (const uint4 *)ordered;
-    uint32_t t0 = 0, t1 = 0, t2 = 0;
+    uint32_t t0 = 0, t1 = 0, t2 = 0, b0 = 0;
     uint4 g0 = make_uint4(0, 0, 0, 0), g1 = g0, e0 = g0;
     if (owns) {
         off = offset[slot];
@@ -283,19 +289,21 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
         t2 = cnt > 2 ? list[off + 2] : t0;
         g0 = graw[t0];
         g1 = graw[t1];
-        e0 = oraw[svc_batch_of(prm, t0) * prm.B + (g0.z >> 16)];
+        b0 = svc_batch_of(prm, t0);
+        e0 = oraw[b0 * prm.B + (g0.z >> 16)];
     }
 
     for (uint32_t k = 0; k < cnt_max; k++) {
         const bool live = k < cnt;                                        // this group still has a run to service
-        uint32_t t3 = t0;
+        uint32_t t3 = t0, b1 = b0;
         uint4 g2 = g1, e1 = e0;
         if (live) {
             t3 = k + 3 < cnt ? list[off + k + 3] : t0;
             g2 = graw[t2];
-            e1 = oraw[svc_batch_of(prm, t1) * prm.B + (g1.z >> 16)];
+            b1 = svc_batch_of(prm, t1);
+            e1 = oraw[b1 * prm.B + (g1.z >> 16)];
         }
-        const uint32_t t = t0, b = svc_batch_of(prm, t), base = b * prm.B;
+        const uint32_t t = t0, b = b0, base = b * prm.B;
         const uint32_t first = g0.z >> 16, n = live ? (g0.w & 0xffffu) : 0u;
         const uint32_t n_max = __reduce_max_sync(kFullWarp, n);
 
@@ -316,11 +324,11 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             // is the page already mapped for READ / WRITE / ATOMIC?  Its mask words sit on lane `owner`.
             const uint32_t wi = page >> 5, sh = page & 31u;
             const int owner = (int)(wi / W), lw = (int)(wi % W);
-            uint32_t auth = 0;
+            uint32_t a0 = p0[0], a1 = p1[0], a2 = p2[0];
 #pragma unroll
-            for (int w = 0; w < W; w++)
-                if (w == lw)
-                    auth = ((p0[w] >> sh) & 1u) | (((p1[w] >> sh) & 1u) << 1) | (((p2[w] >> sh) & 1u) << 2);
+            for (int w = 1; w < W; w++)
+                if (w == lw) { a0 = p0[w]; a1 = p1[w]; a2 = p2[w]; }
+            uint32_t auth = ((a0 >> sh) & 1u) | (((a1 >> sh) & 1u) << 1) | (((a2 >> sh) & 1u) << 2);
             if (G > 1)
                 auth = __shfl_sync(kFullWarp, auth, gb + owner);
             const svc_entry_eval ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, state, logical, auth);
@@ -421,7 +429,11 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             const uint32_t r0 = tot & 1023u, r1 = (tot >> 10) & 1023u, r2 = tot >> 20;
             run_cnt = r0 + r1 + r2;
             if (__any_sync(kFullWarp, run_cnt != 0u)) {
+#ifdef UVMTIER_EXPERIMENT_SPREAD
+                run_off = svc_claim_runs(&g_dbg_counters[(blockIdx.x & 1023u) * 32u], gl == 0 ? run_cnt : 0u, lane);
+#else
                 run_off = svc_claim_runs(&counters[0], gl == 0 ? run_cnt : 0u, lane);
+#endif
                 if (G > 1)
                     run_off = __shfl_sync(kFullWarp, run_off, gb);
                 // where a run that is still open at the end of this lane's words stops: first stop position in the
@@ -463,14 +475,10 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
                         const uint32_t pos = is0 ? k0 : (is1 ? k1 : k2);
                         k0 += is0; k1 += is1; k2 += 1u - is0 - is1;
                         if (pos < prm.run_cap) {
-                            uvmtier_copy_run_t r;
-                            r.slot = slot;
-                            r.first_page = (uint16_t)first_page;
-                            r.num_pages = (uint16_t)(end - first_page);
-                            r.src = (uint16_t)(is0 ? 0u : (is1 ? 1u : (uint32_t)UVMTIER_RUN_SRC_ZERO));
-                            r.prefetch = (uint16_t)((pf[w] >> s) & 1u);
-                            r.pad = 0;
-                            runs[pos] = r;
+                            // uvmtier_copy_run_t: slot | first_page:16, num_pages:10, src:3, prefetch:1, pad:2
+                            const uint32_t src = is0 ? 0u : (is1 ? 1u : (uint32_t)UVMTIER_RUN_SRC_ZERO);
+                            ((uint2 *)runs)[pos] = make_uint2(slot, first_page | ((end - first_page) << 16) | (src << 26) |
+                                                                        (((pf[w] >> s) & 1u) << 29));
                         }
                     }
                 }
@@ -502,6 +510,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
         t0 = t1; t1 = t2; t2 = t3;
         g0 = g1; g1 = g2;
         e0 = e1;
+        b0 = b1;
     }
     if (owns) {
         st_words<W>(st.gpu_resident + wbase, gres);

@@ -68,7 +68,9 @@ struct block_state_ptrs {
 // uvm_fault_access_type_to_prot, UVM/uvm_hal_types.h:522-537
 __device__ __forceinline__ uint32_t svc_prot_of(uint32_t acc)
 {
-    return acc == ACC_ATOMIC_STRONG ? PROT_RWA : ((acc == ACC_ATOMIC_WEAK || acc == ACC_WRITE) ? PROT_RW : PROT_RO);
+    // PREFETCH, READ -> RO; WRITE, ATOMIC_WEAK -> RW; ATOMIC_STRONG -> RWA; anything else -> RO: two bits per
+    // access type, looked up in a constant
+    return (0x57A5u >> (2u * (acc & 7u))) & 3u;
 }
 
 // State slot of a run, or 0xFFFFFFFF when its va_block lies in no va_range of its VA space.

@@ -43,12 +43,28 @@ k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ g
     }
 }
 
+// Also counts the light slots (fewer than heavy_min entries) by number of runs: hist[kLightBins - 1 - min(runs,
+// kLightBins - 1)], so that k_service_sort_lists can line them up with the longest lists first.  cursor[0] = list
+// space handed out, cursor[1] = number of light slots.
+constexpr uint32_t kLightBins = 256;
 __global__ void __launch_bounds__(256)
-k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t *__restrict__ offset, uint32_t *__restrict__ cursor)
+k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t heavy_min, uint32_t *__restrict__ offset,
+                uint32_t *__restrict__ cursor, uint32_t *__restrict__ hist)
 {
+    __shared__ uint32_t s_hist[kLightBins];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
-    const uint32_t c = slot < n_slots ? cw[slot].x : 0u;
+    const uint2 cwv = slot < n_slots ? cw[slot] : make_uint2(0u, 0u);
+    const uint32_t c = cwv.x;
+    s_hist[threadIdx.x] = 0;
+    __syncthreads();
+    if (c && cwv.y < heavy_min)
+        atomicAdd(&s_hist[kLightBins - 1u - min(c, kLightBins - 1u)], 1u);
+    __syncthreads();
+    if (s_hist[threadIdx.x]) {
+        atomicAdd(&hist[threadIdx.x], s_hist[threadIdx.x]);
+        atomicAdd(&cursor[1], s_hist[threadIdx.x]);
+    }
     uint32_t incl = c;
     for (int d = 1; d < 32; d <<= 1) {
         const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
@@ -82,21 +98,46 @@ k_service_fill(uint32_t total, const uint2 *__restrict__ slotpos, const uint32_t
 // One warp per slot: up to 32 runs in registers, up to kSortWarpKeys in the warp's slice of shared memory.
 constexpr uint32_t kSortWarpKeys = 512;
 constexpr int kSortThreads = 256;
+static_assert(kLightBins == (uint32_t)kSortThreads, "one thread per bin in the histogram scan");
 __global__ void __launch_bounds__(kSortThreads)
 k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
-                     uint32_t *__restrict__ list, uint32_t heavy_min, uint32_t *__restrict__ big, uint32_t *__restrict__ heavy)
+                     uint32_t *__restrict__ list, uint32_t heavy_min, uint32_t *__restrict__ big, uint32_t *__restrict__ heavy,
+                     const uint32_t *__restrict__ hist, uint32_t *__restrict__ bin_cursor, uint32_t *__restrict__ light)
 {
     __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
+    __shared__ uint32_t s_base[kLightBins], s_part[kSortThreads / 32];
     const int lane = threadIdx.x & 31;
     uint32_t *s_keys = s_all + (threadIdx.x >> 5) * kSortWarpKeys;
     const uint32_t n_warps = gridDim.x * (kSortThreads / 32);
+    {
+        // where each bin of the light list starts: exclusive scan of the histogram (kLightBins == kSortThreads)
+        const uint32_t v = hist[threadIdx.x];
+        uint32_t x = v;
+        for (int d = 1; d < 32; d <<= 1) {
+            const uint32_t y = __shfl_up_sync(0xffffffffu, x, d);
+            if (lane >= d) x += y;
+        }
+        if (lane == 31) s_part[threadIdx.x >> 5] = x;
+        __syncthreads();
+        uint32_t before = 0;
+        for (uint32_t w = 0; w < (threadIdx.x >> 5); w++) before += s_part[w];
+        s_base[threadIdx.x] = before + x - v;
+        __syncthreads();
+    }
     for (uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += n_warps) {
         const uint2 c = cw[slot];
         const uint32_t cnt = c.x;
         if (!cnt)
             continue;
-        if (lane == 0 && c.y >= heavy_min)
-            heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
+        if (lane == 0) {
+            if (c.y >= heavy_min) {
+                heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
+            }
+            else {
+                const uint32_t bin = kLightBins - 1u - min(cnt, kLightBins - 1u);
+                light[s_base[bin] + atomicAdd(&bin_cursor[bin], 1u)] = slot;
+            }
+        }
         if (cnt < 2)
             continue;
         uint32_t *l = list + offset[slot];

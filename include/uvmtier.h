@@ -305,7 +305,10 @@ typedef struct {
  *   gpu_pte[k]        gpu_state->pte_bits[UVM_PTE_BITS_GPU_READ/WRITE/ATOMIC]
  *   prefetch_info     va_block->prefetch_info                                 (:478-483)
  *   logical_prot      compute_logical_prot() of the block's VMA: 0 NONE, 1 READ_ONLY, 3 READ_WRITE_ATOMIC
- *   preferred_location policy->preferred_location (UVMTIER_ID_INVALID = none) */
+ *   preferred_location policy->preferred_location (UVMTIER_ID_INVALID = none)
+ *   gpu_evicted       gpu_state->evicted: pages an eviction moved off this GPU and that have not come back
+ *                     (UVM/uvm_va_block.h:161-164, set :5023-5037, cleared :4978-4988).  May be NULL when the
+ *                     caller never evicts (the servicing pass then skips it). */
 typedef struct {
     uvmtier_page_mask_t *gpu_resident;
     uvmtier_page_mask_t *cpu_resident[2];
@@ -313,6 +316,7 @@ typedef struct {
     uvmtier_prefetch_info_t *prefetch_info;
     uint8_t *logical_prot;
     uint16_t *preferred_location;
+    uvmtier_page_mask_t *gpu_evicted;
 } uvmtier_block_state_t;
 
 #define UVMTIER_SF_SERVICED         0x0001u /* page added to new_residency (:1560-1579) */
@@ -341,16 +345,23 @@ typedef struct {
     uvmtier_page_mask_t new_residency; /* per_processor_masks[gpu].new_residency after the prefetch hint */
 } uvmtier_service_group_t;           /* 96 bytes */
 
-/* One contiguous page run to move into HBM (block_copy_resident_pages_between coalesces consecutive pages
- * with the same cause when both sides are block-contiguous, UVM/uvm_va_block.c:4242-4335). */
+/* One contiguous page run to move between tiers (block_copy_resident_pages_between coalesces consecutive pages
+ * with the same cause when both sides are block-contiguous, UVM/uvm_va_block.c:4242-4335).  The servicing pass
+ * only produces runs into HBM (dst 0); uvmtier_make_resident_device also produces runs into the CPU nodes. */
+#define UVMTIER_RUN_SRC_DRAM 0u
+#define UVMTIER_RUN_SRC_CXL  1u
+#define UVMTIER_RUN_SRC_HBM  2u
 #define UVMTIER_RUN_SRC_ZERO 7u
+#define UVMTIER_RUN_DST_HBM  0u
+#define UVMTIER_RUN_DST_DRAM 1u
+#define UVMTIER_RUN_DST_CXL  2u
 typedef struct {
     uint32_t slot;
     uint16_t first_page;
     uint16_t num_pages : 10;
-    uint16_t src : 3;                /* CPU node (0 DRAM, 1 CXL) or UVMTIER_RUN_SRC_ZERO (first touch) */
+    uint16_t src : 3;                /* UVMTIER_RUN_SRC_*: CPU node 0 / 1, this GPU, or zero fill (first touch) */
     uint16_t prefetch : 1;           /* cause is PREFETCH rather than the fault */
-    uint16_t pad : 2;
+    uint16_t dst : 2;                /* UVMTIER_RUN_DST_* */
 } uvmtier_copy_run_t;                /* 8 bytes */
 
 /* Allocates (zeroed, logical_prot = READ_WRITE_ATOMIC, no preferred location, prefetch_info =
@@ -405,6 +416,69 @@ NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint3
                                                        const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
                                                        uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
                                                        uint32_t run_cap, uint32_t *d_counters);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (1c) make_resident on the state table -- UVM/uvm_va_block.c:4877-5114                       */
+/* ------------------------------------------------------------------------------------------ */
+
+/* uvm_make_resident_cause_t (UVM/uvm_va_block_types.h:116-129) */
+#define UVMTIER_CAUSE_REPLAYABLE_FAULT     0u
+#define UVMTIER_CAUSE_NON_REPLAYABLE_FAULT 1u
+#define UVMTIER_CAUSE_ACCESS_COUNTER       2u
+#define UVMTIER_CAUSE_PREFETCH             3u
+#define UVMTIER_CAUSE_EVICTION             4u
+#define UVMTIER_CAUSE_API_TOOLS            5u
+#define UVMTIER_CAUSE_API_MIGRATE          6u
+#define UVMTIER_CAUSE_API_SET_RANGE_GROUP  7u
+#define UVMTIER_CAUSE_API_HINT             8u
+
+#define UVMTIER_MR_HAS_PAGE_MASK     0x1u  /* page_mask = d_page_masks[mask_row], else NULL (= the whole region) */
+#define UVMTIER_MR_HAS_PREFETCH_MASK 0x2u  /* prefetch_page_mask = d_prefetch_masks[mask_row] (fault causes only) */
+#define UVMTIER_MR_EVICT_GPU_PAGES   0x4u  /* page_mask = the block's gpu_resident pages in the region: what
+                                              uvm_va_block_evict_chunks builds for a 2 MB root chunk (:13055-13080) */
+
+/* One uvm_va_block_make_resident call (UVM/uvm_va_block.h:770-777): move the pages of `region` (and page_mask)
+ * to dest_tier.  dest_tier = UVMTIER_TIER_HBM is dest_id = this GPU; UVMTIER_TIER_DRAM / _CXL is dest_id = CPU
+ * with make_resident.dest_nid = node 0 / 1. */
+typedef struct {
+    uint32_t slot;
+    uint16_t region_first, region_outer;
+    uint8_t  dest_tier;
+    uint8_t  cause;                  /* UVMTIER_CAUSE_* */
+    uint16_t flags;                  /* UVMTIER_MR_* */
+    uint32_t mask_row;
+} uvmtier_make_resident_req_t;       /* 16 bytes */
+
+/* What the call leaves in va_block_context->make_resident (UVM/uvm_va_block_types.h:197-242). */
+typedef struct {
+    uint32_t slot;
+    uint16_t migrated[3];            /* pages copied from CPU node 0, CPU node 1, this GPU */
+    uint16_t first_touch;            /* pages resident nowhere: populated and zeroed at the destination */
+    uint32_t run_offset;             /* first copy run of this request in the run array */
+    uint16_t run_count;
+    uint16_t unmapped;               /* GPU mappings removed (pages the GPU had mapped that left it) */
+    uint32_t reserved[3];
+    uvmtier_page_mask_t pages_migrated;
+    uvmtier_page_mask_t pages_changed_residency;
+} uvmtier_make_resident_result_t;    /* 160 bytes */
+
+/* Batched uvm_va_block_make_resident (= _copy + _finish, :5086-5114) on the flat state table: residency algebra
+ * (block_copy_resident_pages :4660-4847: copy = page_mask & ~resident(dest); GPU destination takes from CPU node
+ * 0 then node 1; CPU destination takes from the other CPU node first, then from the GPU), first touch
+ * (:4581-4619), state update (:4990-5040: resident masks, gpu_evicted set on EVICTION / cleared on return),
+ * clearing of every other residency (break_read_duplication_in_region :4538-4579), removal of the GPU's mappings
+ * of pages that leave it (:4919-4926), and the copy list: runs d_runs[run_offset .. run_offset + run_count) per
+ * request (uvmtier_copy_runs_device executes them).  Requests of one call must name distinct slots (a va_block
+ * is locked for the duration of a make_resident; two requests on one block in the same call would race).
+ * d_page_masks / d_prefetch_masks may be NULL when no request refers to them.  d_counters[0] += number of runs
+ * (the caller zeroes it, or keeps accumulating behind a servicing pass). */
+NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n_requests,
+                                       const uvmtier_make_resident_req_t *d_requests,
+                                       const uvmtier_page_mask_t *d_page_masks,
+                                       const uvmtier_page_mask_t *d_prefetch_masks,
+                                       const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                       uvmtier_make_resident_result_t *d_results, uvmtier_copy_run_t *d_runs,
+                                       uint32_t run_cap, uint32_t *d_counters);
 
 /* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
@@ -535,9 +609,12 @@ NV_STATUS uvmtier_copy_page_list(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t
                                  const uint64_t *h_dst_off, const uint64_t *h_src_off, uint32_t page_size, int method);
 
 /* Executes the copy runs produced by the servicing / make_resident passes: run r moves pages
- * [first_page, first_page + num_pages) of slot r.slot from tier (DRAM for src 0, CXL for src 1) into the HBM
- * tier at the same block offset; UVMTIER_RUN_SRC_ZERO runs zero-fill (block_populate_gpu_chunk zeroes new
- * chunks, UVM/uvm_va_block.c:3011).  n_runs is read from the device counter d_n_runs (clamped to run_cap). */
+ * [first_page, first_page + num_pages) of slot r.slot from the tier r.src names (DRAM, CXL, HBM) to the tier
+ * r.dst names, at the same block offset (slot * 2 MB + page * 4 KB in every arena); UVMTIER_RUN_SRC_ZERO runs
+ * zero-fill the destination (block_populate_gpu_chunk zeroes new chunks, UVM/uvm_va_block.c:3011; CPU pages
+ * :1977-1983).  DRAM <-> CXL runs replace the reference's kmap + memcpy page loop (:3972-3984) with the same SM
+ * copy kernel reading and writing host-mapped memory.  n_runs is read from the device counter d_n_runs (clamped
+ * to run_cap).  Runs are grouped by (src, dst) pair; the pairs execute one after the other on the stream. */
 NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs,
                                    uint32_t run_cap, int method);
 

@@ -5,6 +5,13 @@
 
 #include <stdint.h>
 
+// A kernel defined in a header that more than one .cu file includes: internal linkage.
+#ifdef UVMTIER_SIMT_EMU
+#define UVMTIER_KERNEL static
+#else
+#define UVMTIER_KERNEL static __global__
+#endif
+
 // Dynamic shared memory of the running CTA (the emulator gives every CTA the same static buffer).
 #ifdef UVMTIER_SIMT_EMU
 #define UVMTIER_DYN_SMEM(name) unsigned char *name = (unsigned char *)simt::g_dynamic_smem

@@ -29,7 +29,7 @@ struct uvmtier_tier {
 
 struct uvmtier_tiers {
     uvmtier_tier t[UVMTIER_MAX_TIERS];
-    uint64_t *d_lists;    // scratch for uvmtier_copy_runs_device: 3 page lists + counters
+    uint64_t *d_lists;    // scratch for uvmtier_copy_runs_device: the page list (all pairs) and the per-pair counters
     uint32_t *d_list_count;
     uint32_t list_cap;
     uint32_t *h_list_count;   // pinned
@@ -67,6 +67,8 @@ void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx)
         tier_release(ctx, &ctx->tiers->t[i]);
     if (ctx->tiers->d_lists)
         cudaFree(ctx->tiers->d_lists);
+    if (ctx->tiers->d_list_count)
+        cudaFree(ctx->tiers->d_list_count);
     if (ctx->tiers->h_list_count)
         cudaFreeHost(ctx->tiers->h_list_count);
     free(ctx->tiers);
@@ -343,60 +345,82 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
 {
     if (!ctx || !d_runs || !d_n_runs)
         return NV_ERR_INVALID_ARGUMENT;
-    if (!ctx->tiers || !ctx->tiers->t[UVMTIER_TIER_HBM].used)
+    if (!ctx->tiers)
         return NV_ERR_INVALID_STATE;
     if (!run_cap)
         return NV_OK;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     uvmtier_tiers *ts = ctx->tiers;
-    // a run has at most 512 pages, but the lists are sized from the HBM arena: no more pages than it holds
-    const uint64_t hbm_pages = ts->t[UVMTIER_TIER_HBM].info.bytes / UVMTIER_PAGE_SIZE;
-    const uint32_t want = (uint32_t)(hbm_pages < 0x7fffffffull ? hbm_pages : 0x7fffffffull);
-    if (want > ts->list_cap) {
-        if (ts->d_lists) {
-            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-            UVMTIER_CUDA(cudaFree(ts->d_lists));
-            ts->d_lists = NULL;
-        }
-        UVMTIER_CUDA(cudaMalloc(&ts->d_lists, (size_t)want * 3 * sizeof(uint64_t) + 64));
-        ts->d_list_count = (uint32_t *)(ts->d_lists + (size_t)want * 3);
-        ts->list_cap = want;
-    }
+    if (!ts->d_list_count)
+        UVMTIER_CUDA(cudaMalloc(&ts->d_list_count, 2 * kRunPairs * sizeof(uint32_t)));
     if (!ts->h_list_count)
-        UVMTIER_CUDA(cudaHostAlloc(&ts->h_list_count, 64, cudaHostAllocPortable));
-    uint64_t *l0 = ts->d_lists, *l1 = l0 + ts->list_cap, *lz = l1 + ts->list_cap;
-    UVMTIER_CUDA(cudaMemsetAsync(ts->d_list_count, 0, 16, ctx->stream));
+        UVMTIER_CUDA(cudaHostAlloc(&ts->h_list_count, kRunPairs * sizeof(uint32_t), cudaHostAllocPortable));
+    uint32_t *d_pair_count = ts->d_list_count, *d_pair_cursor = ts->d_list_count + kRunPairs;
+    UVMTIER_CUDA(cudaMemsetAsync(ts->d_list_count, 0, 2 * kRunPairs * sizeof(uint32_t), ctx->stream));
     size_t grid = ((size_t)run_cap + 255) / 256, cap = (size_t)ctx->sm_count * 8;
     if (grid > cap)
         grid = cap;
-    UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, l0, l1, lz, ts->d_list_count,
-                   ts->list_cap);
-    // the list lengths size the copy grids: one small D2H read (the reference also walks its masks on the CPU)
-    UVMTIER_CUDA(cudaMemcpyAsync(ts->h_list_count, ts->d_list_count, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_LAUNCH(k_count_run_pages, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, d_pair_count);
+    // the per-pair page counts size the list and the copy grids: one small D2H read (the reference also walks its
+    // masks on the CPU)
+    UVMTIER_CUDA(cudaMemcpyAsync(ts->h_list_count, d_pair_count, kRunPairs * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-    uint8_t *hbm = (uint8_t *)ts->t[UVMTIER_TIER_HBM].info.device_ptr;
-    for (int which = 0; which < 2; which++) {
-        const uint32_t n = ts->h_list_count[which] < ts->list_cap ? ts->h_list_count[which] : ts->list_cap;
+    run_pair_bases bases;
+    uint64_t total = 0;
+    for (uint32_t p = 0; p < kRunPairs; p++) {
+        bases.base[p] = (uint32_t)total;
+        total += ts->h_list_count[p];
+    }
+    if (!total)
+        return NV_OK;
+    if (total > 0xffffffffull)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (total > ts->list_cap) {
+        if (ts->d_lists) {
+            UVMTIER_CUDA(cudaFree(ts->d_lists));
+            ts->d_lists = NULL;
+            ts->list_cap = 0;
+        }
+        const uint64_t want = total + total / 4 + 4096;
+        UVMTIER_CUDA(cudaMalloc(&ts->d_lists, want * sizeof(uint64_t)));
+        ts->list_cap = (uint32_t)(want < 0xffffffffull ? want : 0xffffffffull);
+    }
+    UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, bases, d_pair_cursor, ts->d_lists,
+                   ts->list_cap);
+    static const uint32_t src_tier_of[4] = {UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL, UVMTIER_TIER_HBM, 0};
+    static const uint32_t dst_tier_of[3] = {UVMTIER_TIER_HBM, UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL};
+    for (uint32_t pair = 0; pair < kRunPairs; pair++) {
+        const uint32_t n = ts->h_list_count[pair];
         if (!n)
             continue;
-        const uint32_t tier = which == 0 ? UVMTIER_TIER_DRAM : UVMTIER_TIER_CXL;
-        if (!ts->t[tier].used)
+        const uint32_t src = pair / 3, dst_tier = dst_tier_of[pair % 3];
+        if (!ts->t[dst_tier].used)
+            return NV_ERR_INVALID_STATE;
+        uint8_t *dst_base = (uint8_t *)ts->t[dst_tier].info.device_ptr;
+        const uint64_t *list = ts->d_lists + bases.base[pair];
+        if (src == 3) {                                   // first touch: zero fill at the destination
+            const uint32_t zg = n < (uint32_t)ctx->sm_count * 16 ? n : (uint32_t)ctx->sm_count * 16;
+            UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, dst_base, list, (uint64_t)n, 1u);
+            continue;
+        }
+        const uint32_t src_tier = src_tier_of[src];
+        if (src_tier == dst_tier) {
+            uvmtier_set_error("uvmtier_copy_runs_device: a run names the same tier as source and destination",
+                              cudaErrorInvalidValue, __FILE__, __LINE__);
+            return NV_ERR_INVALID_ARGUMENT;
+        }
+        if (!ts->t[src_tier].used)
             return NV_ERR_INVALID_STATE;
         copy_list_params p;
-        p.src_base = (const uint8_t *)ts->t[tier].info.device_ptr;
-        p.dst_base = hbm;
-        p.src_off = which == 0 ? l0 : l1;
-        p.dst_off = p.src_off;
+        p.src_base = (const uint8_t *)ts->t[src_tier].info.device_ptr;
+        p.dst_base = dst_base;
+        p.src_off = list;
+        p.dst_off = list;
         p.n_pages = n;
         p.pieces_per_page = 1;
         NV_STATUS st = launch_copy(ctx, p, method);
         if (st != NV_OK)
             return st;
-    }
-    const uint32_t nz = ts->h_list_count[2] < ts->list_cap ? ts->h_list_count[2] : ts->list_cap;
-    if (nz) {
-        const uint32_t zg = nz < (uint32_t)ctx->sm_count * 16 ? nz : (uint32_t)ctx->sm_count * 16;
-        UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, hbm, lz, (uint64_t)nz, 1u);
     }
     return NV_OK;
 }

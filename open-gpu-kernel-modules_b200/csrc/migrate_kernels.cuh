@@ -204,19 +204,48 @@ __global__ void __launch_bounds__(256) k_zero_pages(uint8_t *base, const uint64_
     }
 }
 
-// Expands copy runs into per-page offset lists: for run r, page j: offset = slot * 2 MB + (first_page + j) * 4 KB
-// (the same offset in the source tier and in HBM).  Three lists: from DRAM, from CXL, zero-fill.  Counters:
-// list_count[3].  One thread per run; pages are appended with one atomicAdd per run.
+// Copy runs are executed per (source, destination) pair.  pair = src_code * 3 + dst, src_code 0 DRAM, 1 CXL, 2 HBM,
+// 3 zero fill; dst 0 HBM, 1 DRAM, 2 CXL (UVMTIER_RUN_SRC_* / UVMTIER_RUN_DST_*).
+constexpr uint32_t kRunPairs = 12;
+struct run_pair_bases { uint32_t base[kRunPairs]; };
+__device__ __forceinline__ uint32_t run_pair_of(const uvmtier_copy_run_t &run)
+{
+    const uint32_t src = run.src == UVMTIER_RUN_SRC_ZERO ? 3u : (run.src > 2u ? 2u : (uint32_t)run.src);
+    const uint32_t dst = run.dst > 2u ? 2u : (uint32_t)run.dst;
+    return src * 3u + dst;
+}
+
+// Pass 1: pages per pair (sizes the page list and places each pair's segment in it).
+__global__ void __launch_bounds__(256) k_count_run_pages(const uvmtier_copy_run_t *runs, const uint32_t *n_runs_dev, uint32_t run_cap,
+                                                         uint32_t *pair_count)
+{
+    __shared__ uint32_t s_count[kRunPairs];
+    if (threadIdx.x < kRunPairs) s_count[threadIdx.x] = 0;
+    __syncthreads();
+    const uint32_t n_runs = min(*n_runs_dev, run_cap);
+    for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
+        const uvmtier_copy_run_t run = runs[r];
+        if (run.num_pages)
+            atomicAdd(&s_count[run_pair_of(run)], (uint32_t)run.num_pages);
+    }
+    __syncthreads();
+    if (threadIdx.x < kRunPairs && s_count[threadIdx.x])
+        atomicAdd(&pair_count[threadIdx.x], s_count[threadIdx.x]);
+}
+
+// Pass 2: expands the runs into one page-offset list, pair after pair: for run r, page j the offset
+// slot * 2 MB + (first_page + j) * 4 KB (the same offset in every tier's arena).  One thread per run; a run's pages
+// are appended to its pair's segment with one atomicAdd.
 __global__ void __launch_bounds__(256) k_expand_runs(const uvmtier_copy_run_t *runs, const uint32_t *n_runs_dev, uint32_t run_cap,
-                                                     uint64_t *list0, uint64_t *list1, uint64_t *listz, uint32_t *list_count,
-                                                     uint32_t list_cap)
+                                                     run_pair_bases bases, uint32_t *pair_cursor, uint64_t *list, uint32_t list_cap)
 {
     const uint32_t n_runs = min(*n_runs_dev, run_cap);
     for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
         const uvmtier_copy_run_t run = runs[r];
-        const uint32_t which = run.src == 0 ? 0u : (run.src == 1 ? 1u : 2u);
-        uint64_t *list = which == 0 ? list0 : (which == 1 ? list1 : listz);
-        const uint32_t at = atomicAdd(&list_count[which], (uint32_t)run.num_pages);
+        if (!run.num_pages)
+            continue;
+        const uint32_t pair = run_pair_of(run);
+        const uint32_t at = bases.base[pair] + atomicAdd(&pair_cursor[pair], (uint32_t)run.num_pages);
         const uint64_t base = (uint64_t)run.slot * UVMTIER_VA_BLOCK_SIZE + (uint64_t)run.first_page * UVMTIER_PAGE_SIZE;
         for (uint32_t j = 0; j < run.num_pages; j++)
             if (at + j < list_cap)

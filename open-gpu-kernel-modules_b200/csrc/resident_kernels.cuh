@@ -1,0 +1,144 @@
+// resident_kernels.cuh -- uvm_va_block_make_resident on the flat state table, one request per warp.
+// Device code only (host side: resident.cu); also compiled by tests/simt for the CPU emulator.
+//
+// Reference (UVM = kernel-open/nvidia-uvm, uvm_va_block.c): uvm_va_block_make_resident (:5086-5114) =
+// _copy (:4877-4976: unmap, populate, block_copy_resident_pages :4660-4847) + _finish (:5042-5084:
+// block_make_resident_update_state :4990-5040, block_copy_set_first_touch_residency :4581-4619,
+// break_read_duplication_in_region :4538-4579).  Callers: uvm_va_block_migrate_locked (uvm_migrate.c:225-289),
+// uvm_va_block_evict_chunks (:12999-13130, cause EVICTION, page_mask = chunk pages & gpu resident), the CPU fault
+// handler, and the GPU fault path (which this library runs inside the servicing pass instead).
+//
+// Processors of the table: this GPU, and the CPU with two NUMA nodes (0 = host DRAM, 1 = CXL).  Residency is
+// exclusive (no read duplication in the harness), CPU pages are allocated on the node the request names
+// (block_populate_pages_cpu's first choice, :1887-2018), so every page of a request has at most one source.
+// Masks: one 32-bit word per lane, lanes 16-31 mirror lanes 0-15 (mask512.cuh helpers are half-warp wide).
+#pragma once
+
+#include "service_kernels.cuh"
+
+namespace uvmtier_k {
+
+constexpr int kResThreads = 128;
+
+struct resident_kparams {
+    uint32_t n_requests, n_slots, run_cap;
+};
+
+__global__ void __launch_bounds__(kResThreads)
+k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restrict__ reqs,
+                const uint32_t *__restrict__ page_masks, const uint32_t *__restrict__ prefetch_masks, block_state_ptrs st,
+                uvmtier_make_resident_result_t *__restrict__ results, uvmtier_copy_run_t *__restrict__ runs,
+                uint32_t *__restrict__ counters)
+{
+    const int lane = threadIdx.x & 31, l = lane & 15;
+    const uint32_t n_warps = gridDim.x * (kResThreads / 32);
+    for (uint32_t q = blockIdx.x * (kResThreads / 32) + (threadIdx.x >> 5); q < prm.n_requests; q += n_warps) {
+        const uvmtier_make_resident_req_t rq = reqs[q];
+        uint32_t *res = (uint32_t *)&results[q];
+        const uint32_t slot = rq.slot;
+        const bool dst_gpu = rq.dest_tier == UVMTIER_TIER_HBM;
+        const bool valid = slot < prm.n_slots && rq.region_first <= rq.region_outer && rq.region_outer <= 512u &&
+                           (dst_gpu || rq.dest_tier == UVMTIER_TIER_DRAM || rq.dest_tier == UVMTIER_TIER_CXL);
+        if (!valid) {                                                     // uniform across the warp
+            if (lane < 16) {
+                if (l < 8) res[l] = l == 0 ? 0xffffffffu : 0u;            // slot 0xFFFFFFFF marks a rejected request
+                res[8 + l] = 0;
+                res[24 + l] = 0;
+            }
+            continue;
+        }
+        const size_t w = (size_t)slot * 16 + l;
+        uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
+        uint32_t pte0 = st.gpu_pte[0][w], pte1 = st.gpu_pte[1][w], pte2 = st.gpu_pte[2][w];
+        uint32_t evicted = st.gpu_evicted ? st.gpu_evicted[w] : 0u;
+
+        // page_mask restricted to the region; NULL page_mask = the whole region
+        uint32_t pm = hw_range((int)rq.region_first, (int)rq.region_outer, l);
+        if (rq.flags & UVMTIER_MR_HAS_PAGE_MASK)
+            pm &= page_masks[(size_t)rq.mask_row * 16 + l];
+        if (rq.flags & UVMTIER_MR_EVICT_GPU_PAGES)
+            pm &= gres;                                                   // pages_to_evict (:13078)
+        const uint32_t pf = (rq.flags & UVMTIER_MR_HAS_PREFETCH_MASK) ? prefetch_masks[(size_t)rq.mask_row * 16 + l] : 0u;
+
+        // block_copy_resident_pages: what is missing at the destination, and where each page comes from
+        const int nid = rq.dest_tier == UVMTIER_TIER_CXL ? 1 : 0;
+        const uint32_t dst_res = dst_gpu ? gres : (nid ? c1 : c0);
+        const uint32_t copy = pm & ~dst_res;                              // :4687-4692
+        uint32_t from[3];                                                 // CPU node 0, CPU node 1, this GPU
+        if (dst_gpu) {
+            from[0] = copy & c0;                                          // CPU nodes in ascending order (:4490)
+            from[1] = copy & ~from[0] & c1;
+            from[2] = 0;
+        }
+        else {
+            // the CPU itself is the closest source: the other node first (:4486-4497), then the GPU
+            const uint32_t other = copy & (nid ? c0 : c1);
+            from[nid] = 0;
+            from[nid ^ 1] = other;
+            from[2] = copy & ~other & gres;
+        }
+        const uint32_t migrated = from[0] | from[1] | from[2];
+        // pages resident nowhere are populated (and zeroed) at the destination: first touch (:4581-4619)
+        const uint32_t touch = copy & ~migrated;
+        const uint32_t dst_code = dst_gpu ? UVMTIER_RUN_DST_HBM : (nid ? UVMTIER_RUN_DST_CXL : UVMTIER_RUN_DST_DRAM);
+
+        // copy list: per source in the order the reference visits them, then the zero fills
+        const int order0 = dst_gpu ? 0 : (nid ^ 1), order1 = dst_gpu ? 1 : 2;
+        const uint32_t r0 = svc_emit_runs(from[order0], pf, slot, (uint32_t)order0, NULL, 0u, 0u, lane);
+        const uint32_t r1 = svc_emit_runs(from[order1], pf, slot, (uint32_t)order1, NULL, 0u, 0u, lane);
+        const uint32_t r2 = svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, NULL, 0u, 0u, lane);
+        const uint32_t run_cnt = r0 + r1 + r2;
+        uint32_t run_off = 0;
+        if (lane == 0 && run_cnt)
+            run_off = atomicAdd(&counters[0], run_cnt);
+        run_off = __shfl_sync(HW_FULL, run_off, 0);
+        svc_emit_runs(from[order0], pf, slot, (uint32_t)order0, runs, run_off, prm.run_cap, lane, dst_code);
+        svc_emit_runs(from[order1], pf, slot, (uint32_t)order1, runs, run_off + r0, prm.run_cap, lane, dst_code);
+        svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, runs, run_off + r0 + r1, prm.run_cap, lane, dst_code);
+
+        // make_resident_copy unmaps every processor from the pages that are not resident on the destination
+        // (:4919-4926); the only mapper in the table is this GPU
+        const uint32_t unmap = copy & pte0;
+        pte0 &= ~copy; pte1 &= ~copy; pte2 &= ~copy;
+
+        // _finish: the destination becomes resident (update_state + first touch), everybody else loses the pages
+        // of page_mask (break_read_duplication_in_region clears all of region & page_mask, not only what moved)
+        const uint32_t now = migrated | touch;
+        if (dst_gpu) {
+            gres |= now;
+            c0 &= ~pm;
+            c1 &= ~pm;
+            evicted &= ~migrated;                                         // block_make_resident_clear_evicted :4978-4988
+        }
+        else {
+            if (nid) { c1 |= now; c0 &= ~pm; }
+            else     { c0 |= now; c1 &= ~pm; }
+            gres &= ~pm;
+            if (rq.cause == UVMTIER_CAUSE_EVICTION)
+                evicted |= from[2];                                       // :5023-5037: the GPUs the pages came from
+        }
+
+        const uint32_t n0 = hw_weight(from[0]), n1 = hw_weight(from[1]), n2 = hw_weight(from[2]);
+        const uint32_t nt = hw_weight(touch), nu = hw_weight(unmap);
+        if (lane < 16) {
+            st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;
+            st.gpu_pte[0][w] = pte0; st.gpu_pte[1][w] = pte1; st.gpu_pte[2][w] = pte2;
+            if (st.gpu_evicted)
+                st.gpu_evicted[w] = evicted;
+            // result: 8 header words, then pages_migrated and pages_changed_residency
+            if (l < 8) {
+                uint32_t v = 0;
+                if (l == 0) v = slot;
+                if (l == 1) v = n0 | (n1 << 16);
+                if (l == 2) v = n2 | (nt << 16);
+                if (l == 3) v = run_off;
+                if (l == 4) v = run_cnt | (nu << 16);
+                res[l] = v;
+            }
+            res[8 + l] = migrated;                                        // make_resident.pages_migrated
+            res[24 + l] = now;                                            // pages_changed_residency (:5005-5008, :4614-4617)
+        }
+    }
+}
+
+} // namespace uvmtier_k

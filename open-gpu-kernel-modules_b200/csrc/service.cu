@@ -111,6 +111,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     bs.prefetch_info = state->prefetch_info;
     bs.logical_prot = state->logical_prot;
     bs.preferred_location = state->preferred_location;
+    bs.gpu_evicted = (uint32_t *)state->gpu_evicted;
 
     // The working space still holds the previous call's numbers.  The packed per-slot counters, the list cursor,
     // the two work lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset:
@@ -202,10 +203,11 @@ NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     memset(out, 0, sizeof(*out));
-    // one allocation: 6 mask arrays, prefetch_info, preferred_location, logical_prot
+    // one allocation: 6 mask arrays, prefetch_info, preferred_location, logical_prot, then (64-byte aligned) gpu_evicted
     const size_t mask_bytes = n * 64;
+    const size_t evicted_at = (6 * mask_bytes + n * 4 + n * 2 + n + 63) & ~(size_t)63;
     char *base = NULL;
-    UVMTIER_CUDA(cudaMalloc(&base, 6 * mask_bytes + n * 4 + n * 2 + n));
+    UVMTIER_CUDA(cudaMalloc(&base, evicted_at + mask_bytes));
     out->gpu_resident = (uvmtier_page_mask_t *)base;
     out->cpu_resident[0] = (uvmtier_page_mask_t *)(base + mask_bytes);
     out->cpu_resident[1] = (uvmtier_page_mask_t *)(base + 2 * mask_bytes);
@@ -215,7 +217,9 @@ NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_
     out->prefetch_info = (uvmtier_prefetch_info_t *)(base + 6 * mask_bytes);
     out->preferred_location = (uint16_t *)(base + 6 * mask_bytes + n * 4);
     out->logical_prot = (uint8_t *)(base + 6 * mask_bytes + n * 4 + n * 2);
+    out->gpu_evicted = (uvmtier_page_mask_t *)(base + evicted_at);
     UVMTIER_CUDA(cudaMemsetAsync(base, 0, 6 * mask_bytes, ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(base + evicted_at, 0, mask_bytes, ctx->stream));
     // prefetch_info = {UVMTIER_ID_INVALID (0x0101), 0}; preferred_location = 0x0101; logical_prot = 3
     UVMTIER_CUDA(cudaMemset2DAsync(out->prefetch_info, 4, 0x01, 2, n, ctx->stream));
     UVMTIER_CUDA(cudaMemset2DAsync((char *)out->prefetch_info + 2, 4, 0x00, 2, n, ctx->stream));

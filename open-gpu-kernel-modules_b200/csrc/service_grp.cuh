@@ -519,6 +519,15 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
         st_words<W>(st.gpu_pte[0] + wbase, p0);
         st_words<W>(st.gpu_pte[1] + wbase, p1);
         st_words<W>(st.gpu_pte[2] + wbase, p2);
+        if (st.gpu_evicted) {
+            // pages that an eviction had moved off the GPU and that came back (block_make_resident_clear_evicted,
+            // uvm_va_block.c:4978-4988): evicted pages are never GPU resident, so whatever is resident now came back
+            uint32_t ev[W];
+            ld_words<W>(st.gpu_evicted + wbase, ev);
+#pragma unroll
+            for (int w = 0; w < W; w++) ev[w] &= ~gres[w];
+            st_words<W>(st.gpu_evicted + wbase, ev);
+        }
         if (gl == 0)
             st.prefetch_info[slot] = pi;
     }

@@ -63,6 +63,7 @@ struct block_state_ptrs {
     uvmtier_prefetch_info_t *prefetch_info;
     uint8_t *logical_prot;
     uint16_t *preferred_location;
+    uint32_t *gpu_evicted;                     // may be NULL
 };
 
 // uvm_fault_access_type_to_prot, UVM/uvm_hal_types.h:522-537
@@ -86,7 +87,8 @@ __device__ __forceinline__ uint32_t svc_slot(const service_kparams &prm, uint32_
 // Counts (and, with runs != NULL, writes) the copy runs of mask `m`: maximal sequences of consecutive pages
 // with the same cause (UVM/uvm_va_block.c:4242-4335).  Warp-synchronous; word per lane, half-warp wide.
 __device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint32_t slot, uint32_t src,
-                                                  uvmtier_copy_run_t *runs, uint32_t at, uint32_t run_cap, int lane)
+                                                  uvmtier_copy_run_t *runs, uint32_t at, uint32_t run_cap, int lane,
+                                                  uint32_t dst = UVMTIER_RUN_DST_HBM)
 {
     const int l = lane & 15;
     uint32_t pm = __shfl_up_sync(HW_FULL, m >> 31, 1, 16);
@@ -127,7 +129,7 @@ __device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint3
             r.num_pages = (uint16_t)(end - first);
             r.src = (uint16_t)src;
             r.prefetch = (uint16_t)((pf >> s) & 1u);
-            r.pad = 0;
+            r.dst = (uint16_t)dst;
             runs[k] = r;
         }
         k++;
@@ -211,7 +213,7 @@ __device__ __forceinline__ svc_entry_eval svc_eval_entry(uint32_t acc, uint32_t 
 // (a duplicate inherits "fatal" / "invalid prefetch"), so every lane evaluates its entry from its neighbour's last
 // result and the warp repeats until nothing changes: as many rounds as the longest chain of duplicates, and the
 // result of the sequential scan.
-__global__ void __launch_bounds__(kSvcThreads)
+UVMTIER_KERNEL void __launch_bounds__(kSvcThreads)
 k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                  const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
                  block_state_ptrs st, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
@@ -388,6 +390,10 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
         if (lane < 16) {
             st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;
             st.gpu_pte[0][w] = pte0; st.gpu_pte[1][w] = pte1; st.gpu_pte[2][w] = pte2;
+            // pages that an eviction had moved off the GPU and that came back (block_make_resident_clear_evicted,
+            // uvm_va_block.c:4978-4988): evicted pages are never GPU resident, so whatever is resident now came back
+            if (st.gpu_evicted)
+                st.gpu_evicted[w] &= ~gres;
             if (l == 0)
                 st.prefetch_info[slot] = pi;
         }
@@ -397,7 +403,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
 // Runs whose va_block lies in no va_range: service_fault_batch_fatal_notify, one entry at a time
 // (:1656-1698, :2022-2031).  One thread per batch that has such runs; sequential like the reference because an
 // entry inherits the invalid-prefetch flag of the sorted entry before it.
-__global__ void __launch_bounds__(128)
+UVMTIER_KERNEL void __launch_bounds__(128)
 k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restrict__ ordered,
                    const uvmtier_fault_group_t *__restrict__ groups, uvmtier_fault_batch_t *__restrict__ batches,
                    const uvmtier_instance_ptr_entry_t *__restrict__ tbl, const uint32_t *__restrict__ batch_unmapped,

@@ -231,6 +231,34 @@ class Context:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt):
                 self.free(p)
 
+    # ---- (1c) make_resident ----
+    def make_resident(self, requests, page_masks, prefetch_masks, layout, dstate, run_cap=1 << 18, execute=False):
+        """uvmtier_make_resident_device on host arrays (requests: MAKE_RESIDENT_REQ_DT; masks: uint64 [n, 8] or
+        None).  Downloads results, copy runs, the run count and the state; execute=True also runs the copy runs
+        (uvmtier_copy_runs_device) before returning."""
+        from .blockstate import COPY_RUN_DT, MAKE_RESIDENT_RESULT_DT
+        n = len(requests)
+        d_req = self.to_device(requests)
+        d_pm = self.to_device(page_masks) if page_masks is not None else 0
+        d_pf = self.to_device(prefetch_masks) if prefetch_masks is not None else 0
+        d_res = self.alloc(max(n, 1) * 160); d_runs = self.alloc(max(run_cap, 1) * 8); d_cnt = self.alloc(8)
+        try:
+            _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(d_cnt), 0, ctypes.c_size_t(8)), "memset")
+            _check(lib().uvmtier_make_resident_device(self._h, ctypes.c_uint32(n), P(d_req), P(d_pm), P(d_pf), P(layout),
+                                                      ctypes.byref(dstate.ptrs), P(d_res), P(d_runs), ctypes.c_uint32(run_cap),
+                                                      P(d_cnt)), "uvmtier_make_resident_device")
+            if execute:
+                _check(lib().uvmtier_copy_runs_device(self._h, P(d_runs), P(d_cnt), ctypes.c_uint32(run_cap), ctypes.c_int(0)),
+                       "uvmtier_copy_runs_device")
+            self.synchronize()
+            cnt = self.from_device(d_cnt, 2, "<u4")
+            return dict(results=self.from_device(d_res, n, MAKE_RESIDENT_RESULT_DT),
+                        runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT), n_runs=int(cnt[0]), state=dstate.download())
+        finally:
+            for p in (d_req, d_pm, d_pf, d_res, d_runs, d_cnt):
+                if p:
+                    self.free(p)
+
     # ---- (3) tiers + page-list migration ----
     def tier_create(self, tier, nbytes, numa_node=-1):
         """uvmtier_tier_create -> TierInfo (device_ptr, host view as numpy uint8 for host tiers)."""
@@ -307,7 +335,8 @@ class DeviceBlockState:
         p = self.ptrs
         return (("gpu_resident", p.gpu_resident), ("cpu_resident0", p.cpu_resident[0]), ("cpu_resident1", p.cpu_resident[1]),
                 ("gpu_pte0", p.gpu_pte[0]), ("gpu_pte1", p.gpu_pte[1]), ("gpu_pte2", p.gpu_pte[2]),
-                ("prefetch_info", p.prefetch_info), ("logical_prot", p.logical_prot), ("preferred_location", p.preferred_location))
+                ("prefetch_info", p.prefetch_info), ("logical_prot", p.logical_prot), ("preferred_location", p.preferred_location),
+                ("gpu_evicted", p.gpu_evicted))
 
     def upload(self, host_state):
         assert host_state.n == self.n

@@ -13,14 +13,25 @@ SERVICE_GROUP_DT = np.dtype([("slot", "<u4"), ("region_first", "<u2"), ("region_
 COPY_RUN_DT = np.dtype([("slot", "<u4"), ("first_page", "<u2"), ("bits", "<u2")])   # bits: num_pages:10 src:3 prefetch:1
 PREFETCH_INFO_DT = np.dtype([("last_migration_proc_id", "<u2"), ("fault_migrations_to_last_proc", "<u2")])
 assert (VA_LAYOUT_DT.itemsize, SERVICE_GROUP_DT.itemsize, COPY_RUN_DT.itemsize) == (24, 96, 8)
+# uvmtier_make_resident_req_t / _result_t (include/uvmtier.h section 1c)
+MAKE_RESIDENT_REQ_DT = np.dtype([("slot", "<u4"), ("region_first", "<u2"), ("region_outer", "<u2"), ("dest_tier", "u1"),
+                                 ("cause", "u1"), ("flags", "<u2"), ("mask_row", "<u4")])
+MAKE_RESIDENT_RESULT_DT = np.dtype([("slot", "<u4"), ("migrated", "<u2", (3,)), ("first_touch", "<u2"), ("run_offset", "<u4"),
+                                    ("run_count", "<u2"), ("unmapped", "<u2"), ("reserved", "<u4", (3,)),
+                                    ("pages_migrated", "<u8", (8,)), ("pages_changed_residency", "<u8", (8,))])
+assert (MAKE_RESIDENT_REQ_DT.itemsize, MAKE_RESIDENT_RESULT_DT.itemsize) == (16, 160)
+MR_HAS_PAGE_MASK, MR_HAS_PREFETCH_MASK, MR_EVICT_GPU_PAGES = 1, 2, 4
+CAUSE_REPLAYABLE_FAULT, CAUSE_EVICTION, CAUSE_API_MIGRATE = 0, 4, 6
+TIER_HBM, TIER_DRAM, TIER_CXL = 0, 1, 2
 
 STATE_FIELDS = ("gpu_resident", "cpu_resident0", "cpu_resident1", "gpu_pte0", "gpu_pte1", "gpu_pte2", "prefetch_info",
-                "logical_prot", "preferred_location")
+                "logical_prot", "preferred_location", "gpu_evicted")
 
 
 class BlockStatePtrs(ctypes.Structure):
     _fields_ = [("gpu_resident", ctypes.c_void_p), ("cpu_resident", ctypes.c_void_p * 2), ("gpu_pte", ctypes.c_void_p * 3),
-                ("prefetch_info", ctypes.c_void_p), ("logical_prot", ctypes.c_void_p), ("preferred_location", ctypes.c_void_p)]
+                ("prefetch_info", ctypes.c_void_p), ("logical_prot", ctypes.c_void_p), ("preferred_location", ctypes.c_void_p),
+                ("gpu_evicted", ctypes.c_void_p)]
 
 
 class HostBlockState:
@@ -31,6 +42,7 @@ class HostBlockState:
         self.n = n_slots
         self.gpu_resident, self.cpu_resident0, self.cpu_resident1 = z(), z(), z()
         self.gpu_pte0, self.gpu_pte1, self.gpu_pte2 = z(), z(), z()
+        self.gpu_evicted = z()
         self.prefetch_info = np.zeros(n_slots, PREFETCH_INFO_DT)
         self.prefetch_info["last_migration_proc_id"] = 257
         self.logical_prot = np.full(n_slots, 3, "u1")
@@ -53,6 +65,7 @@ class HostBlockState:
         s.prefetch_info = self.prefetch_info.ctypes.data
         s.logical_prot = self.logical_prot.ctypes.data
         s.preferred_location = self.preferred_location.ctypes.data
+        s.gpu_evicted = self.gpu_evicted.ctypes.data
         return s
 
     def assert_equal(self, other, what=""):

@@ -1,0 +1,132 @@
+/*
+ * oracle_resident.c -- TEST INFRASTRUCTURE ONLY: CPU restatement of uvm_va_block_make_resident on the flat
+ * per-slot state table (UVM = kernel-open/nvidia-uvm, uvm_va_block.c):
+ *   M1  uvm_va_block_make_resident :5086-5114 = _copy :4877-4976 + _finish :5042-5084
+ *   M1b block_populate_pages :3099-3182 (destination pages exist for everything that is copied or first touched)
+ *   M2  block_copy_resident_pages :4660-4847, _mask :4460-4536, _from :4379-4452
+ *   M4  block_make_resident_update_state :4990-5040, block_copy_set_first_touch_residency :4581-4619,
+ *       break_read_duplication_in_region :4538-4579, block_make_resident_clear_evicted :4978-4988
+ *   M6  uvm_va_block_evict_chunks :12999-13130 (request flag 4: page_mask = gpu resident pages, cause EVICTION)
+ *
+ * Processors of the table: one GPU and the CPU with two NUMA nodes (0 = DRAM, 1 = CXL).  Harness policy as in
+ * oracle_service.c: no read duplication (residency is exclusive), CPU destination pages are allocated on the node
+ * the request names (block_populate_pages_cpu's first choice), the GPU can copy from the CPU directly (no staging).
+ *
+ * Pinning: PARITY UNPINNED.  The reference holds no vectors for make_resident masks and these functions
+ * have not been compiled against the shims; every step below cites the lines it restates.
+ */
+#include "oracle_common.h"
+#include "ref_api.h"
+
+uint32_t oracle_emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uint32_t slot, unsigned src, unsigned dst,
+                          ref_copy_run_t *runs, uint32_t at, uint32_t cap);
+
+static or_mask_t *node_mask(or_mask_t *cpu, int nid) { return &cpu[nid]; }
+
+/* Processes the requests in order.  Returns the number of copy runs needed (only run_cap are written). */
+uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t *reqs, const uint64_t *page_masks,
+                              const uint64_t *prefetch_masks, uint32_t n_slots, const ref_block_state_t *st,
+                              ref_make_resident_result_t *results, ref_copy_run_t *runs, uint32_t run_cap)
+{
+    uint32_t q, nrun = 0;
+    for (q = 0; q < n_requests; q++) {
+        const ref_make_resident_req_t *rq = &reqs[q];
+        ref_make_resident_result_t *res = &results[q];
+        const uint32_t slot = rq->slot;
+        const bool dst_gpu = rq->dest_tier == 0;
+        const int nid = rq->dest_tier == 2 ? 1 : 0;                  /* make_resident.dest_nid */
+        or_mask_t gpu, cpu[2], pte[3], evicted, pm, pf, copy, from[3], migrated, touch, now, unmap, *dst_res;
+        int i, order[2];
+        uint32_t k = 0;
+
+        memset(res, 0, sizeof(*res));
+        if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > OR_PAGES || rq->dest_tier > 2) {
+            res->slot = 0xFFFFFFFFu;
+            continue;
+        }
+        res->slot = slot;
+        res->run_offset = nrun;
+        or_load(&gpu, st->gpu_resident + 8 * (size_t)slot);
+        or_load(&cpu[0], st->cpu_resident[0] + 8 * (size_t)slot);
+        or_load(&cpu[1], st->cpu_resident[1] + 8 * (size_t)slot);
+        for (i = 0; i < 3; i++) or_load(&pte[i], st->gpu_pte[i] + 8 * (size_t)slot);
+        or_zero(&evicted);
+        if (st->gpu_evicted) or_load(&evicted, st->gpu_evicted + 8 * (size_t)slot);
+
+        /* page_mask clipped to the region (uvm_page_mask_region_clear_outside); NULL = whole region */
+        or_zero(&pm);
+        or_fill_range(&pm, rq->region_first, rq->region_outer);
+        if (rq->flags & 1) {
+            or_mask_t m;
+            or_load(&m, page_masks + 8 * (size_t)rq->mask_row);
+            or_and(&pm, &pm, &m);
+        }
+        if (rq->flags & 4)
+            or_and(&pm, &pm, &gpu);                                   /* pages_to_evict :13078 */
+        or_zero(&pf);
+        if (rq->flags & 2)
+            or_load(&pf, prefetch_masks + 8 * (size_t)rq->mask_row);
+
+        /* block_copy_resident_pages: copy_page_mask = page_mask & ~resident(dst, dest_nid)  :4687-4692 */
+        dst_res = dst_gpu ? &gpu : node_mask(cpu, nid);
+        or_andnot(&copy, &pm, dst_res);
+        for (i = 0; i < 3; i++) or_zero(&from[i]);
+        if (dst_gpu) {
+            /* sources with direct copy access: the CPU, node after node (:4707-4712, :4486-4497) */
+            or_mask_t rest = copy;
+            or_and(&from[0], &rest, &cpu[0]);
+            or_andnot(&rest, &rest, &from[0]);
+            or_and(&from[1], &rest, &cpu[1]);
+            order[0] = 0; order[1] = 1;
+        }
+        else {
+            /* destination CPU: everything resident elsewhere is a source, closest first -- the CPU itself (the
+             * other node; the destination node holds none of copy_page_mask), then the GPU  (:4754-4785) */
+            or_mask_t rest = copy;
+            or_and(&from[nid ^ 1], &rest, &cpu[nid ^ 1]);
+            or_andnot(&rest, &rest, &from[nid ^ 1]);
+            or_and(&from[2], &rest, &gpu);
+            order[0] = nid ^ 1; order[1] = 2;
+        }
+        or_or(&migrated, &from[0], &from[1]);
+        or_or(&migrated, &migrated, &from[2]);
+        or_andnot(&touch, &copy, &migrated);                          /* resident nowhere: populated + zeroed */
+        for (i = 0; i < 2; i++)
+            k += oracle_emit_runs(&from[order[i]], &pf, slot, (unsigned)order[i], rq->dest_tier, runs, nrun + k, run_cap);
+        k += oracle_emit_runs(&touch, &pf, slot, 7, rq->dest_tier, runs, nrun + k, run_cap);
+        res->run_count = (uint16_t)k;
+        nrun += k;
+        for (i = 0; i < 3; i++) res->migrated[i] = (uint16_t)or_weight(&from[i]);
+        res->first_touch = (uint16_t)or_weight(&touch);
+
+        /* make_resident_copy :4919-4926: unmap every mapped processor from the pages not resident on the destination */
+        or_and(&unmap, &copy, &pte[0]);
+        res->unmapped = (uint16_t)or_weight(&unmap);
+        for (i = 0; i < 3; i++) or_andnot(&pte[i], &pte[i], &copy);
+
+        /* _finish: update_state (dst |= migrated; evicted), first touch (dst |= touch), then every other
+         * residency loses region & page_mask  (:5061-5074) */
+        or_or(&now, &migrated, &touch);
+        or_or(dst_res, dst_res, &now);
+        if (dst_gpu) {
+            or_andnot(&cpu[0], &cpu[0], &pm);
+            or_andnot(&cpu[1], &cpu[1], &pm);
+            or_andnot(&evicted, &evicted, &migrated);                 /* :5038-5039 */
+        }
+        else {
+            or_andnot(&cpu[nid ^ 1], &cpu[nid ^ 1], &pm);             /* uvm_va_block_cpu_clear_resident_all_chunks :672-700 */
+            or_andnot(&gpu, &gpu, &pm);
+            if (rq->cause == 4)
+                or_or(&evicted, &evicted, &from[2]);                  /* :5023-5037 */
+        }
+        or_store(res->pages_migrated, &migrated);
+        or_store(res->pages_changed_residency, &now);
+
+        or_store(st->gpu_resident + 8 * (size_t)slot, &gpu);
+        or_store(st->cpu_resident[0] + 8 * (size_t)slot, &cpu[0]);
+        or_store(st->cpu_resident[1] + 8 * (size_t)slot, &cpu[1]);
+        for (i = 0; i < 3; i++) or_store(st->gpu_pte[i] + 8 * (size_t)slot, &pte[i]);
+        if (st->gpu_evicted) or_store(st->gpu_evicted + 8 * (size_t)slot, &evicted);
+    }
+    return nrun;
+}

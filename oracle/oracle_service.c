@@ -13,9 +13,9 @@
  * to `return processor_id`, uvm_va_block.c:11560-11712, when the page is not resident on it); CPU memory
  * has two NUMA nodes (0 = DRAM, 1 = CXL); both tiers and HBM back a va_block contiguously.
  *
- * Pinning: no known-answer vectors exist in the reference for this stage.  The batch-level loop and the
- * permission logic are additionally pinned against the reference's own code where it compiles
- * (oracle/_ref/libref_service.so, see ref_service_glue.c); the prefetch leg inside is the KAT-pinned one.
+ * Pinning: PARITY UNPINNED for this stage beyond its prefetch leg (which is the KAT-pinned oracle_prefetch.c).
+ * No known-answer vectors exist in the reference for it, and service_fault_batch_block_locked with its callees
+ * in uvm_va_block.c (13 k lines) has not been compiled against the shims.
  * Batches are applied in trace order, exactly like uvm_parent_gpu_service_replayable_faults (:2906-2960).
  */
 #include "oracle_common.h"
@@ -48,7 +48,7 @@ static void mask_ptr_store(uint64_t *base, uint32_t slot, const or_mask_t *m) { 
 
 /* Emits the copy runs of `pages` from source `src`: consecutive pages with the same cause form one run
  * (block_copy_resident_pages_between, uvm_va_block.c:4143-4335, both sides block-contiguous). */
-static uint32_t emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uint32_t slot, unsigned src,
+uint32_t oracle_emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uint32_t slot, unsigned src, unsigned dst,
                           ref_copy_run_t *runs, uint32_t at, uint32_t cap)
 {
     unsigned p = 0;
@@ -60,7 +60,7 @@ static uint32_t emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uin
         for (q = p + 1; q < OR_PAGES && or_test(pages, q) && (unsigned)or_test(prefetch, q) == cause; q++) {}
         if (at + n < cap) {
             ref_copy_run_t *r = &runs[at + n];
-            r->slot = slot; r->first_page = (uint16_t)p; r->num_pages = q - p; r->src = src; r->prefetch = cause; r->pad = 0;
+            r->slot = slot; r->first_page = (uint16_t)p; r->num_pages = q - p; r->src = src; r->prefetch = cause; r->dst = dst;
         }
         n++;
         p = q;
@@ -263,9 +263,9 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                 rec->first_touch = (uint16_t)or_weight(&touch);
                 {
                     uint32_t k = 0;
-                    k += emit_runs(&from0, &pf_mask, slot, 0, runs, nrun + k, run_cap);
-                    k += emit_runs(&from1, &pf_mask, slot, 1, runs, nrun + k, run_cap);
-                    k += emit_runs(&touch, &pf_mask, slot, 7, runs, nrun + k, run_cap);
+                    k += oracle_emit_runs(&from0, &pf_mask, slot, 0, 0, runs, nrun + k, run_cap);
+                    k += oracle_emit_runs(&from1, &pf_mask, slot, 1, 0, runs, nrun + k, run_cap);
+                    k += oracle_emit_runs(&touch, &pf_mask, slot, 7, 0, runs, nrun + k, run_cap);
                     rec->run_count = (uint16_t)k;
                     nrun += k;
                 }
@@ -276,6 +276,14 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                 mask_ptr_store(st->gpu_resident, slot, &gpu_res);
                 mask_ptr_store(st->cpu_resident[0], slot, &cpu0);
                 mask_ptr_store(st->cpu_resident[1], slot, &cpu1);
+                if (st->gpu_evicted) {
+                    /* block_make_resident_update_state :5038-5039 -> block_make_resident_clear_evicted :4978-4988 */
+                    or_mask_t evicted, migrated;
+                    or_or(&migrated, &from0, &from1);
+                    mask_ptr_load(&evicted, st->gpu_evicted, slot);
+                    or_andnot(&evicted, &evicted, &migrated);
+                    mask_ptr_store(st->gpu_evicted, slot, &evicted);
+                }
 
                 /* service_finish :12063-12302: map the faulting GPU.  compute_new_permission (:11019-11066): the
                  * page is now resident on the faulting GPU, which has native atomics on its own memory, and no

@@ -133,7 +133,29 @@ typedef struct {
     ref_prefetch_info_t *prefetch_info;
     uint8_t *logical_prot;          /* compute_logical_prot(): 0 NONE, 1 READ_ONLY, 3 READ_WRITE_ATOMIC */
     uint16_t *preferred_location;   /* policy->preferred_location, 257 = none */
+    uint64_t *gpu_evicted;          /* gpu_state->evicted (may be NULL) */
 } ref_block_state_t;
+
+/* uvm_va_block_make_resident request / result, same layout as uvmtier_make_resident_req_t / _result_t */
+typedef struct {
+    uint32_t slot;
+    uint16_t region_first, region_outer;
+    uint8_t  dest_tier;             /* 0 HBM (this GPU), 1 CPU node 0 (DRAM), 2 CPU node 1 (CXL) */
+    uint8_t  cause;                 /* uvm_make_resident_cause_t; 4 = EVICTION */
+    uint16_t flags;                 /* 1 page mask given, 2 prefetch mask given, 4 page_mask = gpu resident pages */
+    uint32_t mask_row;
+} ref_make_resident_req_t;          /* 16 bytes */
+typedef struct {
+    uint32_t slot;
+    uint16_t migrated[3];
+    uint16_t first_touch;
+    uint32_t run_offset;
+    uint16_t run_count;
+    uint16_t unmapped;
+    uint32_t reserved[3];
+    uint64_t pages_migrated[8];
+    uint64_t pages_changed_residency[8];
+} ref_make_resident_result_t;       /* 160 bytes */
 
 #define REF_SF_SERVICED         0x0001
 #define REF_SF_DUPLICATE        0x0002
@@ -166,9 +188,9 @@ typedef struct {
     uint32_t slot;
     uint16_t first_page;
     uint16_t num_pages : 10;
-    uint16_t src : 3;               /* 0 CPU node 0, 1 CPU node 1, 7 = zero-fill (first touch) */
+    uint16_t src : 3;               /* 0 CPU node 0, 1 CPU node 1, 2 this GPU, 7 = zero-fill (first touch) */
     uint16_t prefetch : 1;          /* run cause is PREFETCH (runs also split where the cause changes) */
-    uint16_t pad : 2;
+    uint16_t dst : 2;               /* 0 this GPU, 1 CPU node 0, 2 CPU node 1 */
 } ref_copy_run_t;                   /* 8 bytes */
 
 #endif

@@ -1,0 +1,94 @@
+"""Helpers for the make_resident tests: request builders, runners (oracle / SIMT emulator), comparison."""
+import ctypes
+
+import numpy as np
+
+from uvmtier_testlib import P, bool_from_masks, masks_from_bool
+
+from uvmtier.blockstate import (CAUSE_API_MIGRATE, CAUSE_EVICTION, CAUSE_REPLAYABLE_FAULT, COPY_RUN_DT,  # noqa: F401
+                                MAKE_RESIDENT_REQ_DT, MAKE_RESIDENT_RESULT_DT, MR_EVICT_GPU_PAGES, MR_HAS_PAGE_MASK,
+                                MR_HAS_PREFETCH_MASK, TIER_CXL, TIER_DRAM, TIER_HBM, HostBlockState)
+
+RESULT_FIELDS = ("slot", "migrated", "first_touch", "run_count", "unmapped", "pages_migrated", "pages_changed_residency")
+
+
+def random_requests(n_slots, seed, frac=0.6, evict_frac=0.25, bad=0):
+    """At most one request per slot (a va_block is locked during make_resident), random destination, region,
+    optional page / prefetch masks; a share of them are evictions of whatever the GPU holds."""
+    rng = np.random.default_rng(seed)
+    slots = np.nonzero(rng.random(n_slots) < frac)[0]
+    rng.shuffle(slots)
+    n = len(slots)
+    rq = np.zeros(n + bad, MAKE_RESIDENT_REQ_DT)
+    rq["slot"][:n] = slots
+    a = rng.integers(0, 512, n)
+    b = rng.integers(0, 513, n)
+    whole = rng.random(n) < 0.3
+    rq["region_first"][:n] = np.where(whole, 0, np.minimum(a, b))
+    rq["region_outer"][:n] = np.where(whole, 512, np.maximum(a, b))
+    evict = rng.random(n) < evict_frac
+    rq["dest_tier"][:n] = np.where(evict, rng.choice([TIER_DRAM, TIER_CXL], n), rng.choice([TIER_HBM, TIER_DRAM, TIER_CXL], n))
+    rq["cause"][:n] = np.where(evict, CAUSE_EVICTION, rng.choice([CAUSE_API_MIGRATE, CAUSE_REPLAYABLE_FAULT], n))
+    has_pm = ~evict & (rng.random(n) < 0.5)
+    has_pf = ~evict & (rq["cause"][:n] == CAUSE_REPLAYABLE_FAULT) & (rng.random(n) < 0.6)
+    rq["flags"][:n] = np.where(evict, MR_EVICT_GPU_PAGES, has_pm * MR_HAS_PAGE_MASK + has_pf * MR_HAS_PREFETCH_MASK)
+    rq["mask_row"][:n] = np.arange(n)
+    page_masks = masks_from_bool(rng.random((n, 512)) < rng.random((n, 1)))
+    prefetch_masks = masks_from_bool(rng.random((n, 512)) < 0.5)
+    if bad:                                           # rejected requests: slot out of range, inverted region, bad tier
+        rq["slot"][n:] = [n_slots + 3, 0, 0][:bad]
+        rq["region_first"][n:] = [0, 9, 0][:bad]
+        rq["region_outer"][n:] = [4, 3, 4][:bad]
+        rq["dest_tier"][n:] = [0, 0, 5][:bad]
+    return rq, page_masks, prefetch_masks
+
+
+def run_oracle(orc, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
+    st = state.copy()
+    ptrs = st.ptrs()
+    res = np.zeros(len(rq), MAKE_RESIDENT_RESULT_DT)
+    runs = np.zeros(run_cap, COPY_RUN_DT)
+    fn = orc.oracle_make_resident
+    fn.restype = ctypes.c_uint32
+    n_runs = fn(ctypes.c_uint32(len(rq)), P(rq), P(page_masks), P(prefetch_masks), ctypes.c_uint32(st.n), ctypes.byref(ptrs),
+                P(res), P(runs), ctypes.c_uint32(run_cap))
+    return dict(results=res, runs=runs, n_runs=int(n_runs), state=st)
+
+
+def run_simt(sim, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
+    st = state.copy()
+    ptrs = st.ptrs()
+    res = np.zeros(len(rq), MAKE_RESIDENT_RESULT_DT)
+    runs = np.zeros(run_cap, COPY_RUN_DT)
+    counters = np.zeros(2, "<u4")
+    sim.simt_make_resident(ctypes.c_uint32(len(rq)), P(rq), P(page_masks), P(prefetch_masks), ctypes.c_uint32(st.n),
+                           ctypes.byref(ptrs), P(res), P(runs), ctypes.c_uint32(run_cap), P(counters))
+    return dict(results=res, runs=runs, n_runs=int(counters[0]), state=st)
+
+
+def assert_equal(want, got, what=""):
+    want["state"].assert_equal(got["state"], what)
+    a, b = want["results"], got["results"]
+    for f in RESULT_FIELDS:
+        assert np.array_equal(a[f], b[f]), "%s result.%s" % (what, f)
+    assert want["n_runs"] == got["n_runs"], "%s n_runs %d vs %d" % (what, want["n_runs"], got["n_runs"])
+    has = np.nonzero(a["run_count"] > 0)[0]
+    if len(has):                                      # runs per request (their place in the array is free)
+        within = np.concatenate([np.arange(c) for c in a["run_count"][has]])
+        ia = np.repeat(a["run_offset"][has].astype(np.int64), a["run_count"][has]) + within
+        ib = np.repeat(b["run_offset"][has].astype(np.int64), a["run_count"][has]) + within
+        assert np.array_equal(want["runs"][ia], got["runs"][ib]), what + " copy runs"
+
+
+def check_invariants(before, res):
+    """Size-independent properties of make_resident."""
+    st = res["state"]
+    g, c0, c1 = (bool_from_masks(m) for m in (st.gpu_resident, st.cpu_resident0, st.cpu_resident1))
+    assert not (g & c0).any() and not (g & c1).any() and not (c0 & c1).any(), "a page is resident in two places"
+    gb, c0b, c1b = (bool_from_masks(m) for m in (before.gpu_resident, before.cpu_resident0, before.cpu_resident1))
+    # nothing is lost: a page resident somewhere before is resident somewhere after
+    assert not ((gb | c0b | c1b) & ~(g | c0 | c1)).any(), "a resident page vanished"
+    p0 = bool_from_masks(st.gpu_pte0)
+    assert not (p0 & ~g).any(), "the GPU maps a page that is not resident on it"
+    ev = bool_from_masks(st.gpu_evicted)
+    assert not (ev & g).any(), "an evicted page is GPU resident"

@@ -45,6 +45,13 @@ def run():
         ds.upload(st0)
         svc = ctx.service_fault_batches(r, layout, ds)
         S.assert_service_equal(S.run_service_oracle(orc, k1, gp, tbl, layout, st0), svc, 256, "smoke service")
+
+        # (1c) make_resident as a call of its own: migrations and evictions on the state the faults left
+        import residentlib as R
+        st1 = svc["state"]
+        rq, pm, pf = R.random_requests(st1.n, 6)
+        mr = ctx.make_resident(rq, pm, pf, layout, ds)
+        R.assert_equal(R.run_oracle(orc, rq, pm, pf, st1), mr, "smoke make_resident")
         ds.free()
 
         # (3) migration: 4 KB pages DRAM -> HBM in random order, byte exact

@@ -1,0 +1,110 @@
+"""GPU tests of uvmtier_make_resident_device (section 1c): the masks, counts and copy runs are bit-exact against the
+CPU restatement, and executing the runs moves the right bytes between HBM, host DRAM and the CXL node in every
+direction (promotion, eviction, DRAM <-> CXL demotion / promotion, first-touch zero fill)."""
+import numpy as np
+import pytest
+
+import residentlib as R
+import servicelib as S
+import uvmtier
+import uvmtier_testlib as T
+from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, tracegen as TG
+
+pytestmark = pytest.mark.gpu
+
+
+def _state(n_slots, seed):
+    st = S.random_state(n_slots, seed)
+    rng = np.random.default_rng(seed + 100)
+    cpu = T.bool_from_masks(st.cpu_resident0) | T.bool_from_masks(st.cpu_resident1)
+    st.gpu_evicted = T.masks_from_bool(cpu & (rng.random(cpu.shape) < 0.3))
+    return st
+
+
+@pytest.mark.parametrize("seed,n_slots", [(1, 96), (5, 4096)])
+def test_make_resident_matches_oracle(seed, n_slots):
+    st0 = _state(n_slots, seed)
+    rq, pm, pf = R.random_requests(n_slots, seed, bad=3)
+    want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0, run_cap=1 << 20)
+    lay = dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1)
+    layout = S.make_layout(lay)
+    with uvmtier.Context(0) as c:
+        ds = c.block_state_alloc(layout)
+        ds.upload(st0)
+        got = c.make_resident(rq, pm, pf, layout, ds, run_cap=1 << 20)
+        ds.free()
+    R.assert_equal(want, got, "seed %d" % seed)
+    R.check_invariants(st0, got)
+
+
+def test_moves_between_all_tiers_are_byte_exact():
+    """Three waves on 48 va_blocks with real data behind the masks: everything the requests name goes to the GPU,
+    then half of the blocks are evicted to the CXL node and the other half to DRAM, then the CXL half is promoted to
+    DRAM (CPU to CPU).  After each wave every resident page holds the bytes it started with (or zeros if it was
+    first touched), wherever it lives now."""
+    n = 48
+    rng = np.random.default_rng(3)
+    st0 = S.random_state(n, 9, populated=0.8)
+    with uvmtier.Context(0) as c:
+        info = {t: c.tier_create(t, n << 21) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
+        views = {t: info[t].host_view() for t in (TIER_DRAM, TIER_CXL)}
+        # the truth: one 4 KB pattern per page, placed in the arena of the tier that holds the page
+        truth = TG.rng_stream(77, n * 512 * 1024).view(np.uint8).reshape(n * 512, 4096)
+        where = {TIER_HBM: T.bool_from_masks(st0.gpu_resident).ravel(), TIER_DRAM: T.bool_from_masks(st0.cpu_resident0).ravel(),
+                 TIER_CXL: T.bool_from_masks(st0.cpu_resident1).ravel()}
+        hbm0 = np.full((n * 512, 4096), 0xEE, np.uint8)
+        hbm0[where[TIER_HBM]] = truth[where[TIER_HBM]]
+        uvmtier._check(uvmtier.lib().uvmtier_memcpy_h2d(c.handle, uvmtier.P(info[TIER_HBM].device_ptr), uvmtier.P(hbm0),
+                                                        __import__("ctypes").c_size_t(hbm0.nbytes)), "h2d")
+        for t in (TIER_DRAM, TIER_CXL):
+            v = views[t].reshape(n * 512, 4096)
+            v[:] = 0xEE
+            v[where[t]] = truth[where[t]]
+        resident0 = where[TIER_HBM] | where[TIER_DRAM] | where[TIER_CXL]
+
+        lay = dict(va_base=TG.VA_BASE, blocks_per_space=n, n_spaces=1)
+        layout = S.make_layout(lay)
+        ds = c.block_state_alloc(layout)
+        ds.upload(st0)
+
+        def check(state, touched, what):
+            hbm = c.from_device(info[TIER_HBM].device_ptr, n << 21, np.uint8).reshape(n * 512, 4096)
+            bufs = {TIER_HBM: hbm, TIER_DRAM: views[TIER_DRAM].reshape(n * 512, 4096), TIER_CXL: views[TIER_CXL].reshape(n * 512, 4096)}
+            masks = {TIER_HBM: T.bool_from_masks(state.gpu_resident).ravel(), TIER_DRAM: T.bool_from_masks(state.cpu_resident0).ravel(),
+                     TIER_CXL: T.bool_from_masks(state.cpu_resident1).ravel()}
+            for t, m in masks.items():
+                keep = m & resident0
+                assert np.array_equal(bufs[t][keep], truth[keep]), "%s: bytes of pages resident on tier %d" % (what, t)
+                assert not bufs[t][m & touched].any(), "%s: first-touched pages on tier %d are zero" % (what, t)
+            return masks
+
+        def all_blocks(dest, cause, flags, slots):
+            rq = np.zeros(len(slots), R.MAKE_RESIDENT_REQ_DT)
+            rq["slot"] = slots; rq["region_outer"] = 512; rq["dest_tier"] = dest; rq["cause"] = cause; rq["flags"] = flags
+            return rq
+
+        # wave 1: promotion of a random half of every block's pages to the GPU (page masks)
+        pm = T.masks_from_bool(rng.random((n, 512)) < 0.5)
+        rq = all_blocks(TIER_HBM, R.CAUSE_API_MIGRATE, R.MR_HAS_PAGE_MASK, np.arange(n))
+        rq["mask_row"] = np.arange(n)
+        a = c.make_resident(rq, pm, None, layout, ds, execute=True)
+        touched = T.bool_from_masks(pm).ravel() & ~resident0
+        m1 = check(a["state"], touched, "promotion")
+        assert m1[TIER_HBM][T.bool_from_masks(pm).ravel()].all() and int(a["results"]["first_touch"].sum()) == int(touched.sum())
+
+        # wave 2: eviction of whatever the GPU holds: even blocks to the CXL node, odd blocks to DRAM
+        rq = np.concatenate([all_blocks(TIER_CXL, R.CAUSE_EVICTION, R.MR_EVICT_GPU_PAGES, np.arange(0, n, 2)),
+                             all_blocks(TIER_DRAM, R.CAUSE_EVICTION, R.MR_EVICT_GPU_PAGES, np.arange(1, n, 2))])
+        b = c.make_resident(rq, None, None, layout, ds, execute=True)
+        m2 = check(b["state"], touched, "eviction")
+        assert not m2[TIER_HBM].any() and np.array_equal(T.bool_from_masks(b["state"].gpu_evicted).ravel(), m1[TIER_HBM])
+        assert int(b["results"]["migrated"][:, 2].sum()) == int(m1[TIER_HBM].sum())
+
+        # wave 3: the even blocks' CXL pages move to DRAM (CPU to CPU through the GPU's copy kernel)
+        rq = all_blocks(TIER_DRAM, R.CAUSE_API_MIGRATE, 0, np.arange(0, n, 2))
+        d = c.make_resident(rq, None, None, layout, ds, execute=True)
+        m3 = check(d["state"], touched | ~(resident0 | touched), "CXL -> DRAM")
+        even = np.repeat(np.arange(n) % 2 == 0, 512)
+        assert not m3[TIER_CXL][even].any() and m3[TIER_DRAM][even].all()         # whole-block region: the rest is first touch
+        assert int(d["results"]["migrated"][:, 1].sum()) == int(m2[TIER_CXL][even].sum())
+        ds.free()

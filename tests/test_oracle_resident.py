@@ -1,0 +1,103 @@
+"""CPU tests of uvm_va_block_make_resident on the state table (section 1c of include/uvmtier.h): the product's
+kernel under the SIMT emulator vs the CPU restatement, directed cases for the reference's rules (source order,
+first touch, eviction marks, unmapping, page_mask / region clipping), and a promotion / eviction round trip."""
+import numpy as np
+import pytest
+
+import residentlib as R
+import servicelib as S
+import uvmtier_testlib as T
+
+
+def _state(n_slots, seed):
+    st = S.random_state(n_slots, seed)
+    rng = np.random.default_rng(seed + 100)
+    # some pages carry an eviction mark: always pages that live on the CPU now
+    cpu = T.bool_from_masks(st.cpu_resident0) | T.bool_from_masks(st.cpu_resident1)
+    st.gpu_evicted = T.masks_from_bool(cpu & (rng.random(cpu.shape) < 0.3))
+    return st
+
+
+@pytest.mark.parametrize("seed", [1, 2, 3])
+def test_simt_make_resident_matches_oracle(seed):
+    n_slots = 96
+    st0 = _state(n_slots, seed)
+    rq, pm, pf = R.random_requests(n_slots, seed, bad=3)
+    want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0)
+    got = R.run_simt(T.load_simt(), rq, pm, pf, st0)
+    R.assert_equal(want, got, "seed %d" % seed)
+    R.check_invariants(st0, got)
+    assert (want["results"]["slot"][-3:] == 0xFFFFFFFF).all()          # the three malformed requests are rejected
+    assert int(want["results"]["migrated"].sum()) > 1000 and int(want["results"]["first_touch"].sum()) > 100
+
+
+def _one(st, **kw):
+    rq = np.zeros(1, R.MAKE_RESIDENT_REQ_DT)
+    for k, v in kw.items():
+        rq[k] = v
+    return rq
+
+
+def _bits(mask_row):
+    return set(np.nonzero(T.bool_from_masks(mask_row.reshape(1, 8))[0])[0].tolist())
+
+
+def test_directed_rules():
+    orc = T.load_oracle()
+    st = R.HostBlockState(2)
+    setb = lambda m, s, pages: [m.__setitem__((s, p // 64), m[s, p // 64] | np.uint64(1 << (p % 64))) for p in pages]
+    setb(st.cpu_resident0, 0, [1, 2, 3]); setb(st.cpu_resident1, 0, [4, 5, 9]); setb(st.gpu_resident, 0, [6, 7, 8])
+    for m in (st.gpu_pte0, st.gpu_pte1):
+        setb(m, 0, [6, 7])
+    # (a) to the GPU, region [0, 12): node 0 then node 1 as sources, pages 0, 10, 11 are first touch
+    r = R.run_oracle(orc, _one(st, slot=0, region_first=0, region_outer=12, dest_tier=R.TIER_HBM, cause=R.CAUSE_API_MIGRATE), None, None, st)
+    res = r["results"][0]
+    assert list(res["migrated"]) == [3, 3, 0] and res["first_touch"] == 3 and res["unmapped"] == 0
+    runs = r["runs"][:res["run_count"]]
+    assert [(int(x["first_page"]), int(x["bits"]) & 1023, (int(x["bits"]) >> 10) & 7, int(x["bits"]) >> 14) for x in runs] == \
+        [(1, 3, 0, 0), (4, 2, 1, 0), (9, 1, 1, 0), (0, 1, 7, 0), (10, 2, 7, 0)]
+    assert _bits(r["state"].gpu_resident[0]) == set(range(12)) and not r["state"].cpu_resident0[0].any()
+    # (b) eviction to the CXL node: only what the GPU holds moves, mappings go, the pages are marked evicted
+    r = R.run_oracle(orc, _one(st, slot=0, region_first=0, region_outer=512, dest_tier=R.TIER_CXL, cause=R.CAUSE_EVICTION,
+                               flags=R.MR_EVICT_GPU_PAGES), None, None, st)
+    res = r["results"][0]
+    assert list(res["migrated"]) == [0, 0, 3] and res["first_touch"] == 0 and res["unmapped"] == 2
+    assert _bits(r["state"].cpu_resident1[0]) == {4, 5, 9, 6, 7, 8} and _bits(r["state"].cpu_resident0[0]) == {1, 2, 3}
+    assert _bits(r["state"].gpu_evicted[0]) == {6, 7, 8} and not r["state"].gpu_pte0[0].any()
+    x = r["runs"][0]
+    assert (int(x["first_page"]), int(x["bits"]) & 1023, (int(x["bits"]) >> 10) & 7, int(x["bits"]) >> 14) == (6, 3, 2, 2)
+    # (c) DRAM -> CXL demotion with a page mask: CPU to CPU copy, the other node loses every page of the mask
+    pm = T.masks_from_bool(np.isin(np.arange(512), [2, 3, 4, 7, 300]).reshape(1, 512))
+    r = R.run_oracle(orc, _one(st, slot=0, region_first=0, region_outer=256, dest_tier=R.TIER_CXL, cause=R.CAUSE_API_MIGRATE,
+                               flags=R.MR_HAS_PAGE_MASK), pm, None, st)
+    res = r["results"][0]
+    assert list(res["migrated"]) == [2, 0, 1] and res["first_touch"] == 0          # 2, 3 from DRAM, 7 from the GPU; 4 is there
+    assert _bits(r["state"].cpu_resident0[0]) == {1} and _bits(r["state"].gpu_resident[0]) == {6, 8}
+    assert not r["state"].gpu_evicted[0].any()                                     # not an eviction
+    # (d) coming back to the GPU clears the eviction mark, and a prefetch mask splits the runs by cause
+    st2 = st.copy()
+    setb(st2.gpu_evicted, 0, [1, 2, 3, 4])
+    pf = T.masks_from_bool(np.isin(np.arange(512), [2]).reshape(1, 512))
+    r = R.run_oracle(orc, _one(st2, slot=0, region_first=1, region_outer=4, dest_tier=R.TIER_HBM, cause=R.CAUSE_REPLAYABLE_FAULT,
+                               flags=R.MR_HAS_PREFETCH_MASK), None, pf, st2)
+    assert _bits(r["state"].gpu_evicted[0]) == {4}
+    runs = r["runs"][:r["results"]["run_count"][0]]
+    assert [(int(x["first_page"]), int(x["bits"]) & 1023, (int(x["bits"]) >> 13) & 1) for x in runs] == [(1, 1, 0), (2, 1, 1), (3, 1, 0)]
+
+
+def test_promote_evict_round_trip_restores_residency_on_one_tier():
+    """Everything to the GPU, then everything evicted to DRAM: every page that was resident anywhere (or was touched)
+    ends on node 0, the GPU is empty, and the eviction marks are exactly the pages that left the GPU."""
+    n_slots = 64
+    st0 = _state(n_slots, 7)
+    sim = T.load_simt()
+    up = np.zeros(n_slots, R.MAKE_RESIDENT_REQ_DT)
+    up["slot"] = np.arange(n_slots); up["region_outer"] = 512; up["dest_tier"] = R.TIER_HBM; up["cause"] = R.CAUSE_API_MIGRATE
+    a = R.run_simt(sim, up, None, None, st0)
+    assert (T.bool_from_masks(a["state"].gpu_resident)).all() and not a["state"].gpu_evicted.any()
+    down = up.copy()
+    down["dest_tier"] = R.TIER_DRAM; down["cause"] = R.CAUSE_EVICTION; down["flags"] = R.MR_EVICT_GPU_PAGES
+    b = R.run_simt(sim, down, None, None, a["state"])
+    assert T.bool_from_masks(b["state"].cpu_resident0).all() and not b["state"].gpu_resident.any()
+    assert T.bool_from_masks(b["state"].gpu_evicted).all() and not b["state"].gpu_pte0.any()
+    assert int(b["results"]["migrated"][:, 2].sum()) == n_slots * 512 and b["n_runs"] == n_slots

@@ -64,6 +64,33 @@ __device__ __forceinline__ uint64_t shfl_xor_u64(uint64_t v, int m)
     return ((uint64_t)hi << 32) | lo;
 }
 
+// Bitonic sort of T keys, one per thread of the CTA (ascending by thread id).  s0 / s1: T keys each.
+template <int T>
+__device__ __forceinline__ uint64_t fault_sort_keys(uint64_t key, int tid, uint64_t *s0, uint64_t *s1)
+{
+    int buf = 0;
+#pragma unroll
+    for (int k = 2; k <= T; k <<= 1) {
+#pragma unroll
+        for (int j = k >> 1; j > 0; j >>= 1) {
+            uint64_t other;
+            if (j < 32) {
+                other = shfl_xor_u64(key, j);
+            }
+            else {
+                uint64_t *s = buf ? s1 : s0;
+                s[tid] = key;
+                __syncthreads();
+                other = s[tid ^ j];
+                buf ^= 1;
+            }
+            const bool keep_min = ((tid & j) == 0) == ((tid & k) == 0);
+            key = (keep_min == (key < other)) ? key : other;
+        }
+    }
+    return key;
+}
+
 // ------------------------------------------------------------------------------------------------
 // F1 only: one thread per packet.
 __global__ void __launch_bounds__(256)
@@ -146,7 +173,9 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
     f.valid = 0; f.flags = 0; f.utlb_id = 0; f.access_type = 0; f.fault_address = 0; f.inst_address = 0; f.inst_aperture = 0; f.ve_id = 0;
     uint32_t w7 = 0;
     if (inwin) {
-        ring_idx = (uint32_t)(((uint64_t)prm.get + base + (uint32_t)tid) % prm.ring_entries);
+        // get < ring_entries and base + tid < n_entries < ring_entries: at most one wrap (:975)
+        const uint64_t at = (uint64_t)prm.get + base + (uint32_t)tid;
+        ring_idx = (uint32_t)(at >= prm.ring_entries ? at - prm.ring_entries : at);
         const uint4 a = ld_stream_v4((const uint4 *)&ring[ring_idx]);
         const uint4 b = ld_stream_v4((const uint4 *)&ring[ring_idx] + 1);
         w7 = b.w;
@@ -341,25 +370,15 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
         key = ((uint64_t)rank << (ib + 3 + kPageBits)) | ((mypage & ((1ull << kPageBits) - 1)) << (ib + 3)) |
               ((uint64_t)(7u - myacc) << ib) | (uint64_t)tid;
 
-    // bitonic sort of T keys: partner distances < 32 by shuffle, >= 32 through shared memory (ping-pong)
-    int buf = 0;
-    for (int k = 2; k <= T; k <<= 1) {
-        for (int j = k >> 1; j > 0; j >>= 1) {
-            uint64_t other;
-            if (j < 32) {
-                other = shfl_xor_u64(key, j);
-            }
-            else {
-                uint64_t *s = buf ? s_sort1 : s_sort0;
-                s[tid] = key;
-                __syncthreads();
-                other = s[tid ^ j];
-                buf ^= 1;
-            }
-            const bool up = (tid & k) == 0;
-            const bool keep_min = ((tid & j) == 0) == up;
-            key = (keep_min == (key < other)) ? key : other;
-        }
+    // bitonic sort of T keys: partner distances < 32 by shuffle, >= 32 through shared memory (ping-pong); the
+    // network is unrolled for the CTA size (the generic loop spent more instructions on its control than on keys)
+    switch (T) {
+        case 32: key = fault_sort_keys<32>(key, tid, s_sort0, s_sort1); break;
+        case 64: key = fault_sort_keys<64>(key, tid, s_sort0, s_sort1); break;
+        case 128: key = fault_sort_keys<128>(key, tid, s_sort0, s_sort1); break;
+        case 256: key = fault_sort_keys<256>(key, tid, s_sort0, s_sort1); break;
+        case 512: key = fault_sort_keys<512>(key, tid, s_sort0, s_sort1); break;
+        default: key = fault_sort_keys<1024>(key, tid, s_sort0, s_sort1); break;
     }
     // publish the sorted keys for neighbour lookups
     __syncthreads();

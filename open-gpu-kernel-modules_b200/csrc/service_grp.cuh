@@ -462,23 +462,35 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
                 }
                 const uint32_t ex = incl - rpk;
                 uint32_t k0 = run_off + (ex & 1023u), k1 = run_off + r0 + ((ex >> 10) & 1023u), k2 = run_off + r0 + r1 + (ex >> 20);
+                // Every lane works on ITS first word that still holds run starts (picked with selects: the words
+                // are registers).  Walking the words in a fixed order instead made the warp pass through all W
+                // words with the handful of lanes whose runs sit in that word (ncu r1_m: 30 % of the kernel's
+                // instructions at 4 active lanes).
+                uint32_t words_left = 0;
 #pragma unroll
-                for (int w = 0; w < W; w++) {
-                    uint32_t s_bits = start[w];
+                for (int w = 0; w < W; w++) words_left |= start[w] ? (1u << w) : 0u;
+                while (words_left) {
+                    const int j = __ffs((int)words_left) - 1;
+                    words_left &= words_left - 1u;
+                    uint32_t s_bits = start[0], stop_j = stop[0], next_j = next_abs[0], f0 = from0[0], f1 = from1[0], pf_j = pf[0];
+#pragma unroll
+                    for (int w = 1; w < W; w++)
+                        if (j == w) { s_bits = start[w]; stop_j = stop[w]; next_j = next_abs[w]; f0 = from0[w]; f1 = from1[w]; pf_j = pf[w]; }
+                    const uint32_t page0 = 32u * (word0 + (uint32_t)j);
                     while (s_bits) {
                         const int s = __ffs((int)s_bits) - 1;
                         s_bits &= s_bits - 1;
-                        const uint32_t rest = s == 31 ? 0u : (stop[w] >> (s + 1));
-                        const uint32_t first_page = 32u * (word0 + w) + (uint32_t)s;
-                        const uint32_t end = rest ? first_page + (uint32_t)__ffs((int)rest) : next_abs[w];
-                        const uint32_t is0 = (from0[w] >> s) & 1u, is1 = (from1[w] >> s) & 1u;
+                        const uint32_t rest = s == 31 ? 0u : (stop_j >> (s + 1));
+                        const uint32_t first_page = page0 + (uint32_t)s;
+                        const uint32_t end = rest ? first_page + (uint32_t)__ffs((int)rest) : next_j;
+                        const uint32_t is0 = (f0 >> s) & 1u, is1 = (f1 >> s) & 1u;
                         const uint32_t pos = is0 ? k0 : (is1 ? k1 : k2);
                         k0 += is0; k1 += is1; k2 += 1u - is0 - is1;
                         if (pos < prm.run_cap) {
-                            // uvmtier_copy_run_t: slot | first_page:16, num_pages:10, src:3, prefetch:1, pad:2
+                            // uvmtier_copy_run_t: slot | first_page:16, num_pages:10, src:3, prefetch:1, dst:2 (0 = HBM)
                             const uint32_t src = is0 ? 0u : (is1 ? 1u : (uint32_t)UVMTIER_RUN_SRC_ZERO);
                             ((uint2 *)runs)[pos] = make_uint2(slot, first_page | ((end - first_page) << 16) | (src << 26) |
-                                                                        (((pf[w] >> s) & 1u) << 29));
+                                                                        (((pf_j >> s) & 1u) << 29));
                         }
                     }
                 }

@@ -21,25 +21,40 @@ k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ g
                 const uvmtier_fault_batch_t *__restrict__ batches, const uvmtier_instance_ptr_entry_t *__restrict__ tbl,
                 unsigned long long *__restrict__ cw, uint32_t *__restrict__ batch_unmapped, uint2 *__restrict__ slotpos)
 {
-    const uint32_t total = prm.n_batches * prm.B;
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-        const uint32_t b = svc_batch_of(prm, t), g = t - b * prm.B;
-        const uvmtier_fault_batch_t bt = batches[b];
-        uint2 sp = make_uint2(0xffffffffu, 0u);
-        if (bt.status == NV_OK && g < bt.num_block_groups) {
-            const uvmtier_fault_group_t grp = groups[t];
-            if (!(grp.flags & 1u)) {                        // fatal fault type: service_fault_batch skips it (:2294-2303)
-                const uint32_t slot = svc_slot(prm, tbl[grp.ctx].va_space, grp.block_start);
+    const uint32_t total = prm.n_batches * prm.B, stride = gridDim.x * blockDim.x;
+    // two runs per thread and iteration: the loads of both are in flight before either is used (the kernel is a
+    // chain of dependent loads: batch header, run, table row, atomic)
+    for (uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += 2 * stride) {
+        uint32_t t[2], b[2];
+        uint32_t status[2], ngroups[2];
+        uvmtier_fault_group_t grp[2];
+        bool in[2];
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            t[u] = t0 + (uint32_t)u * stride;
+            in[u] = t[u] < total;
+            b[u] = in[u] ? svc_batch_of(prm, t[u]) : 0u;
+            status[u] = batches[b[u]].status;
+            ngroups[u] = batches[b[u]].num_block_groups;
+            grp[u] = groups[in[u] ? t[u] : 0u];
+        }
+#pragma unroll
+        for (int u = 0; u < 2; u++) {
+            if (!in[u])
+                continue;
+            uint2 sp = make_uint2(0xffffffffu, 0u);
+            if (status[u] == NV_OK && t[u] - b[u] * prm.B < ngroups[u] && !(grp[u].flags & 1u)) {   // flags bit 0: fatal fault
+                const uint32_t slot = svc_slot(prm, tbl[grp[u].ctx].va_space, grp[u].block_start);  // type, skipped (:2294-2303)
                 if (slot == 0xffffffffu) {
-                    batch_unmapped[b] = 1u;
+                    batch_unmapped[b[u]] = 1u;
                 }
                 else {
-                    const unsigned long long old = atomicAdd(&cw[slot], ((unsigned long long)grp.block_faults << 32) | 1ull);
+                    const unsigned long long old = atomicAdd(&cw[slot], ((unsigned long long)grp[u].block_faults << 32) | 1ull);
                     sp = make_uint2(slot, (uint32_t)old);
                 }
             }
+            slotpos[t[u]] = sp;
         }
-        slotpos[t] = sp;
     }
 }
 
@@ -82,10 +97,21 @@ k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t heavy_m
 __global__ void __launch_bounds__(kSvcThreads)
 k_service_fill(uint32_t total, const uint2 *__restrict__ slotpos, const uint32_t *__restrict__ offset, uint32_t *__restrict__ list)
 {
-    for (uint32_t t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
-        const uint2 sp = slotpos[t];
-        if (sp.x != 0xffffffffu)
-            list[offset[sp.x] + sp.y] = t;
+    const uint32_t stride = gridDim.x * blockDim.x;
+    for (uint32_t t0 = blockIdx.x * blockDim.x + threadIdx.x; t0 < total; t0 += 4 * stride) {
+        uint2 sp[4];
+        uint32_t off[4];
+#pragma unroll
+        for (int u = 0; u < 4; u++) {
+            const uint32_t t = t0 + (uint32_t)u * stride;
+            sp[u] = t < total ? slotpos[t] : make_uint2(0xffffffffu, 0u);
+        }
+#pragma unroll
+        for (int u = 0; u < 4; u++) off[u] = sp[u].x != 0xffffffffu ? offset[sp[u].x] : 0u;
+#pragma unroll
+        for (int u = 0; u < 4; u++)
+            if (sp[u].x != 0xffffffffu)
+                list[off[u] + sp[u].y] = t0 + (uint32_t)u * stride;
     }
 }
 
@@ -124,26 +150,44 @@ k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint3
         s_base[threadIdx.x] = before + x - v;
         __syncthreads();
     }
-    for (uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5); slot < n_slots; slot += n_warps) {
-        const uint2 c = cw[slot];
-        const uint32_t cnt = c.x;
+    // the next slot's counters and list start are loaded while this slot's list is sorted
+    uint32_t slot = blockIdx.x * (kSortThreads / 32) + (threadIdx.x >> 5);
+    uint2 c = slot < n_slots ? cw[slot] : make_uint2(0u, 0u);
+    uint32_t off = slot < n_slots ? offset[slot] : 0u;
+    // lane 0: the slot's place in its work list comes back from an atomic; the store that needs it waits until the
+    // next slot is taken up, so the sort below does not stall on it
+    uint32_t *pend_at = NULL;
+    uint32_t pend_slot = 0;
+    for (; slot < n_slots;) {
+        const uint32_t this_slot = slot, cnt = c.x, this_off = off;
+        const uint2 this_c = c;
+        slot += n_warps;
+        c = slot < n_slots ? cw[slot] : make_uint2(0u, 0u);
+        off = slot < n_slots ? offset[slot] : 0u;
+        if (pend_at) {
+            *pend_at = pend_slot;
+            pend_at = NULL;
+        }
         if (!cnt)
             continue;
         if (lane == 0) {
-            if (c.y >= heavy_min) {
-                heavy[1u + atomicAdd(&heavy[0], 1u)] = slot;
+            if (this_c.y >= heavy_min) {
+                pend_at = &heavy[1u + atomicAdd(&heavy[0], 1u)];
             }
             else {
                 const uint32_t bin = kLightBins - 1u - min(cnt, kLightBins - 1u);
-                light[s_base[bin] + atomicAdd(&bin_cursor[bin], 1u)] = slot;
+                pend_at = &light[s_base[bin] + atomicAdd(&bin_cursor[bin], 1u)];
             }
+            pend_slot = this_slot;
         }
         if (cnt < 2)
             continue;
-        uint32_t *l = list + offset[slot];
+        uint32_t *l = list + this_off;
         if (cnt <= 32) {
             uint32_t key = (uint32_t)lane < cnt ? l[lane] : 0xffffffffu;
+#pragma unroll
             for (int k = 2; k <= 32; k <<= 1)
+#pragma unroll
                 for (int j = k >> 1; j > 0; j >>= 1) {
                     const uint32_t other = __shfl_xor_sync(0xffffffffu, key, j);
                     const bool up = (lane & k) == 0, keep_min = ((lane & j) == 0) == up;
@@ -151,6 +195,30 @@ k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint3
                 }
             if ((uint32_t)lane < cnt)
                 l[lane] = key;
+        }
+        else if (cnt <= 64) {
+            // two keys per lane (elements lane and lane + 32): the bitonic network of 64, distance 32 inside the lane
+            uint32_t k0 = l[lane], k1 = (uint32_t)lane + 32u < cnt ? l[lane + 32] : 0xffffffffu;
+#pragma unroll
+            for (int k = 2; k <= 64; k <<= 1)
+#pragma unroll
+                for (int j = k >> 1; j > 0; j >>= 1) {
+                    if (j == 32) {
+                        const uint32_t lo = min(k0, k1), hi = max(k0, k1);
+                        k0 = lo; k1 = hi;
+                    }
+                    else {
+                        const uint32_t o0 = __shfl_xor_sync(0xffffffffu, k0, j), o1 = __shfl_xor_sync(0xffffffffu, k1, j);
+                        // element lane + 32 has bit 5 set: in the k = 32 round its direction is descending
+                        const bool up0 = k == 64 || (lane & k) == 0, up1 = k == 64 || (k < 32 && (lane & k) == 0);
+                        const bool low = (lane & j) == 0;
+                        k0 = ((low == up0) == (k0 < o0)) ? k0 : o0;
+                        k1 = ((low == up1) == (k1 < o1)) ? k1 : o1;
+                    }
+                }
+            l[lane] = k0;
+            if ((uint32_t)lane + 32u < cnt)
+                l[lane + 32] = k1;
         }
         else if (cnt <= kSortWarpKeys) {
             uint32_t P = 64;
@@ -171,9 +239,11 @@ k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint3
             __syncwarp();
         }
         else if (lane == 0) {
-            big[1u + atomicAdd(&big[0], 1u)] = slot;
+            big[1u + atomicAdd(&big[0], 1u)] = this_slot;
         }
     }
+    if (pend_at)
+        *pend_at = pend_slot;
 }
 
 // Long lists (a va_block that many batches touch): one CTA per list, bitonic sort in shared memory up to

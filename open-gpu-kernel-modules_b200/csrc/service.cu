@@ -23,8 +23,8 @@ constexpr uint32_t kHeavyMinEntries = 96;
 
 // Carves the working space for one call out of `base`.
 struct service_scratch_view {
-    uint32_t *cw, *cursor, *hist, *bin_cursor, *big, *heavy, *batch_unmapped;   // zeroed at the start of every call
-    uint32_t *offset, *light, *slotpos, *list;                           // fully rewritten before use
+    uint32_t *cw, *cursor, *hist, *big, *heavy, *batch_unmapped;   // zeroed at the start of every call
+    uint32_t *offset, *light, *light_rank, *slotpos, *list;                           // fully rewritten before use
     size_t zero_words, words;
 };
 static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint32_t n_batches, size_t total)
@@ -39,13 +39,13 @@ static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint3
     v.cw = p; p += 2 * slots4;
     v.cursor = p; p += 4;
     v.hist = p; p += kLightBins;
-    v.bin_cursor = p; p += kLightBins;
     v.big = p; p += big_cap;
     v.heavy = p; p += heavy_cap;
     v.batch_unmapped = p; p += batches4;
     v.zero_words = (size_t)(p - base);
     v.offset = p; p += slots4;
     v.light = p; p += slots4;
+    v.light_rank = p; p += slots4;
     v.slotpos = p; p += 2 * total4;
     v.list = p; p += total4;
     v.words = (size_t)(p - base);
@@ -133,13 +133,14 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     static const char *heavy_env = getenv("UVMTIER_SERVICE_HEAVY_MIN");
     const uint32_t heavy_min = heavy_env ? (uint32_t)strtoul(heavy_env, NULL, 0) : kHeavyMinEntries;
     const uint32_t list_heavy_min = heavy_min < kHeavyMinEntries ? kHeavyMinEntries : heavy_min;
-    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, list_heavy_min, v.offset, v.cursor, v.hist);
+    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, list_heavy_min, v.offset, v.cursor, v.hist,
+                   v.light_rank);
     UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
     size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
     if (sgrid > cap)
         sgrid = cap;
     UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
-                   v.big, v.heavy, v.hist, v.bin_cursor, v.light);
+                   v.big, v.heavy, v.hist, v.light_rank, v.light);
     UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, cw, v.offset, v.list, v.big);
 
     // lanes per va_block x CTAs per SM the kernel is compiled for; UVMTIER_SERVICE_LANES / UVMTIER_SERVICE_MINCTAS
@@ -288,7 +289,7 @@ constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of
 constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size
 constexpr uint32_t kNoAllocMaxBatches = 4096;
 // scratch_view() of the largest problem, with room for its alignment padding
-constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 4 + 2 * kLightBins + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
+constexpr size_t kNoAllocWords = (size_t)kNoAllocMaxSlots * 5 + kLightBins + (kNoAllocMaxEntries / kSortWarpKeys + 8) +
                                  (kNoAllocMaxEntries / kHeavyMinEntries + 8) + kNoAllocMaxBatches +
                                  (size_t)kNoAllocMaxEntries * 3 + 64;
 

@@ -59,27 +59,36 @@ k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ g
 }
 
 // Also counts the light slots (fewer than heavy_min entries) by number of runs: hist[kLightBins - 1 - min(runs,
-// kLightBins - 1)], so that k_service_sort_lists can line them up with the longest lists first.  cursor[0] = list
-// space handed out, cursor[1] = number of light slots.
+// kLightBins - 1)], and gives every light slot its rank inside its bin (light_rank[slot]), so that
+// k_service_sort_lists can line them up with the longest lists first.  cursor[0] = list space handed out,
+// cursor[1] = number of light slots.
 constexpr uint32_t kLightBins = 256;
 __global__ void __launch_bounds__(256)
 k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t heavy_min, uint32_t *__restrict__ offset,
-                uint32_t *__restrict__ cursor, uint32_t *__restrict__ hist)
+                uint32_t *__restrict__ cursor, uint32_t *__restrict__ hist, uint32_t *__restrict__ light_rank)
 {
-    __shared__ uint32_t s_hist[kLightBins];
+    __shared__ uint32_t s_hist[kLightBins], s_cta_base[kLightBins];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
     const int lane = threadIdx.x & 31;
     const uint2 cwv = slot < n_slots ? cw[slot] : make_uint2(0u, 0u);
     const uint32_t c = cwv.x;
     s_hist[threadIdx.x] = 0;
     __syncthreads();
-    if (c && cwv.y < heavy_min)
-        atomicAdd(&s_hist[kLightBins - 1u - min(c, kLightBins - 1u)], 1u);
+    // the slot's rank inside its bin = this CTA's share of the bin (one global atomic per CTA and bin: thousands of
+    // slots share a few dozen bins, per-slot global atomics on them serialise) + the slot's rank inside the CTA
+    const bool is_light = c && cwv.y < heavy_min;
+    const uint32_t bin = kLightBins - 1u - min(c, kLightBins - 1u);
+    uint32_t rank = 0;
+    if (is_light)
+        rank = atomicAdd(&s_hist[bin], 1u);
     __syncthreads();
     if (s_hist[threadIdx.x]) {
-        atomicAdd(&hist[threadIdx.x], s_hist[threadIdx.x]);
+        s_cta_base[threadIdx.x] = atomicAdd(&hist[threadIdx.x], s_hist[threadIdx.x]);
         atomicAdd(&cursor[1], s_hist[threadIdx.x]);
     }
+    __syncthreads();
+    if (is_light)
+        light_rank[slot] = s_cta_base[bin] + rank;
     uint32_t incl = c;
     for (int d = 1; d < 32; d <<= 1) {
         const uint32_t y = __shfl_up_sync(0xffffffffu, incl, d);
@@ -128,7 +137,7 @@ static_assert(kLightBins == (uint32_t)kSortThreads, "one thread per bin in the h
 __global__ void __launch_bounds__(kSortThreads)
 k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
                      uint32_t *__restrict__ list, uint32_t heavy_min, uint32_t *__restrict__ big, uint32_t *__restrict__ heavy,
-                     const uint32_t *__restrict__ hist, uint32_t *__restrict__ bin_cursor, uint32_t *__restrict__ light)
+                     const uint32_t *__restrict__ hist, const uint32_t *__restrict__ light_rank, uint32_t *__restrict__ light)
 {
     __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
     __shared__ uint32_t s_base[kLightBins], s_part[kSortThreads / 32];
@@ -176,7 +185,7 @@ k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint3
             }
             else {
                 const uint32_t bin = kLightBins - 1u - min(cnt, kLightBins - 1u);
-                pend_at = &light[s_base[bin] + atomicAdd(&bin_cursor[bin], 1u)];
+                pend_at = &light[s_base[bin] + light_rank[this_slot]];
             }
             pend_slot = this_slot;
         }

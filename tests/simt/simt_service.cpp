@@ -43,10 +43,10 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
     counters[0] = counters[1] = 0;
     memset(entry_flags, 0, total * sizeof(uint16_t));
     simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_count(prm, groups, batches, tbl, cw64.data(), unmapped.data(), slotpos.data()); });
-    std::vector<uint32_t> hist(kLightBins, 0), bin_cursor(kLightBins, 0), light(n_slots + 1, 0);
-    simt::launch(dim3((n_slots + 255) / 256), dim3(256), [&] { k_service_alloc(n_slots, cw, heavy_min, offset.data(), cursor.data(), hist.data()); });
+    std::vector<uint32_t> hist(kLightBins, 0), light_rank(n_slots + 1, 0), light(n_slots + 1, 0);
+    simt::launch(dim3((n_slots + 255) / 256), dim3(256), [&] { k_service_alloc(n_slots, cw, heavy_min, offset.data(), cursor.data(), hist.data(), light_rank.data()); });
     simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_fill((uint32_t)total, slotpos.data(), offset.data(), list.data()); });
-    simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, cw, offset.data(), list.data(), heavy_min, big.data(), heavy.data(), hist.data(), bin_cursor.data(), light.data()); });
+    simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, cw, offset.data(), list.data(), heavy_min, big.data(), heavy.data(), hist.data(), light_rank.data(), light.data()); });
     simt::launch(dim3(2), dim3(kSortBigThreads), [&] { k_service_sort_big(cw, offset.data(), list.data(), big.data()); });
     const uint32_t ggrid = (uint32_t)(((size_t)n_slots * lanes_per_block + kGrpThreads - 1) / kGrpThreads);
 #define GRP(G) simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<G, 1>(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), light.data(), cursor.data() + 1, entry_flags, service, runs, counters); })

@@ -22,9 +22,6 @@ namespace uvmtier_k {
 
 constexpr int kGrpThreads = 128;
 constexpr uint32_t kFullWarp = 0xffffffffu;
-#ifdef UVMTIER_EXPERIMENT_SPREAD
-static __device__ uint32_t g_dbg_counters[1024 * 32];
-#endif
 
 // ---- levels of <= 32 leaves inside one word (same arithmetic as pf_tree_select, offset 0) ----
 __device__ __forceinline__ uint32_t pf_word_levels(uint32_t w, uint32_t fw, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3,
@@ -215,8 +212,10 @@ __device__ __forceinline__ uint32_t pf_get_hint_grp(bool has, const uint32_t (&f
 
 // Claims n consecutive elements of the run array for every lane of the warp (n = 0: none) with ONE atomic: a
 // single counter would otherwise serialise a million of them.  The exclusive prefix over the lanes is summed
-// bit-plane by bit-plane with ballots (the values are small).  Returns the calling lane's first element.
-__device__ __forceinline__ uint32_t svc_claim_runs(uint32_t *counter, uint32_t n, int lane)
+// bit-plane by bit-plane with ballots (the values are small).  In two halves, so that the atomic's round trip to
+// L2 overlaps whatever the caller puts between them: _issue returns lane 0's pending answer and this lane's
+// prefix, _collect turns them into the calling lane's first element.
+__device__ __forceinline__ uint32_t svc_claim_runs_issue(uint32_t *counter, uint32_t n, int lane, uint32_t *before_out)
 {
     const uint32_t below = (1u << lane) - 1u;
     uint32_t before = 0, total = 0;
@@ -225,10 +224,15 @@ __device__ __forceinline__ uint32_t svc_claim_runs(uint32_t *counter, uint32_t n
         before += (uint32_t)__popc(plane & below) << j;
         total += (uint32_t)__popc(plane) << j;
     }
+    *before_out = before;
     uint32_t base = 0;
     if (lane == 0)
         base = atomicAdd(counter, total);
-    return __shfl_sync(kFullWarp, base, 0) + before;
+    return base;
+}
+__device__ __forceinline__ uint32_t svc_claim_runs_collect(uint32_t pending_base, uint32_t before)
+{
+    return __shfl_sync(kFullWarp, pending_base, 0) + before;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -298,6 +302,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
         uint32_t t3 = t0, b1 = b0;
         uint4 g2 = g1, e1 = e0;
         if (live) {
+            // (plain loads: forcing their issue point with volatile inline-asm loads measured 4 % slower)
             t3 = k + 3 < cnt ? list[off + k + 3] : t0;
             g2 = graw[t2];
             b1 = svc_batch_of(prm, t1);
@@ -428,14 +433,26 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             const uint32_t tot = G > 1 ? __shfl_sync(kFullWarp, incl, gb + G - 1) : incl;
             const uint32_t r0 = tot & 1023u, r1 = (tot >> 10) & 1023u, r2 = tot >> 20;
             run_cnt = r0 + r1 + r2;
-            if (__any_sync(kFullWarp, run_cnt != 0u)) {
-#ifdef UVMTIER_EXPERIMENT_SPREAD
-                run_off = svc_claim_runs(&g_dbg_counters[(blockIdx.x & 1023u) * 32u], gl == 0 ? run_cnt : 0u, lane);
-#else
-                run_off = svc_claim_runs(&counters[0], gl == 0 ? run_cnt : 0u, lane);
-#endif
-                if (G > 1)
-                    run_off = __shfl_sync(kFullWarp, run_off, gb);
+            // run-array space for the whole warp: the atomic is issued here, its answer is picked up after the state
+            // update and the stop positions below (its round trip to L2 was 13 % of the kernel's stall samples)
+            const bool any_runs = __any_sync(kFullWarp, run_cnt != 0u);
+            uint32_t claim_pending = 0, claim_before = 0;
+            if (any_runs) {
+                claim_pending = svc_claim_runs_issue(&counters[0], gl == 0 ? run_cnt : 0u, lane, &claim_before);
+            }
+            // uvm_va_block_make_resident_finish :5042-5084 and the mapping step (:11019-11066, :12063-12080)
+#pragma unroll
+            for (int w = 0; w < W; w++) {
+                gres[w] |= newres[w];
+                c0[w] &= ~newres[w];
+                c1[w] &= ~newres[w];
+                p0[w] |= newres[w];
+                if (logical == PROT_RWA) {
+                    p1[w] |= newres[w];
+                    p2[w] |= newres[w];
+                }
+            }
+            if (any_runs) {
                 // where a run that is still open at the end of this lane's words stops: first stop position in the
                 // following lanes
                 uint32_t stop[W], next_abs[W];
@@ -460,6 +477,9 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
                     next_abs[w] = nxt;
                     if (stop[w]) nxt = 32u * (word0 + w) + (uint32_t)__ffs((int)stop[w]) - 1u;
                 }
+                run_off = svc_claim_runs_collect(claim_pending, claim_before);
+                if (G > 1)
+                    run_off = __shfl_sync(kFullWarp, run_off, gb);
                 const uint32_t ex = incl - rpk;
                 uint32_t k0 = run_off + (ex & 1023u), k1 = run_off + r0 + ((ex >> 10) & 1023u), k2 = run_off + r0 + r1 + (ex >> 20);
                 // Every lane works on ITS first word that still holds run starts (picked with selects: the words
@@ -497,18 +517,6 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             }
             if (!run_cnt)
                 run_off = 0;
-            // uvm_va_block_make_resident_finish :5042-5084 and the mapping step (:11019-11066, :12063-12080)
-#pragma unroll
-            for (int w = 0; w < W; w++) {
-                gres[w] |= newres[w];
-                c0[w] &= ~newres[w];
-                c1[w] &= ~newres[w];
-                p0[w] |= newres[w];
-                if (logical == PROT_RWA) {
-                    p1[w] |= newres[w];
-                    p2[w] |= newres[w];
-                }
-            }
         }
         // ---- record: 32-byte header by the first lane, every lane its words of new_residency ----
         if (live) {

@@ -413,7 +413,7 @@ k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restric
     if (b >= prm.n_batches || !batch_unmapped[b])
         return;
     const uint32_t base = b * prm.B, ng = batches[b].num_block_groups;
-    uint32_t ip_sum = 0;
+    uint32_t ip_sum = 0, dup_sum = 0;
     for (uint32_t g = 0; g < ng; g++) {
         const uvmtier_fault_group_t grp = groups[base + g];
         if (grp.flags & 1u)
@@ -437,6 +437,7 @@ k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restric
             }
             if (dup)
                 fl |= UVMTIER_SF_DUPLICATE;
+            dup_sum += dup ? e.num_instances : (uint32_t)e.num_instances - 1u;   // update_batch_and_notify_fault (:1692, :1200-1203)
             if (acc == ACC_PREFETCH) {
                 fl |= UVMTIER_SF_INVALID_PREFETCH;
                 ip_sum += e.num_instances;
@@ -455,6 +456,8 @@ k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restric
     }
     if (ip_sum)
         atomicAdd(&batches[b].num_invalid_prefetch_faults, ip_sum);
+    if (dup_sum)
+        atomicAdd(&batches[b].num_duplicate_faults, dup_sum);
 }
 
 } // namespace uvmtier_k

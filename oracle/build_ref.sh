@@ -65,6 +65,17 @@ if [ -f "$HERE/ref_faults_glue.c" ]; then
     echo "build_ref: built $OUT/libref_faults.so"
 fi
 
+# ---------------- service leg: service_fault_batch_block_locked and its helpers, verbatim ----------------
+if [ -f "$HERE/ref_service_glue.c" ]; then
+    pin uvm_tools.h 2b366fbdaa63bdef
+    sed -n '1214,1272p;1293,1360p;1375,1597p;1656,1693p' "$UVM/uvm_gpu_replayable_faults.c" > "$TMP/x_service.h"
+    sed -n '181,188p;522,537p' "$UVM/uvm_hal_types.h" > "$TMP/x_prot.h"
+    sed -n '46,62p' "$UVM/uvm_tools.h" > "$TMP/x_tools_reason.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_service_glue.c" "$HERE/ref_faults_blackwell.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_prefetch.c" -o "$OUT/libref_service.so"
+    echo "build_ref: built $OUT/libref_service.so"
+fi
+
 # ---------------- residency / migration leg ----------------
 if [ -f "$HERE/ref_resident_glue.c" ]; then
     sed -n '36,80p' "$UVM/uvm_va_block_types.h" > "$TMP/x_va_block_types.h"

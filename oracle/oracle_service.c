@@ -13,9 +13,15 @@
  * to `return processor_id`, uvm_va_block.c:11560-11712, when the page is not resident on it); CPU memory
  * has two NUMA nodes (0 = DRAM, 1 = CXL); both tiers and HBM back a va_block contiguously.
  *
- * Pinning: PARITY UNPINNED for this stage beyond its prefetch leg (which is the KAT-pinned oracle_prefetch.c).
- * No known-answer vectors exist in the reference for it, and service_fault_batch_block_locked with its callees
- * in uvm_va_block.c (13 k lines) has not been compiled against the shims.
+ * Pinning: no known-answer vectors exist in the reference for this stage.  The ENTRY LOOP (duplicates,
+ * permissions, authorised-already, new_residency / region, batch counters, fatal / invalid-prefetch marks) is
+ * pinned against the reference's own service_fault_batch_block_locked, check_fault_access_permissions,
+ * fault_entry_duplicate_flags, mark_fault_* and service_fault_batch_fatal_notify compiled verbatim
+ * (oracle/_ref/libref_service.so, ref_service_glue.c; tests/test_oracle_service.py -k reference) -- which found
+ * and fixed one divergence (duplicates of faults outside every va_range are counted too, :1692).  The BACK HALF
+ * (oracle_service_block_apply: prefetch hint = the KAT-pinned oracle_prefetch.c; make_resident algebra, copy
+ * list, mapping) stays PARITY UNPINNED: its callees live in uvm_va_block.c (13 k lines) and have not been compiled
+ * against the shims.
  * Batches are applied in trace order, exactly like uvm_parent_gpu_service_replayable_faults (:2906-2960).
  */
 #include "oracle_common.h"
@@ -66,6 +72,97 @@ uint32_t oracle_emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uin
         p = q;
     }
     return n;
+}
+
+/*
+ * The back half of servicing one va_block run: uvm_va_block_service_locked (uvm_va_block.c:12307-12359) with what
+ * service_fault_batch_block_locked built -- the new_residency mask of the faulting GPU and the faulted region.
+ * Prefetch hint, make_resident (copy list, residency), mapping.  Fills the rest of *rec, appends copy runs at
+ * runs[*nrun].  Also called by oracle/ref_service_glue.c, where the reference's own entry loop builds the mask.
+ */
+void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_state_t *st, uint32_t slot, uint64_t block_start,
+                                const uint64_t *new_residency, unsigned region_first, unsigned region_outer,
+                                ref_service_group_t *rec, ref_copy_run_t *runs, uint32_t *nrun_io, uint32_t run_cap)
+{
+    or_mask_t pf_mask, cpu0, cpu1, todo, from0, from1, touch, any_cpu, newres, gpu_res, pte[3];
+    ref_prefetch_block_t pb;
+    uint32_t hint, nrun = *nrun_io;
+    unsigned rf = region_first, ro = region_outer, p, i;
+    const unsigned logical = st->logical_prot[slot];
+
+    or_load(&newres, new_residency);
+    mask_ptr_load(&gpu_res, st->gpu_resident, slot);
+    for (i = 0; i < 3; i++) mask_ptr_load(&pte[i], st->gpu_pte[i], slot);
+
+    /* get_prefetch_hint :11828-11881: exactly one destination processor */
+    memset(&pb, 0, sizeof(pb));
+    pb.start = block_start; pb.big_page_size = 65536; pb.num_pages = 512;
+    pb.faulted_first = (uint16_t)rf; pb.faulted_outer = (uint16_t)ro;
+    pb.new_residency = (uint16_t)lay->gpu_id; pb.preferred_location = st->preferred_location[slot];
+    mask_ptr_load(&cpu0, st->cpu_resident[0], slot);
+    mask_ptr_load(&cpu1, st->cpu_resident[1], slot);
+    or_or(&any_cpu, &cpu0, &cpu1);
+    pb.flags = REF_PF_HAS_RESIDENT_MASK | REF_PF_GPU_VA_SPACE_REGISTERED |
+               ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0);
+    oracle_prefetch_get_hint_va_block(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot], pf_mask.w, &hint);
+    rec->hint_residency = (uint16_t)hint;
+    if (hint != 257) {
+        or_or(&newres, &newres, &pf_mask);
+        for (p = 0; p < OR_WORDS; p++) if (newres.w[p]) { rf = 64 * p + (unsigned)__builtin_ctzll(newres.w[p]); break; }
+        for (p = OR_WORDS; p-- > 0;) if (newres.w[p]) { ro = 64 * p + 64 - (unsigned)__builtin_clzll(newres.w[p]); break; }
+        rec->prefetch_count = (uint16_t)or_weight(&pf_mask);
+    }
+    else {
+        or_zero(&pf_mask);
+    }
+    rec->region_first = (uint16_t)rf; rec->region_outer = (uint16_t)ro;
+    or_store(rec->new_residency, &newres);
+
+    /* make_resident_copy: block_copy_resident_pages :4660-4847, GPU destination, CPU nodes as sources */
+    or_andnot(&todo, &newres, &gpu_res);                 /* :4687-4690 */
+    or_and(&from0, &todo, &cpu0);                        /* node 0 first (for_each_possible_uvm_node) */
+    or_andnot(&todo, &todo, &from0);
+    or_and(&from1, &todo, &cpu1);
+    or_andnot(&touch, &todo, &from1);                    /* resident nowhere: populated + zeroed at the destination */
+    rec->migrated[0] = (uint16_t)or_weight(&from0);
+    rec->migrated[1] = (uint16_t)or_weight(&from1);
+    rec->first_touch = (uint16_t)or_weight(&touch);
+    {
+        uint32_t k = 0;
+        k += oracle_emit_runs(&from0, &pf_mask, slot, 0, 0, runs, nrun + k, run_cap);
+        k += oracle_emit_runs(&from1, &pf_mask, slot, 1, 0, runs, nrun + k, run_cap);
+        k += oracle_emit_runs(&touch, &pf_mask, slot, 7, 0, runs, nrun + k, run_cap);
+        rec->run_count = (uint16_t)k;
+        nrun += k;
+    }
+    /* make_resident_finish :5042-5084: dst |= migrated | first touch; everyone else loses the region's pages */
+    or_or(&gpu_res, &gpu_res, &newres);
+    or_andnot(&cpu0, &cpu0, &newres);
+    or_andnot(&cpu1, &cpu1, &newres);
+    mask_ptr_store(st->gpu_resident, slot, &gpu_res);
+    mask_ptr_store(st->cpu_resident[0], slot, &cpu0);
+    mask_ptr_store(st->cpu_resident[1], slot, &cpu1);
+    if (st->gpu_evicted) {
+        /* block_make_resident_update_state :5038-5039 -> block_make_resident_clear_evicted :4978-4988 */
+        or_mask_t evicted, migrated;
+        or_or(&migrated, &from0, &from1);
+        mask_ptr_load(&evicted, st->gpu_evicted, slot);
+        or_andnot(&evicted, &evicted, &migrated);
+        mask_ptr_store(st->gpu_evicted, slot, &evicted);
+    }
+
+    /* service_finish :12063-12302: map the faulting GPU.  compute_new_permission (:11019-11066): the page is now
+     * resident on the faulting GPU, which has native atomics on its own memory, and no other faultable processor
+     * holds an atomic mapping of a page that just moved, so a read-write VMA maps READ_WRITE_ATOMIC whatever the
+     * access type; a read-only VMA maps READ_ONLY. */
+    {
+        const unsigned new_prot = logical == PROT_RWA ? PROT_RWA : PROT_RO;
+        for (i = 0; i < new_prot; i++) {
+            or_or(&pte[i], &pte[i], &newres);
+            mask_ptr_store(st->gpu_pte[i], slot, &pte[i]);
+        }
+    }
+    *nrun_io = nrun;
 }
 
 /*
@@ -134,6 +231,8 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                     }
                     if (dup)
                         fl |= REF_SF_DUPLICATE;
+                    /* update_batch_and_notify_fault, called by service_fault_batch_fatal_notify (:1692, :1200-1203) */
+                    batch[b].num_duplicate_faults += dup ? e->num_instances : (uint32_t)e->num_instances - 1;
                     if (acc == ACC_PREFETCH) {
                         fl |= REF_SF_INVALID_PREFETCH;
                         batch[b].num_invalid_prefetch_faults += e->num_instances;
@@ -221,82 +320,7 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                 continue;
 
             /* ---- uvm_va_block_service_locked, uvm_va_block.c:12307-12359 ---- */
-            {
-                or_mask_t pf_mask, cpu0, cpu1, todo, from0, from1, touch, any_cpu;
-                ref_prefetch_block_t pb;
-                uint32_t hint;
-                unsigned rf = first_page, ro = last_page + 1, p;
-
-                /* get_prefetch_hint :11828-11881: exactly one destination processor */
-                memset(&pb, 0, sizeof(pb));
-                pb.start = grp->block_start; pb.big_page_size = 65536; pb.num_pages = 512;
-                pb.faulted_first = (uint16_t)rf; pb.faulted_outer = (uint16_t)ro;
-                pb.new_residency = (uint16_t)lay->gpu_id; pb.preferred_location = st->preferred_location[slot];
-                mask_ptr_load(&cpu0, st->cpu_resident[0], slot);
-                mask_ptr_load(&cpu1, st->cpu_resident[1], slot);
-                or_or(&any_cpu, &cpu0, &cpu1);
-                pb.flags = REF_PF_HAS_RESIDENT_MASK | REF_PF_GPU_VA_SPACE_REGISTERED |
-                           ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0);
-                oracle_prefetch_get_hint_va_block(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot],
-                                                  pf_mask.w, &hint);
-                rec->hint_residency = (uint16_t)hint;
-                if (hint != 257) {
-                    or_or(&newres, &newres, &pf_mask);
-                    for (p = 0; p < OR_WORDS; p++) if (newres.w[p]) { rf = 64 * p + (unsigned)__builtin_ctzll(newres.w[p]); break; }
-                    for (p = OR_WORDS; p-- > 0;) if (newres.w[p]) { ro = 64 * p + 64 - (unsigned)__builtin_clzll(newres.w[p]); break; }
-                    rec->prefetch_count = (uint16_t)or_weight(&pf_mask);
-                }
-                else {
-                    or_zero(&pf_mask);
-                }
-                rec->region_first = (uint16_t)rf; rec->region_outer = (uint16_t)ro;
-                or_store(rec->new_residency, &newres);
-
-                /* make_resident_copy: block_copy_resident_pages :4660-4847, GPU destination, CPU nodes as sources */
-                or_andnot(&todo, &newres, &gpu_res);                 /* :4687-4690 */
-                or_and(&from0, &todo, &cpu0);                        /* node 0 first (for_each_possible_uvm_node) */
-                or_andnot(&todo, &todo, &from0);
-                or_and(&from1, &todo, &cpu1);
-                or_andnot(&touch, &todo, &from1);                    /* resident nowhere: populated + zeroed at the destination */
-                rec->migrated[0] = (uint16_t)or_weight(&from0);
-                rec->migrated[1] = (uint16_t)or_weight(&from1);
-                rec->first_touch = (uint16_t)or_weight(&touch);
-                {
-                    uint32_t k = 0;
-                    k += oracle_emit_runs(&from0, &pf_mask, slot, 0, 0, runs, nrun + k, run_cap);
-                    k += oracle_emit_runs(&from1, &pf_mask, slot, 1, 0, runs, nrun + k, run_cap);
-                    k += oracle_emit_runs(&touch, &pf_mask, slot, 7, 0, runs, nrun + k, run_cap);
-                    rec->run_count = (uint16_t)k;
-                    nrun += k;
-                }
-                /* make_resident_finish :5042-5084: dst |= migrated | first touch; everyone else loses the region's pages */
-                or_or(&gpu_res, &gpu_res, &newres);
-                or_andnot(&cpu0, &cpu0, &newres);
-                or_andnot(&cpu1, &cpu1, &newres);
-                mask_ptr_store(st->gpu_resident, slot, &gpu_res);
-                mask_ptr_store(st->cpu_resident[0], slot, &cpu0);
-                mask_ptr_store(st->cpu_resident[1], slot, &cpu1);
-                if (st->gpu_evicted) {
-                    /* block_make_resident_update_state :5038-5039 -> block_make_resident_clear_evicted :4978-4988 */
-                    or_mask_t evicted, migrated;
-                    or_or(&migrated, &from0, &from1);
-                    mask_ptr_load(&evicted, st->gpu_evicted, slot);
-                    or_andnot(&evicted, &evicted, &migrated);
-                    mask_ptr_store(st->gpu_evicted, slot, &evicted);
-                }
-
-                /* service_finish :12063-12302: map the faulting GPU.  compute_new_permission (:11019-11066): the
-                 * page is now resident on the faulting GPU, which has native atomics on its own memory, and no
-                 * other faultable processor holds an atomic mapping of a page that just moved, so a read-write
-                 * VMA maps READ_WRITE_ATOMIC whatever the access type; a read-only VMA maps READ_ONLY. */
-                {
-                    const unsigned new_prot = logical == PROT_RWA ? PROT_RWA : PROT_RO;
-                    for (i = 0; i < new_prot; i++) {
-                        or_or(&pte[i], &pte[i], &newres);
-                        mask_ptr_store(st->gpu_pte[i], slot, &pte[i]);
-                    }
-                }
-            }
+            oracle_service_block_apply(lay, st, slot, grp->block_start, newres.w, first_page, last_page + 1, rec, runs, &nrun, run_cap);
         }
     }
     if (n_runs)

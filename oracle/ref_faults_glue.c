@@ -61,6 +61,7 @@ typedef struct uvm_replayable_fault_buffer_struct {
     NvU32 cached_get;
     NvU32 cached_put;
     NvU32 utlb_count;
+    struct uvm_service_block_context_struct *block_service_context_ptr;   /* used by ref_service_glue.c only */
 } uvm_replayable_fault_buffer_t;
 
 typedef struct {

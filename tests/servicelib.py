@@ -66,6 +66,45 @@ def run_service_oracle(orc, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap
     return dict(flags=flags, records=svc[:nsvc], runs=runs, n_runs=n_runs.value, batch=batch, state=st)
 
 
+def run_service_ref(ref, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20):
+    """oracle/_ref/libref_service.so: the reference's own service_fault_batch_block_locked (verbatim) drives the
+    entry loop; the back half is the CPU restatement.  Same outputs as run_service_oracle, except that entry
+    flags carry only what the reference keeps per entry (fatal + reason + cancel mode, invalid prefetch)."""
+    B = int(gp["max_batch_size"][0])
+    nb = len(k1["batch"])
+    flags, _, runs, _ = _alloc_outputs(nb, B, run_cap)
+    svc = np.zeros(nb * B, SERVICE_GROUP_DT)
+    batch = k1["batch"].copy()
+    st = state.copy()
+    ptrs = st.ptrs()
+    n_runs = ctypes.c_uint32(0)
+    fn = ref.ref_service_fault_batches
+    fn.restype = ctypes.c_uint32
+    nsvc = fn(ctypes.c_uint32(nb), ctypes.c_uint32(B), P(k1["ordered_rec"]), P(k1["groups"]), P(batch), P(table), P(layout),
+              ctypes.byref(ptrs), ctypes.c_uint(pf[0]), ctypes.c_uint(pf[1]), ctypes.c_uint(pf[2]), P(flags), P(svc), P(runs),
+              ctypes.c_uint32(run_cap), ctypes.byref(n_runs))
+    return dict(flags=flags, records=svc[:nsvc], runs=runs, n_runs=n_runs.value, batch=batch, state=st)
+
+
+REF_FLAG_MASK = 0x0004 | 0x0008 | 0x0700 | 0x1000     # FATAL, INVALID_PREFETCH, fatal reason, cancel mode
+
+
+def assert_ref_equals_oracle(ref_res, orc_res, what=""):
+    """Reference loop vs restated loop: everything except the flags the reference does not keep per entry and
+    page_fault_count (a local variable of the reference's function)."""
+    assert np.array_equal(ref_res["flags"] & REF_FLAG_MASK, orc_res["flags"] & REF_FLAG_MASK), what + " entry flags"
+    for f in ("num_duplicate_faults", "num_invalid_prefetch_faults"):
+        assert np.array_equal(ref_res["batch"][f], orc_res["batch"][f]), "%s batch.%s" % (what, f)
+    ref_res["state"].assert_equal(orc_res["state"], what)
+    a, b = ref_res["records"], orc_res["records"]
+    assert len(a) == len(b), "%s number of records %d vs %d" % (what, len(a), len(b))
+    for f in RECORD_FIELDS:
+        if f != "page_fault_count":
+            assert np.array_equal(a[f], b[f]), "%s record.%s" % (what, f)
+    assert ref_res["n_runs"] == orc_res["n_runs"]
+    assert np.array_equal(ref_res["runs"][:ref_res["n_runs"]], orc_res["runs"][:orc_res["n_runs"]]), what + " copy runs"
+
+
 def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, lanes=4, heavy_min=96):
     """The product's servicing kernels under the CPU SIMT emulator.  lanes = lanes per va_block of the group kernel;
     slots holding heavy_min entries or more go to the warp-per-block kernel (0 = all of them, 0xffffffff = none)."""

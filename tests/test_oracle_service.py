@@ -178,3 +178,40 @@ def test_prefetch_threshold_flows_into_service(thr):
     st0 = S.random_state(lay["blocks_per_space"], 8, ro_frac=0, none_frac=0)
     _, want, got = _both(pk, gp, tbl, lay, st0, pf=(1, thr, 1))
     S.assert_service_equal(want, got, 256, "thr %d" % thr)
+
+
+# ------------------------------------------------------------------------------------------------
+# The CPU restatement against the reference's own entry loop (service_fault_batch_block_locked and its helpers,
+# compiled verbatim into oracle/_ref/libref_service.so).
+def _ref_vs_oracle(pk, gp, tbl, lay, st0, what, pf=(1, 51, 1)):
+    ref = T.load_ref("service")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_service.so not built (needs /root/reference)")
+    k1 = _k1(pk, gp, tbl)
+    layout = S.make_layout(lay)
+    a = S.run_service_ref(ref, k1, gp, tbl, layout, st0, pf)
+    b = S.run_service_oracle(T.load_oracle(), k1, gp, tbl, layout, st0, pf)
+    S.assert_ref_equals_oracle(a, b, what)
+    return a, b
+
+
+@pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
+@pytest.mark.parametrize("B", [256, 48])
+def test_oracle_matches_the_reference_entry_loop(dist, B):
+    pk, tbl, lay = TG.fault_trace(3000, 41, dist, 2, total_va_bytes=SMALL_VA)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 14)
+    a, _ = _ref_vs_oracle(pk, TG.gpu_params(B), tbl, lay, st0, "%s %d" % (dist, B))
+    assert len(a["records"]) > 5
+
+
+def test_oracle_matches_the_reference_on_unmapped_addresses_fatal_types_and_read_only_ranges():
+    pk, tbl, lay = TG.fault_trace(2500, 8, "adversarial", 2, total_va_bytes=SMALL_VA)
+    out = np.arange(2500) % 5 == 2
+    pk[out, 3] |= 0x40                                          # far above the managed range: no va_range
+    fatal = np.arange(2500) % 11 == 3
+    pk[fatal, 7] = (pk[fatal, 7] & ~np.uint32(0x1F)) | TG.HW_FAULT_TYPE_PDE_SIZE
+    pk[fatal, 3] |= 0x80                                        # the reference asserts that a va_block never mixes fatal
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 6, ro_frac=0.4, none_frac=0.2)   # fault types with serviceable ones (:1449)
+    a, b = _ref_vs_oracle(pk, TG.gpu_params(128), tbl, lay, st0, "unmapped + fatal + read-only")
+    assert int((a["flags"] & 4 != 0).sum()) > 100 and int((a["flags"] & 8 != 0).sum()) > 10
+    assert int(a["batch"]["num_duplicate_faults"].sum()) > 100

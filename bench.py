@@ -127,8 +127,8 @@ def build_workload(seed, trace):
 # ----------------------------------------------------------------------------------------------- CPU arm
 def _ref_worker(args):
     """One process: the CPU implementation on a shard of whole batches.  Stage A/B run the reference's own C
-    (oracle/_ref/libref_faults.so) when it was built, stage C/D/E the CPU port (oracle) -- its prefetch leg is
-    bit-identical to the reference's uvm_perf_prefetch.c."""
+    (oracle/_ref/libref_faults.so) when it was built; stage C/D/E the reference's own per-va_block entry loop
+    (oracle/_ref/libref_service.so) with the CPU port of the uvm_va_block.c back half behind it, else the port."""
     pk, tbl, gp, layout, state, reps = args
     sys.path.insert(0, os.path.join(ROOT, "tests"))
     import faultlib as F
@@ -136,7 +136,8 @@ def _ref_worker(args):
     import uvmtier_testlib as T
     orc = T.load_oracle()
     rf = T.load_ref("faults")
-    kind = "reference" if rf is not None else "port"
+    rs = T.load_ref("service")
+    kind = "reference" if rf is not None and rs is not None else "port"
     sim_like = None
     best = 1e30
     B = int(gp["max_batch_size"][0])
@@ -149,7 +150,10 @@ def _ref_worker(args):
         if sim_like is None:
             sim_like = _port_sorted_view(orc, pk, gp, tbl, r)
         t1 = time.perf_counter()
-        S.run_service_oracle(orc, sim_like, gp, tbl, layout, state, run_cap=1 << 22)
+        if rs is not None:
+            S.run_service_ref(rs, sim_like, gp, tbl, layout, state, run_cap=1 << 22)
+        else:
+            S.run_service_oracle(orc, sim_like, gp, tbl, layout, state, run_cap=1 << 22)
         t_c = time.perf_counter() - t1
         best = min(best, t_ab + t_c)
     return best, kind
@@ -239,7 +243,8 @@ def run_reference_arm(args, rank):
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
             "config": {"workload": workload_name(args.trace),
-                       "cpu": "fetch/merge/sort: the reference's own C (oracle/_ref); per-va_block service: CPU port (oracle)"},
+                       "cpu": "fetch/merge/sort and the per-va_block entry loop: the reference's own C (oracle/_ref); "
+                              "prefetch hint + make_resident behind it: CPU port (oracle)"},
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": "%d entries per step sharded over %d processes, each with its own va_block state" % (n, cores)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -528,7 +533,7 @@ def main():
         v1, kind, ns = cpu_arm(wl, 1, reps=2)
         line["cpu_baseline"] = {"value": v1, "unit": UNIT, "cores": 1, "kind": kind,
                                 "sample": "full step (%d entries), best of 2, 1 thread (the reference services one GPU on one thread); "
-                                          "fetch/merge/sort = reference C, service = CPU port" % ns}
+                                          "fetch/merge/sort + service entry loop = reference C, make_resident back half = CPU port" % ns}
     if rank == 0:
         print(json.dumps(line))
     if dist is not None:

@@ -629,6 +629,49 @@ NV_STATUS uvmtier_checksum_pages_device(uvmtier_ctx_t *ctx, uint32_t tier, size_
 NV_STATUS uvmtier_tier_memcpy_peak(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, uint64_t bytes, int reps,
                                    float *out_best_ms);
 
+/* ------------------------------------------------------------------------------------------ */
+/* Ops table -- the reference dispatches through per-arch function-pointer tables chosen at GPU */
+/* init (uvm_fault_buffer_hal_struct UVM/uvm_hal.h:848-864, uvm_ce_hal_struct :813-838); a      */
+/* harness built from the reference's C swaps implementations the same way.   */
+/* ------------------------------------------------------------------------------------------ */
+typedef struct {
+    /* fetch_fault_buffer_entries + preprocess_fault_batch (UVM/uvm_gpu_replayable_faults.c:844, :1134), host buffers */
+    NV_STATUS (*fetch_preprocess)(uvmtier_ctx_t *, uvmtier_fault_packet_t *h_ring, uint32_t ring_entries, uint32_t get,
+                                  uint32_t put, int clear_valid, uint32_t *h_disposition, uvmtier_ordered_fault_t *h_ordered,
+                                  uvmtier_fault_group_t *h_groups, uvmtier_fault_batch_t *h_batches,
+                                  uvmtier_fault_buffer_entry_t *h_entries, uint32_t *out_get);
+    /* the same on device buffers */
+    NV_STATUS (*fetch_preprocess_device)(uvmtier_ctx_t *, uvmtier_fault_packet_t *d_ring, uint32_t ring_entries, uint32_t get,
+                                         uint32_t put, int clear_valid, uint32_t *d_disposition,
+                                         uvmtier_ordered_fault_t *d_ordered, uvmtier_fault_group_t *d_groups,
+                                         uvmtier_fault_batch_t *d_batches, uvmtier_fault_buffer_entry_t *d_entries,
+                                         uint32_t *out_get);
+    /* service_fault_batch (:2232) down to uvm_va_block_service_locked (UVM/uvm_va_block.c:12307) */
+    NV_STATUS (*service)(uvmtier_ctx_t *, uint32_t n_batches, const uvmtier_ordered_fault_t *, const uvmtier_fault_group_t *,
+                         uvmtier_fault_batch_t *, const uvmtier_va_layout_t *, const uvmtier_block_state_t *,
+                         uint16_t *d_entry_flags, uvmtier_service_group_t *, uvmtier_copy_run_t *, uint32_t run_cap,
+                         uint32_t *d_counters);
+    /* uvm_perf_prefetch_get_hint_va_block (UVM/uvm_perf_prefetch.h:92-98), host buffers */
+    NV_STATUS (*prefetch_get_hint)(uvmtier_ctx_t *, size_t n_blocks, const uvmtier_prefetch_block_t *,
+                                   const uvmtier_page_mask_t *resident, const uvmtier_page_mask_t *faulted,
+                                   const uvmtier_page_mask_t *thrashing, const uvmtier_page_mask_t *cpu_read_mapped,
+                                   uvmtier_prefetch_info_t *, uvmtier_page_mask_t *out_prefetch_mask, uint32_t *out_residency);
+    /* uvm_va_block_make_resident (UVM/uvm_va_block.h:770-777), batched */
+    NV_STATUS (*make_resident)(uvmtier_ctx_t *, uint32_t n_requests, const uvmtier_make_resident_req_t *,
+                               const uvmtier_page_mask_t *d_page_masks, const uvmtier_page_mask_t *d_prefetch_masks,
+                               const uvmtier_va_layout_t *, const uvmtier_block_state_t *, uvmtier_make_resident_result_t *,
+                               uvmtier_copy_run_t *, uint32_t run_cap, uint32_t *d_counters);
+    /* the CE pushes of block_copy_resident_pages_between (UVM/uvm_va_block.c:4069-4377) for a list of runs */
+    NV_STATUS (*copy_runs)(uvmtier_ctx_t *, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs, uint32_t run_cap,
+                           int method);
+    /* ce_hal->memcopy / block_copy_pages (UVM/uvm_va_block.c:3863-3991) for a list of pages */
+    NV_STATUS (*copy_page_list)(uvmtier_ctx_t *, uint32_t dst_tier, uint32_t src_tier, size_t n, const uint64_t *h_dst_off,
+                                const uint64_t *h_src_off, uint32_t page_size, int method);
+} uvmtier_ops_t;
+
+/* The B200 implementation of every slot. */
+extern const uvmtier_ops_t uvmtier_gpu_ops;
+
 #ifdef __cplusplus
 }
 #endif

@@ -253,3 +253,14 @@ NV_STATUS uvmtier_stage_reserve(uvmtier_ctx_t *ctx, size_t d_bytes, size_t h_byt
     }
     return NV_OK;
 }
+
+// The ops table (include/uvmtier.h): one slot per reference interface this library replaces.
+extern "C" const uvmtier_ops_t uvmtier_gpu_ops = {
+    uvmtier_fetch_preprocess_fault_batches,
+    uvmtier_fetch_preprocess_fault_batches_device,
+    uvmtier_service_fault_batches_device,
+    uvmtier_perf_prefetch_get_hint_va_block,
+    uvmtier_make_resident_device,
+    uvmtier_copy_runs_device,
+    uvmtier_copy_page_list,
+};

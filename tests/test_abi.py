@@ -27,6 +27,18 @@ def test_library_exports_every_declared_symbol():
     assert not missing, "declared in include/ but not exported: %s" % missing
 
 
+def test_ops_table_points_at_the_entry_points():
+    """uvmtier_gpu_ops (the table a reference-side harness dispatches through) holds the exported functions, in the
+    order include/uvmtier.h declares its slots."""
+    lib = uvmtier.lib()
+    slots = ("uvmtier_fetch_preprocess_fault_batches", "uvmtier_fetch_preprocess_fault_batches_device",
+             "uvmtier_service_fault_batches_device", "uvmtier_perf_prefetch_get_hint_va_block", "uvmtier_make_resident_device",
+             "uvmtier_copy_runs_device", "uvmtier_copy_page_list")
+    table = (ctypes.c_void_p * len(slots)).in_dll(lib, "uvmtier_gpu_ops")
+    for k, name in enumerate(slots):
+        assert table[k] == ctypes.cast(getattr(lib, name), ctypes.c_void_p).value, name
+
+
 def test_version_and_defaults():
     assert b"sm_100a" in uvmtier.lib().uvmtier_version()
     cfg = uvmtier.default_config()

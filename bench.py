@@ -504,6 +504,16 @@ def main():
     dom_is_k1 = k1_ms >= svc_ms
     dom_bytes, dom_ms = (k1_bytes, k1_ms) if dom_is_k1 else (svc_bytes, svc_ms)
     achieved = dom_bytes / (dom_ms * 1e-3) / 1e9
+    # DRAM bytes per launch from the committed ncu capture (dram__bytes_read.sum + dram__bytes_write.sum summed over
+    # the pass's kernels; uniform trace only -- other traces were not captured)
+    traffic, traffic_src = None, None
+    try:
+        tr = json.load(open(os.path.join(ROOT, "profiles", "ncu_traffic.json")))
+        if args.trace == "uniform":
+            traffic = tr["k_fault_fetch_preprocess_dram_bytes_per_launch" if dom_is_k1 else "service_pass_dram_bytes_per_launch"]
+            traffic_src = tr["source"]
+    except Exception:
+        pass
     line = {
         "metric": METRIC, "value": world * n / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
@@ -520,7 +530,8 @@ def main():
         "gpu_launches": int(launches),
         "clocks": clocks,
         "roofline": {"bound": "hbm", "kernel": "k_fault_fetch_preprocess" if dom_is_k1 else "service pass (k_service_count, k_service_alloc, k_service_fill, k_service_sort_lists/_big, k_service_blocks_grp, k_service_blocks, k_service_unmapped)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "traffic_unit": "bytes of DRAM traffic per launch (ncu)", "traffic_source": traffic_src,
                      "peak_source": peak_src, "algorithmic_bytes_per_launch": int(dom_bytes), "ms_per_launch": dom_ms,
                      "frac_of_nominal_8TBs": achieved / 8000.0},
         "kernels": {"k_fault_fetch_preprocess_ms": k1_ms, "k_fault_fetch_preprocess_GBs": k1_bytes / (k1_ms * 1e-3) / 1e9,

@@ -228,7 +228,10 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
     const uint4 *oraw = (const uint4 *)ordered, *graw = (const uint4 *)groups;
     for (uint32_t q = blockIdx.x * (kSvcThreads / 32) + warp; q < n_heavy; q += n_warps) {
         const uint32_t slot = heavy[1u + q];
-        const uint32_t cnt = cw[slot].x;
+        const uint2 cwv = cw[slot];
+        const uint32_t cnt = cwv.x;
+        // one run per lane pays only when runs are short; long runs are better served 32 entries at a time
+        const bool short_runs = cwv.y <= 4u * cwv.x;
         const uint32_t off = offset[slot];
         const size_t w = (size_t)slot * 16 + l;
         uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
@@ -238,15 +241,80 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
 
         // Three runs in flight (as in k_service_blocks_grp): run k+1's first 32 entries, run k+2's group and run
         // k+3's id are loaded while run k is worked on -- a hot va_block is one long chain of dependent steps.
-        uint32_t t0 = list[off];
-        uint32_t t1 = cnt > 1 ? list[off + 1] : t0;
-        uint32_t t2 = cnt > 2 ? list[off + 2] : t0;
-        uint4 g0 = graw[t0], g1 = graw[t1];
-        uint4 e0 = make_uint4(0, 0, 0, 0);
-        if ((uint32_t)lane < (g0.w & 0xffffu))
-            e0 = oraw[svc_batch_of(prm, t0) * prm.B + (g0.z >> 16) + lane];
+        uint32_t t0 = 0, t1 = 0, t2 = 0;
+        uint4 g0 = make_uint4(0, 0, 0, 0), g1 = g0, e0 = g0;
+        auto prime = [&](uint32_t at) {                                   // (re)fills the pipeline for run `at`
+            t0 = list[off + at];
+            t1 = at + 1 < cnt ? list[off + at + 1] : t0;
+            t2 = at + 2 < cnt ? list[off + at + 2] : t0;
+            g0 = graw[t0];
+            g1 = graw[t1];
+            e0 = make_uint4(0, 0, 0, 0);
+            if ((uint32_t)lane < (g0.w & 0xffffu))
+                e0 = oraw[svc_batch_of(prm, t0) * prm.B + (g0.z >> 16) + lane];
+        };
+        prime(0);
 
-        for (uint32_t k = 0; k < cnt; k++) {
+        // A run in which no entry needs service leaves the block's state as it was.  Once that happens (typically:
+        // the block is fully resident and mapped, and faults on it are stale), the next runs are independent of each
+        // other as long as they also need no service: they are evaluated 32 at a time, one run per lane, against the
+        // current masks; the runs before the first one that does need service are final, that one goes through the
+        // regular path below.  A hot va_block is otherwise one chain of thousands of dependent steps.
+        bool streak = false;
+        for (uint32_t k = 0; k < cnt;) {
+            if (short_runs && streak && cnt - k >= 2) {
+                const uint32_t m = min(32u, cnt - k);
+                const bool mine = (uint32_t)lane < m;
+                uint32_t ts = 0;
+                uint4 gs = make_uint4(0, 0, 0, 0);
+                if (mine) {
+                    ts = list[off + k + lane];
+                    gs = graw[ts];
+                }
+                const uint32_t bs = svc_batch_of(prm, ts), base_s = bs * prm.B, first_s = gs.z >> 16;
+                const uint32_t ns = mine ? (gs.w & 0xffffu) : 0u;
+                const uint32_t ns_max = __reduce_max_sync(HW_FULL, ns);
+                uint32_t state = 0, prev_page = 0xffffffffu, dsum = 0, isum = 0;
+                bool needs_service = false;
+                for (uint32_t i = 0; i < ns_max; i++) {
+                    const bool on = i < ns;
+                    uint4 e = make_uint4(0, 0, 0, 0);
+                    if (on)
+                        e = oraw[base_s + first_s + i];
+                    const uint32_t acc = (e.w >> 24) & 7u, num_instances = e.w & 0xffffu, access_type_mask = (e.w >> 16) & 0xffu;
+                    const uint32_t page = on ? (e.x - gs.x) >> 12 : 0u;
+                    const bool dup = on && i > 0 && page == prev_page;
+                    const int wl = (int)((page >> 5) & 15u);
+                    const uint32_t w0 = __shfl_sync(HW_FULL, pte0, wl), w1 = __shfl_sync(HW_FULL, pte1, wl), w2 = __shfl_sync(HW_FULL, pte2, wl);
+                    const uint32_t sh = page & 31u;
+                    const uint32_t auth = ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
+                    const svc_entry_eval ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, state, logical, auth);
+                    if (on) {
+                        entry_flags[base_s + first_s + i] = (uint16_t)ev.flags;   // rewritten later if the run is not final
+                        dsum += dup ? num_instances : num_instances - 1u;
+                        isum += ev.ip_add;
+                        needs_service |= ev.serviced;
+                        state = ev.state;
+                        prev_page = page;
+                    }
+                }
+                const uint32_t bad = __ballot_sync(HW_FULL, mine && needs_service);
+                const uint32_t adv = bad ? (uint32_t)__ffs((int)bad) - 1u : m;
+                if ((uint32_t)lane < adv) {
+                    if (dsum) atomicAdd(&batches[bs].num_duplicate_faults, dsum);
+                    if (isum) atomicAdd(&batches[bs].num_invalid_prefetch_faults, isum);
+                    uint4 *rec = (uint4 *)&service[ts];
+                    rec[0] = make_uint4(slot, 0u, 0u, 0u);
+                    rec[1] = make_uint4((uint32_t)UVMTIER_ID_INVALID << 16, 0u, bs << 16, ts - base_s);
+                    rec[2] = rec[3] = rec[4] = rec[5] = make_uint4(0u, 0u, 0u, 0u);
+                }
+                k += adv;
+                streak = adv == m;
+                if (k < cnt)
+                    prime(k);
+                if (streak || k >= cnt)
+                    continue;
+            }
             const uint32_t t3 = k + 3 < cnt ? list[off + k + 3] : t0;
             const uint4 g2 = graw[t2];
             uint4 e1 = make_uint4(0, 0, 0, 0);
@@ -386,6 +454,8 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
             t0 = t1; t1 = t2; t2 = t3;
             g0 = g1; g1 = g2;
             e0 = e1;
+            streak = page_faults == 0;
+            k++;
         }
         if (lane < 16) {
             st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;

@@ -215,3 +215,34 @@ def test_oracle_matches_the_reference_on_unmapped_addresses_fatal_types_and_read
     a, b = _ref_vs_oracle(pk, TG.gpu_params(128), tbl, lay, st0, "unmapped + fatal + read-only")
     assert int((a["flags"] & 4 != 0).sum()) > 100 and int((a["flags"] & 8 != 0).sum()) > 10
     assert int(a["batch"]["num_duplicate_faults"].sum()) > 100
+
+
+def test_runs_that_need_no_service_are_evaluated_32_at_a_time():
+    """Two va_blocks, almost fully resident and mapped, touched by ~150 batches: most runs need no service (the warp
+    kernel evaluates them one per lane, speculatively), a few hit one of the unmapped pages and must be applied in
+    order, in between."""
+    rng = np.random.default_rng(5)
+    n = 2400
+    tbl = TG.instance_ptr_table(1)
+    lay = dict(va_base=TG.VA_BASE, blocks_per_space=2, n_spaces=1)
+    page = rng.integers(0, 512, n)
+    blk = rng.integers(0, 2, n)
+    addr = (TG.VA_BASE + (blk.astype(np.uint64) << np.uint64(21)) + (page.astype(np.uint64) << np.uint64(12))).astype(np.uint64)
+    acc = rng.choice([TG.HW_VIRT_READ, TG.HW_VIRT_WRITE, TG.HW_VIRT_ATOMIC_STRONG, TG.HW_VIRT_PREFETCH], n)
+    pk = TG.encode_packets(np.full(n, tbl["instance_ptr"][0]), addr, acc, rng.integers(0, 8, n),
+                           [TG.T1_CLIENTS[i] for i in rng.integers(0, 8, n)], np.arange(n) + 1)
+    gp = TG.gpu_params(16)
+    st0 = S.HostBlockState(2)
+    full = np.ones((2, 512), bool)
+    holes = np.zeros((2, 512), bool)
+    holes[0, [7, 130, 131, 400]] = True
+    holes[1, 32:48] = True                                    # one 64 KB big page of block 1 still lives on the CXL node
+    st0.gpu_resident = T.masks_from_bool(full & ~holes)
+    st0.cpu_resident1 = T.masks_from_bool(holes)
+    for m in ("gpu_pte0", "gpu_pte1", "gpu_pte2"):
+        setattr(st0, m, T.masks_from_bool(full & ~holes))
+    for pf in ((1, 51, 1), (0, 51, 1)):                      # with the prefetcher off every hole needs its own service
+        _, want, got = _both(pk, gp, tbl, lay, st0, pf=pf, lanes=4, heavy_min=ALL_HEAVY)
+        S.assert_service_equal(want, got, 16, "speculative runs, prefetch %d" % pf[0])
+    rec = want["records"]
+    assert len(rec) > 250 and 8 <= int((rec["page_fault_count"] > 0).sum()) <= 40

@@ -403,7 +403,7 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
  * Limits (NV_ERR_INVALID_ARGUMENT beyond them, uvmtier_last_error() says which):
  *   n_spaces * blocks_per_space <= 65536 va_block slots (128 GB of VA),
  *   n_batches * max_batch_size  <= 262144 entries,  n_batches <= 4096.
- * The array is about 3.9 MB and every GPU that loads the library holds it until the process exits.
+ * The array is about 4.5 MB and every GPU that loads the library holds it until the process exits.
  * The first call on a GPU looks up the array's device address (with that GPU current); make that first call
  * before any stream capture is begun.  All calls on a GPU share the one array, which keeps the previous call's
  * contents: the function clears the parts that have to start at zero itself, but two calls whose GPU work

@@ -283,7 +283,7 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
 //
 // What: the pass above keeps its working space in a buffer it grows with cudaMalloc.  This variant keeps the same
 // working space in one fixed array that is part of the library image.  Every GPU that loads the library carries
-// the array (about 3.9 MB) until the process exits; the price of never allocating is a hard ceiling on the
+// the array (about 4.5 MB) until the process exits; the price of never allocating is a hard ceiling on the
 // problem size.
 constexpr uint32_t kNoAllocMaxSlots = 65536;        // va_block slots: 128 GB of VA
 constexpr uint32_t kNoAllocMaxEntries = 262144;     // n_batches * max_batch_size

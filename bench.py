@@ -459,10 +459,11 @@ def main():
         chk(lib.uvmtier_memset_device(h, P(d_flush), 0, ctypes.c_size_t(L2_FLUSH_BYTES)), "flush")
         ctx.synchronize()
         t0 = time.perf_counter()
-        chk(lib.uvmtier_memcpy_h2d_async(h, P(d_ring), P(hp_ring), ctypes.c_size_t(ring_host.nbytes)), "h2d ring")
-        chk(lib.uvmtier_fetch_preprocess_fault_batches_device(h, P(d_ring), ctypes.c_uint32(n + 1), ctypes.c_uint32(0),
-                                                              ctypes.c_uint32(n), ctypes.c_int(1), P(d_disp), P(d_ord),
-                                                              P(d_grp), P(d_bat), None, ctypes.byref(new_get)), "fetch_preprocess")
+        # the ring crosses PCIe from pinned host memory in 8 chunks; each chunk is preprocessed as soon as it is there
+        chk(lib.uvmtier_fetch_preprocess_fault_batches_streamed(h, P(hp_ring), P(d_ring), ctypes.c_uint32(n + 1), ctypes.c_uint32(0),
+                                                                ctypes.c_uint32(n), ctypes.c_int(1), ctypes.c_uint32(nb // 8),
+                                                                P(d_disp), P(d_ord), P(d_grp), P(d_bat), None,
+                                                                ctypes.byref(new_get)), "fetch_preprocess_streamed")
         chk(lib.uvmtier_service_fault_batches_device(h, ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout),
                                                      ctypes.byref(ds.ptrs), P(d_flags), P(d_svc), P(d_runs),
                                                      ctypes.c_uint32(RUN_CAP), P(d_cnt)), "service")

@@ -277,6 +277,22 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmt
                                                         uvmtier_fault_group_t *d_groups,
                                                         uvmtier_fault_batch_t *d_batches,
                                                         uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
+/* The same for a ring that lives in PINNED HOST memory (where the hardware writes it in the reference: the fault
+ * buffer is sysmem, UVM/uvm_gpu_replayable_faults.c:149-184), results stay on the device.  The packets of
+ * [get, put) are copied to the same positions of d_ring in chunks of chunk_batches batches on a second stream,
+ * and every chunk is preprocessed on the context's stream as soon as it has arrived: the copy of chunk c+1
+ * overlaps the kernels of chunk c.  chunk_batches = 0 picks one (at most UVMTIER_MAX_COPY_CHUNKS chunks per
+ * call).  The host ring is not modified: VALID bits are cleared in d_ring only (clear_valid), the host owner
+ * clears its own for [get, *out_get).  Enqueues only; uvmtier_synchronize waits. */
+#define UVMTIER_MAX_COPY_CHUNKS 64
+NV_STATUS uvmtier_fetch_preprocess_fault_batches_streamed(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_ring_pinned,
+                                                          uvmtier_fault_packet_t *d_ring, uint32_t ring_entries,
+                                                          uint32_t get, uint32_t put, int clear_valid,
+                                                          uint32_t chunk_batches, uint32_t *d_disposition,
+                                                          uvmtier_ordered_fault_t *d_ordered,
+                                                          uvmtier_fault_group_t *d_groups,
+                                                          uvmtier_fault_batch_t *d_batches,
+                                                          uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
 /* Host-buffer form of the above: h_ring is copied in, results are copied out (h_entries may be NULL).
  * The caller's ring is updated (cleared VALID bits) when clear_valid != 0. */
 NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *h_ring,

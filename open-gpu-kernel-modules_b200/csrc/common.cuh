@@ -41,6 +41,8 @@ struct uvmtier_ctx {
     void *h_stage;              // pinned
     size_t h_stage_bytes;
     cudaEvent_t events[UVMTIER_MAX_EVENTS];   // lazily created timing events
+    cudaStream_t copy_stream;                 // lazily created: host->device chunks of the streamed fetch entry point
+    cudaEvent_t copy_events[UVMTIER_MAX_COPY_CHUNKS + 1];
     struct uvmtier_fault_state *faults;   // lazily created by the fault entry points
     struct uvmtier_service_scratch svc;   // scratch of the servicing pass
     struct uvmtier_tiers *tiers;          // lazily created by the migration entry points

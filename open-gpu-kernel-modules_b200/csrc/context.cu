@@ -104,6 +104,13 @@ void uvmtier_deinit(uvmtier_ctx_t *ctx)
     for (int i = 0; i < UVMTIER_MAX_EVENTS; i++)
         if (ctx->events[i])
             cudaEventDestroy(ctx->events[i]);
+    for (int i = 0; i <= UVMTIER_MAX_COPY_CHUNKS; i++)
+        if (ctx->copy_events[i])
+            cudaEventDestroy(ctx->copy_events[i]);
+    if (ctx->copy_stream) {
+        cudaStreamSynchronize(ctx->copy_stream);
+        cudaStreamDestroy(ctx->copy_stream);
+    }
     if (ctx->d_stage)
         cudaFree(ctx->d_stage);
     if (ctx->h_stage)

@@ -150,6 +150,58 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmt
     return NV_OK;
 }
 
+NV_STATUS uvmtier_fetch_preprocess_fault_batches_streamed(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_ring,
+                                                          uvmtier_fault_packet_t *d_ring, uint32_t ring_entries, uint32_t get,
+                                                          uint32_t put, int clear_valid, uint32_t chunk_batches,
+                                                          uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
+                                                          uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                          uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get)
+{
+    if (!ctx || !h_ring || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    const uint32_t n = put >= get ? put - get : ring_entries - get + put;
+    if (out_get)
+        *out_get = put;
+    if (!n)
+        return NV_OK;
+    if (!d_disposition || !d_ordered || !d_groups || !d_batches)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t B = ctx->faults->gp.max_batch_size, n_batches = (n + B - 1) / B;
+    uint32_t per = chunk_batches ? chunk_batches : (n_batches + 7) / 8;
+    if ((n_batches + per - 1) / per > UVMTIER_MAX_COPY_CHUNKS)
+        per = (n_batches + UVMTIER_MAX_COPY_CHUNKS - 1) / UVMTIER_MAX_COPY_CHUNKS;
+    const uint32_t n_chunks = (n_batches + per - 1) / per;
+    if (!ctx->copy_stream)
+        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (uint32_t c = 0; c <= n_chunks; c++)
+        if (!ctx->copy_events[c])
+            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->copy_events[c], cudaEventDisableTiming));
+    // the copies may overwrite d_ring only after everything already queued on the context's stream (an earlier
+    // pass reading it) is done
+    UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[n_chunks], ctx->stream));
+    UVMTIER_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_events[n_chunks], 0));
+    for (uint32_t c = 0; c < n_chunks; c++) {
+        const uint32_t e0 = c * per * B, e1 = (c + 1) * per * B < n ? (c + 1) * per * B : n;       // entries, from `get`
+        const uint32_t first = (uint32_t)(((uint64_t)get + e0) % ring_entries), cnt = e1 - e0;
+        const uint32_t head = cnt < ring_entries - first ? cnt : ring_entries - first;          // up to the wrap (:975)
+        UVMTIER_CUDA(cudaMemcpyAsync(d_ring + first, h_ring + first, (size_t)head * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
+        if (head < cnt)
+            UVMTIER_CUDA(cudaMemcpyAsync(d_ring, h_ring, (size_t)(cnt - head) * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
+        UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[c], ctx->copy_stream));
+        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->copy_events[c], 0));
+        const uint32_t last = (uint32_t)(((uint64_t)get + e1) % ring_entries);
+        NV_STATUS st = uvmtier_fetch_preprocess_fault_batches_device(ctx, d_ring, ring_entries, first, last, clear_valid,
+                                                                     d_disposition + e0, d_ordered + e0, d_groups + e0,
+                                                                     d_batches + c * per, d_entries ? d_entries + e0 : NULL, NULL);
+        if (st != NV_OK)
+            return st;
+    }
+    return NV_OK;
+}
+
 NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fault_packet_t *h_ring, uint32_t ring_entries,
                                                  uint32_t get, uint32_t put, int clear_valid, uint32_t *h_disposition,
                                                  uvmtier_ordered_fault_t *h_ordered, uvmtier_fault_group_t *h_groups,

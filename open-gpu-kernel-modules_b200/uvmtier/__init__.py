@@ -201,6 +201,41 @@ class Context:
                "uvmtier_fetch_preprocess_fault_batches")
         return dict(disp=disp, ordered=ordered, groups=groups, batch=batch, entries=entries, get=new_get.value)
 
+    def fetch_preprocess_fault_batches_streamed(self, ring, get, put, clear_valid=True, chunk_batches=0):
+        """uvmtier_fetch_preprocess_fault_batches_streamed on a copy of `ring` in pinned host memory: the ring is
+        copied to the device chunk by chunk while earlier chunks are preprocessed.  Returns the same dict as
+        fetch_preprocess_fault_batches plus ring_device (the device ring after the call: VALID bits cleared)."""
+        from .layouts import BATCH_DT, FAULT_ENTRY_DT, GROUP_DT, ORDERED_DT
+        ring = np.ascontiguousarray(ring)
+        ring_entries = len(ring)
+        n = put - get if put >= get else ring_entries - get + put
+        B = self._fault_B
+        nb = (n + B - 1) // B
+        hp = ctypes.c_void_p()
+        _check(lib().uvmtier_mem_alloc_host_pinned(self._h, ctypes.c_size_t(ring.nbytes), ctypes.byref(hp)), "pinned")
+        ctypes.memmove(hp.value, ring.ctypes.data, ring.nbytes)
+        d_ring = self.alloc(ring.nbytes)
+        d_disp, d_ord, d_grp, d_bat = self.alloc(n * 4), self.alloc(n * 16), self.alloc(n * 16), self.alloc(nb * 32)
+        d_ent = self.alloc(n * FAULT_ENTRY_DT.itemsize)
+        try:
+            for p, nbytes, v in ((d_ring, ring.nbytes, 0), (d_ord, n * 16, 0xff), (d_grp, n * 16, 0xff),
+                                 (d_ent, n * FAULT_ENTRY_DT.itemsize, 0)):
+                _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(p), ctypes.c_int(v), ctypes.c_size_t(nbytes)), "memset")
+            new_get = ctypes.c_uint32(0)
+            _check(lib().uvmtier_fetch_preprocess_fault_batches_streamed(
+                self._h, hp, P(d_ring), ctypes.c_uint32(ring_entries), ctypes.c_uint32(get), ctypes.c_uint32(put),
+                ctypes.c_int(1 if clear_valid else 0), ctypes.c_uint32(chunk_batches), P(d_disp), P(d_ord), P(d_grp), P(d_bat),
+                P(d_ent), ctypes.byref(new_get)), "uvmtier_fetch_preprocess_fault_batches_streamed")
+            self.synchronize()
+            return dict(disp=self.from_device(d_disp, n, "<u4"), ordered=self.from_device(d_ord, n, ORDERED_DT),
+                        groups=self.from_device(d_grp, n, GROUP_DT), batch=self.from_device(d_bat, nb, BATCH_DT),
+                        entries=self.from_device(d_ent, n, FAULT_ENTRY_DT), get=new_get.value,
+                        ring_device=self.from_device(d_ring, ring.shape, ring.dtype))
+        finally:
+            for p in (d_ring, d_disp, d_ord, d_grp, d_bat, d_ent):
+                self.free(p)
+            lib().uvmtier_mem_free_host_pinned(self._h, hp)
+
     # ---- (1b) servicing ----
     def block_state_alloc(self, layout):
         """uvmtier_block_state_alloc -> DeviceBlockState (device pointers + upload/download helpers)."""

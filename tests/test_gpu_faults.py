@@ -123,3 +123,31 @@ def test_gpu_baseline_size_1m_entries(ctx):
         nxt_same_batch = valid[1:] & valid[:-1] & (pos[1:] != 0)
         ok = (k1[1:] > k1[:-1]) | ((k1[1:] == k1[:-1]) & (k2[1:] > k2[:-1]))
         assert ok[nxt_same_batch].all()
+
+
+@pytest.mark.parametrize("chunk_batches,get", [(0, 0), (3, 0), (1, 0), (7, 900)])
+def test_streamed_fetch_from_a_pinned_host_ring_equals_the_device_form(ctx, chunk_batches, get):
+    """uvmtier_fetch_preprocess_fault_batches_streamed: the ring stays in pinned host memory and crosses PCIe in
+    chunks while earlier chunks are preprocessed.  Same results as the host-buffer form, for chunks that do not
+    divide the trace, a single batch per chunk, and a ring segment that wraps."""
+    n, B = 5000, 64
+    pk, tbl, _ = TG.fault_trace(n, 17, "stream", 2)
+    gp = TG.gpu_params(B)
+    ctx.fault_buffer_init(gp, tbl)
+    ring_entries = n + 300
+    ring = np.zeros((ring_entries, 8), np.uint32)
+    idx = (get + np.arange(n)) % ring_entries
+    ring[idx] = pk
+    put = int((get + n) % ring_entries)
+    ring_a = ring.copy()
+    a = ctx.fetch_preprocess_fault_batches(ring_a, get, put)
+    b = ctx.fetch_preprocess_fault_batches_streamed(ring, get, put, chunk_batches=chunk_batches)
+    assert a["get"] == b["get"] == put
+    for k in ("disp", "batch", "entries"):
+        assert np.array_equal(a[k], b[k]), k
+    nb = len(a["batch"])
+    for bi in range(nb):                      # slots past num_coalesced / num_block_groups are unspecified
+        m, g = int(a["batch"]["num_coalesced_faults"][bi]), int(a["batch"]["num_block_groups"][bi])
+        assert np.array_equal(a["ordered"][bi * B:bi * B + m], b["ordered"][bi * B:bi * B + m])
+        assert np.array_equal(a["groups"][bi * B:bi * B + g], b["groups"][bi * B:bi * B + g])
+    assert np.array_equal(ring_a, b["ring_device"])          # VALID bits cleared on the device copy, host ring untouched

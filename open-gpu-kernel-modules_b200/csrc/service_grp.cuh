@@ -443,6 +443,9 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             // uvm_va_block_make_resident_finish :5042-5084 and the mapping step (:11019-11066, :12063-12080)
 #pragma unroll
             for (int w = 0; w < W; w++) {
+                // make_resident_copy first unmaps the pages that are not yet resident here (:4919-4926) ...
+                p0[w] &= ~todo[w]; p1[w] &= ~todo[w]; p2[w] &= ~todo[w];
+                // ... then residency moves and the faulting GPU is mapped
                 gres[w] |= newres[w];
                 c0[w] &= ~newres[w];
                 c1[w] &= ~newres[w];

@@ -419,6 +419,11 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 svc_emit_runs(from0, pf, slot, 0u, runs, run_off, prm.run_cap, lane);
                 svc_emit_runs(from1, pf, slot, 1u, runs, run_off + r0, prm.run_cap, lane);
                 svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, runs, run_off + r0 + r1, prm.run_cap, lane);
+                // make_resident_copy first unmaps the pages that are not yet resident here (:4919-4926)
+                {
+                    const uint32_t arriving = newres & ~gres;
+                    pte0 &= ~arriving; pte1 &= ~arriving; pte2 &= ~arriving;
+                }
                 // uvm_va_block_make_resident_finish :5042-5084
                 gres |= newres;
                 c0 &= ~newres;

@@ -72,13 +72,19 @@ if [ -f "$HERE/ref_service_glue.c" ]; then
     sed -n '181,188p;522,537p' "$UVM/uvm_hal_types.h" > "$TMP/x_prot.h"
     sed -n '46,62p' "$UVM/uvm_tools.h" > "$TMP/x_tools_reason.h"
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_service_glue.c" "$HERE/ref_faults_blackwell.c" \
-        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_prefetch.c" -o "$OUT/libref_service.so"
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        -o "$OUT/libref_service.so"
     echo "build_ref: built $OUT/libref_service.so"
 fi
 
-# ---------------- residency / migration leg ----------------
+# ---------------- residency leg: uvm_va_block_make_resident and its mask algebra, verbatim ----------------
 if [ -f "$HERE/ref_resident_glue.c" ]; then
     sed -n '36,80p' "$UVM/uvm_va_block_types.h" > "$TMP/x_va_block_types.h"
-    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" -o "$OUT/libref_resident.so"
+    sed -n '116,129p;149,159p;324,328p' "$UVM/uvm_va_block_types.h" > "$TMP/x_resident_types.h"
+    sed -n '197,242p' "$UVM/uvm_va_block_types.h" > "$TMP/x_make_resident_ctx.h"
+    sed -n '183,195p;584,593p;609,701p;721,734p;2406,2430p;3569,3577p;4379,4452p;4460,4536p;4538,4579p;4581,4619p;4625,4653p;4660,4847p;4877,4976p;4978,5114p' \
+        "$UVM/uvm_va_block.c" > "$TMP/x_resident.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        -o "$OUT/libref_resident.so"
     echo "build_ref: built $OUT/libref_resident.so"
 fi

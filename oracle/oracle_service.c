@@ -32,6 +32,9 @@ enum { PROT_NONE = 0, PROT_RO = 1, PROT_RW = 2, PROT_RWA = 3 };
 enum { REASON_INVALID_ADDRESS = 1, REASON_INVALID_PERMISSIONS = 2 };   /* UvmEventFatalReason, uvm_types.h:514-529 */
 enum { CANCEL_ALL = 0, CANCEL_WRITE_AND_ATOMIC = 1 };                  /* uvm_hal_types.h:262-271 */
 
+uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t *reqs, const uint64_t *page_masks,
+                              const uint64_t *prefetch_masks, uint32_t n_slots, const ref_block_state_t *st,
+                              ref_make_resident_result_t *results, ref_copy_run_t *runs, uint32_t run_cap);
 void oracle_prefetch_get_hint_va_block(size_t n, const ref_prefetch_block_t *blk, const uint64_t *resident,
                                        const uint64_t *faulted, const uint64_t *thrashing,
                                        const uint64_t *cpu_read_mapped, ref_prefetch_info_t *info,
@@ -84,7 +87,7 @@ void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_stat
                                 const uint64_t *new_residency, unsigned region_first, unsigned region_outer,
                                 ref_service_group_t *rec, ref_copy_run_t *runs, uint32_t *nrun_io, uint32_t run_cap)
 {
-    or_mask_t pf_mask, cpu0, cpu1, todo, from0, from1, touch, any_cpu, newres, gpu_res, pte[3];
+    or_mask_t pf_mask, cpu0, cpu1, any_cpu, newres, gpu_res, pte[3];
     ref_prefetch_block_t pb;
     uint32_t hint, nrun = *nrun_io;
     unsigned rf = region_first, ro = region_outer, p, i;
@@ -118,37 +121,23 @@ void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_stat
     rec->region_first = (uint16_t)rf; rec->region_outer = (uint16_t)ro;
     or_store(rec->new_residency, &newres);
 
-    /* make_resident_copy: block_copy_resident_pages :4660-4847, GPU destination, CPU nodes as sources */
-    or_andnot(&todo, &newres, &gpu_res);                 /* :4687-4690 */
-    or_and(&from0, &todo, &cpu0);                        /* node 0 first (for_each_possible_uvm_node) */
-    or_andnot(&todo, &todo, &from0);
-    or_and(&from1, &todo, &cpu1);
-    or_andnot(&touch, &todo, &from1);                    /* resident nowhere: populated + zeroed at the destination */
-    rec->migrated[0] = (uint16_t)or_weight(&from0);
-    rec->migrated[1] = (uint16_t)or_weight(&from1);
-    rec->first_touch = (uint16_t)or_weight(&touch);
+    /* uvm_va_block_make_resident(dest = the faulting GPU, region, page_mask = new_residency, prefetch mask, cause =
+     * REPLAYABLE_FAULT): the restatement in oracle_resident.c, which is compared with the reference's own
+     * uvm_va_block_make_resident (oracle/_ref/libref_resident.so).  Copy list, residency, eviction marks, unmapping. */
     {
-        uint32_t k = 0;
-        k += oracle_emit_runs(&from0, &pf_mask, slot, 0, 0, runs, nrun + k, run_cap);
-        k += oracle_emit_runs(&from1, &pf_mask, slot, 1, 0, runs, nrun + k, run_cap);
-        k += oracle_emit_runs(&touch, &pf_mask, slot, 7, 0, runs, nrun + k, run_cap);
-        rec->run_count = (uint16_t)k;
-        nrun += k;
-    }
-    /* make_resident_finish :5042-5084: dst |= migrated | first touch; everyone else loses the region's pages */
-    or_or(&gpu_res, &gpu_res, &newres);
-    or_andnot(&cpu0, &cpu0, &newres);
-    or_andnot(&cpu1, &cpu1, &newres);
-    mask_ptr_store(st->gpu_resident, slot, &gpu_res);
-    mask_ptr_store(st->cpu_resident[0], slot, &cpu0);
-    mask_ptr_store(st->cpu_resident[1], slot, &cpu1);
-    if (st->gpu_evicted) {
-        /* block_make_resident_update_state :5038-5039 -> block_make_resident_clear_evicted :4978-4988 */
-        or_mask_t evicted, migrated;
-        or_or(&migrated, &from0, &from1);
-        mask_ptr_load(&evicted, st->gpu_evicted, slot);
-        or_andnot(&evicted, &evicted, &migrated);
-        mask_ptr_store(st->gpu_evicted, slot, &evicted);
+        ref_make_resident_req_t rq;
+        ref_make_resident_result_t res;
+        memset(&rq, 0, sizeof(rq));
+        rq.slot = slot; rq.region_first = (uint16_t)rf; rq.region_outer = (uint16_t)ro; rq.dest_tier = 0; rq.cause = 0;
+        rq.flags = 1 | 2; rq.mask_row = 0;
+        oracle_make_resident(1, &rq, newres.w, pf_mask.w, 0xFFFFFFFFu, st, &res, runs ? runs + (nrun < run_cap ? nrun : run_cap) : NULL,
+                             nrun < run_cap ? run_cap - nrun : 0);
+        rec->migrated[0] = res.migrated[0];
+        rec->migrated[1] = res.migrated[1];
+        rec->first_touch = res.first_touch;
+        rec->run_count = res.run_count;
+        nrun += res.run_count;
+        for (i = 0; i < 3; i++) mask_ptr_load(&pte[i], st->gpu_pte[i], slot);      /* after the unmapping */
     }
 
     /* service_finish :12063-12302: map the faulting GPU.  compute_new_permission (:11019-11066): the page is now

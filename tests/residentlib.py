@@ -55,6 +55,19 @@ def run_oracle(orc, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
     return dict(results=res, runs=runs, n_runs=int(n_runs), state=st)
 
 
+def run_ref(ref, rq, page_masks, prefetch_masks, state, run_cap=1 << 18, gpu_id=1):
+    """oracle/_ref/libref_resident.so: the reference's own uvm_va_block_make_resident (verbatim) on the flat table."""
+    st = state.copy()
+    ptrs = st.ptrs()
+    res = np.zeros(len(rq), MAKE_RESIDENT_RESULT_DT)
+    runs = np.zeros(run_cap, COPY_RUN_DT)
+    fn = ref.ref_make_resident
+    fn.restype = ctypes.c_uint32
+    n_runs = fn(ctypes.c_uint32(len(rq)), P(rq), P(page_masks), P(prefetch_masks), ctypes.c_uint32(st.n), ctypes.c_uint32(gpu_id),
+                ctypes.byref(ptrs), P(res), P(runs), ctypes.c_uint32(run_cap))
+    return dict(results=res, runs=runs, n_runs=int(n_runs), state=st)
+
+
 def run_simt(sim, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
     st = state.copy()
     ptrs = st.ptrs()
@@ -89,6 +102,6 @@ def check_invariants(before, res):
     # nothing is lost: a page resident somewhere before is resident somewhere after
     assert not ((gb | c0b | c1b) & ~(g | c0 | c1)).any(), "a resident page vanished"
     p0 = bool_from_masks(st.gpu_pte0)
-    assert not (p0 & ~g).any(), "the GPU maps a page that is not resident on it"
+    assert not (p0 & gb & ~g).any(), "the GPU still maps a page that left it"
     ev = bool_from_masks(st.gpu_evicted)
     assert not (ev & g).any(), "an evicted page is GPU resident"

@@ -30,6 +30,10 @@ def random_state(n_slots, seed, gpu_id=1, populated=0.7, ro_frac=0.1, none_frac=
     rd = gres & (r < 0.8)
     wr = rd & (r < 0.5)
     at = wr & (r < 0.3)
+    # a few remote mappings: the GPU maps pages that live in CPU memory (make_resident unmaps them when they move)
+    remote = ((where == 1) | (where == 2)) & (rng.random((n_slots, 512)) < 0.02)
+    rd |= remote
+    wr |= remote & (r < 0.5)
     st.gpu_pte0, st.gpu_pte1, st.gpu_pte2 = masks_from_bool(rd), masks_from_bool(wr), masks_from_bool(at)
     u = rng.random(n_slots)
     st.logical_prot = np.where(u < none_frac, 0, np.where(u < none_frac + ro_frac, 1, 3)).astype("u1")

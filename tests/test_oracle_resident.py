@@ -101,3 +101,22 @@ def test_promote_evict_round_trip_restores_residency_on_one_tier():
     assert T.bool_from_masks(b["state"].cpu_resident0).all() and not b["state"].gpu_resident.any()
     assert T.bool_from_masks(b["state"].gpu_evicted).all() and not b["state"].gpu_pte0.any()
     assert int(b["results"]["migrated"][:, 2].sum()) == n_slots * 512 and b["n_runs"] == n_slots
+
+
+# ------------------------------------------------------------------------------------------------
+# The CPU restatement against the reference's own uvm_va_block_make_resident (compiled verbatim into
+# oracle/_ref/libref_resident.so).
+@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5])
+def test_oracle_matches_the_reference_make_resident(seed):
+    ref = T.load_ref("resident")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_resident.so not built (needs /root/reference)")
+    n_slots = 128
+    st0 = _state(n_slots, seed)
+    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3)
+    want = R.run_ref(ref, rq, pm, pf, st0)
+    got = R.run_oracle(T.load_oracle(), rq, pm, pf, st0)
+    R.assert_equal(want, got, "reference vs restatement, seed %d" % seed)
+    res = want["results"]
+    assert int(res["migrated"][:, 0].sum()) > 500 and int(res["migrated"][:, 1].sum()) > 200 and int(res["migrated"][:, 2].sum()) > 300
+    assert int(res["first_touch"].sum()) > 100 and int(res["unmapped"].sum()) > 50

@@ -12,8 +12,15 @@
  * oracle_service.c: no read duplication (residency is exclusive), CPU destination pages are allocated on the node
  * the request names (block_populate_pages_cpu's first choice), the GPU can copy from the CPU directly (no staging).
  *
- * Pinning: PARITY UNPINNED.  The reference holds no vectors for make_resident masks and these functions
- * have not been compiled against the shims; every step below cites the lines it restates.
+ * Pinning: the reference holds no vectors for make_resident masks, so this file is checked against the
+ * reference's own code: oracle/ref_resident_glue.c compiles uvm_va_block_make_resident, _copy, _finish,
+ * block_copy_resident_pages{,_mask,_from}, block_make_resident_update_state, block_copy_set_first_touch_residency,
+ * break_read_duplication_in_region and block_make_resident_clear_evicted VERBATIM from uvm_va_block.c against the
+ * shims (oracle/_ref/libref_resident.so; page allocation, PTE writes and the copy push are stand-ins that record
+ * masks), and tests/test_oracle_resident.py::test_oracle_matches_the_reference_make_resident requires identical
+ * results, copy runs and block state on random requests.  M6 (flag 4) builds the request the way
+ * uvm_va_block_evict_chunks does (:13080-13110) and then runs the pinned make_resident; the chunk walk above it is
+ * out of scope.
  */
 #include "oracle_common.h"
 #include "ref_api.h"

@@ -19,9 +19,11 @@
  * fault_entry_duplicate_flags, mark_fault_* and service_fault_batch_fatal_notify compiled verbatim
  * (oracle/_ref/libref_service.so, ref_service_glue.c; tests/test_oracle_service.py -k reference) -- which found
  * and fixed one divergence (duplicates of faults outside every va_range are counted too, :1692).  The BACK HALF
- * (oracle_service_block_apply: prefetch hint = the KAT-pinned oracle_prefetch.c; make_resident algebra, copy
- * list, mapping) stays PARITY UNPINNED: its callees live in uvm_va_block.c (13 k lines) and have not been compiled
- * against the shims.
+ * (oracle_service_block_apply) is three steps: the prefetch hint = oracle_prefetch.c, pinned by the reference's
+ * known-answer vectors and by libref_prefetch.so; residency = oracle_make_resident, pinned by the reference's
+ * uvm_va_block_make_resident compiled verbatim (libref_resident.so, see oracle_resident.c); and the mapping of the
+ * serviced pages on the faulting GPU (uvm_va_block.c:11019-11066, 12063-12080), which is the one step that is a
+ * restatement only: its callees (block_map_gpu_to, PTE batches) write page tables and are out of scope.
  * Batches are applied in trace order, exactly like uvm_parent_gpu_service_replayable_faults (:2906-2960).
  */
 #include "oracle_common.h"

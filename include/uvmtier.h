@@ -324,7 +324,14 @@ typedef struct {
  *   preferred_location policy->preferred_location (UVMTIER_ID_INVALID = none)
  *   gpu_evicted       gpu_state->evicted: pages an eviction moved off this GPU and that have not come back
  *                     (UVM/uvm_va_block.h:161-164, set :5023-5037, cleared :4978-4988).  May be NULL when the
- *                     caller never evicts (the servicing pass then skips it). */
+ *                     caller never evicts (the servicing pass then skips it).
+ *   read_duplicated   va_block->read_duplicated_pages (UVM/uvm_va_block.h:436-441): pages with a copy on more than
+ *                     one processor, made by UVMTIER_MR_READ_DUPLICATE requests (:5164-5332) and broken again by
+ *                     every other make_resident, the servicing pass included (:4538-4579).  NULL = read
+ *                     duplication is off for the table (the reference's default policy): uvmtier_block_state_alloc
+ *                     leaves it NULL, uvmtier_block_state_enable_read_duplication adds it.  Invariant the library
+ *                     keeps and expects of tables it is handed: a read_duplicated page has a CPU copy (true of
+ *                     every page the reference marks in a block with one GPU, :5279-5310). */
 typedef struct {
     uvmtier_page_mask_t *gpu_resident;
     uvmtier_page_mask_t *cpu_resident[2];
@@ -333,6 +340,7 @@ typedef struct {
     uint8_t *logical_prot;
     uint16_t *preferred_location;
     uvmtier_page_mask_t *gpu_evicted;
+    uvmtier_page_mask_t *read_duplicated;
 } uvmtier_block_state_t;
 
 #define UVMTIER_SF_SERVICED         0x0001u /* page added to new_residency (:1560-1579) */
@@ -384,6 +392,9 @@ typedef struct {
  * {UVMTIER_ID_INVALID, 0}) / frees the state table of n_spaces * blocks_per_space slots. */
 NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uvmtier_block_state_t *out);
 NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *state);
+/* Adds a zeroed read_duplicated mask array to a table made by uvmtier_block_state_alloc (freed with it). */
+NV_STATUS uvmtier_block_state_enable_read_duplication(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout,
+                                                      uvmtier_block_state_t *state);
 
 /* service_fault_batch (:2232-2377) for ALL batches of a preprocess call: every va_block run is serviced
  * like service_fault_batch_block_locked (:1375-1597) -> uvm_va_block_service_locked
@@ -452,6 +463,12 @@ NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint3
 #define UVMTIER_MR_HAS_PREFETCH_MASK 0x2u  /* prefetch_page_mask = d_prefetch_masks[mask_row] (fault causes only) */
 #define UVMTIER_MR_EVICT_GPU_PAGES   0x4u  /* page_mask = the block's gpu_resident pages in the region: what
                                               uvm_va_block_evict_chunks builds for a 2 MB root chunk (:13055-13080) */
+#define UVMTIER_MR_READ_DUPLICATE    0x8u  /* uvm_va_block_make_resident_read_duplicate (:5164-5332): COPY instead
+                                              of MOVE -- the sources keep their pages, write access to them is
+                                              revoked, read_duplicated |= pages_migrated; a CPU destination on
+                                              another NUMA node switches node instead (one CPU page table).  Needs
+                                              state->read_duplicated; not with cause EVICTION or _EVICT_GPU_PAGES
+                                              (the reference asserts), such requests are rejected. */
 
 /* One uvm_va_block_make_resident call (UVM/uvm_va_block.h:770-777): move the pages of `region` (and page_mask)
  * to dest_tier.  dest_tier = UVMTIER_TIER_HBM is dest_id = this GPU; UVMTIER_TIER_DRAM / _CXL is dest_id = CPU

@@ -45,6 +45,7 @@ extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n
     bs.logical_prot = state->logical_prot;
     bs.preferred_location = state->preferred_location;
     bs.gpu_evicted = (uint32_t *)state->gpu_evicted;
+    bs.read_duplicated = (uint32_t *)state->read_duplicated;
 
     const size_t warps_per_cta = kResThreads / 32;
     size_t grid = ((size_t)n_requests + warps_per_cta - 1) / warps_per_cta, cap = (size_t)ctx->sm_count * 16;

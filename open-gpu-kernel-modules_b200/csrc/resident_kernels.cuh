@@ -4,13 +4,15 @@
 // Reference (UVM = kernel-open/nvidia-uvm, uvm_va_block.c): uvm_va_block_make_resident (:5086-5114) =
 // _copy (:4877-4976: unmap, populate, block_copy_resident_pages :4660-4847) + _finish (:5042-5084:
 // block_make_resident_update_state :4990-5040, block_copy_set_first_touch_residency :4581-4619,
-// break_read_duplication_in_region :4538-4579).  Callers: uvm_va_block_migrate_locked (uvm_migrate.c:225-289),
+// break_read_duplication_in_region :4538-4579); with UVMTIER_MR_READ_DUPLICATE the COPY variant
+// uvm_va_block_make_resident_read_duplicate (:5164-5332, block_prep_read_duplicate_mapping :5120-5162).  Callers: uvm_va_block_migrate_locked (uvm_migrate.c:225-289),
 // uvm_va_block_evict_chunks (:12999-13130, cause EVICTION, page_mask = chunk pages & gpu resident), the CPU fault
 // handler, and the GPU fault path (which this library runs inside the servicing pass instead).
 //
-// Processors of the table: this GPU, and the CPU with two NUMA nodes (0 = host DRAM, 1 = CXL).  Residency is
-// exclusive (no read duplication in the harness), CPU pages are allocated on the node the request names
-// (block_populate_pages_cpu's first choice, :1887-2018), so every page of a request has at most one source.
+// Processors of the table: this GPU, and the CPU with two NUMA nodes (0 = host DRAM, 1 = CXL).  CPU pages are
+// allocated on the node the request names (block_populate_pages_cpu's first choice, :1887-2018).  A page lives on
+// one CPU node at most; it can be on the CPU and on the GPU only while read-duplicated, and is then copied from
+// the closest holder (block_copy_resident_pages_mask :4486-4497).
 // Masks: one 32-bit word per lane, lanes 16-31 mirror lanes 0-15 (mask512.cuh helpers are half-warp wide).
 #pragma once
 
@@ -37,8 +39,11 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
         uint32_t *res = (uint32_t *)&results[q];
         const uint32_t slot = rq.slot;
         const bool dst_gpu = rq.dest_tier == UVMTIER_TIER_HBM;
+        const bool rdup = (rq.flags & UVMTIER_MR_READ_DUPLICATE) != 0;
         const bool valid = slot < prm.n_slots && rq.region_first <= rq.region_outer && rq.region_outer <= 512u &&
-                           (dst_gpu || rq.dest_tier == UVMTIER_TIER_DRAM || rq.dest_tier == UVMTIER_TIER_CXL);
+                           (dst_gpu || rq.dest_tier == UVMTIER_TIER_DRAM || rq.dest_tier == UVMTIER_TIER_CXL) &&
+                           !(rdup && (!st.read_duplicated || rq.cause == UVMTIER_CAUSE_EVICTION ||
+                                      (rq.flags & UVMTIER_MR_EVICT_GPU_PAGES)));   // :5304 asserts cause != EVICTION
         if (!valid) {                                                     // uniform across the warp
             if (lane < 16) {
                 if (l < 8) res[l] = l == 0 ? 0xffffffffu : 0u;            // slot 0xFFFFFFFF marks a rejected request
@@ -51,6 +56,7 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
         uint32_t gres = st.gpu_resident[w], c0 = st.cpu_resident[0][w], c1 = st.cpu_resident[1][w];
         uint32_t pte0 = st.gpu_pte[0][w], pte1 = st.gpu_pte[1][w], pte2 = st.gpu_pte[2][w];
         uint32_t evicted = st.gpu_evicted ? st.gpu_evicted[w] : 0u;
+        uint32_t rd = st.read_duplicated ? st.read_duplicated[w] : 0u;
 
         // page_mask restricted to the region; NULL page_mask = the whole region
         uint32_t pm = hw_range((int)rq.region_first, (int)rq.region_outer, l);
@@ -96,26 +102,51 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
         svc_emit_runs(from[order1], pf, slot, (uint32_t)order1, runs, run_off + r0, prm.run_cap, lane, dst_code);
         svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, runs, run_off + r0 + r1, prm.run_cap, lane, dst_code);
 
-        // make_resident_copy unmaps every processor from the pages that are not resident on the destination
-        // (:4919-4926); the only mapper in the table is this GPU
-        const uint32_t unmap = copy & pte0;
-        pte0 &= ~copy; pte1 &= ~copy; pte2 &= ~copy;
-
-        // _finish: the destination becomes resident (update_state + first touch), everybody else loses the pages
-        // of page_mask (break_read_duplication_in_region clears all of region & page_mask, not only what moved)
         const uint32_t now = migrated | touch;
-        if (dst_gpu) {
-            gres |= now;
-            c0 &= ~pm;
-            c1 &= ~pm;
-            evicted &= ~migrated;                                         // block_make_resident_clear_evicted :4978-4988
+        uint32_t unmap, changed;
+        if (rdup) {
+            // pages entering read duplication (:5222-5243, block_prep_read_duplicate_mapping): everybody but the holder
+            // is unmapped and the holder loses write access.  The only mapper in the table is this GPU: it loses its
+            // mappings of such CPU pages and WRITE / ATOMIC on such pages of its own.
+            const uint32_t fresh = pm & ~rd, on_cpu = fresh & (c0 | c1), on_gpu = fresh & gres;
+            unmap = on_cpu & pte0;
+            pte0 &= ~on_cpu; pte1 &= ~(on_cpu | on_gpu); pte2 &= ~(on_cpu | on_gpu);
+            // :5259-5307: the destination gains first touch + migrated, the sources keep theirs -- except the other
+            // CPU node (one CPU page table: those pages switch node) -- and what migrated is read-duplicated
+            if (dst_gpu) {
+                gres |= now;
+                evicted &= ~migrated;
+            }
+            else if (nid) { c1 |= now; c0 &= ~migrated; }
+            else          { c0 |= now; c1 &= ~migrated; }
+            rd |= migrated;
+            changed = touch;                                              // only first touch reports (:4614-4617)
         }
         else {
-            if (nid) { c1 |= now; c0 &= ~pm; }
-            else     { c0 |= now; c1 &= ~pm; }
-            gres &= ~pm;
-            if (rq.cause == UVMTIER_CAUSE_EVICTION)
-                evicted |= from[2];                                       // :5023-5037: the GPUs the pages came from
+            // make_resident_copy unmaps every processor from the pages that are not resident on the destination
+            // (:4919-4926) and every processor but the destination from the read-duplicated pages (:4931-4939); the
+            // only mapper in the table is this GPU
+            const uint32_t gone = copy | (dst_gpu ? 0u : (pm & rd));
+            unmap = gone & pte0;
+            pte0 &= ~gone; pte1 &= ~gone; pte2 &= ~gone;
+            // _finish: the destination becomes resident (update_state + first touch), everybody else loses the pages
+            // of page_mask (break_read_duplication_in_region clears all of region & page_mask, not only what moved)
+            rd &= ~pm;
+            if (dst_gpu) {
+                gres |= now;
+                c0 &= ~pm;
+                c1 &= ~pm;
+                evicted &= ~migrated;                                     // block_make_resident_clear_evicted :4978-4988
+            }
+            else {
+                if (nid) { c1 |= now; c0 &= ~pm; }
+                else     { c0 |= now; c1 &= ~pm; }
+                gres &= ~pm;
+                // :5023-5037: every GPU that was a source gets ALL the migrated pages marked (copy_mask)
+                if (rq.cause == UVMTIER_CAUSE_EVICTION && hw_any(from[2], lane))
+                    evicted |= migrated;
+            }
+            changed = now;                                                // pages_changed_residency (:5005-5008, :4614-4617)
         }
 
         const uint32_t n0 = hw_weight(from[0]), n1 = hw_weight(from[1]), n2 = hw_weight(from[2]);
@@ -125,6 +156,8 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
             st.gpu_pte[0][w] = pte0; st.gpu_pte[1][w] = pte1; st.gpu_pte[2][w] = pte2;
             if (st.gpu_evicted)
                 st.gpu_evicted[w] = evicted;
+            if (st.read_duplicated)
+                st.read_duplicated[w] = rd;
             // result: 8 header words, then pages_migrated and pages_changed_residency
             if (l < 8) {
                 uint32_t v = 0;
@@ -136,7 +169,7 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
                 res[l] = v;
             }
             res[8 + l] = migrated;                                        // make_resident.pages_migrated
-            res[24 + l] = now;                                            // pages_changed_residency (:5005-5008, :4614-4617)
+            res[24 + l] = changed;
         }
     }
 }

@@ -112,6 +112,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     bs.logical_prot = state->logical_prot;
     bs.preferred_location = state->preferred_location;
     bs.gpu_evicted = (uint32_t *)state->gpu_evicted;
+    bs.read_duplicated = (uint32_t *)state->read_duplicated;
 
     // The working space still holds the previous call's numbers.  The packed per-slot counters, the list cursor,
     // the two work lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset:
@@ -237,7 +238,28 @@ NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *st
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     if (state->gpu_resident)
         UVMTIER_CUDA(cudaFree(state->gpu_resident));
+    if (state->read_duplicated)
+        UVMTIER_CUDA(cudaFree(state->read_duplicated));
     memset(state, 0, sizeof(*state));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_block_state_enable_read_duplication(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *lay,
+                                                      uvmtier_block_state_t *state)
+{
+    if (!ctx || !lay || !state || !state->gpu_resident || !lay->n_spaces || !lay->blocks_per_space)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (state->read_duplicated)
+        return NV_OK;
+    const size_t n = (size_t)lay->n_spaces * lay->blocks_per_space;
+    if (n > kMaxSlots)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    void *p = NULL;
+    UVMTIER_CUDA(cudaMalloc(&p, n * 64));
+    UVMTIER_CUDA(cudaMemsetAsync(p, 0, n * 64, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    state->read_duplicated = (uvmtier_page_mask_t *)p;
     return NV_OK;
 }
 

@@ -551,6 +551,15 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             for (int w = 0; w < W; w++) ev[w] &= ~gres[w];
             st_words<W>(st.gpu_evicted + wbase, ev);
         }
+        if (st.read_duplicated) {
+            // break_read_duplication_in_region (:4538-4579): the pages handed to make_resident are the ones that lost
+            // their CPU copy; a read-duplicated page of a one-GPU block always has one (:5279-5310)
+            uint32_t rd[W];
+            ld_words<W>(st.read_duplicated + wbase, rd);
+#pragma unroll
+            for (int w = 0; w < W; w++) rd[w] &= c0[w] | c1[w];
+            st_words<W>(st.read_duplicated + wbase, rd);
+        }
         if (gl == 0)
             st.prefetch_info[slot] = pi;
     }

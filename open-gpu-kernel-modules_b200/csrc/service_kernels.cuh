@@ -64,6 +64,7 @@ struct block_state_ptrs {
     uint8_t *logical_prot;
     uint16_t *preferred_location;
     uint32_t *gpu_evicted;                     // may be NULL
+    uint32_t *read_duplicated;                 // NULL = read duplication is off for the table
 };
 
 // uvm_fault_access_type_to_prot, UVM/uvm_hal_types.h:522-537
@@ -469,6 +470,11 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
             // uvm_va_block.c:4978-4988): evicted pages are never GPU resident, so whatever is resident now came back
             if (st.gpu_evicted)
                 st.gpu_evicted[w] &= ~gres;
+            // break_read_duplication_in_region (:4538-4579) clears read_duplicated for every page handed to
+            // make_resident; those are exactly the pages that lost their CPU copy (a read-duplicated page of a
+            // one-GPU block always has one, :5279-5310), so what still has a CPU copy stays duplicated
+            if (st.read_duplicated)
+                st.read_duplicated[w] &= c0 | c1;
             if (l == 0)
                 st.prefetch_info[slot] = pi;
         }

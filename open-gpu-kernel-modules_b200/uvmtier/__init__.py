@@ -366,15 +366,25 @@ class DeviceBlockState:
         self.ptrs = BlockStatePtrs()
         _check(lib().uvmtier_block_state_alloc(ctx.handle, P(layout), ctypes.byref(self.ptrs)), "uvmtier_block_state_alloc")
 
+    def enable_read_duplication(self):
+        """uvmtier_block_state_enable_read_duplication: adds the (zeroed) read_duplicated mask array."""
+        if not self.ptrs.read_duplicated:
+            _check(lib().uvmtier_block_state_enable_read_duplication(self.ctx.handle, P(self.layout), ctypes.byref(self.ptrs)),
+                   "uvmtier_block_state_enable_read_duplication")
+        return self
+
     def _fields(self):
         p = self.ptrs
-        return (("gpu_resident", p.gpu_resident), ("cpu_resident0", p.cpu_resident[0]), ("cpu_resident1", p.cpu_resident[1]),
-                ("gpu_pte0", p.gpu_pte[0]), ("gpu_pte1", p.gpu_pte[1]), ("gpu_pte2", p.gpu_pte[2]),
-                ("prefetch_info", p.prefetch_info), ("logical_prot", p.logical_prot), ("preferred_location", p.preferred_location),
-                ("gpu_evicted", p.gpu_evicted))
+        f = (("gpu_resident", p.gpu_resident), ("cpu_resident0", p.cpu_resident[0]), ("cpu_resident1", p.cpu_resident[1]),
+             ("gpu_pte0", p.gpu_pte[0]), ("gpu_pte1", p.gpu_pte[1]), ("gpu_pte2", p.gpu_pte[2]),
+             ("prefetch_info", p.prefetch_info), ("logical_prot", p.logical_prot), ("preferred_location", p.preferred_location),
+             ("gpu_evicted", p.gpu_evicted))
+        return f + ((("read_duplicated", p.read_duplicated),) if p.read_duplicated else ())
 
     def upload(self, host_state):
         assert host_state.n == self.n
+        if host_state.read_duplicated is not None:
+            self.enable_read_duplication()
         for name, dptr in self._fields():
             a = np.ascontiguousarray(getattr(host_state, name))
             _check(lib().uvmtier_memcpy_h2d(self.ctx.handle, ctypes.c_void_p(dptr), P(a), ctypes.c_size_t(a.nbytes)), "h2d")
@@ -382,6 +392,8 @@ class DeviceBlockState:
     def download(self):
         from .blockstate import HostBlockState
         h = HostBlockState(self.n)
+        if self.ptrs.read_duplicated:
+            h.enable_read_duplication()
         for name, dptr in self._fields():
             a = getattr(h, name)
             _check(lib().uvmtier_memcpy_d2h(self.ctx.handle, P(a), ctypes.c_void_p(dptr), ctypes.c_size_t(a.nbytes)), "d2h")

@@ -20,18 +20,18 @@ MAKE_RESIDENT_RESULT_DT = np.dtype([("slot", "<u4"), ("migrated", "<u2", (3,)), 
                                     ("run_count", "<u2"), ("unmapped", "<u2"), ("reserved", "<u4", (3,)),
                                     ("pages_migrated", "<u8", (8,)), ("pages_changed_residency", "<u8", (8,))])
 assert (MAKE_RESIDENT_REQ_DT.itemsize, MAKE_RESIDENT_RESULT_DT.itemsize) == (16, 160)
-MR_HAS_PAGE_MASK, MR_HAS_PREFETCH_MASK, MR_EVICT_GPU_PAGES = 1, 2, 4
+MR_HAS_PAGE_MASK, MR_HAS_PREFETCH_MASK, MR_EVICT_GPU_PAGES, MR_READ_DUPLICATE = 1, 2, 4, 8
 CAUSE_REPLAYABLE_FAULT, CAUSE_EVICTION, CAUSE_API_MIGRATE = 0, 4, 6
 TIER_HBM, TIER_DRAM, TIER_CXL = 0, 1, 2
 
 STATE_FIELDS = ("gpu_resident", "cpu_resident0", "cpu_resident1", "gpu_pte0", "gpu_pte1", "gpu_pte2", "prefetch_info",
-                "logical_prot", "preferred_location", "gpu_evicted")
+                "logical_prot", "preferred_location", "gpu_evicted", "read_duplicated")
 
 
 class BlockStatePtrs(ctypes.Structure):
     _fields_ = [("gpu_resident", ctypes.c_void_p), ("cpu_resident", ctypes.c_void_p * 2), ("gpu_pte", ctypes.c_void_p * 3),
                 ("prefetch_info", ctypes.c_void_p), ("logical_prot", ctypes.c_void_p), ("preferred_location", ctypes.c_void_p),
-                ("gpu_evicted", ctypes.c_void_p)]
+                ("gpu_evicted", ctypes.c_void_p), ("read_duplicated", ctypes.c_void_p)]
 
 
 class HostBlockState:
@@ -43,15 +43,22 @@ class HostBlockState:
         self.gpu_resident, self.cpu_resident0, self.cpu_resident1 = z(), z(), z()
         self.gpu_pte0, self.gpu_pte1, self.gpu_pte2 = z(), z(), z()
         self.gpu_evicted = z()
+        self.read_duplicated = None                      # read duplication is off until enable_read_duplication()
         self.prefetch_info = np.zeros(n_slots, PREFETCH_INFO_DT)
         self.prefetch_info["last_migration_proc_id"] = 257
         self.logical_prot = np.full(n_slots, 3, "u1")
         self.preferred_location = np.full(n_slots, 257, "<u2")
 
+    def enable_read_duplication(self):
+        if self.read_duplicated is None:
+            self.read_duplicated = np.zeros((self.n, 8), "<u8")
+        return self
+
     def copy(self):
         c = HostBlockState(self.n)
         for f in STATE_FIELDS:
-            setattr(c, f, getattr(self, f).copy())
+            v = getattr(self, f)
+            setattr(c, f, None if v is None else v.copy())
         return c
 
     def ptrs(self):
@@ -66,11 +73,15 @@ class HostBlockState:
         s.logical_prot = self.logical_prot.ctypes.data
         s.preferred_location = self.preferred_location.ctypes.data
         s.gpu_evicted = self.gpu_evicted.ctypes.data
+        s.read_duplicated = None if self.read_duplicated is None else self.read_duplicated.ctypes.data
         return s
 
     def assert_equal(self, other, what=""):
         for f in STATE_FIELDS:
             a, b = getattr(self, f), getattr(other, f)
+            if a is None or b is None:
+                assert a is None and b is None, "%s state.%s present on one side only" % (what, f)
+                continue
             if not np.array_equal(a, b):
                 bad = np.nonzero((a != b).reshape(self.n, -1).any(axis=1))[0] if a.dtype.names is None else np.nonzero(a != b)[0]
                 raise AssertionError("%s state.%s differs at slots %s" % (what, f, bad[:8]))

@@ -7,10 +7,13 @@
  *   M4  block_make_resident_update_state :4990-5040, block_copy_set_first_touch_residency :4581-4619,
  *       break_read_duplication_in_region :4538-4579, block_make_resident_clear_evicted :4978-4988
  *   M6  uvm_va_block_evict_chunks :12999-13130 (request flag 4: page_mask = gpu resident pages, cause EVICTION)
+ *   M1r uvm_va_block_make_resident_read_duplicate :5164-5332, block_prep_read_duplicate_mapping :5120-5162
+ *       (request flag 8; state table with a read_duplicated mask)
  *
  * Processors of the table: one GPU and the CPU with two NUMA nodes (0 = DRAM, 1 = CXL).  Harness policy as in
- * oracle_service.c: no read duplication (residency is exclusive), CPU destination pages are allocated on the node
- * the request names (block_populate_pages_cpu's first choice), the GPU can copy from the CPU directly (no staging).
+ * oracle_service.c: residency is exclusive unless the caller read-duplicates, CPU destination pages are allocated
+ * on the node the request names (block_populate_pages_cpu's first choice), the GPU can copy from the CPU directly
+ * (no staging).
  *
  * Pinning: the reference holds no vectors for make_resident masks, so this file is checked against the
  * reference's own code: oracle/ref_resident_glue.c compiles uvm_va_block_make_resident, _copy, _finish,
@@ -42,12 +45,14 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         const uint32_t slot = rq->slot;
         const bool dst_gpu = rq->dest_tier == 0;
         const int nid = rq->dest_tier == 2 ? 1 : 0;                  /* make_resident.dest_nid */
-        or_mask_t gpu, cpu[2], pte[3], evicted, pm, pf, copy, from[3], migrated, touch, now, unmap, *dst_res;
+        const bool rdup = (rq->flags & 8) != 0;                      /* uvm_va_block_make_resident_read_duplicate */
+        or_mask_t gpu, cpu[2], pte[3], evicted, rd, pm, pf, copy, from[3], migrated, touch, now, unmap, *dst_res;
         int i, order[2];
-        uint32_t k = 0;
+        uint32_t k = 0, n_unmapped = 0;
 
         memset(res, 0, sizeof(*res));
-        if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > OR_PAGES || rq->dest_tier > 2) {
+        if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > OR_PAGES || rq->dest_tier > 2 ||
+            (rdup && (!st->read_duplicated || rq->cause == 4 || (rq->flags & 4)))) {    /* :5304 asserts !EVICTION */
             res->slot = 0xFFFFFFFFu;
             continue;
         }
@@ -59,6 +64,8 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         for (i = 0; i < 3; i++) or_load(&pte[i], st->gpu_pte[i] + 8 * (size_t)slot);
         or_zero(&evicted);
         if (st->gpu_evicted) or_load(&evicted, st->gpu_evicted + 8 * (size_t)slot);
+        or_zero(&rd);
+        if (st->read_duplicated) or_load(&rd, st->read_duplicated + 8 * (size_t)slot);
 
         /* page_mask clipped to the region (uvm_page_mask_region_clear_outside); NULL = whole region */
         or_zero(&pm);
@@ -74,8 +81,39 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         if (rq->flags & 2)
             or_load(&pf, prefetch_masks + 8 * (size_t)rq->mask_row);
 
-        /* block_copy_resident_pages: copy_page_mask = page_mask & ~resident(dst, dest_nid)  :4687-4692 */
         dst_res = dst_gpu ? &gpu : node_mask(cpu, nid);
+        if (rdup) {
+            /* pages entering read duplication (:5222-5243): for every processor holding pages of
+             * page_mask & ~read_duplicated, unmap everybody else and revoke its write access
+             * (block_prep_read_duplicate_mapping :5120-5162).  The GPU is the only mapper of the table:
+             * it loses its mappings of such CPU pages, and WRITE / ATOMIC on such pages of its own. */
+            or_mask_t fresh, on_cpu, on_gpu, hit;
+            or_andnot(&fresh, &pm, &rd);
+            or_or(&on_cpu, &cpu[0], &cpu[1]);
+            or_and(&on_cpu, &on_cpu, &fresh);
+            or_and(&hit, &on_cpu, &pte[0]);
+            n_unmapped += or_weight(&hit);
+            for (i = 0; i < 3; i++) or_andnot(&pte[i], &pte[i], &on_cpu);
+            or_and(&on_gpu, &gpu, &fresh);
+            or_andnot(&pte[1], &pte[1], &on_gpu);
+            or_andnot(&pte[2], &pte[2], &on_gpu);
+        }
+        else {
+            /* make_resident_copy :4919-4926: unmap every mapped processor from the pages not resident on the
+             * destination; :4931-4939: and every processor but the destination from the read-duplicated pages */
+            or_mask_t gone;
+            or_andnot(&gone, &pm, dst_res);
+            if (!dst_gpu) {
+                or_mask_t dup;
+                or_and(&dup, &pm, &rd);
+                or_or(&gone, &gone, &dup);
+            }
+            or_and(&unmap, &gone, &pte[0]);
+            n_unmapped += or_weight(&unmap);
+            for (i = 0; i < 3; i++) or_andnot(&pte[i], &pte[i], &gone);
+        }
+
+        /* block_copy_resident_pages: copy_page_mask = page_mask & ~resident(dst, dest_nid)  :4687-4692 */
         or_andnot(&copy, &pm, dst_res);
         for (i = 0; i < 3; i++) or_zero(&from[i]);
         if (dst_gpu) {
@@ -105,35 +143,47 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         nrun += k;
         for (i = 0; i < 3; i++) res->migrated[i] = (uint16_t)or_weight(&from[i]);
         res->first_touch = (uint16_t)or_weight(&touch);
+        res->unmapped = (uint16_t)n_unmapped;
 
-        /* make_resident_copy :4919-4926: unmap every mapped processor from the pages not resident on the destination */
-        or_and(&unmap, &copy, &pte[0]);
-        res->unmapped = (uint16_t)or_weight(&unmap);
-        for (i = 0; i < 3; i++) or_andnot(&pte[i], &pte[i], &copy);
-
-        /* _finish: update_state (dst |= migrated; evicted), first touch (dst |= touch), then every other
-         * residency loses region & page_mask  (:5061-5074) */
         or_or(&now, &migrated, &touch);
-        or_or(dst_res, dst_res, &now);
-        if (dst_gpu) {
-            or_andnot(&cpu[0], &cpu[0], &pm);
-            or_andnot(&cpu[1], &cpu[1], &pm);
-            or_andnot(&evicted, &evicted, &migrated);                 /* :5038-5039 */
+        if (rdup) {
+            /* :5259-5302: first touch and migrated pages become resident at the destination, the sources KEEP
+             * theirs -- except the other CPU node (one CPU page table: the pages switch node, :5288-5297) --
+             * and every migrated page is read-duplicated from now on */
+            or_or(dst_res, dst_res, &now);
+            if (!dst_gpu)
+                or_andnot(&cpu[nid ^ 1], &cpu[nid ^ 1], &migrated);
+            or_or(&rd, &rd, &migrated);
+            if (dst_gpu)
+                or_andnot(&evicted, &evicted, &migrated);             /* :5306-5307 */
+            or_store(res->pages_changed_residency, &touch);           /* only first touch reports (:4614-4617) */
         }
         else {
-            or_andnot(&cpu[nid ^ 1], &cpu[nid ^ 1], &pm);             /* uvm_va_block_cpu_clear_resident_all_chunks :672-700 */
-            or_andnot(&gpu, &gpu, &pm);
-            if (rq->cause == 4)
-                or_or(&evicted, &evicted, &from[2]);                  /* :5023-5037 */
+            /* _finish: update_state (dst |= migrated; evicted), first touch (dst |= touch), then every other
+             * residency loses region & page_mask and read duplication ends there  (:5061-5074, :4538-4579) */
+            or_or(dst_res, dst_res, &now);
+            or_andnot(&rd, &rd, &pm);
+            if (dst_gpu) {
+                or_andnot(&cpu[0], &cpu[0], &pm);
+                or_andnot(&cpu[1], &cpu[1], &pm);
+                or_andnot(&evicted, &evicted, &migrated);             /* :5038-5039 */
+            }
+            else {
+                or_andnot(&cpu[nid ^ 1], &cpu[nid ^ 1], &pm);         /* uvm_va_block_cpu_clear_resident_all_chunks :672-700 */
+                or_andnot(&gpu, &gpu, &pm);
+                if (rq->cause == 4 && or_weight(&from[2]))
+                    or_or(&evicted, &evicted, &migrated);             /* :5023-5037: every involved GPU gets copy_mask */
+            }
+            or_store(res->pages_changed_residency, &now);
         }
         or_store(res->pages_migrated, &migrated);
-        or_store(res->pages_changed_residency, &now);
 
         or_store(st->gpu_resident + 8 * (size_t)slot, &gpu);
         or_store(st->cpu_resident[0] + 8 * (size_t)slot, &cpu[0]);
         or_store(st->cpu_resident[1] + 8 * (size_t)slot, &cpu[1]);
         for (i = 0; i < 3; i++) or_store(st->gpu_pte[i] + 8 * (size_t)slot, &pte[i]);
         if (st->gpu_evicted) or_store(st->gpu_evicted + 8 * (size_t)slot, &evicted);
+        if (st->read_duplicated) or_store(st->read_duplicated + 8 * (size_t)slot, &rd);
     }
     return nrun;
 }

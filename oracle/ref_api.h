@@ -134,6 +134,7 @@ typedef struct {
     uint8_t *logical_prot;          /* compute_logical_prot(): 0 NONE, 1 READ_ONLY, 3 READ_WRITE_ATOMIC */
     uint16_t *preferred_location;   /* policy->preferred_location, 257 = none */
     uint64_t *gpu_evicted;          /* gpu_state->evicted (may be NULL) */
+    uint64_t *read_duplicated;      /* va_block->read_duplicated_pages (NULL = read duplication off) */
 } ref_block_state_t;
 
 /* uvm_va_block_make_resident request / result, same layout as uvmtier_make_resident_req_t / _result_t */
@@ -142,7 +143,8 @@ typedef struct {
     uint16_t region_first, region_outer;
     uint8_t  dest_tier;             /* 0 HBM (this GPU), 1 CPU node 0 (DRAM), 2 CPU node 1 (CXL) */
     uint8_t  cause;                 /* uvm_make_resident_cause_t; 4 = EVICTION */
-    uint16_t flags;                 /* 1 page mask given, 2 prefetch mask given, 4 page_mask = gpu resident pages */
+    uint16_t flags;                 /* 1 page mask given, 2 prefetch mask given, 4 page_mask = gpu resident pages,
+                                       8 uvm_va_block_make_resident_read_duplicate (copy, sources keep their pages) */
     uint32_t mask_row;
 } ref_make_resident_req_t;          /* 16 bytes */
 typedef struct {

@@ -15,6 +15,7 @@
  *   :4877-4976  uvm_va_block_make_resident_copy
  *   :4978-5114  block_make_resident_clear_evicted, block_make_resident_update_state,
  *               uvm_va_block_make_resident_finish, uvm_va_block_make_resident
+ *   :5120-5162  block_prep_read_duplicate_mapping       :5164-5332  uvm_va_block_make_resident_read_duplicate
  * and of uvm_va_block_types.h (:116-129 cause enum, :149-159 page tracking, :197-242 the make_resident context,
  * :324-328 transfer mode), against stand-ins for what those functions call elsewhere:
  *   block_populate_pages                 -> CPU destination: the pages of page_mask & ~resident(dest node) are
@@ -23,10 +24,12 @@
  *   block_copy_resident_pages_between    -> its mask protocol verbatim in spirit (:4112-4117 early outs, :4368-4374
  *                                           copied_pages / migrated_pages), the CE pushes replaced by recording the
  *                                           copy runs (oracle_emit_runs)
- *   uvm_va_block_unmap_mask              -> clears the GPU's pte bits for the mask (the only mapper in the table)
+ *   uvm_va_block_unmap_mask, _unmap      -> clears the GPU's pte bits for the mask (the only mapper in the table)
+ *   uvm_va_block_revoke_prot             -> clears the GPU's WRITE and ATOMIC pte bits for the mask (CPU mappings are
+ *                                           not part of the table); block_unmap_cpu -> nothing
  *   trackers, tools events, PMM marks, chunk checks -> no-ops
  *
- * What this pins: M1 / M2 / M4 -- which pages are copied from which processor / NUMA node in which order, what
+ * What this pins: M1 / M1r / M2 / M4 -- which pages are copied from which processor / NUMA node in which order, what
  * counts as first touch, the residency, eviction and mapping state after the call -- for the three destinations of
  * the flat table (this GPU, CPU node 0 = DRAM, CPU node 1 = CXL).
  */
@@ -173,6 +176,23 @@ static NV_STATUS block_copy_resident_pages_between(uvm_va_block_t *block, uvm_va
                                                    uvm_va_block_transfer_mode_t transfer_mode, uvm_page_mask_t *migrated_pages,
                                                    NvU32 *copied_pages, uvm_tracker_t *copy_tracker);
 
+typedef enum { UVM_PROT_NONE, UVM_PROT_READ_ONLY, UVM_PROT_READ_WRITE, UVM_PROT_READ_WRITE_ATOMIC, UVM_PROT_MAX } uvm_prot_t; /* uvm_hal_types.h:181-188 */
+static NV_STATUS uvm_va_block_unmap(uvm_va_block_t *va_block, uvm_va_block_context_t *ctx, uvm_processor_id_t id,
+                                    uvm_va_block_region_t region, const uvm_page_mask_t *mask, uvm_tracker_t *tracker);
+static NV_STATUS uvm_va_block_revoke_prot(uvm_va_block_t *va_block, uvm_va_block_context_t *ctx, uvm_processor_id_t id,
+                                          uvm_va_block_region_t region, const uvm_page_mask_t *mask, uvm_prot_t prot,
+                                          uvm_tracker_t *tracker);
+static void block_unmap_cpu(uvm_va_block_t *b, uvm_va_block_context_t *c, uvm_va_block_region_t r, const uvm_page_mask_t *m)
+{ (void)b; (void)c; (void)r; (void)m; }
+static void uvm_tools_record_read_duplicate(uvm_va_block_t *b, uvm_processor_id_t id, uvm_va_block_region_t r, const uvm_page_mask_t *m)
+{ (void)b; (void)id; (void)r; (void)m; }
+static bool uvm_va_block_is_dead(uvm_va_block_t *b) { (void)b; return false; }
+static int g_uvm_page_mask_cache;
+#define NV_UVM_GFP_FLAGS 0
+static uvm_page_mask_t g_scratch_mask;
+#define kmem_cache_alloc(cache, flags) ((void)(cache), &g_scratch_mask)
+#define kmem_cache_free(cache, p) ((void)(cache), (void)(p))
+
 #include "x_resident.h"         /* the uvm_va_block.c extracts listed at the top, verbatim */
 
 static uvm_page_mask_t *block_resident_mask_get_alloc(uvm_va_block_t *block, uvm_processor_id_t processor, int nid)
@@ -199,6 +219,33 @@ static NV_STATUS uvm_va_block_unmap_mask(uvm_va_block_t *va_block, uvm_va_block_
         g_unmapped += uvm_page_mask_weight(&hit);
     for (k = 0; k < 3; k++)
         uvm_page_mask_andnot(&gs->pte_bits[k], &gs->pte_bits[k], mask);
+    return NV_OK;
+}
+/* uvm_va_block_unmap (:10478-10578) / uvm_va_block_revoke_prot (:10662-10760) for one processor */
+static NV_STATUS uvm_va_block_unmap(uvm_va_block_t *va_block, uvm_va_block_context_t *ctx, uvm_processor_id_t id,
+                                    uvm_va_block_region_t region, const uvm_page_mask_t *mask, uvm_tracker_t *tracker)
+{
+    uvm_processor_mask_t one;
+    uvm_page_mask_t clipped;
+    (void)tracker;
+    uvm_processor_mask_zero(&one);
+    uvm_processor_mask_set(&one, id);
+    uvm_page_mask_init_from_region(&clipped, region, mask);
+    return uvm_va_block_unmap_mask(va_block, ctx, &one, region, &clipped);
+}
+static NV_STATUS uvm_va_block_revoke_prot(uvm_va_block_t *va_block, uvm_va_block_context_t *ctx, uvm_processor_id_t id,
+                                          uvm_va_block_region_t region, const uvm_page_mask_t *mask, uvm_prot_t prot,
+                                          uvm_tracker_t *tracker)
+{
+    uvm_va_block_gpu_state_t *gs = va_block->gpus[g_gpu_id.val];
+    uvm_page_mask_t clipped;
+    int k;
+    (void)ctx; (void)tracker;
+    if (!uvm_id_equal(id, g_gpu_id))
+        return NV_OK;
+    uvm_page_mask_init_from_region(&clipped, region, mask);
+    for (k = (int)prot - 1; k < 3; k++)                               /* READ_WRITE revokes WRITE and ATOMIC */
+        uvm_page_mask_andnot(&gs->pte_bits[k], &gs->pte_bits[k], &clipped);
     return NV_OK;
 }
 /* block_populate_pages (:3099-3182): populate = page_mask & ~resident(dest); CPU destination: the pages are
@@ -288,7 +335,8 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         int k;
 
         memset(res, 0, sizeof(*res));
-        if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > PAGES_PER_UVM_VA_BLOCK || rq->dest_tier > 2) {
+        if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > PAGES_PER_UVM_VA_BLOCK || rq->dest_tier > 2 ||
+            ((rq->flags & 8) && (!st->read_duplicated || rq->cause == UVM_MAKE_RESIDENT_CAUSE_EVICTION || (rq->flags & 4)))) {
             res->slot = 0xFFFFFFFFu;
             continue;
         }
@@ -308,6 +356,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         for (k = 0; k < 3; k++) load_mask(&gs.pte_bits[k], st->gpu_pte[k], slot);
         uvm_page_mask_zero(&gs.evicted);
         if (st->gpu_evicted) load_mask(&gs.evicted, st->gpu_evicted, slot);
+        if (st->read_duplicated) load_mask(&blk.read_duplicated_pages, st->read_duplicated, slot);
         for (k = 0; k < 2; k++) {
             load_mask(&ns[k].resident, st->cpu_resident[k], slot);
             uvm_page_mask_copy(&ns[k].allocated, &ns[k].resident);    /* resident pages have chunks */
@@ -330,8 +379,12 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         ctx.make_resident.cpu_pages_used.node_masks = tracking_ptr;
         g_unmapped = 0; g_from[0] = g_from[1] = g_from[2] = 0;
 
-        uvm_va_block_make_resident(&blk, NULL, &ctx, dest, region, (rq->flags & 5) ? &pm : NULL, (rq->flags & 2) ? &pf : NULL,
-                                   (uvm_make_resident_cause_t)rq->cause);
+        if (rq->flags & 8)
+            uvm_va_block_make_resident_read_duplicate(&blk, NULL, &ctx, dest, region, (rq->flags & 1) ? &pm : NULL,
+                                                      (rq->flags & 2) ? &pf : NULL, (uvm_make_resident_cause_t)rq->cause);
+        else
+            uvm_va_block_make_resident(&blk, NULL, &ctx, dest, region, (rq->flags & 5) ? &pm : NULL, (rq->flags & 2) ? &pf : NULL,
+                                       (uvm_make_resident_cause_t)rq->cause);
 
         /* pages resident nowhere were populated (zeroed) at the destination: the first-touch runs come last */
         uvm_page_mask_andnot(&touch, &ctx.make_resident.pages_changed_residency, &ctx.make_resident.pages_migrated);
@@ -350,6 +403,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         store_mask(st->gpu_resident, slot, &gs.resident);
         for (k = 0; k < 3; k++) store_mask(st->gpu_pte[k], slot, &gs.pte_bits[k]);
         if (st->gpu_evicted) store_mask(st->gpu_evicted, slot, &gs.evicted);
+        if (st->read_duplicated) store_mask(st->read_duplicated, slot, &blk.read_duplicated_pages);
         for (k = 0; k < 2; k++) store_mask(st->cpu_resident[k], slot, &ns[k].resident);
     }
     return g_nrun;

@@ -7,14 +7,32 @@ from uvmtier_testlib import P, bool_from_masks, masks_from_bool
 
 from uvmtier.blockstate import (CAUSE_API_MIGRATE, CAUSE_EVICTION, CAUSE_REPLAYABLE_FAULT, COPY_RUN_DT,  # noqa: F401
                                 MAKE_RESIDENT_REQ_DT, MAKE_RESIDENT_RESULT_DT, MR_EVICT_GPU_PAGES, MR_HAS_PAGE_MASK,
-                                MR_HAS_PREFETCH_MASK, TIER_CXL, TIER_DRAM, TIER_HBM, HostBlockState)
+                                MR_HAS_PREFETCH_MASK, MR_READ_DUPLICATE, TIER_CXL, TIER_DRAM, TIER_HBM, HostBlockState)
 
 RESULT_FIELDS = ("slot", "migrated", "first_touch", "run_count", "unmapped", "pages_migrated", "pages_changed_residency")
 
 
-def random_requests(n_slots, seed, frac=0.6, evict_frac=0.25, bad=0):
+def with_read_duplication(st, seed, dup=0.15, quirk=0.01):
+    """Turns read duplication on for a random state: a share of the CPU-resident pages also have a GPU copy (the GPU
+    maps such pages read-only at most), and a few CPU-only pages carry the mark a NUMA node switch leaves
+    (uvm_va_block.c:5288-5310).  Every read_duplicated page has a CPU copy."""
+    rng = np.random.default_rng(seed + 500)
+    st.enable_read_duplication()
+    cpu = bool_from_masks(st.cpu_resident0) | bool_from_masks(st.cpu_resident1)
+    both = cpu & (rng.random(cpu.shape) < dup)
+    st.gpu_resident |= masks_from_bool(both)
+    st.gpu_pte1 &= ~masks_from_bool(both)
+    st.gpu_pte2 &= ~masks_from_bool(both)
+    st.gpu_evicted &= ~masks_from_bool(both)
+    st.read_duplicated = masks_from_bool(both | (cpu & (rng.random(cpu.shape) < quirk)))
+    return st
+
+
+def random_requests(n_slots, seed, frac=0.6, evict_frac=0.25, bad=0, rdup_frac=0.0, evict_cause_frac=0.0):
     """At most one request per slot (a va_block is locked during make_resident), random destination, region,
-    optional page / prefetch masks; a share of them are evictions of whatever the GPU holds."""
+    optional page / prefetch masks; a share of them are evictions of whatever the GPU holds.  rdup_frac of the others
+    are read-duplicating copies; evict_cause_frac of the moves to the CPU carry cause EVICTION without the
+    "GPU pages only" flag (the eviction marks then cover everything that migrated, :5023-5037)."""
     rng = np.random.default_rng(seed)
     slots = np.nonzero(rng.random(n_slots) < frac)[0]
     rng.shuffle(slots)
@@ -31,7 +49,11 @@ def random_requests(n_slots, seed, frac=0.6, evict_frac=0.25, bad=0):
     rq["cause"][:n] = np.where(evict, CAUSE_EVICTION, rng.choice([CAUSE_API_MIGRATE, CAUSE_REPLAYABLE_FAULT], n))
     has_pm = ~evict & (rng.random(n) < 0.5)
     has_pf = ~evict & (rq["cause"][:n] == CAUSE_REPLAYABLE_FAULT) & (rng.random(n) < 0.6)
-    rq["flags"][:n] = np.where(evict, MR_EVICT_GPU_PAGES, has_pm * MR_HAS_PAGE_MASK + has_pf * MR_HAS_PREFETCH_MASK)
+    rdup = ~evict & (rng.random(n) < rdup_frac)
+    plain_evict = ~evict & ~rdup & ~has_pf & (rq["dest_tier"][:n] != TIER_HBM) & (rng.random(n) < evict_cause_frac)
+    rq["cause"][:n] = np.where(plain_evict, CAUSE_EVICTION, rq["cause"][:n])
+    rq["flags"][:n] = np.where(evict, MR_EVICT_GPU_PAGES,
+                               has_pm * MR_HAS_PAGE_MASK + has_pf * MR_HAS_PREFETCH_MASK + rdup * MR_READ_DUPLICATE)
     rq["mask_row"][:n] = np.arange(n)
     page_masks = masks_from_bool(rng.random((n, 512)) < rng.random((n, 1)))
     prefetch_masks = masks_from_bool(rng.random((n, 512)) < 0.5)
@@ -97,7 +119,12 @@ def check_invariants(before, res):
     """Size-independent properties of make_resident."""
     st = res["state"]
     g, c0, c1 = (bool_from_masks(m) for m in (st.gpu_resident, st.cpu_resident0, st.cpu_resident1))
-    assert not (g & c0).any() and not (g & c1).any() and not (c0 & c1).any(), "a page is resident in two places"
+    rd = bool_from_masks(st.read_duplicated) if st.read_duplicated is not None else np.zeros_like(g)
+    assert not (g & (c0 | c1) & ~rd).any(), "a page is resident in two places without being read-duplicated"
+    assert not (c0 & c1).any(), "a page is resident on two CPU nodes"
+    assert not (rd & ~(c0 | c1)).any(), "a read-duplicated page has no CPU copy"
+    p1 = bool_from_masks(st.gpu_pte1)
+    assert not (p1 & g & (c0 | c1)).any(), "the GPU can write a page that has a second copy"
     gb, c0b, c1b = (bool_from_masks(m) for m in (before.gpu_resident, before.cpu_resident0, before.cpu_resident1))
     # nothing is lost: a page resident somewhere before is resident somewhere after
     assert not ((gb | c0b | c1b) & ~(g | c0 | c1)).any(), "a resident page vanished"

@@ -19,6 +19,7 @@ extern "C" int simt_make_resident(uint32_t n_requests, const uvmtier_make_reside
     bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0]; bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1]; bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
     bs.prefetch_info = state->prefetch_info; bs.logical_prot = state->logical_prot; bs.preferred_location = state->preferred_location;
     bs.gpu_evicted = (uint32_t *)state->gpu_evicted;
+    bs.read_duplicated = (uint32_t *)state->read_duplicated;
     simt::launch(dim3(3), dim3(kResThreads), [&] { k_make_resident(prm, reqs, page_masks, prefetch_masks, bs, results, runs, counters); });
     return 0;
 }

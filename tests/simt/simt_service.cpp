@@ -33,6 +33,7 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
     bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0]; bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1]; bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
     bs.prefetch_info = state->prefetch_info; bs.logical_prot = state->logical_prot; bs.preferred_location = state->preferred_location;
     bs.gpu_evicted = (uint32_t *)state->gpu_evicted;
+    bs.read_duplicated = (uint32_t *)state->read_duplicated;
 
     // (runs, entries) per slot packed in 64 bits, like the device array
     std::vector<unsigned long long> cw64(n_slots + 1, 0);

@@ -13,18 +13,20 @@ from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, tracegen as TG
 pytestmark = pytest.mark.gpu
 
 
-def _state(n_slots, seed):
+def _state(n_slots, seed, rdup=False):
     st = S.random_state(n_slots, seed)
     rng = np.random.default_rng(seed + 100)
     cpu = T.bool_from_masks(st.cpu_resident0) | T.bool_from_masks(st.cpu_resident1)
     st.gpu_evicted = T.masks_from_bool(cpu & (rng.random(cpu.shape) < 0.3))
-    return st
+    return R.with_read_duplication(st, seed) if rdup else st
 
 
-@pytest.mark.parametrize("seed,n_slots", [(1, 96), (5, 4096)])
-def test_make_resident_matches_oracle(seed, n_slots):
-    st0 = _state(n_slots, seed)
-    rq, pm, pf = R.random_requests(n_slots, seed, bad=3)
+@pytest.mark.parametrize("seed,n_slots,rdup", [(1, 96, False), (5, 4096, False), (2, 96, True), (6, 4096, True)])
+def test_make_resident_matches_oracle(seed, n_slots, rdup):
+    """rdup: the table has read-duplicated pages and 40 % of the requests are read-duplicating copies
+    (uvm_va_block_make_resident_read_duplicate); some moves to the CPU carry cause EVICTION without the flag."""
+    st0 = _state(n_slots, seed, rdup)
+    rq, pm, pf = R.random_requests(n_slots, seed, bad=3, rdup_frac=0.4 if rdup else 0.0, evict_cause_frac=0.3)
     want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0, run_cap=1 << 20)
     lay = dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1)
     layout = S.make_layout(lay)
@@ -107,4 +109,24 @@ def test_moves_between_all_tiers_are_byte_exact():
         even = np.repeat(np.arange(n) % 2 == 0, 512)
         assert not m3[TIER_CXL][even].any() and m3[TIER_DRAM][even].all()         # whole-block region: the rest is first touch
         assert int(d["results"]["migrated"][:, 1].sum()) == int(m2[TIER_CXL][even].sum())
+
+        # wave 4: read-duplicate the first half of every block onto the GPU: both copies hold the same bytes, the CPU
+        # keeps its pages, and the GPU's copy is marked read_duplicated
+        ds.enable_read_duplication()
+        rq = all_blocks(TIER_HBM, R.CAUSE_API_MIGRATE, R.MR_READ_DUPLICATE, np.arange(n))
+        rq["region_outer"] = 256
+        e = c.make_resident(rq, None, None, layout, ds, execute=True)
+        m4 = check(e["state"], touched | ~(resident0 | touched), "read duplication")
+        first_half = np.tile(np.arange(512) < 256, n)
+        rd = T.bool_from_masks(e["state"].read_duplicated).ravel()
+        assert np.array_equal(m4[TIER_DRAM], m3[TIER_DRAM]) and np.array_equal(m4[TIER_CXL], m3[TIER_CXL])
+        assert m4[TIER_HBM][first_half].all() and not m4[TIER_HBM][~first_half].any()
+        assert np.array_equal(rd, first_half & (m3[TIER_DRAM] | m3[TIER_CXL]))
+        # wave 5: moving the odd blocks to the CXL node for real breaks the duplication again
+        rq = all_blocks(TIER_CXL, R.CAUSE_API_MIGRATE, 0, np.arange(1, n, 2))
+        f = c.make_resident(rq, None, None, layout, ds, execute=True)
+        m5 = check(f["state"], touched | ~(resident0 | touched), "move after read duplication")
+        odd = ~even
+        assert m5[TIER_CXL][odd].all() and not m5[TIER_HBM][odd].any() and not m5[TIER_DRAM][odd].any()
+        assert not T.bool_from_masks(f["state"].read_duplicated).ravel()[odd].any()
         ds.free()

@@ -9,20 +9,20 @@ import servicelib as S
 import uvmtier_testlib as T
 
 
-def _state(n_slots, seed):
+def _state(n_slots, seed, rdup=False):
     st = S.random_state(n_slots, seed)
     rng = np.random.default_rng(seed + 100)
     # some pages carry an eviction mark: always pages that live on the CPU now
     cpu = T.bool_from_masks(st.cpu_resident0) | T.bool_from_masks(st.cpu_resident1)
     st.gpu_evicted = T.masks_from_bool(cpu & (rng.random(cpu.shape) < 0.3))
-    return st
+    return R.with_read_duplication(st, seed) if rdup else st
 
 
-@pytest.mark.parametrize("seed", [1, 2, 3])
-def test_simt_make_resident_matches_oracle(seed):
+@pytest.mark.parametrize("seed,rdup", [(1, False), (2, False), (3, False), (4, True), (5, True), (6, True)])
+def test_simt_make_resident_matches_oracle(seed, rdup):
     n_slots = 96
-    st0 = _state(n_slots, seed)
-    rq, pm, pf = R.random_requests(n_slots, seed, bad=3)
+    st0 = _state(n_slots, seed, rdup)
+    rq, pm, pf = R.random_requests(n_slots, seed, bad=3, rdup_frac=0.4 if rdup else 0.0, evict_cause_frac=0.3)
     want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0)
     got = R.run_simt(T.load_simt(), rq, pm, pf, st0)
     R.assert_equal(want, got, "seed %d" % seed)
@@ -106,14 +106,17 @@ def test_promote_evict_round_trip_restores_residency_on_one_tier():
 # ------------------------------------------------------------------------------------------------
 # The CPU restatement against the reference's own uvm_va_block_make_resident (compiled verbatim into
 # oracle/_ref/libref_resident.so).
-@pytest.mark.parametrize("seed", [1, 2, 3, 4, 5])
-def test_oracle_matches_the_reference_make_resident(seed):
+@pytest.mark.parametrize("seed,rdup", [(1, False), (2, False), (3, False), (4, False), (5, False),
+                                       (11, True), (12, True), (13, True), (14, True), (15, True)])
+def test_oracle_matches_the_reference_make_resident(seed, rdup):
+    """rdup: the table carries read_duplicated pages and 40 % of the requests are
+    uvm_va_block_make_resident_read_duplicate calls (the others break read duplication where they land)."""
     ref = T.load_ref("resident")
     if ref is None:
         pytest.skip("oracle/_ref/libref_resident.so not built (needs /root/reference)")
     n_slots = 128
-    st0 = _state(n_slots, seed)
-    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3)
+    st0 = _state(n_slots, seed, rdup)
+    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3, rdup_frac=0.4 if rdup else 0.0, evict_cause_frac=0.3)
     want = R.run_ref(ref, rq, pm, pf, st0)
     got = R.run_oracle(T.load_oracle(), rq, pm, pf, st0)
     R.assert_equal(want, got, "reference vs restatement, seed %d" % seed)

@@ -246,3 +246,24 @@ def test_runs_that_need_no_service_are_evaluated_32_at_a_time():
         S.assert_service_equal(want, got, 16, "speculative runs, prefetch %d" % pf[0])
     rec = want["records"]
     assert len(rec) > 250 and 8 <= int((rec["page_fault_count"] > 0).sum()) <= 40
+
+
+@pytest.mark.parametrize("lanes,heavy_min", [(4, 96), (1, NONE_HEAVY), (16, NONE_HEAVY), (4, ALL_HEAVY)])
+def test_servicing_breaks_read_duplication(lanes, heavy_min):
+    """A table with read-duplicated pages (uvm_va_block_make_resident_read_duplicate made them): a fault the GPU
+    raises on such a page -- a write, since its write access was revoked -- goes through make_resident, which
+    drops the CPU copy and the read_duplicated mark of every page it is handed (uvm_va_block.c:4538-4579)."""
+    import residentlib as R
+    pk, tbl, lay = TG.fault_trace(1500, 41, "hotset", 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(128)
+    st0 = R.with_read_duplication(S.random_state(lay["blocks_per_space"] * 2, 9), 9, dup=0.3)
+    k1, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
+    S.assert_service_equal(want, got, 128, "read duplication, lanes %d heavy_min %d" % (lanes, heavy_min))
+    before, after = T.bool_from_masks(st0.read_duplicated), T.bool_from_masks(got["state"].read_duplicated)
+    assert not (after & ~before).any() and int((before & ~after).sum()) > 200
+    cpu = T.bool_from_masks(got["state"].cpu_resident0) | T.bool_from_masks(got["state"].cpu_resident1)
+    assert not (after & ~cpu).any() and not (T.bool_from_masks(got["state"].gpu_resident) & cpu & ~after).any()
+    ref = T.load_ref("service")
+    if ref is not None and lanes == 4 and heavy_min == 96:
+        layout = S.make_layout(lay)
+        S.assert_ref_equals_oracle(S.run_service_ref(ref, k1, gp, tbl, layout, st0), want, "read duplication")

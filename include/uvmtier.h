@@ -408,7 +408,8 @@ NV_STATUS uvmtier_block_state_enable_read_duplication(uvmtier_ctx_t *ctx, const 
  *   d_service       [n_batches*max_batch_size] record of run g of batch b at b*max_batch_size + g
  *                   (page_fault_count == 0 and slot set: examined, nothing to service)
  *   d_runs/run_cap  copy runs; d_counters[0] = runs needed (if > run_cap the list is truncated and the call
- *                   must be repeated on a fresh state with a larger buffer), d_counters[1] = records written
+ *                   must be repeated on a fresh state with a larger buffer), d_counters[1] = 0 (reserved; the
+ *                   number of records of batch b is d_batches[b].num_block_groups)
  * Scratch (per-slot counters and the per-block run lists) lives in the context and is reused. */
 NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
                                                const uvmtier_ordered_fault_t *d_ordered,
@@ -416,6 +417,34 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
                                                const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
                                                uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
                                                uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters);
+
+/* uvm_parent_gpu_service_replayable_faults (UVM/uvm_gpu_replayable_faults.c:2906-2960) for a ring in PINNED HOST
+ * memory: the reference's loop is fetch -> preprocess -> service, one batch after the other; here the packets of
+ * [get, put) cross the link in chunks of chunk_batches batches (0 picks one) on a second stream and every chunk is
+ * preprocessed AND serviced as soon as it has arrived, while the next chunk is still in flight.  Runs that touch
+ * the same va_block are applied in batch order, exactly as when the whole trace is serviced in one pass (chunk
+ * order is batch order); records carry trace-wide batch numbers; d_counters accumulate over the chunks.
+ *
+ * What the caller of service_fault_batch consumes afterwards -- the batch headers, the per-fault flags and the
+ * two counters -- can be copied back chunk by chunk on a third stream: pass pinned buffers in `readback`
+ * (NULL, or NULL members, skip it).  Service records and copy runs stay on the device, where
+ * uvmtier_copy_runs_device consumes them.  Enqueues only; uvmtier_synchronize waits for everything, copies back
+ * included.  Other arguments as in uvmtier_fetch_preprocess_fault_batches_streamed and
+ * uvmtier_service_fault_batches_device. */
+typedef struct {
+    uvmtier_fault_batch_t *h_batches;   /* [n_batches] pinned */
+    uint16_t *h_entry_flags;            /* [n] pinned, n = (put - get) mod ring_entries */
+    uint32_t *h_counters;               /* [2] pinned */
+} uvmtier_service_readback_t;
+NV_STATUS uvmtier_service_replayable_faults_streamed(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_ring_pinned,
+                                                     uvmtier_fault_packet_t *d_ring, uint32_t ring_entries,
+                                                     uint32_t get, uint32_t put, int clear_valid, uint32_t chunk_batches,
+                                                     uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
+                                                     uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                     const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                                     uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                     uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters,
+                                                     const uvmtier_service_readback_t *readback, uint32_t *out_get);
 
 /* The same servicing pass for callers that are not allowed to allocate.  (This entry point has no counterpart
  * in the reference; it exists for the user-space setting.)

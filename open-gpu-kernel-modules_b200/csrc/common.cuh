@@ -21,13 +21,36 @@ struct uvmtier_fault_state {
     uint32_t threads;      // CTA size = next power of two >= max_batch_size (>= 32)
     uint32_t idx_bits;
     size_t smem_bytes;
+    uint32_t generation;   // bumped by every uvmtier_fault_buffer_init (the table's contents may have changed)
 };
 
 // Scratch of the servicing pass (service.cu), grown on demand and reused.
 struct uvmtier_service_scratch {
     uint32_t *d_base;
     size_t cap_words;
+    // CUDA graph of the last uvmtier_service_replayable_faults_streamed call whose arguments repeated (service.cu)
+    cudaGraphExec_t graph_exec;
+    uint64_t graph_launches;                  // kernel launches inside the graph
+    unsigned char graph_key[384];             // the arguments the graph (or the last eager call) was built from
+    int graph_key_seen;                       // consecutive calls with graph_key
 };
+
+struct uvmtier_ctx;
+// Chunked host->device streaming of a pinned ring (faults.cu), shared by the streamed entry points.
+struct uvmtier_chunk_plan { uint32_t n, B, n_batches, per, n_chunks; };
+NV_STATUS uvmtier_streamed_begin(struct uvmtier_ctx *ctx, uint32_t ring_entries, uint32_t get, uint32_t put,
+                                 uint32_t chunk_batches, uvmtier_chunk_plan *plan);
+// Copies chunk c into d_ring and makes the context's stream wait for it; [*first, *last) is its ring range.
+NV_STATUS uvmtier_streamed_copy_chunk(struct uvmtier_ctx *ctx, const uvmtier_chunk_plan &plan, uint32_t c,
+                                      const uvmtier_fault_packet_t *h_ring, uvmtier_fault_packet_t *d_ring,
+                                      uint32_t ring_entries, uint32_t get, uint32_t *e0, uint32_t *e1, uint32_t *first,
+                                      uint32_t *last, cudaStream_t waiter = NULL);
+// uvmtier_fetch_preprocess_fault_batches_device on a stream of the caller's choice
+NV_STATUS uvmtier_fetch_preprocess_on_stream(struct uvmtier_ctx *ctx, cudaStream_t stream, uvmtier_fault_packet_t *d_ring,
+                                             uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
+                                             uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
+                                             uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
 
 struct uvmtier_ctx {
     int device;
@@ -43,6 +66,11 @@ struct uvmtier_ctx {
     cudaEvent_t events[UVMTIER_MAX_EVENTS];   // lazily created timing events
     cudaStream_t copy_stream;                 // lazily created: host->device chunks of the streamed fetch entry point
     cudaEvent_t copy_events[UVMTIER_MAX_COPY_CHUNKS + 1];
+    cudaStream_t aux_stream[3];               // lazily created: side branches of the servicing pass (service.cu),
+    cudaEvent_t aux_events[4];                //   [2] = the preprocess kernels of the streamed service entry point
+    cudaEvent_t k1_events[UVMTIER_MAX_COPY_CHUNKS + 1];
+    cudaStream_t d2h_stream;                  // lazily created: chunked copy-back of the streamed service entry point
+    cudaEvent_t d2h_events[UVMTIER_MAX_COPY_CHUNKS + 1];
     struct uvmtier_fault_state *faults;   // lazily created by the fault entry points
     struct uvmtier_service_scratch svc;   // scratch of the servicing pass
     struct uvmtier_tiers *tiers;          // lazily created by the migration entry points

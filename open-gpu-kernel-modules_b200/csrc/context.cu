@@ -111,6 +111,24 @@ void uvmtier_deinit(uvmtier_ctx_t *ctx)
         cudaStreamSynchronize(ctx->copy_stream);
         cudaStreamDestroy(ctx->copy_stream);
     }
+    for (int i = 0; i <= UVMTIER_MAX_COPY_CHUNKS; i++)
+        if (ctx->d2h_events[i])
+            cudaEventDestroy(ctx->d2h_events[i]);
+    for (int i = 0; i < 4; i++)
+        if (ctx->aux_events[i])
+            cudaEventDestroy(ctx->aux_events[i]);
+    for (int i = 0; i <= UVMTIER_MAX_COPY_CHUNKS; i++)
+        if (ctx->k1_events[i])
+            cudaEventDestroy(ctx->k1_events[i]);
+    for (int i = 0; i < 3; i++)
+        if (ctx->aux_stream[i]) {
+            cudaStreamSynchronize(ctx->aux_stream[i]);
+            cudaStreamDestroy(ctx->aux_stream[i]);
+        }
+    if (ctx->d2h_stream) {
+        cudaStreamSynchronize(ctx->d2h_stream);
+        cudaStreamDestroy(ctx->d2h_stream);
+    }
     if (ctx->d_stage)
         cudaFree(ctx->d_stage);
     if (ctx->h_stage)

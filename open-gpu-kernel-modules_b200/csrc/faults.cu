@@ -55,6 +55,8 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
     fs->gp = *gp;
     fs->gp.coalesce = gp->coalesce != 0;
     fs->n_rows = (uint32_t)n_rows;
+    static std::atomic<uint32_t> generation{0};
+    fs->generation = ++generation;
     fs->threads = threads;
     fs->idx_bits = idx_bits;
     fs->smem_bytes = fault_smem_bytes(threads, gp->utlb_per_gpc_count * gp->gpc_count, (uint32_t)n_rows);
@@ -119,6 +121,18 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmt
                                                         uvmtier_fault_batch_t *d_batches,
                                                         uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get)
 {
+    return uvmtier_fetch_preprocess_on_stream(ctx, ctx ? ctx->stream : NULL, d_ring, ring_entries, get, put, clear_valid,
+                                              d_disposition, d_ordered, d_groups, d_batches, d_entries, out_get);
+}
+
+} // extern "C"
+
+NV_STATUS uvmtier_fetch_preprocess_on_stream(uvmtier_ctx_t *ctx, cudaStream_t stream, uvmtier_fault_packet_t *d_ring,
+                                             uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
+                                             uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
+                                             uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get)
+{
     if (!ctx || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
         return NV_ERR_INVALID_ARGUMENT;
     if (!ctx->faults)
@@ -145,10 +159,12 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmt
     prm.idx_bits = fs->idx_bits;
     prm.clear_valid = clear_valid != 0;
     const uint32_t n_batches = (n + prm.B - 1) / prm.B;
-    UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, ctx->stream, prm, d_ring,
+    UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, stream, prm, d_ring,
                    fs->d_table, d_disposition, d_ordered, d_groups, d_batches, d_entries);
     return NV_OK;
 }
+
+extern "C" {
 
 NV_STATUS uvmtier_fetch_preprocess_fault_batches_streamed(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_ring,
                                                           uvmtier_fault_packet_t *d_ring, uint32_t ring_entries, uint32_t get,
@@ -168,34 +184,18 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_streamed(uvmtier_ctx_t *ctx, co
         return NV_OK;
     if (!d_disposition || !d_ordered || !d_groups || !d_batches)
         return NV_ERR_INVALID_ARGUMENT;
-    UVMTIER_CUDA(cudaSetDevice(ctx->device));
-    const uint32_t B = ctx->faults->gp.max_batch_size, n_batches = (n + B - 1) / B;
-    uint32_t per = chunk_batches ? chunk_batches : (n_batches + 7) / 8;
-    if ((n_batches + per - 1) / per > UVMTIER_MAX_COPY_CHUNKS)
-        per = (n_batches + UVMTIER_MAX_COPY_CHUNKS - 1) / UVMTIER_MAX_COPY_CHUNKS;
-    const uint32_t n_chunks = (n_batches + per - 1) / per;
-    if (!ctx->copy_stream)
-        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
-    for (uint32_t c = 0; c <= n_chunks; c++)
-        if (!ctx->copy_events[c])
-            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->copy_events[c], cudaEventDisableTiming));
-    // the copies may overwrite d_ring only after everything already queued on the context's stream (an earlier
-    // pass reading it) is done
-    UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[n_chunks], ctx->stream));
-    UVMTIER_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_events[n_chunks], 0));
-    for (uint32_t c = 0; c < n_chunks; c++) {
-        const uint32_t e0 = c * per * B, e1 = (c + 1) * per * B < n ? (c + 1) * per * B : n;       // entries, from `get`
-        const uint32_t first = (uint32_t)(((uint64_t)get + e0) % ring_entries), cnt = e1 - e0;
-        const uint32_t head = cnt < ring_entries - first ? cnt : ring_entries - first;          // up to the wrap (:975)
-        UVMTIER_CUDA(cudaMemcpyAsync(d_ring + first, h_ring + first, (size_t)head * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
-        if (head < cnt)
-            UVMTIER_CUDA(cudaMemcpyAsync(d_ring, h_ring, (size_t)(cnt - head) * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
-        UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[c], ctx->copy_stream));
-        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->copy_events[c], 0));
-        const uint32_t last = (uint32_t)(((uint64_t)get + e1) % ring_entries);
-        NV_STATUS st = uvmtier_fetch_preprocess_fault_batches_device(ctx, d_ring, ring_entries, first, last, clear_valid,
-                                                                     d_disposition + e0, d_ordered + e0, d_groups + e0,
-                                                                     d_batches + c * per, d_entries ? d_entries + e0 : NULL, NULL);
+    uvmtier_chunk_plan plan;
+    NV_STATUS st = uvmtier_streamed_begin(ctx, ring_entries, get, put, chunk_batches, &plan);
+    if (st != NV_OK)
+        return st;
+    for (uint32_t c = 0; c < plan.n_chunks; c++) {
+        uint32_t e0, e1, first, last;
+        st = uvmtier_streamed_copy_chunk(ctx, plan, c, h_ring, d_ring, ring_entries, get, &e0, &e1, &first, &last);
+        if (st != NV_OK)
+            return st;
+        st = uvmtier_fetch_preprocess_fault_batches_device(ctx, d_ring, ring_entries, first, last, clear_valid,
+                                                           d_disposition + e0, d_ordered + e0, d_groups + e0,
+                                                           d_batches + c * plan.per, d_entries ? d_entries + e0 : NULL, NULL);
         if (st != NV_OK)
             return st;
     }
@@ -254,3 +254,50 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fau
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Chunk plan and host->device streaming shared by the streamed entry points (here and in service.cu).
+NV_STATUS uvmtier_streamed_begin(uvmtier_ctx_t *ctx, uint32_t ring_entries, uint32_t get, uint32_t put, uint32_t chunk_batches,
+                                 uvmtier_chunk_plan *plan)
+{
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    plan->n = put >= get ? put - get : ring_entries - get + put;
+    plan->B = ctx->faults->gp.max_batch_size;
+    plan->n_batches = (plan->n + plan->B - 1) / plan->B;
+    uint32_t per = chunk_batches ? chunk_batches : (plan->n_batches + 7) / 8;
+    if ((plan->n_batches + per - 1) / per > UVMTIER_MAX_COPY_CHUNKS)
+        per = (plan->n_batches + UVMTIER_MAX_COPY_CHUNKS - 1) / UVMTIER_MAX_COPY_CHUNKS;
+    plan->per = per;
+    plan->n_chunks = (plan->n_batches + per - 1) / per;
+    if (!ctx->copy_stream)
+        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    for (uint32_t c = 0; c <= plan->n_chunks; c++)
+        if (!ctx->copy_events[c])
+            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->copy_events[c], cudaEventDisableTiming));
+    // the copies may overwrite d_ring only after everything already queued on the context's stream (an earlier
+    // pass reading it) is done
+    UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[plan->n_chunks], ctx->stream));
+    UVMTIER_CUDA(cudaStreamWaitEvent(ctx->copy_stream, ctx->copy_events[plan->n_chunks], 0));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_streamed_copy_chunk(uvmtier_ctx_t *ctx, const uvmtier_chunk_plan &plan, uint32_t c,
+                                      const uvmtier_fault_packet_t *h_ring, uvmtier_fault_packet_t *d_ring,
+                                      uint32_t ring_entries, uint32_t get, uint32_t *e0_out, uint32_t *e1_out,
+                                      uint32_t *first_out, uint32_t *last_out, cudaStream_t waiter)
+{
+    const uint32_t B = plan.B, per = plan.per, n = plan.n;
+    const uint32_t e0 = c * per * B, e1 = (c + 1) * per * B < n ? (c + 1) * per * B : n;       // entries, from `get`
+    const uint32_t first = (uint32_t)(((uint64_t)get + e0) % ring_entries), cnt = e1 - e0;
+    const uint32_t head = cnt < ring_entries - first ? cnt : ring_entries - first;          // up to the wrap (:975)
+    UVMTIER_CUDA(cudaMemcpyAsync(d_ring + first, h_ring + first, (size_t)head * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
+    if (head < cnt)
+        UVMTIER_CUDA(cudaMemcpyAsync(d_ring, h_ring, (size_t)(cnt - head) * 32, cudaMemcpyHostToDevice, ctx->copy_stream));
+    UVMTIER_CUDA(cudaEventRecord(ctx->copy_events[c], ctx->copy_stream));
+    UVMTIER_CUDA(cudaStreamWaitEvent(waiter ? waiter : ctx->stream, ctx->copy_events[c], 0));
+    *e0_out = e0;
+    *e1_out = e1;
+    *first_out = first;
+    *last_out = (uint32_t)(((uint64_t)get + e1) % ring_entries);
+    return NV_OK;
+}

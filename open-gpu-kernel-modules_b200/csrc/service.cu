@@ -80,7 +80,8 @@ static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, cons
 static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,
                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const uvmtier_va_layout_t *lay,
                               const uvmtier_block_state_t *state, uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
-                              uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters)
+                              uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters, uint32_t batch_base = 0,
+                              bool zero_outputs = true)
 {
     const uint32_t B = ctx->faults->gp.max_batch_size;
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
@@ -100,6 +101,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults;
     prm.run_cap = run_cap;
     prm.B_shift = svc_log2_or_none(B);
+    prm.batch_base = batch_base;
 
     block_state_ptrs bs;
     bs.gpu_resident = (uint32_t *)state->gpu_resident;
@@ -118,8 +120,10 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     // the two work lists' lengths and the per-batch flags are accumulated into and must start at zero (one memset:
     // they are adjacent); offsets, (slot, position) pairs and run lists are fully rewritten before they are read.
     UVMTIER_CUDA(cudaMemsetAsync(base, 0, v.zero_words * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+    if (zero_outputs) {                                     // a chunked caller has done both for the whole trace
+        UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+        UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+    }
 
     const uvmtier_instance_ptr_entry_t *d_tbl = ctx->faults->d_table;
     const uint2 *cw = (const uint2 *)v.cw;
@@ -142,7 +146,35 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
         sgrid = cap;
     UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
                    v.big, v.heavy, v.hist, v.light_rank, v.light);
-    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, cw, v.offset, v.list, v.big);
+    // Three independent branches from here: the light va_blocks (lane groups), the heavy ones (their long lists are
+    // sorted first, then a warp each) and the runs outside every va_range.  They touch different va_blocks, records
+    // and entry flags, and add to the batch counters atomically; the two small branches run on side streams next
+    // to the big one (UVMTIER_SERVICE_FORK=0 keeps everything on the context's stream).
+    static const char *fork_env = getenv("UVMTIER_SERVICE_FORK");
+    const bool fork = !(fork_env && atoi(fork_env) == 0);
+    cudaStream_t s_heavy = ctx->stream, s_unmapped = ctx->stream;
+    if (fork) {
+        for (int i = 0; i < 2; i++)
+            if (!ctx->aux_stream[i])
+                UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->aux_stream[i], cudaStreamNonBlocking));
+        for (int i = 0; i < 4; i++)
+            if (!ctx->aux_events[i])
+                UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->aux_events[i], cudaEventDisableTiming));
+        s_heavy = ctx->aux_stream[0];
+        s_unmapped = ctx->aux_stream[1];
+        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[0], ctx->stream));
+        UVMTIER_CUDA(cudaStreamWaitEvent(s_heavy, ctx->aux_events[0], 0));
+        UVMTIER_CUDA(cudaStreamWaitEvent(s_unmapped, ctx->aux_events[0], 0));
+    }
+    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, s_heavy, cw, v.offset, v.list, v.big);
+    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, s_heavy, prm, d_ordered, d_groups, d_batches, bs, cw,
+                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, s_unmapped, prm, d_ordered, d_groups, d_batches, d_tbl,
+                   v.batch_unmapped, d_entry_flags, d_service);
+    if (fork) {
+        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[1], s_heavy));
+        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[2], s_unmapped));
+    }
 
     // lanes per va_block x CTAs per SM the kernel is compiled for; UVMTIER_SERVICE_LANES / UVMTIER_SERVICE_MINCTAS
     // pick another instantiation (for experiments)
@@ -158,13 +190,11 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
         default: st = minctas == 7 ? launch_grp<4, 7>(GRP_ARGS) : minctas == 6 ? launch_grp<4, 6>(GRP_ARGS) : (minctas == 5 ? launch_grp<4, 5>(GRP_ARGS) : launch_grp<4, 4>(GRP_ARGS)); break;
     }
 #undef GRP_ARGS
-    if (st != NV_OK)
-        return st;
-    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs, cw,
-                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
-    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, d_tbl,
-                   v.batch_unmapped, d_entry_flags, d_service);
-    return NV_OK;
+    if (fork) {                                             // join, also when the launch above failed
+        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[1], 0));
+        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[2], 0));
+    }
+    return st;
 }
 
 static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, const void *d_ordered, const void *d_groups,
@@ -187,9 +217,33 @@ static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, cons
     return NV_OK;
 }
 
+// Grows the context's working space to what a pass over n_batches batches needs.
+static NV_STATUS service_scratch_reserve(uvmtier_ctx_t *ctx, uint32_t n_slots, uint32_t n_batches, size_t total)
+{
+    uvmtier_service_scratch *s = &ctx->svc;
+    const size_t words = scratch_view(NULL, n_slots, n_batches, total).words;
+    if (words > s->cap_words) {
+        if (s->graph_exec) {                              // the graph holds the old working space's address
+            cudaGraphExecDestroy(s->graph_exec);
+            s->graph_exec = NULL;
+        }
+        s->graph_key_seen = 0;
+        if (s->d_base) {
+            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+            UVMTIER_CUDA(cudaFree(s->d_base));
+            s->d_base = NULL;
+            s->cap_words = 0;
+        }
+        UVMTIER_CUDA(cudaMalloc(&s->d_base, words * sizeof(uint32_t)));
+        s->cap_words = words;
+    }
+    return NV_OK;
+}
+
 void uvmtier_service_scratch_destroy(uvmtier_ctx_t *ctx)
 {
     uvmtier_service_scratch *s = &ctx->svc;
+    if (s->graph_exec) cudaGraphExecDestroy(s->graph_exec);
     if (s->d_base) cudaFree(s->d_base);
     memset(s, 0, sizeof(*s));
 }
@@ -277,20 +331,226 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
     const size_t total = (size_t)n_batches * ctx->faults->gp.max_batch_size;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
-    uvmtier_service_scratch *s = &ctx->svc;
-    const size_t words = scratch_view(NULL, n_slots, n_batches, total).words;
-    if (words > s->cap_words) {
-        if (s->d_base) {
-            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-            UVMTIER_CUDA(cudaFree(s->d_base));
-            s->d_base = NULL;
-            s->cap_words = 0;
-        }
-        UVMTIER_CUDA(cudaMalloc(&s->d_base, words * sizeof(uint32_t)));
-        s->cap_words = words;
+    const NV_STATUS st = service_scratch_reserve(ctx, n_slots, n_batches, total);
+    if (st != NV_OK)
+        return st;
+    return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                        d_runs, run_cap, d_counters);
+}
+
+} // extern "C"
+
+// Everything uvmtier_service_replayable_faults_streamed puts on the three streams.  Streams, events and working
+// space exist already (streamed_prepare), so this is pure enqueueing and can run under stream capture.
+struct streamed_args {
+    const uvmtier_fault_packet_t *h_ring;
+    uvmtier_fault_packet_t *d_ring;
+    uint32_t ring_entries, get, put;
+    int clear_valid;
+    uint32_t chunk_batches;
+    uint32_t *d_disposition;
+    uvmtier_ordered_fault_t *d_ordered;
+    uvmtier_fault_group_t *d_groups;
+    uvmtier_fault_batch_t *d_batches;
+    uvmtier_va_layout_t lay;
+    uvmtier_block_state_t state;
+    uint16_t *d_entry_flags;
+    uvmtier_service_group_t *d_service;
+    uvmtier_copy_run_t *d_runs;
+    uint32_t run_cap;
+    uint32_t *d_counters;
+    uvmtier_service_readback_t rb;
+    uint32_t tunables[4];                                   // what the kernels' parameters are derived from
+    uvmtier_fault_gpu_params_t gp;
+    const void *d_table;
+    uint32_t table_rows, table_generation;
+};
+static_assert(sizeof(streamed_args) <= sizeof(((uvmtier_service_scratch *)0)->graph_key), "graph key too small");
+
+static NV_STATUS streamed_prepare(uvmtier_ctx_t *ctx, const streamed_args &a, uvmtier_chunk_plan *plan, bool back)
+{
+    const uint32_t n = a.put >= a.get ? a.put - a.get : a.ring_entries - a.get + a.put;
+    plan->B = ctx->faults->gp.max_batch_size;
+    const uint32_t n_batches = (n + plan->B - 1) / plan->B;
+    uint32_t per = a.chunk_batches ? a.chunk_batches : (n_batches + 7) / 8;
+    if ((n_batches + per - 1) / per > UVMTIER_MAX_COPY_CHUNKS)
+        per = (n_batches + UVMTIER_MAX_COPY_CHUNKS - 1) / UVMTIER_MAX_COPY_CHUNKS;
+    const uint32_t n_chunks = (n_batches + per - 1) / per;
+    if (!ctx->copy_stream)
+        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
+    if (back && !ctx->d2h_stream)
+        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->d2h_stream, cudaStreamNonBlocking));
+    if (!ctx->aux_stream[2])
+        UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->aux_stream[2], cudaStreamNonBlocking));
+    for (uint32_t c = 0; c <= n_chunks; c++) {
+        if (!ctx->copy_events[c])
+            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->copy_events[c], cudaEventDisableTiming));
+        if (!ctx->k1_events[c])
+            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->k1_events[c], cudaEventDisableTiming));
+        if (back && !ctx->d2h_events[c])
+            UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->d2h_events[c], cudaEventDisableTiming));
     }
-    return service_pass(ctx, s->d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service, d_runs,
-                        run_cap, d_counters);
+    return service_scratch_reserve(ctx, a.lay.n_spaces * a.lay.blocks_per_space, per, (size_t)per * plan->B);
+}
+
+static NV_STATUS streamed_enqueue(uvmtier_ctx_t *ctx, const streamed_args &a, bool back)
+{
+    const uvmtier_fault_packet_t *h_ring = a.h_ring;
+    uvmtier_fault_packet_t *d_ring = a.d_ring;
+    const uint32_t ring_entries = a.ring_entries, get = a.get, put = a.put, chunk_batches = a.chunk_batches, run_cap = a.run_cap;
+    const int clear_valid = a.clear_valid;
+    uint32_t *d_disposition = a.d_disposition, *d_counters = a.d_counters;
+    uvmtier_ordered_fault_t *d_ordered = a.d_ordered;
+    uvmtier_fault_group_t *d_groups = a.d_groups;
+    uvmtier_fault_batch_t *d_batches = a.d_batches;
+    const uvmtier_va_layout_t *lay = &a.lay;
+    const uvmtier_block_state_t *state = &a.state;
+    uint16_t *d_entry_flags = a.d_entry_flags;
+    uvmtier_service_group_t *d_service = a.d_service;
+    uvmtier_copy_run_t *d_runs = a.d_runs;
+    const uvmtier_service_readback_t *rb = &a.rb;
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    uvmtier_chunk_plan plan;
+    NV_STATUS st = uvmtier_streamed_begin(ctx, ring_entries, get, put, chunk_batches, &plan);
+    if (st != NV_OK)
+        return st;
+    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, (size_t)plan.n_batches * plan.B * sizeof(uint16_t), ctx->stream));
+    for (uint32_t c = 0; c < plan.n_chunks; c++) {
+        uint32_t e0, e1, first, last;
+        // the chunk is preprocessed on a stream of its own, next to the servicing of the chunk before it
+        cudaStream_t s_k1 = ctx->aux_stream[2];
+        st = uvmtier_streamed_copy_chunk(ctx, plan, c, h_ring, d_ring, ring_entries, get, &e0, &e1, &first, &last, s_k1);
+        if (st != NV_OK)
+            return st;
+        const uint32_t b0 = c * plan.per, nb = (e1 - e0 + plan.B - 1) / plan.B;
+        st = uvmtier_fetch_preprocess_on_stream(ctx, s_k1, d_ring, ring_entries, first, last, clear_valid, d_disposition + e0,
+                                                d_ordered + e0, d_groups + e0, d_batches + b0, NULL, NULL);
+        if (st != NV_OK)
+            return st;
+        UVMTIER_CUDA(cudaEventRecord(ctx->k1_events[c], s_k1));
+        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->k1_events[c], 0));
+        st = service_pass(ctx, ctx->svc.d_base, nb, d_ordered + e0, d_groups + e0, d_batches + b0, lay, state, d_entry_flags + e0,
+                          d_service + e0, d_runs, run_cap, d_counters, b0, false);
+        if (st != NV_OK)
+            return st;
+        if (back) {
+            UVMTIER_CUDA(cudaEventRecord(ctx->d2h_events[c], ctx->stream));
+            UVMTIER_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, ctx->d2h_events[c], 0));
+            if (rb->h_batches)
+                UVMTIER_CUDA(cudaMemcpyAsync(rb->h_batches + b0, d_batches + b0, (size_t)nb * sizeof(*d_batches),
+                                             cudaMemcpyDeviceToHost, ctx->d2h_stream));
+            if (rb->h_entry_flags)
+                UVMTIER_CUDA(cudaMemcpyAsync(rb->h_entry_flags + e0, d_entry_flags + e0, (size_t)(e1 - e0) * sizeof(uint16_t),
+                                             cudaMemcpyDeviceToHost, ctx->d2h_stream));
+        }
+    }
+    if (back) {
+        // the counters are final after the last chunk; the context's stream then waits for the copy-back stream, so
+        // that uvmtier_synchronize covers it
+        if (rb->h_counters) {
+            UVMTIER_CUDA(cudaEventRecord(ctx->d2h_events[plan.n_chunks], ctx->stream));
+            UVMTIER_CUDA(cudaStreamWaitEvent(ctx->d2h_stream, ctx->d2h_events[plan.n_chunks], 0));
+            UVMTIER_CUDA(cudaMemcpyAsync(rb->h_counters, d_counters, 2 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->d2h_stream));
+        }
+        UVMTIER_CUDA(cudaEventRecord(ctx->d2h_events[plan.n_chunks], ctx->d2h_stream));
+        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->d2h_events[plan.n_chunks], 0));
+    }
+    return NV_OK;
+}
+
+extern "C" {
+
+NV_STATUS uvmtier_service_replayable_faults_streamed(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *h_ring,
+                                                     uvmtier_fault_packet_t *d_ring, uint32_t ring_entries, uint32_t get,
+                                                     uint32_t put, int clear_valid, uint32_t chunk_batches,
+                                                     uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
+                                                     uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                     const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                                     uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                     uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters,
+                                                     const uvmtier_service_readback_t *rb, uint32_t *out_get)
+{
+    if (!ctx || !h_ring || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t n = put >= get ? put - get : ring_entries - get + put;
+    if (out_get)
+        *out_get = put;
+    if (!d_disposition && n)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t B_all = ctx->faults ? ctx->faults->gp.max_batch_size : 0;
+    const NV_STATUS ok = service_check_args(ctx, B_all ? (n + B_all - 1) / B_all : 0, d_ordered, d_groups, d_batches, lay, state,
+                                            d_entry_flags, d_service, d_runs, run_cap, d_counters);
+    if (ok != NV_OK || !n)
+        return ok;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+
+    streamed_args a;
+    memset(&a, 0, sizeof(a));                               // padding too: the struct is compared bytewise
+    a.h_ring = h_ring; a.d_ring = d_ring; a.ring_entries = ring_entries; a.get = get; a.put = put;
+    a.clear_valid = clear_valid != 0; a.chunk_batches = chunk_batches;
+    a.d_disposition = d_disposition; a.d_ordered = d_ordered; a.d_groups = d_groups; a.d_batches = d_batches;
+    a.lay = *lay; a.state = *state;
+    a.d_entry_flags = d_entry_flags; a.d_service = d_service; a.d_runs = d_runs; a.run_cap = run_cap; a.d_counters = d_counters;
+    if (rb)
+        a.rb = *rb;
+    a.tunables[0] = ctx->cfg.uvm_perf_prefetch_enable; a.tunables[1] = ctx->cfg.uvm_perf_prefetch_threshold;
+    a.tunables[2] = ctx->cfg.uvm_perf_prefetch_min_faults; a.tunables[3] = ctx->cfg.uvm_perf_fault_coalesce;
+    a.gp = ctx->faults->gp; a.d_table = ctx->faults->d_table; a.table_rows = ctx->faults->n_rows;
+    a.table_generation = ctx->faults->generation;
+    const bool back = a.rb.h_batches || a.rb.h_entry_flags || a.rb.h_counters;
+    uvmtier_chunk_plan plan;
+    NV_STATUS st = streamed_prepare(ctx, a, &plan, back);
+    if (st != NV_OK)
+        return st;
+
+    // A servicing loop calls this with the same buffers over and over; the per-chunk work is some twenty stream
+    // operations, and enqueueing them costs more host time than the GPU needs to execute them.  When a call repeats
+    // the previous call's arguments exactly, everything it enqueues is captured into a CUDA graph once and replayed
+    // from then on (UVMTIER_GRAPHS=0 turns this off).  The graph is dropped when the arguments, the tunables or the
+    // fault-buffer configuration (every uvmtier_fault_buffer_init is a new generation) change, or the working space moves.
+    static const char *graphs_env = getenv("UVMTIER_GRAPHS");
+    const bool graphs = !(graphs_env && atoi(graphs_env) == 0);
+    uvmtier_service_scratch *s = &ctx->svc;
+    const bool same = s->graph_key_seen > 0 && memcmp(s->graph_key, &a, sizeof(a)) == 0;
+    if (!same) {
+        if (s->graph_exec) {
+            cudaGraphExecDestroy(s->graph_exec);
+            s->graph_exec = NULL;
+        }
+        memset(s->graph_key, 0, sizeof(s->graph_key));
+        memcpy(s->graph_key, &a, sizeof(a));
+        s->graph_key_seen = 1;
+        return streamed_enqueue(ctx, a, back);
+    }
+    s->graph_key_seen++;
+    if (!graphs)
+        return streamed_enqueue(ctx, a, back);
+    if (!s->graph_exec) {
+        cudaGraph_t graph = NULL;
+        const uint64_t before = g_uvmtier_launches.load();
+        UVMTIER_CUDA(cudaStreamBeginCapture(ctx->stream, cudaStreamCaptureModeThreadLocal));
+        st = streamed_enqueue(ctx, a, back);
+        const cudaError_t ce = cudaStreamEndCapture(ctx->stream, &graph);
+        s->graph_launches = g_uvmtier_launches.load() - before;
+        g_uvmtier_launches.fetch_sub(s->graph_launches);    // nothing ran yet; the replay below counts them
+        if (st != NV_OK || ce != cudaSuccess || !graph) {
+            if (graph)
+                cudaGraphDestroy(graph);
+            cudaGetLastError();
+            s->graph_key_seen = 0;                          // do not try again with these arguments right away
+            return st != NV_OK ? st : streamed_enqueue(ctx, a, back);
+        }
+        const cudaError_t ie = cudaGraphInstantiate(&s->graph_exec, graph, 0);
+        cudaGraphDestroy(graph);
+        if (ie != cudaSuccess) {
+            s->graph_exec = NULL;
+            cudaGetLastError();
+            return streamed_enqueue(ctx, a, back);
+        }
+    }
+    UVMTIER_CUDA(cudaGraphLaunch(s->graph_exec, ctx->stream));
+    g_uvmtier_launches.fetch_add(s->graph_launches, std::memory_order_relaxed);
+    return NV_OK;
 }
 
 } // extern "C"

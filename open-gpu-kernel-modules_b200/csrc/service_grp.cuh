@@ -526,7 +526,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             uint32_t *rec = (uint32_t *)&service[t];
             if (gl == 0) {
                 ((uint4 *)rec)[0] = make_uint4(slot, rf | (ro << 16), page_faults | (n_pf << 16), n0 | (n1 << 16));
-                ((uint4 *)rec)[1] = make_uint4(nt | (hint << 16), run_off, run_cnt | (b << 16), t - base);
+                ((uint4 *)rec)[1] = make_uint4(nt | (hint << 16), run_off, run_cnt | ((b + prm.batch_base) << 16), t - base);
             }
             st_words<W>(rec + 8 + word0, newres);
         }

@@ -40,6 +40,7 @@ struct service_kparams {
     uint32_t pf_enable, pf_threshold, pf_min_faults;
     uint32_t run_cap;
     uint32_t B_shift;                          // log2(B) when B is a power of two, else 0xffffffff
+    uint32_t batch_base;                       // batch number of d_batches[0] (a pass over one chunk of a longer trace)
 };
 
 __host__ __device__ __forceinline__ uint32_t svc_log2_or_none(uint32_t B)
@@ -306,7 +307,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                     if (isum) atomicAdd(&batches[bs].num_invalid_prefetch_faults, isum);
                     uint4 *rec = (uint4 *)&service[ts];
                     rec[0] = make_uint4(slot, 0u, 0u, 0u);
-                    rec[1] = make_uint4((uint32_t)UVMTIER_ID_INVALID << 16, 0u, bs << 16, ts - base_s);
+                    rec[1] = make_uint4((uint32_t)UVMTIER_ID_INVALID << 16, 0u, (bs + prm.batch_base) << 16, ts - base_s);
                     rec[2] = rec[3] = rec[4] = rec[5] = make_uint4(0u, 0u, 0u, 0u);
                 }
                 k += adv;
@@ -450,7 +451,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                         case 3: v = n0 | (n1 << 16); break;
                         case 4: v = nt | (hint << 16); break;
                         case 5: v = run_off; break;
-                        case 6: v = run_cnt | (b << 16); break;
+                        case 6: v = run_cnt | ((b + prm.batch_base) << 16); break;
                         case 7: v = t - base; break;
                     }
                     rec[l] = v;
@@ -531,7 +532,7 @@ k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restric
         uvmtier_service_group_t rec;
         rec.slot = 0xffffffffu; rec.region_first = 0; rec.region_outer = 0; rec.page_fault_count = 0; rec.prefetch_count = 0;
         rec.migrated[0] = 0; rec.migrated[1] = 0; rec.first_touch = 0; rec.hint_residency = UVMTIER_ID_INVALID;
-        rec.run_offset = 0; rec.run_count = 0; rec.batch = (uint16_t)b; rec.group = g;
+        rec.run_offset = 0; rec.run_count = 0; rec.batch = (uint16_t)(b + prm.batch_base); rec.group = g;
         for (int k = 0; k < 8; k++) rec.new_residency.bitmap[k] = 0;
         service[base + g] = rec;
     }

@@ -266,6 +266,75 @@ class Context:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt):
                 self.free(p)
 
+    def service_replayable_faults_streamed(self, ring, get, put, layout, dstate, run_cap=1 << 20, chunk_batches=0,
+                                           clear_valid=True, repeat=1, before_each=None):
+        """uvmtier_service_replayable_faults_streamed on a copy of `ring` in pinned host memory: fetch -> preprocess ->
+        service chunk by chunk while later chunks cross the link; batch headers, entry flags and counters come back
+        through the chunked copy-back (pinned buffers), everything else is downloaded afterwards.  Same dict as
+        service_fault_batches plus the preprocess outputs (ordered, groups, disp).  repeat > 1 makes the same call
+        again with the same buffers (before_each() restores the state table): the library then replays a CUDA graph."""
+        from .blockstate import COPY_RUN_DT, SERVICE_GROUP_DT
+        from .layouts import BATCH_DT, GROUP_DT, ORDERED_DT
+
+        class Readback(ctypes.Structure):
+            _fields_ = [("h_batches", ctypes.c_void_p), ("h_entry_flags", ctypes.c_void_p), ("h_counters", ctypes.c_void_p)]
+
+        ring = np.ascontiguousarray(ring)
+        ring_entries = len(ring)
+        n = put - get if put >= get else ring_entries - get + put
+        B = self._fault_B
+        nb = (n + B - 1) // B
+        total = nb * B
+        pinned = []
+
+        def pin(nbytes):
+            hp = ctypes.c_void_p()
+            _check(lib().uvmtier_mem_alloc_host_pinned(self._h, ctypes.c_size_t(max(nbytes, 8)), ctypes.byref(hp)), "pinned")
+            pinned.append(hp)
+            return hp
+
+        hp = pin(ring.nbytes)
+        ctypes.memmove(hp.value, ring.ctypes.data, ring.nbytes)
+        rb = Readback(pin(nb * 32).value, pin(total * 2).value, pin(8).value)
+        ctypes.memset(rb.h_entry_flags, 0, total * 2)
+        d_ring = self.alloc(ring.nbytes)
+        d_disp, d_ord, d_grp, d_bat = self.alloc(total * 4), self.alloc(total * 16), self.alloc(total * 16), self.alloc(nb * 32)
+        d_flags = self.alloc(total * 2); d_svc = self.alloc(total * 96); d_runs = self.alloc(max(run_cap, 1) * 8)
+        d_cnt = self.alloc(8)
+        devs = (d_ring, d_disp, d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt)
+        try:
+            for p, nbytes, v in ((d_ring, ring.nbytes, 0), (d_ord, total * 16, 0xff), (d_grp, total * 16, 0xff), (d_svc, total * 96, 0),
+                                 (d_flags, total * 2, 0)):
+                _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(p), ctypes.c_int(v), ctypes.c_size_t(nbytes)), "memset")
+            new_get = ctypes.c_uint32(0)
+            for _ in range(repeat):
+                if before_each is not None:
+                    before_each()
+                    ctypes.memset(rb.h_entry_flags, 0xAB, total * 2)
+                    ctypes.memset(rb.h_batches, 0xAB, nb * 32)
+                _check(lib().uvmtier_service_replayable_faults_streamed(
+                    self._h, hp, P(d_ring), ctypes.c_uint32(ring_entries), ctypes.c_uint32(get), ctypes.c_uint32(put),
+                    ctypes.c_int(1 if clear_valid else 0), ctypes.c_uint32(chunk_batches), P(d_disp), P(d_ord), P(d_grp), P(d_bat),
+                    P(layout), ctypes.byref(dstate.ptrs), P(d_flags), P(d_svc), P(d_runs), ctypes.c_uint32(run_cap), P(d_cnt),
+                    ctypes.byref(rb), ctypes.byref(new_get)), "uvmtier_service_replayable_faults_streamed")
+                self.synchronize()
+            host = lambda ptr, count, dt: np.frombuffer((ctypes.c_char * (count * np.dtype(dt).itemsize)).from_address(ptr),
+                                                        dtype=dt, count=count).copy()
+            cnt = host(rb.h_counters, 2, "<u4")
+            ctypes.memset(rb.h_entry_flags + n * 2, 0, (total - n) * 2)      # the copy-back covers the n entries of the trace
+            return dict(flags=host(rb.h_entry_flags, total, "<u2"), service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
+                        runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT), n_runs=int(cnt[0]), n_records=int(cnt[1]),
+                        batch=host(rb.h_batches, nb, BATCH_DT), state=dstate.download(), get=new_get.value,
+                        ordered=self.from_device(d_ord, total, ORDERED_DT), groups=self.from_device(d_grp, total, GROUP_DT),
+                        disp=self.from_device(d_disp, n, "<u4"),
+                        device_copies=dict(flags=self.from_device(d_flags, total, "<u2"), batch=self.from_device(d_bat, nb, BATCH_DT),
+                                           counters=self.from_device(d_cnt, 2, "<u4")))
+        finally:
+            for p in devs:
+                self.free(p)
+            for h in pinned:
+                lib().uvmtier_mem_free_host_pinned(self._h, h)
+
     # ---- (1c) make_resident ----
     def make_resident(self, requests, page_masks, prefetch_masks, layout, dstate, run_cap=1 << 18, execute=False):
         """uvmtier_make_resident_device on host arrays (requests: MAKE_RESIDENT_REQ_DT; masks: uint64 [n, 8] or

@@ -101,3 +101,49 @@ def test_gpu_service_baseline_size(ctx):
     runs = got["runs"][:got["n_runs"]]
     cpu_runs = runs[((runs["bits"] >> 10) & 7) != 7]
     assert int((cpu_runs["bits"] & 0x3FF).sum()) == moved
+
+
+@pytest.mark.parametrize("dist,chunk_batches,get,repeat", [("hotset", 0, 0, 1), ("uniform", 5, 0, 1), ("stream", 1, 0, 1),
+                                                           ("hotset", 7, 700, 1), ("hotset", 0, 0, 4), ("uniform", 9, 700, 3)])
+def test_streamed_fetch_preprocess_service_equals_the_one_pass_form(dist, chunk_batches, get, repeat):
+    """uvmtier_service_replayable_faults_streamed: the ring stays in pinned host memory; every chunk is preprocessed
+    and serviced while the next one is in flight.  Same flags, batch counters, records (with trace-wide batch
+    numbers), copy runs and final state as servicing the whole trace in one pass -- for chunks that do not divide
+    the trace, one batch per chunk, and a ring segment that wraps; many va_blocks are hit from several chunks.
+    repeat > 1: the call is made again with the same buffers on a restored state table, which the library serves
+    from a CUDA graph captured on the second call; the last call's results are the ones compared."""
+    import uvmtier
+    n, B = 20000, 64
+    pk, tbl, lay = TG.fault_trace(n, 23, dist, 2, total_va_bytes=256 << 21)
+    gp = TG.gpu_params(B)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 8)
+    layout = S.make_layout(lay)
+    ring_entries = n + 1000
+    ring = np.zeros((ring_entries, 8), np.uint32)
+    ring[(get + np.arange(n)) % ring_entries] = pk
+    put = int((get + n) % ring_entries)
+    with uvmtier.Context(0) as ctx:
+        ctx.fault_buffer_init(gp, tbl)
+        ds = ctx.block_state_alloc(layout)
+        ds.upload(st0)
+        launches = []
+
+        def restore():
+            ds.upload(st0)
+            launches.append(uvmtier.lib().uvmtier_kernel_launch_count())
+
+        uvmtier.lib().uvmtier_kernel_launch_count.restype = __import__("ctypes").c_uint64
+        got = ctx.service_replayable_faults_streamed(ring, get, put, layout, ds, run_cap=1 << 20, chunk_batches=chunk_batches,
+                                                     repeat=repeat, before_each=restore)
+        launches.append(uvmtier.lib().uvmtier_kernel_launch_count())
+        per_call = np.diff(launches)
+        assert (per_call == per_call[0]).all() and per_call[0] > 0     # replays count the kernels of the graph
+        ds.free()
+        k1, _, one = gpu_pipeline(ctx, pk, gp, tbl, lay, st0, run_cap=1 << 20)
+    assert got["get"] == put
+    # the copy-back through pinned memory carries what the device holds
+    assert np.array_equal(got["flags"], got["device_copies"]["flags"]) and np.array_equal(got["batch"], got["device_copies"]["batch"])
+    assert got["n_runs"] == int(got["device_copies"]["counters"][0])
+    want = S.run_service_oracle(T.load_oracle(), k1, gp, tbl, layout, st0, run_cap=1 << 20)
+    S.assert_service_equal(want, got, B, "streamed %s" % dist)
+    S.assert_service_equal(want, one, B, "one pass %s" % dist)

@@ -729,6 +729,15 @@ typedef struct {
     /* ce_hal->memcopy / block_copy_pages (UVM/uvm_va_block.c:3863-3991) for a list of pages */
     NV_STATUS (*copy_page_list)(uvmtier_ctx_t *, uint32_t dst_tier, uint32_t src_tier, size_t n, const uint64_t *h_dst_off,
                                 const uint64_t *h_src_off, uint32_t page_size, int method);
+    /* uvm_parent_gpu_service_replayable_faults (UVM/uvm_gpu_replayable_faults.c:2906-2960): the whole loop, from a
+     * ring in pinned host memory to the serviced batches, chunk by chunk */
+    NV_STATUS (*service_replayable_faults)(uvmtier_ctx_t *, const uvmtier_fault_packet_t *h_ring_pinned,
+                                           uvmtier_fault_packet_t *d_ring, uint32_t ring_entries, uint32_t get, uint32_t put,
+                                           int clear_valid, uint32_t chunk_batches, uint32_t *d_disposition,
+                                           uvmtier_ordered_fault_t *, uvmtier_fault_group_t *, uvmtier_fault_batch_t *,
+                                           const uvmtier_va_layout_t *, const uvmtier_block_state_t *, uint16_t *d_entry_flags,
+                                           uvmtier_service_group_t *, uvmtier_copy_run_t *, uint32_t run_cap,
+                                           uint32_t *d_counters, const uvmtier_service_readback_t *, uint32_t *out_get);
 } uvmtier_ops_t;
 
 /* The B200 implementation of every slot. */

@@ -288,4 +288,5 @@ extern "C" const uvmtier_ops_t uvmtier_gpu_ops = {
     uvmtier_make_resident_device,
     uvmtier_copy_runs_device,
     uvmtier_copy_page_list,
+    uvmtier_service_replayable_faults_streamed,
 };

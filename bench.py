@@ -289,6 +289,25 @@ def migration_numbers(ctx, lib, P, rank, world, dist, nbytes=256 << 20):
         peak = ctx.tier_memcpy_peak_gbs(dst, src, nbytes, 3)
         out["%s_to_%s" % (names[src], names[dst])] = {"GBs": round(gbs, 2), "copy_engine_peak_GBs": round(peak, 2),
                                                        "frac_of_link_peak": round(gbs / peak, 3)}
+    # the fork's CXL P2P DMA request (one contiguous range between the CXL buffer and HBM, 2 MB pages)
+    hnd = ctypes.c_void_p()
+    st = lib.uvmtier_p2p_register_cxl_buffer(ctx.handle, ctypes.c_void_p(info[TIER_CXL].host_ptr), ctypes.c_uint64(nbytes),
+                                             ctypes.c_uint32(2), ctypes.byref(hnd))
+    assert st == 0, hex(st)
+    for flag, key in ((1, "cxl_p2p_dma_cxl_to_gpu"), (0, "cxl_p2p_dma_gpu_to_cxl")):
+        best = 1e30
+        for r in range(4):
+            lib.uvmtier_event_record(ctx.handle, 900)
+            st = lib.uvmtier_p2p_cxl_dma_request(ctx.handle, hnd, ctypes.c_uint64(0), ctypes.c_uint64(0), ctypes.c_uint64(nbytes),
+                                                 ctypes.c_uint32(flag | 2), None)
+            assert st == 0, hex(st)
+            lib.uvmtier_event_record(ctx.handle, 901)
+            lib.uvmtier_event_elapsed_ms(ctx.handle, 900, 901, ctypes.byref(ms))
+            if r:
+                best = min(best, ms.value)
+        peak = out["cxl_to_hbm" if flag else "hbm_to_cxl"]["copy_engine_peak_GBs"]
+        out[key] = {"GBs": round(nbytes / (best * 1e-3) / 1e9, 2), "frac_of_link_peak": round(nbytes / (best * 1e-3) / 1e9 / peak, 3)}
+    assert lib.uvmtier_p2p_unregister_cxl_buffer(ctx.handle, hnd) == 0
     if dist is not None and world > 1:
         # NVLink peer push: every rank copies its HBM arena into the next rank's (ring), all at once
         import torch

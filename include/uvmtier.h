@@ -45,7 +45,9 @@ typedef uint32_t NV_STATUS;
 #define NV_ERR_NO_MEMORY                   0x00000051u
 #define NV_ERR_NOT_SUPPORTED               0x00000056u
 #define NV_ERR_INVALID_CHANNEL             0x00000024u
-#define NV_ERR_GPU_NOT_FULL_POWER          0x0000001Au /* used for "no usable CUDA device" */
+#define NV_ERR_GPU_NOT_FULL_POWER          0x00000011u /* used for "no usable CUDA device" */
+#define NV_ERR_GPU_IS_LOST                 0x0000000Fu
+#define NV_ERR_INSUFFICIENT_RESOURCES      0x0000001Au
 #define NV_WARN_MISMATCHED_TARGET          0x00010004u
 #define NV_WARN_MORE_PROCESSING_REQUIRED   0x00010005u
 #endif
@@ -690,6 +692,51 @@ NV_STATUS uvmtier_checksum_pages_device(uvmtier_ctx_t *ctx, uint32_t tier, size_
  * "measured link peak" the copy kernels are compared with. */
 NV_STATUS uvmtier_tier_memcpy_peak(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t src_tier, uint64_t bytes, int reps,
                                    float *out_best_ms);
+
+/* ------------------------------------------------------------------------------------------ */
+/* (3b) The fork's CXL P2P DMA surface -- src/nvidia/src/kernel/mem_mgr/p2p_cxl.c              */
+/* ------------------------------------------------------------------------------------------ */
+/* What CXLMemUring added to the driver as a second front door to the copy path: register a CXL-backed buffer,
+ * ask for DMA between it and GPU memory, unregister (RM controls NV2080_CTRL_CMD_BUS_REGISTER_CXL_BUFFER /
+ * _CXL_P2P_DMA_REQUEST / _UNREGISTER_CXL_BUFFER, src/common/sdk/nvidia/inc/ctrl/ctrl2080/ctrl2080bus.h:1400-1560;
+ * user-space flow tests/cxl_p2p_test.c:532-632).  Same validation rules, limits and status codes; the copy is
+ * this library's TMA page-copy pipeline instead of memmgrMemCopy on a copy engine.
+ *
+ * Differences a user-space library cannot avoid: the buffer is pinned with cudaHostRegister (the reference pins
+ * with pin_user_pages, kernel-open/nvidia/nv-p2p.c:1140-1260), the "physical" page array holds the pages' host
+ * virtual addresses, and gpuOffset is an offset into this context's HBM tier (the reference: an FB offset). */
+#define UVMTIER_CXL_P2P_PAGE_SIZE_4K          4096u          /* p2p_cxl.c:38-39 */
+#define UVMTIER_CXL_P2P_PAGE_SIZE_2M          (2u << 20)
+#define UVMTIER_CXL_P2P_MAX_BUFFER_SIZE       (1ull << 40)   /* :218 */
+#define UVMTIER_CXL_P2P_MAX_REGISTERED_BUFFERS 256u          /* :221 */
+#define UVMTIER_CXL_P2P_DMA_FLAG_CXL_TO_GPU   0x1u           /* :35; clear = GPU to CXL */
+#define UVMTIER_CXL_P2P_DMA_FLAG_ASYNC        0x2u           /* ctrl2080bus.h:1495: enqueue only */
+#define UVMTIER_CXL_P2P_DMA_MAX_TRANSFER      0xFFFFF000ull  /* a request above 4 GB - 1 is clamped to this (:617-622) */
+typedef struct uvmtier_cxl_buffer uvmtier_cxl_buffer_t;
+
+/* RmP2PGetCxlSystemInfo (:99-137): CXL memory devices = CPU-less NUMA nodes with memory; version 2 when none is
+ * found (the reference's default when enumeration fails).  Any out pointer may be NULL. */
+NV_STATUS uvmtier_p2p_get_cxl_system_info(uint32_t *num_devices, uint32_t *num_memory_devices, uint32_t *link_up,
+                                          uint32_t *cxl_version);
+/* RmP2PRegisterCxlBuffer (:225-352).  NV_ERR_INVALID_ARGUMENT: size 0, NULL out, version outside 1..3, size above
+ * 1 TB, base + size overflow; NV_ERR_INSUFFICIENT_RESOURCES: 256 buffers registered already.  2 MB pages when base
+ * and size are 2 MB multiples (_cxlP2PCanUseHugePages :149-160), else 4 KB pages covering [base, base + size). */
+NV_STATUS uvmtier_p2p_register_cxl_buffer(uvmtier_ctx_t *ctx, void *base, uint64_t size, uint32_t cxl_version,
+                                          uvmtier_cxl_buffer_t **out_handle);
+/* RmP2PUnregisterCxlBuffer (:361-421): NV_ERR_INVALID_ARGUMENT for NULL, NV_ERR_INVALID_STATE if not registered. */
+NV_STATUS uvmtier_p2p_unregister_cxl_buffer(uvmtier_ctx_t *ctx, uvmtier_cxl_buffer_t *handle);
+/* RmP2PGetCxlPages (:423-481) / RmP2PPutCxlPages (:483-514): the page array of [offset, offset + size). */
+NV_STATUS uvmtier_p2p_get_cxl_pages(uvmtier_cxl_buffer_t *handle, uint64_t offset, uint64_t size, uint64_t *page_addrs,
+                                    uint32_t *page_count, uint32_t *page_size);
+NV_STATUS uvmtier_p2p_put_cxl_pages(uvmtier_cxl_buffer_t *handle, uint64_t offset, uint64_t size);
+/* RmP2PCxlDmaRequest (:516-677): copies min(size, UVMTIER_CXL_P2P_DMA_MAX_TRANSFER) bytes between
+ * HBM tier + gpu_offset and buffer + cxl_offset.  NV_ERR_INVALID_ARGUMENT: NULL ctx / handle, size 0, range
+ * outside the buffer (or outside the HBM tier); NV_ERR_INVALID_STATE: buffer not registered, no HBM tier.
+ * Waits for the copy unless UVMTIER_CXL_P2P_DMA_FLAG_ASYNC is set.  *out_bytes (may be NULL) = bytes moved. */
+NV_STATUS uvmtier_p2p_cxl_dma_request(uvmtier_ctx_t *ctx, uvmtier_cxl_buffer_t *handle, uint64_t gpu_offset,
+                                      uint64_t cxl_offset, uint64_t size, uint32_t flags, uint64_t *out_bytes);
+/* Registered buffers / bytes in this process (g_cxlRegisteredBufferCount, g_cxlTotalRegisteredSize :143-144). */
+void uvmtier_p2p_cxl_registered(uint32_t *count, uint64_t *bytes);
 
 /* ------------------------------------------------------------------------------------------ */
 /* Ops table -- the reference dispatches through per-arch function-pointer tables chosen at GPU */

@@ -475,3 +475,272 @@ NV_STATUS uvmtier_tier_memcpy_peak(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// The fork's CXL P2P DMA surface (include/uvmtier.h section 3b; src/nvidia/src/kernel/mem_mgr/p2p_cxl.c).
+// Registration pins the buffer and builds its page array; a DMA request is one contiguous range between the HBM
+// tier and the buffer, moved by the page-copy pipeline above (4 KB pieces through TMA) with a small load/store
+// kernel for what does not fill a piece or is not 16-byte aligned.
+struct uvmtier_cxl_buffer {
+    uint64_t magic;
+    void *base;               // baseAddress
+    uint8_t *device_base;     // the address the kernels use
+    uint64_t size;
+    uint32_t cxl_version;
+    uint32_t page_count, page_size;
+    uint64_t *pages;          // pPageArray
+    bool registered, huge, pinned_here;
+    void *pin_base;           // what cudaHostRegister was given: the whole pages around [base, base + size)
+    int device;
+};
+static const uint64_t kCxlMagic = 0x43584C5032504255ull;   // "CXLP2PBU"
+static std::atomic<uint32_t> g_cxl_count{0};               // g_cxlRegisteredBufferCount (p2p_cxl.c:143)
+static std::atomic<uint64_t> g_cxl_bytes{0};               // g_cxlTotalRegisteredSize (:144)
+
+// Bytes that the 4 KB pipeline does not take: any alignment, any length.
+static __global__ void __launch_bounds__(256) k_copy_bytes(uint8_t *dst, const uint8_t *src, uint64_t n)
+{
+    const uint64_t tid = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x, nth = (uint64_t)gridDim.x * blockDim.x;
+    if ((((uintptr_t)dst | (uintptr_t)src) & 15u) == 0) {
+        const uint64_t n16 = n / 16;
+        for (uint64_t i = tid; i < n16; i += nth)
+            ((uint4 *)dst)[i] = ((const uint4 *)src)[i];
+        for (uint64_t i = n16 * 16 + tid; i < n; i += nth)
+            dst[i] = src[i];
+    }
+    else {
+        for (uint64_t i = tid; i < n; i += nth)
+            dst[i] = src[i];
+    }
+}
+
+extern "C" {
+
+NV_STATUS uvmtier_p2p_get_cxl_system_info(uint32_t *num_devices, uint32_t *num_memory_devices, uint32_t *link_up,
+                                          uint32_t *cxl_version)
+{
+    // nv_enumerate_cxl_devices walks the PCI bus for CXL DVSECs; what user space sees of a CXL memory expander is
+    // a NUMA node with memory and no CPUs
+    uint32_t n = 0;
+    DIR *d = opendir("/sys/devices/system/node");
+    if (d) {
+        struct dirent *e;
+        while ((e = readdir(d)) != NULL) {
+            int node;
+            if (sscanf(e->d_name, "node%d", &node) != 1)
+                continue;
+            char path[128], buf[256];
+            snprintf(path, sizeof(path), "/sys/devices/system/node/node%d/cpulist", node);
+            const int got = read_small_file(path, buf, sizeof(buf));
+            bool has_cpus = false;
+            for (int i = 0; i < got; i++)
+                if (buf[i] >= '0' && buf[i] <= '9')
+                    has_cpus = true;
+            if (got >= 0 && !has_cpus)
+                n++;
+        }
+        closedir(d);
+    }
+    if (num_devices) *num_devices = n;
+    if (num_memory_devices) *num_memory_devices = n;
+    if (link_up) *link_up = n > 0;
+    if (cxl_version) *cxl_version = 2;                     // the reference's default (:118-126)
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_p2p_register_cxl_buffer(uvmtier_ctx_t *ctx, void *base, uint64_t size, uint32_t cxl_version,
+                                          uvmtier_cxl_buffer_t **out_handle)
+{
+    const uint64_t addr = (uint64_t)(uintptr_t)base;
+    if (!ctx || size == 0 || !out_handle || cxl_version < 1 || cxl_version > 3)       // :241-246
+        return NV_ERR_INVALID_ARGUMENT;
+    if (size > UVMTIER_CXL_P2P_MAX_BUFFER_SIZE)                                       // :248-253
+        return NV_ERR_INVALID_ARGUMENT;
+    if (addr + size < addr)                                                           // :255-260
+        return NV_ERR_INVALID_ARGUMENT;
+    if (g_cxl_count.load() >= UVMTIER_CXL_P2P_MAX_REGISTERED_BUFFERS)                 // :262-267
+        return NV_ERR_INSUFFICIENT_RESOURCES;
+    if (!base)
+        return NV_ERR_INVALID_ADDRESS;                                                // pinning address 0 fails
+    uvmtier_cxl_buffer *h = (uvmtier_cxl_buffer *)calloc(1, sizeof(*h));
+    if (!h)
+        return NV_ERR_NO_MEMORY;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    // pin + map: memory that is registered already (one of this library's host tiers, or the caller's own
+    // cudaHostRegister) is used as it is
+    void *dptr = NULL;
+    if (cudaHostGetDevicePointer(&dptr, base, 0) != cudaSuccess) {
+        cudaGetLastError();
+        h->pin_base = (void *)(uintptr_t)(addr & ~(uint64_t)4095);
+        const uint64_t pin_bytes = ((addr + size + 4095) & ~(uint64_t)4095) - (addr & ~(uint64_t)4095);
+        const cudaError_t e = cudaHostRegister(h->pin_base, pin_bytes, cudaHostRegisterMapped | cudaHostRegisterPortable);
+        if (e != cudaSuccess) {
+            uvmtier_set_error("cudaHostRegister (CXL buffer)", e, __FILE__, __LINE__);
+            cudaGetLastError();
+            free(h);
+            return e == cudaErrorMemoryAllocation ? NV_ERR_NO_MEMORY : NV_ERR_INVALID_ADDRESS;
+        }
+        h->pinned_here = true;
+        if (cudaHostGetDevicePointer(&dptr, base, 0) != cudaSuccess) {
+            cudaGetLastError();
+            cudaHostUnregister(h->pin_base);
+            free(h);
+            return NV_ERR_INVALID_STATE;
+        }
+    }
+    // _cxlP2PCanUseHugePages (:149-160), else 4 KB pages spanning the range (nv-p2p.c:1166-1167)
+    h->huge = (addr & (UVMTIER_CXL_P2P_PAGE_SIZE_2M - 1)) == 0 && (size & (UVMTIER_CXL_P2P_PAGE_SIZE_2M - 1)) == 0 &&
+              size >= UVMTIER_CXL_P2P_PAGE_SIZE_2M;
+    h->page_size = h->huge ? UVMTIER_CXL_P2P_PAGE_SIZE_2M : UVMTIER_CXL_P2P_PAGE_SIZE_4K;
+    const uint64_t start = h->huge ? addr : (addr & ~(uint64_t)4095);
+    const uint64_t count = h->huge ? size / UVMTIER_CXL_P2P_PAGE_SIZE_2M : ((addr + size - 1) >> 12) - (start >> 12) + 1;
+    if (count == 0 || count > (1ull << 28)) {                                         // nv-p2p.c:1169-1174
+        if (h->pinned_here) cudaHostUnregister(h->pin_base);
+        free(h);
+        return NV_ERR_INVALID_ARGUMENT;
+    }
+    h->pages = (uint64_t *)malloc(count * sizeof(uint64_t));
+    if (!h->pages) {
+        if (h->pinned_here) cudaHostUnregister(h->pin_base);
+        free(h);
+        return NV_ERR_NO_MEMORY;
+    }
+    for (uint64_t i = 0; i < count; i++)
+        h->pages[i] = start + i * h->page_size;
+    h->magic = kCxlMagic;
+    h->base = base;
+    h->device_base = (uint8_t *)dptr;
+    h->size = size;
+    h->cxl_version = cxl_version;
+    h->page_count = (uint32_t)count;
+    h->registered = true;
+    h->device = ctx->device;
+    g_cxl_count.fetch_add(1);
+    g_cxl_bytes.fetch_add(size);
+    *out_handle = h;
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_p2p_unregister_cxl_buffer(uvmtier_ctx_t *ctx, uvmtier_cxl_buffer_t *h)
+{
+    if (!h || h->magic != kCxlMagic)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!h->registered)
+        return NV_ERR_INVALID_STATE;
+    h->registered = false;
+    if (ctx) {
+        cudaSetDevice(ctx->device);
+        cudaStreamSynchronize(ctx->stream);                // a request may still be in flight (ASYNC)
+    }
+    if (h->pinned_here)
+        cudaHostUnregister(h->pin_base);
+    free(h->pages);
+    h->pages = NULL;
+    const uint64_t size = h->size;
+    h->magic = 0;
+    free(h);
+    if (g_cxl_count.load() > 0)
+        g_cxl_count.fetch_sub(1);
+    if (g_cxl_bytes.load() >= size)
+        g_cxl_bytes.fetch_sub(size);
+    else
+        g_cxl_bytes.store(0);
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_p2p_get_cxl_pages(uvmtier_cxl_buffer_t *h, uint64_t offset, uint64_t size, uint64_t *page_addrs,
+                                    uint32_t *page_count, uint32_t *page_size)
+{
+    if (!h || h->magic != kCxlMagic || !page_addrs || !page_count || !page_size)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!h->registered)
+        return NV_ERR_INVALID_STATE;
+    if (offset + size > h->size)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t start = (uint32_t)(offset / h->page_size);
+    const uint32_t n = (uint32_t)((offset + size + h->page_size - 1) / h->page_size) - start;
+    if (start + n > h->page_count)
+        return NV_ERR_INVALID_ARGUMENT;
+    for (uint32_t i = 0; i < n; i++)
+        page_addrs[i] = h->pages[start + i];
+    *page_count = n;
+    *page_size = h->page_size;
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_p2p_put_cxl_pages(uvmtier_cxl_buffer_t *h, uint64_t offset, uint64_t size)
+{
+    (void)offset; (void)size;
+    if (!h || h->magic != kCxlMagic)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!h->registered)
+        return NV_ERR_INVALID_STATE;
+    return NV_OK;                                          // pages stay pinned until unregistration (:506-513)
+}
+
+NV_STATUS uvmtier_p2p_cxl_dma_request(uvmtier_ctx_t *ctx, uvmtier_cxl_buffer_t *h, uint64_t gpu_offset, uint64_t cxl_offset,
+                                      uint64_t size, uint32_t flags, uint64_t *out_bytes)
+{
+    if (out_bytes)
+        *out_bytes = 0;
+    if (!ctx || !h || h->magic != kCxlMagic || size == 0)                             // :535-551
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!h->registered)                                                               // :553-557
+        return NV_ERR_INVALID_STATE;
+    if (cxl_offset > h->size || size > h->size - cxl_offset)                          // :559-565
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers || !ctx->tiers->t[UVMTIER_TIER_HBM].used)
+        return NV_ERR_INVALID_STATE;
+    const uvmtier_tier_info_t *hbm = &ctx->tiers->t[UVMTIER_TIER_HBM].info;
+    uint64_t bytes = size;
+    if (bytes > 0xFFFFFFFFull)                                                        // :617-622
+        bytes = UVMTIER_CXL_P2P_DMA_MAX_TRANSFER;
+    if (gpu_offset > hbm->bytes || bytes > hbm->bytes - gpu_offset)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    const bool to_gpu = (flags & UVMTIER_CXL_P2P_DMA_FLAG_CXL_TO_GPU) != 0;
+    uint8_t *gpu = (uint8_t *)hbm->device_ptr + gpu_offset, *cxl = h->device_base + cxl_offset;
+    uint8_t *dst = to_gpu ? gpu : cxl;
+    const uint8_t *src = to_gpu ? cxl : gpu;
+    uint64_t body = 0;
+    if ((((uintptr_t)dst | (uintptr_t)src) & 15u) == 0) {
+        // whole 4 KB pieces through the TMA pipeline: 2 MB "pages" first (one list-free linear range), then 4 KB ones
+        copy_list_params p;
+        p.src_off = NULL;
+        p.dst_off = NULL;
+        const uint64_t big = bytes >> 21, small = (bytes - (big << 21)) >> 12;
+        if (big) {
+            p.src_base = src; p.dst_base = dst; p.n_pages = big; p.pieces_per_page = 512;
+            const NV_STATUS st = launch_copy(ctx, p, 0);
+            if (st != NV_OK)
+                return st;
+        }
+        if (small) {
+            p.src_base = src + (big << 21); p.dst_base = dst + (big << 21); p.n_pages = small; p.pieces_per_page = 1;
+            const NV_STATUS st = launch_copy(ctx, p, 0);
+            if (st != NV_OK)
+                return st;
+        }
+        body = (big << 21) + (small << 12);
+    }
+    if (body < bytes) {
+        const uint64_t rest = bytes - body;
+        uint64_t grid = (rest / 16 + 255) / 256 + 1;
+        if (grid > (uint64_t)ctx->sm_count * 8)
+            grid = (uint64_t)ctx->sm_count * 8;
+        UVMTIER_LAUNCH(k_copy_bytes, (int)grid, 256, 0, ctx->stream, dst + body, src + body, rest);
+    }
+    if (out_bytes)
+        *out_bytes = bytes;
+    if (!(flags & UVMTIER_CXL_P2P_DMA_FLAG_ASYNC))
+        UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    return NV_OK;
+}
+
+void uvmtier_p2p_cxl_registered(uint32_t *count, uint64_t *bytes)
+{
+    if (count) *count = g_cxl_count.load();
+    if (bytes) *bytes = g_cxl_bytes.load();
+}
+
+} // extern "C"

@@ -28,7 +28,7 @@ constexpr uint32_t kCopyThreads = 32;
 struct copy_list_params {
     const uint8_t *src_base;
     uint8_t *dst_base;
-    const uint64_t *src_off;     // per page
+    const uint64_t *src_off;     // per page; NULL = page i at i * page size (one contiguous range)
     const uint64_t *dst_off;
     uint64_t n_pages;
     uint32_t pieces_per_page;    // page_size / 4096
@@ -76,8 +76,9 @@ __device__ __forceinline__ void piece_addr(const copy_list_params &p, uint64_t u
 {
     const uint64_t page = u / p.pieces_per_page;
     const uint64_t within = (u - page * p.pieces_per_page) * kPiece;
-    *src = p.src_base + p.src_off[page] + within;
-    *dst = p.dst_base + p.dst_off[page] + within;
+    const uint64_t lin = page * p.pieces_per_page * kPiece;
+    *src = p.src_base + (p.src_off ? p.src_off[page] : lin) + within;
+    *dst = p.dst_base + (p.dst_off ? p.dst_off[page] : lin) + within;
 }
 
 // Persistent TMA pipeline.  kCtasPerSm CTAs of one warp per SM; CTA c takes items c, c + grid, ... (an item =
@@ -115,8 +116,9 @@ __global__ void __launch_bounds__(kCopyThreads, kCtasPerSm) k_copy_pages_tma(cop
         if (k < my_items && u < n_pieces) {
             const uint64_t page = u >> ppp_shift;
             const uint64_t within = (u & (p.pieces_per_page - 1)) * kPiece;
-            my_src = p.src_base + p.src_off[page] + within;
-            my_dst = p.dst_base + p.dst_off[page] + within;
+            const uint64_t lin = page << (ppp_shift + 12);                 // kPiece = 4096
+            my_src = p.src_base + (p.src_off ? p.src_off[page] : lin) + within;
+            my_dst = p.dst_base + (p.dst_off ? p.dst_off[page] : lin) + within;
         }
     };
     auto load = [&](uint64_t k) {                      // all lanes call; lane 0 issues

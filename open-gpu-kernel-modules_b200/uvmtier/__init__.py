@@ -384,6 +384,32 @@ class Context:
                                             ctypes.c_size_t(len(dst_off)), P(dst_off), P(src_off), ctypes.c_uint32(page_size),
                                             ctypes.c_int(method)), "uvmtier_copy_page_list")
 
+    # ---- (3b) the fork's CXL P2P DMA surface ----
+    def p2p_register_cxl_buffer(self, base_addr, size, cxl_version=2):
+        """uvmtier_p2p_register_cxl_buffer -> (status, handle).  Does not raise: the status is what callers test."""
+        h = ctypes.c_void_p()
+        st = lib().uvmtier_p2p_register_cxl_buffer(self._h, ctypes.c_void_p(base_addr), ctypes.c_uint64(size),
+                                                   ctypes.c_uint32(cxl_version), ctypes.byref(h))
+        return int(st), h
+
+    def p2p_unregister_cxl_buffer(self, handle):
+        return int(lib().uvmtier_p2p_unregister_cxl_buffer(self._h, handle))
+
+    def p2p_get_cxl_pages(self, handle, offset, size, cap=1 << 20):
+        """-> (status, page addresses, page size)"""
+        addrs = np.zeros(cap, "<u8")
+        n, ps = ctypes.c_uint32(0), ctypes.c_uint32(0)
+        st = lib().uvmtier_p2p_get_cxl_pages(handle, ctypes.c_uint64(offset), ctypes.c_uint64(size), P(addrs), ctypes.byref(n),
+                                             ctypes.byref(ps))
+        return int(st), addrs[:n.value].copy(), ps.value
+
+    def p2p_cxl_dma_request(self, handle, gpu_offset, cxl_offset, size, flags=0):
+        """-> (status, bytes moved)"""
+        moved = ctypes.c_uint64(0)
+        st = lib().uvmtier_p2p_cxl_dma_request(self._h, handle, ctypes.c_uint64(gpu_offset), ctypes.c_uint64(cxl_offset),
+                                               ctypes.c_uint64(size), ctypes.c_uint32(flags), ctypes.byref(moved))
+        return int(st), moved.value
+
     def checksum_pages(self, tier, off, page_size):
         off = np.ascontiguousarray(off, "<u8")
         d_off = self.to_device(off); d_out = self.alloc(len(off) * 8)

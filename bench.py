@@ -66,6 +66,8 @@ class ClockSampler(threading.Thread):
          "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
          "clocks_event_reasons.sw_power_cap")
 
+    PAD = 0.06
+
     def __init__(self, index):
         super().__init__(daemon=True)
         self.index = index
@@ -88,7 +90,10 @@ class ClockSampler(threading.Thread):
         sm, mx, reasons, n_in = [], 0, set(), 0
         for t, r in self.rows:
             try:
-                inside = any(a <= t <= b for a, b in windows) if windows else True
+                # the timed regions last a few milliseconds and nvidia-smi answers every 50 ms: a sample counts when it
+                # falls within one sampling period of a timed region (the GPU runs the warm-up steps right before it
+                # and the next phase right after it, so it is under the same load)
+                inside = any(a - self.PAD <= t <= b + self.PAD for a, b in windows) if windows else True
                 mx = max(mx, float(r[2]))
                 if not inside:
                     continue

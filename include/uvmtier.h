@@ -545,6 +545,89 @@ NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n_requests,
                                        uint32_t run_cap, uint32_t *d_counters);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (1d) Which HBM root chunk to evict -- UVM/uvm_pmm_gpu.c:1395-1500                           */
+/* ------------------------------------------------------------------------------------------ */
+/* The reference keeps every allocated 2 MB root chunk on one of two lists, root_chunks.va_block_unused (its
+ * va_block has no page resident on the GPU) and root_chunks.va_block_used; every list move goes to the tail
+ * (root_chunk_update_eviction_list :1430-1448), and pick_root_chunk_to_evict (:1460-1500) takes the head of
+ * the unused list, else the head of the used list: least recently serviced first.  A va_block of the state table
+ * is one root chunk (2 MB blocks, UVM/uvm_va_block.c:3547-3566), so the two lists are one 64-bit stamp per slot:
+ *   0                          the va_block holds no root chunk
+ *   bit 63 | sequence number   on va_block_used;  bit 63 clear: on va_block_unused
+ * where the sequence number is that of the last move.  The moves come from block_mark_memory_used (after every
+ * make_resident that leaves the GPU with resident pages, :5076-5077 and the fault path), from
+ * block_clear_resident_processor (the GPU's last page left, :3579-3603), from chunk allocation
+ * (chunk_update_lists_locked :639-643) and from the free after an eviction; they are applied by the two
+ * "note" calls below, in the order the reference would have made them ((batch, run) order of a servicing pass,
+ * request order of a make_resident call). */
+#define UVMTIER_PMM_USED (1ull << 63)
+typedef struct {
+    uint64_t *d_stamp;               /* [n_slots], device */
+    uint32_t *d_scratch;             /* working space of the calls below, device */
+    uint64_t  clock;                 /* sequence numbers handed out so far */
+    uint32_t  n_slots;
+    uint32_t  capacity_chunks;       /* root chunks HBM can hold: what the caller keeps chunks_in_use below */
+} uvmtier_pmm_t;
+NV_STATUS uvmtier_pmm_create(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uint32_t capacity_chunks,
+                             uvmtier_pmm_t *out);
+NV_STATUS uvmtier_pmm_destroy(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm);
+/* The list moves of one servicing pass (d_service as written by uvmtier_service_fault_batches_device for
+ * n_batches batches): every serviced run moves its va_block to the tail of va_block_used. */
+NV_STATUS uvmtier_pmm_note_service_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
+                                          const uvmtier_fault_batch_t *d_batches, const uvmtier_service_group_t *d_service);
+/* The list moves of one uvmtier_make_resident_device call: to the GPU -> tail of va_block_used; the GPU's last
+ * pages left -> tail of va_block_unused; an UVMTIER_MR_EVICT_GPU_PAGES request that emptied the GPU -> the chunk
+ * is freed (stamp 0), as evict_root_chunk does after uvm_va_block_evict_chunks (:1290-1380). */
+NV_STATUS uvmtier_pmm_note_make_resident_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_requests,
+                                                const uvmtier_make_resident_req_t *d_requests,
+                                                const uvmtier_make_resident_result_t *d_results,
+                                                const uvmtier_block_state_t *state);
+/* How many va_blocks touched by these preprocessed batches hold no root chunk (each needs one when it is
+ * serviced: block_populate_gpu_chunk, UVM/uvm_va_block.c:2974-3049), and how many chunks are in use now:
+ * d_out[0] = needed, d_out[1] = in use. */
+NV_STATUS uvmtier_pmm_count_needed_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
+                                          const uvmtier_fault_group_t *d_groups, const uvmtier_fault_batch_t *d_batches,
+                                          const uvmtier_va_layout_t *layout, uint32_t *d_out);
+/* pick_root_chunk_to_evict, k times: writes one eviction request per victim (whole block, cause EVICTION, flag
+ * UVMTIER_MR_EVICT_GPU_PAGES, destination dest_tier = UVMTIER_TIER_DRAM or _CXL) to d_requests[0 .. *d_count),
+ * in no particular order; fewer than k when fewer chunks are allocated.  The victims keep their stamps until
+ * uvmtier_pmm_note_make_resident_device sees their evictions. */
+NV_STATUS uvmtier_pmm_pick_chunks_to_evict_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t k, uint32_t dest_tier,
+                                                  uvmtier_make_resident_req_t *d_requests, uint32_t *d_count);
+/* Pages resident on the GPU, on CPU node 0 (DRAM) and on CPU node 1 (CXL): d_out[0..2]. */
+NV_STATUS uvmtier_block_state_count_pages_device(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout,
+                                                 const uvmtier_block_state_t *state, uint32_t *d_out);
+
+/* Servicing under HBM oversubscription (BASELINE config D): the preprocessed batches are serviced in chunks of
+ * chunk_batches batches; before a chunk is serviced, room is made for the root chunks it needs --
+ *     k = chunks in use + chunks needed - pmm->capacity_chunks  victims
+ * are picked in the reference's order (pick_root_chunk_to_evict), evicted with make_resident (cause EVICTION) and
+ * their pages copied out; then the chunk is serviced and its pages copied in.  The reference evicts on demand, one
+ * root chunk at a time, when block_populate_gpu_chunk finds no free chunk (UVM/uvm_pmm_gpu.c:1502-1560); evicting a
+ * chunk's worth ahead takes the same victims from the same lists as long as no victim is faulted on again within the
+ * chunk of batches (then the reference would have evicted it a little later) -- chunk_batches = 1 is the closest.
+ * Where evicted pages go is this library's policy, the reference has none: host DRAM while it holds
+ * fewer than dram_capacity_pages pages of this table, the CXL node after that.
+ * d_entry_flags / d_service / d_batches are filled as by uvmtier_service_fault_batches_device; the copy runs are
+ * consumed chunk by chunk (execute_copies != 0 runs them through uvmtier_copy_runs_device: the tiers must exist),
+ * record.run_offset counts within the record's chunk.  Synchronises once per chunk (two counters cross to the host). */
+typedef struct {
+    uint32_t passes;                 /* chunks of batches serviced */
+    uint32_t eviction_waves;
+    uint32_t evicted_to_dram, evicted_to_cxl;   /* root chunks */
+    uint32_t peak_chunks_in_use, chunks_in_use; /* after the last pass */
+    uint64_t pages_evicted, pages_promoted;     /* pages copied out of / into HBM (first touch included) */
+    uint32_t reserved[4];
+} uvmtier_tiering_stats_t;
+NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
+                                                      const uvmtier_ordered_fault_t *d_ordered,
+                                                      const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                      const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                                      uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                      uint32_t chunk_batches, uint64_t dram_capacity_pages, int execute_copies,
+                                                      uvmtier_tiering_stats_t *out_stats);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */
 

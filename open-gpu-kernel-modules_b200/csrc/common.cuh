@@ -52,6 +52,13 @@ NV_STATUS uvmtier_fetch_preprocess_on_stream(struct uvmtier_ctx *ctx, cudaStream
                                              uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
                                              uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
 
+// uvmtier_service_fault_batches_device for one chunk of a longer trace (service.cu)
+NV_STATUS uvmtier_service_pass_chunk(struct uvmtier_ctx *ctx, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,
+                                     const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                     const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
+                                     uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t run_cap,
+                                     uint32_t *d_counters, uint32_t batch_base);
+
 struct uvmtier_ctx {
     int device;
     int sm_count;

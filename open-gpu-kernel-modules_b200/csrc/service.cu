@@ -340,6 +340,27 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
 
 } // extern "C"
 
+// A servicing pass over one chunk of a longer trace (pmm.cu): d_* point at the chunk, records carry batch numbers
+// from batch_base, the counters and entry flags are the caller's to zero.
+NV_STATUS uvmtier_service_pass_chunk(uvmtier_ctx_t *ctx, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,
+                                     const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                     const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
+                                     uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t run_cap,
+                                     uint32_t *d_counters, uint32_t batch_base)
+{
+    const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                                            d_runs, run_cap, d_counters);
+    if (ok != NV_OK || !n_batches)
+        return ok;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    const NV_STATUS st = service_scratch_reserve(ctx, lay->n_spaces * lay->blocks_per_space, n_batches,
+                                                 (size_t)n_batches * ctx->faults->gp.max_batch_size);
+    if (st != NV_OK)
+        return st;
+    return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service, d_runs,
+                        run_cap, d_counters, batch_base, false);
+}
+
 // Everything uvmtier_service_replayable_faults_streamed puts on the three streams.  Streams, events and working
 // space exist already (streamed_prepare), so this is pure enqueueing and can run under stream capture.
 struct streamed_args {

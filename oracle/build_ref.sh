@@ -88,3 +88,11 @@ if [ -f "$HERE/ref_resident_glue.c" ]; then
         -o "$OUT/libref_resident.so"
     echo "build_ref: built $OUT/libref_resident.so"
 fi
+
+# ---------------- PMM leg: the eviction order (pick_root_chunk_to_evict and the list moves), verbatim ----------------
+if [ -f "$HERE/ref_pmm_glue.c" ]; then
+    pin uvm_pmm_gpu.c 579fbaf9e0b9de07
+    sed -n '1395,1414p;1416,1428p;1430,1448p;1450,1458p;1460,1500p' "$UVM/uvm_pmm_gpu.c" > "$TMP/x_pmm.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_pmm_glue.c" -o "$OUT/libref_pmm.so"
+    echo "build_ref: built $OUT/libref_pmm.so"
+fi

@@ -210,25 +210,30 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
     for (uint32_t b0 = 0; b0 < n_batches; b0 += chunk_batches) {
         const uint32_t nb = n_batches - b0 < chunk_batches ? n_batches - b0 : chunk_batches;
         const size_t e0 = (size_t)b0 * B;
-        // how many root chunks this chunk of batches needs, how many are in use, where the pages are
-        st = uvmtier_pmm_count_needed_device(ctx, pmm, nb, d_groups + e0, d_batches + b0, lay, d_cnt);
-        if (st != NV_OK)
-            return st;
-        st = uvmtier_block_state_count_pages_device(ctx, lay, state, d_cnt + 2);
-        if (st != NV_OK)
-            return st;
-        UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-        UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-        if (h_cnt[6] > evict_run_cap || h_cnt[8] > svc_run_cap)           // the chunk before this one: its copy list was cut
-            return NV_ERR_NO_MEMORY;
-        const uint32_t needed = h_cnt[0], in_use = h_cnt[1];
-        const uint64_t dram_pages = h_cnt[3];
-        uint32_t k = (uint64_t)in_use + needed > pmm->capacity_chunks ? in_use + needed - pmm->capacity_chunks : 0;
-        if (k > in_use)
-            k = in_use;                                                   // the chunk alone overflows HBM: evict all there is
-        if (k > kmax)
-            k = kmax;
-        if (k) {
+        // Make room: count what the chunk needs, evict the overflow, count again -- a victim that this very chunk of
+        // batches faults on comes back and needs a chunk again, so the second count can ask for a few more.
+        uint32_t needed = 0, in_use = 0;
+        for (int round = 0; round < 8; round++) {
+            st = uvmtier_pmm_count_needed_device(ctx, pmm, nb, d_groups + e0, d_batches + b0, lay, d_cnt);
+            if (st != NV_OK)
+                return st;
+            st = uvmtier_block_state_count_pages_device(ctx, lay, state, d_cnt + 2);
+            if (st != NV_OK)
+                return st;
+            UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+            if (h_cnt[6] > evict_run_cap || h_cnt[8] > svc_run_cap)       // an earlier copy list was cut
+                return NV_ERR_NO_MEMORY;
+            needed = h_cnt[0];
+            in_use = h_cnt[1];
+            const uint64_t dram_pages = h_cnt[3];
+            uint32_t k = (uint64_t)in_use + needed > pmm->capacity_chunks ? in_use + needed - pmm->capacity_chunks : 0;
+            if (k > in_use)
+                k = in_use;                                               // the chunk alone overflows HBM: evict all there is
+            if (k > kmax)
+                k = kmax;
+            if (!k)
+                break;
             const uint32_t dest = dram_pages + (uint64_t)k * UVMTIER_PAGES_PER_VA_BLOCK <= dram_capacity_pages ? UVMTIER_TIER_DRAM
                                                                                                                 : UVMTIER_TIER_CXL;
             st = uvmtier_pmm_pick_chunks_to_evict_device(ctx, pmm, k, dest, d_req, d_cnt + 5);
@@ -250,6 +255,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
             }
             stats.eviction_waves++;
             if (dest == UVMTIER_TIER_DRAM) stats.evicted_to_dram += k; else stats.evicted_to_cxl += k;
+            in_use -= k;                                                  // what the next count will find (if there is none)
         }
         // service the chunk, note its list moves, bring its pages in
         UVMTIER_CUDA(cudaMemsetAsync(d_cnt + 8, 0, 2 * sizeof(uint32_t), ctx->stream));
@@ -271,17 +277,22 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                 return st;
         }
         stats.passes++;
-        const uint32_t after = in_use - k + needed;
+        const uint32_t after = in_use + needed;
         if (after > stats.peak_chunks_in_use)
             stats.peak_chunks_in_use = after;
         stats.chunks_in_use = after;
     }
-    // the tallies, and whether a run array overflowed in the last chunk (the others were checked as the loop went)
+    // the tallies, the chunks in use now, and whether a run array overflowed in the last chunk (the others were
+    // checked as the loop went)
+    st = uvmtier_pmm_count_needed_device(ctx, pmm, 0, NULL, NULL, lay, d_cnt);
+    if (st != NV_OK)
+        return st;
     UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     UVMTIER_CUDA(cudaMemcpyAsync(h_cnt + 16, d_acc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
     if (h_cnt[6] > evict_run_cap || h_cnt[8] > svc_run_cap)
         return NV_ERR_NO_MEMORY;
+    stats.chunks_in_use = h_cnt[1];
     stats.pages_evicted = ((const unsigned long long *)(h_cnt + 16))[0];
     stats.pages_promoted = ((const unsigned long long *)(h_cnt + 16))[1];
     if (out_stats)

@@ -72,6 +72,19 @@ TIER_HBM, TIER_DRAM, TIER_CXL, TIER_PEER0 = 0, 1, 2, 8
 TIERF_CXL_EMULATED = 0x1
 
 
+class PmmState(ctypes.Structure):
+    """uvmtier_pmm_t"""
+    _fields_ = [("d_stamp", ctypes.c_void_p), ("d_scratch", ctypes.c_void_p), ("clock", ctypes.c_uint64),
+                ("n_slots", ctypes.c_uint32), ("capacity_chunks", ctypes.c_uint32)]
+
+
+class TieringStats(ctypes.Structure):
+    """uvmtier_tiering_stats_t"""
+    _fields_ = [("passes", ctypes.c_uint32), ("eviction_waves", ctypes.c_uint32), ("evicted_to_dram", ctypes.c_uint32),
+                ("evicted_to_cxl", ctypes.c_uint32), ("peak_chunks_in_use", ctypes.c_uint32), ("chunks_in_use", ctypes.c_uint32),
+                ("pages_evicted", ctypes.c_uint64), ("pages_promoted", ctypes.c_uint64), ("reserved", ctypes.c_uint32 * 4)]
+
+
 class TierInfo(ctypes.Structure):
     """uvmtier_tier_info_t"""
     _fields_ = [("bytes", ctypes.c_uint64), ("device_ptr", ctypes.c_void_p), ("host_ptr", ctypes.c_void_p),
@@ -334,6 +347,42 @@ class Context:
                 self.free(p)
             for h in pinned:
                 lib().uvmtier_mem_free_host_pinned(self._h, h)
+
+    # ---- (1d) eviction order + servicing under an HBM capacity ----
+    def pmm_create(self, layout, capacity_chunks):
+        pmm = PmmState()
+        _check(lib().uvmtier_pmm_create(self._h, P(layout), ctypes.c_uint32(capacity_chunks), ctypes.byref(pmm)), "uvmtier_pmm_create")
+        return pmm
+
+    def pmm_destroy(self, pmm):
+        _check(lib().uvmtier_pmm_destroy(self._h, ctypes.byref(pmm)), "uvmtier_pmm_destroy")
+
+    def pmm_stamps(self, pmm):
+        return self.from_device(pmm.d_stamp, pmm.n_slots, "<u8")
+
+    def service_fault_batches_tiered(self, k1, layout, dstate, pmm, chunk_batches, dram_capacity_pages, execute_copies=True):
+        """uvmtier_service_fault_batches_tiered_device on the results of fetch_preprocess_fault_batches (dict k1, host
+        arrays, padded to whole batches).  Returns flags / records / batch headers / state / stats / stamps."""
+        from .blockstate import SERVICE_GROUP_DT
+        from .layouts import BATCH_DT
+        nb = len(k1["batch"])
+        total = len(k1["ordered"])
+        d_ord = self.to_device(k1["ordered"]); d_grp = self.to_device(k1["groups"]); d_bat = self.to_device(k1["batch"])
+        d_flags = self.alloc(total * 2); d_svc = self.alloc(total * 96)
+        stats = TieringStats()
+        try:
+            _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(d_svc), 0, ctypes.c_size_t(total * 96)), "memset")
+            _check(lib().uvmtier_service_fault_batches_tiered_device(
+                self._h, ctypes.byref(pmm), ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(dstate.ptrs),
+                P(d_flags), P(d_svc), ctypes.c_uint32(chunk_batches), ctypes.c_uint64(dram_capacity_pages),
+                ctypes.c_int(1 if execute_copies else 0), ctypes.byref(stats)), "uvmtier_service_fault_batches_tiered_device")
+            self.synchronize()
+            return dict(flags=self.from_device(d_flags, total, "<u2"), service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
+                        batch=self.from_device(d_bat, nb, BATCH_DT), state=dstate.download(), stats=stats,
+                        stamps=self.pmm_stamps(pmm))
+        finally:
+            for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
+                self.free(p)
 
     # ---- (1c) make_resident ----
     def make_resident(self, requests, page_masks, prefetch_masks, layout, dstate, run_cap=1 << 18, execute=False):

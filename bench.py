@@ -345,6 +345,60 @@ def migration_numbers(ctx, lib, P, rank, world, dist, nbytes=256 << 20):
     return out
 
 
+def oversubscription_numbers(ctx, lib, P, rank):
+    """BASELINE config D, bounded: the fault path with HBM oversubscribed 1.5x.  1 GB of VA (512 va_blocks) with room
+    for 341 root chunks in HBM; a uniform trace keeps touching all of it, so every chunk of batches evicts least
+    recently used va_blocks (to host DRAM until it holds 192 MB of this table, then to the CXL node) before it is
+    serviced.  Real pages move: eviction copies HBM -> host, servicing copies host -> HBM.  Timed end to end on the host
+    clock (the loop synchronises once per chunk of batches by design)."""
+    import uvmtier
+    from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, tracegen as TG
+    from uvmtier.blockstate import HostBlockState, make_layout
+    blocks, n_entries, B, chunk_batches = 512, 65536, 256, 2
+    pk, tbl, lay = TG.fault_trace(n_entries, 77 + rank, "uniform", 1, blocks << 21)
+    gp = TG.gpu_params(B)
+    ctx.fault_buffer_init(gp, tbl)
+    layout = make_layout(lay)
+    st = HostBlockState(blocks)
+    st.cpu_resident0[:] = np.uint64(0xFFFFFFFFFFFFFFFF)                  # everything starts in host DRAM
+    ring = np.zeros((n_entries + 1, 8), np.uint32)
+    ring[:n_entries] = pk
+    k1 = ctx.fetch_preprocess_fault_batches(ring, 0, n_entries)
+    nb = len(k1["batch"])
+    info = {t: ctx.tier_create(t, blocks << 21) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
+    ds = ctx.block_state_alloc(layout)
+    ds.upload(st)
+    capacity = blocks * 2 // 3
+    pmm = ctx.pmm_create(layout, capacity)
+    d_ord, d_grp, d_bat = ctx.to_device(k1["ordered"]), ctx.to_device(k1["groups"]), ctx.to_device(k1["batch"])
+    d_flags, d_svc = ctx.alloc(nb * B * 2), ctx.alloc(nb * B * 96)
+    stats = uvmtier.TieringStats()
+    ctx.synchronize()
+    launches0 = lib.uvmtier_kernel_launch_count()
+    t0 = time.perf_counter()
+    st_code = lib.uvmtier_service_fault_batches_tiered_device(
+        ctx.handle, ctypes.byref(pmm), ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(ds.ptrs), P(d_flags),
+        P(d_svc), ctypes.c_uint32(chunk_batches), ctypes.c_uint64(96 * 512), ctypes.c_int(1), ctypes.byref(stats))
+    ctx.synchronize()
+    dt = time.perf_counter() - t0
+    assert st_code == 0, hex(st_code)
+    out = {"workload": "uniform trace, %d entries over %d va_blocks (1 GB of VA), HBM holds %d root chunks (VA / 1.5)" % (n_entries, blocks, capacity),
+           "chunk_batches": chunk_batches, "entries_per_s": n_entries / dt, "ms": dt * 1e3, "passes": stats.passes,
+           "eviction_waves": stats.eviction_waves, "root_chunks_evicted_to_dram": stats.evicted_to_dram,
+           "root_chunks_evicted_to_cxl": stats.evicted_to_cxl, "peak_chunks_in_use": stats.peak_chunks_in_use,
+           "GB_evicted": stats.pages_evicted * 4096 / 1e9, "GB_promoted": stats.pages_promoted * 4096 / 1e9,
+           "link_GBs": (stats.pages_evicted + stats.pages_promoted) * 4096 / dt / 1e9,
+           "gpu_launches": int(lib.uvmtier_kernel_launch_count() - launches0),
+           "policy": "victims in the reference's order (pick_root_chunk_to_evict); evicted pages to host DRAM up to 192 MB, then CXL"}
+    for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
+        ctx.free(p)
+    ctx.pmm_destroy(pmm)
+    ds.free()
+    for t in (TIER_HBM, TIER_DRAM, TIER_CXL):
+        ctx.tier_destroy(t)
+    return out
+
+
 # ----------------------------------------------------------------------------------------------- GPU arm
 def main():
     ap = argparse.ArgumentParser()
@@ -527,6 +581,9 @@ def main():
     migration = None
     if not args.no_migration:
         migration = migration_numbers(ctx, lib, P, rank, world, dist)
+    oversub = None
+    if not args.no_migration and rank == 0:
+        oversub = oversubscription_numbers(ctx, lib, P, rank)
     clocks = sampler.stop(windows=((wall0, wall1), (wall2, wall3)))
 
     # ---- max over ranks ----
@@ -574,6 +631,7 @@ def main():
                     "service_pass_ms": svc_ms, "service_pass_GBs": svc_bytes / (svc_ms * 1e-3) / 1e9,
                     "coalesced_entries": n_coalesced, "va_block_runs": n_groups, "copy_runs": n_runs, "va_blocks_touched": touched},
         "migration": migration,
+        "oversubscription": oversub,
         "wall_s_timed_region": wall1 - wall0,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

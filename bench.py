@@ -254,7 +254,7 @@ def run_reference_arm(args, rank):
                              "sample": "%d entries per step sharded over %d processes, each with its own va_block state" % (n, cores)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
-    print(json.dumps(line))
+    emit(line)
 
 
 # ----------------------------------------------------------------------------------------------- migration leg
@@ -400,6 +400,15 @@ def oversubscription_numbers(ctx, lib, P, rank):
 
 
 # ----------------------------------------------------------------------------------------------- GPU arm
+_REAL_STDOUT = None
+
+
+def emit(line):
+    sys.stdout.flush()
+    data = (json.dumps(line) + "\n").encode()
+    os.write(_REAL_STDOUT if _REAL_STDOUT is not None else 1, data)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -410,6 +419,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-migration", action="store_true")
     args = ap.parse_args()
+
+    # stdout carries exactly one JSON line: libraries that print banners on fd 1 (NCCL's version line) are sent to
+    # stderr, and the line is written to the real stdout at the end
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
 
     rank, world, local_rank = env_int("RANK", 0), env_int("WORLD_SIZE", 1), env_int("LOCAL_RANK", 0)
     if args.impl == "reference":
@@ -640,7 +656,7 @@ def main():
                                 "sample": "full step (%d entries), best of 2, 1 thread (the reference services one GPU on one thread); "
                                           "fetch/merge/sort + service entry loop = reference C, make_resident back half = CPU port" % ns}
     if rank == 0:
-        print(json.dumps(line))
+        emit(line)
     if dist is not None:
         dist.barrier()
         dist.destroy_process_group()

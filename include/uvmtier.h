@@ -628,6 +628,72 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                                                       uvmtier_tiering_stats_t *out_stats);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (1e) Access-counter notifications -- UVM/uvm_gpu_access_counters.c                          */
+/* ------------------------------------------------------------------------------------------ */
+/* The sibling front end on the same back end: the GPU reports regions it keeps reaching remotely and the driver
+ * migrates them to it.  32-byte NVC365 packets (UVM/clc365.h:33-80) are fetched (:862-940), parsed
+ * (UVM/uvm_turing_access_counter_buffer.c:154-198), sorted by (va_space, gpu, address) (preprocess_notifications
+ * :974-992), expanded per va_block into a page mask (expand_notification_block :1287-1354) and passed through the
+ * fault path's back half (service_va_block_locked :1079-1249 -> uvm_va_block_service_locked).  Uses the
+ * instance-pointer table and max_batch_size of uvmtier_fault_buffer_init (uvm_perf_access_counter_batch_count has
+ * the same default, 256). */
+typedef struct { uint32_t w[8]; } uvmtier_access_counter_packet_t;       /* NVC365_NOTIFY_BUF_SIZE = 32 */
+
+/* uvm_access_counter_buffer_entry_t (UVM/uvm_hal_types.h:481-520) */
+typedef struct {
+    uint64_t address;                /* canonical VA of the tracked region */
+    uint64_t instance_ptr;           /* instance_ptr.address */
+    uint32_t instance_aperture;      /* uvm_aperture_t value (UVM_APERTURE_VID = 10, _SYS = 9) */
+    uint32_t mmu_engine_id;
+    uint32_t ve_id;
+    uint32_t counter_value;
+    uint32_t sub_granularity;        /* one bit per 1/32 of the tracked region */
+    uint32_t bank, tag;
+    uint32_t valid;                  /* entry was fetched */
+} uvmtier_access_counter_entry_t;    /* 48 bytes */
+
+/* One element of batch_context->notifications[] after preprocess_notifications (the sorted pointer array). */
+#define UVMTIER_AC_CTX_NONE 0xFFFFu  /* instance pointer did not translate: va_space NULL, entry ignored (:957-960) */
+typedef struct {
+    uint64_t address;
+    uint16_t index;                  /* index into this batch's notification_cache (ring order) */
+    uint16_t ctx;                    /* row of the instance-pointer table, or UVMTIER_AC_CTX_NONE */
+    uint32_t sub_granularity;
+} uvmtier_ordered_notification_t;    /* 16 bytes */
+
+/* current_config of the notification buffer (:328-353) and the one harness choice the expansion depends on: the
+ * size of the CPU chunks backing a va_block (uvm_va_block_get_physical_size, UVM/uvm_va_block.c:2353-2373).  With
+ * 2 MB tracking and 2 MB CPU chunks a notification expands to the 64 KB sub-regions its sub_granularity names,
+ * otherwise to the one page at its address (:1325-1352); other tracking granularities are ignored (:1303-1306). */
+typedef struct {
+    uint64_t granularity_bytes;      /* default 2 MB */
+    uint64_t cpu_chunk_bytes;        /* default 2 MB (tiers back a va_block contiguously); 4096 = page-sized chunks */
+} uvmtier_access_counter_config_t;
+NV_STATUS uvmtier_access_counters_init(uvmtier_ctx_t *ctx, const uvmtier_access_counter_config_t *cfg /* NULL: defaults */);
+
+/* fetch + parse + preprocess for all batches between GET and PUT, one CTA per batch; outputs sliced like the fault
+ * path's (batch b at b * max_batch_size).  d_groups: runs of notifications of one (va_space, gpu, va_block), what
+ * service_notifications_in_block (:1356-1427) handles in one call; untranslated notifications sort first and belong
+ * to no group.  d_batches: num_cached_faults = num_coalesced_faults = notifications fetched, is_single_instance_ptr
+ * (:925-930), num_block_groups.  d_entries: optional parsed entries in ring order.  Ordering compares page numbers
+ * (tracked regions are at least 64 KB aligned); ties keep cache order. */
+NV_STATUS uvmtier_access_counters_fetch_preprocess_device(uvmtier_ctx_t *ctx, uvmtier_access_counter_packet_t *d_ring,
+                                                          uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
+                                                          uvmtier_ordered_notification_t *d_ordered,
+                                                          uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                          uvmtier_access_counter_entry_t *d_entries, uint32_t *out_get);
+/* service_notifications_batch (:1513-1615) for all batches: per va_block run, in batch order, the notifications are
+ * expanded into accessed pages -- only while the GPU still maps something in the block (:1103-1104), pages already
+ * on the GPU are stale (:1122-1123) -- then prefetch hint, make_resident to the GPU, mapping.  Records, copy runs and
+ * counters as uvmtier_service_fault_batches_device (page_fault_count = pages the notifications named). */
+NV_STATUS uvmtier_access_counters_service_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                 const uvmtier_ordered_notification_t *d_ordered,
+                                                 const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                 const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                                 uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
+                                                 uint32_t run_cap, uint32_t *d_counters);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */
 

@@ -21,6 +21,7 @@ struct uvmtier_fault_state {
     uint32_t threads;      // CTA size = next power of two >= max_batch_size (>= 32)
     uint32_t idx_bits;
     size_t smem_bytes;
+    uint32_t ac_granularity_2m, ac_cpu_chunk_2m;   // access-counter configuration (uvmtier_access_counters_init)
     uint32_t generation;   // bumped by every uvmtier_fault_buffer_init (the table's contents may have changed)
 };
 

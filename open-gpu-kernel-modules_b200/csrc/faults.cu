@@ -10,7 +10,8 @@
 
 #include <stdlib.h>
 
-#include "fault_kernels.cuh"
+#define UVMTIER_AC_PREPROCESS
+#include "access_counter_kernels.cuh"   // includes fault_kernels.cuh
 
 using namespace uvmtier_k;
 
@@ -55,6 +56,8 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
     fs->gp = *gp;
     fs->gp.coalesce = gp->coalesce != 0;
     fs->n_rows = (uint32_t)n_rows;
+    fs->ac_granularity_2m = 1;
+    fs->ac_cpu_chunk_2m = 1;
     static std::atomic<uint32_t> generation{0};
     fs->generation = ++generation;
     fs->threads = threads;
@@ -254,6 +257,57 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fau
 }
 
 } // extern "C"
+
+// ------------------------------------------------------------------------------------------------
+// Access-counter notifications, front end (include/uvmtier.h section 1e).
+extern "C" NV_STATUS uvmtier_access_counters_init(uvmtier_ctx_t *ctx, const uvmtier_access_counter_config_t *cfg)
+{
+    if (!ctx)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;                       // the table and the batch size come from uvmtier_fault_buffer_init
+    const uint64_t gran = cfg && cfg->granularity_bytes ? cfg->granularity_bytes : (2ull << 20);
+    const uint64_t chunk = cfg && cfg->cpu_chunk_bytes ? cfg->cpu_chunk_bytes : (2ull << 20);
+    if ((gran != (64ull << 10) && gran != (2ull << 20) && gran != (16ull << 20) && gran != (16ull << 30)) ||   // :198-218
+        (chunk != 4096 && chunk != (64ull << 10) && chunk != (2ull << 20)))
+        return NV_ERR_INVALID_ARGUMENT;
+    ctx->faults->ac_granularity_2m = gran == (2ull << 20);
+    ctx->faults->ac_cpu_chunk_2m = chunk == (2ull << 20);
+    return NV_OK;
+}
+
+extern "C" NV_STATUS uvmtier_access_counters_fetch_preprocess_device(uvmtier_ctx_t *ctx, uvmtier_access_counter_packet_t *d_ring,
+                                                                     uint32_t ring_entries, uint32_t get, uint32_t put,
+                                                                     int clear_valid, uvmtier_ordered_notification_t *d_ordered,
+                                                                     uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                                     uvmtier_access_counter_entry_t *d_entries, uint32_t *out_get)
+{
+    if (!ctx || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    const uvmtier_fault_state *fs = ctx->faults;
+    const uint32_t n = put >= get ? put - get : ring_entries - get + put;
+    if (out_get)
+        *out_get = put;
+    if (!n)
+        return NV_OK;
+    if (!d_ordered || !d_groups || !d_batches)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    ac_kparams prm;
+    prm.B = fs->gp.max_batch_size;
+    prm.va_bits = fs->gp.va_bits;
+    prm.ring_entries = ring_entries;
+    prm.get = get;
+    prm.n_entries = n;
+    prm.tbl_n = fs->n_rows;
+    prm.idx_bits = fs->idx_bits;
+    prm.clear_valid = clear_valid != 0;
+    UVMTIER_LAUNCH(k_access_counters_fetch_preprocess, (n + prm.B - 1) / prm.B, fs->threads, 0, ctx->stream, prm, d_ring,
+                   fs->d_table, d_ordered, d_groups, d_batches, d_entries);
+    return NV_OK;
+}
 
 // ------------------------------------------------------------------------------------------------
 // Chunk plan and host->device streaming shared by the streamed entry points (here and in service.cu).

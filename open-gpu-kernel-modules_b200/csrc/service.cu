@@ -14,6 +14,8 @@
 #include "service_kernels.cuh"
 #include "service_lists.cuh"
 #include "service_grp.cuh"
+#define UVMTIER_AC_SERVICE
+#include "access_counter_kernels.cuh"
 
 using namespace uvmtier_k;
 
@@ -359,6 +361,67 @@ NV_STATUS uvmtier_service_pass_chunk(uvmtier_ctx_t *ctx, uint32_t n_batches, con
         return st;
     return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service, d_runs,
                         run_cap, d_counters, batch_base, false);
+}
+
+// Access-counter notifications, servicing (include/uvmtier.h section 1e): the list front end of the fault path
+// (runs per va_block, in batch order), then a warp per va_block -- the light list first, then the heavy one.
+extern "C" NV_STATUS uvmtier_access_counters_service_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                            const uvmtier_ordered_notification_t *d_ordered,
+                                                            const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                            const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                                            uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
+                                                            uint32_t run_cap, uint32_t *d_counters)
+{
+    const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_service, d_service, d_runs,
+                                            run_cap, d_counters);
+    if (ok != NV_OK || !n_batches)
+        return ok;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    const uint32_t B = ctx->faults->gp.max_batch_size;
+    const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * B;
+    const NV_STATUS rs = service_scratch_reserve(ctx, n_slots, n_batches, total);
+    if (rs != NV_OK)
+        return rs;
+    const service_scratch_view v = scratch_view(ctx->svc.d_base, n_slots, n_batches, total);
+    service_kparams prm;
+    memset(&prm, 0, sizeof(prm));
+    prm.va_base = lay->va_base; prm.B = B; prm.n_batches = n_batches; prm.blocks_per_space = lay->blocks_per_space;
+    prm.n_spaces = lay->n_spaces; prm.gpu_id = lay->gpu_id; prm.n_slots = n_slots;
+    prm.pf_enable = ctx->cfg.uvm_perf_prefetch_enable; prm.pf_threshold = ctx->cfg.uvm_perf_prefetch_threshold;
+    prm.pf_min_faults = ctx->cfg.uvm_perf_prefetch_min_faults; prm.run_cap = run_cap; prm.B_shift = svc_log2_or_none(B);
+    block_state_ptrs bs;
+    bs.gpu_resident = (uint32_t *)state->gpu_resident;
+    bs.cpu_resident[0] = (uint32_t *)state->cpu_resident[0]; bs.cpu_resident[1] = (uint32_t *)state->cpu_resident[1];
+    bs.gpu_pte[0] = (uint32_t *)state->gpu_pte[0]; bs.gpu_pte[1] = (uint32_t *)state->gpu_pte[1]; bs.gpu_pte[2] = (uint32_t *)state->gpu_pte[2];
+    bs.prefetch_info = state->prefetch_info; bs.logical_prot = state->logical_prot; bs.preferred_location = state->preferred_location;
+    bs.gpu_evicted = (uint32_t *)state->gpu_evicted; bs.read_duplicated = (uint32_t *)state->read_duplicated;
+    UVMTIER_CUDA(cudaMemsetAsync(ctx->svc.d_base, 0, v.zero_words * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    const uint2 *cw = (const uint2 *)v.cw;
+    const size_t cap = (size_t)ctx->sm_count * 8;
+    size_t grid = (total + kSvcThreads - 1) / kSvcThreads;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, ctx->faults->d_table,
+                   (unsigned long long *)v.cw, v.batch_unmapped, (uint2 *)v.slotpos);
+    UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, kHeavyMinEntries, v.offset, v.cursor, v.hist,
+                   v.light_rank);
+    UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
+    size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
+    if (sgrid > cap)
+        sgrid = cap;
+    UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, kHeavyMinEntries, v.big,
+                   v.heavy, v.hist, v.light_rank, v.light);
+    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, ctx->stream, cw, v.offset, v.list, v.big);
+    ac_service_cfg cfg;
+    cfg.granularity_2m = ctx->faults->ac_granularity_2m;
+    cfg.cpu_chunk_2m = ctx->faults->ac_cpu_chunk_2m;
+    UVMTIER_LAUNCH(k_access_counters_blocks, ctx->sm_count * 4, kSvcThreads, 0, ctx->stream, prm, cfg, d_ordered, d_groups, bs, cw,
+                   v.offset, v.list, (const uint32_t *)v.light, (const uint32_t *)(v.cursor + 1), d_service, d_runs, d_counters);
+    UVMTIER_LAUNCH(k_access_counters_blocks, ctx->sm_count * 2, kSvcThreads, 0, ctx->stream, prm, cfg, d_ordered, d_groups, bs, cw,
+                   v.offset, v.list, (const uint32_t *)(v.heavy + 1), (const uint32_t *)v.heavy, d_service, d_runs, d_counters);
+    return NV_OK;
 }
 
 // Everything uvmtier_service_replayable_faults_streamed puts on the three streams.  Streams, events and working

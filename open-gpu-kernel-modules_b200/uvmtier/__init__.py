@@ -384,6 +384,50 @@ class Context:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
                 self.free(p)
 
+    # ---- (1e) access-counter notifications ----
+    def access_counters_init(self, granularity_bytes=2 << 20, cpu_chunk_bytes=2 << 20):
+        cfg = (ctypes.c_uint64 * 2)(granularity_bytes, cpu_chunk_bytes)
+        _check(lib().uvmtier_access_counters_init(self._h, cfg), "uvmtier_access_counters_init")
+
+    def access_counters_service(self, ring, get, put, layout, dstate, run_cap=1 << 20, clear_valid=True):
+        """uvmtier_access_counters_fetch_preprocess_device + uvmtier_access_counters_service_device on a notification
+        ring (host array, uploaded).  Returns the preprocess outputs, records, runs and the state."""
+        from .blockstate import COPY_RUN_DT, SERVICE_GROUP_DT
+        from .layouts import BATCH_DT, GROUP_DT
+        onotif = np.dtype([("address", "<u8"), ("index", "<u2"), ("ctx", "<u2"), ("sub_granularity", "<u4")])
+        ring = np.ascontiguousarray(ring)
+        ring_entries = len(ring)
+        n = put - get if put >= get else ring_entries - get + put
+        B = self._fault_B
+        nb = (n + B - 1) // B
+        total = nb * B
+        d_ring = self.to_device(ring)
+        d_ord, d_grp, d_bat, d_ent = self.alloc(total * 16), self.alloc(total * 16), self.alloc(nb * 32), self.alloc(total * 48)
+        d_svc, d_runs, d_cnt = self.alloc(total * 96), self.alloc(max(run_cap, 1) * 8), self.alloc(8)
+        devs = (d_ring, d_ord, d_grp, d_bat, d_ent, d_svc, d_runs, d_cnt)
+        try:
+            for p_, nbytes in ((d_ord, total * 16), (d_grp, total * 16), (d_ent, total * 48), (d_svc, total * 96)):
+                _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(p_), 0, ctypes.c_size_t(nbytes)), "memset")
+            new_get = ctypes.c_uint32(0)
+            _check(lib().uvmtier_access_counters_fetch_preprocess_device(
+                self._h, P(d_ring), ctypes.c_uint32(ring_entries), ctypes.c_uint32(get), ctypes.c_uint32(put),
+                ctypes.c_int(1 if clear_valid else 0), P(d_ord), P(d_grp), P(d_bat), P(d_ent), ctypes.byref(new_get)),
+                "uvmtier_access_counters_fetch_preprocess_device")
+            _check(lib().uvmtier_access_counters_service_device(
+                self._h, ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(dstate.ptrs), P(d_svc),
+                P(d_runs), ctypes.c_uint32(run_cap), P(d_cnt)), "uvmtier_access_counters_service_device")
+            self.synchronize()
+            cnt = self.from_device(d_cnt, 2, "<u4")
+            return dict(ordered=self.from_device(d_ord, total, onotif), groups=self.from_device(d_grp, total, GROUP_DT),
+                        batch=self.from_device(d_bat, nb, BATCH_DT), entries=self.from_device(d_ent, total, np.dtype("V48")),
+                        ring=self.from_device(d_ring, ring.shape, ring.dtype), n=n, get=new_get.value,
+                        service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
+                        runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT), n_runs=int(cnt[0]),
+                        flags=np.zeros(total, "<u2"), state=dstate.download())
+        finally:
+            for p_ in devs:
+                self.free(p_)
+
     # ---- (1c) make_resident ----
     def make_resident(self, requests, page_masks, prefetch_masks, layout, dstate, run_cap=1 << 18, execute=False):
         """uvmtier_make_resident_device on host arrays (requests: MAKE_RESIDENT_REQ_DT; masks: uint64 [n, 8] or

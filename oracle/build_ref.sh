@@ -96,3 +96,13 @@ if [ -f "$HERE/ref_pmm_glue.c" ]; then
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_pmm_glue.c" -o "$OUT/libref_pmm.so"
     echo "build_ref: built $OUT/libref_pmm.so"
 fi
+
+# ---------------- access-counter leg: expansion + service_va_block_locked, verbatim, on the service leg's shims ----------------
+if [ -f "$HERE/ref_access_counters_glue.c" ]; then
+    pin uvm_gpu_access_counters.c 67b82fdfd551a698
+    sed -n '198,218p;1079,1251p;1253,1260p;1287,1354p' "$UVM/uvm_gpu_access_counters.c" > "$TMP/x_access_counters.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_access_counters_glue.c" "$HERE/ref_faults_blackwell.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        -o "$OUT/libref_access_counters.so"
+    echo "build_ref: built $OUT/libref_access_counters.so"
+fi

@@ -13,9 +13,11 @@
  * notification_cache order (the canonical choice of the fault path).  Untranslated notifications (va_space NULL)
  * sort first and are skipped.
  *
- * Pinning: PARITY UNPINNED by compiled reference code this round -- the plan is to compile
- * expand_notification_block and service_va_block_locked against the shims of ref_service_glue.c.  The reference
- * holds no vectors for this path; every step cites the lines it restates.
+ * Pinning: the servicing half (expand_notification_block, service_va_block_locked) is compared with the reference's
+ * own functions compiled verbatim (oracle/_ref/libref_access_counters.so, ref_access_counters_glue.c;
+ * tests/test_oracle_access_counters.py -k reference): records, copy runs and state identical.  The front half
+ * (parse, fetch, the two sorts) is a restatement only -- PARITY UNPINNED for it: the reference holds no vectors and
+ * its fetch loop has not been compiled against the shims; every step cites the lines it restates.
  */
 #include <stdlib.h>
 

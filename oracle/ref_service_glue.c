@@ -39,9 +39,10 @@ struct uvm_va_block_struct {
     int lock;
     uvm_va_space_t *va_space;
     struct { uvm_va_policy_t policy; } *managed_range, range_storage;
+    uvm_processor_mask_t resident, mapped;           /* used by the access-counter leg (ref_access_counters_glue.c) */
     uint32_t slot;                                   /* harness: row of the flat state table */
 };
-typedef struct { struct { void *vma; } hmm; } uvm_va_block_context_t;
+typedef struct { struct { void *vma; } hmm; void *mm; } uvm_va_block_context_t;
 typedef struct { uvm_va_block_t *va_block; uvm_va_block_region_t region; } uvm_reverse_map_t;
 typedef struct { struct { NvU64 start, end; } node; } uvm_range_group_range_t;
 static inline NvU64 uvm_va_block_size(uvm_va_block_t *b) { return b->end - b->start + 1; }
@@ -65,7 +66,7 @@ typedef struct uvm_va_block_retry_struct uvm_va_block_retry_t;
 
 /* uvm_service_block_context_t: the fields the loop touches (uvm_va_block_types.h:262-340) */
 typedef struct uvm_service_block_context_struct {
-    uvm_processor_mask_t resident_processors;
+    uvm_processor_mask_t resident_processors, update_processors;
     NvU32 thrashing_pin_count, read_duplicate_count;
     uvm_page_mask_t thrashing_pin_mask, read_duplicate_mask;
     struct { uvm_page_mask_t new_residency; } per_processor_masks[UVM_ID_MAX_PROCESSORS_S];

@@ -74,6 +74,22 @@ def run_service_oracle(orc, k, B, tbl, layout, state, pf=(1, 51, 1), granularity
     return dict(records=svc[:nsvc], runs=runs, n_runs=n_runs.value, state=st, flags=np.zeros(nb * B, "<u2"), batch=k["batch"].copy())
 
 
+def run_service_ref(ref, k, B, tbl, layout, state, pf=(1, 51, 1), granularity_2m=True, cpu_chunk_2m=True, run_cap=1 << 20):
+    """oracle/_ref/libref_access_counters.so: the reference's own expand_notification_block and service_va_block_locked
+    (verbatim); same contract as run_service_oracle."""
+    nb = len(k["batch"])
+    svc, runs = np.zeros(nb * B, SERVICE_GROUP_DT), np.zeros(run_cap, COPY_RUN_DT)
+    st = state.copy()
+    ptrs = st.ptrs()
+    n_runs = ctypes.c_uint32(0)
+    fn = ref.ref_access_counters_service
+    fn.restype = ctypes.c_uint32
+    nsvc = fn(ctypes.c_uint32(nb), ctypes.c_uint32(B), P(k["ordered"]), P(k["groups"]), P(k["batch"]), P(tbl), P(layout),
+              ctypes.byref(ptrs), ctypes.c_uint(pf[0]), ctypes.c_uint(pf[1]), ctypes.c_uint(pf[2]), ctypes.c_int(granularity_2m),
+              ctypes.c_int(cpu_chunk_2m), P(svc), P(runs), ctypes.c_uint32(run_cap), ctypes.byref(n_runs))
+    return dict(records=svc[:nsvc], runs=runs, n_runs=n_runs.value, state=st)
+
+
 def run_service_simt(sim, k, B, tbl, layout, state, pf=(1, 51, 1), granularity_2m=True, cpu_chunk_2m=True, run_cap=1 << 20,
                      heavy_min=96):
     nb = len(k["batch"])

@@ -86,3 +86,32 @@ def test_simt_service_matches_oracle(cpu_chunk_2m, granularity_2m, heavy_min):
     else:
         assert moved == 0                                        # other tracking granularities are ignored (:1303-1306)
         want["state"].assert_equal(st0)
+
+
+# ------------------------------------------------------------------------------------------------
+# The restatement against the reference's own expand_notification_block + service_va_block_locked (compiled verbatim
+# into oracle/_ref/libref_access_counters.so).
+@pytest.mark.parametrize("seed,cpu_chunk_2m,granularity_2m", [(1, True, True), (2, True, True), (3, False, True), (4, False, True),
+                                                              (5, True, False)])
+def test_oracle_matches_the_reference_expansion_and_service(seed, cpu_chunk_2m, granularity_2m):
+    ref = T.load_ref("access_counters")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_access_counters.so not built (needs /root/reference)")
+    B = 128
+    pk, tbl, lay = notifications(2500, 40 + seed, 2, 64)
+    n = len(pk)
+    ring = np.zeros((n + 1, 8), np.uint32)
+    ring[:n] = pk
+    orc = T.load_oracle()
+    k = A.run_preprocess(orc, "oracle_access_counters_fetch_preprocess", ring, 0, n, B, tbl)
+    layout = S.make_layout(lay)
+    st0 = state_with_mappings(lay["blocks_per_space"] * 2, 50 + seed)
+    want = A.run_service_ref(ref, k, B, tbl, layout, st0, granularity_2m=granularity_2m, cpu_chunk_2m=cpu_chunk_2m)
+    got = A.run_service_oracle(orc, k, B, tbl, layout, st0, granularity_2m=granularity_2m, cpu_chunk_2m=cpu_chunk_2m)
+    want["state"].assert_equal(got["state"], "reference vs restatement")
+    assert len(want["records"]) == len(got["records"]) and want["n_runs"] == got["n_runs"]
+    for f in S.RECORD_FIELDS:
+        assert np.array_equal(want["records"][f], got["records"][f]), f
+    assert np.array_equal(want["runs"][:want["n_runs"]], got["runs"][:got["n_runs"]])
+    if granularity_2m:
+        assert int(want["records"]["page_fault_count"].sum()) > 50

@@ -106,3 +106,14 @@ if [ -f "$HERE/ref_access_counters_glue.c" ]; then
         -o "$OUT/libref_access_counters.so"
     echo "build_ref: built $OUT/libref_access_counters.so"
 fi
+
+# ---------------- access-counter front half: parse + fetch + preprocess, verbatim, on the fault leg's shims ----------------
+if [ -f "$HERE/ref_access_counters_front_glue.c" ]; then
+    pin uvm_turing_access_counter_buffer.c b4afc3558d7cc578
+    sed -n '481,520p' "$UVM/uvm_hal_types.h" > "$TMP/x_ac_entry.h"
+    sed -n '88,198p' "$UVM/uvm_turing_access_counter_buffer.c" > "$TMP/x_ac_turing.h"
+    sed -n '798,821p;834,860p;862,940p;942,969p;974,992p' "$UVM/uvm_gpu_access_counters.c" > "$TMP/x_ac_front.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_access_counters_front_glue.c" "$HERE/ref_faults_blackwell.c" \
+        "$HERE/ref_faults_hopper.c" -o "$OUT/libref_access_counters_front.so"
+    echo "build_ref: built $OUT/libref_access_counters_front.so"
+fi

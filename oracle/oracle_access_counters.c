@@ -13,11 +13,14 @@
  * notification_cache order (the canonical choice of the fault path).  Untranslated notifications (va_space NULL)
  * sort first and are skipped.
  *
- * Pinning: the servicing half (expand_notification_block, service_va_block_locked) is compared with the reference's
- * own functions compiled verbatim (oracle/_ref/libref_access_counters.so, ref_access_counters_glue.c;
- * tests/test_oracle_access_counters.py -k reference): records, copy runs and state identical.  The front half
- * (parse, fetch, the two sorts) is a restatement only -- PARITY UNPINNED for it: the reference holds no vectors and
- * its fetch loop has not been compiled against the shims; every step cites the lines it restates.
+ * Pinning: both halves are compared with the reference's own functions compiled verbatim
+ * (tests/test_oracle_access_counters.py -k reference): the servicing half (expand_notification_block,
+ * service_va_block_locked) by oracle/_ref/libref_access_counters.so -- records, copy runs and state identical; the
+ * front half (uvm_hal_turing_access_counter_buffer_parse_entry, fetch_access_counter_buffer_entries,
+ * translate_notifications_instance_ptrs, preprocess_notifications) by oracle/_ref/libref_access_counters_front.so --
+ * parsed entries, counters, cleared VALID bits, runs and the sorted order identical up to the order of
+ * notifications that compare equal, which the reference leaves undefined (unstable sort) and nothing downstream
+ * depends on.
  */
 #include <stdlib.h>
 

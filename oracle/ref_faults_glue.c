@@ -88,6 +88,7 @@ struct uvm_parent_gpu_struct {
     struct { struct { int service_lock; } replayable_faults; } isr;
     uvm_fault_buffer_hal_t *fault_buffer_hal;
     uvm_arch_hal_t *arch_hal;
+    struct uvm_access_counter_buffer_hal_struct *access_counter_buffer_hal;   /* used by ref_access_counters_front_glue.c only */
     NvU32 hw_put;                          /* harness: what read_put returns */
     NvU32 written_get;                     /* harness: last write_get */
 };

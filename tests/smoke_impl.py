@@ -54,6 +54,23 @@ def run():
         R.assert_equal(R.run_oracle(orc, rq, pm, pf, st1), mr, "smoke make_resident")
         ds.free()
 
+        # (1e) access-counter notifications: fetch + sort + expansion + servicing on the same table shape
+        import aclib as A
+        from test_oracle_access_counters import notifications, state_with_mappings
+        npk, ntbl, nlay = notifications(2000, 3, 2, 64)
+        nring = np.zeros((len(npk) + 1, 8), np.uint32)
+        nring[:len(npk)] = npk
+        ctx.fault_buffer_init(gp, ntbl)
+        ctx.access_counters_init()
+        nlayout = S.make_layout(nlay)
+        nst0 = state_with_mappings(128, 4)
+        nds = ctx.block_state_alloc(nlayout)
+        nds.upload(nst0)
+        got = ctx.access_counters_service(nring, 0, len(npk), nlayout, nds)
+        nds.free()
+        nk = A.run_preprocess(orc, "oracle_access_counters_fetch_preprocess", nring, 0, len(npk), 256, ntbl)
+        S.assert_service_equal(A.run_service_oracle(orc, nk, 256, ntbl, nlayout, nst0), got, 256, "smoke access counters")
+
         # (3) migration: 4 KB pages DRAM -> HBM in random order, byte exact
         nbytes = 8 << 20
         info = {t: ctx.tier_create(t, nbytes) for t in (TIER_HBM, TIER_DRAM)}
@@ -67,5 +84,5 @@ def run():
 
         launches = uvmtier.kernel_launch_count() - before
         assert launches >= 10, "smoke: CUDA kernels were not launched"
-    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, migration)" %
+    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, make_resident, access counters, migration)" %
           (uvmtier.lib().uvmtier_version().decode(), launches))

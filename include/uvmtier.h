@@ -934,6 +934,17 @@ typedef struct {
                                            const uvmtier_va_layout_t *, const uvmtier_block_state_t *, uint16_t *d_entry_flags,
                                            uvmtier_service_group_t *, uvmtier_copy_run_t *, uint32_t run_cap,
                                            uint32_t *d_counters, const uvmtier_service_readback_t *, uint32_t *out_get);
+    /* uvm_access_counter_buffer_hal_struct::parse_entry + fetch_access_counter_buffer_entries + preprocess_notifications
+     * (UVM/uvm_hal.h:866-885, UVM/uvm_gpu_access_counters.c:862-992) */
+    NV_STATUS (*access_counters_fetch_preprocess)(uvmtier_ctx_t *, uvmtier_access_counter_packet_t *d_ring, uint32_t ring_entries,
+                                                  uint32_t get, uint32_t put, int clear_valid, uvmtier_ordered_notification_t *,
+                                                  uvmtier_fault_group_t *, uvmtier_fault_batch_t *,
+                                                  uvmtier_access_counter_entry_t *d_entries, uint32_t *out_get);
+    /* service_notifications_batch (UVM/uvm_gpu_access_counters.c:1513-1615) */
+    NV_STATUS (*access_counters_service)(uvmtier_ctx_t *, uint32_t n_batches, const uvmtier_ordered_notification_t *,
+                                         const uvmtier_fault_group_t *, uvmtier_fault_batch_t *, const uvmtier_va_layout_t *,
+                                         const uvmtier_block_state_t *, uvmtier_service_group_t *, uvmtier_copy_run_t *,
+                                         uint32_t run_cap, uint32_t *d_counters);
 } uvmtier_ops_t;
 
 /* The B200 implementation of every slot. */

@@ -289,4 +289,6 @@ extern "C" const uvmtier_ops_t uvmtier_gpu_ops = {
     uvmtier_copy_runs_device,
     uvmtier_copy_page_list,
     uvmtier_service_replayable_faults_streamed,
+    uvmtier_access_counters_fetch_preprocess_device,
+    uvmtier_access_counters_service_device,
 };

@@ -33,7 +33,8 @@ def test_ops_table_points_at_the_entry_points():
     lib = uvmtier.lib()
     slots = ("uvmtier_fetch_preprocess_fault_batches", "uvmtier_fetch_preprocess_fault_batches_device",
              "uvmtier_service_fault_batches_device", "uvmtier_perf_prefetch_get_hint_va_block", "uvmtier_make_resident_device",
-             "uvmtier_copy_runs_device", "uvmtier_copy_page_list", "uvmtier_service_replayable_faults_streamed")
+             "uvmtier_copy_runs_device", "uvmtier_copy_page_list", "uvmtier_service_replayable_faults_streamed",
+             "uvmtier_access_counters_fetch_preprocess_device", "uvmtier_access_counters_service_device")
     table = (ctypes.c_void_p * len(slots)).in_dll(lib, "uvmtier_gpu_ops")
     for k, name in enumerate(slots):
         assert table[k] == ctypes.cast(getattr(lib, name), ctypes.c_void_p).value, name

@@ -685,7 +685,9 @@ NV_STATUS uvmtier_access_counters_fetch_preprocess_device(uvmtier_ctx_t *ctx, uv
 /* service_notifications_batch (:1513-1615) for all batches: per va_block run, in batch order, the notifications are
  * expanded into accessed pages -- only while the GPU still maps something in the block (:1103-1104), pages already
  * on the GPU are stale (:1122-1123) -- then prefetch hint, make_resident to the GPU, mapping.  Records, copy runs and
- * counters as uvmtier_service_fault_batches_device (page_fault_count = pages the notifications named). */
+ * counters as uvmtier_service_fault_batches_device (page_fault_count = pages the notifications named); the records
+ * are also what uvmtier_pmm_note_service_device takes, so a promotion moves its va_block to the tail of the
+ * eviction order like a serviced fault does. */
 NV_STATUS uvmtier_access_counters_service_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
                                                  const uvmtier_ordered_notification_t *d_ordered,
                                                  const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,

@@ -183,8 +183,10 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     const uint32_t B = ctx->faults->gp.max_batch_size;
     const uint64_t chunk_entries = (uint64_t)chunk_batches * B;
-    // victims per wave: never more than the va_blocks one chunk of batches can touch
-    const uint32_t kmax = (uint32_t)(chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots);
+    // victims per wave: never more than the va_blocks one chunk of batches can touch, and at most 65536 (the run
+    // array of a wave is sized for them; a larger overflow takes more waves)
+    const uint64_t kmax64 = chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots;
+    const uint32_t kmax = (uint32_t)(kmax64 < 65536 ? kmax64 : 65536);
     const uint32_t evict_run_cap = kmax * 256u;                           // a block's GPU pages: at most 256 runs
     const uint64_t svc_cap64 = chunk_entries * 16 > (1u << 16) ? chunk_entries * 16 : (1u << 16);
     const uint32_t svc_run_cap = (uint32_t)(svc_cap64 < 0x7fffffffull ? svc_cap64 : 0x7fffffffull);

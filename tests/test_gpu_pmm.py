@@ -48,7 +48,7 @@ def cpu_tiered(orc, k1, gp, tbl, lay, layout, st0, capacity, chunk_batches, dram
         for _ in range(8):                      # evict, then count again: a victim this chunk faults on needs a chunk again
             needed = sum(1 for s in slots if stamp[s] == 0)
             in_use = int((stamp != 0).sum())
-            k = min(max(in_use + needed - capacity, 0), in_use, min(chunk_batches * B, n_slots))
+            k = min(max(in_use + needed - capacity, 0), in_use, min(chunk_batches * B, n_slots, 65536))
             if not k:
                 break
             dram_pages = int(T.bool_from_masks(st.cpu_resident0).sum())

@@ -107,6 +107,19 @@ if [ -f "$HERE/ref_access_counters_glue.c" ]; then
     echo "build_ref: built $OUT/libref_access_counters.so"
 fi
 
+# ---------------- thrashing detector: event callback + detection / reset, verbatim, on its own stand-ins ----------------
+if [ -f "$HERE/ref_thrashing_glue.c" ]; then
+    pin uvm_perf_thrashing.c 6faca5e5b498600d
+    sed -n '30,43p' "$UVM/uvm_perf_utils.h" > "$TMP/x_perf_saturating.h"
+    sed -n '36,119p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_thrashing_types.h"
+    sed -n '376,384p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_thrashing_stamps.h"
+    sed -n '1023,1073p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_thrashing_detect.h"
+    sed -n '1077,1093p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_thrashing_region.h"
+    sed -n '1230,1380p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_thrashing_event.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_thrashing_glue.c" -o "$OUT/libref_thrashing.so"
+    echo "build_ref: built $OUT/libref_thrashing.so"
+fi
+
 # ---------------- access-counter front half: parse + fetch + preprocess, verbatim, on the fault leg's shims ----------------
 if [ -f "$HERE/ref_access_counters_front_glue.c" ]; then
     pin uvm_turing_access_counter_buffer.c b4afc3558d7cc578

@@ -1,0 +1,70 @@
+"""CPU tests of the thrashing detector (section 1f of include/uvmtier.h): the restatement against the reference's own
+event callback compiled verbatim (oracle/_ref/libref_thrashing.so), on directed sequences and on random event
+streams; per-va_block processing order (what the device entry point uses) gives the time-order result."""
+import numpy as np
+import pytest
+
+import thrashlib as TH
+import uvmtier_testlib as T
+
+
+def events(rows):
+    ev = np.zeros(len(rows), TH.EVENT_DT)
+    for i, r in enumerate(rows):
+        ev[i] = tuple(r) + (0,) * (8 - len(r))
+    return ev
+
+
+def test_ping_pong_on_one_page_is_detected_at_the_threshold():
+    orc = T.load_oracle()
+    # (time, slot, first, n, processor, kind, flags): two processors take page 7 of va_block 2 from each other every 100 us
+    ev = events([(1000 + 100000 * i, 2, 7, 1, i & 1, 0, 0) for i in range(6)])
+    st = TH.run_oracle(orc, ev, 4)
+    # event 0 only stamps the block; event 1 opens the tracking (other processor inside the window) and stamps the page;
+    # events 2, 3, 4 are thrashing events 1, 2, 3 -> detected by event 4; event 5 is the fourth
+    assert st.blocks["tracked"].tolist() == [0, 0, 1, 0] and st.blocks["num_thrashing_pages"][2] == 1
+    assert st.thrashing_pages[2 * 16] == 1 << 7 and st.counters[0] == 1
+    w = int(st.page_word[2 * 512 + 7])
+    assert (w >> 60) & 7 == 4 and (w >> 58) & 1 == 1 and (w & ((1 << 58) - 1)) == (1000 + 500000) >> 6
+    assert st.page_procs[2 * 512 + 7] == 3 and st.blocks["last_thrashing_time_stamp"][2] == 1000 + 500000
+    # one processor alone never opens the tracking, however fast it faults
+    ev = events([(1000 + 100 * i, 1, 0, 512, 1, 0, 0) for i in range(50)])
+    st = TH.run_oracle(orc, ev, 2)
+    assert st.blocks["tracked"].sum() == 0 and st.counters[0] == 0 and not st.page_word.any()
+
+
+def test_window_expiry_resets_a_thrashing_page_and_user_migrations_clear_a_region():
+    orc = T.load_oracle()
+    rows = [(1000 + 1000 * i, 0, 0, 4, i & 1, i & 1, 0) for i in range(8)]      # migrations and revocations alternate
+    rows.append((1000 + 8000 + 2 * TH.LAPSE_NS, 0, 0, 2, 0, 0, 0))               # after the window: pages 0, 1 reset
+    rows.append((1000 + 9000 + 2 * TH.LAPSE_NS, 0, 3, 1, 0, 0, TH.EV_RESET))     # cudaMemPrefetchAsync-like: page 3 cleared
+    st = TH.run_oracle(orc, events(rows), 1)
+    assert st.thrashing_pages[0] == 0b0100 and st.blocks["num_thrashing_pages"][0] == 1 and st.counters.tolist()[:2] == [4, 3]
+    assert st.page_word[0] == 0 and st.page_word[1] == 0 and st.page_word[3] == 0 and st.page_procs[3] == 0
+    assert (int(st.page_word[2]) >> 58) & 3 == 3 and (int(st.page_word[2]) >> 60) & 7 == 6
+    # the reset event does not stamp the block (it returns before the epilogue)
+    assert st.blocks["last_time_stamp"][0] == 1000 + 8000 + 2 * TH.LAPSE_NS
+
+
+@pytest.mark.parametrize("seed,n_slots,n_events,threshold,lapse", [(1, 64, 20000, 3, TH.LAPSE_NS), (42, 8, 15000, 1, TH.LAPSE_NS),
+                                                                   (7, 200, 30000, 7, 100000), (0xC0FFEE, 32, 20000, 5, 4096)])
+def test_restatement_matches_reference_event_callback(seed, n_slots, n_events, threshold, lapse):
+    orc, ref = T.load_oracle(), T.load_ref("thrashing")
+    ev = TH.ping_pong_events(n_slots, n_events, seed, lapse_ns=lapse)
+    want = TH.run_ref(ref, ev, n_slots, lapse, threshold)
+    got = TH.run_oracle(orc, ev, n_slots, lapse, threshold)
+    TH.assert_state_equal(want, got, "seed %d" % seed)
+    assert want.counters[0] > 20 and want.counters[1] > 5 and want.blocks["tracked"].sum() > 2
+    # grouped by va_block (the device entry point's order): the va_blocks are independent, so nothing changes
+    again = TH.run_oracle(orc, TH.by_slot(ev), n_slots, lapse, threshold)
+    TH.assert_state_equal(want, again, "by slot, seed %d" % seed)
+
+
+def test_directed_sequences_match_reference():
+    orc, ref = T.load_oracle(), T.load_ref("thrashing")
+    rows = [(1000 + 100000 * i, 2, 7, 1, i & 1, 0, 0) for i in range(6)]
+    rows += [(10 ** 7 + 1000 * i, 0, 0, 4, i & 1, i & 1, 0) for i in range(8)]
+    rows += [(10 ** 7 + 8000 + 2 * TH.LAPSE_NS, 0, 0, 2, 0, 0, 0), (10 ** 7 + 9000 + 2 * TH.LAPSE_NS, 0, 3, 1, 0, 0, TH.EV_RESET)]
+    rows += [(10 ** 8 + 63 * i, 1, 500, 12, i % 3, 1, 0) for i in range(20)]     # time stamps closer than the 64 ns unit
+    ev = events(rows)
+    TH.assert_state_equal(TH.run_ref(ref, ev, 4), TH.run_oracle(orc, ev, 4), "directed")

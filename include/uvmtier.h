@@ -696,6 +696,71 @@ NV_STATUS uvmtier_access_counters_service_device(uvmtier_ctx_t *ctx, uint32_t n_
                                                  uint32_t run_cap, uint32_t *d_counters);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (1f) Thrashing detection -- UVM/uvm_perf_thrashing.c:1230-1380                              */
+/* ------------------------------------------------------------------------------------------ */
+
+/* The reference learns about thrashing from two perf events, raised under the va_block lock: a MIGRATION
+ * (uvm_va_block.c:4291,4303) and a permission REVOCATION.  thrashing_event_cb (:1230-1380) keeps, per page, the time
+ * of the last event, a 3-bit count of events that followed the previous one within `lapse` and the processors
+ * involved; a page whose count reaches `threshold` enters the va_block's thrashing_pages mask (thrashing_detected
+ * :1023-1040) -- the mask uvm_perf_thrashing_get_thrashing_pages (:1803) hands to the prefetcher, which leaves those
+ * pages alone (uvm_perf_prefetch.c:378-381,407) -- and leaves it when the window passes without an event
+ * (thrashing_reset_page :1045-1073) or a user-driven migration covers it (:1272-1285).  Per-page state only exists
+ * once two different processors touched the va_block inside the window (:1316-1337).
+ * Built: this detector.  Not built: the hint that pins or throttles a thrashing page (:1455-1800); no page is ever
+ * pinned or throttled here.  Events of evictions and of the first half of staged copies are not sent (:1254-1260). */
+#define UVMTIER_PERF_EVENT_MIGRATION  0u
+#define UVMTIER_PERF_EVENT_REVOCATION 1u
+#define UVMTIER_PERF_EVENT_RESETS     0x1u /* flags: a migration whose cause is not a fault, an access counter or a
+                                            * prefetch, or that copies instead of moving, or under read duplication */
+typedef struct {
+    uint64_t time_stamp;     /* ns (NV_GETTIME() at the callback); events of a va_block arrive in time order */
+    uint32_t slot;           /* va_block: its row of the state table                                          */
+    uint16_t first_page;     /* region: (address - block start) / 4K                                          */
+    uint16_t num_pages;      /* bytes / 4K; first_page + num_pages <= 512                                      */
+    uint16_t processor;      /* migration.dst / revocation.proc_id, < 32                                       */
+    uint8_t kind;            /* UVMTIER_PERF_EVENT_MIGRATION / _REVOCATION                                     */
+    uint8_t flags;           /* UVMTIER_PERF_EVENT_RESETS                                                      */
+    uint32_t reserved;
+} uvmtier_perf_event_t;      /* 24 bytes */
+
+typedef struct {
+    uint64_t last_time_stamp;           /* block_thrashing_info_t (:88-119), the detector's fields */
+    uint64_t last_thrashing_time_stamp;
+    uint16_t last_processor;
+    uint16_t num_thrashing_pages;
+    uint32_t tracked;                   /* pages != NULL */
+    uint64_t reserved;
+} uvmtier_thrashing_block_t;            /* 32 bytes */
+
+/* Device tables, one row per va_block slot of the layout.  d_page_word: the reference's first bit-field word of
+ * page_thrashing_info_t (:46-63) -- bits 0-57 last_time_stamp in 64 ns units, 58 has_migration_events,
+ * 59 has_revocation_events, 60-62 num_thrashing_events, 63 pinned (always 0 here).  d_thrashing_pages: 16 words per
+ * slot, the layout of the residency masks, so it can be passed wherever a thrashing mask is taken (section 2). */
+typedef struct {
+    uvmtier_thrashing_block_t *d_blocks;
+    uint64_t *d_page_word;        /* n_slots * 512 */
+    uint32_t *d_page_processors;  /* n_slots * 512: page_thrashing_info_t.processors */
+    uint32_t *d_thrashing_pages;  /* n_slots * 16 */
+    uint32_t *d_scratch;
+    uint64_t lapse_ns;            /* uvm_perf_thrashing_lapse_usec * 1000 (default 500 us, :264) */
+    uint32_t threshold;           /* uvm_perf_thrashing_threshold (default 3, :246); 1..7 */
+    uint32_t n_slots;
+} uvmtier_thrashing_t;
+
+/* lapse_ns = 0 and threshold = 0 take the reference's defaults.  Tables start out all zero (no history). */
+NV_STATUS uvmtier_thrashing_create(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uint64_t lapse_ns, uint32_t threshold,
+                                   uvmtier_thrashing_t *out);
+NV_STATUS uvmtier_thrashing_destroy(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t);
+
+/* Applies n_events events, asynchronously on the context's stream.  d_events must be grouped by slot (all events of a
+ * va_block next to each other, in time order); the groups may come in any order.  d_counters (4 words, zeroed
+ * here): [0] pages detected as thrashing (the reference's num_thrashing statistic), [1] pages reset, [2] events
+ * dropped -- malformed, or belonging to a second group of a va_block that already had one in this call. */
+NV_STATUS uvmtier_thrashing_note_events_device(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, uint32_t n_events,
+                                               const uvmtier_perf_event_t *d_events, uint32_t *d_counters);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */
 

@@ -78,6 +78,13 @@ class PmmState(ctypes.Structure):
                 ("n_slots", ctypes.c_uint32), ("capacity_chunks", ctypes.c_uint32)]
 
 
+class ThrashingState(ctypes.Structure):
+    """uvmtier_thrashing_t"""
+    _fields_ = [("d_blocks", ctypes.c_void_p), ("d_page_word", ctypes.c_void_p), ("d_page_processors", ctypes.c_void_p),
+                ("d_thrashing_pages", ctypes.c_void_p), ("d_scratch", ctypes.c_void_p), ("lapse_ns", ctypes.c_uint64),
+                ("threshold", ctypes.c_uint32), ("n_slots", ctypes.c_uint32)]
+
+
 class TieringStats(ctypes.Structure):
     """uvmtier_tiering_stats_t"""
     _fields_ = [("passes", ctypes.c_uint32), ("eviction_waves", ctypes.c_uint32), ("evicted_to_dram", ctypes.c_uint32),
@@ -356,6 +363,34 @@ class Context:
 
     def pmm_destroy(self, pmm):
         _check(lib().uvmtier_pmm_destroy(self._h, ctypes.byref(pmm)), "uvmtier_pmm_destroy")
+
+    def thrashing_create(self, layout, lapse_ns=0, threshold=0):
+        t = ThrashingState()
+        _check(lib().uvmtier_thrashing_create(self._h, P(layout), ctypes.c_uint64(lapse_ns), ctypes.c_uint32(threshold), ctypes.byref(t)),
+               "uvmtier_thrashing_create")
+        return t
+
+    def thrashing_destroy(self, t):
+        _check(lib().uvmtier_thrashing_destroy(self._h, ctypes.byref(t)), "uvmtier_thrashing_destroy")
+
+    def thrashing_note_events(self, t, events):
+        """uvmtier_thrashing_note_events_device on a host array of uvmtier_perf_event_t (24-byte records, grouped by
+        slot).  Returns the four counters."""
+        d_ev, d_cnt = self.to_device(events), self.alloc(16)
+        try:
+            _check(lib().uvmtier_thrashing_note_events_device(self._h, ctypes.byref(t), ctypes.c_uint32(len(events)), P(d_ev), P(d_cnt)),
+                   "uvmtier_thrashing_note_events_device")
+            self.synchronize()
+            return self.from_device(d_cnt, 4, "<u4")
+        finally:
+            self.free(d_ev); self.free(d_cnt)
+
+    def thrashing_tables(self, t):
+        """The detector's tables back on the host: va_block records (32-byte rows), page words, page processors, masks."""
+        n = t.n_slots
+        return dict(blocks=self.from_device(t.d_blocks, n * 32, "u1"), page_word=self.from_device(t.d_page_word, n * 512, "<u8"),
+                    page_procs=self.from_device(t.d_page_processors, n * 512, "<u4"),
+                    thrashing_pages=self.from_device(t.d_thrashing_pages, n * 16, "<u4"))
 
     def pmm_stamps(self, pmm):
         return self.from_device(pmm.d_stamp, pmm.n_slots, "<u8")

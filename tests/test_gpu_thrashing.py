@@ -1,0 +1,61 @@
+"""GPU tests of the thrashing detector through the C ABI vs the CPU restatement: every table bit-exact, over several
+calls (history carries over), plus what the entry point does with events it cannot place."""
+import numpy as np
+import pytest
+
+import servicelib as S
+import thrashlib as TH
+import uvmtier
+import uvmtier_testlib as T
+from uvmtier import tracegen as TG
+
+pytestmark = pytest.mark.gpu
+
+
+def gpu_state(ctx, t, counters):
+    tb = ctx.thrashing_tables(t)
+    st = TH.State(t.n_slots)
+    st.blocks = tb["blocks"].view(TH.BLOCK_DT)
+    st.page_word, st.page_procs, st.thrashing_pages = tb["page_word"], tb["page_procs"], tb["thrashing_pages"]
+    st.counters = counters
+    return st
+
+
+@pytest.mark.parametrize("seed,n_slots,n_events,threshold,lapse,calls", [(1, 64, 20000, 3, TH.LAPSE_NS, 1), (42, 8, 15000, 1, TH.LAPSE_NS, 3),
+                                                                         (7, 2048, 60000, 7, 100000, 2), (9, 32, 20000, 5, 4096, 4)])
+def test_gpu_thrashing_tables_match_oracle(seed, n_slots, n_events, threshold, lapse, calls):
+    orc = T.load_oracle()
+    ev = TH.ping_pong_events(n_slots, n_events, seed, lapse_ns=lapse)
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1))
+    want = TH.State(n_slots)
+    total = np.zeros(4, "<u4")
+    with uvmtier.Context(0) as ctx:
+        t = ctx.thrashing_create(layout, lapse, threshold)
+        for part in np.array_split(ev, calls):                    # time slices: each call continues the history
+            part = TH.by_slot(part)
+            total += ctx.thrashing_note_events(t, part)
+            TH.run_oracle(orc, part, n_slots, lapse, threshold, st=want)
+        got = gpu_state(ctx, t, total)
+        ctx.thrashing_destroy(t)
+    TH.assert_state_equal(want, got, "seed %d" % seed)
+    assert total[2] == 0 and want.counters[0] > 20 and int(want.blocks["num_thrashing_pages"].sum()) == int(
+        sum(bin(int(w)).count("1") for w in want.thrashing_pages))
+
+
+def test_events_that_cannot_be_placed_are_dropped_and_counted():
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=4, n_spaces=1))
+    rows = [(1000, 1, 0, 8, 0, 0, 0), (2000, 1, 0, 8, 1, 0, 0), (3000, 9, 0, 8, 0, 0, 0), (4000, 2, 510, 8, 0, 0, 0),
+            (5000, 2, 0, 8, 40, 0, 0), (6000, 1, 0, 8, 0, 0, 0), (7000, 1, 0, 8, 1, 0, 0)]   # slot 9, page 518, processor 40, slot 1 again
+    ev = np.zeros(len(rows), TH.EVENT_DT)
+    for i, r in enumerate(rows):
+        ev[i] = tuple(r) + (0,)
+    with uvmtier.Context(0) as ctx:
+        t = ctx.thrashing_create(layout)
+        assert t.lapse_ns == 500000 and t.threshold == 3
+        cnt = ctx.thrashing_note_events(t, ev)
+        tb = ctx.thrashing_tables(t)
+        assert ctx.thrashing_note_events(t, ev[:0]).tolist() == [0, 0, 0, 0]
+        ctx.thrashing_destroy(t)
+    assert cnt.tolist() == [0, 0, 5, 0]
+    blocks = tb["blocks"].view(TH.BLOCK_DT)
+    assert blocks["last_time_stamp"].tolist() == [0, 2000, 0, 0] and blocks["tracked"].tolist() == [0, 1, 0, 0]

@@ -466,6 +466,53 @@ def access_counter_numbers(ctx, lib, P, rank):
     return out
 
 
+def thrashing_numbers(ctx, lib, P, rank):
+    """The thrashing detector on the 64 GB table shape: 32768 va_blocks x 32 events of 16 pages each per call, two
+    processors taking turns inside the window (every page of a region is read, stamped and written back).  Device
+    resident events, grouped by va_block; CUDA events on the library's stream."""
+    from uvmtier.blockstate import make_layout
+    from uvmtier import tracegen as TG
+    n_slots, per, pages, calls = 32768, 32, 16, 6
+    n = n_slots * per
+    rng = np.random.default_rng(11 + rank)
+    layout = make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots // 4, n_spaces=4))
+    ev_dt = np.dtype([("time_stamp", "<u8"), ("slot", "<u4"), ("first_page", "<u2"), ("num_pages", "<u2"), ("processor", "<u2"),
+                      ("kind", "u1"), ("flags", "u1"), ("reserved", "<u4")])
+    t = ctx.thrashing_create(layout)
+    d_cnt = ctx.alloc(16)
+    ms, times, det = ctypes.c_float(0), [], 0
+    for it in range(calls):
+        ev = np.zeros(n, ev_dt)
+        k = np.tile(np.arange(per, dtype=np.uint64), n_slots)
+        ev["slot"] = np.repeat(np.arange(n_slots, dtype=np.uint32), per)
+        ev["time_stamp"] = np.uint64(1000) + (np.uint64(it * per) + k) * np.uint64(20000) + rng.integers(0, 5000, n).astype(np.uint64)
+        ev["first_page"] = rng.integers(0, 4, n).astype(np.uint16) * 128 + rng.integers(0, 8, n).astype(np.uint16)
+        ev["num_pages"] = pages
+        ev["processor"] = (k & np.uint64(1)).astype(np.uint16)
+        ev["kind"] = (rng.random(n) < 0.15).astype(np.uint8)
+        d_ev = ctx.to_device(ev)
+        lib.uvmtier_event_record(ctx.handle, 920)
+        st = lib.uvmtier_thrashing_note_events_device(ctx.handle, ctypes.byref(t), ctypes.c_uint32(n), P(d_ev), P(d_cnt))
+        lib.uvmtier_event_record(ctx.handle, 921)
+        assert st == 0, hex(st)
+        lib.uvmtier_event_elapsed_ms(ctx.handle, 920, 921, ctypes.byref(ms))
+        cnt = ctx.from_device(d_cnt, 4, "<u4")
+        assert cnt[2] == 0
+        det += int(cnt[0])
+        if it >= 2:
+            times.append(ms.value)
+        ctx.free(d_ev)
+    masks = ctx.from_device(t.d_thrashing_pages, n_slots * 16, "<u4")
+    thrashing_pages = int(np.unpackbits(masks.view(np.uint8)).sum())
+    ctx.thrashing_destroy(t)
+    ctx.free(d_cnt)
+    m = float(np.mean(times))
+    alg = n * pages * 24 + n * 24 + n_slots * 2 * 96       # page word + processors read and written, events, va_block rows
+    return {"events": n, "va_blocks": n_slots, "pages_per_event": pages, "ms": m, "events_per_s": n / (m * 1e-3),
+            "algorithmic_bytes": alg, "GBps": alg / (m * 1e-3) / 1e9, "detections": det, "thrashing_pages": thrashing_pages,
+            "what": "two processors alternate on 16-page regions every 20 us (window 500 us, threshold 3)"}
+
+
 # ----------------------------------------------------------------------------------------------- GPU arm
 _REAL_STDOUT = None
 
@@ -670,6 +717,9 @@ def main():
     access = None
     if not args.no_migration and rank == 0:
         access = access_counter_numbers(ctx, lib, P, rank)
+    thrash = None
+    if not args.no_migration and rank == 0:
+        thrash = thrashing_numbers(ctx, lib, P, rank)
     clocks = sampler.stop(windows=((wall0, wall1), (wall2, wall3)))
 
     # ---- max over ranks ----
@@ -719,6 +769,7 @@ def main():
         "migration": migration,
         "oversubscription": oversub,
         "access_counters": access,
+        "thrashing": thrash,
         "wall_s_timed_region": wall1 - wall0,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -74,9 +74,8 @@ NV_STATUS uvmtier_thrashing_note_events_device(uvmtier_ctx_t *ctx, uvmtier_thras
     UVMTIER_LAUNCH(k_thrash_heads, (int)grid, kThrashThreads, 0, ctx->stream, n_events, d_events, t->n_slots, t->d_scratch, d_counters);
     // one warp per va_block with events; at most n_slots of them
     const uint64_t segs = n_events < t->n_slots ? n_events : t->n_slots;
-    uint64_t grid2 = (segs * 32 + kThrashThreads - 1) / kThrashThreads;
-    if (grid2 > (uint64_t)ctx->sm_count * 8)
-        grid2 = (uint64_t)ctx->sm_count * 8;
+    // (no cap on the grid: a warp's chain of events is latency bound, the block scheduler balances the chains)
+    const uint64_t grid2 = (segs * 32 + kThrashThreads - 1) / kThrashThreads;
     UVMTIER_LAUNCH(k_thrash_events, (int)grid2, kThrashThreads, 0, ctx->stream, n_events, d_events, t->n_slots,
                    (unsigned long long)t->lapse_ns, t->threshold, t->d_blocks, (unsigned long long *)t->d_page_word,
                    t->d_page_processors, t->d_thrashing_pages, t->d_scratch, d_counters);

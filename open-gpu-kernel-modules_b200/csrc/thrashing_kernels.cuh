@@ -61,10 +61,13 @@ k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, 
         uint32_t mask = lane < 16 ? masks[(size_t)slot * 16 + lane] : 0u;
         unsigned long long *words = page_word + (size_t)slot * 512;
         uint32_t *procs = page_procs + (size_t)slot * 512;
+        uvmtier_perf_event_t e_next = ev[i];
         for (; i < n_events; i++) {
-            const uvmtier_perf_event_t e = ev[i];
+            const uvmtier_perf_event_t e = e_next;
             if (e.slot != slot)
                 break;
+            if (i + 1 < n_events)
+                e_next = ev[i + 1];                        // in flight while this event's pages are worked on
             if (!thrash_event_ok(e, n_slots)) {
                 dropped += lane == 0;
                 continue;

@@ -71,6 +71,17 @@ def run():
         nk = A.run_preprocess(orc, "oracle_access_counters_fetch_preprocess", nring, 0, len(npk), 256, ntbl)
         S.assert_service_equal(A.run_service_oracle(orc, nk, 256, ntbl, nlayout, nst0), got, 256, "smoke access counters")
 
+        # (2c) thrashing detector: two processors fighting over a few va_blocks
+        import thrashlib as TH
+        tev = TH.by_slot(TH.ping_pong_events(16, 3000, 3))
+        tt = ctx.thrashing_create(S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=16, n_spaces=1)))
+        tcnt = ctx.thrashing_note_events(tt, tev)
+        ttab = ctx.thrashing_tables(tt)
+        ctx.thrashing_destroy(tt)
+        twant = TH.run_oracle(orc, tev, 16)
+        assert np.array_equal(ttab["thrashing_pages"], twant.thrashing_pages) and np.array_equal(ttab["page_word"], twant.page_word)
+        assert tcnt[0] == twant.counters[0] and tcnt[0] > 0, "smoke: thrashing detections differ"
+
         # (3) migration: 4 KB pages DRAM -> HBM in random order, byte exact
         nbytes = 8 << 20
         info = {t: ctx.tier_create(t, nbytes) for t in (TIER_HBM, TIER_DRAM)}
@@ -84,5 +95,5 @@ def run():
 
         launches = uvmtier.kernel_launch_count() - before
         assert launches >= 10, "smoke: CUDA kernels were not launched"
-    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, make_resident, access counters, migration)" %
+    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, make_resident, access counters, thrashing, migration)" %
           (uvmtier.lib().uvmtier_version().decode(), launches))

@@ -59,3 +59,26 @@ def test_events_that_cannot_be_placed_are_dropped_and_counted():
     assert cnt.tolist() == [0, 0, 5, 0]
     blocks = tb["blocks"].view(TH.BLOCK_DT)
     assert blocks["last_time_stamp"].tolist() == [0, 2000, 0, 0] and blocks["tracked"].tolist() == [0, 1, 0, 0]
+
+
+def test_thrashing_entry_points_reject_bad_calls():
+    import ctypes
+    lib = uvmtier.lib()
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=4, n_spaces=1))
+    INVALID_ARGUMENT = 0x1F
+    with uvmtier.Context(0) as ctx:
+        h = ctx.handle
+        launches = uvmtier.kernel_launch_count()
+        t = uvmtier.ThrashingState()
+        assert lib.uvmtier_thrashing_create(h, uvmtier.P(layout), ctypes.c_uint64(0), ctypes.c_uint32(8), ctypes.byref(t)) == INVALID_ARGUMENT
+        assert lib.uvmtier_thrashing_create(h, None, ctypes.c_uint64(0), ctypes.c_uint32(3), ctypes.byref(t)) == INVALID_ARGUMENT
+        d = ctx.alloc(64)
+        # a table that was never created, missing counters, events announced but not given
+        assert lib.uvmtier_thrashing_note_events_device(h, ctypes.byref(t), ctypes.c_uint32(1), uvmtier.P(d), uvmtier.P(d)) == INVALID_ARGUMENT
+        t = ctx.thrashing_create(layout)
+        assert lib.uvmtier_thrashing_note_events_device(h, ctypes.byref(t), ctypes.c_uint32(1), uvmtier.P(d), None) == INVALID_ARGUMENT
+        assert lib.uvmtier_thrashing_note_events_device(h, ctypes.byref(t), ctypes.c_uint32(1), None, uvmtier.P(d)) == INVALID_ARGUMENT
+        assert uvmtier.kernel_launch_count() == launches
+        ctx.thrashing_destroy(t)
+        assert t.d_blocks is None and t.n_slots == 0
+        ctx.free(d)

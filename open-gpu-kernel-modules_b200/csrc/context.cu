@@ -16,6 +16,7 @@ void uvmtier_set_error(const char *what, cudaError_t err, const char *file, int 
 void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx);
 void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx);
 void uvmtier_service_scratch_destroy(uvmtier_ctx_t *ctx);
+NV_STATUS uvmtier_service_prepare(uvmtier_ctx_t *ctx);
 
 extern "C" {
 
@@ -87,6 +88,25 @@ NV_STATUS uvmtier_init(int device, const uvmtier_config_t *cfg, uvmtier_ctx_t **
         uvmtier_set_error("cudaStreamCreateWithFlags", e, __FILE__, __LINE__);
         free(ctx);
         return uvmtier_status_from_cuda(e);
+    }
+    // Everything the servicing pass needs besides memory exists from here on: its two side streams, the events that
+    // fork and join them, and the device address of the fixed working space of the no-alloc entry point (looking it
+    // up loads the module that holds the array).  A servicing call then creates nothing, whichever comes first.
+    for (int i = 0; i < 2 && e == cudaSuccess; i++)
+        e = cudaStreamCreateWithFlags(&ctx->aux_stream[i], cudaStreamNonBlocking);
+    for (int i = 0; i < 4 && e == cudaSuccess; i++)
+        e = cudaEventCreateWithFlags(&ctx->aux_events[i], cudaEventDisableTiming);
+    NV_STATUS ps = NV_OK;
+    if (e != cudaSuccess) {
+        uvmtier_set_error("side streams of the servicing pass", e, __FILE__, __LINE__);
+        ps = uvmtier_status_from_cuda(e);
+    }
+    else {
+        ps = uvmtier_service_prepare(ctx);
+    }
+    if (ps != NV_OK) {
+        uvmtier_deinit(ctx);
+        return ps;
     }
     *out_ctx = ctx;
     return NV_OK;

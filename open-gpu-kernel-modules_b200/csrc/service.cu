@@ -54,30 +54,6 @@ static service_scratch_view scratch_view(uint32_t *base, uint32_t n_slots, uint3
     return v;
 }
 
-static uint32_t service_lanes_per_block()
-{
-    static int lanes = -1;
-    if (lanes < 0) {
-        const char *e = getenv("UVMTIER_SERVICE_LANES");
-        const int v = e ? atoi(e) : 4;
-        lanes = (v == 1 || v == 2 || v == 4 || v == 8 || v == 16) ? v : 4;
-    }
-    return (uint32_t)lanes;
-}
-
-template <int G, int M>
-static NV_STATUS launch_grp(uvmtier_ctx_t *ctx, const service_kparams &prm, const uvmtier_ordered_fault_t *d_ordered,
-                            const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const block_state_ptrs &bs,
-                            const service_scratch_view &v, uint32_t heavy_min, uint16_t *d_entry_flags,
-                            uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t *d_counters)
-{
-    const size_t threads = (size_t)prm.n_slots * G;
-    const uint32_t grid = (uint32_t)((threads + kGrpThreads - 1) / kGrpThreads);
-    UVMTIER_LAUNCH((k_service_blocks_grp<G, M>), grid, kGrpThreads, 0, ctx->stream, prm, d_ordered, d_groups, d_batches, bs,
-                   (const uint2 *)v.cw, v.offset, v.list, v.light, v.cursor + 1, d_entry_flags, d_service, d_runs, d_counters);
-    return NV_OK;
-}
-
 // The whole pass on the context's stream, working space at `base` (v.words words).
 static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,
                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const uvmtier_va_layout_t *lay,
@@ -135,11 +111,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
         grid = cap;
     UVMTIER_LAUNCH(k_service_count, (int)grid, kSvcThreads, 0, ctx->stream, prm, d_groups, d_batches, d_tbl,
                    (unsigned long long *)v.cw, v.batch_unmapped, (uint2 *)v.slotpos);
-    // UVMTIER_SERVICE_HEAVY_MIN moves the group / warp split up (for experiments; 0xffffffff = no block on a warp).
-    // It cannot go below kHeavyMinEntries: that is what bounds the length of the heavy list.
-    static const char *heavy_env = getenv("UVMTIER_SERVICE_HEAVY_MIN");
-    const uint32_t heavy_min = heavy_env ? (uint32_t)strtoul(heavy_env, NULL, 0) : kHeavyMinEntries;
-    const uint32_t list_heavy_min = heavy_min < kHeavyMinEntries ? kHeavyMinEntries : heavy_min;
+    const uint32_t list_heavy_min = kHeavyMinEntries;
     UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, list_heavy_min, v.offset, v.cursor, v.hist,
                    v.light_rank);
     UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
@@ -148,54 +120,40 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
         sgrid = cap;
     UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
                    v.big, v.heavy, v.hist, v.light_rank, v.light);
-    // Three independent branches from here: the light va_blocks (lane groups), the heavy ones (their long lists are
-    // sorted first, then a warp each) and the runs outside every va_range.  They touch different va_blocks, records
-    // and entry flags, and add to the batch counters atomically; the two small branches run on side streams next
-    // to the big one (UVMTIER_SERVICE_FORK=0 keeps everything on the context's stream).
-    static const char *fork_env = getenv("UVMTIER_SERVICE_FORK");
-    const bool fork = !(fork_env && atoi(fork_env) == 0);
-    cudaStream_t s_heavy = ctx->stream, s_unmapped = ctx->stream;
-    if (fork) {
-        for (int i = 0; i < 2; i++)
-            if (!ctx->aux_stream[i])
-                UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->aux_stream[i], cudaStreamNonBlocking));
-        for (int i = 0; i < 4; i++)
-            if (!ctx->aux_events[i])
-                UVMTIER_CUDA(cudaEventCreateWithFlags(&ctx->aux_events[i], cudaEventDisableTiming));
-        s_heavy = ctx->aux_stream[0];
-        s_unmapped = ctx->aux_stream[1];
-        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[0], ctx->stream));
-        UVMTIER_CUDA(cudaStreamWaitEvent(s_heavy, ctx->aux_events[0], 0));
-        UVMTIER_CUDA(cudaStreamWaitEvent(s_unmapped, ctx->aux_events[0], 0));
-    }
+    // Three independent branches from here: the light va_blocks (lane groups), the heavy ones (their long lists
+    // are sorted first, then a warp each) and the runs outside every va_range.  They touch different va_blocks,
+    // records and entry flags, and add to the batch counters atomically; the two small branches run on side streams
+    // (created with the context) next to the big one.
+    cudaStream_t s_heavy = ctx->aux_stream[0], s_unmapped = ctx->aux_stream[1];
+    UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[0], ctx->stream));
+    UVMTIER_CUDA(cudaStreamWaitEvent(s_heavy, ctx->aux_events[0], 0));
+    UVMTIER_CUDA(cudaStreamWaitEvent(s_unmapped, ctx->aux_events[0], 0));
     UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, s_heavy, cw, v.offset, v.list, v.big);
     UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, s_heavy, prm, d_ordered, d_groups, d_batches, bs, cw,
                    v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
     UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, s_unmapped, prm, d_ordered, d_groups, d_batches, d_tbl,
                    v.batch_unmapped, d_entry_flags, d_service);
-    if (fork) {
-        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[1], s_heavy));
-        UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[2], s_unmapped));
-    }
-
-    // lanes per va_block x CTAs per SM the kernel is compiled for; UVMTIER_SERVICE_LANES / UVMTIER_SERVICE_MINCTAS
-    // pick another instantiation (for experiments)
-    static const char *minctas_env = getenv("UVMTIER_SERVICE_MINCTAS");
-    const int minctas = minctas_env ? atoi(minctas_env) : 0;
-#define GRP_ARGS ctx, prm, d_ordered, d_groups, d_batches, bs, v, list_heavy_min, d_entry_flags, d_service, d_runs, d_counters
+    UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[1], s_heavy));
+    UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[2], s_unmapped));
+    // light va_blocks: four lanes each
     NV_STATUS st = NV_OK;
-    switch (service_lanes_per_block()) {
-        case 1: st = launch_grp<1, 1>(GRP_ARGS); break;
-        case 2: st = minctas == 4 ? launch_grp<2, 4>(GRP_ARGS) : (minctas == 3 ? launch_grp<2, 3>(GRP_ARGS) : launch_grp<2, 2>(GRP_ARGS)); break;
-        case 8: st = minctas == 8 ? launch_grp<8, 8>(GRP_ARGS) : (minctas == 6 ? launch_grp<8, 6>(GRP_ARGS) : launch_grp<8, 5>(GRP_ARGS)); break;
-        case 16: st = launch_grp<16, 8>(GRP_ARGS); break;
-        default: st = minctas == 7 ? launch_grp<4, 7>(GRP_ARGS) : minctas == 6 ? launch_grp<4, 6>(GRP_ARGS) : (minctas == 5 ? launch_grp<4, 5>(GRP_ARGS) : launch_grp<4, 4>(GRP_ARGS)); break;
+    {
+        // one wave: as many CTAs as the GPU keeps resident (fewer when the table is small); v.cursor[2] is the work counter
+        uint32_t grid = (uint32_t)(((size_t)n_slots * kGrpLanes + kGrpThreads - 1) / kGrpThreads);
+        if (grid > (uint32_t)ctx->sm_count * kGrpMinCtas)
+            grid = (uint32_t)ctx->sm_count * kGrpMinCtas;
+        k_service_blocks_grp<kGrpLanes, kGrpMinCtas><<<grid, kGrpThreads, 0, ctx->stream>>>(
+            prm, d_ordered, d_groups, d_batches, bs, cw, v.offset, v.list, v.light, v.cursor + 1, d_entry_flags, d_service, d_runs,
+            d_counters, v.cursor + 2);
+        g_uvmtier_launches.fetch_add(1, std::memory_order_relaxed);
+        const cudaError_t le = cudaGetLastError();
+        if (le != cudaSuccess) {                                // the side streams are joined below all the same
+            uvmtier_set_error("k_service_blocks_grp", le, __FILE__, __LINE__);
+            st = uvmtier_status_from_cuda(le);
+        }
     }
-#undef GRP_ARGS
-    if (fork) {                                             // join, also when the launch above failed
-        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[1], 0));
-        UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[2], 0));
-    }
+    UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[1], 0));
+    UVMTIER_CUDA(cudaStreamWaitEvent(ctx->stream, ctx->aux_events[2], 0));
     return st;
 }
 
@@ -665,6 +623,21 @@ static __device__ __align__(256) uint32_t g_service_scratch[kNoAllocWords];
 // address is looked up once per GPU, with that GPU current, and kept here.
 static uint32_t *g_service_scratch_addr[64];
 
+// Called by uvmtier_init with the context's GPU current: resolves the array's device address once per GPU.  This
+// first touch is also what makes the CUDA runtime load this file's module (and with it reserve the array), so it
+// happens while the caller is setting up, not in a servicing call made under memory pressure.
+NV_STATUS uvmtier_service_prepare(uvmtier_ctx_t *ctx)
+{
+    if (ctx->device < 0 || ctx->device >= 64)
+        return NV_OK;                                                     // the no-alloc entry point rejects such a context
+    if (!g_service_scratch_addr[ctx->device]) {
+        uint32_t *p = NULL;
+        UVMTIER_CUDA(cudaGetSymbolAddress((void **)&p, g_service_scratch));
+        g_service_scratch_addr[ctx->device] = p;
+    }
+    return NV_OK;
+}
+
 extern "C" NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
                                                                   const uvmtier_ordered_fault_t *d_ordered,
                                                                   const uvmtier_fault_group_t *d_groups,
@@ -700,11 +673,8 @@ extern "C" NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t 
     if (scratch_view(NULL, n_slots, n_batches, total).words > kNoAllocWords)
         return NV_ERR_INVALID_ARGUMENT;                                   // cannot happen within the three limits above
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
-    if (!g_service_scratch_addr[ctx->device]) {
-        uint32_t *p = NULL;
-        UVMTIER_CUDA(cudaGetSymbolAddress((void **)&p, g_service_scratch));
-        g_service_scratch_addr[ctx->device] = p;
-    }
+    if (!g_service_scratch_addr[ctx->device])                             // uvmtier_init looked it up; cannot be missing
+        return NV_ERR_INVALID_STATE;
     return service_pass(ctx, g_service_scratch_addr[ctx->device], n_batches, d_ordered, d_groups, d_batches, lay, state,
                         d_entry_flags, d_service, d_runs, run_cap, d_counters);
 }

@@ -21,32 +21,9 @@
 namespace uvmtier_k {
 
 constexpr int kGrpThreads = 128;
+constexpr int kGrpLanes = 4;                    // lanes per va_block the library runs with (W = 4 mask words per lane)
+constexpr int kGrpMinCtas = 4;                  // CTAs per SM the register allocation leaves room for
 constexpr uint32_t kFullWarp = 0xffffffffu;
-
-// ---- levels of <= 32 leaves inside one word (same arithmetic as pf_tree_select, offset 0) ----
-__device__ __forceinline__ uint32_t pf_word_levels(uint32_t w, uint32_t fw, uint32_t m0, uint32_t m1, uint32_t m2, uint32_t m3,
-                                                   uint32_t m4, uint32_t m5)
-{
-    const uint32_t c2 = w - ((w >> 1) & 0x55555555u);
-    const uint32_t c2e = c2 & 0x33333333u, c2o = (c2 >> 2) & 0x33333333u;
-    const uint32_t c4 = c2e + c2o;
-    const uint32_t c8 = (c4 + (c4 >> 4)) & 0x0f0f0f0fu;
-    const uint32_t c16 = (c8 + (c8 >> 8)) & 0x00ff00ffu;
-    const uint32_t c32 = (c16 + (c16 >> 16)) & 0x3fu;
-    const uint32_t a2 = (fw | (fw >> 1)) & 0x55555555u;
-    const uint32_t a4 = (a2 | (a2 >> 2)) & 0x11111111u;
-    const uint32_t a8 = (a4 | (a4 >> 4)) & 0x01010101u;
-    const uint32_t a16 = (a8 | (a8 >> 8)) & 0x00010001u;
-    const uint32_t s1 = m0 <= 1u ? (w & fw) : 0u;
-    const uint32_t d2e = ((c2e + (8u - m1) * 0x11111111u) >> 3) & 0x11111111u;
-    const uint32_t d2o = ((c2o + (8u - m1) * 0x11111111u) >> 3) & 0x11111111u;
-    const uint32_t s2 = (d2e & a2) | ((d2o & (a2 >> 2)) << 2);
-    const uint32_t s4 = (((c4 + (8u - m2) * 0x11111111u) >> 3) & 0x11111111u) & a4;
-    const uint32_t s8 = (((c8 + (128u - m3) * 0x01010101u) >> 7) & 0x01010101u) & a8;
-    const uint32_t s16 = (((c16 + (0x8000u - m4) * 0x00010001u) >> 15) & 0x00010001u) & a16;
-    const uint32_t s32 = (c32 >= m5 && fw != 0u) ? 0xffffffffu : 0u;
-    return s1 | ((s2 << 2) - s2) | ((s4 << 4) - s4) | ((s8 << 8) - s8) | ((s16 << 16) - s16) | s32;
-}
 
 // ---- reductions over the G lanes of each group; every lane of the warp takes part (xor butterflies stay inside
 //      the aligned group of G lanes) ----
@@ -109,8 +86,8 @@ template <int W> __device__ __forceinline__ void st_words(uint32_t *p, const uin
 // Prefetch hint of a whole aligned va_block held by a group (uvm_perf_prefetch_prenotify_fault_migrations
 // :327-413 + :477-500, GPU destination, no thrashing).  Called by all 32 lanes; `has` = this group's run has
 // serviced faults (otherwise f is zero, nothing is selected and *pi stays as it is).  f = faulted (new_residency)
-// words of this lane, gres = resident on the GPU.  Tree nodes of up to 32 leaves: SWAR inside a word, evaluated
-// only for words that hold a fault (most lanes have at most one; the loop runs until the slowest lane is done);
+// words of this lane, gres = resident on the GPU.  Tree nodes of up to 32 leaves: decided per word from its
+// population alone (the filled big pages pass every level below);
 // up to 32 W leaves: sums of this lane's per-word populations; above: an xor butterfly over the group (at step d
 // the sum covers the aligned 2d-lane node this lane belongs to).  Writes the prefetch mask to out[],
 // *n_prefetch = its population over the group, updates *pi (kept identically by every lane of the group), returns
@@ -123,8 +100,6 @@ __device__ __forceinline__ uint32_t pf_get_hint_grp(bool has, const uint32_t (&f
 {
     constexpr int W = 16 / G;
     const bool first_touch = has && block_empty && gpu_id == pref;          // :363-366
-    const uint32_t m0 = thr / 100u + 1u, m1 = (2u * thr) / 100u + 1u, m2 = (4u * thr) / 100u + 1u,
-                   m3 = (8u * thr) / 100u + 1u, m4 = (16u * thr) / 100u + 1u, m5 = (32u * thr) / 100u + 1u;
     uint32_t pages[W], cnt[W];
     uint32_t anyw = 0, weight = 0, lane_cnt = 0;
 #pragma unroll
@@ -139,23 +114,14 @@ __device__ __forceinline__ uint32_t pf_get_hint_grp(bool has, const uint32_t (&f
         anyw |= (f[w] != 0u) ? (1u << w) : 0u;
         weight += __popc(f[w]);
     }
-    // nodes of 2 .. 32 leaves
-    if constexpr (W == 1) {
-        out[0] = pf_word_levels(pages[0], f[0], m0, m1, m2, m3, m4, m5);
-    }
-    else {
-        uint32_t left = anyw;
-        while (__any_sync(kFullWarp, left != 0u)) {
-            const int j = left ? __ffs((int)left) - 1 : 0;
-            uint32_t pg = pages[0], fj = f[0];
+    // nodes of 2 .. 32 leaves.  Every big page that holds a fault is filled above, so each node of up to 16 leaves
+    // around a fault is full and passes (count * 100 > size * thr) for every threshold below 100, and none does at
+    // 100; what is left to decide inside the word is its node of 32 leaves.
+    if (thr < 100u) {
 #pragma unroll
-            for (int w = 1; w < W; w++)
-                if (j == w) { pg = pages[w]; fj = f[w]; }
-            const uint32_t lv = pf_word_levels(pg, left ? fj : 0u, m0, m1, m2, m3, m4, m5);
-#pragma unroll
-            for (int w = 0; w < W; w++)
-                if (j == w) out[w] |= lv;
-            left &= left - 1u;
+        for (int w = 0; w < W; w++) {
+            const uint32_t fill = ((f[w] & 0xffffu) ? 0xffffu : 0u) | ((f[w] >> 16) ? 0xffff0000u : 0u);
+            out[w] = fill | ((f[w] != 0u && cnt[w] * 100u > 32u * thr) ? 0xffffffffu : 0u);
         }
     }
     // nodes of 64 .. 32 W leaves: this lane's words
@@ -247,21 +213,31 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
                      const uint32_t *__restrict__ list, const uint32_t *__restrict__ light,
                      const uint32_t *__restrict__ n_light, uint16_t *__restrict__ entry_flags,
                      uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
-                     uint32_t *__restrict__ counters)
+                     uint32_t *__restrict__ counters, uint32_t *__restrict__ work)
 {
     constexpr int W = 16 / G;
-    // light[] holds the slots this kernel services, longest run list first: the groups of a warp then have about
-    // the same number of steps (a warp takes as many as its longest list) and the long warps start first
-    const uint32_t gid = (blockIdx.x * blockDim.x + threadIdx.x) / G;
     const int lane = threadIdx.x & 31, gl = lane & (G - 1), gb = lane & ~(G - 1);
+    const uint32_t n_slots_light = *n_light;
+    // The grid is one wave of resident CTAs; every warp keeps taking the next 32 / G slots of light[] from a counter
+    // until the list is used up.  light[] holds the slots this kernel services, longest run list first: the groups of
+    // a warp then have about the same number of steps (a warp takes as many as its longest list), and a warp that
+    // finishes early takes up the next, shorter, lists -- no second wave of CTAs on a half-empty GPU.
+    for (;;) {
+    uint32_t item = 0;
+    if (lane == 0)
+        item = atomicAdd(work, 1u);
+    item = __shfl_sync(kFullWarp, item, 0);
+    if (item * (32u / G) >= n_slots_light)
+        break;                                                            // the whole warp
+    const uint32_t gid = item * (32u / G) + (uint32_t)lane / G;
     uint32_t slot = 0, cnt = 0;
-    if (gid < *n_light) {
+    if (gid < n_slots_light) {
         slot = light[gid];
         cnt = cw[slot].x;
     }
     const uint32_t cnt_max = __reduce_max_sync(kFullWarp, cnt);
     if (!cnt_max)
-        return;                                                           // the whole warp
+        continue;
     const bool owns = cnt != 0;
     const uint32_t word0 = (uint32_t)gl * W;                              // first mask word of this lane
     const size_t wbase = (size_t)slot * 16 + word0;
@@ -563,6 +539,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
         if (gl == 0)
             st.prefetch_info[slot] = pi;
     }
+    }   // next work item
 }
 
 } // namespace uvmtier_k

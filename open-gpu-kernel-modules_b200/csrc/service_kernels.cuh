@@ -88,9 +88,11 @@ __device__ __forceinline__ uint32_t svc_slot(const service_kparams &prm, uint32_
 // ------------------------------------------------------------------------------------------------
 // Counts (and, with runs != NULL, writes) the copy runs of mask `m`: maximal sequences of consecutive pages
 // with the same cause (UVM/uvm_va_block.c:4242-4335).  Warp-synchronous; word per lane, half-warp wide.
+// Lanes 16-31 mirror lanes 0-15 in most callers and do not write (both_halves = false); with both_halves the two
+// half-warps work on two different va_blocks and both write.
 __device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint32_t slot, uint32_t src,
                                                   uvmtier_copy_run_t *runs, uint32_t at, uint32_t run_cap, int lane,
-                                                  uint32_t dst = UVMTIER_RUN_DST_HBM)
+                                                  uint32_t dst = UVMTIER_RUN_DST_HBM, bool both_halves = false)
 {
     const int l = lane & 15;
     uint32_t pm = __shfl_up_sync(HW_FULL, m >> 31, 1, 16);
@@ -124,7 +126,7 @@ __device__ __forceinline__ uint32_t svc_emit_runs(uint32_t m, uint32_t pf, uint3
         const uint32_t rest = s == 31 ? 0u : (stop >> (s + 1));
         const uint32_t first = (uint32_t)(32 * l + s);
         const uint32_t end = rest ? first + (uint32_t)__ffs((int)rest) : next_abs;
-        if (k < run_cap && lane < 16) {
+        if (k < run_cap && (lane < 16 || both_halves)) {
             uvmtier_copy_run_t r;
             r.slot = slot;
             r.first_page = (uint16_t)first;

@@ -109,9 +109,9 @@ def assert_ref_equals_oracle(ref_res, orc_res, what=""):
     assert np.array_equal(ref_res["runs"][:ref_res["n_runs"]], orc_res["runs"][:orc_res["n_runs"]]), what + " copy runs"
 
 
-def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, lanes=4, heavy_min=96):
-    """The product's servicing kernels under the CPU SIMT emulator.  lanes = lanes per va_block of the group kernel;
-    slots holding heavy_min entries or more go to the warp-per-block kernel (0 = all of them, 0xffffffff = none)."""
+def run_service_simt(sim, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 << 20, lanes=1, heavy_min=96):
+    """The product's servicing kernels under the CPU SIMT emulator.  Slots holding heavy_min entries or more go to the
+    warp-per-block kernel (0 = all of them, 0xffffffff = none), the others to the lane-group kernel (`lanes` is unused)."""
     B = int(gp["max_batch_size"][0])
     nb = len(k1["batch"])
     flags, svc, runs, counters = _alloc_outputs(nb, B, run_cap)

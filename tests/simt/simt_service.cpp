@@ -1,8 +1,8 @@
 // simt_service.cpp -- runs the servicing-pass kernels (service_kernels.cuh, service_grp.cuh) under the CPU SIMT
 // emulator with the same launch sequence as service_pass() in service.cu.  TEST INFRASTRUCTURE ONLY.
 //
-// lanes_per_block: 1, 2, 4, 8 or 16 (the group kernel's template parameter).  heavy_min: slots whose runs hold at
-// least this many entries are serviced by the warp-per-block kernel (0xffffffff = none, 0 = all).
+// lanes_per_block: unused (kept for the callers' signature).  heavy_min: slots whose runs hold at least this many
+// entries are serviced by the warp-per-block kernel (0xffffffff = none, 0 = all), the others by a group of four lanes each.
 #include "simt.h"
 
 #include <vector>
@@ -49,16 +49,9 @@ extern "C" int simt_service_fault_batches(uint32_t n_batches, uint32_t B, const 
     simt::launch(dim3(2), dim3(kSvcThreads), [&] { k_service_fill((uint32_t)total, slotpos.data(), offset.data(), list.data()); });
     simt::launch(dim3(3), dim3(kSortThreads), [&] { k_service_sort_lists(n_slots, cw, offset.data(), list.data(), heavy_min, big.data(), heavy.data(), hist.data(), light_rank.data(), light.data()); });
     simt::launch(dim3(2), dim3(kSortBigThreads), [&] { k_service_sort_big(cw, offset.data(), list.data(), big.data()); });
-    const uint32_t ggrid = (uint32_t)(((size_t)n_slots * lanes_per_block + kGrpThreads - 1) / kGrpThreads);
-#define GRP(G) simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<G, 1>(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), light.data(), cursor.data() + 1, entry_flags, service, runs, counters); })
-    switch (lanes_per_block) {
-        case 1: GRP(1); break;
-        case 2: GRP(2); break;
-        case 8: GRP(8); break;
-        case 16: GRP(16); break;
-        default: GRP(4); break;
-    }
-#undef GRP
+    (void)lanes_per_block;
+    const uint32_t ggrid = 2;   // fewer CTAs than work items: the warps keep pulling from the counter
+    simt::launch(dim3(ggrid), dim3(kGrpThreads), [&] { k_service_blocks_grp<kGrpLanes, 1>(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), light.data(), cursor.data() + 1, entry_flags, service, runs, counters, cursor.data() + 2); });
     simt::launch(dim3(3), dim3(kSvcThreads), [&] { k_service_blocks(prm, ordered, groups, batches, bs, cw, offset.data(), list.data(), heavy.data(), entry_flags, service, runs, counters); });
     simt::launch(dim3((n_batches + 127) / 128), dim3(128), [&] { k_service_unmapped(prm, ordered, groups, batches, tbl, unmapped.data(), entry_flags, service); });
     return 0;

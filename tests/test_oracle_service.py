@@ -30,7 +30,7 @@ def _both(pk, gp, tbl, lay, st0, pf=(1, 51, 1), **simt_args):
 @pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
 @pytest.mark.parametrize("B", [256, 48])
 def test_simt_service_matches_oracle(dist, B):
-    """Default split: va_blocks with few entries on 4-lane groups, the others on a warp each."""
+    """Default split: va_blocks with few entries on a group of four lanes each, the others on a warp each."""
     pk, tbl, lay = TG.fault_trace(1200, 21, dist, 2, total_va_bytes=SMALL_VA)
     gp = TG.gpu_params(B)
     st0 = S.random_state(lay["blocks_per_space"] * 2, 4)
@@ -40,16 +40,29 @@ def test_simt_service_matches_oracle(dist, B):
 
 
 @pytest.mark.parametrize("dist", ["uniform", "hotset", "adversarial"])
-@pytest.mark.parametrize("lanes,heavy_min", [(1, NONE_HEAVY), (2, NONE_HEAVY), (4, NONE_HEAVY), (8, NONE_HEAVY), (16, NONE_HEAVY),
-                                             (4, ALL_HEAVY), (4, 24)])
-def test_every_kernel_variant_matches_oracle(dist, lanes, heavy_min):
-    """Each lanes-per-block instantiation of the group kernel on its own, the warp-per-block kernel on its own
-    (entries filtered 32 at a time), and a split in the middle of this trace's weights."""
+@pytest.mark.parametrize("heavy_min", [NONE_HEAVY, ALL_HEAVY, 24])
+def test_every_kernel_variant_matches_oracle(dist, heavy_min):
+    """The lane-group kernel on its own, the warp-per-block kernel on its own (entries filtered 32 at a
+    time), and a split in the middle of this trace's weights."""
     pk, tbl, lay = TG.fault_trace(900, 33, dist, 2, total_va_bytes=SMALL_VA)
     gp = TG.gpu_params(128)
     st0 = S.random_state(lay["blocks_per_space"] * 2, 5)
-    _, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
-    S.assert_service_equal(want, got, 128, "%s lanes %d heavy_min %d" % (dist, lanes, heavy_min))
+    _, want, got = _both(pk, gp, tbl, lay, st0, heavy_min=heavy_min)
+    S.assert_service_equal(want, got, 128, "%s heavy_min %d" % (dist, heavy_min))
+
+
+@pytest.mark.parametrize("pf", [(1, 0, 1), (1, 1, 1), (1, 25, 1), (1, 50, 1), (1, 75, 3), (1, 99, 1), (1, 100, 1), (1, 51, 20), (0, 51, 1)])
+@pytest.mark.parametrize("heavy_min", [NONE_HEAVY, ALL_HEAVY])
+def test_prefetch_tunables_on_both_kernels(pf, heavy_min):
+    """Prefetch threshold 0..100, min_faults, prefetcher off: the lane-group kernel decides the levels inside a word from its
+    page count (filled big pages pass every level below them unless the threshold is 100), the
+    warp kernel evaluates every node; both must agree with the reference's leaf-to-root walk."""
+    pk, tbl, lay = TG.fault_trace(1500, 57, "uniform", 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(64)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 6, populated=0.55)
+    _, want, got = _both(pk, gp, tbl, lay, st0, pf=pf, heavy_min=heavy_min)
+    S.assert_service_equal(want, got, 64, "pf %s heavy_min %d" % (pf, heavy_min))
+    S.check_service_invariants(got, st0)
 
 
 def test_long_chains_of_duplicates_in_the_entry_parallel_filter():
@@ -71,8 +84,8 @@ def test_long_chains_of_duplicates_in_the_entry_parallel_filter():
     st0.gpu_pte1[1:] = 0
     st0.gpu_pte2[1:] = 0
     st0.gpu_pte0[3] = 0
-    for lanes, heavy_min in ((4, ALL_HEAVY), (4, NONE_HEAVY)):
-        k1, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
+    for heavy_min in (ALL_HEAVY, NONE_HEAVY):
+        k1, want, got = _both(pk, gp, tbl, lay, st0, heavy_min=heavy_min)
         S.assert_service_equal(want, got, 512, "heavy_min %d" % heavy_min)
     assert int((want["flags"] & 2 != 0).sum()) > 200 and int((want["flags"] & 4 != 0).sum()) > 20
 
@@ -242,14 +255,14 @@ def test_runs_that_need_no_service_are_evaluated_32_at_a_time():
     for m in ("gpu_pte0", "gpu_pte1", "gpu_pte2"):
         setattr(st0, m, T.masks_from_bool(full & ~holes))
     for pf in ((1, 51, 1), (0, 51, 1)):                      # with the prefetcher off every hole needs its own service
-        _, want, got = _both(pk, gp, tbl, lay, st0, pf=pf, lanes=4, heavy_min=ALL_HEAVY)
+        _, want, got = _both(pk, gp, tbl, lay, st0, pf=pf, heavy_min=ALL_HEAVY)
         S.assert_service_equal(want, got, 16, "speculative runs, prefetch %d" % pf[0])
     rec = want["records"]
     assert len(rec) > 250 and 8 <= int((rec["page_fault_count"] > 0).sum()) <= 40
 
 
-@pytest.mark.parametrize("lanes,heavy_min", [(4, 96), (1, NONE_HEAVY), (16, NONE_HEAVY), (4, ALL_HEAVY)])
-def test_servicing_breaks_read_duplication(lanes, heavy_min):
+@pytest.mark.parametrize("heavy_min", [96, NONE_HEAVY, ALL_HEAVY])
+def test_servicing_breaks_read_duplication(heavy_min):
     """A table with read-duplicated pages (uvm_va_block_make_resident_read_duplicate made them): a fault the GPU
     raises on such a page -- a write, since its write access was revoked -- goes through make_resident, which
     drops the CPU copy and the read_duplicated mark of every page it is handed (uvm_va_block.c:4538-4579)."""
@@ -257,13 +270,13 @@ def test_servicing_breaks_read_duplication(lanes, heavy_min):
     pk, tbl, lay = TG.fault_trace(1500, 41, "hotset", 2, total_va_bytes=SMALL_VA)
     gp = TG.gpu_params(128)
     st0 = R.with_read_duplication(S.random_state(lay["blocks_per_space"] * 2, 9), 9, dup=0.3)
-    k1, want, got = _both(pk, gp, tbl, lay, st0, lanes=lanes, heavy_min=heavy_min)
-    S.assert_service_equal(want, got, 128, "read duplication, lanes %d heavy_min %d" % (lanes, heavy_min))
+    k1, want, got = _both(pk, gp, tbl, lay, st0, heavy_min=heavy_min)
+    S.assert_service_equal(want, got, 128, "read duplication, heavy_min %d" % heavy_min)
     before, after = T.bool_from_masks(st0.read_duplicated), T.bool_from_masks(got["state"].read_duplicated)
     assert not (after & ~before).any() and int((before & ~after).sum()) > 200
     cpu = T.bool_from_masks(got["state"].cpu_resident0) | T.bool_from_masks(got["state"].cpu_resident1)
     assert not (after & ~cpu).any() and not (T.bool_from_masks(got["state"].gpu_resident) & cpu & ~after).any()
     ref = T.load_ref("service")
-    if ref is not None and lanes == 4 and heavy_min == 96:
+    if ref is not None and heavy_min == 96:
         layout = S.make_layout(lay)
         S.assert_ref_equals_oracle(S.run_service_ref(ref, k1, gp, tbl, layout, st0), want, "read duplication")

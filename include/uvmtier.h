@@ -252,6 +252,13 @@ typedef struct {
 NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_params_t *gpu_params,
                                     const uvmtier_instance_ptr_entry_t *h_table, size_t n_rows);
 
+/* Optional output of every fetch entry point below: batch_context->utlbs[u].num_pending_faults (uvm_fault_utlb_info_t,
+ * UVM/uvm_gpu.h:62-84; cleared at UVM/uvm_gpu_replayable_faults.c:879-883, counted at :966 for every entry that
+ * opens a new representative, read by the cancel path at :2302).  Batch b of a call writes utlb_count =
+ * gpc_count * utlb_per_gpc_count counters at d_utlb_pending[b * utlb_count]; the caller sizes the device array for
+ * the batches of its largest call.  NULL (the state after uvmtier_fault_buffer_init) switches the output off. */
+NV_STATUS uvmtier_fault_buffer_set_utlb_pending_output(uvmtier_ctx_t *ctx, uint16_t *d_utlb_pending);
+
 /* F1 only: parse n packets (uvm_hal_volta_fault_buffer_parse_replayable_entry without clearing the
  * valid bit).  num_instances / access_type_mask are 0. */
 NV_STATUS uvmtier_fault_buffer_parse_entries_device(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *d_packets,

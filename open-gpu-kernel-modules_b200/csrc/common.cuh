@@ -23,6 +23,7 @@ struct uvmtier_fault_state {
     size_t smem_bytes;
     uint32_t ac_granularity_2m, ac_cpu_chunk_2m;   // access-counter configuration (uvmtier_access_counters_init)
     uint32_t generation;   // bumped by every uvmtier_fault_buffer_init (the table's contents may have changed)
+    uint16_t *d_utlb_pending;   // optional output, uvmtier_fault_buffer_set_utlb_pending_output
 };
 
 // Scratch of the servicing pass (service.cu), grown on demand and reused.
@@ -51,7 +52,8 @@ NV_STATUS uvmtier_fetch_preprocess_on_stream(struct uvmtier_ctx *ctx, cudaStream
                                              uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
                                              uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
                                              uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
-                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get);
+                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get,
+                                             uint32_t utlb_batch_base = 0);
 
 // uvmtier_service_fault_batches_device for one chunk of a longer trace (service.cu)
 NV_STATUS uvmtier_service_pass_chunk(struct uvmtier_ctx *ctx, uint32_t n_batches, const uvmtier_ordered_fault_t *d_ordered,

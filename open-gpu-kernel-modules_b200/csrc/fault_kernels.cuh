@@ -130,7 +130,8 @@ __global__ void __launch_bounds__(kFaultMaxThreads)
 k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__ ring,
                          const uvmtier_instance_ptr_entry_t *__restrict__ tbl, uint32_t *__restrict__ disp,
                          uvmtier_ordered_fault_t *__restrict__ ordered, uvmtier_fault_group_t *__restrict__ groups,
-                         uvmtier_fault_batch_t *__restrict__ batches, uvmtier_fault_buffer_entry_t *__restrict__ entries)
+                         uvmtier_fault_batch_t *__restrict__ batches, uvmtier_fault_buffer_entry_t *__restrict__ entries,
+                         uint16_t *__restrict__ utlb_pending)
 {
     const int T = (int)blockDim.x, tid = (int)threadIdx.x, lane = tid & 31, warp = tid >> 5, W = T >> 5;
     const uint32_t U = prm.utlb_count;
@@ -344,6 +345,19 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
     }
     const int not_single = __syncthreads_or(breaks_single);
     const uint32_t num_coalesced = (uint32_t)__syncthreads_count(act && st == ST_NEW);
+
+    // utlbs[].num_pending_faults (:881, :966): entries that opened a new representative, per uTLB.  The per-warp
+    // uTLB table of phase 2 is free again: its first U slots take the counts.
+    if (utlb_pending) {
+        for (uint32_t k = tid; k < U; k += T)
+            s_tbl[k] = 0;
+        __syncthreads();
+        if (act && st == ST_NEW)
+            atomicAdd((uint32_t *)(s_tbl + (myutlb & ~1u)), (myutlb & 1u) ? 0x10000u : 1u);   // two 16-bit counters per word
+        __syncthreads();
+        for (uint32_t k = tid; k < U; k += T)
+            utlb_pending[(size_t)blockIdx.x * U + k] = s_tbl[k];
+    }
 
     // ---- phase 5: instance pointer -> (va_space, gpu) and the packed sort key (F3) ----
     int ctx = -1;

@@ -69,9 +69,23 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
         UVMTIER_CUDA(cudaMemcpyAsync(fs->d_table, h_table, n_rows * sizeof(*h_table), cudaMemcpyHostToDevice, ctx->stream));
         UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
     }
+    if (fs->smem_bytes > 200 * 1024)
+        return NV_ERR_INVALID_ARGUMENT;                     // more uTLBs than a CTA's shared memory can track
     if (fs->smem_bytes > 48 * 1024)
         UVMTIER_CUDA(cudaFuncSetAttribute(k_fault_fetch_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)fs->smem_bytes));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_fault_buffer_set_utlb_pending_output(uvmtier_ctx_t *ctx, uint16_t *d_utlb_pending)
+{
+    if (!ctx)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    ctx->faults->d_utlb_pending = d_utlb_pending;
+    static std::atomic<uint32_t> bump{0x80000000u};
+    ctx->faults->generation = ++bump;                       // a replayed graph of the streamed entry point holds the old pointer
     return NV_OK;
 }
 
@@ -134,7 +148,7 @@ NV_STATUS uvmtier_fetch_preprocess_on_stream(uvmtier_ctx_t *ctx, cudaStream_t st
                                              uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
                                              uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
                                              uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
-                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get)
+                                             uvmtier_fault_buffer_entry_t *d_entries, uint32_t *out_get, uint32_t utlb_batch_base)
 {
     if (!ctx || !d_ring || !ring_entries || get >= ring_entries || put >= ring_entries)
         return NV_ERR_INVALID_ARGUMENT;
@@ -162,8 +176,10 @@ NV_STATUS uvmtier_fetch_preprocess_on_stream(uvmtier_ctx_t *ctx, cudaStream_t st
     prm.idx_bits = fs->idx_bits;
     prm.clear_valid = clear_valid != 0;
     const uint32_t n_batches = (n + prm.B - 1) / prm.B;
-    UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, stream, prm, d_ring,
-                   fs->d_table, d_disposition, d_ordered, d_groups, d_batches, d_entries);
+    // the optional per-uTLB counts of batch b land at d_utlb_pending[(utlb_batch_base + b) * utlb_count + u]
+    uint16_t *up = fs->d_utlb_pending ? fs->d_utlb_pending + (size_t)utlb_batch_base * prm.utlb_count : NULL;
+    UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, stream, prm, d_ring, fs->d_table,
+                   d_disposition, d_ordered, d_groups, d_batches, d_entries, up);
     return NV_OK;
 }
 
@@ -196,9 +212,9 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_streamed(uvmtier_ctx_t *ctx, co
         st = uvmtier_streamed_copy_chunk(ctx, plan, c, h_ring, d_ring, ring_entries, get, &e0, &e1, &first, &last);
         if (st != NV_OK)
             return st;
-        st = uvmtier_fetch_preprocess_fault_batches_device(ctx, d_ring, ring_entries, first, last, clear_valid,
-                                                           d_disposition + e0, d_ordered + e0, d_groups + e0,
-                                                           d_batches + c * plan.per, d_entries ? d_entries + e0 : NULL, NULL);
+        st = uvmtier_fetch_preprocess_on_stream(ctx, ctx->stream, d_ring, ring_entries, first, last, clear_valid,
+                                                d_disposition + e0, d_ordered + e0, d_groups + e0, d_batches + c * plan.per,
+                                                d_entries ? d_entries + e0 : NULL, NULL, c * plan.per);
         if (st != NV_OK)
             return st;
     }

@@ -466,7 +466,7 @@ static NV_STATUS streamed_enqueue(uvmtier_ctx_t *ctx, const streamed_args &a, bo
             return st;
         const uint32_t b0 = c * plan.per, nb = (e1 - e0 + plan.B - 1) / plan.B;
         st = uvmtier_fetch_preprocess_on_stream(ctx, s_k1, d_ring, ring_entries, first, last, clear_valid, d_disposition + e0,
-                                                d_ordered + e0, d_groups + e0, d_batches + b0, NULL, NULL);
+                                                d_ordered + e0, d_groups + e0, d_batches + b0, NULL, NULL, b0);
         if (st != NV_OK)
             return st;
         UVMTIER_CUDA(cudaEventRecord(ctx->k1_events[c], s_k1));

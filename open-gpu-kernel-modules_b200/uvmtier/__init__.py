@@ -193,6 +193,11 @@ class Context:
                "uvmtier_fault_buffer_init")
         self._fault_B = int(gpu_params["max_batch_size"][0])
 
+    def fault_buffer_set_utlb_pending_output(self, dptr):
+        """uvmtier_fault_buffer_set_utlb_pending_output: device array of uint16 [n_batches, utlb_count], or None."""
+        _check(lib().uvmtier_fault_buffer_set_utlb_pending_output(self._h, ctypes.c_void_p(dptr if dptr else None)),
+               "uvmtier_fault_buffer_set_utlb_pending_output")
+
     def fault_buffer_parse_entries(self, packets):
         from .layouts import FAULT_ENTRY_DT
         out = np.zeros(len(packets), FAULT_ENTRY_DT)

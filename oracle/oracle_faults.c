@@ -160,6 +160,11 @@ static int cmp_item_main(const void *a, const void *b)
     return x->idx < y->idx ? -1 : (x->idx > y->idx ? 1 : 0);
 }
 
+/* Optional extra output of oracle_faults_fetch_preprocess: utlbs[u].num_pending_faults of batch b
+ * (uvm_gpu.h:62-84; cleared :881, counted :966) at out[b * utlb_count + u].  NULL switches it off. */
+static uint16_t *g_utlb_out;
+void oracle_faults_set_utlb_output(uint16_t *out) { g_utlb_out = out; }
+
 int oracle_faults_fetch_preprocess(uint32_t *ring, uint32_t n_entries, const ref_fault_gpu_params_t *gp,
                                    const ref_instance_ptr_entry_t *tbl, size_t tbl_n, ref_fault_entry_t *entries,
                                    uint32_t *ordered, uint32_t *ordered_va_space, uint32_t *ordered_gpu,
@@ -229,6 +234,9 @@ int oracle_faults_fetch_preprocess(uint32_t *ring, uint32_t n_entries, const ref
         ob->num_coalesced_faults = coalesced;
         ob->is_single_instance_ptr = single;
         ob->max_utlb_id = max_utlb;
+        if (g_utlb_out)
+            for (i = 0; i < utlb_count; i++)
+                g_utlb_out[(size_t)nb * utlb_count + i] = (uint16_t)utlb_pending[i];
 
         /* ---- F3: preprocess_fault_batch :1134-1178 ---- */
         for (i = 0, m = 0; i < n; i++)

@@ -245,6 +245,11 @@ static void export_entry(const uvm_fault_buffer_entry_t *e, ref_fault_entry_t *o
  *   batch[b]            counters
  * The ring is modified (valid bits cleared), like the reference does.
  */
+/* Optional extra output: batch_context->utlbs[u].num_pending_faults after the fetch of batch b, at
+ * out[b * utlb_count + u].  NULL switches it off. */
+static uint16_t *g_utlb_out;
+void ref_faults_set_utlb_output(uint16_t *out) { g_utlb_out = out; }
+
 int ref_faults_fetch_preprocess(uint32_t *ring, uint32_t n_entries, const ref_fault_gpu_params_t *gp,
                                 const ref_instance_ptr_entry_t *tbl, size_t tbl_n, ref_fault_entry_t *entries,
                                 uint32_t *ordered, uint32_t *ordered_va_space, uint32_t *ordered_gpu,
@@ -291,6 +296,9 @@ int ref_faults_fetch_preprocess(uint32_t *ring, uint32_t n_entries, const ref_fa
         ob->num_coalesced_faults = bc.num_coalesced_faults;
         ob->is_single_instance_ptr = bc.is_single_instance_ptr;
         ob->max_utlb_id = bc.max_utlb_id;
+        if (g_utlb_out)
+            for (j = 0; j < utlb_count; j++)
+                g_utlb_out[(size_t)b * utlb_count + j] = (uint16_t)bc.utlbs[j].num_pending_faults;
         st = preprocess_fault_batch(&gpu, &bc);
         ob->status = st;
         for (j = 0; j < bc.num_cached_faults; j++)

@@ -49,9 +49,22 @@ def run_fetch_preprocess(lib, prefix, packets, gp, table):
     batch = np.zeros(n_batches(n, B) + 1, BATCH_DT)
     fn = getattr(lib, prefix + "_faults_fetch_preprocess")
     fn.restype = ctypes.c_int
+    # utlbs[].num_pending_faults per batch (optional output of both checkers)
+    U = utlb_count(gp)
+    utlb = np.zeros((len(batch), U), "<u2")
+    setter = getattr(lib, prefix + "_faults_set_utlb_output", None)
+    if setter is not None:
+        setter(P(utlb))
     nb = fn(P(ring), ctypes.c_uint32(n), P(gp), P(table), ctypes.c_size_t(len(table)), P(entries), P(ordered), P(vs),
             P(gpu), P(batch))
-    return dict(entries=entries, ordered=ordered, va_space=vs, gpu=gpu, batch=batch[:nb], ring_after=ring)
+    if setter is not None:
+        setter(None)
+    return dict(entries=entries, ordered=ordered, va_space=vs, gpu=gpu, batch=batch[:nb], ring_after=ring,
+                utlb_pending=utlb[:nb] if setter is not None else None)
+
+
+def utlb_count(gp):
+    return int(gp["gpc_count"][0]) * int(gp["utlb_per_gpc_count"][0])
 
 
 def assert_fetch_equal(a, b, what=""):
@@ -75,6 +88,8 @@ def assert_fetch_equal(a, b, what=""):
                 assert np.array_equal(a[key][base:base + nco], b[key][base:base + nco]), "%s %s batch %d" % (what, key, k)
         base += int(bt["num_cached_faults"])
     assert np.array_equal(a["ring_after"], b["ring_after"]), what + " ring valid bits"
+    if a.get("utlb_pending") is not None and b.get("utlb_pending") is not None:
+        assert np.array_equal(a["utlb_pending"], b["utlb_pending"]), what + " utlbs[].num_pending_faults"
 
 
 def directed_quirk_trace():
@@ -114,7 +129,7 @@ def product_to_checker_view(n, B, table, disp, ordered, groups, batch, entries, 
                 ordered_rec=ordered, groups=groups)
 
 
-def run_fetch_preprocess_simt(sim, packets, gp, table, clear_valid=1, get=0):
+def run_fetch_preprocess_simt(sim, packets, gp, table, clear_valid=1, get=0, force_cta_kernel=0):
     n = len(packets)
     B = int(gp["max_batch_size"][0])
     ring = packets.copy()
@@ -126,11 +141,14 @@ def run_fetch_preprocess_simt(sim, packets, gp, table, clear_valid=1, get=0):
     sim.simt_fault_fetch_preprocess.restype = ctypes.c_int
     # ring of n+1 entries so that put = n is a legal index (the ring never wraps here)
     ring1 = np.zeros((n + 1, 8), np.uint32); ring1[:n] = ring
+    utlb = np.zeros((len(batch), utlb_count(gp)), "<u2")
     r = sim.simt_fault_fetch_preprocess(P(ring1), ctypes.c_uint32(n + 1), ctypes.c_uint32(get), ctypes.c_uint32(n), P(gp),
                                         P(table), ctypes.c_uint32(len(table)), ctypes.c_int(clear_valid), P(disp),
-                                        P(ordered), P(groups), P(batch), P(entries))
+                                        P(ordered), P(groups), P(batch), P(entries), P(utlb), ctypes.c_int(force_cta_kernel))
     assert r == len(batch), r
-    return product_to_checker_view(n, B, table, disp, ordered, groups, batch, entries, ring1[:n].copy())
+    res = product_to_checker_view(n, B, table, disp, ordered, groups, batch, entries, ring1[:n].copy())
+    res["utlb_pending"] = utlb
+    return res
 
 
 def check_groups(res, table, B):

@@ -44,7 +44,7 @@ int simt_fault_fetch_preprocess(uvmtier_fault_packet_t *ring, uint32_t ring_entr
                                 const uvmtier_fault_gpu_params_t *gp, const uvmtier_instance_ptr_entry_t *tbl,
                                 uint32_t tbl_n, int clear_valid, uint32_t *disp, uvmtier_ordered_fault_t *ordered,
                                 uvmtier_fault_group_t *groups, uvmtier_fault_batch_t *batches,
-                                uvmtier_fault_buffer_entry_t *entries)
+                                uvmtier_fault_buffer_entry_t *entries, uint16_t *utlb_pending, int force_cta_kernel)
 {
     uint32_t threads = 32, idx_bits = 5;
     while (threads < gp->max_batch_size) { threads <<= 1; idx_bits++; }
@@ -64,10 +64,11 @@ int simt_fault_fetch_preprocess(uvmtier_fault_packet_t *ring, uint32_t ring_entr
     prm.idx_bits = idx_bits;
     prm.clear_valid = clear_valid != 0;
     const uint32_t n_batches = (n + prm.B - 1) / prm.B;
+    (void)force_cta_kernel;
     if (fault_smem_bytes(threads, prm.utlb_count, tbl_n) > sizeof(simt::g_dynamic_smem))
         return -1;
     simt::launch(dim3(n_batches), dim3(threads),
-                 [&] { k_fault_fetch_preprocess(prm, ring, tbl, disp, ordered, groups, batches, entries); });
+                 [&] { k_fault_fetch_preprocess(prm, ring, tbl, disp, ordered, groups, batches, entries, utlb_pending); });
     return (int)n_batches;
 }
 

@@ -13,12 +13,21 @@ pytestmark = pytest.mark.gpu
 def gpu_fetch(ctx, pk, gp, tbl, clear_valid=True):
     ctx.fault_buffer_init(gp, tbl)
     n = len(pk)
+    B = int(gp["max_batch_size"][0])
     ring = np.zeros((n + 1, 8), np.uint32)
     ring[:n] = pk
+    # utlbs[].num_pending_faults: optional output, one row of counters per batch
+    nb, U = (n + B - 1) // B, F.utlb_count(gp)
+    d_utlb = ctx.alloc(max(nb * U * 2, 2))
+    ctx.fault_buffer_set_utlb_pending_output(d_utlb)
     r = ctx.fetch_preprocess_fault_batches(ring, 0, n, clear_valid=clear_valid)
+    utlb = ctx.from_device(d_utlb, nb * U, "<u2").reshape(nb, U)
+    ctx.fault_buffer_set_utlb_pending_output(None)
+    ctx.free(d_utlb)
     assert r["get"] == n
-    return F.product_to_checker_view(n, int(gp["max_batch_size"][0]), tbl, r["disp"], r["ordered"], r["groups"], r["batch"],
-                                     r["entries"], ring[:n].copy())
+    res = F.product_to_checker_view(n, B, tbl, r["disp"], r["ordered"], r["groups"], r["batch"], r["entries"], ring[:n].copy())
+    res["utlb_pending"] = utlb
+    return res
 
 
 def test_gpu_matches_golden_vectors(ctx):

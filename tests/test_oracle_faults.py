@@ -54,13 +54,15 @@ def test_oracle_matches_reference_build(dist, n_spaces):
 
 
 @pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
-@pytest.mark.parametrize("B", [256, 32, 100, 1000])
-def test_simt_kernel_matches_oracle(dist, B):
+@pytest.mark.parametrize("B,cta", [(256, 0), (32, 0), (64, 0), (100, 0), (200, 0), (1000, 0)])
+def test_simt_kernel_matches_oracle(dist, B, cta):
+    """One CTA per batch, batch sizes that do and do not fill the CTA; results include utlbs[].num_pending_faults."""
     orc, sim = T.load_oracle(), T.load_simt()
     pk, tbl, _ = TG.fault_trace(1500, 0xC0FFEE, dist, 4)
     gp = TG.gpu_params(B)
     want = F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl)
-    got = F.run_fetch_preprocess_simt(sim, pk, gp, tbl)
+    got = F.run_fetch_preprocess_simt(sim, pk, gp, tbl, force_cta_kernel=cta)
+    assert got["utlb_pending"].sum() == want["batch"]["num_coalesced_faults"].sum()
     F.assert_fetch_equal(want, got, "%s %d" % (dist, B))
     F.check_groups(got, tbl, B)
 

@@ -109,18 +109,26 @@ class ClockSampler(threading.Thread):
 
 
 # ----------------------------------------------------------------------------------------------- workload
-def build_workload(seed, trace):
+def build_workload(seed, trace, rank=0, world=1):
     """Trace + instance-pointer table + initial va_block state (everything resident on the CPU tiers: 70 % host
-    DRAM, 30 % CXL node, nothing on the GPU yet, read-write VMAs)."""
-    from uvmtier import tracegen as TG
+    DRAM, 30 % CXL node, nothing on the GPU yet, read-write VMAs).
+    world > 1: ONE VA of world x 64 GB and ONE trace of world x 1M entries over it; the va_blocks of
+    every VA space are cut into `world` contiguous ranges (block b -> GPU b * world / n_blocks) and every GPU gets
+    the faults on the blocks it owns, in ring order, plus the state table of its range."""
+    from uvmtier import sharding as SH, tracegen as TG
     from uvmtier.blockstate import HostBlockState, make_layout
-    pk, tbl, lay = TG.fault_trace(N_ENTRIES, seed, trace, N_SPACES, VA_BYTES)
+    pk, tbl, lay = TG.fault_trace(N_ENTRIES * world, seed, trace, N_SPACES, VA_BYTES * world)
+    if world > 1:
+        bps = lay["blocks_per_space"]
+        pk = np.ascontiguousarray(SH.split_trace_by_owner(pk, lay["va_base"], bps, world)[rank])
+        first, outer = SH.block_range(bps, world, rank)
+        lay = dict(lay, va_base=lay["va_base"] + (first << 21), blocks_per_space=outer - first)
     gp = TG.gpu_params(BATCH)
     n_slots = lay["blocks_per_space"] * N_SPACES
     st = HostBlockState(n_slots)
     # ~25 % of every va_block's 64 KB chunks live on the CXL node, the rest on host DRAM (tiering works on
     # multi-page extents, not single pages)
-    rs = TG.Stream(seed ^ 0x5EED, n_slots * 2)
+    rs = TG.Stream((seed + 1000 * rank) ^ 0x5EED, n_slots * 2)
     chunk_bits = (rs.take(n_slots) & rs.take(n_slots)).astype("<u4")                  # 32 chunks of 16 pages per block
     chunks = np.unpackbits(chunk_bits.view(np.uint8).reshape(n_slots, 4), axis=1, bitorder="little")
     pages = np.repeat(chunks, 16, axis=1)
@@ -313,32 +321,6 @@ def migration_numbers(ctx, lib, P, rank, world, dist, nbytes=256 << 20):
         peak = out["cxl_to_hbm" if flag else "hbm_to_cxl"]["copy_engine_peak_GBs"]
         out[key] = {"GBs": round(nbytes / (best * 1e-3) / 1e9, 2), "frac_of_link_peak": round(nbytes / (best * 1e-3) / 1e9 / peak, 3)}
     assert lib.uvmtier_p2p_unregister_cxl_buffer(ctx.handle, hnd) == 0
-    if dist is not None and world > 1:
-        # NVLink peer push: every rank copies its HBM arena into the next rank's (ring), all at once
-        import torch
-        hnd = (ctypes.c_uint8 * 64)()
-        st = lib.uvmtier_tier_ipc_export(ctx.handle, TIER_HBM, hnd)
-        assert st == 0, hex(st)
-        mine = torch.tensor(list(bytes(hnd)), dtype=torch.uint8, device="cuda")
-        allh = [torch.zeros_like(mine) for _ in range(world)]
-        dist.all_gather(allh, mine)
-        nxt = (rank + 1) % world
-        peer = (ctypes.c_uint8 * 64)(*allh[nxt].cpu().tolist())
-        st = lib.uvmtier_tier_ipc_import(ctx.handle, TIER_PEER0, peer, ctypes.c_uint64(nbytes))
-        assert st == 0, hex(st)
-        ctx.synchronize(); dist.barrier()
-        push = timed(TIER_PEER0, TIER_HBM)
-        ctx.synchronize(); dist.barrier()
-        pull = timed(TIER_HBM, TIER_PEER0)
-        ctx.synchronize(); dist.barrier()
-        t = torch.tensor([push, pull], dtype=torch.float64, device="cuda")
-        dist.all_reduce(t, op=dist.ReduceOp.MIN)
-        out["nvlink_peer_push_ring"] = {"GBs_per_gpu_min": round(float(t[0]), 2), "GBs_aggregate": round(float(t[0]) * world, 2),
-                                        "nominal_per_direction_GBs": 900, "measured_reference_GBs": 770,
-                                        "frac_of_770": round(float(t[0]) / 770, 3)}
-        out["nvlink_peer_pull_ring"] = {"GBs_per_gpu_min": round(float(t[1]), 2), "frac_of_770": round(float(t[1]) / 770, 3)}
-        lib.uvmtier_tier_destroy(ctx.handle, TIER_PEER0)
-        dist.barrier()
     ctx.free(d_s); ctx.free(d_d)
     for t in (TIER_HBM, TIER_DRAM, TIER_CXL):
         ctx.tier_destroy(t)
@@ -513,6 +495,98 @@ def thrashing_numbers(ctx, lib, P, rank):
             "what": "two processors alternate on 16-page regions every 20 us (window 500 us, threshold 3)"}
 
 
+def peer_numbers(ctx, lib, P, rank, world, dist, region_bytes=1 << 30):
+    """BASELINE config E, the NVLink leg: every GPU moves a 1 GiB page list (4 KB pages, random placement) to the
+    next GPU of the ring (push: the source GPU's SMs store into the peer's HBM, uvm_va_block.c:3427-3457) and from
+    it (pull), all ranks at once.  Each rank's HBM arena has a source half, filled with the fork's test pattern
+    (tests/cxl_p2p_test.c:467-476: byte i = (i + seed) & 0xFF, plus the page number in the first 8 bytes so that a
+    misplaced page cannot pass), and a landing half, filled with 0xEE before every leg.  After each leg the receiver
+    checksums the pages that landed and compares them with the sender's checksums of the pages it sent; a mismatch
+    fails the run.  The peak the copies are compared with is measured in the same run on the same arenas:
+    cudaMemcpyAsync between the two GPUs (the copy engine, what ce_hal->memcopy does), 1 GiB, best of 3."""
+    import torch
+    from uvmtier import TIER_HBM, TIER_PEER0
+    info = ctx.tier_create(TIER_HBM, 2 * region_bytes)
+    hnd = (ctypes.c_uint8 * 64)()
+    st = lib.uvmtier_tier_ipc_export(ctx.handle, TIER_HBM, hnd)
+    assert st == 0, hex(st)
+    mine = torch.tensor(list(bytes(hnd)), dtype=torch.uint8, device="cuda")
+    allh = [torch.zeros_like(mine) for _ in range(world)]
+    dist.all_gather(allh, mine)
+    nxt, prv = (rank + 1) % world, (rank - 1) % world
+    peer = (ctypes.c_uint8 * 64)(*allh[nxt].cpu().tolist())
+    st = lib.uvmtier_tier_ipc_import(ctx.handle, TIER_PEER0, peer, ctypes.c_uint64(2 * region_bytes))
+    assert st == 0, hex(st)
+
+    def barrier():
+        ctx.synchronize(); dist.barrier(); ctx.synchronize()
+
+    # the copy-engine peak, every rank at once like the legs below (contents do not matter yet)
+    barrier()
+    peak_push = ctx.tier_memcpy_peak_gbs(TIER_PEER0, TIER_HBM, region_bytes, 3)
+    barrier()
+    peak_pull = ctx.tier_memcpy_peak_gbs(TIER_HBM, TIER_PEER0, region_bytes, 3)
+    barrier()
+
+    n_pages = region_bytes // 4096
+    perm = np.random.default_rng(7).permutation(n_pages).astype(np.uint64)          # the same on every rank
+    s_off = np.arange(n_pages, dtype=np.uint64) * np.uint64(4096)
+    d_off = np.uint64(region_bytes) + perm * np.uint64(4096)
+    d_s, d_d = ctx.to_device(s_off), ctx.to_device(d_off)
+    seed = 17 + rank
+    pat = np.tile(np.roll(np.arange(256, dtype=np.uint8), -seed), region_bytes // 256).reshape(n_pages, 4096)
+    pat[:, :8] = (np.arange(n_pages, dtype=np.uint64) | (np.uint64(rank + 1) << np.uint64(48))).view(np.uint8).reshape(n_pages, 8)
+    base = info.device_ptr
+
+    def chk(st_):
+        if st_ != 0:
+            raise RuntimeError("peer leg: 0x%x %s" % (st_, lib.uvmtier_last_error().decode()))
+
+    chk(lib.uvmtier_memcpy_h2d(ctx.handle, ctypes.c_void_p(base), P(pat), ctypes.c_size_t(region_bytes)))
+    del pat
+    cs_src = ctx.checksum_pages(TIER_HBM, s_off, 4096)
+    t = torch.from_numpy(cs_src.view(np.int64).copy()).cuda()
+    allcs = [torch.zeros_like(t) for _ in range(world)]
+    dist.all_gather(allcs, t)
+    ms = ctypes.c_float(0)
+
+    def leg(dst, src, expect_from):
+        chk(lib.uvmtier_memset_device(ctx.handle, ctypes.c_void_p(base + region_bytes), 0xEE, ctypes.c_size_t(region_bytes)))
+        barrier()
+        best = 1e30
+        for r in range(4):
+            lib.uvmtier_event_record(ctx.handle, 900)
+            chk(lib.uvmtier_copy_page_list_device(ctx.handle, dst, src, ctypes.c_size_t(n_pages), P(d_d), P(d_s), 4096, 0))
+            lib.uvmtier_event_record(ctx.handle, 901)
+            lib.uvmtier_event_elapsed_ms(ctx.handle, 900, 901, ctypes.byref(ms))
+            if r:
+                best = min(best, ms.value)
+        barrier()
+        got = ctx.checksum_pages(TIER_HBM, d_off, 4096)
+        want = allcs[expect_from].cpu().numpy().view(np.uint64)
+        return region_bytes / (best * 1e-3) / 1e9, bool(np.array_equal(got, want))
+
+    push, ok_push = leg(TIER_PEER0, TIER_HBM, prv)       # my pages land in the next GPU; what landed here came from prv
+    pull, ok_pull = leg(TIER_HBM, TIER_PEER0, nxt)       # I fetch the next GPU's pages
+    tt = torch.tensor([push, pull, peak_push, peak_pull, float(ok_push), float(ok_pull)], dtype=torch.float64, device="cuda")
+    dist.all_reduce(tt, op=dist.ReduceOp.MIN)
+    push, pull, peak_push, peak_pull, ok_push, ok_pull = [float(x) for x in tt.tolist()]
+    out = {"page_size": 4096, "order": "random permutation", "bytes_per_gpu": region_bytes, "pattern": "fork pattern (i + seed) & 0xFF + page number",
+           "nvlink_peer_push_ring": {"GBs_per_gpu_min": round(push, 2), "GBs_aggregate": round(push * world, 2),
+                                     "copy_engine_peak_GBs": round(peak_push, 2), "frac_of_measured_peak": round(push / peak_push, 3),
+                                     "nominal_per_direction_GBs": 900, "verified": ok_push == 1.0},
+           "nvlink_peer_pull_ring": {"GBs_per_gpu_min": round(pull, 2), "copy_engine_peak_GBs": round(peak_pull, 2),
+                                     "frac_of_measured_peak": round(pull / peak_pull, 3), "verified": ok_pull == 1.0},
+           "peak": "cudaMemcpyAsync GPU to GPU, 1 GiB, best of 3, all ranks at once (minimum over ranks)"}
+    lib.uvmtier_tier_destroy(ctx.handle, TIER_PEER0)
+    barrier()
+    ctx.free(d_s); ctx.free(d_d)
+    ctx.tier_destroy(TIER_HBM)
+    if not (ok_push == 1.0 and ok_pull == 1.0):
+        raise RuntimeError("NVLink peer copy moved wrong bytes: %s" % json.dumps(out))
+    return out
+
+
 # ----------------------------------------------------------------------------------------------- GPU arm
 _REAL_STDOUT = None
 
@@ -560,8 +634,10 @@ def main():
     lib = uvmtier.lib()
     ctx = uvmtier.Context(local_rank)
     h = ctx.handle
-    wl = build_workload(1 + rank, args.trace)
-    n, nb = N_ENTRIES, N_ENTRIES // BATCH
+    wl = build_workload(1, args.trace, rank, world)
+    n = len(wl["packets"])                  # this rank's share of the world x 1M-entry trace
+    nb = (n + BATCH - 1) // BATCH
+    ncap = nb * BATCH                       # per-entry outputs are sliced by batch: batch b at b * BATCH
     ctx.fault_buffer_init(wl["gpu_params"], wl["table"])
     layout = wl["layout"]
 
@@ -574,8 +650,8 @@ def main():
     ring_host[:n] = wl["packets"]
     d_ring0 = ctx.to_device(ring_host)           # pristine copy
     d_ring = ctx.alloc(ring_host.nbytes)
-    d_disp, d_ord, d_grp, d_bat = ctx.alloc(n * 4), ctx.alloc(n * 16), ctx.alloc(n * 16), ctx.alloc(nb * 32)
-    d_flags, d_svc, d_runs, d_cnt = ctx.alloc(n * 2), ctx.alloc(n * 96), ctx.alloc(RUN_CAP * 8), ctx.alloc(8)
+    d_disp, d_ord, d_grp, d_bat = ctx.alloc(ncap * 4), ctx.alloc(ncap * 16), ctx.alloc(ncap * 16), ctx.alloc(nb * 32)
+    d_flags, d_svc, d_runs, d_cnt = ctx.alloc(ncap * 2), ctx.alloc(ncap * 96), ctx.alloc(RUN_CAP * 8), ctx.alloc(8)
     ds0 = ctx.block_state_alloc(layout); ds0.upload(wl["state"])       # pristine state
     ds = ctx.block_state_alloc(layout)
     state_bytes = wl["n_slots"] * (6 * 64 + 4 + 2 + 1)
@@ -634,8 +710,9 @@ def main():
     n_coalesced = int(bat["num_coalesced_faults"].sum()); n_groups = int(bat["num_block_groups"].sum()); n_runs = int(cnt[0])
     assert n_runs <= RUN_CAP, "copy-run buffer too small"
     k1_bytes = n * 32 + n * 4 + n_coalesced * 16 + n_groups * 16 + nb * 32
-    svc_rec = ctx.from_device(d_svc, n, BS.SERVICE_GROUP_DT)
-    live = svc_rec["page_fault_count"] > 0
+    svc_rec = ctx.from_device(d_svc, ncap, BS.SERVICE_GROUP_DT)
+    written = (np.arange(ncap) % BATCH) < np.repeat(bat["num_block_groups"], BATCH)     # records the pass wrote
+    live = written & (svc_rec["page_fault_count"] > 0)
     touched = len(np.unique(svc_rec["slot"][live]))
     svc_bytes = n_groups * (16 + 96 + 8) + n_coalesced * (16 + 2) + touched * 2 * (6 * 64 + 8) + n_runs * 8
     k1_ms, svc_ms = float(np.mean(t_k1)), float(np.mean(t_svc))
@@ -649,8 +726,8 @@ def main():
         v[...] = arr
         return v
     hp_ring = pinned(ring_host)
-    hp_bat = pinned(np.zeros(nb, L.BATCH_DT)); hp_flags = pinned(np.zeros(n, "<u2")); hp_cnt = pinned(np.zeros(2, "<u4"))
-    hp_svc = pinned(np.zeros(n, BS.SERVICE_GROUP_DT)); hp_runs = pinned(np.zeros(max(n_runs, 1), BS.COPY_RUN_DT))
+    hp_bat = pinned(np.zeros(nb, L.BATCH_DT)); hp_flags = pinned(np.zeros(ncap, "<u2")); hp_cnt = pinned(np.zeros(2, "<u4"))
+    hp_svc = pinned(np.zeros(ncap, BS.SERVICE_GROUP_DT)); hp_runs = pinned(np.zeros(max(n_runs, 1), BS.COPY_RUN_DT))
     # What comes back to the host every step is what the reference's caller of service_fault_batch looks at
     # afterwards: the per-batch headers (status, duplicate / invalid-prefetch / fatal counts -> cancel + replay
     # policy), the per-fault flags (which entries to cancel and how) and the run counter.  Service records and copy
@@ -690,7 +767,7 @@ def main():
                 ctypes.byref(new_get)), "service_replayable_faults_streamed")
         if full:
             chk(lib.uvmtier_memcpy_d2h_async(h, P(hp_ring), P(d_ring), ctypes.c_size_t(ring_host.nbytes)), "d2h ring")
-            chk(lib.uvmtier_memcpy_d2h_async(h, P(hp_svc), P(d_svc), ctypes.c_size_t(n * 96)), "d2h")
+            chk(lib.uvmtier_memcpy_d2h_async(h, P(hp_svc), P(d_svc), ctypes.c_size_t(ncap * 96)), "d2h")
             chk(lib.uvmtier_memcpy_d2h_async(h, P(hp_runs), P(d_runs), ctypes.c_size_t(max(n_runs, 1) * 8)), "d2h")
         ctx.synchronize()
         return time.perf_counter() - t0
@@ -711,6 +788,8 @@ def main():
     migration = None
     if not args.no_migration:
         migration = migration_numbers(ctx, lib, P, rank, world, dist)
+        if dist is not None and world > 1:
+            migration["nvlink_peer"] = peer_numbers(ctx, lib, P, rank, world, dist)
     oversub = None
     if not args.no_migration and rank == 0:
         oversub = oversubscription_numbers(ctx, lib, P, rank)
@@ -744,14 +823,17 @@ def main():
     except Exception:
         pass
     line = {
-        "metric": METRIC, "value": world * n / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
+        "metric": METRIC, "value": world * N_ENTRIES / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
         "config": {"workload": workload_name(args.trace), "batch": BATCH, "va_spaces": N_SPACES,
-                   "l2": "flushed between iterations (256 MiB memset)", "rng": "uvm_test_rng KISS stream, seed 1+rank",
+                   "l2": "flushed between iterations (256 MiB memset)", "rng": "uvm_test_rng KISS stream, seed 1",
                    "initial_residency": "all pages on the CPU tiers (75% DRAM / 25% CXL node), none on the GPU",
-                   "sharding": "one trace + 64 GB VA per GPU, no data-path collective"},
-        "e2e": {"value": world * n / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_result),
+                   "sharding": ("one GPU: the whole 64 GB VA and the whole 1M-entry trace" if world == 1 else
+                                "ONE VA of %d x 64 GB (4 VA spaces) cut into %d contiguous va_block ranges, ONE trace of %d x 1M "
+                                "entries split by the owner of the faulting va_block (uvmtier/sharding.py); every GPU services "
+                                "its own range, no data-path collective; weak scaling" % (world, world, world))},
+        "e2e": {"value": world * N_ENTRIES / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_result),
                 "ms_per_step": e2e_ms,
                 "result": "batch headers + per-fault flags + run counter (what the caller of service_fault_batch consumes)",
                 "full_readback": {"value": n / (e2e_full_ms * 1e-3), "ms_per_step": e2e_full_ms, "d2h_bytes_per_step": int(d2h_full),

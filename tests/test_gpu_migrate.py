@@ -178,3 +178,65 @@ def test_copy_runs_from_the_service_pass_move_the_right_bytes():
         assert (hbm[untouched.ravel()] == 0xAB).all()
         assert from0.sum() > 100 and from1.sum() > 30 and touched.sum() > 30
         ds.free()
+
+
+def _peer_roundtrip(c, info, peer_tier, peer_read, page_size, method):
+    """HBM -> peer tier (push: this GPU's SMs store into the peer arena, uvm_va_block.c:3427-3457) with the pages
+    shuffled, then peer -> HBM (pull) back into place; both arenas compared byte for byte with numpy indexing."""
+    import ctypes
+    n = ARENA // page_size
+    rng = np.random.default_rng(page_size + method)
+    src = TG.rng_stream(77 + method, ARENA // 4).view(np.uint8)
+    uvmtier._check(uvmtier.lib().uvmtier_memcpy_h2d(c.handle, ctypes.c_void_p(info[TIER_HBM].device_ptr), T_P(src),
+                                                   ctypes.c_size_t(ARENA)), "h2d")
+    perm = rng.permutation(n).astype(np.uint64) * np.uint64(page_size)
+    lin = np.arange(n, dtype=np.uint64) * np.uint64(page_size)
+    c.copy_page_list(peer_tier, TIER_HBM, perm, lin, page_size, method)          # push
+    landed = peer_read()
+    want = np.empty_like(src)
+    want.reshape(n, page_size)[(perm // np.uint64(page_size)).astype(np.int64)] = src.reshape(n, page_size)
+    assert np.array_equal(landed, want), "push moved wrong bytes"
+    assert np.array_equal(c.checksum_pages(peer_tier, perm, page_size), np_checksum(src, lin, page_size))
+    hbm_fill(c, info, 0xEE, ARENA)
+    c.copy_page_list(TIER_HBM, peer_tier, lin, perm, page_size, method)          # pull, back into place
+    assert np.array_equal(hbm_read(c, info), src), "pull moved wrong bytes"
+
+
+def T_P(a):
+    import uvmtier_testlib as T
+    return T.P(a)
+
+
+@pytest.mark.parametrize("page_size", [4096, 65536, 2 << 20])
+@pytest.mark.parametrize("method", [0, 1])
+def test_peer_tier_on_one_gpu_byte_exact(tiers, page_size, method):
+    """The peer-tier mechanism on a single GPU: a second arena of the same GPU registered as UVMTIER_TIER_PEER0
+    through uvmtier_tier_register (what uvmtier_tier_map_peer / _ipc_import do with another GPU's arena)."""
+    import ctypes
+    c, info = tiers
+    d_peer = c.alloc(ARENA)
+    try:
+        uvmtier._check(uvmtier.lib().uvmtier_tier_register(c.handle, ctypes.c_uint32(uvmtier.TIER_PEER0), ctypes.c_void_p(d_peer), None,
+                                                          ctypes.c_uint64(ARENA)), "tier_register")
+        _peer_roundtrip(c, info, uvmtier.TIER_PEER0, lambda: c.from_device(d_peer, ARENA, np.uint8), page_size, method)
+    finally:
+        c.tier_destroy(uvmtier.TIER_PEER0)
+        c.free(d_peer)
+
+
+@pytest.mark.parametrize("page_size", [4096, 2 << 20])
+def test_peer_tier_on_a_second_gpu_byte_exact(tiers, page_size):
+    """Two GPUs in one process: uvmtier_tier_map_peer maps GPU 1's HBM arena as this context's peer tier; pages
+    cross NVLink by SM stores (push) and SM loads (pull).  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    c, info = tiers
+    peer = uvmtier.Context(1)
+    try:
+        pinfo = peer.tier_create(TIER_HBM, ARENA)
+        c.tier_map_peer(0, peer)
+        _peer_roundtrip(c, info, uvmtier.TIER_PEER0, lambda: peer.from_device(pinfo.device_ptr, ARENA, np.uint8), page_size, 0)
+    finally:
+        c.tier_destroy(uvmtier.TIER_PEER0)
+        peer.close()

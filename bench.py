@@ -150,7 +150,10 @@ def _ref_worker(args):
     orc = T.load_oracle()
     rf = T.load_ref("faults")
     rs = T.load_ref("service")
-    kind = "reference" if rf is not None and rs is not None else "port"
+    # the back half of the reference's entry loop: the reference's own prefetch file and make_resident when they were
+    # built too (then nothing on the CPU arm's data path is a restatement except the mapping of the serviced pages)
+    back = rs is not None and S.use_reference_back_half(rs, T.load_ref("prefetch"), T.load_ref("resident"))
+    kind = "reference" if rf is not None and rs is not None and back else "port"
     sim_like = None
     best = 1e30
     B = int(gp["max_batch_size"][0])
@@ -238,6 +241,17 @@ def workload_name(trace):
             "trees over 64 GB VA (32768 va_blocks)" % trace)
 
 
+def config_dict(trace, world):
+    """The `config` object of the JSON line: the same keys and values in both arms."""
+    return {"workload": workload_name(trace), "batch": BATCH, "va_spaces": N_SPACES,
+            "l2": "flushed between iterations (256 MiB memset)", "rng": "uvm_test_rng KISS stream, seed 1",
+            "initial_residency": "all pages on the CPU tiers (75% DRAM / 25% CXL node), none on the GPU",
+            "sharding": ("one GPU: the whole 64 GB VA and the whole 1M-entry trace" if world == 1 else
+                         "ONE VA of %d x 64 GB (4 VA spaces) cut into %d contiguous va_block ranges, ONE trace of %d x 1M "
+                         "entries split by the owner of the faulting va_block (uvmtier/sharding.py); every GPU services "
+                         "its own range, no data-path collective; weak scaling" % (world, world, world))}
+
+
 def run_reference_arm(args, rank):
     if rank != 0:
         return
@@ -255,11 +269,11 @@ def run_reference_arm(args, rank):
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "u64", "data": "synthetic",
-            "config": {"workload": workload_name(args.trace),
-                       "cpu": "fetch/merge/sort and the per-va_block entry loop: the reference's own C (oracle/_ref); "
-                              "prefetch hint + make_resident behind it: CPU port (oracle)"},
+            "config": config_dict(args.trace, 1),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": kind,
-                             "sample": "%d entries per step sharded over %d processes, each with its own va_block state" % (n, cores)},
+                             "sample": "%d entries per step sharded over %d processes, each with its own va_block state; "
+                                       "fetch/merge/sort, the per-va_block entry loop, the prefetch hint and make_resident are the "
+                                       "reference's own C (oracle/_ref), the mapping of the serviced pages is restated" % (n, cores)},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0}
     emit(line)
@@ -826,13 +840,7 @@ def main():
         "metric": METRIC, "value": world * N_ENTRIES / (ms_step * 1e-3), "unit": UNIT, "n_gpus": world, "steps": steps,
         "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "u64", "data": "synthetic",
-        "config": {"workload": workload_name(args.trace), "batch": BATCH, "va_spaces": N_SPACES,
-                   "l2": "flushed between iterations (256 MiB memset)", "rng": "uvm_test_rng KISS stream, seed 1",
-                   "initial_residency": "all pages on the CPU tiers (75% DRAM / 25% CXL node), none on the GPU",
-                   "sharding": ("one GPU: the whole 64 GB VA and the whole 1M-entry trace" if world == 1 else
-                                "ONE VA of %d x 64 GB (4 VA spaces) cut into %d contiguous va_block ranges, ONE trace of %d x 1M "
-                                "entries split by the owner of the faulting va_block (uvmtier/sharding.py); every GPU services "
-                                "its own range, no data-path collective; weak scaling" % (world, world, world))},
+        "config": config_dict(args.trace, world),
         "e2e": {"value": world * N_ENTRIES / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_result),
                 "ms_per_step": e2e_ms,
                 "result": "batch headers + per-fault flags + run counter (what the caller of service_fault_batch consumes)",
@@ -858,7 +866,8 @@ def main():
         v1, kind, ns = cpu_arm(wl, 1, reps=2)
         line["cpu_baseline"] = {"value": v1, "unit": UNIT, "cores": 1, "kind": kind,
                                 "sample": "full step (%d entries), best of 2, 1 thread (the reference services one GPU on one thread); "
-                                          "fetch/merge/sort + service entry loop = reference C, make_resident back half = CPU port" % ns}
+                                          "fetch/merge/sort, entry loop, prefetch hint and make_resident = the reference's own C "
+                                          "when kind is reference, the CPU restatement when it is port" % ns}
     if rank == 0:
         emit(line)
     if dist is not None:

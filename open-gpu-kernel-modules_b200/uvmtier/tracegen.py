@@ -1,14 +1,12 @@
 """Synthetic replayable-fault traces, block state and page lists for the harness.
 
-All randomness comes from the reference's own test generator (uvm_test_rng, UVM/uvm_test_rng.c:37-62,
-exposed by the library as uvmtier_test_rng_fill): one u32 stream per seed, shaped with numpy.
+All randomness comes from the reference's own test generator (uvm_test_rng, UVM/uvm_test_rng.c:37-62), computed here
+in numpy (rng_stream; the library's uvmtier_test_rng_fill is the same stream in C for C callers): one u32 stream per
+seed, shaped with numpy.  Nothing in this module loads a shared library, so the CPU reference arm of bench.py builds
+its inputs without mapping the product.
 Packets are raw 32-byte NVC369_BUF_ENTRY records (UVM/clc369.h:33-66).
 """
-import ctypes
-
 import numpy as np
-
-from . import lib, P
 
 # HW access type encodings, hwref/volta/gv100/dev_fault.h:246-251
 HW_VIRT_READ, HW_VIRT_WRITE, HW_VIRT_ATOMIC_STRONG, HW_VIRT_PREFETCH, HW_VIRT_ATOMIC_WEAK = 0, 1, 2, 3, 4
@@ -28,10 +26,103 @@ GPU_PARAMS_DT = np.dtype([("max_batch_size", "<u4"), ("utlb_per_gpc_count", "<u4
 assert GPU_PARAMS_DT.itemsize == 32
 
 
+_MZ, _MW = 36969 * 65536 - 1, 18000 * 65536 - 1     # moduli of the two multiply-with-carry generators
+_LANES = 1 << 16
+
+
+def _xs_step(x):
+    """jsr ^= jsr << 17; jsr ^= jsr >> 13; jsr ^= jsr << 5 on uint32 (scalar or array)."""
+    x = x ^ ((x << np.uint32(17)) & np.uint32(0xFFFFFFFF))
+    x = x ^ (x >> np.uint32(13))
+    return x ^ ((x << np.uint32(5)) & np.uint32(0xFFFFFFFF))
+
+
+def _xs_apply(cols, x):
+    """Applies the GF(2)-linear map given by its 32 columns (images of the unit vectors) to every element of x."""
+    y = np.zeros_like(x)
+    for i in range(32):
+        y ^= np.where((x >> np.uint32(i)) & np.uint32(1), cols[i], np.uint32(0)).astype(np.uint32)
+    return y
+
+
+def _lane_starts(n_lanes, x0, jump):
+    """x0, jump(x0), jump(jump(x0)), ... for n_lanes lanes, by doubling: jump is a function (array, k) -> array that
+    advances every element by k lane strides."""
+    out = np.array([x0], dtype=np.uint64)
+    while len(out) < n_lanes:
+        out = np.concatenate([out, jump(out, len(out))])
+    return out[:n_lanes]
+
+
 def rng_stream(seed, n):
-    out = np.empty(n, np.uint32)
-    lib().uvmtier_test_rng_fill(ctypes.c_uint32(seed & 0xFFFFFFFF), ctypes.c_size_t(n), P(out))
-    return out
+    """The first n outputs of uvm_test_rng_32 for `seed` (UVM/uvm_test_rng.c:37-62: Marsaglia's KISS with z = 362436069,
+    w = 521288629, jcong = 380116160, jsr = seed), in numpy.  The four generators are recurrences; each is run on 65536
+    lanes in lockstep, lane j starting at element j * S of the sequence, which jump-ahead makes cheap: a lag-1
+    multiply-with-carry state advances by a modular multiplication (state' = state / 2^16 mod a * 2^16 - 1), the
+    congruential one by an affine map, the xorshift by a 32 x 32 matrix over GF(2).  Bit-identical to the C loop
+    (tests/test_oracle_faults.py compares them)."""
+    n = int(n)
+    if n <= 0:
+        return np.zeros(0, np.uint32)
+    R = min(_LANES, n)
+    S = (n + R - 1) // R                                   # elements per lane
+    with np.errstate(over="ignore"):
+        # ---- lane starts ----
+        def mwc_starts(s0, m):
+            binv_s = pow(pow(65536, -1, m), S, m)          # one lane stride
+            def jump(x, k):
+                return (x * np.uint64(pow(binv_s, k, m))) % np.uint64(m)
+            return _lane_starts(R, s0, jump)
+        z = mwc_starts(362436069, _MZ)
+        w = mwc_starts(521288629, _MW)
+        # x' = 69069 x + 1234567 (mod 2^32): S steps = x -> A x + C
+        A, C, a, c, k = 1, 0, 69069, 1234567, S
+        while k:
+            if k & 1:
+                A, C = (A * a) & 0xFFFFFFFF, (C * a + c) & 0xFFFFFFFF
+            a, c = (a * a) & 0xFFFFFFFF, (c * a + c) & 0xFFFFFFFF
+            k >>= 1
+        def lcg_jump(x, kk):
+            AA, CC, aa, cc = 1, 0, A, C
+            while kk:
+                if kk & 1:
+                    AA, CC = (AA * aa) & 0xFFFFFFFF, (CC * aa + cc) & 0xFFFFFFFF
+                aa, cc = (aa * aa) & 0xFFFFFFFF, (cc * aa + cc) & 0xFFFFFFFF
+                kk >>= 1
+            return (x * np.uint64(AA) + np.uint64(CC)) & np.uint64(0xFFFFFFFF)
+        jc = _lane_starts(R, 380116160, lcg_jump)
+        # xorshift: columns of M^S by square-and-multiply on the matrix
+        def mat_mul(p, q):                                 # columns of p o q
+            return _xs_apply(p, q)
+        ident = (np.uint32(1) << np.arange(32, dtype=np.uint32)).astype(np.uint32)
+        base = _xs_step(ident.copy())
+        ms, bk, k = ident.copy(), base, S
+        while k:
+            if k & 1:
+                ms = mat_mul(bk, ms)
+            bk = mat_mul(bk, bk)
+            k >>= 1
+        def xs_jump(x, kk):
+            cols, b2 = ident.copy(), ms
+            while kk:
+                if kk & 1:
+                    cols = mat_mul(b2, cols)
+                b2 = mat_mul(b2, b2)
+                kk >>= 1
+            return _xs_apply(cols, x.astype(np.uint32)).astype(np.uint64)
+        js = _lane_starts(R, seed & 0xFFFFFFFF, xs_jump).astype(np.uint32)
+        # ---- lockstep ----
+        z = z.astype(np.uint64); w = w.astype(np.uint64)
+        jc = jc.astype(np.uint32)
+        out = np.empty((R, S), np.uint32)
+        for t in range(S):
+            z = np.uint64(36969) * (z & np.uint64(65535)) + (z >> np.uint64(16))
+            w = np.uint64(18000) * (w & np.uint64(65535)) + (w >> np.uint64(16))
+            jc = jc * np.uint32(69069) + np.uint32(1234567)
+            js = _xs_step(js)
+            mwc = (((z & np.uint64(0xFFFF)) << np.uint64(16)) + w).astype(np.uint32)      # (z << 16) + w, 32 bits
+            out[:, t] = (mwc ^ jc) + js
+    return out.reshape(-1)[:n].copy()
 
 
 class Stream:

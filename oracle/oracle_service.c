@@ -54,6 +54,23 @@ static unsigned prot_of(unsigned acc)
  * (uvm_va_block.c:12361-12416 with uvm_enable_builtin_tests set, as in the reference's own test runs) */
 static bool logical_ok(unsigned logical_prot, unsigned acc) { return prot_of(acc) <= logical_prot; }
 
+/* The back half's two callees.  Default: the restatements in this directory.  oracle_service_set_back_half() swaps in
+ * functions of the same contract -- in practice ref_prefetch_get_hint_va_block (oracle/_ref/libref_prefetch.so: the
+ * reference's uvm_perf_prefetch.c compiled unmodified) and ref_make_resident (libref_resident.so: the reference's
+ * uvm_va_block_make_resident compiled verbatim), so that the whole CPU arm runs the reference's own code. */
+typedef void (*prefetch_hint_fn)(size_t, const ref_prefetch_block_t *, const uint64_t *, const uint64_t *, const uint64_t *,
+                                 const uint64_t *, ref_prefetch_info_t *, uint64_t *, uint32_t *);
+/* ref_make_resident also takes the id of the GPU the table belongs to (the restatement reads it from nowhere: one GPU) */
+typedef uint32_t (*ref_make_resident_fn)(uint32_t, const ref_make_resident_req_t *, const uint64_t *, const uint64_t *, uint32_t,
+                                         uint32_t, const ref_block_state_t *, ref_make_resident_result_t *, ref_copy_run_t *, uint32_t);
+static prefetch_hint_fn g_prefetch_hint = oracle_prefetch_get_hint_va_block;
+static ref_make_resident_fn g_ref_make_resident;
+void oracle_service_set_back_half(void *prefetch_hint, void *ref_make_resident)
+{
+    g_prefetch_hint = prefetch_hint ? (prefetch_hint_fn)prefetch_hint : oracle_prefetch_get_hint_va_block;
+    g_ref_make_resident = (ref_make_resident_fn)ref_make_resident;
+}
+
 static void mask_ptr_load(or_mask_t *m, uint64_t *base, uint32_t slot) { or_load(m, base + 8 * (size_t)slot); }
 static void mask_ptr_store(uint64_t *base, uint32_t slot, const or_mask_t *m) { or_store(base + 8 * (size_t)slot, m); }
 
@@ -109,7 +126,7 @@ void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_stat
     or_or(&any_cpu, &cpu0, &cpu1);
     pb.flags = REF_PF_HAS_RESIDENT_MASK | REF_PF_GPU_VA_SPACE_REGISTERED |
                ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0);
-    oracle_prefetch_get_hint_va_block(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot], pf_mask.w, &hint);
+    g_prefetch_hint(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot], pf_mask.w, &hint);
     rec->hint_residency = (uint16_t)hint;
     if (hint != 257) {
         or_or(&newres, &newres, &pf_mask);
@@ -132,8 +149,12 @@ void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_stat
         memset(&rq, 0, sizeof(rq));
         rq.slot = slot; rq.region_first = (uint16_t)rf; rq.region_outer = (uint16_t)ro; rq.dest_tier = 0; rq.cause = 0;
         rq.flags = 1 | 2; rq.mask_row = 0;
-        oracle_make_resident(1, &rq, newres.w, pf_mask.w, 0xFFFFFFFFu, st, &res, runs ? runs + (nrun < run_cap ? nrun : run_cap) : NULL,
-                             nrun < run_cap ? run_cap - nrun : 0);
+        if (g_ref_make_resident)
+            g_ref_make_resident(1, &rq, newres.w, pf_mask.w, 0xFFFFFFFFu, lay->gpu_id, st, &res,
+                                runs ? runs + (nrun < run_cap ? nrun : run_cap) : NULL, nrun < run_cap ? run_cap - nrun : 0);
+        else
+            oracle_make_resident(1, &rq, newres.w, pf_mask.w, 0xFFFFFFFFu, st, &res, runs ? runs + (nrun < run_cap ? nrun : run_cap) : NULL,
+                                 nrun < run_cap ? run_cap - nrun : 0);
         rec->migrated[0] = res.migrated[0];
         rec->migrated[1] = res.migrated[1];
         rec->first_touch = res.first_touch;

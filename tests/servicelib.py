@@ -90,6 +90,21 @@ def run_service_ref(ref, k1, gp, table, layout, state, pf=(1, 51, 1), run_cap=1 
     return dict(flags=flags, records=svc[:nsvc], runs=runs, n_runs=n_runs.value, batch=batch, state=st)
 
 
+def use_reference_back_half(svc_lib, ref_prefetch, ref_resident, pf=(1, 51, 1)):
+    """Routes the back half of the servicing checker `svc_lib` (liboracle.so or libref_service.so) to the reference's
+    own code: uvm_perf_prefetch.c compiled unmodified (libref_prefetch.so) and uvm_va_block_make_resident compiled
+    verbatim (libref_resident.so).  Pass None, None to go back to the restatements.  Returns True when hooked."""
+    fn = svc_lib.oracle_service_set_back_half
+    fn.argtypes = [ctypes.c_void_p, ctypes.c_void_p]
+    fn.restype = None
+    if ref_prefetch is None or ref_resident is None:
+        fn(None, None)
+        return False
+    ref_prefetch.ref_prefetch_init(ctypes.c_uint(pf[0]), ctypes.c_uint(pf[1]), ctypes.c_uint(pf[2]))
+    fn(ctypes.cast(ref_prefetch.ref_prefetch_get_hint_va_block, ctypes.c_void_p), ctypes.cast(ref_resident.ref_make_resident, ctypes.c_void_p))
+    return True
+
+
 REF_FLAG_MASK = 0x0004 | 0x0008 | 0x0700 | 0x1000     # FATAL, INVALID_PREFETCH, fatal reason, cancel mode
 
 

@@ -165,3 +165,30 @@ def test_oracle_and_simt_match_golden_vectors():
                     batch=g[pre + "batch"], ring_after=g[pre + "ring_after"])
         F.assert_fetch_equal(want, F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl), "golden %d oracle" % k)
         F.assert_fetch_equal(want, F.run_fetch_preprocess_simt(sim, pk, gp, tbl), "golden %d simt" % k)
+
+
+def test_numpy_kiss_stream_is_the_reference_generator():
+    """tracegen.rng_stream (numpy, lanes + jump-ahead) against a line-by-line loop of uvm_test_rng_32
+    (UVM/uvm_test_rng.c:37-62) and against the library's C routine, lengths around the lane boundaries."""
+    import ctypes
+    import uvmtier
+
+    def loop(seed, n):
+        z, w, jcong, jsr, M = 362436069, 521288629, 380116160, seed & 0xFFFFFFFF, 0xFFFFFFFF
+        out = []
+        for _ in range(n):
+            z = (36969 * (z & 65535) + (z >> 16)) & M
+            w = (18000 * (w & 65535) + (w >> 16)) & M
+            jcong = (69069 * jcong + 1234567) & M
+            jsr ^= (jsr << 17) & M
+            jsr ^= jsr >> 13
+            jsr ^= (jsr << 5) & M
+            out.append((((((z << 16) + w) & M) ^ jcong) + jsr) & M)
+        return np.array(out, np.uint32)
+
+    for seed, n in ((1, 1), (42, 3000), (0xC0FFEE, 70001)):
+        assert np.array_equal(TG.rng_stream(seed, n), loop(seed, n)), (seed, n)
+    for seed, n in ((7, 65536), (7, 65537), (123456789, 1 << 20)):
+        c = np.empty(n, np.uint32)
+        uvmtier.lib().uvmtier_test_rng_fill(ctypes.c_uint32(seed), ctypes.c_size_t(n), T.P(c))
+        assert np.array_equal(TG.rng_stream(seed, n), c), (seed, n)

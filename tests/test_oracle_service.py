@@ -280,3 +280,26 @@ def test_servicing_breaks_read_duplication(heavy_min):
     if ref is not None and heavy_min == 96:
         layout = S.make_layout(lay)
         S.assert_ref_equals_oracle(S.run_service_ref(ref, k1, gp, tbl, layout, st0), want, "read duplication")
+
+
+@pytest.mark.parametrize("dist", ["uniform", "hotset", "adversarial"])
+def test_reference_code_end_to_end_equals_the_restatement(dist):
+    """The CPU arm with NO restated step on the data path except the mapping of the serviced pages: the reference's
+    entry loop (libref_service.so) calling the reference's prefetch file (libref_prefetch.so) and the reference's
+    uvm_va_block_make_resident (libref_resident.so).  Same records, copy runs, counters and state as the restatement."""
+    rs, rp, rr = T.load_ref("service"), T.load_ref("prefetch"), T.load_ref("resident")
+    if rs is None or rp is None or rr is None:
+        pytest.skip("reference libraries not built (no /root/reference)")
+    pk, tbl, lay = TG.fault_trace(2500, 91, dist, 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(128)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 12)
+    k1 = _k1(pk, gp, tbl)
+    layout = S.make_layout(lay)
+    want = S.run_service_oracle(T.load_oracle(), k1, gp, tbl, layout, st0)
+    assert S.use_reference_back_half(rs, rp, rr)
+    try:
+        got = S.run_service_ref(rs, k1, gp, tbl, layout, st0)
+    finally:
+        S.use_reference_back_half(rs, None, None)
+    S.assert_ref_equals_oracle(got, want, "reference end to end, %s" % dist)
+    assert int((want["records"]["page_fault_count"] > 0).sum()) >= 4

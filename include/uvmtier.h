@@ -463,14 +463,16 @@ NV_STATUS uvmtier_service_replayable_faults_streamed(uvmtier_ctx_t *ctx, const u
  * integrations that fix their memory budget at start-up and forbid allocator calls afterwards are in the same
  * position.  uvmtier_service_fault_batches_device grows its working space with cudaMalloc; this variant uses a
  * fixed array that is part of the library image instead and calls no cudaMalloc / cudaFree or any other
- * allocating routine.  Arguments, results and semantics are those of uvmtier_service_fault_batches_device.
+ * allocating routine (it enqueues kernels, two memsets and event records / waits on existing streams).  Arguments, results and semantics are those of uvmtier_service_fault_batches_device.
  *
  * Limits (NV_ERR_INVALID_ARGUMENT beyond them, uvmtier_last_error() says which):
  *   n_spaces * blocks_per_space <= 65536 va_block slots (128 GB of VA),
  *   n_batches * max_batch_size  <= 262144 entries,  n_batches <= 4096.
  * The array is about 4.5 MB and every GPU that loads the library holds it until the process exits.
- * The first call on a GPU looks up the array's device address (with that GPU current); make that first call
- * before any stream capture is begun.  All calls on a GPU share the one array, which keeps the previous call's
+ * Nothing is created by the call itself: uvmtier_init has already looked up the array's device address (with the
+ * context's GPU current; that lookup is also what makes the CUDA runtime load the array) and created the pass's two
+ * side streams and their events -- so create the context while memory is still to be had, and before any stream
+ * capture is begun.  All calls on a GPU share the one array, which keeps the previous call's
  * contents: the function clears the parts that have to start at zero itself, but two calls whose GPU work
  * overlaps (different streams or contexts on the same GPU) race on it -- serialise them. */
 NV_STATUS uvmtier_service_fault_batches_noalloc_device(uvmtier_ctx_t *ctx, uint32_t n_batches,

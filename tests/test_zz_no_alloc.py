@@ -93,6 +93,25 @@ def test_no_alloc_service_matches_the_regular_entry_point_twice_in_a_row():
             _same(want, got, "call %d (%s)" % (call, dist))
 
 
+def test_no_alloc_service_as_the_first_servicing_call_of_a_context():
+    """A caller that may not allocate has, by definition, not run the allocating entry point first.  On a fresh
+    context the no-alloc call must find everything it needs already in place (uvmtier_init sets up the side streams,
+    their events and the fixed array's address), and give the regular entry point's results."""
+    run_cap = 1 << 18
+    pk, tbl, lay = TG.fault_trace(6000, 21, "uniform", 2, total_va_bytes=512 << 21)
+    gp = TG.gpu_params(128)
+    layout = S.make_layout(lay)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 21)
+    with uvmtier.Context(0) as fresh:
+        r = _preprocess(fresh, pk, gp, tbl)
+        got = _service(fresh, "uvmtier_service_fault_batches_noalloc_device", r, layout, st0, run_cap)
+    with uvmtier.Context(0) as other:
+        r2 = _preprocess(other, pk, gp, tbl)
+        want = _service(other, "uvmtier_service_fault_batches_device", r2, layout, st0, run_cap)
+    assert int((want["flags"] & 1).sum()) > 100
+    _same(want, got, "no-alloc first")
+
+
 def test_no_alloc_service_rejects_sizes_beyond_its_fixed_array():
     lib = uvmtier.lib()
     with uvmtier.Context(0) as ctx:

@@ -280,50 +280,111 @@ def run_reference_arm(args, rank):
 
 
 # ----------------------------------------------------------------------------------------------- migration leg
-def migration_numbers(ctx, lib, P, rank, world, dist, nbytes=256 << 20):
-    """Page-migration GB/s (config C, bounded): 4 KB pages in random order, host DRAM / CXL node <-> HBM, SM-driven
-    TMA copies vs the copy-engine peak measured on the same buffers; NVLink peer push when world > 1."""
+def migration_numbers(ctx, lib, P, rank, world, dist, arena=8 << 30):
+    """Page-migration GB/s (BASELINE config C as a compact sweep, and config A's CPU copy beside it):
+      * 4 KB / 64 KB / 2 MB pages x {1 GB, 8 GB} x {DRAM->HBM, CXL->HBM, HBM->DRAM, HBM->CXL}, pages placed by a random
+        permutation, SM-driven TMA copies (uvmtier_copy_page_list_device).  Every point is measured right after the
+        copy-engine peak of the same direction, size and buffers (cudaMemcpyAsync, best of 2), all ranks doing the same
+        pair at the same time, so the fraction compares like with like also when eight GPUs share the host;
+      * DRAM->CXL for 64 MB and 1 GB: the reference's CPU page loop (uvm_va_block.c:3946-3991, kmap + memcpy per page,
+        compiled verbatim: oracle/_ref/libref_copy.so) on 1 thread and on all cores, and the GPU moving the same pages;
+      * the fork's CXL P2P DMA request (one contiguous range, 2 MB pages)."""
     import uvmtier
-    from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, TIER_PEER0
-    info = {t: ctx.tier_create(t, nbytes) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
+    from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM
+    info = {t: ctx.tier_create(t, arena) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
     for t in (TIER_DRAM, TIER_CXL):
         info[t].host_view()[:] = 0x5A
-    n_pages = nbytes // 4096
-    rng = np.random.default_rng(7)
-    s_off = np.arange(n_pages, dtype=np.uint64) * np.uint64(4096)
-    d_off = rng.permutation(n_pages).astype(np.uint64) * np.uint64(4096)
-    d_s, d_d = ctx.to_device(s_off), ctx.to_device(d_off)
     ms = ctypes.c_float(0)
-    out = {"page_size": 4096, "order": "random permutation", "bytes": nbytes, "unit": "GB/s",
+    out = {"order": "random permutation", "unit": "GB/s",
            "cxl_node": "emulated on a DRAM node (no CPU-less NUMA node on this machine)" if info[TIER_CXL].flags & 1 else
            "NUMA node %d" % info[TIER_CXL].numa_node}
 
-    def timed(dst, src, n=n_pages, reps=3):
+    def sync_all():
+        ctx.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def timed(dst, src, d_d, d_s, n, page_size, reps=2):
         best = 1e30
         for r in range(reps + 1):
             lib.uvmtier_event_record(ctx.handle, 900)
-            st = lib.uvmtier_copy_page_list_device(ctx.handle, dst, src, ctypes.c_size_t(n), P(d_d), P(d_s), 4096, 0)
+            st = lib.uvmtier_copy_page_list_device(ctx.handle, dst, src, ctypes.c_size_t(n), P(d_d), P(d_s), page_size, 0)
             assert st == 0, hex(st)
             lib.uvmtier_event_record(ctx.handle, 901)
             lib.uvmtier_event_elapsed_ms(ctx.handle, 900, 901, ctypes.byref(ms))
             if r:
                 best = min(best, ms.value)
-        return n * 4096 / (best * 1e-3) / 1e9
+        return n * page_size / (best * 1e-3) / 1e9
 
     names = {TIER_HBM: "hbm", TIER_DRAM: "dram", TIER_CXL: "cxl"}
-    for dst, src in ((TIER_HBM, TIER_DRAM), (TIER_HBM, TIER_CXL), (TIER_DRAM, TIER_HBM), (TIER_CXL, TIER_HBM)):
-        gbs = timed(dst, src)
-        peak = ctx.tier_memcpy_peak_gbs(dst, src, nbytes, 3)
-        out["%s_to_%s" % (names[src], names[dst])] = {"GBs": round(gbs, 2), "copy_engine_peak_GBs": round(peak, 2),
-                                                       "frac_of_link_peak": round(gbs / peak, 3)}
+    sweep = []
+    rng = np.random.default_rng(7)
+    for nbytes in (1 << 30, arena):
+        for page_size in (4096, 65536, 2 << 20):
+            n = nbytes // page_size
+            s_off = np.arange(n, dtype=np.uint64) * np.uint64(page_size)
+            d_off = rng.permutation(n).astype(np.uint64) * np.uint64(page_size)
+            d_s, d_d = ctx.to_device(s_off), ctx.to_device(d_off)
+            for dst, src in ((TIER_HBM, TIER_DRAM), (TIER_HBM, TIER_CXL), (TIER_DRAM, TIER_HBM), (TIER_CXL, TIER_HBM)):
+                sync_all()
+                peak = ctx.tier_memcpy_peak_gbs(dst, src, nbytes, 2)
+                gbs = timed(dst, src, d_d, d_s, n, page_size)
+                row = {"direction": "%s_to_%s" % (names[src], names[dst]), "page_size": page_size, "bytes": nbytes,
+                       "GBs": round(gbs, 2), "copy_engine_peak_GBs": round(peak, 2), "frac_of_link_peak": round(gbs / peak, 3)}
+                sweep.append(row)
+                if page_size == 4096 and nbytes == 1 << 30:
+                    out[row["direction"]] = {k: row[k] for k in ("GBs", "copy_engine_peak_GBs", "frac_of_link_peak")}
+            ctx.free(d_s); ctx.free(d_d)
+    out["sweep"] = sweep
+    out["min_frac_of_link_peak"] = min(r["frac_of_link_peak"] for r in sweep)
+
+    # ---- DRAM -> CXL: the reference's CPU page loop beside the GPU (rank 0 only: the host cores are shared) ----
+    if rank == 0:
+        sys.path.insert(0, os.path.join(ROOT, "tests"))
+        import uvmtier_testlib as T
+        rc = T.load_ref("copy")
+        cpu = {"what": "uvm_va_block.c:3946-3991 compiled verbatim (kmap + memcpy(PAGE_SIZE) per page), DRAM tier -> CXL tier",
+               "available": rc is not None}
+        src_p, dst_p = info[TIER_DRAM].host_ptr, info[TIER_CXL].host_ptr
+        cores = os.cpu_count() or 1
+        for nbytes, key in ((64 << 20, "64MB"), (1 << 30, "1GB")):
+            blocks = nbytes >> 21
+            entry = {}
+            if rc is not None:
+                rc.ref_copy_pages_cpu.restype = ctypes.c_uint64
+                rc.ref_copy_pages_cpu.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_uint32, ctypes.c_uint32, ctypes.c_uint32,
+                                                  ctypes.c_uint32]
+                for threads in (1, cores):
+                    best = 1e30
+                    for _ in range(3):
+                        th = [threading.Thread(target=rc.ref_copy_pages_cpu,
+                                               args=(dst_p, src_p, t * blocks // threads, (t + 1) * blocks // threads, 0, 512))
+                              for t in range(threads)]
+                        t0 = time.perf_counter()
+                        for x in th: x.start()
+                        for x in th: x.join()
+                        best = min(best, time.perf_counter() - t0)
+                    entry["cpu_%d_thread%s_GBs" % (threads, "" if threads == 1 else "s")] = round(nbytes / best / 1e9, 2)
+            n = nbytes // 4096
+            lin = np.arange(n, dtype=np.uint64) * np.uint64(4096)
+            d_l = ctx.to_device(lin)
+            entry["gpu_GBs"] = round(timed(TIER_CXL, TIER_DRAM, d_l, d_l, n, 4096), 2)
+            ctx.free(d_l)
+            cpu[key] = entry
+        cpu["cores"] = cores
+        out["dram_to_cxl"] = cpu
+
     # the fork's CXL P2P DMA request (one contiguous range between the CXL buffer and HBM, 2 MB pages)
+    nbytes = 1 << 30
     hnd = ctypes.c_void_p()
     st = lib.uvmtier_p2p_register_cxl_buffer(ctx.handle, ctypes.c_void_p(info[TIER_CXL].host_ptr), ctypes.c_uint64(nbytes),
                                              ctypes.c_uint32(2), ctypes.byref(hnd))
     assert st == 0, hex(st)
-    for flag, key in ((1, "cxl_p2p_dma_cxl_to_gpu"), (0, "cxl_p2p_dma_gpu_to_cxl")):
+    for flag, key, dst, src in ((1, "cxl_p2p_dma_cxl_to_gpu", TIER_HBM, TIER_CXL), (0, "cxl_p2p_dma_gpu_to_cxl", TIER_CXL, TIER_HBM)):
+        sync_all()
+        peak = ctx.tier_memcpy_peak_gbs(dst, src, nbytes, 2)
         best = 1e30
-        for r in range(4):
+        for r in range(3):
             lib.uvmtier_event_record(ctx.handle, 900)
             st = lib.uvmtier_p2p_cxl_dma_request(ctx.handle, hnd, ctypes.c_uint64(0), ctypes.c_uint64(0), ctypes.c_uint64(nbytes),
                                                  ctypes.c_uint32(flag | 2), None)
@@ -332,10 +393,9 @@ def migration_numbers(ctx, lib, P, rank, world, dist, nbytes=256 << 20):
             lib.uvmtier_event_elapsed_ms(ctx.handle, 900, 901, ctypes.byref(ms))
             if r:
                 best = min(best, ms.value)
-        peak = out["cxl_to_hbm" if flag else "hbm_to_cxl"]["copy_engine_peak_GBs"]
-        out[key] = {"GBs": round(nbytes / (best * 1e-3) / 1e9, 2), "frac_of_link_peak": round(nbytes / (best * 1e-3) / 1e9 / peak, 3)}
+        out[key] = {"GBs": round(nbytes / (best * 1e-3) / 1e9, 2), "copy_engine_peak_GBs": round(peak, 2),
+                    "frac_of_link_peak": round(nbytes / (best * 1e-3) / 1e9 / peak, 3)}
     assert lib.uvmtier_p2p_unregister_cxl_buffer(ctx.handle, hnd) == 0
-    ctx.free(d_s); ctx.free(d_d)
     for t in (TIER_HBM, TIER_DRAM, TIER_CXL):
         ctx.tier_destroy(t)
     return out
@@ -601,6 +661,55 @@ def peer_numbers(ctx, lib, P, rank, world, dist, region_bytes=1 << 30):
     return out
 
 
+def other_trace_numbers(ctx, lib, P, trace, steps=5, warmup=3):
+    """The same device-resident step (K1 + service pass, L2 flushed, CUDA events on the library's stream) on another
+    address distribution of the 1M-entry trace: `stream` (sequential pages, 30-70 % duplicates, a few hundred va_blocks
+    with long runs) or `hotset` (90 % of the faults on 1 % of the va_blocks)."""
+    from uvmtier import layouts as L
+    wl = build_workload(1, trace)
+    n = len(wl["packets"]); nb = (n + BATCH - 1) // BATCH; ncap = nb * BATCH
+    ctx.fault_buffer_init(wl["gpu_params"], wl["table"])
+    ring_host = np.zeros((n + 1, 8), np.uint32); ring_host[:n] = wl["packets"]
+    d_ring0, d_ring = ctx.to_device(ring_host), ctx.alloc(ring_host.nbytes)
+    d_disp, d_ord, d_grp, d_bat = ctx.alloc(ncap * 4), ctx.alloc(ncap * 16), ctx.alloc(ncap * 16), ctx.alloc(nb * 32)
+    d_flags, d_svc, d_runs, d_cnt = ctx.alloc(ncap * 2), ctx.alloc(ncap * 96), ctx.alloc(RUN_CAP * 8), ctx.alloc(8)
+    ds0 = ctx.block_state_alloc(wl["layout"]); ds0.upload(wl["state"])
+    ds = ctx.block_state_alloc(wl["layout"])
+    state_bytes = wl["n_slots"] * (6 * 64 + 4 + 2 + 1)
+    d_flush = ctx.alloc(L2_FLUSH_BYTES)
+    new_get, ms = ctypes.c_uint32(0), ctypes.c_float(0)
+    t_k1, t_svc = [], []
+    for it in range(warmup + steps):
+        lib.uvmtier_memcpy_d2d_async(ctx.handle, P(d_ring), P(d_ring0), ctypes.c_size_t(ring_host.nbytes))
+        lib.uvmtier_memcpy_d2d_async(ctx.handle, ctypes.c_void_p(ds.ptrs.gpu_resident), ctypes.c_void_p(ds0.ptrs.gpu_resident),
+                                     ctypes.c_size_t(state_bytes))
+        lib.uvmtier_memset_device(ctx.handle, P(d_flush), 0, ctypes.c_size_t(L2_FLUSH_BYTES))
+        lib.uvmtier_event_record(ctx.handle, 930)
+        st1 = lib.uvmtier_fetch_preprocess_fault_batches_device(ctx.handle, P(d_ring), ctypes.c_uint32(n + 1), ctypes.c_uint32(0),
+                                                                ctypes.c_uint32(n), ctypes.c_int(1), P(d_disp), P(d_ord), P(d_grp),
+                                                                P(d_bat), None, ctypes.byref(new_get))
+        lib.uvmtier_event_record(ctx.handle, 931)
+        st2 = lib.uvmtier_service_fault_batches_device(ctx.handle, ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(wl["layout"]),
+                                                       ctypes.byref(ds.ptrs), P(d_flags), P(d_svc), P(d_runs), ctypes.c_uint32(RUN_CAP),
+                                                       P(d_cnt))
+        lib.uvmtier_event_record(ctx.handle, 932)
+        assert st1 == 0 and st2 == 0, (hex(st1), hex(st2))
+        lib.uvmtier_event_elapsed_ms(ctx.handle, 930, 931, ctypes.byref(ms)); a = ms.value
+        lib.uvmtier_event_elapsed_ms(ctx.handle, 931, 932, ctypes.byref(ms)); b = ms.value
+        if it >= warmup:
+            t_k1.append(a); t_svc.append(b)
+    bat = ctx.from_device(d_bat, nb, L.BATCH_DT)
+    cnt = ctx.from_device(d_cnt, 2, "<u4")
+    k1, svc = float(np.mean(t_k1)), float(np.mean(t_svc))
+    out = {"ms_per_step": k1 + svc, "k_fault_fetch_preprocess_ms": k1, "service_pass_ms": svc, "entries_per_s": n / ((k1 + svc) * 1e-3),
+           "coalesced_entries": int(bat["num_coalesced_faults"].sum()), "va_block_runs": int(bat["num_block_groups"].sum()),
+           "copy_runs": int(cnt[0]), "steps": steps}
+    for p_ in (d_ring0, d_ring, d_disp, d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt, d_flush):
+        ctx.free(p_)
+    ds.free(); ds0.free()
+    return out
+
+
 # ----------------------------------------------------------------------------------------------- GPU arm
 _REAL_STDOUT = None
 
@@ -813,6 +922,9 @@ def main():
     thrash = None
     if not args.no_migration and rank == 0:
         thrash = thrashing_numbers(ctx, lib, P, rank)
+    other = None
+    if not args.no_migration and world == 1 and args.trace == "uniform":
+        other = {t: other_trace_numbers(ctx, lib, P, t) for t in ("stream", "hotset")}
     clocks = sampler.stop(windows=((wall0, wall1), (wall2, wall3)))
 
     # ---- max over ranks ----
@@ -860,6 +972,7 @@ def main():
         "oversubscription": oversub,
         "access_counters": access,
         "thrashing": thrash,
+        "other_traces": other,
         "wall_s_timed_region": wall1 - wall0,
     }
     if rank == 0 and world == 1 and not args.no_cpu_baseline:

@@ -626,7 +626,9 @@ typedef struct {
     uint32_t evicted_to_dram, evicted_to_cxl;   /* root chunks */
     uint32_t peak_chunks_in_use, chunks_in_use; /* after the last pass */
     uint64_t pages_evicted, pages_promoted;     /* pages copied out of / into HBM (first touch included) */
-    uint32_t reserved[4];
+    uint32_t overcommitted_passes;              /* chunks of batches that alone needed more root chunks than HBM holds:
+                                                   everything else was evicted and they were serviced over capacity */
+    uint32_t reserved[3];
 } uvmtier_tiering_stats_t;
 NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
                                                       const uvmtier_ordered_fault_t *d_ordered,

@@ -178,7 +178,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
         return NV_ERR_INVALID_STATE;
     if (!n_batches)
         return NV_OK;
-    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service)
+    if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || n_batches > 65536u)   // 16-bit batch numbers
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     const uint32_t B = ctx->faults->gp.max_batch_size;
@@ -188,7 +188,11 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
     const uint64_t kmax64 = chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots;
     const uint32_t kmax = (uint32_t)(kmax64 < 65536 ? kmax64 : 65536);
     const uint32_t evict_run_cap = kmax * 256u;                           // a block's GPU pages: at most 256 runs
-    const uint64_t svc_cap64 = chunk_entries * 16 > (1u << 16) ? chunk_entries * 16 : (1u << 16);
+    // copy runs of one servicing pass, worst case: every page a va_block receives is a run of its own, a va_block
+    // receives at most its 512 pages, and a pass touches at most min(entries, slots) va_blocks -- so the list is never
+    // cut and the copies never run on a truncated list
+    const uint64_t svc_blocks = chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots;
+    const uint64_t svc_cap64 = svc_blocks * UVMTIER_PAGES_PER_VA_BLOCK;
     const uint32_t svc_run_cap = (uint32_t)(svc_cap64 < 0x7fffffffull ? svc_cap64 : 0x7fffffffull);
     // working space: counters, tallies, requests, results, the two run arrays
     const size_t o_cnt = 0, o_acc = 256, o_req = 512, o_res = uvmtier_align_up(o_req + (size_t)kmax * sizeof(uvmtier_make_resident_req_t), 256),
@@ -214,8 +218,12 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
         const size_t e0 = (size_t)b0 * B;
         // Make room: count what the chunk needs, evict the overflow, count again -- a victim that this very chunk of
         // batches faults on comes back and needs a chunk again, so the second count can ask for a few more.
+        // Rounds repeat until nothing overflows; a wave takes at most kmax victims, so the bound is what it takes to
+        // empty HBM, plus the recounts.
         uint32_t needed = 0, in_use = 0;
-        for (int round = 0; round < 8; round++) {
+        bool fits = false;
+        const int max_rounds = (int)(pmm->n_slots / (kmax ? kmax : 1u)) + 8;
+        for (int round = 0; round < max_rounds; round++) {
             st = uvmtier_pmm_count_needed_device(ctx, pmm, nb, d_groups + e0, d_batches + b0, lay, d_cnt);
             if (st != NV_OK)
                 return st;
@@ -234,8 +242,10 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                 k = in_use;                                               // the chunk alone overflows HBM: evict all there is
             if (k > kmax)
                 k = kmax;
-            if (!k)
+            if (!k) {
+                fits = true;
                 break;
+            }
             const uint32_t dest = dram_pages + (uint64_t)k * UVMTIER_PAGES_PER_VA_BLOCK <= dram_capacity_pages ? UVMTIER_TIER_DRAM
                                                                                                                 : UVMTIER_TIER_CXL;
             st = uvmtier_pmm_pick_chunks_to_evict_device(ctx, pmm, k, dest, d_req, d_cnt + 5);
@@ -259,6 +269,10 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
             if (dest == UVMTIER_TIER_DRAM) stats.evicted_to_dram += k; else stats.evicted_to_cxl += k;
             in_use -= k;                                                  // what the next count will find (if there is none)
         }
+        if (!fits)
+            return NV_ERR_NO_MEMORY;                                      // still over capacity after emptying HBM wave by wave
+        if ((uint64_t)in_use + needed > pmm->capacity_chunks)
+            stats.overcommitted_passes++;                                 // the chunk of batches alone needs more than HBM holds
         // service the chunk, note its list moves, bring its pages in
         UVMTIER_CUDA(cudaMemsetAsync(d_cnt + 8, 0, 2 * sizeof(uint32_t), ctx->stream));
         st = uvmtier_service_pass_chunk(ctx, nb, d_ordered + e0, d_groups + e0, d_batches + b0, lay, state, d_entry_flags + e0,

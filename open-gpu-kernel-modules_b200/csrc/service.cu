@@ -174,6 +174,8 @@ static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, cons
     if (!ctx->faults->gp.max_batch_size || n_slots64 == 0 || n_slots64 > kMaxSlots ||
         (size_t)n_batches * ctx->faults->gp.max_batch_size > 0xffffffffu)
         return NV_ERR_INVALID_ARGUMENT;
+    if (n_batches > 65536u)                                 // uvmtier_service_group_t.batch is 16 bits wide
+        return NV_ERR_INVALID_ARGUMENT;
     return NV_OK;
 }
 

@@ -89,6 +89,13 @@ if [ -f "$HERE/ref_resident_glue.c" ]; then
     echo "build_ref: built $OUT/libref_resident.so"
 fi
 
+# ---------------- copy leg: the CPU page-copy loop of block_copy_pages (kmap + memcpy per page), verbatim ----------------
+if [ -f "$HERE/ref_copy_glue.c" ]; then
+    sed -n '3946,3991p' "$UVM/uvm_va_block.c" > "$TMP/x_copy_pages.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_copy_glue.c" -o "$OUT/libref_copy.so"
+    echo "build_ref: built $OUT/libref_copy.so"
+fi
+
 # ---------------- PMM leg: the eviction order (pick_root_chunk_to_evict and the list moves), verbatim ----------------
 if [ -f "$HERE/ref_pmm_glue.c" ]; then
     pin uvm_pmm_gpu.c 579fbaf9e0b9de07

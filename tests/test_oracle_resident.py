@@ -123,3 +123,24 @@ def test_oracle_matches_the_reference_make_resident(seed, rdup):
     res = want["results"]
     assert int(res["migrated"][:, 0].sum()) > 500 and int(res["migrated"][:, 1].sum()) > 200 and int(res["migrated"][:, 2].sum()) > 300
     assert int(res["first_touch"].sum()) > 100 and int(res["unmapped"].sum()) > 50
+
+
+def test_reference_cpu_page_copy_loop_is_byte_exact():
+    """libref_copy.so = block_copy_pages (uvm_va_block.c:3946-3991) compiled verbatim with kmap -> identity: copies the
+    pages of a region of every va_block, one memcpy(PAGE_SIZE) per page, and marks them dirty at the destination."""
+    import ctypes
+    rc = T.load_ref("copy")
+    if rc is None:
+        pytest.skip("reference libraries not built (no /root/reference)")
+    rc.ref_copy_pages_cpu.restype = ctypes.c_uint64
+    rc.ref_copy_pages_cpu.argtypes = [ctypes.c_void_p, ctypes.c_void_p] + [ctypes.c_uint32] * 4
+    blocks = 5
+    src = np.random.default_rng(3).integers(0, 256, blocks << 21, dtype=np.uint8)
+    dst = np.full(blocks << 21, 0xEE, np.uint8)
+    marked = rc.ref_copy_pages_cpu(dst.ctypes.data, src.ctypes.data, 1, 4, 7, 300)
+    assert marked == 3 * (300 - 7)
+    want = np.full(blocks << 21, 0xEE, np.uint8)
+    for b in range(1, 4):
+        lo, hi = (b << 21) + 7 * 4096, (b << 21) + 300 * 4096
+        want[lo:hi] = src[lo:hi]
+    assert np.array_equal(dst, want)

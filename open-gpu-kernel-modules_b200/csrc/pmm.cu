@@ -218,11 +218,13 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
         const size_t e0 = (size_t)b0 * B;
         // Make room: count what the chunk needs, evict the overflow, count again -- a victim that this very chunk of
         // batches faults on comes back and needs a chunk again, so the second count can ask for a few more.
-        // Rounds repeat until nothing overflows; a wave takes at most kmax victims, so the bound is what it takes to
-        // empty HBM, plus the recounts.
+        // Rounds repeat until nothing overflows.  A victim that this chunk of batches faults on needs a chunk again, so
+        // the overflow shrinks geometrically rather than at once; a wave takes at most kmax victims.  The bound covers
+        // emptying HBM wave by wave plus the recounts; a pass that still does not fit is serviced over capacity and
+        // counted (stats.overcommitted_passes).
         uint32_t needed = 0, in_use = 0;
         bool fits = false;
-        const int max_rounds = (int)(pmm->n_slots / (kmax ? kmax : 1u)) + 8;
+        const int max_rounds = (int)(pmm->n_slots / (kmax ? kmax : 1u)) + 64;
         for (int round = 0; round < max_rounds; round++) {
             st = uvmtier_pmm_count_needed_device(ctx, pmm, nb, d_groups + e0, d_batches + b0, lay, d_cnt);
             if (st != NV_OK)
@@ -269,10 +271,8 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
             if (dest == UVMTIER_TIER_DRAM) stats.evicted_to_dram += k; else stats.evicted_to_cxl += k;
             in_use -= k;                                                  // what the next count will find (if there is none)
         }
-        if (!fits)
-            return NV_ERR_NO_MEMORY;                                      // still over capacity after emptying HBM wave by wave
-        if ((uint64_t)in_use + needed > pmm->capacity_chunks)
-            stats.overcommitted_passes++;                                 // the chunk of batches alone needs more than HBM holds
+        if (!fits || (uint64_t)in_use + needed > pmm->capacity_chunks)
+            stats.overcommitted_passes++;                                 // e.g. the chunk of batches alone needs more than HBM holds
         // service the chunk, note its list moves, bring its pages in
         UVMTIER_CUDA(cudaMemsetAsync(d_cnt + 8, 0, 2 * sizeof(uint32_t), ctx->stream));
         st = uvmtier_service_pass_chunk(ctx, nb, d_ordered + e0, d_groups + e0, d_batches + b0, lay, state, d_entry_flags + e0,

@@ -96,6 +96,20 @@ if [ -f "$HERE/ref_copy_glue.c" ]; then
     echo "build_ref: built $OUT/libref_copy.so"
 fi
 
+# ---------------- the fork's CXL P2P DMA file, whole and unmodified ----------------
+P2P="$REF/src/nvidia/src/kernel/mem_mgr"
+if [ -f "$HERE/ref_cxl_p2p_glue.c" ] && [ -f "$P2P/p2p_cxl.c" ]; then
+    got="$(sha256sum "$P2P/p2p_cxl.c" | cut -c1-16)"
+    if [ "$got" != "5526c5812ec155d1" ]; then echo "build_ref: p2p_cxl.c sha256 prefix $got != pinned 5526c5812ec155d1" >&2; exit 1; fi
+    # the nine RM headers it includes become empty files (the glue defines what the file uses of them)
+    for h in core/core.h gpu/gpu.h mem_mgr/p2p.h os/os.h nvport/nvport.h gpu/mem_mgr/mem_mgr.h gpu/mem_mgr/mem_desc.h \
+             gpu/mem_mgr/ce_utils.h gpu/bus/kern_bus.h; do
+        mkdir -p "$TMP/rmstub/$(dirname "$h")"; : > "$TMP/rmstub/$h"
+    done
+    gcc $CFLAGS -I"$TMP/rmstub" -I"$P2P" -I"$HERE" -I"$INC" "$HERE/ref_cxl_p2p_glue.c" -o "$OUT/libref_cxl_p2p.so"
+    echo "build_ref: built $OUT/libref_cxl_p2p.so"
+fi
+
 # ---------------- PMM leg: the eviction order (pick_root_chunk_to_evict and the list moves), verbatim ----------------
 if [ -f "$HERE/ref_pmm_glue.c" ]; then
     pin uvm_pmm_gpu.c 579fbaf9e0b9de07

@@ -7,10 +7,11 @@
  *   RmP2PCxlDmaRequest       :516-677  (checks :535-565, 4 GB clamp :617-622)
  * Status codes are the reference's (kernel-open/common/inc/nvstatuscodes.h).
  *
- * Pinning: PARITY UNPINNED by compiled reference code -- p2p_cxl.c is RM code (memdesc, memmgr, OBJGPU) and does
- * not build outside the RM tree.  The vectors the reference holds for this surface are the byte pattern and the
- * register -> DMA -> verify -> unregister flow of tests/cxl_p2p_test.c:467-513, 532-632, which
- * tests/test_gpu_cxl_p2p.py replays; the functions below restate the checks line by line.
+ * Pinning: by the reference's own file compiled UNMODIFIED (oracle/_ref/libref_cxl_p2p.so, ref_cxl_p2p_glue.c: RM
+ * objects replaced by stand-ins, the kernel's page pinning by its page arithmetic): tests/test_oracle_cxl_p2p.py
+ * compares every status code, the page geometry of a registration, the window of RmP2PGetCxlPages and the bytes of a
+ * DMA request (4 GB clamp) on directed and random arguments.  The byte pattern and the register -> DMA -> verify ->
+ * unregister flow of tests/cxl_p2p_test.c:467-513, 532-632 are replayed on the GPU by tests/test_gpu_cxl_p2p.py.
  */
 #include <stdint.h>
 

@@ -522,6 +522,51 @@ def access_counter_numbers(ctx, lib, P, rank):
     return out
 
 
+def nonreplayable_numbers(ctx, lib, P, rank):
+    """Non-replayable faults on the 64 GB table shape, bounded: 262144 copy-engine faults (uniform pages, every page on
+    the CPU tiers) parsed, translated and serviced one by one in buffer order per va_block.  Device-resident shadow
+    buffer, CUDA events on the library's stream."""
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    import nonreplaylib as NR
+    from uvmtier import tracegen as TG
+    from uvmtier.blockstate import HostBlockState, make_layout
+    n, B, n_spaces, blocks = 262144, 256, 4, 8192
+    tbl = TG.instance_ptr_table(n_spaces)
+    ctx.fault_buffer_init(TG.gpu_params(B), tbl)
+    lay = dict(va_base=TG.VA_BASE, blocks_per_space=blocks, n_spaces=n_spaces, gpu_id=1)
+    layout = make_layout(lay)
+    pk = NR.shadow_buffer(n, 13 + rank, lay, tbl, fatal_frac=0.0, stale_frac=0.0, outside_frac=0.0)
+    st = HostBlockState(n_spaces * blocks)
+    st.cpu_resident0[:] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    ds, ds0 = ctx.block_state_alloc(layout), ctx.block_state_alloc(layout)
+    ds0.upload(st)
+    d_pk = ctx.to_device(pk)
+    run_cap = 1 << 22
+    d_flags, d_svc, d_runs, d_cnt = ctx.alloc(n * 2), ctx.alloc(n * 96), ctx.alloc(run_cap * 8), ctx.alloc(8)
+    state_bytes = n_spaces * blocks * (6 * 64 + 7)
+    ms, times = ctypes.c_float(0), []
+    for it in range(6):
+        lib.uvmtier_memcpy_d2d_async(ctx.handle, ctypes.c_void_p(ds.ptrs.gpu_resident), ctypes.c_void_p(ds0.ptrs.gpu_resident),
+                                     ctypes.c_size_t(state_bytes))
+        lib.uvmtier_event_record(ctx.handle, 940)
+        st1 = lib.uvmtier_service_non_replayable_faults_device(ctx.handle, P(d_pk), ctypes.c_uint32(n), P(layout), ctypes.byref(ds.ptrs), None,
+                                                               P(d_flags), P(d_svc), P(d_runs), ctypes.c_uint32(run_cap), P(d_cnt))
+        lib.uvmtier_event_record(ctx.handle, 941)
+        assert st1 == 0, hex(st1)
+        lib.uvmtier_event_elapsed_ms(ctx.handle, 940, 941, ctypes.byref(ms))
+        if it >= 2:
+            times.append(ms.value)
+    cnt = ctx.from_device(d_cnt, 2, "<u4")
+    flags = ctx.from_device(d_flags, n, "<u2")
+    m = float(np.mean(times))
+    out = {"faults": n, "va_blocks": n_spaces * blocks, "ms": m, "faults_per_s": n / (m * 1e-3), "serviced": int((flags & 1).sum()),
+           "copy_runs": int(cnt[0]), "what": "copy-engine faults, every page on host DRAM, serviced in buffer order per va_block"}
+    for p_ in (d_pk, d_flags, d_svc, d_runs, d_cnt):
+        ctx.free(p_)
+    ds.free(); ds0.free()
+    return out
+
+
 def thrashing_numbers(ctx, lib, P, rank):
     """The thrashing detector on the 64 GB table shape: 32768 va_blocks x 32 events of 16 pages each per call, two
     processors taking turns inside the window (every page of a region is read, stamped and written back).  Device
@@ -922,6 +967,9 @@ def main():
     thrash = None
     if not args.no_migration and rank == 0:
         thrash = thrashing_numbers(ctx, lib, P, rank)
+    nonrep = None
+    if not args.no_migration and rank == 0:
+        nonrep = nonreplayable_numbers(ctx, lib, P, rank)
     other = None
     if not args.no_migration and world == 1 and args.trace == "uniform":
         other = {t: other_trace_numbers(ctx, lib, P, t) for t in ("stream", "hotset")}
@@ -972,6 +1020,7 @@ def main():
         "oversubscription": oversub,
         "access_counters": access,
         "thrashing": thrash,
+        "non_replayable_faults": nonrep,
         "other_traces": other,
         "wall_s_timed_region": wall1 - wall0,
     }

@@ -772,6 +772,35 @@ NV_STATUS uvmtier_thrashing_note_events_device(uvmtier_ctx_t *ctx, uvmtier_thras
                                                const uvmtier_perf_event_t *d_events, uint32_t *d_counters);
 
 /* ------------------------------------------------------------------------------------------ */
+/* (1g) Non-replayable faults -- UVM/uvm_gpu_non_replayable_faults.c                           */
+/* ------------------------------------------------------------------------------------------ */
+/* The other fault front end on the same back end: faults of engines that cannot replay (copy engines, host) arrive
+ * in a buffer RM owns; UVM receives a copy of the pending packets (the "shadow buffer",
+ * fetch_non_replayable_fault_buffer_entries :179-236), parses them with the same packet parser
+ * (uvm_hal_volta_fault_buffer_parse_non_replayable_entry, UVM/uvm_volta_fault_buffer.c:436-445) and services them
+ * one by one in buffer order (uvm_parent_gpu_service_non_replayable_fault_buffer :777-802 -> service_fault :757 ->
+ * service_fault_once :606-712 -> service_managed_fault_in_block_locked :345-445): no coalescing, no sort, no duplicate
+ * or already-authorised shortcut -- logical permission check, new_residency = the one page, uvm_va_block_service_locked.
+ *
+ *   d_shadow_buffer   n_faults packets (NVC369 layout; the VALID bit is not looked at, nothing is written back)
+ *   d_entries         optional [n_faults] parsed entries (num_instances 1, access_type_mask = the one bit)
+ *   d_entry_flags     [ceil(n_faults / B) * B], B = max_batch_size of uvmtier_fault_buffer_init: per fault
+ *                     UVMTIER_SF_SERVICED | access type, or UVMTIER_SF_FATAL | reason (UvmEventFatalReason: 1 address
+ *                     in no va_range, :570-574 with no ATS; 2 logical permissions, :383-387; 3 fatal fault type,
+ *                     :221-224), or 0 for a fault whose channel is gone (:623-632, dropped)
+ *   d_service         [ceil(n_faults / B) * B] record i belongs to fault i (all zero for dropped and fatal-type faults)
+ *   d_runs / d_counters   as uvmtier_service_fault_batches_device
+ * Faults on one va_block are applied in buffer order; different va_blocks run in parallel.  What the reference
+ * does after servicing -- clearing the channel's faulted bit (:328-343) or killing the channel (:500-533) -- is
+ * hardware control and stays with the caller, which reads d_entry_flags. */
+NV_STATUS uvmtier_service_non_replayable_faults_device(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *d_shadow_buffer,
+                                                       uint32_t n_faults, const uvmtier_va_layout_t *layout,
+                                                       const uvmtier_block_state_t *state,
+                                                       uvmtier_fault_buffer_entry_t *d_entries, uint16_t *d_entry_flags,
+                                                       uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
+                                                       uint32_t run_cap, uint32_t *d_counters);
+
+/* ------------------------------------------------------------------------------------------ */
 /* (2) Prefetch hint -- UVM/uvm_perf_prefetch.c                                                */
 /* ------------------------------------------------------------------------------------------ */
 
@@ -1023,6 +1052,11 @@ typedef struct {
                                          const uvmtier_fault_group_t *, uvmtier_fault_batch_t *, const uvmtier_va_layout_t *,
                                          const uvmtier_block_state_t *, uvmtier_service_group_t *, uvmtier_copy_run_t *,
                                          uint32_t run_cap, uint32_t *d_counters);
+    /* uvm_parent_gpu_service_non_replayable_fault_buffer (UVM/uvm_gpu_non_replayable_faults.c:777-802) */
+    NV_STATUS (*service_non_replayable_faults)(uvmtier_ctx_t *, const uvmtier_fault_packet_t *d_shadow_buffer, uint32_t n_faults,
+                                               const uvmtier_va_layout_t *, const uvmtier_block_state_t *,
+                                               uvmtier_fault_buffer_entry_t *d_entries, uint16_t *d_entry_flags,
+                                               uvmtier_service_group_t *, uvmtier_copy_run_t *, uint32_t run_cap, uint32_t *d_counters);
 } uvmtier_ops_t;
 
 /* The B200 implementation of every slot. */

@@ -60,7 +60,7 @@ NV_STATUS uvmtier_service_pass_chunk(struct uvmtier_ctx *ctx, uint32_t n_batches
                                      const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
                                      const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
                                      uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t run_cap,
-                                     uint32_t *d_counters, uint32_t batch_base);
+                                     uint32_t *d_counters, uint32_t batch_base, bool non_replayable = false);
 
 struct uvmtier_ctx {
     int device;

@@ -311,4 +311,5 @@ extern "C" const uvmtier_ops_t uvmtier_gpu_ops = {
     uvmtier_service_replayable_faults_streamed,
     uvmtier_access_counters_fetch_preprocess_device,
     uvmtier_access_counters_service_device,
+    uvmtier_service_non_replayable_faults_device,
 };

@@ -125,6 +125,90 @@ k_fault_parse(const uvmtier_fault_packet_t *__restrict__ packets, size_t n, uint
 }
 
 // ------------------------------------------------------------------------------------------------
+// Non-replayable faults, front end (UVM/uvm_gpu_non_replayable_faults.c): fetch_non_replayable_fault_buffer_entries
+// (:179-236) parses the shadow-buffer copy -- the same 32-byte packet, no valid bit to clear, one instance per entry, no
+// coalescing -- and service_fault_once (:606-712) looks every entry's channel up and services the entries one after
+// the other, in buffer order.  Here: one thread per packet; the entry becomes a va_block run of its own, in the layout
+// the servicing pass takes (run g of "batch" b is entry b * B + g, so the pass applies the runs of a va_block in
+// buffer order).  A fatal fault type or an instance pointer that does not translate (:623-632: the channel is gone,
+// the entry is dropped) makes a run the pass skips (flags bit 0).
+__global__ void __launch_bounds__(256)
+k_nonreplayable_prepare(const uvmtier_fault_packet_t *__restrict__ packets, uint32_t n, uint32_t B, uint32_t utlb_per_gpc,
+                        uint32_t va_bits, const uvmtier_instance_ptr_entry_t *__restrict__ tbl, uint32_t tbl_n,
+                        uvmtier_ordered_fault_t *__restrict__ ordered, uvmtier_fault_group_t *__restrict__ groups,
+                        uvmtier_fault_batch_t *__restrict__ batches, uint16_t *__restrict__ entry_flags,
+                        uvmtier_fault_buffer_entry_t *__restrict__ entries)
+{
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint4 a = ld_stream_v4((const uint4 *)&packets[i]);
+        const uint4 b = ld_stream_v4((const uint4 *)&packets[i] + 1);
+        fault_fields f;
+        fd_decode(a.x, a.y, a.z, a.w, b.x, b.y, b.z, b.w, utlb_per_gpc, va_bits, &f);
+        const bool fatal = (f.flags & UVMTIER_FE_FATAL) != 0;
+        int ctx = -1;
+        for (uint32_t k = 0; k < tbl_n; k++) {
+            const uvmtier_instance_ptr_entry_t r = tbl[k];
+            if (r.instance_ptr == f.inst_address && r.aperture == f.inst_aperture && (r.ve_id == UVMTIER_VE_ID_ANY || r.ve_id == f.ve_id)) {
+                ctx = (int)k;
+                break;
+            }
+        }
+        uvmtier_ordered_fault_t o;
+        o.fault_address = f.fault_address;
+        o.fault_index = (uint16_t)(i % B);
+        o.ctx = (uint16_t)(ctx < 0 ? 0 : ctx);
+        o.num_instances = 1;                                                        // :215
+        o.access_type_mask = (uint8_t)(1u << f.access_type);                        // :216
+        o.fault_access_type = (uint8_t)(f.access_type | (fatal ? UVMTIER_OF_FATAL : 0u));
+        ordered[i] = o;
+        uvmtier_fault_group_t g;
+        g.block_start = f.fault_address & ~((uint64_t)UVMTIER_VA_BLOCK_SIZE - 1);
+        g.ctx = o.ctx;
+        g.first_fault_index = o.fault_index;
+        g.block_faults = 1;
+        g.flags = (fatal || ctx < 0) ? 1u : 0u;
+        groups[i] = g;
+        // a fatal fault type is reported as such (fatal_reason = UvmEventFatalReasonInvalidFaultType, :221-224) -- if its
+        // channel still exists; a dropped entry reports nothing
+        if (fatal && ctx >= 0)
+            entry_flags[i] = (uint16_t)(UVMTIER_SF_FATAL | (3u << UVMTIER_SF_REASON_SHIFT));
+        if (i % B == 0) {
+            uvmtier_fault_batch_t bt;
+            const uint32_t left = n - i;
+            bt.num_cached_faults = bt.num_coalesced_faults = left < B ? left : B;
+            bt.is_single_instance_ptr = 0;
+            bt.max_utlb_id = 0;
+            bt.status = NV_OK;
+            bt.num_duplicate_faults = 0;
+            bt.num_invalid_prefetch_faults = 0;
+            bt.num_block_groups = bt.num_cached_faults;
+            batches[i / B] = bt;
+        }
+        if (entries) {
+            uvmtier_fault_buffer_entry_t e;
+            e.fault_address = f.fault_address;
+            e.timestamp = f.timestamp;
+            e.instance_ptr_address = f.inst_address;
+            e.client_id = (uint16_t)f.client_id;
+            e.mmu_engine_id = (uint16_t)f.engine_id;
+            e.utlb_id = (uint16_t)f.utlb_id;
+            e.num_instances = 1;
+            e.instance_ptr_aperture = (uint8_t)f.inst_aperture;
+            e.fault_type = (uint8_t)f.fault_type;
+            e.fault_access_type = (uint8_t)f.access_type;
+            e.client_type = (uint8_t)f.client_type;
+            e.mmu_engine_type = (uint8_t)f.engine_type;
+            e.gpc_id = (uint8_t)f.gpc_id;
+            e.ve_id = (uint8_t)f.ve_id;
+            e.flags = (uint8_t)f.flags;
+            e.access_type_mask = (uint8_t)(1u << f.access_type);
+            for (int k = 0; k < 7; k++) e.pad[k] = 0;
+            entries[i] = e;
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
 // One CTA per batch.  blockDim.x = T = power of two >= B, 32 <= T <= 1024.
 __global__ void __launch_bounds__(kFaultMaxThreads)
 k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__ ring,

@@ -274,6 +274,49 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches(uvmtier_ctx_t *ctx, uvmtier_fau
 
 } // extern "C"
 
+// Non-replayable faults (include/uvmtier.h section 1g): parse + translate, one run per fault, then the servicing pass
+// without the "already authorised" shortcut.
+extern "C" NV_STATUS uvmtier_service_non_replayable_faults_device(uvmtier_ctx_t *ctx, const uvmtier_fault_packet_t *d_shadow_buffer,
+                                                                  uint32_t n_faults, const uvmtier_va_layout_t *lay,
+                                                                  const uvmtier_block_state_t *state,
+                                                                  uvmtier_fault_buffer_entry_t *d_entries, uint16_t *d_entry_flags,
+                                                                  uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs,
+                                                                  uint32_t run_cap, uint32_t *d_counters)
+{
+    if (!ctx || !lay || !state)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->faults)
+        return NV_ERR_INVALID_STATE;
+    if (!n_faults)
+        return NV_OK;
+    if (!d_shadow_buffer)
+        return NV_ERR_INVALID_ARGUMENT;
+    const uint32_t B = ctx->faults->gp.max_batch_size;
+    const uint32_t nb = (n_faults + B - 1) / B;
+    const size_t total = (size_t)nb * B;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    // working space: the sorted view the servicing pass takes (here in buffer order) and its run and batch arrays
+    const size_t ob = uvmtier_align_up(total * sizeof(uvmtier_ordered_fault_t), 256), gb = uvmtier_align_up(total * sizeof(uvmtier_fault_group_t), 256);
+    NV_STATUS st = uvmtier_stage_reserve(ctx, ob + gb + (size_t)nb * sizeof(uvmtier_fault_batch_t), 0);
+    if (st != NV_OK)
+        return st;
+    uvmtier_ordered_fault_t *d_ord = (uvmtier_ordered_fault_t *)ctx->d_stage;
+    uvmtier_fault_group_t *d_grp = (uvmtier_fault_group_t *)((char *)ctx->d_stage + ob);
+    uvmtier_fault_batch_t *d_bat = (uvmtier_fault_batch_t *)((char *)ctx->d_stage + ob + gb);
+    if (!d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs) || nb > 65536u)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaMemsetAsync(d_counters, 0, 2 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, total * sizeof(uint16_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d_service, 0, total * sizeof(uvmtier_service_group_t), ctx->stream));   // dropped entries: all zero
+    size_t grid = (n_faults + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_nonreplayable_prepare, (int)grid, 256, 0, ctx->stream, d_shadow_buffer, n_faults, B,
+                   ctx->faults->gp.utlb_per_gpc_count, ctx->faults->gp.va_bits, ctx->faults->d_table, ctx->faults->n_rows, d_ord, d_grp,
+                   d_bat, d_entry_flags, d_entries);
+    return uvmtier_service_pass_chunk(ctx, nb, d_ord, d_grp, d_bat, lay, state, d_entry_flags, d_service, d_runs, run_cap, d_counters, 0, true);
+}
+
 // ------------------------------------------------------------------------------------------------
 // Access-counter notifications, front end (include/uvmtier.h section 1e).
 extern "C" NV_STATUS uvmtier_access_counters_init(uvmtier_ctx_t *ctx, const uvmtier_access_counter_config_t *cfg)

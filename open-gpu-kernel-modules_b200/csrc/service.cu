@@ -59,7 +59,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const uvmtier_va_layout_t *lay,
                               const uvmtier_block_state_t *state, uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
                               uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters, uint32_t batch_base = 0,
-                              bool zero_outputs = true)
+                              bool zero_outputs = true, bool non_replayable = false)
 {
     const uint32_t B = ctx->faults->gp.max_batch_size;
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
@@ -80,6 +80,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     prm.run_cap = run_cap;
     prm.B_shift = svc_log2_or_none(B);
     prm.batch_base = batch_base;
+    prm.non_replayable = non_replayable ? 1u : 0u;
 
     block_state_ptrs bs;
     bs.gpu_resident = (uint32_t *)state->gpu_resident;
@@ -308,7 +309,7 @@ NV_STATUS uvmtier_service_pass_chunk(uvmtier_ctx_t *ctx, uint32_t n_batches, con
                                      const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
                                      const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state, uint16_t *d_entry_flags,
                                      uvmtier_service_group_t *d_service, uvmtier_copy_run_t *d_runs, uint32_t run_cap,
-                                     uint32_t *d_counters, uint32_t batch_base)
+                                     uint32_t *d_counters, uint32_t batch_base, bool non_replayable)
 {
     const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
                                             d_runs, run_cap, d_counters);
@@ -320,7 +321,7 @@ NV_STATUS uvmtier_service_pass_chunk(uvmtier_ctx_t *ctx, uint32_t n_batches, con
     if (st != NV_OK)
         return st;
     return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service, d_runs,
-                        run_cap, d_counters, batch_base, false);
+                        run_cap, d_counters, batch_base, false, non_replayable);
 }
 
 // Access-counter notifications, servicing (include/uvmtier.h section 1e): the list front end of the fault path

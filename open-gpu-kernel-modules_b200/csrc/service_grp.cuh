@@ -312,6 +312,8 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
             uint32_t auth = ((a0 >> sh) & 1u) | (((a1 >> sh) & 1u) << 1) | (((a2 >> sh) & 1u) << 2);
             if (G > 1)
                 auth = __shfl_sync(kFullWarp, auth, gb + owner);
+            if (prm.non_replayable)
+                auth = 0;
             const svc_entry_eval ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, state, logical, auth);
             if (on) {
                 dup_sum += dup ? num_instances : num_instances - 1u;  // :1200-1203
@@ -323,7 +325,7 @@ k_service_blocks_grp(service_kparams prm, const uvmtier_ordered_fault_t *__restr
                     page_faults++;
                 }
                 if (gl == 0)
-                    entry_flags[base + first + i] = (uint16_t)ev.flags;
+                    entry_flags[base + first + i] = (uint16_t)(prm.non_replayable ? ev.flags & ~(1u << UVMTIER_SF_CANCEL_SHIFT) : ev.flags);
                 state = ev.state;
                 prev_page = page;
             }

@@ -41,6 +41,8 @@ struct service_kparams {
     uint32_t run_cap;
     uint32_t B_shift;                          // log2(B) when B is a power of two, else 0xffffffff
     uint32_t batch_base;                       // batch number of d_batches[0] (a pass over one chunk of a longer trace)
+    uint32_t non_replayable;                   // servicing non-replayable faults (UVM/uvm_gpu_non_replayable_faults.c:345-445):
+                                               // no "already authorised" shortcut, no cancel mode in the flags
 };
 
 __host__ __device__ __forceinline__ uint32_t svc_log2_or_none(uint32_t B)
@@ -229,6 +231,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
     const int lane = threadIdx.x & 31, l = lane & 15, warp = threadIdx.x >> 5;
     const uint32_t n_warps = gridDim.x * (kSvcThreads / 32);
     const uint32_t n_heavy = heavy[0];
+    const uint32_t flag_mask = prm.non_replayable ? ~(1u << UVMTIER_SF_CANCEL_SHIFT) : ~0u;
     const uint4 *oraw = (const uint4 *)ordered, *graw = (const uint4 *)groups;
     for (uint32_t q = blockIdx.x * (kSvcThreads / 32) + warp; q < n_heavy; q += n_warps) {
         const uint32_t slot = heavy[1u + q];
@@ -291,10 +294,10 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                     const int wl = (int)((page >> 5) & 15u);
                     const uint32_t w0 = __shfl_sync(HW_FULL, pte0, wl), w1 = __shfl_sync(HW_FULL, pte1, wl), w2 = __shfl_sync(HW_FULL, pte2, wl);
                     const uint32_t sh = page & 31u;
-                    const uint32_t auth = ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
+                    const uint32_t auth = prm.non_replayable ? 0u : ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
                     const svc_entry_eval ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, state, logical, auth);
                     if (on) {
-                        entry_flags[base_s + first_s + i] = (uint16_t)ev.flags;   // rewritten later if the run is not final
+                        entry_flags[base_s + first_s + i] = (uint16_t)(ev.flags & flag_mask);   // rewritten later if the run is not final
                         dsum += dup ? num_instances : num_instances - 1u;
                         isum += ev.ip_add;
                         needs_service |= ev.serviced;
@@ -349,7 +352,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 const int wl = (int)((page >> 5) & 15u);
                 const uint32_t w0 = __shfl_sync(HW_FULL, pte0, wl), w1 = __shfl_sync(HW_FULL, pte1, wl), w2 = __shfl_sync(HW_FULL, pte2, wl);
                 const uint32_t sh = page & 31u;
-                const uint32_t auth = ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
+                const uint32_t auth = prm.non_replayable ? 0u : ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
                 svc_entry_eval ev;
                 uint32_t state = 0;
                 for (;;) {
@@ -364,7 +367,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                         break;
                 }
                 if (valid) {
-                    entry_flags[base + first + i] = (uint16_t)ev.flags;
+                    entry_flags[base + first + i] = (uint16_t)(ev.flags & flag_mask);
                     if (ev.serviced)
                         atomicOr(&s_newres[warp][page >> 5], 1u << sh);
                 }
@@ -511,7 +514,7 @@ k_service_unmapped(service_kparams prm, const uvmtier_ordered_fault_t *__restric
             const uint32_t acc = e.fault_access_type & 7u;
             uint32_t fl = 0;
             bool dup = false;
-            if (s > 0) {
+            if (s > 0 && !prm.non_replayable) {                           // (non-replayable faults know no duplicates)
                 const uvmtier_ordered_fault_t pe = ordered[base + s - 1];
                 dup = tbl[pe.ctx].va_space == va_space && pe.fault_address == e.fault_address;
             }

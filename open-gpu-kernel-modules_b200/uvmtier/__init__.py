@@ -469,6 +469,32 @@ class Context:
             for p_ in devs:
                 self.free(p_)
 
+    # ---- (1g) non-replayable faults ----
+    def service_non_replayable_faults(self, packets, layout, dstate, run_cap=1 << 20):
+        """uvmtier_service_non_replayable_faults_device on a host array of packets (the shadow-buffer copy).  Downloads
+        entries, per-fault flags, records, copy runs, the run count and the state."""
+        from .blockstate import COPY_RUN_DT, SERVICE_GROUP_DT
+        from .layouts import FAULT_ENTRY_DT
+        n = len(packets)
+        B = self._fault_B
+        total = (n + B - 1) // B * B
+        d_pk = self.to_device(np.ascontiguousarray(packets))
+        d_ent, d_flags, d_svc = self.alloc(max(n, 1) * 48), self.alloc(max(total, 1) * 2), self.alloc(max(total, 1) * 96)
+        d_runs, d_cnt = self.alloc(max(run_cap, 1) * 8), self.alloc(8)
+        try:
+            _check(lib().uvmtier_service_non_replayable_faults_device(self._h, P(d_pk), ctypes.c_uint32(n), P(layout),
+                                                                      ctypes.byref(dstate.ptrs), P(d_ent), P(d_flags), P(d_svc), P(d_runs),
+                                                                      ctypes.c_uint32(run_cap), P(d_cnt)),
+                   "uvmtier_service_non_replayable_faults_device")
+            self.synchronize()
+            cnt = self.from_device(d_cnt, 2, "<u4")
+            return dict(entries=self.from_device(d_ent, n, FAULT_ENTRY_DT), flags=self.from_device(d_flags, total, "<u2"),
+                        service=self.from_device(d_svc, total, SERVICE_GROUP_DT), runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT),
+                        n_runs=int(cnt[0]), state=dstate.download())
+        finally:
+            for p_ in (d_pk, d_ent, d_flags, d_svc, d_runs, d_cnt):
+                self.free(p_)
+
     # ---- (1c) make_resident ----
     def make_resident(self, requests, page_masks, prefetch_masks, layout, dstate, run_cap=1 << 18, execute=False):
         """uvmtier_make_resident_device on host arrays (requests: MAKE_RESIDENT_REQ_DT; masks: uint64 [n, 8] or

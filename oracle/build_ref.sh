@@ -77,6 +77,17 @@ if [ -f "$HERE/ref_service_glue.c" ]; then
     echo "build_ref: built $OUT/libref_service.so"
 fi
 
+# ---------------- non-replayable faults: service_managed_fault_in_block_locked, verbatim, on the service leg's shims ----------------
+if [ -f "$HERE/ref_nonreplayable_glue.c" ]; then
+    got="$(sha256sum "$UVM/uvm_gpu_non_replayable_faults.c" | cut -c1-16)"
+    if [ "$got" != "588e72e5e3163f2e" ]; then echo "build_ref: uvm_gpu_non_replayable_faults.c sha256 prefix $got != pinned 588e72e5e3163f2e" >&2; exit 1; fi
+    sed -n '345,445p' "$UVM/uvm_gpu_non_replayable_faults.c" > "$TMP/x_nonreplayable.h"
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_nonreplayable_glue.c" "$HERE/ref_faults_blackwell.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        -o "$OUT/libref_nonreplayable.so"
+    echo "build_ref: built $OUT/libref_nonreplayable.so"
+fi
+
 # ---------------- residency leg: uvm_va_block_make_resident and its mask algebra, verbatim ----------------
 if [ -f "$HERE/ref_resident_glue.c" ]; then
     sed -n '36,80p' "$UVM/uvm_va_block_types.h" > "$TMP/x_va_block_types.h"

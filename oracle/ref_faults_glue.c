@@ -56,12 +56,14 @@ struct uvm_fault_service_batch_context_struct {
     uvm_fault_buffer_entry_t *last_fault;
 };
 
+typedef struct { NvU32 batch_id; } uvm_non_replayable_fault_buffer_t;      /* the one field the non-replayable leg touches */
 typedef struct uvm_replayable_fault_buffer_struct {
     NvU32 max_faults;
     NvU32 cached_get;
     NvU32 cached_put;
     NvU32 utlb_count;
     struct uvm_service_block_context_struct *block_service_context_ptr;   /* used by ref_service_glue.c only */
+    uvm_non_replayable_fault_buffer_t *non_replayable_ptr;                /* used by ref_nonreplayable_glue.c only */
 } uvm_replayable_fault_buffer_t;
 
 typedef struct {

@@ -54,6 +54,16 @@ def run():
         R.assert_equal(R.run_oracle(orc, rq, pm, pf, st1), mr, "smoke make_resident")
         ds.free()
 
+        # (1g) non-replayable faults: parse + translate + one-by-one servicing of a shadow buffer
+        import nonreplaylib as NR
+        ctx.fault_buffer_init(gp, tbl)
+        nrpk = NR.shadow_buffer(1500, 8, lay, tbl)
+        nrds = ctx.block_state_alloc(layout)
+        nrds.upload(st0)
+        nrgot = ctx.service_non_replayable_faults(nrpk, layout, nrds)
+        nrds.free()
+        NR.assert_equal(NR.run_checker(orc, "oracle", nrpk, gp, tbl, layout, st0), nrgot, "smoke non-replayable faults")
+
         # (1e) access-counter notifications: fetch + sort + expansion + servicing on the same table shape
         import aclib as A
         from test_oracle_access_counters import notifications, state_with_mappings
@@ -95,5 +105,5 @@ def run():
 
         launches = uvmtier.kernel_launch_count() - before
         assert launches >= 10, "smoke: CUDA kernels were not launched"
-    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, make_resident, access counters, thrashing, migration)" %
+    print("smoke ok: %s, %d kernel launches (prefetch, fault batches, service, make_resident, non-replayable faults, access counters, thrashing, migration)" %
           (uvmtier.lib().uvmtier_version().decode(), launches))

@@ -350,7 +350,19 @@ typedef struct {
     uint16_t *preferred_location;
     uvmtier_page_mask_t *gpu_evicted;
     uvmtier_page_mask_t *read_duplicated;
+    /* Other GPUs of the box that hold pages of these va_blocks: their gpu_state->resident masks (the reference keeps
+     * one uvm_va_block_gpu_state_t per GPU in the va_block, UVM/uvm_va_block.h:101-230, 304-310), in ascending
+     * uvm_gpu_id_t, which is also "closest first" among GPUs (uvm_processor_mask_find_closest_id, UVM/uvm_va_space.c:
+     * 1879-1924).  Bit k of peer_direct: this GPU copies from peer k directly (block_get_can_copy_from_mask); clear:
+     * the pages only such a GPU holds are staged through CPU pages (UVM/uvm_va_block.c:3140-3170, :4754-4829).  Peer
+     * k's HBM arena is tier UVMTIER_TIER_PEER0 + k of the context that executes the copy runs.  n_peers = 0 (what
+     * uvmtier_block_state_alloc leaves): a one-GPU table. */
+    uvmtier_page_mask_t *peer_resident[4];
+    uint16_t peer_gpu_id[4];
+    uint32_t n_peers;
+    uint32_t peer_direct;
 } uvmtier_block_state_t;
+#define UVMTIER_MAX_PEER_GPUS 4u
 
 #define UVMTIER_SF_SERVICED         0x0001u /* page added to new_residency (:1560-1579) */
 #define UVMTIER_SF_DUPLICATE        0x0002u /* check_fault_entry_duplicate (:1180-1191) */
@@ -384,6 +396,7 @@ typedef struct {
 #define UVMTIER_RUN_SRC_DRAM 0u
 #define UVMTIER_RUN_SRC_CXL  1u
 #define UVMTIER_RUN_SRC_HBM  2u
+#define UVMTIER_RUN_SRC_PEER0 3u        /* 3 + k: HBM of peer GPU k of the state table (tier UVMTIER_TIER_PEER0 + k) */
 #define UVMTIER_RUN_SRC_ZERO 7u
 #define UVMTIER_RUN_DST_HBM  0u
 #define UVMTIER_RUN_DST_DRAM 1u
@@ -401,6 +414,14 @@ typedef struct {
  * {UVMTIER_ID_INVALID, 0}) / frees the state table of n_spaces * blocks_per_space slots. */
 NV_STATUS uvmtier_block_state_alloc(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uvmtier_block_state_t *out);
 NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *state);
+/* Adds another GPU to a table made by uvmtier_block_state_alloc: a zeroed resident mask array (freed with the table)
+ * for the GPU with id peer_gpu_id, which must be above the ids of the peers added before and differ from
+ * layout->gpu_id; direct != 0: this GPU can copy from it directly.  NV_ERR_INSUFFICIENT_RESOURCES beyond
+ * UVMTIER_MAX_PEER_GPUS.  The servicing passes (sections 1b, 1e, 1g) take one-GPU tables only and answer
+ * NV_ERR_NOT_SUPPORTED otherwise: in the sharded set-up every GPU services the faults on the va_blocks it
+ * owns; pages that sit on another GPU are moved with uvmtier_make_resident_device. */
+NV_STATUS uvmtier_block_state_add_peer(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uvmtier_block_state_t *state,
+                                       uint32_t peer_gpu_id, int direct);
 /* Adds a zeroed read_duplicated mask array to a table made by uvmtier_block_state_alloc (freed with it). */
 NV_STATUS uvmtier_block_state_enable_read_duplication(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout,
                                                       uvmtier_block_state_t *state);
@@ -530,16 +551,19 @@ typedef struct {
     uint32_t run_offset;             /* first copy run of this request in the run array */
     uint16_t run_count;
     uint16_t unmapped;               /* GPU mappings removed (pages the GPU had mapped that left it) */
-    uint32_t reserved[3];
+    uint16_t migrated_peer[4];       /* pages copied from peer GPU k of the table */
+    uint32_t reserved;
     uvmtier_page_mask_t pages_migrated;
     uvmtier_page_mask_t pages_changed_residency;
 } uvmtier_make_resident_result_t;    /* 160 bytes */
 
 /* Batched uvm_va_block_make_resident (= _copy + _finish, :5086-5114) on the flat state table: residency algebra
- * (block_copy_resident_pages :4660-4847: copy = page_mask & ~resident(dest); GPU destination takes from CPU node
- * 0 then node 1; CPU destination takes from the other CPU node first, then from the GPU), first touch
+ * (block_copy_resident_pages :4660-4847: copy = page_mask & ~resident(dest); GPU destination takes from the other
+ * GPUs of the table it can copy from directly, in ascending id, then from CPU node 0, then node 1, and what only a GPU
+ * without direct access holds goes through CPU pages on node 0 in two runs; CPU destination takes from the other CPU
+ * node first, then from the GPUs in ascending id, this one among them), first touch
  * (:4581-4619), state update (:4990-5040: resident masks, gpu_evicted set on EVICTION / cleared on return),
- * clearing of every other residency (break_read_duplication_in_region :4538-4579), removal of the GPU's mappings
+ * clearing of every other residency, the other GPUs' included (break_read_duplication_in_region :4538-4579), removal of the GPU's mappings
  * of pages that leave it (:4919-4926), and the copy list: runs d_runs[run_offset .. run_offset + run_count) per
  * request (uvmtier_copy_runs_device executes them).  Requests of one call must name distinct slots (a va_block
  * is locked for the duration of a make_resident; two requests on one block in the same call would race).

@@ -387,9 +387,14 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
     }
     UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, bases, d_pair_cursor, ts->d_lists,
                    ts->list_cap);
-    static const uint32_t src_tier_of[4] = {UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL, UVMTIER_TIER_HBM, 0};
+    static const uint32_t src_tier_of[8] = {UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL, UVMTIER_TIER_HBM, UVMTIER_TIER_PEER0,
+                                            UVMTIER_TIER_PEER0 + 1, UVMTIER_TIER_PEER0 + 2, UVMTIER_TIER_PEER0 + 3, 0};
     static const uint32_t dst_tier_of[3] = {UVMTIER_TIER_HBM, UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL};
-    for (uint32_t pair = 0; pair < kRunPairs; pair++) {
+    // Sources in this order: the peer GPUs first -- a page staged through DRAM (peer -> DRAM, then DRAM -> HBM,
+    // UVM/uvm_va_block.c:4754-4829) needs its first hop done before the DRAM -> HBM pair runs -- then DRAM, CXL, HBM, zero fill.
+    static const uint32_t src_order[8] = {3, 4, 5, 6, 0, 1, 2, 7};
+    for (uint32_t step = 0; step < kRunPairs; step++) {
+        const uint32_t pair = src_order[step / 3] * 3 + step % 3;
         const uint32_t n = ts->h_list_count[pair];
         if (!n)
             continue;
@@ -398,7 +403,7 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
             return NV_ERR_INVALID_STATE;
         uint8_t *dst_base = (uint8_t *)ts->t[dst_tier].info.device_ptr;
         const uint64_t *list = ts->d_lists + bases.base[pair];
-        if (src == 3) {                                   // first touch: zero fill at the destination
+        if (src == UVMTIER_RUN_SRC_ZERO) {                // first touch: zero fill at the destination
             const uint32_t zg = n < (uint32_t)ctx->sm_count * 16 ? n : (uint32_t)ctx->sm_count * 16;
             UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, dst_base, list, (uint64_t)n, 1u);
             continue;

@@ -206,13 +206,13 @@ __global__ void __launch_bounds__(256) k_zero_pages(uint8_t *base, const uint64_
     }
 }
 
-// Copy runs are executed per (source, destination) pair.  pair = src_code * 3 + dst, src_code 0 DRAM, 1 CXL, 2 HBM,
-// 3 zero fill; dst 0 HBM, 1 DRAM, 2 CXL (UVMTIER_RUN_SRC_* / UVMTIER_RUN_DST_*).
-constexpr uint32_t kRunPairs = 12;
+// Copy runs are executed per (source, destination) pair.  pair = src * 3 + dst, src 0 DRAM, 1 CXL, 2 HBM, 3..6 the HBM
+// of peer GPU 0..3 of the state table, 7 zero fill; dst 0 HBM, 1 DRAM, 2 CXL (UVMTIER_RUN_SRC_* / UVMTIER_RUN_DST_*).
+constexpr uint32_t kRunPairs = 24;
 struct run_pair_bases { uint32_t base[kRunPairs]; };
 __device__ __forceinline__ uint32_t run_pair_of(const uvmtier_copy_run_t &run)
 {
-    const uint32_t src = run.src == UVMTIER_RUN_SRC_ZERO ? 3u : (run.src > 2u ? 2u : (uint32_t)run.src);
+    const uint32_t src = (uint32_t)run.src;
     const uint32_t dst = run.dst > 2u ? 2u : (uint32_t)run.dst;
     return src * 3u + dst;
 }

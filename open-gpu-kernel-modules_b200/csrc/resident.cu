@@ -3,7 +3,7 @@
 // resident_kernels.cuh.
 //
 // Algorithmic bytes per request: 16 (request) + [64 page mask] + [64 prefetch mask] + the block's state read and
-// written (7 masks x 64 B x 2) + 160 (result) + 8 per copy run.
+// written (7 masks x 64 B x 2, + 1 mask x 64 B x 2 per other GPU in the table) + 160 (result) + 8 per copy run.
 #include "common.cuh"
 
 #include "resident_kernels.cuh"
@@ -33,6 +33,20 @@ extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n
     prm.n_requests = n_requests;
     prm.n_slots = (uint32_t)n_slots64;
     prm.run_cap = run_cap;
+    prm.gpu_id = lay->gpu_id;
+    if (state->n_peers > UVMTIER_MAX_PEER_GPUS)
+        return NV_ERR_INVALID_ARGUMENT;
+    peer_state_ptrs peers;
+    memset(&peers, 0, sizeof(peers));
+    peers.n_peers = state->n_peers;
+    peers.direct = state->peer_direct;
+    for (uint32_t k = 0; k < state->n_peers; k++) {
+        if (!state->peer_resident[k] || (k && state->peer_gpu_id[k] <= state->peer_gpu_id[k - 1]) ||
+            state->peer_gpu_id[k] == lay->gpu_id)
+            return NV_ERR_INVALID_ARGUMENT;
+        peers.resident[k] = (uint32_t *)state->peer_resident[k];
+        peers.gpu_id[k] = state->peer_gpu_id[k];
+    }
 
     block_state_ptrs bs;
     bs.gpu_resident = (uint32_t *)state->gpu_resident;
@@ -52,6 +66,6 @@ extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n
     if (grid > cap)
         grid = cap;
     UVMTIER_LAUNCH(k_make_resident, (int)grid, kResThreads, 0, ctx->stream, prm, d_requests, (const uint32_t *)d_page_masks,
-                   (const uint32_t *)d_prefetch_masks, bs, d_results, d_runs, d_counters);
+                   (const uint32_t *)d_prefetch_masks, bs, peers, d_results, d_runs, d_counters);
     return NV_OK;
 }

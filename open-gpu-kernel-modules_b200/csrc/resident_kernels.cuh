@@ -9,10 +9,15 @@
 // uvm_va_block_evict_chunks (:12999-13130, cause EVICTION, page_mask = chunk pages & gpu resident), the CPU fault
 // handler, and the GPU fault path (which this library runs inside the servicing pass instead).
 //
-// Processors of the table: this GPU, and the CPU with two NUMA nodes (0 = host DRAM, 1 = CXL).  CPU pages are
+// Processors of the table: this GPU, the CPU with two NUMA nodes (0 = host DRAM, 1 = CXL), and up to four other GPUs
+// of the box that hold pages of the same va_blocks (residency only; uvmtier_block_state_add_peer).  CPU pages are
 // allocated on the node the request names (block_populate_pages_cpu's first choice, :1887-2018).  A page lives on
 // one CPU node at most; it can be on the CPU and on the GPU only while read-duplicated, and is then copied from
 // the closest holder (block_copy_resident_pages_mask :4486-4497).
+// Source order with other GPUs (block_copy_resident_pages :4707-4829, closest first = uvm_va_space.c:1879-1924):
+// destination this GPU: the GPUs it can copy from directly in ascending id, CPU node 0, CPU node 1, then the pages
+// only GPUs without direct access hold, staged through CPU pages on node 0 (one run GPU -> DRAM per such GPU, one run
+// DRAM -> HBM for their union); destination CPU: the other CPU node, then all GPUs in ascending id, this one among them.
 // Masks: one 32-bit word per lane, lanes 16-31 mirror lanes 0-15 (mask512.cuh helpers are half-warp wide).
 #pragma once
 
@@ -24,12 +29,22 @@ constexpr int kResThreads = 128;
 
 struct resident_kparams {
     uint32_t n_requests, n_slots, run_cap;
+    uint32_t gpu_id;                           // uvm_gpu_id_t of this GPU (places it among the other GPUs)
 };
+
+// the other GPUs of the table (uvmtier_block_state_t.peer_*), ascending gpu id
+struct peer_state_ptrs {
+    uint32_t *resident[UVMTIER_MAX_PEER_GPUS];
+    uint32_t gpu_id[UVMTIER_MAX_PEER_GPUS];
+    uint32_t n_peers, direct;
+};
+
+constexpr int kResSegs = 8;                    // most copy-list segments of one request (4 GPUs, 2 CPU legs, staging, zero fill)
 
 __global__ void __launch_bounds__(kResThreads)
 k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restrict__ reqs,
                 const uint32_t *__restrict__ page_masks, const uint32_t *__restrict__ prefetch_masks, block_state_ptrs st,
-                uvmtier_make_resident_result_t *__restrict__ results, uvmtier_copy_run_t *__restrict__ runs,
+                peer_state_ptrs peers, uvmtier_make_resident_result_t *__restrict__ results, uvmtier_copy_run_t *__restrict__ runs,
                 uint32_t *__restrict__ counters)
 {
     const int lane = threadIdx.x & 31, l = lane & 15;
@@ -42,7 +57,7 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
         const bool rdup = (rq.flags & UVMTIER_MR_READ_DUPLICATE) != 0;
         const bool valid = slot < prm.n_slots && rq.region_first <= rq.region_outer && rq.region_outer <= 512u &&
                            (dst_gpu || rq.dest_tier == UVMTIER_TIER_DRAM || rq.dest_tier == UVMTIER_TIER_CXL) &&
-                           !(rdup && (!st.read_duplicated || rq.cause == UVMTIER_CAUSE_EVICTION ||
+                           !(rdup && (!st.read_duplicated || rq.cause == UVMTIER_CAUSE_EVICTION || peers.n_peers ||
                                       (rq.flags & UVMTIER_MR_EVICT_GPU_PAGES)));   // :5304 asserts cause != EVICTION
         if (!valid) {                                                     // uniform across the warp
             if (lane < 16) {
@@ -70,37 +85,92 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
         const int nid = rq.dest_tier == UVMTIER_TIER_CXL ? 1 : 0;
         const uint32_t dst_res = dst_gpu ? gres : (nid ? c1 : c0);
         const uint32_t copy = pm & ~dst_res;                              // :4687-4692
-        uint32_t from[3];                                                 // CPU node 0, CPU node 1, this GPU
+        uint32_t from[3] = {0u, 0u, 0u};                                  // CPU node 0, CPU node 1, this GPU
+        uint32_t pres[UVMTIER_MAX_PEER_GPUS], from_peer[UVMTIER_MAX_PEER_GPUS], staged = 0;
+#pragma unroll
+        for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++) {
+            pres[j] = j < peers.n_peers ? peers.resident[j][w] : 0u;
+            from_peer[j] = 0;
+        }
+        const uint32_t dst_code = dst_gpu ? UVMTIER_RUN_DST_HBM : (nid ? UVMTIER_RUN_DST_CXL : UVMTIER_RUN_DST_DRAM);
+        // copy list segments in the order the reference visits the sources, the zero fills last
+        uint32_t seg_m[kResSegs], seg_src[kResSegs], seg_dst[kResSegs];
+        int ns = 0;
+#define RES_SEG(mask_, src_, dst_) do { seg_m[ns] = (mask_); seg_src[ns] = (src_); seg_dst[ns] = (dst_); ns++; } while (0)
+        uint32_t rest = copy;
         if (dst_gpu) {
-            from[0] = copy & c0;                                          // CPU nodes in ascending order (:4490)
-            from[1] = copy & ~from[0] & c1;
-            from[2] = 0;
+#pragma unroll
+            for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++)           // GPUs with direct copy access (:4707-4745)
+                if (j < peers.n_peers && ((peers.direct >> j) & 1u)) {
+                    from_peer[j] = rest & pres[j];
+                    rest &= ~from_peer[j];
+                    RES_SEG(from_peer[j], UVMTIER_RUN_SRC_PEER0 + j, dst_code);
+                }
+            from[0] = rest & c0;                                          // CPU nodes in ascending order (:4490)
+            rest &= ~from[0];
+            RES_SEG(from[0], UVMTIER_RUN_SRC_DRAM, dst_code);
+            from[1] = rest & c1;
+            rest &= ~from[1];
+            RES_SEG(from[1], UVMTIER_RUN_SRC_CXL, dst_code);
+            if (peers.n_peers && (peers.direct ^ ((1u << peers.n_peers) - 1u))) {
+                // what only GPUs without direct access hold goes through staging pages on CPU node 0
+                // (block_populate_pages pages_staged :3140-3170; copies :4754-4785 then :4803-4829)
+#pragma unroll
+                for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++)
+                    if (j < peers.n_peers && !((peers.direct >> j) & 1u)) {
+                        const uint32_t hop = rest & pres[j];
+                        rest &= ~hop;
+                        from_peer[j] = hop;
+                        staged |= hop;
+                        RES_SEG(hop, UVMTIER_RUN_SRC_PEER0 + j, UVMTIER_RUN_DST_DRAM);
+                    }
+                RES_SEG(staged, UVMTIER_RUN_SRC_DRAM, dst_code);
+            }
         }
         else {
-            // the CPU itself is the closest source: the other node first (:4486-4497), then the GPU
-            const uint32_t other = copy & (nid ? c0 : c1);
-            from[nid] = 0;
-            from[nid ^ 1] = other;
-            from[2] = copy & ~other & gres;
+            // the CPU itself is the closest source: the other node first (:4486-4497), then the GPUs in ascending id
+            from[nid ^ 1] = rest & (nid ? c0 : c1);
+            rest &= ~from[nid ^ 1];
+            RES_SEG(from[nid ^ 1], (uint32_t)(nid ^ 1), dst_code);
+            bool self_done = false;
+#pragma unroll
+            for (uint32_t j = 0; j <= UVMTIER_MAX_PEER_GPUS; j++) {
+                if (j > peers.n_peers)
+                    break;
+                if (!self_done && (j == peers.n_peers || peers.gpu_id[j < UVMTIER_MAX_PEER_GPUS ? j : 0] > prm.gpu_id)) {
+                    from[2] = rest & gres;
+                    rest &= ~from[2];
+                    RES_SEG(from[2], UVMTIER_RUN_SRC_HBM, dst_code);
+                    self_done = true;
+                }
+                if (j < peers.n_peers && j < UVMTIER_MAX_PEER_GPUS) {
+                    from_peer[j] = rest & pres[j];
+                    rest &= ~from_peer[j];
+                    RES_SEG(from_peer[j], UVMTIER_RUN_SRC_PEER0 + j, dst_code);
+                }
+            }
         }
-        const uint32_t migrated = from[0] | from[1] | from[2];
         // pages resident nowhere are populated (and zeroed) at the destination: first touch (:4581-4619)
-        const uint32_t touch = copy & ~migrated;
-        const uint32_t dst_code = dst_gpu ? UVMTIER_RUN_DST_HBM : (nid ? UVMTIER_RUN_DST_CXL : UVMTIER_RUN_DST_DRAM);
+        const uint32_t touch = rest;
+        const uint32_t migrated = copy & ~touch;
+        RES_SEG(touch, UVMTIER_RUN_SRC_ZERO, dst_code);
+#undef RES_SEG
 
-        // copy list: per source in the order the reference visits them, then the zero fills
-        const int order0 = dst_gpu ? 0 : (nid ^ 1), order1 = dst_gpu ? 1 : 2;
-        const uint32_t r0 = svc_emit_runs(from[order0], pf, slot, (uint32_t)order0, NULL, 0u, 0u, lane);
-        const uint32_t r1 = svc_emit_runs(from[order1], pf, slot, (uint32_t)order1, NULL, 0u, 0u, lane);
-        const uint32_t r2 = svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, NULL, 0u, 0u, lane);
-        const uint32_t run_cnt = r0 + r1 + r2;
+        uint32_t seg_at[kResSegs], run_cnt = 0;
+#pragma unroll
+        for (int i = 0; i < kResSegs; i++) {
+            seg_at[i] = run_cnt;
+            if (i < ns)
+                run_cnt += svc_emit_runs(seg_m[i], pf, slot, seg_src[i], NULL, 0u, 0u, lane);
+        }
         uint32_t run_off = 0;
         if (lane == 0 && run_cnt)
             run_off = atomicAdd(&counters[0], run_cnt);
         run_off = __shfl_sync(HW_FULL, run_off, 0);
-        svc_emit_runs(from[order0], pf, slot, (uint32_t)order0, runs, run_off, prm.run_cap, lane, dst_code);
-        svc_emit_runs(from[order1], pf, slot, (uint32_t)order1, runs, run_off + r0, prm.run_cap, lane, dst_code);
-        svc_emit_runs(touch, pf, slot, UVMTIER_RUN_SRC_ZERO, runs, run_off + r0 + r1, prm.run_cap, lane, dst_code);
+#pragma unroll
+        for (int i = 0; i < kResSegs; i++)
+            if (i < ns)
+                svc_emit_runs(seg_m[i], pf, slot, seg_src[i], runs, run_off + seg_at[i], prm.run_cap, lane, seg_dst[i]);
 
         const uint32_t now = migrated | touch;
         uint32_t unmap, changed;
@@ -132,6 +202,9 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
             // _finish: the destination becomes resident (update_state + first touch), everybody else loses the pages
             // of page_mask (break_read_duplication_in_region clears all of region & page_mask, not only what moved)
             rd &= ~pm;
+#pragma unroll
+            for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++)
+                pres[j] &= ~pm;
             if (dst_gpu) {
                 gres |= now;
                 c0 &= ~pm;
@@ -149,7 +222,11 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
             changed = now;                                                // pages_changed_residency (:5005-5008, :4614-4617)
         }
 
-        const uint32_t n0 = hw_weight(from[0]), n1 = hw_weight(from[1]), n2 = hw_weight(from[2]);
+        const uint32_t n0 = hw_weight(from[0]) + hw_weight(staged), n1 = hw_weight(from[1]), n2 = hw_weight(from[2]);
+        uint32_t np[UVMTIER_MAX_PEER_GPUS];
+#pragma unroll
+        for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++)
+            np[j] = j < peers.n_peers ? hw_weight(from_peer[j]) : 0u;
         const uint32_t nt = hw_weight(touch), nu = hw_weight(unmap);
         if (lane < 16) {
             st.gpu_resident[w] = gres; st.cpu_resident[0][w] = c0; st.cpu_resident[1][w] = c1;
@@ -158,6 +235,10 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
                 st.gpu_evicted[w] = evicted;
             if (st.read_duplicated)
                 st.read_duplicated[w] = rd;
+#pragma unroll
+            for (uint32_t j = 0; j < UVMTIER_MAX_PEER_GPUS; j++)
+                if (j < peers.n_peers)
+                    peers.resident[j][w] = pres[j];
             // result: 8 header words, then pages_migrated and pages_changed_residency
             if (l < 8) {
                 uint32_t v = 0;
@@ -166,6 +247,8 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
                 if (l == 2) v = n2 | (nt << 16);
                 if (l == 3) v = run_off;
                 if (l == 4) v = run_cnt | (nu << 16);
+                if (l == 5) v = np[0] | (np[1] << 16);                    // migrated_peer[0..3]
+                if (l == 6) v = np[2] | (np[3] << 16);
                 res[l] = v;
             }
             res[8 + l] = migrated;                                        // make_resident.pages_migrated

@@ -167,6 +167,11 @@ static NV_STATUS service_check_args(uvmtier_ctx_t *ctx, uint32_t n_batches, cons
         return NV_ERR_INVALID_ARGUMENT;
     if (!ctx->faults)
         return NV_ERR_INVALID_STATE;
+    if (state->n_peers) {                                   // the servicing passes know one GPU (uvmtier_block_state_add_peer)
+        uvmtier_set_error("the servicing passes take one-GPU state tables; this one names other GPUs (uvmtier_block_state_add_peer)",
+                          cudaErrorNotSupported, __FILE__, __LINE__);
+        return NV_ERR_NOT_SUPPORTED;
+    }
     if (!n_batches)
         return NV_OK;
     if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || !d_counters || (run_cap && !d_runs))
@@ -257,7 +262,37 @@ NV_STATUS uvmtier_block_state_free(uvmtier_ctx_t *ctx, uvmtier_block_state_t *st
         UVMTIER_CUDA(cudaFree(state->gpu_resident));
     if (state->read_duplicated)
         UVMTIER_CUDA(cudaFree(state->read_duplicated));
+    for (uint32_t k = 0; k < state->n_peers && k < UVMTIER_MAX_PEER_GPUS; k++)
+        if (state->peer_resident[k])
+            UVMTIER_CUDA(cudaFree(state->peer_resident[k]));
     memset(state, 0, sizeof(*state));
+    return NV_OK;
+}
+
+NV_STATUS uvmtier_block_state_add_peer(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *lay, uvmtier_block_state_t *state,
+                                       uint32_t peer_gpu_id, int direct)
+{
+    if (!ctx || !lay || !state || !state->gpu_resident || !lay->n_spaces || !lay->blocks_per_space)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (state->n_peers >= UVMTIER_MAX_PEER_GPUS)
+        return NV_ERR_INSUFFICIENT_RESOURCES;
+    // ascending uvm_gpu_id_t (1 .. 0xFFFF fit the table), none of them this GPU
+    if (!peer_gpu_id || peer_gpu_id > 0xffffu || peer_gpu_id == lay->gpu_id ||
+        (state->n_peers && state->peer_gpu_id[state->n_peers - 1] >= peer_gpu_id))
+        return NV_ERR_INVALID_ARGUMENT;
+    const size_t n = (size_t)lay->n_spaces * lay->blocks_per_space;
+    if (n > kMaxSlots)
+        return NV_ERR_INVALID_ARGUMENT;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    void *p = NULL;
+    UVMTIER_CUDA(cudaMalloc(&p, n * 64));
+    UVMTIER_CUDA(cudaMemsetAsync(p, 0, n * 64, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    const uint32_t k = state->n_peers++;
+    state->peer_resident[k] = (uvmtier_page_mask_t *)p;
+    state->peer_gpu_id[k] = (uint16_t)peer_gpu_id;
+    if (direct)
+        state->peer_direct |= 1u << k;
     return NV_OK;
 }
 

@@ -628,6 +628,12 @@ class DeviceBlockState:
                    "uvmtier_block_state_enable_read_duplication")
         return self
 
+    def add_peer(self, gpu_id, direct=True):
+        """uvmtier_block_state_add_peer: another GPU that holds pages of these va_blocks (ascending gpu id)."""
+        _check(lib().uvmtier_block_state_add_peer(self.ctx.handle, P(self.layout), ctypes.byref(self.ptrs), ctypes.c_uint32(gpu_id),
+                                                  ctypes.c_int(1 if direct else 0)), "uvmtier_block_state_add_peer")
+        return self
+
     def _fields(self):
         p = self.ptrs
         f = (("gpu_resident", p.gpu_resident), ("cpu_resident0", p.cpu_resident[0]), ("cpu_resident1", p.cpu_resident[1]),
@@ -643,6 +649,13 @@ class DeviceBlockState:
         for name, dptr in self._fields():
             a = np.ascontiguousarray(getattr(host_state, name))
             _check(lib().uvmtier_memcpy_h2d(self.ctx.handle, ctypes.c_void_p(dptr), P(a), ctypes.c_size_t(a.nbytes)), "h2d")
+        for k, (gid, direct, mask) in enumerate(host_state.peers):
+            if k >= self.ptrs.n_peers:
+                self.add_peer(gid, direct)
+            assert self.ptrs.peer_gpu_id[k] == gid and bool((self.ptrs.peer_direct >> k) & 1) == bool(direct), "peer set differs"
+            a = np.ascontiguousarray(mask)
+            _check(lib().uvmtier_memcpy_h2d(self.ctx.handle, ctypes.c_void_p(self.ptrs.peer_resident[k]), P(a),
+                                            ctypes.c_size_t(a.nbytes)), "h2d")
 
     def download(self):
         from .blockstate import HostBlockState
@@ -652,6 +665,11 @@ class DeviceBlockState:
         for name, dptr in self._fields():
             a = getattr(h, name)
             _check(lib().uvmtier_memcpy_d2h(self.ctx.handle, P(a), ctypes.c_void_p(dptr), ctypes.c_size_t(a.nbytes)), "d2h")
+        for k in range(self.ptrs.n_peers):
+            h.add_peer(self.ptrs.peer_gpu_id[k], bool((self.ptrs.peer_direct >> k) & 1))
+            a = h.peers[k][2]
+            _check(lib().uvmtier_memcpy_d2h(self.ctx.handle, P(a), ctypes.c_void_p(self.ptrs.peer_resident[k]),
+                                            ctypes.c_size_t(a.nbytes)), "d2h")
         return h
 
     def free(self):

@@ -17,7 +17,7 @@ assert (VA_LAYOUT_DT.itemsize, SERVICE_GROUP_DT.itemsize, COPY_RUN_DT.itemsize) 
 MAKE_RESIDENT_REQ_DT = np.dtype([("slot", "<u4"), ("region_first", "<u2"), ("region_outer", "<u2"), ("dest_tier", "u1"),
                                  ("cause", "u1"), ("flags", "<u2"), ("mask_row", "<u4")])
 MAKE_RESIDENT_RESULT_DT = np.dtype([("slot", "<u4"), ("migrated", "<u2", (3,)), ("first_touch", "<u2"), ("run_offset", "<u4"),
-                                    ("run_count", "<u2"), ("unmapped", "<u2"), ("reserved", "<u4", (3,)),
+                                    ("run_count", "<u2"), ("unmapped", "<u2"), ("migrated_peer", "<u2", (4,)), ("reserved", "<u4"),
                                     ("pages_migrated", "<u8", (8,)), ("pages_changed_residency", "<u8", (8,))])
 assert (MAKE_RESIDENT_REQ_DT.itemsize, MAKE_RESIDENT_RESULT_DT.itemsize) == (16, 160)
 MR_HAS_PAGE_MASK, MR_HAS_PREFETCH_MASK, MR_EVICT_GPU_PAGES, MR_READ_DUPLICATE = 1, 2, 4, 8
@@ -31,7 +31,11 @@ STATE_FIELDS = ("gpu_resident", "cpu_resident0", "cpu_resident1", "gpu_pte0", "g
 class BlockStatePtrs(ctypes.Structure):
     _fields_ = [("gpu_resident", ctypes.c_void_p), ("cpu_resident", ctypes.c_void_p * 2), ("gpu_pte", ctypes.c_void_p * 3),
                 ("prefetch_info", ctypes.c_void_p), ("logical_prot", ctypes.c_void_p), ("preferred_location", ctypes.c_void_p),
-                ("gpu_evicted", ctypes.c_void_p), ("read_duplicated", ctypes.c_void_p)]
+                ("gpu_evicted", ctypes.c_void_p), ("read_duplicated", ctypes.c_void_p),
+                ("peer_resident", ctypes.c_void_p * 4), ("peer_gpu_id", ctypes.c_uint16 * 4), ("n_peers", ctypes.c_uint32),
+                ("peer_direct", ctypes.c_uint32)]
+
+MAX_PEERS = 4
 
 
 class HostBlockState:
@@ -48,6 +52,13 @@ class HostBlockState:
         self.prefetch_info["last_migration_proc_id"] = 257
         self.logical_prot = np.full(n_slots, 3, "u1")
         self.preferred_location = np.full(n_slots, 257, "<u2")
+        # other GPUs holding pages of these va_blocks: (gpu id, direct copy access, resident masks), ascending gpu id
+        self.peers = []
+
+    def add_peer(self, gpu_id, direct=True, resident=None):
+        assert len(self.peers) < 4 and all(p[0] < gpu_id for p in self.peers), "peers in ascending gpu id, at most 4"
+        self.peers.append([int(gpu_id), bool(direct), np.zeros((self.n, 8), "<u8") if resident is None else resident.copy()])
+        return self
 
     def enable_read_duplication(self):
         if self.read_duplicated is None:
@@ -59,6 +70,7 @@ class HostBlockState:
         for f in STATE_FIELDS:
             v = getattr(self, f)
             setattr(c, f, None if v is None else v.copy())
+        c.peers = [[g, d, m.copy()] for g, d, m in self.peers]
         return c
 
     def ptrs(self):
@@ -74,6 +86,12 @@ class HostBlockState:
         s.preferred_location = self.preferred_location.ctypes.data
         s.gpu_evicted = self.gpu_evicted.ctypes.data
         s.read_duplicated = None if self.read_duplicated is None else self.read_duplicated.ctypes.data
+        s.n_peers = len(self.peers)
+        s.peer_direct = 0
+        for k, (g, d, m) in enumerate(self.peers):
+            s.peer_resident[k] = m.ctypes.data
+            s.peer_gpu_id[k] = g
+            s.peer_direct |= (1 << k) if d else 0
         return s
 
     def assert_equal(self, other, what=""):
@@ -85,6 +103,11 @@ class HostBlockState:
             if not np.array_equal(a, b):
                 bad = np.nonzero((a != b).reshape(self.n, -1).any(axis=1))[0] if a.dtype.names is None else np.nonzero(a != b)[0]
                 raise AssertionError("%s state.%s differs at slots %s" % (what, f, bad[:8]))
+        assert len(self.peers) == len(other.peers), what + " number of peers"
+        for k, ((g, d, a), (g2, d2, b)) in enumerate(zip(self.peers, other.peers)):
+            assert (g, d) == (g2, d2), what + " peer ids"
+            if not np.array_equal(a, b):
+                raise AssertionError("%s state.peer_resident[%d] differs at slots %s" % (what, k, np.nonzero((a != b).any(axis=1))[0][:8]))
 
 
 def make_layout(lay, gpu_id=1):

@@ -95,6 +95,7 @@ if [ -f "$HERE/ref_resident_glue.c" ]; then
     sed -n '197,242p' "$UVM/uvm_va_block_types.h" > "$TMP/x_make_resident_ctx.h"
     sed -n '183,195p;584,593p;609,701p;721,734p;2406,2430p;3569,3577p;4379,4452p;4460,4536p;4538,4579p;4581,4619p;4625,4653p;4660,4847p;4877,4976p;4978,5114p;5120,5162p;5164,5332p' \
         "$UVM/uvm_va_block.c" > "$TMP/x_resident.h"
+    sed -n '3099,3182p' "$UVM/uvm_va_block.c" > "$TMP/x_populate.h"
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
         -o "$OUT/libref_resident.so"
     echo "build_ref: built $OUT/libref_resident.so"

@@ -10,10 +10,12 @@
  *   M1r uvm_va_block_make_resident_read_duplicate :5164-5332, block_prep_read_duplicate_mapping :5120-5162
  *       (request flag 8; state table with a read_duplicated mask)
  *
- * Processors of the table: one GPU and the CPU with two NUMA nodes (0 = DRAM, 1 = CXL).  Harness policy as in
- * oracle_service.c: residency is exclusive unless the caller read-duplicates, CPU destination pages are allocated
- * on the node the request names (block_populate_pages_cpu's first choice), the GPU can copy from the CPU directly
- * (no staging).
+ * Processors of the table: one GPU ("this GPU", the destination and the only mapper), the CPU with two NUMA nodes
+ * (0 = DRAM, 1 = CXL), and up to four other GPUs of the box that hold pages of the same va_blocks (residency only).
+ * Harness policy as in oracle_service.c: residency is exclusive unless the caller read-duplicates (not with other
+ * GPUs in the table), CPU destination pages are allocated on the node the request names (block_populate_pages_cpu's
+ * first choice), this GPU copies from the CPU directly and from another GPU directly when the table says so
+ * (peer_direct), else through CPU staging pages on node 0.
  *
  * Pinning: the reference holds no vectors for make_resident masks, so this file is checked against the
  * reference's own code: oracle/ref_resident_glue.c compiles uvm_va_block_make_resident, _copy, _finish,
@@ -33,6 +35,11 @@ uint32_t oracle_emit_runs(const or_mask_t *pages, const or_mask_t *prefetch, uin
 
 static or_mask_t *node_mask(or_mask_t *cpu, int nid) { return &cpu[nid]; }
 
+/* uvm_gpu_id_t of the GPU the table belongs to: only the ORDER of the GPU sources of a CPU destination depends on it
+ * (closest first = ascending id, uvm_va_space.c:1879-1924), and only when the table names other GPUs. */
+static uint32_t g_this_gpu_id = 1;
+void oracle_make_resident_set_gpu_id(uint32_t gpu_id) { g_this_gpu_id = gpu_id; }
+
 /* Processes the requests in order.  Returns the number of copy runs needed (only run_cap are written). */
 uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t *reqs, const uint64_t *page_masks,
                               const uint64_t *prefetch_masks, uint32_t n_slots, const ref_block_state_t *st,
@@ -47,12 +54,13 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         const int nid = rq->dest_tier == 2 ? 1 : 0;                  /* make_resident.dest_nid */
         const bool rdup = (rq->flags & 8) != 0;                      /* uvm_va_block_make_resident_read_duplicate */
         or_mask_t gpu, cpu[2], pte[3], evicted, rd, pm, pf, copy, from[3], migrated, touch, now, unmap, *dst_res;
-        int i, order[2];
-        uint32_t k = 0, n_unmapped = 0;
+        or_mask_t peer[4], from_peer[4], staged;
+        int i;
+        uint32_t k = 0, n_unmapped = 0, np = st->n_peers, j;
 
         memset(res, 0, sizeof(*res));
         if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > OR_PAGES || rq->dest_tier > 2 ||
-            (rdup && (!st->read_duplicated || rq->cause == 4 || (rq->flags & 4)))) {    /* :5304 asserts !EVICTION */
+            (rdup && (!st->read_duplicated || rq->cause == 4 || (rq->flags & 4) || np))) {   /* :5304 asserts !EVICTION */
             res->slot = 0xFFFFFFFFu;
             continue;
         }
@@ -66,6 +74,9 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         if (st->gpu_evicted) or_load(&evicted, st->gpu_evicted + 8 * (size_t)slot);
         or_zero(&rd);
         if (st->read_duplicated) or_load(&rd, st->read_duplicated + 8 * (size_t)slot);
+        for (j = 0; j < 4; j++) { or_zero(&peer[j]); or_zero(&from_peer[j]); }
+        for (j = 0; j < np; j++) or_load(&peer[j], st->peer_resident[j] + 8 * (size_t)slot);
+        or_zero(&staged);
 
         /* page_mask clipped to the region (uvm_page_mask_region_clear_outside); NULL = whole region */
         or_zero(&pm);
@@ -117,31 +128,65 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         or_andnot(&copy, &pm, dst_res);
         for (i = 0; i < 3; i++) or_zero(&from[i]);
         if (dst_gpu) {
-            /* sources with direct copy access: the CPU, node after node (:4707-4712, :4486-4497) */
-            or_mask_t rest = copy;
+            /* first everything from the processors with direct copy access, closest first (:4707-4745, :4486-4497):
+             * the other GPUs in ascending id, then the CPU, node after node */
+            or_mask_t rest = copy, hop;
+            for (j = 0; j < np; j++) {
+                if (!((st->peer_direct >> j) & 1u)) continue;
+                or_and(&from_peer[j], &rest, &peer[j]);
+                or_andnot(&rest, &rest, &from_peer[j]);
+                k += oracle_emit_runs(&from_peer[j], &pf, slot, 3u + j, rq->dest_tier, runs, nrun + k, run_cap);
+            }
             or_and(&from[0], &rest, &cpu[0]);
             or_andnot(&rest, &rest, &from[0]);
+            k += oracle_emit_runs(&from[0], &pf, slot, 0, rq->dest_tier, runs, nrun + k, run_cap);
             or_and(&from[1], &rest, &cpu[1]);
-            order[0] = 0; order[1] = 1;
+            or_andnot(&rest, &rest, &from[1]);
+            k += oracle_emit_runs(&from[1], &pf, slot, 1, rq->dest_tier, runs, nrun + k, run_cap);
+            /* then what only GPUs without direct access hold: staged through CPU pages (pages_staged :3140-3170, allocated
+             * on node 0), copied there from those GPUs (:4754-4785), then from the CPU to the destination (:4803-4829) */
+            for (j = 0; j < np; j++) {
+                if ((st->peer_direct >> j) & 1u) continue;
+                or_and(&hop, &rest, &peer[j]);
+                or_andnot(&rest, &rest, &hop);
+                or_or(&from_peer[j], &from_peer[j], &hop);
+                or_or(&staged, &staged, &hop);
+                k += oracle_emit_runs(&hop, &pf, slot, 3u + j, 1 /* DRAM */, runs, nrun + k, run_cap);
+            }
+            k += oracle_emit_runs(&staged, &pf, slot, 0, rq->dest_tier, runs, nrun + k, run_cap);
         }
         else {
             /* destination CPU: everything resident elsewhere is a source, closest first -- the CPU itself (the
-             * other node; the destination node holds none of copy_page_mask), then the GPU  (:4754-4785) */
+             * other node; the destination node holds none of copy_page_mask), then the GPUs in ascending id (:4754-4785) */
             or_mask_t rest = copy;
+            bool self_done = false;
             or_and(&from[nid ^ 1], &rest, &cpu[nid ^ 1]);
             or_andnot(&rest, &rest, &from[nid ^ 1]);
-            or_and(&from[2], &rest, &gpu);
-            order[0] = nid ^ 1; order[1] = 2;
+            k += oracle_emit_runs(&from[nid ^ 1], &pf, slot, (unsigned)(nid ^ 1), rq->dest_tier, runs, nrun + k, run_cap);
+            for (j = 0; j <= np; j++) {
+                if (!self_done && (j == np || st->peer_gpu_id[j] > g_this_gpu_id)) {
+                    or_and(&from[2], &rest, &gpu);
+                    or_andnot(&rest, &rest, &from[2]);
+                    k += oracle_emit_runs(&from[2], &pf, slot, 2, rq->dest_tier, runs, nrun + k, run_cap);
+                    self_done = true;
+                }
+                if (j < np) {
+                    or_and(&from_peer[j], &rest, &peer[j]);
+                    or_andnot(&rest, &rest, &from_peer[j]);
+                    k += oracle_emit_runs(&from_peer[j], &pf, slot, 3u + j, rq->dest_tier, runs, nrun + k, run_cap);
+                }
+            }
         }
         or_or(&migrated, &from[0], &from[1]);
         or_or(&migrated, &migrated, &from[2]);
+        for (j = 0; j < np; j++) or_or(&migrated, &migrated, &from_peer[j]);
         or_andnot(&touch, &copy, &migrated);                          /* resident nowhere: populated + zeroed */
-        for (i = 0; i < 2; i++)
-            k += oracle_emit_runs(&from[order[i]], &pf, slot, (unsigned)order[i], rq->dest_tier, runs, nrun + k, run_cap);
         k += oracle_emit_runs(&touch, &pf, slot, 7, rq->dest_tier, runs, nrun + k, run_cap);
         res->run_count = (uint16_t)k;
         nrun += k;
         for (i = 0; i < 3; i++) res->migrated[i] = (uint16_t)or_weight(&from[i]);
+        res->migrated[0] = (uint16_t)(res->migrated[0] + or_weight(&staged));      /* the second hop of the staged pages */
+        for (j = 0; j < np; j++) res->migrated_peer[j] = (uint16_t)or_weight(&from_peer[j]);
         res->first_touch = (uint16_t)or_weight(&touch);
         res->unmapped = (uint16_t)n_unmapped;
 
@@ -163,6 +208,7 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
              * residency loses region & page_mask and read duplication ends there  (:5061-5074, :4538-4579) */
             or_or(dst_res, dst_res, &now);
             or_andnot(&rd, &rd, &pm);
+            for (j = 0; j < np; j++) or_andnot(&peer[j], &peer[j], &pm);
             if (dst_gpu) {
                 or_andnot(&cpu[0], &cpu[0], &pm);
                 or_andnot(&cpu[1], &cpu[1], &pm);
@@ -184,6 +230,7 @@ uint32_t oracle_make_resident(uint32_t n_requests, const ref_make_resident_req_t
         for (i = 0; i < 3; i++) or_store(st->gpu_pte[i] + 8 * (size_t)slot, &pte[i]);
         if (st->gpu_evicted) or_store(st->gpu_evicted + 8 * (size_t)slot, &evicted);
         if (st->read_duplicated) or_store(st->read_duplicated + 8 * (size_t)slot, &rd);
+        for (j = 0; j < np; j++) or_store(st->peer_resident[j] + 8 * (size_t)slot, &peer[j]);
     }
     return nrun;
 }

@@ -135,6 +135,13 @@ typedef struct {
     uint16_t *preferred_location;   /* policy->preferred_location, 257 = none */
     uint64_t *gpu_evicted;          /* gpu_state->evicted (may be NULL) */
     uint64_t *read_duplicated;      /* va_block->read_duplicated_pages (NULL = read duplication off) */
+    /* other GPUs of the box that hold pages of these va_blocks (uvmtier_block_state_t, same layout): their
+     * gpu_state->resident masks, ascending uvm_gpu_id_t; bit k of peer_direct = this GPU can copy from peer k directly
+     * (block_get_can_copy_from_mask), clear = through the CPU (uvm_va_block.c:3140-3170, :4769-4829) */
+    uint64_t *peer_resident[4];
+    uint16_t peer_gpu_id[4];
+    uint32_t n_peers;
+    uint32_t peer_direct;
 } ref_block_state_t;
 
 /* uvm_va_block_make_resident request / result, same layout as uvmtier_make_resident_req_t / _result_t */
@@ -154,7 +161,8 @@ typedef struct {
     uint32_t run_offset;
     uint16_t run_count;
     uint16_t unmapped;
-    uint32_t reserved[3];
+    uint16_t migrated_peer[4];      /* pages copied from peer GPU k */
+    uint32_t reserved;
     uint64_t pages_migrated[8];
     uint64_t pages_changed_residency[8];
 } ref_make_resident_result_t;       /* 160 bytes */

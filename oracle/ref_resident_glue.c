@@ -116,6 +116,7 @@ static const uvm_va_policy_t *uvm_va_policy_get_region(uvm_va_block_t *b, uvm_va
 typedef struct uvm_va_block_context_struct {
     uvm_page_mask_t scratch_page_mask;
     nodemask_t scratch_node_mask;
+    void *mm;
 #include "x_make_resident_ctx.h" /* :197-242: struct uvm_make_resident_context_struct { ... } make_resident; */
 } uvm_va_block_context_t;
 typedef struct uvm_va_block_retry_struct uvm_va_block_retry_t;
@@ -134,17 +135,21 @@ static void uvm_processor_mask_cache_free(uvm_processor_mask_t *m) { (void)m; }
 static const uvm_processor_mask_t *block_get_can_copy_from_mask(uvm_va_block_t *b, uvm_processor_id_t id) { (void)b; (void)id; return &g_can_copy_from; }
 static const uvm_processor_mask_t *block_get_uvm_lite_gpus(uvm_va_block_t *b) { (void)b; return &g_no_gpus; }
 static uvm_processor_id_t g_gpu_id;
-/* closest first as seen from dst: the processor itself, then the others in id order (CPU before GPUs) */
+/* closest first as seen from dst (uvm_processor_mask_find_closest_id, uvm_va_space.c:1879-1924, on a box where every
+ * GPU has a fast link to every other and to the CPU): the processor itself, then the GPUs in ascending id ("direct
+ * peers, prioritizing GPU peers over CPU"), then the CPU */
 static uvm_processor_id_t closest_next(const uvm_processor_mask_t *m, uvm_processor_id_t dst, int step)
 {
     uvm_processor_id_t id;
     int seen = 0;
     if (uvm_processor_mask_test(m, dst)) { if (step == 0) return dst; seen = 1; }
-    for_each_id_in_mask(id, m) {
+    for_each_gpu_id_in_mask(id, m) {
         if (uvm_id_equal(id, dst)) continue;
         if (seen == step) return id;
         seen++;
     }
+    if (!UVM_ID_IS_CPU(dst) && uvm_processor_mask_test(m, UVM_ID_CPU) && seen == step)
+        return UVM_ID_CPU;
     return UVM_ID_INVALID;
 }
 #define for_each_closest_id(id, mask, dst, va_space) \
@@ -169,6 +174,16 @@ static NV_STATUS uvm_va_block_unmap_mask(uvm_va_block_t *va_block, uvm_va_block_
                                          uvm_va_block_region_t region, const uvm_page_mask_t *mask);
 static NV_STATUS block_populate_pages(uvm_va_block_t *block, uvm_va_block_retry_t *retry, uvm_va_block_context_t *ctx,
                                       uvm_processor_id_t dest_id, uvm_va_block_region_t region, const uvm_page_mask_t *page_mask);
+/* what the verbatim block_populate_pages (:3099-3182) calls */
+typedef struct { int dummy; } uvm_memcg_context_t;
+typedef struct uvm_gpu_struct uvm_gpu_t;
+static uvm_gpu_t *uvm_gpu_get(uvm_gpu_id_t id) { (void)id; return NULL; }
+static NV_STATUS block_populate_pages_gpu(uvm_va_block_t *b, uvm_va_block_retry_t *r, uvm_gpu_t *g, uvm_va_block_region_t region,
+                                          const uvm_page_mask_t *m) { (void)b; (void)r; (void)g; (void)region; (void)m; return NV_OK; }
+static void uvm_memcg_context_start(uvm_memcg_context_t *c, void *mm) { (void)c; (void)mm; }
+static void uvm_memcg_context_end(uvm_memcg_context_t *c) { (void)c; }
+static NV_STATUS block_populate_pages_cpu(uvm_va_block_t *block, const uvm_page_mask_t *populate_mask, uvm_va_block_region_t region,
+                                          uvm_va_block_context_t *ctx, bool staged);
 static NV_STATUS block_copy_resident_pages_between(uvm_va_block_t *block, uvm_va_block_context_t *block_context,
                                                    uvm_processor_id_t dst_id, int dst_nid, uvm_processor_id_t src_id, int src_nid,
                                                    uvm_va_block_region_t region, uvm_page_mask_t *copy_mask,
@@ -194,6 +209,7 @@ static uvm_page_mask_t g_scratch_mask;
 #define kmem_cache_free(cache, p) ((void)(cache), (void)(p))
 
 #include "x_resident.h"         /* the uvm_va_block.c extracts listed at the top, verbatim */
+#include "x_populate.h"         /* uvm_va_block.c:3099-3182 block_populate_pages, verbatim */
 
 static uvm_page_mask_t *block_resident_mask_get_alloc(uvm_va_block_t *block, uvm_processor_id_t processor, int nid)
 {
@@ -201,8 +217,13 @@ static uvm_page_mask_t *block_resident_mask_get_alloc(uvm_va_block_t *block, uvm
 }
 static bool block_is_page_resident_anywhere(uvm_va_block_t *block, uvm_page_index_t page_index)
 {
-    return uvm_page_mask_test(&block->cpu.resident, page_index) ||
-           uvm_page_mask_test(&block->gpus[g_gpu_id.val]->resident, page_index);
+    uvm_processor_id_t id;
+    if (uvm_page_mask_test(&block->cpu.resident, page_index))
+        return true;
+    for_each_gpu_id_in_mask(id, &block->resident)
+        if (uvm_page_mask_test(&block->gpus[id.val]->resident, page_index))
+            return true;
+    return false;
 }
 /* uvm_va_block_unmap_mask (:10580-10660): the GPU of the table is the only mapper */
 static uint32_t g_unmapped;
@@ -248,21 +269,18 @@ static NV_STATUS uvm_va_block_revoke_prot(uvm_va_block_t *va_block, uvm_va_block
         uvm_page_mask_andnot(&gs->pte_bits[k], &gs->pte_bits[k], &clipped);
     return NV_OK;
 }
-/* block_populate_pages (:3099-3182): populate = page_mask & ~resident(dest); CPU destination: the pages are
- * allocated on the destination node (block_populate_pages_cpu's first choice), which is what
+/* block_populate_pages_cpu (:1887-2018), first choice: the pages are allocated on the node the request names -- for a
+ * GPU destination (staging pages) that is uvm_va_block_context_get_node's default, node 0 -- which is what
  * block_select_cpu_node_pages later finds in node_state->allocated */
-static NV_STATUS block_populate_pages(uvm_va_block_t *block, uvm_va_block_retry_t *retry, uvm_va_block_context_t *ctx,
-                                      uvm_processor_id_t dest_id, uvm_va_block_region_t region, const uvm_page_mask_t *page_mask)
+static NV_STATUS block_populate_pages_cpu(uvm_va_block_t *block, const uvm_page_mask_t *populate_mask, uvm_va_block_region_t region,
+                                          uvm_va_block_context_t *ctx, bool staged)
 {
-    (void)retry;
-    if (UVM_ID_IS_CPU(dest_id)) {
-        const int nid = ctx->make_resident.dest_nid;
-        uvm_va_block_cpu_node_state_t *ns = block_node_state_get(block, nid);
-        uvm_page_mask_t populate;
-        uvm_page_mask_init_from_region(&populate, region, page_mask);
-        uvm_page_mask_andnot(&populate, &populate, &ns->resident);
-        uvm_page_mask_or(&ns->allocated, &ns->allocated, &populate);
-    }
+    const int nid = (!staged && ctx->make_resident.dest_nid != NUMA_NO_NODE) ? ctx->make_resident.dest_nid : numa_mem_id();
+    uvm_va_block_cpu_node_state_t *ns = block_node_state_get(block, nid);
+    uvm_page_mask_t populate;
+    uvm_page_mask_init_from_region(&populate, region, populate_mask);
+    uvm_page_mask_andnot(&populate, &populate, &ns->resident);
+    uvm_page_mask_or(&ns->allocated, &ns->allocated, &populate);
     return NV_OK;
 }
 
@@ -270,7 +288,18 @@ static NV_STATUS block_populate_pages(uvm_va_block_t *block, uvm_va_block_retry_
 uint32_t oracle_emit_runs(const void *pages, const void *prefetch, uint32_t slot, unsigned src, unsigned dst,
                           ref_copy_run_t *runs, uint32_t at, uint32_t cap);
 static ref_copy_run_t *g_runs;
-static uint32_t g_nrun, g_run_cap, g_from[3];
+static uint32_t g_nrun, g_run_cap, g_from[7];
+static uvm_processor_id_t g_peer_id[4];
+static uint32_t g_n_peers;
+/* run source code of a processor: CPU node 0 / 1, this GPU 2, peer k 3 + k */
+static unsigned src_code_of(uvm_processor_id_t id, int nid)
+{
+    uint32_t k;
+    if (UVM_ID_IS_CPU(id)) return (unsigned)nid;
+    if (uvm_id_equal(id, g_gpu_id)) return 2u;
+    for (k = 0; k < g_n_peers; k++) if (uvm_id_equal(id, g_peer_id[k])) return 3u + k;
+    return 2u;
+}
 static NV_STATUS block_copy_resident_pages_between(uvm_va_block_t *block, uvm_va_block_context_t *block_context,
                                                    uvm_processor_id_t dst_id, int dst_nid, uvm_processor_id_t src_id, int src_nid,
                                                    uvm_va_block_region_t region, uvm_page_mask_t *copy_mask,
@@ -284,7 +313,7 @@ static NV_STATUS block_copy_resident_pages_between(uvm_va_block_t *block, uvm_va
                                cause == UVM_MAKE_RESIDENT_CAUSE_NON_REPLAYABLE_FAULT ||
                                cause == UVM_MAKE_RESIDENT_CAUSE_ACCESS_COUNTER) && !!prefetch_page_mask;   /* :4094-4096 */
     uvm_page_mask_t none;
-    const unsigned src = UVM_ID_IS_CPU(src_id) ? (unsigned)src_nid : 2u, dst = UVM_ID_IS_CPU(dst_id) ? 1u + (unsigned)dst_nid : 0u;
+    const unsigned src = src_code_of(src_id, src_nid), dst = UVM_ID_IS_CPU(dst_id) ? 1u + (unsigned)dst_nid : 0u;
     (void)region; (void)transfer_mode; (void)copy_tracker;
     *copied_pages = 0;
     if (!uvm_page_mask_andnot(copy_mask, copy_mask, dst_resident_mask))                  /* :4112-4113 */
@@ -320,13 +349,19 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
     uvm_processor_mask_zero(&g_no_gpus);
     uvm_processor_mask_set(&g_can_copy_from, UVM_ID_CPU);
     uvm_processor_mask_set(&g_can_copy_from, g_gpu_id);
+    g_n_peers = st->n_peers;
+    for (q = 0; q < st->n_peers; q++) {
+        g_peer_id[q].val = st->peer_gpu_id[q];
+        if ((st->peer_direct >> q) & 1u)
+            uvm_processor_mask_set(&g_can_copy_from, g_peer_id[q]);
+    }
 
     for (q = 0; q < n_requests; q++) {
         const ref_make_resident_req_t *rq = &reqs[q];
         ref_make_resident_result_t *res = &results[q];
         const uint32_t slot = rq->slot;
         uvm_va_block_t blk;
-        uvm_va_block_gpu_state_t gs;
+        uvm_va_block_gpu_state_t gs, peer_gs[4];
         uvm_va_block_cpu_node_state_t ns[2];
         uvm_va_block_context_t ctx;
         uvm_page_mask_t tracking[2], *tracking_ptr[2] = { &tracking[0], &tracking[1] }, pm, pf, touch;
@@ -336,7 +371,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
 
         memset(res, 0, sizeof(*res));
         if (slot >= n_slots || rq->region_first > rq->region_outer || rq->region_outer > PAGES_PER_UVM_VA_BLOCK || rq->dest_tier > 2 ||
-            ((rq->flags & 8) && (!st->read_duplicated || rq->cause == UVM_MAKE_RESIDENT_CAUSE_EVICTION || (rq->flags & 4)))) {
+            ((rq->flags & 8) && (!st->read_duplicated || rq->cause == UVM_MAKE_RESIDENT_CAUSE_EVICTION || (rq->flags & 4) || st->n_peers))) {
             res->slot = 0xFFFFFFFFu;
             continue;
         }
@@ -353,6 +388,12 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         blk.gpus[gpu_id] = &gs;
         blk.cpu.node_state[0] = &ns[0]; blk.cpu.node_state[1] = &ns[1];
         load_mask(&gs.resident, st->gpu_resident, slot);
+        for (k = 0; k < (int)st->n_peers; k++) {                      /* the other GPUs: residency only */
+            memset(&peer_gs[k], 0, sizeof(peer_gs[k]));
+            load_mask(&peer_gs[k].resident, st->peer_resident[k], slot);
+            blk.gpus[g_peer_id[k].val] = &peer_gs[k];
+            if (!uvm_page_mask_empty(&peer_gs[k].resident)) uvm_processor_mask_set(&blk.resident, g_peer_id[k]);
+        }
         for (k = 0; k < 3; k++) load_mask(&gs.pte_bits[k], st->gpu_pte[k], slot);
         uvm_page_mask_zero(&gs.evicted);
         if (st->gpu_evicted) load_mask(&gs.evicted, st->gpu_evicted, slot);
@@ -377,7 +418,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         dest = rq->dest_tier == 0 ? g_gpu_id : UVM_ID_CPU;
         ctx.make_resident.dest_nid = rq->dest_tier == 0 ? NUMA_NO_NODE : (int)rq->dest_tier - 1;
         ctx.make_resident.cpu_pages_used.node_masks = tracking_ptr;
-        g_unmapped = 0; g_from[0] = g_from[1] = g_from[2] = 0;
+        g_unmapped = 0; memset(g_from, 0, sizeof(g_from));
 
         if (rq->flags & 8)
             uvm_va_block_make_resident_read_duplicate(&blk, NULL, &ctx, dest, region, (rq->flags & 1) ? &pm : NULL,
@@ -394,6 +435,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
             g_nrun += oracle_emit_runs(touch.bitmap, (rq->flags & 2) ? pf.bitmap : none.bitmap, slot, 7, rq->dest_tier, runs, g_nrun, run_cap);
         }
         for (k = 0; k < 3; k++) res->migrated[k] = (uint16_t)g_from[k];
+        for (k = 0; k < 4; k++) res->migrated_peer[k] = (uint16_t)g_from[3 + k];
         res->first_touch = (uint16_t)uvm_page_mask_weight(&touch);
         res->run_count = (uint16_t)(g_nrun - res->run_offset);
         res->unmapped = (uint16_t)g_unmapped;
@@ -401,6 +443,7 @@ uint32_t ref_make_resident(uint32_t n_requests, const ref_make_resident_req_t *r
         memcpy(res->pages_changed_residency, ctx.make_resident.pages_changed_residency.bitmap, 64);
 
         store_mask(st->gpu_resident, slot, &gs.resident);
+        for (k = 0; k < (int)st->n_peers; k++) store_mask(st->peer_resident[k], slot, &peer_gs[k].resident);
         for (k = 0; k < 3; k++) store_mask(st->gpu_pte[k], slot, &gs.pte_bits[k]);
         if (st->gpu_evicted) store_mask(st->gpu_evicted, slot, &gs.evicted);
         if (st->read_duplicated) store_mask(st->read_duplicated, slot, &blk.read_duplicated_pages);

@@ -9,7 +9,25 @@ from uvmtier.blockstate import (CAUSE_API_MIGRATE, CAUSE_EVICTION, CAUSE_REPLAYA
                                 MAKE_RESIDENT_REQ_DT, MAKE_RESIDENT_RESULT_DT, MR_EVICT_GPU_PAGES, MR_HAS_PAGE_MASK,
                                 MR_HAS_PREFETCH_MASK, MR_READ_DUPLICATE, TIER_CXL, TIER_DRAM, TIER_HBM, HostBlockState)
 
-RESULT_FIELDS = ("slot", "migrated", "first_touch", "run_count", "unmapped", "pages_migrated", "pages_changed_residency")
+RESULT_FIELDS = ("slot", "migrated", "migrated_peer", "first_touch", "run_count", "unmapped", "pages_migrated",
+                 "pages_changed_residency")
+
+
+def with_peers(st, seed, peers=((3, True), (5, False)), share=0.25):
+    """Adds other GPUs to a random state: `peers` = (gpu id, direct copy access) in ascending id; a share of the pages
+    that live on the CPU or nowhere move to a peer's memory (every page still lives in one place)."""
+    rng = np.random.default_rng(seed + 900)
+    free = ~bool_from_masks(st.gpu_resident)
+    if st.read_duplicated is not None:
+        free &= ~bool_from_masks(st.read_duplicated)
+    pick = free & (rng.random(free.shape) < share)
+    owner = rng.integers(0, len(peers), free.shape)
+    for k, (gid, direct) in enumerate(peers):
+        mine = pick & (owner == k)
+        st.cpu_resident0 &= ~masks_from_bool(mine)
+        st.cpu_resident1 &= ~masks_from_bool(mine)
+        st.add_peer(gid, direct, masks_from_bool(mine))
+    return st
 
 
 def with_read_duplication(st, seed, dup=0.15, quirk=0.01):
@@ -65,9 +83,10 @@ def random_requests(n_slots, seed, frac=0.6, evict_frac=0.25, bad=0, rdup_frac=0
     return rq, page_masks, prefetch_masks
 
 
-def run_oracle(orc, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
+def run_oracle(orc, rq, page_masks, prefetch_masks, state, run_cap=1 << 18, gpu_id=1):
     st = state.copy()
     ptrs = st.ptrs()
+    orc.oracle_make_resident_set_gpu_id(ctypes.c_uint32(gpu_id))
     res = np.zeros(len(rq), MAKE_RESIDENT_RESULT_DT)
     runs = np.zeros(run_cap, COPY_RUN_DT)
     fn = orc.oracle_make_resident
@@ -90,14 +109,14 @@ def run_ref(ref, rq, page_masks, prefetch_masks, state, run_cap=1 << 18, gpu_id=
     return dict(results=res, runs=runs, n_runs=int(n_runs), state=st)
 
 
-def run_simt(sim, rq, page_masks, prefetch_masks, state, run_cap=1 << 18):
+def run_simt(sim, rq, page_masks, prefetch_masks, state, run_cap=1 << 18, gpu_id=1):
     st = state.copy()
     ptrs = st.ptrs()
     res = np.zeros(len(rq), MAKE_RESIDENT_RESULT_DT)
     runs = np.zeros(run_cap, COPY_RUN_DT)
     counters = np.zeros(2, "<u4")
     sim.simt_make_resident(ctypes.c_uint32(len(rq)), P(rq), P(page_masks), P(prefetch_masks), ctypes.c_uint32(st.n),
-                           ctypes.byref(ptrs), P(res), P(runs), ctypes.c_uint32(run_cap), P(counters))
+                           ctypes.byref(ptrs), P(res), P(runs), ctypes.c_uint32(run_cap), P(counters), ctypes.c_uint32(gpu_id))
     return dict(results=res, runs=runs, n_runs=int(counters[0]), state=st)
 
 

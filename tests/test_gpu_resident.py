@@ -130,3 +130,146 @@ def test_moves_between_all_tiers_are_byte_exact():
         assert m5[TIER_CXL][odd].all() and not m5[TIER_HBM][odd].any() and not m5[TIER_DRAM][odd].any()
         assert not T.bool_from_masks(f["state"].read_duplicated).ravel()[odd].any()
         ds.free()
+
+
+@pytest.mark.parametrize("seed,gpu_id,peers", [(41, 1, ((3, True),)), (42, 3, ((1, True), (2, False), (7, False), (9, True))),
+                                               (43, 5, ((1, False), (2, False), (3, False), (4, False)))])
+def test_make_resident_with_other_gpus_matches_oracle(seed, gpu_id, peers):
+    """Tables that name other GPUs of the box (uvmtier_block_state_add_peer): sources closest first, staging through
+    DRAM for the GPUs without direct access, every other holder loses the pages (tests/test_oracle_resident.py holds
+    the restatement against the reference's own code for the same configurations)."""
+    n_slots = 2048
+    st0 = R.with_peers(_state(n_slots, seed, False), seed, peers)
+    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3, evict_cause_frac=0.3)
+    want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0, run_cap=1 << 20, gpu_id=gpu_id)
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1), gpu_id=gpu_id)
+    with uvmtier.Context(0) as c:
+        ds = c.block_state_alloc(layout)
+        ds.upload(st0)
+        got = c.make_resident(rq, pm, pf, layout, ds, run_cap=1 << 20)
+        ds.free()
+    R.assert_equal(want, got, "peers, seed %d" % seed)
+    assert int(got["results"]["migrated_peer"].sum()) > 5000
+
+
+def _moves_with_peers(c, peer_ptrs, peer_reads, peers, gpu_id, n=32):
+    """Real bytes behind a table with other GPUs: every page's 4 KB pattern sits in the arena of its holder; after
+    'everything to this GPU' and then 'everything to DRAM' each page holds its pattern where the table says it lives."""
+    import ctypes
+    lib = uvmtier.lib()
+    st0 = R.with_peers(S.random_state(n, 19, populated=0.8), 19, peers, share=0.5)
+    info = {t: c.tier_create(t, n << 21) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
+    views = {t: info[t].host_view().reshape(n * 512, 4096) for t in (TIER_DRAM, TIER_CXL)}
+    truth = TG.rng_stream(78, n * 512 * 1024).view(np.uint8).reshape(n * 512, 4096)
+    where = {TIER_HBM: T.bool_from_masks(st0.gpu_resident).ravel(), TIER_DRAM: T.bool_from_masks(st0.cpu_resident0).ravel(),
+             TIER_CXL: T.bool_from_masks(st0.cpu_resident1).ravel()}
+    on_peer = [T.bool_from_masks(m).ravel() for _, _, m in st0.peers]
+    resident0 = where[TIER_HBM] | where[TIER_DRAM] | where[TIER_CXL]
+    for m in on_peer:
+        assert not (m & resident0).any()
+        resident0 = resident0 | m
+
+    def put(dptr, mask):
+        buf = np.full((n * 512, 4096), 0xEE, np.uint8)
+        buf[mask] = truth[mask]
+        uvmtier._check(lib.uvmtier_memcpy_h2d(c.handle, uvmtier.P(dptr), uvmtier.P(buf), ctypes.c_size_t(buf.nbytes)), "h2d")
+
+    put(info[TIER_HBM].device_ptr, where[TIER_HBM])
+    for k, p in enumerate(peer_ptrs):
+        put(p, on_peer[k])
+    for t in (TIER_DRAM, TIER_CXL):
+        views[t][:] = 0xEE
+        views[t][where[t]] = truth[where[t]]
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n, n_spaces=1), gpu_id=gpu_id)
+    ds = c.block_state_alloc(layout)
+    ds.upload(st0)
+    rq = np.zeros(n, R.MAKE_RESIDENT_REQ_DT)
+    rq["slot"] = np.arange(n); rq["region_outer"] = 512; rq["dest_tier"] = TIER_HBM; rq["cause"] = R.CAUSE_API_MIGRATE
+    a = c.make_resident(rq, None, None, layout, ds, execute=True)
+    assert [int(x) for x in a["results"]["migrated_peer"].sum(axis=0)[:len(peers)]] == [int(m.sum()) for m in on_peer]
+    assert T.bool_from_masks(a["state"].gpu_resident).all() and not any(m.any() for _, _, m in a["state"].peers)
+    hbm = c.from_device(info[TIER_HBM].device_ptr, n << 21, np.uint8).reshape(n * 512, 4096)
+    assert np.array_equal(hbm[resident0], truth[resident0]), "bytes after gathering everything on this GPU"
+    assert not hbm[~resident0].any(), "first-touched pages are zero"
+    staged = np.zeros(n * 512, bool)
+    for k, (_, direct) in enumerate(peers):
+        if not direct:
+            staged |= on_peer[k]
+    assert np.array_equal(views[TIER_DRAM][staged], truth[staged]), "the staging pages on node 0 hold the first hop"
+    # and out again: everything to DRAM (the source is this GPU now)
+    rq["dest_tier"] = TIER_DRAM
+    b = c.make_resident(rq, None, None, layout, ds, execute=True)
+    assert np.array_equal(views[TIER_DRAM][resident0], truth[resident0]) and not views[TIER_DRAM][~resident0].any()
+    assert int(b["results"]["migrated"][:, 2].sum()) == n * 512
+    # a page on a peer moves to the CXL node without touching this GPU
+    st1 = ds.download()
+    st1.cpu_resident0[:] = 0
+    st1.peers[0][2][:] = np.uint64(0xFFFFFFFFFFFFFFFF)
+    ds.upload(st1)
+    put(peer_ptrs[0], np.ones(n * 512, bool))
+    rq["dest_tier"] = TIER_CXL
+    d = c.make_resident(rq, None, None, layout, ds, execute=True)
+    assert int(d["results"]["migrated_peer"][:, 0].sum()) == n * 512 and np.array_equal(views[TIER_CXL], truth)
+    ds.free()
+
+
+def test_moves_from_other_gpus_are_byte_exact_alias_arenas():
+    """Two more arenas of this GPU registered as UVMTIER_TIER_PEER0 / PEER0 + 1 stand in for two other GPUs (one with
+    direct copy access, one without): the same mechanism uvmtier_tier_map_peer sets up with a real peer's arena."""
+    import ctypes
+    n = 32
+    with uvmtier.Context(0) as c:
+        ptrs = [c.alloc(n << 21), c.alloc(n << 21)]
+        try:
+            for k, p in enumerate(ptrs):
+                uvmtier._check(uvmtier.lib().uvmtier_tier_register(c.handle, ctypes.c_uint32(uvmtier.TIER_PEER0 + k), ctypes.c_void_p(p),
+                                                                  None, ctypes.c_uint64(n << 21)), "tier_register")
+            _moves_with_peers(c, ptrs, None, ((2, True), (6, False)), gpu_id=4, n=n)
+        finally:
+            for k, p in enumerate(ptrs):
+                c.tier_destroy(uvmtier.TIER_PEER0 + k)
+                c.free(p)
+
+
+def test_moves_from_a_second_gpu_are_byte_exact():
+    """The same with GPU 1's HBM arena mapped through uvmtier_tier_map_peer (pages cross NVLink).  Skipped on a one-GPU box."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    n = 32
+    with uvmtier.Context(0) as c, uvmtier.Context(1) as peer:
+        pinfo = peer.tier_create(TIER_HBM, n << 21)
+        c.tier_map_peer(0, peer)
+        try:
+            _moves_with_peers(c, [pinfo.device_ptr], None, ((2, True),), gpu_id=1, n=n)
+        finally:
+            c.tier_destroy(uvmtier.TIER_PEER0)
+
+
+def test_servicing_passes_refuse_tables_with_other_gpus():
+    import ctypes
+    lib = uvmtier.lib()
+    pk, tbl, lay = TG.fault_trace(512, 3, "uniform", 1, total_va_bytes=64 << 21)
+    gp = TG.gpu_params(256)
+    layout = S.make_layout(lay)
+    with uvmtier.Context(0) as c:
+        c.fault_buffer_init(gp, tbl)
+        ds = c.block_state_alloc(layout)
+        ds.add_peer(3, True)
+        one = c.alloc(4096)
+        try:
+            st = lib.uvmtier_service_fault_batches_device(c.handle, ctypes.c_uint32(2), uvmtier.P(one), uvmtier.P(one), uvmtier.P(one),
+                                                          uvmtier.P(layout), ctypes.byref(ds.ptrs), uvmtier.P(one), uvmtier.P(one),
+                                                          uvmtier.P(one), ctypes.c_uint32(1), uvmtier.P(one))
+            assert st == 0x56                                    # NV_ERR_NOT_SUPPORTED
+            # ids ascend, differ from this GPU's, and four is the limit
+            assert lib.uvmtier_block_state_add_peer(c.handle, uvmtier.P(layout), ctypes.byref(ds.ptrs), ctypes.c_uint32(2), ctypes.c_int(1)) == 0x1F
+            assert lib.uvmtier_block_state_add_peer(c.handle, uvmtier.P(layout), ctypes.byref(ds.ptrs), ctypes.c_uint32(int(layout["gpu_id"][0])),
+                                                    ctypes.c_int(1)) == 0x1F
+            for g in (5, 6, 7):
+                ds.add_peer(g, False)
+            assert lib.uvmtier_block_state_add_peer(c.handle, uvmtier.P(layout), ctypes.byref(ds.ptrs), ctypes.c_uint32(9), ctypes.c_int(1)) != 0
+            assert ds.ptrs.n_peers == 4 and ds.ptrs.peer_direct == 1
+        finally:
+            c.free(one)
+            ds.free()

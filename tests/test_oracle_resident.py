@@ -125,6 +125,52 @@ def test_oracle_matches_the_reference_make_resident(seed, rdup):
     assert int(res["first_touch"].sum()) > 100 and int(res["unmapped"].sum()) > 50
 
 
+@pytest.mark.parametrize("seed,gpu_id,peers", [(21, 1, ((3, True),)), (22, 4, ((2, True), (6, True))), (23, 2, ((1, False), (5, True))),
+                                               (24, 3, ((1, True), (2, False), (7, False), (9, True))), (25, 9, ((4, False),))])
+def test_oracle_matches_the_reference_with_other_gpus(seed, gpu_id, peers):
+    """M2 with several GPUs in the table: sources closest first (the other GPUs in ascending id before the CPU for a GPU
+    destination, uvm_va_space.c:1879-1924), pages held only by a GPU without direct access staged through CPU pages
+    (pages_staged uvm_va_block.c:3140-3170 -- block_populate_pages is compiled verbatim too -- and the two hops
+    :4754-4829), CPU destinations fed by every GPU, every other holder losing the pages afterwards."""
+    ref = T.load_ref("resident")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_resident.so not built (needs /root/reference)")
+    n_slots = 160
+    st0 = R.with_peers(_state(n_slots, seed, False), seed, peers)
+    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3, evict_cause_frac=0.3)
+    want = R.run_ref(ref, rq, pm, pf, st0, gpu_id=gpu_id)
+    got = R.run_oracle(T.load_oracle(), rq, pm, pf, st0, gpu_id=gpu_id)
+    R.assert_equal(want, got, "reference vs restatement with peers, seed %d" % seed)
+    res = want["results"]
+    assert int(res["migrated_peer"].sum()) > 300
+    staged = any(not d for _, d in peers)
+    src = (want["runs"]["bits"][:want["n_runs"]] >> 10) & 7
+    dst = want["runs"]["bits"][:want["n_runs"]] >> 14
+    # a staged page makes two runs: peer -> DRAM, then DRAM -> HBM
+    assert (int(((src >= 3) & (src < 7) & (dst == 1)).sum()) > 20) or not staged
+
+
+@pytest.mark.parametrize("seed,gpu_id,peers", [(31, 1, ((3, True),)), (32, 4, ((2, True), (6, True))), (33, 2, ((1, False), (5, True))),
+                                               (34, 3, ((1, True), (2, False), (7, False), (9, True))), (35, 9, ((4, False),)),
+                                               (36, 5, ((1, False), (2, False), (3, False), (4, False)))])
+def test_simt_make_resident_with_other_gpus_matches_oracle(seed, gpu_id, peers):
+    """The product kernel (under the emulator) on tables that name other GPUs: same masks, counts and copy runs as the
+    restatement, which the test above holds against the reference's code."""
+    n_slots = 128
+    st0 = R.with_peers(_state(n_slots, seed, False), seed, peers)
+    rq, pm, pf = R.random_requests(n_slots, seed, frac=0.9, bad=3, evict_cause_frac=0.3)
+    want = R.run_oracle(T.load_oracle(), rq, pm, pf, st0, gpu_id=gpu_id)
+    got = R.run_simt(T.load_simt(), rq, pm, pf, st0, gpu_id=gpu_id)
+    R.assert_equal(want, got, "emulator vs restatement with peers, seed %d" % seed)
+    assert int(want["results"]["migrated_peer"].sum()) > 300
+    # read duplication is not defined for such tables: the request is rejected, nothing changes
+    st1 = st0.copy().enable_read_duplication()
+    rq1 = _one(st1, slot=0, region_first=0, region_outer=512, dest_tier=R.TIER_HBM, cause=R.CAUSE_API_MIGRATE, flags=R.MR_READ_DUPLICATE)
+    for run in (R.run_oracle(T.load_oracle(), rq1, None, None, st1, gpu_id=gpu_id), R.run_simt(T.load_simt(), rq1, None, None, st1, gpu_id=gpu_id)):
+        assert run["results"]["slot"][0] == 0xFFFFFFFF
+        run["state"].assert_equal(st1, "rejected request")
+
+
 def test_reference_cpu_page_copy_loop_is_byte_exact():
     """libref_copy.so = block_copy_pages (uvm_va_block.c:3946-3991) compiled verbatim with kmap -> identity: copies the
     pages of a region of every va_block, one memcpy(PAGE_SIZE) per page, and marks them dirty at the destination."""

@@ -600,10 +600,26 @@ typedef struct {
     uint64_t  clock;                 /* sequence numbers handed out so far */
     uint32_t  n_slots;
     uint32_t  capacity_chunks;       /* root chunks HBM can hold: what the caller keeps chunks_in_use below */
+    /* uvmtier_pmm_enable_chunk_table: the HBM arena holds capacity_chunks chunks of 2 MB instead of one per va_block;
+     * d_chunk_of_slot[slot] = the chunk behind the va_block (0xFFFFFFFF = none), d_free_bits = one bit per chunk.  NULL:
+     * the arena is VA-sized and slot s lives at s * 2 MB. */
+    uint32_t *d_chunk_of_slot;
+    uint32_t *d_free_bits;
+    uint64_t *d_dram_stamp;          /* [n_slots]: round of the tiered loop in which the va_block's pages last reached DRAM
+                                        from HBM (0 = never / none left there): the order of DRAM -> CXL demotion */
+    uint64_t  round;                 /* rounds of the tiered loop so far */
 } uvmtier_pmm_t;
 NV_STATUS uvmtier_pmm_create(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *layout, uint32_t capacity_chunks,
                              uvmtier_pmm_t *out);
 NV_STATUS uvmtier_pmm_destroy(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm);
+/* Puts root chunks behind the va_blocks (block_populate_gpu_chunk, UVM/uvm_va_block.c:2974-3049; the free after an
+ * eviction, UVM/uvm_pmm_gpu.c:1290-1380): from now on a va_block takes one of the capacity_chunks 2 MB chunks of the HBM
+ * arena when its first page arrives on the GPU (the "note" calls below hand it out) and gives it back when an eviction
+ * empties it, and every copy of this context that names the HBM tier through copy runs (uvmtier_copy_runs_device, the
+ * tiered loop) goes to chunk_of_slot[slot] * 2 MB + page * 4 KB.  The HBM tier then needs capacity_chunks * 2 MB, not the
+ * size of the VA.  Call it on a table without GPU-resident pages (all stamps 0), once per context; which chunk a
+ * va_block gets is arbitrary.  The table belongs to pmm; uvmtier_pmm_destroy detaches it. */
+NV_STATUS uvmtier_pmm_enable_chunk_table(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm);
 /* The list moves of one servicing pass (d_service as written by uvmtier_service_fault_batches_device for
  * n_batches batches): every serviced run moves its va_block to the tail of va_block_used. */
 NV_STATUS uvmtier_pmm_note_service_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
@@ -632,18 +648,28 @@ NV_STATUS uvmtier_block_state_count_pages_device(uvmtier_ctx_t *ctx, const uvmti
                                                  const uvmtier_block_state_t *state, uint32_t *d_out);
 
 /* Servicing under HBM oversubscription (BASELINE config D): the preprocessed batches are serviced in chunks of
- * chunk_batches batches; before a chunk is serviced, room is made for the root chunks it needs --
- *     k = chunks in use + chunks needed - pmm->capacity_chunks  victims
- * are picked in the reference's order (pick_root_chunk_to_evict), evicted with make_resident (cause EVICTION) and
- * their pages copied out; then the chunk is serviced and its pages copied in.  The reference evicts on demand, one
- * root chunk at a time, when block_populate_gpu_chunk finds no free chunk (UVM/uvm_pmm_gpu.c:1502-1560); evicting a
- * chunk's worth ahead takes the same victims from the same lists as long as no victim is faulted on again within the
- * chunk of batches (then the reference would have evicted it a little later) -- chunk_batches = 1 is the closest.
- * Where evicted pages go is this library's policy, the reference has none: host DRAM while it holds
- * fewer than dram_capacity_pages pages of this table, the CXL node after that.
+ * chunk_batches batches ("rounds"); before a round is serviced, room is made for the root chunks it needs.  With
+ *     overflow = chunks in use + va_blocks the round faults on that hold no chunk - pmm->capacity_chunks
+ * victims are taken in the reference's order (pick_root_chunk_to_evict: ascending stamp) until `overflow` of them are
+ * va_blocks the round does not fault on -- a victim the round faults on needs a chunk again at once, so it frees
+ * nothing -- then evicted with make_resident (cause EVICTION) and their pages copied out; then the round is serviced
+ * and its pages copied in.  The reference evicts on demand, one root chunk at a time, when block_populate_gpu_chunk
+ * finds no free chunk and retries the block (NV_ERR_MORE_PROCESSING_REQUIRED, UVM/uvm_va_block.h:736-745,
+ * UVM/uvm_pmm_gpu.c:1502-1560); evicting a round's worth ahead takes the same victims from the same lists as long as
+ * no victim is faulted on again within the round (then the reference would have evicted it a little later) --
+ * chunk_batches = 1 is the closest.  A round that alone faults on more va_blocks than HBM has chunks is serviced over
+ * capacity and counted (not allowed with a chunk table: chunk_batches * max_batch_size <= capacity_chunks then).
+ * Where evicted pages go is this library's policy, the reference has none: host DRAM while it then holds
+ * at most dram_capacity_pages pages of this table, else the CXL node; with UVMTIER_TIERED_DEMOTE room is first made in
+ * DRAM by moving the DRAM pages of the va_blocks that left HBM longest ago (never-promoted ones first; not those the
+ * round faults on) to the CXL node, so that DRAM keeps the warmer pages.
+ * Every decision of a round is taken on the device (counts, weighted radix selection over the stamps, request lists,
+ * copy lists): the call enqueues the whole trace and synchronises once at the end.
  * d_entry_flags / d_service / d_batches are filled as by uvmtier_service_fault_batches_device; the copy runs are
- * consumed chunk by chunk (execute_copies != 0 runs them through uvmtier_copy_runs_device: the tiers must exist),
- * record.run_offset counts within the record's chunk.  Synchronises once per chunk (two counters cross to the host). */
+ * consumed round by round (UVMTIER_TIERED_EXECUTE_COPIES runs them: the tiers must exist), record.run_offset counts
+ * within the record's round. */
+#define UVMTIER_TIERED_EXECUTE_COPIES 1
+#define UVMTIER_TIERED_DEMOTE         2
 typedef struct {
     uint32_t passes;                 /* chunks of batches serviced */
     uint32_t eviction_waves;
@@ -652,14 +678,15 @@ typedef struct {
     uint64_t pages_evicted, pages_promoted;     /* pages copied out of / into HBM (first touch included) */
     uint32_t overcommitted_passes;              /* chunks of batches that alone needed more root chunks than HBM holds:
                                                    everything else was evicted and they were serviced over capacity */
-    uint32_t reserved[3];
+    uint32_t blocks_demoted;                    /* va_blocks whose DRAM pages were moved to the CXL node */
+    uint32_t reserved[2];
 } uvmtier_tiering_stats_t;
 NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
                                                       const uvmtier_ordered_fault_t *d_ordered,
                                                       const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
                                                       const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
                                                       uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
-                                                      uint32_t chunk_batches, uint64_t dram_capacity_pages, int execute_copies,
+                                                      uint32_t chunk_batches, uint64_t dram_capacity_pages, int flags,
                                                       uvmtier_tiering_stats_t *out_stats);
 
 /* ------------------------------------------------------------------------------------------ */

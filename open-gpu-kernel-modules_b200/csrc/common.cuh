@@ -125,5 +125,14 @@ static inline NV_STATUS uvmtier_status_from_cuda(cudaError_t e)
 
 // Makes sure ctx->d_stage / h_stage hold at least `bytes`.
 NV_STATUS uvmtier_stage_reserve(uvmtier_ctx_t *ctx, size_t d_bytes, size_t h_bytes);
+// internal, for the tiered loop (pmm.cu): calls whose sizes are decided on the device
+NV_STATUS uvmtier_make_resident_counted(uvmtier_ctx_t *ctx, uint32_t n_requests, const uint32_t *n_requests_dev,
+                                        const uvmtier_make_resident_req_t *d_requests, const uvmtier_page_mask_t *d_page_masks,
+                                        const uvmtier_page_mask_t *d_prefetch_masks, const uvmtier_va_layout_t *lay,
+                                        const uvmtier_block_state_t *state, uvmtier_make_resident_result_t *d_results,
+                                        uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters);
+NV_STATUS uvmtier_copy_runs_enqueue(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs, uint32_t run_cap,
+                                    uint64_t max_pages, uint32_t pair_mask);
+void uvmtier_tiers_set_chunk_table(uvmtier_ctx_t *ctx, const uint32_t *chunk_of_slot);
 
 static inline size_t uvmtier_align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }

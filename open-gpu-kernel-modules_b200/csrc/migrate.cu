@@ -34,6 +34,8 @@ struct uvmtier_tiers {
     uint32_t list_cap;
     uint32_t *h_list_count;   // pinned
     bool smem_attr_set;
+    const uint32_t *chunk_of_slot;   // slot -> 2 MB chunk of the HBM arena (owned by a uvmtier_pmm_t); NULL = arena is VA-sized
+    uint64_t *d_lists_dst;           // destination offsets when they differ from the source offsets (chunk table); list_cap entries
 };
 
 static uvmtier_tiers *tiers_get(uvmtier_ctx_t *ctx)
@@ -67,6 +69,8 @@ void uvmtier_tiers_destroy(uvmtier_ctx_t *ctx)
         tier_release(ctx, &ctx->tiers->t[i]);
     if (ctx->tiers->d_lists)
         cudaFree(ctx->tiers->d_lists);
+    if (ctx->tiers->d_lists_dst)
+        cudaFree(ctx->tiers->d_lists_dst);
     if (ctx->tiers->d_list_count)
         cudaFree(ctx->tiers->d_list_count);
     if (ctx->tiers->h_list_count)
@@ -310,6 +314,7 @@ NV_STATUS uvmtier_copy_page_list_device(uvmtier_ctx_t *ctx, uint32_t dst_tier, u
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     copy_list_params p;
+    memset(&p, 0, sizeof(p));
     p.src_base = (const uint8_t *)ctx->tiers->t[src_tier].info.device_ptr;
     p.dst_base = (uint8_t *)ctx->tiers->t[dst_tier].info.device_ptr;
     p.src_off = d_src_off;
@@ -340,6 +345,49 @@ NV_STATUS uvmtier_copy_page_list(uvmtier_ctx_t *ctx, uint32_t dst_tier, uint32_t
     return NV_OK;
 }
 
+// The (source, destination) pairs in execution order: the peer GPUs first -- a page staged through DRAM (peer -> DRAM,
+// then DRAM -> HBM, UVM/uvm_va_block.c:4754-4829) needs its first hop done before the DRAM -> HBM pair runs -- then
+// DRAM, CXL, HBM, zero fill.
+static const uint32_t kSrcTierOf[8] = {UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL, UVMTIER_TIER_HBM, UVMTIER_TIER_PEER0,
+                                       UVMTIER_TIER_PEER0 + 1, UVMTIER_TIER_PEER0 + 2, UVMTIER_TIER_PEER0 + 3, 0};
+static const uint32_t kDstTierOf[3] = {UVMTIER_TIER_HBM, UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL};
+static const uint32_t kSrcOrder[8] = {3, 4, 5, 6, 0, 1, 2, 7};
+
+static NV_STATUS copy_lists_reserve(uvmtier_ctx_t *ctx, uint64_t pages)
+{
+    uvmtier_tiers *ts = ctx->tiers;
+    if (!ts->d_list_count)
+        UVMTIER_CUDA(cudaMalloc(&ts->d_list_count, (3 * kRunPairs + 1) * sizeof(uint32_t)));
+    if (!ts->h_list_count)
+        UVMTIER_CUDA(cudaHostAlloc(&ts->h_list_count, kRunPairs * sizeof(uint32_t), cudaHostAllocPortable));
+    if (pages > 0xffffffffull)
+        return NV_ERR_INVALID_ARGUMENT;
+    const bool two = ts->chunk_of_slot != NULL;
+    if (pages > ts->list_cap || (two && !ts->d_lists_dst)) {
+        UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+        if (ts->d_lists) UVMTIER_CUDA(cudaFree(ts->d_lists));
+        if (ts->d_lists_dst) UVMTIER_CUDA(cudaFree(ts->d_lists_dst));
+        ts->d_lists = ts->d_lists_dst = NULL;
+        const uint64_t keep = pages > ts->list_cap ? pages + pages / 4 + 4096 : ts->list_cap;
+        ts->list_cap = 0;
+        UVMTIER_CUDA(cudaMalloc(&ts->d_lists, keep * sizeof(uint64_t)));
+        if (two)
+            UVMTIER_CUDA(cudaMalloc(&ts->d_lists_dst, keep * sizeof(uint64_t)));
+        ts->list_cap = (uint32_t)(keep < 0xffffffffull ? keep : 0xffffffffull);
+    }
+    return NV_OK;
+}
+
+} // extern "C"
+
+void uvmtier_tiers_set_chunk_table(uvmtier_ctx_t *ctx, const uint32_t *chunk_of_slot)
+{
+    if (tiers_get(ctx))
+        ctx->tiers->chunk_of_slot = chunk_of_slot;
+}
+
+extern "C" {
+
 NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs,
                                    uint32_t run_cap, int method)
 {
@@ -351,10 +399,9 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
         return NV_OK;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     uvmtier_tiers *ts = ctx->tiers;
-    if (!ts->d_list_count)
-        UVMTIER_CUDA(cudaMalloc(&ts->d_list_count, 2 * kRunPairs * sizeof(uint32_t)));
-    if (!ts->h_list_count)
-        UVMTIER_CUDA(cudaHostAlloc(&ts->h_list_count, kRunPairs * sizeof(uint32_t), cudaHostAllocPortable));
+    NV_STATUS st = copy_lists_reserve(ctx, 0);
+    if (st != NV_OK)
+        return st;
     uint32_t *d_pair_count = ts->d_list_count, *d_pair_cursor = ts->d_list_count + kRunPairs;
     UVMTIER_CUDA(cudaMemsetAsync(ts->d_list_count, 0, 2 * kRunPairs * sizeof(uint32_t), ctx->stream));
     size_t grid = ((size_t)run_cap + 255) / 256, cap = (size_t)ctx->sm_count * 8;
@@ -373,42 +420,28 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
     }
     if (!total)
         return NV_OK;
-    if (total > 0xffffffffull)
-        return NV_ERR_INVALID_ARGUMENT;
-    if (total > ts->list_cap) {
-        if (ts->d_lists) {
-            UVMTIER_CUDA(cudaFree(ts->d_lists));
-            ts->d_lists = NULL;
-            ts->list_cap = 0;
-        }
-        const uint64_t want = total + total / 4 + 4096;
-        UVMTIER_CUDA(cudaMalloc(&ts->d_lists, want * sizeof(uint64_t)));
-        ts->list_cap = (uint32_t)(want < 0xffffffffull ? want : 0xffffffffull);
-    }
+    st = copy_lists_reserve(ctx, total);
+    if (st != NV_OK)
+        return st;
+    uint64_t *list_dst = ts->chunk_of_slot ? ts->d_lists_dst : ts->d_lists;
     UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, bases, d_pair_cursor, ts->d_lists,
-                   ts->list_cap);
-    static const uint32_t src_tier_of[8] = {UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL, UVMTIER_TIER_HBM, UVMTIER_TIER_PEER0,
-                                            UVMTIER_TIER_PEER0 + 1, UVMTIER_TIER_PEER0 + 2, UVMTIER_TIER_PEER0 + 3, 0};
-    static const uint32_t dst_tier_of[3] = {UVMTIER_TIER_HBM, UVMTIER_TIER_DRAM, UVMTIER_TIER_CXL};
-    // Sources in this order: the peer GPUs first -- a page staged through DRAM (peer -> DRAM, then DRAM -> HBM,
-    // UVM/uvm_va_block.c:4754-4829) needs its first hop done before the DRAM -> HBM pair runs -- then DRAM, CXL, HBM, zero fill.
-    static const uint32_t src_order[8] = {3, 4, 5, 6, 0, 1, 2, 7};
+                   ts->list_cap, ts->chunk_of_slot ? ts->d_lists_dst : (uint64_t *)NULL, ts->chunk_of_slot, (const uint32_t *)NULL);
     for (uint32_t step = 0; step < kRunPairs; step++) {
-        const uint32_t pair = src_order[step / 3] * 3 + step % 3;
+        const uint32_t pair = kSrcOrder[step / 3] * 3 + step % 3;
         const uint32_t n = ts->h_list_count[pair];
         if (!n)
             continue;
-        const uint32_t src = pair / 3, dst_tier = dst_tier_of[pair % 3];
+        const uint32_t src = pair / 3, dst_tier = kDstTierOf[pair % 3];
         if (!ts->t[dst_tier].used)
             return NV_ERR_INVALID_STATE;
         uint8_t *dst_base = (uint8_t *)ts->t[dst_tier].info.device_ptr;
-        const uint64_t *list = ts->d_lists + bases.base[pair];
         if (src == UVMTIER_RUN_SRC_ZERO) {                // first touch: zero fill at the destination
             const uint32_t zg = n < (uint32_t)ctx->sm_count * 16 ? n : (uint32_t)ctx->sm_count * 16;
-            UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, dst_base, list, (uint64_t)n, 1u);
+            UVMTIER_LAUNCH(k_zero_pages, (int)zg, 256, 0, ctx->stream, dst_base, (const uint64_t *)(list_dst + bases.base[pair]),
+                           (uint64_t)n, 1u, (const uint32_t *)NULL, (const uint32_t *)NULL);
             continue;
         }
-        const uint32_t src_tier = src_tier_of[src];
+        const uint32_t src_tier = kSrcTierOf[src];
         if (src_tier == dst_tier) {
             uvmtier_set_error("uvmtier_copy_runs_device: a run names the same tier as source and destination",
                               cudaErrorInvalidValue, __FILE__, __LINE__);
@@ -417,18 +450,86 @@ NV_STATUS uvmtier_copy_runs_device(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t 
         if (!ts->t[src_tier].used)
             return NV_ERR_INVALID_STATE;
         copy_list_params p;
+        memset(&p, 0, sizeof(p));
         p.src_base = (const uint8_t *)ts->t[src_tier].info.device_ptr;
         p.dst_base = dst_base;
-        p.src_off = list;
-        p.dst_off = list;
+        p.src_off = ts->d_lists + bases.base[pair];
+        p.dst_off = list_dst + bases.base[pair];
         p.n_pages = n;
         p.pieces_per_page = 1;
-        NV_STATUS st = launch_copy(ctx, p, method);
+        st = launch_copy(ctx, p, method);
         if (st != NV_OK)
             return st;
     }
     return NV_OK;
 }
+
+} // extern "C"
+
+// The same without a round trip to the host, for callers that enqueue many small lists back to back (the tiered loop):
+// the page counts stay on the device, the list is sized for max_pages pages (more are dropped and reported through
+// *d_overflow), and every pair named in pair_mask (bit = src * 3 + dst) gets a launch whether it has pages or not.
+NV_STATUS uvmtier_copy_runs_enqueue(uvmtier_ctx_t *ctx, const uvmtier_copy_run_t *d_runs, const uint32_t *d_n_runs, uint32_t run_cap,
+                                    uint64_t max_pages, uint32_t pair_mask)
+{
+    if (!ctx || !d_runs || !d_n_runs)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!ctx->tiers)
+        return NV_ERR_INVALID_STATE;
+    if (!run_cap || !max_pages)
+        return NV_OK;
+    uvmtier_tiers *ts = ctx->tiers;
+    NV_STATUS st = copy_lists_reserve(ctx, max_pages);
+    if (st != NV_OK)
+        return st;
+    uint32_t *d_pair_count = ts->d_list_count, *d_pair_cursor = ts->d_list_count + kRunPairs, *d_bases = ts->d_list_count + 2 * kRunPairs;
+    UVMTIER_CUDA(cudaMemsetAsync(ts->d_list_count, 0, 2 * kRunPairs * sizeof(uint32_t), ctx->stream));
+    size_t grid = ((size_t)run_cap + 255) / 256, cap = (size_t)ctx->sm_count * 8;
+    if (grid > cap)
+        grid = cap;
+    UVMTIER_LAUNCH(k_count_run_pages, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, d_pair_count);
+    UVMTIER_LAUNCH(k_pair_bases, 1, 32, 0, ctx->stream, (const uint32_t *)d_pair_count, d_bases);
+    run_pair_bases unused;
+    memset(&unused, 0, sizeof(unused));
+    uint64_t *list_dst = ts->chunk_of_slot ? ts->d_lists_dst : ts->d_lists;
+    UVMTIER_LAUNCH(k_expand_runs, (int)grid, 256, 0, ctx->stream, d_runs, d_n_runs, run_cap, unused, d_pair_cursor, ts->d_lists,
+                   ts->list_cap, ts->chunk_of_slot ? ts->d_lists_dst : (uint64_t *)NULL, ts->chunk_of_slot, (const uint32_t *)d_bases);
+    const size_t smem = (size_t)kStages * kStageBytes;
+    if (!ts->smem_attr_set) {
+        UVMTIER_CUDA(cudaFuncSetAttribute(k_copy_pages_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        ts->smem_attr_set = true;
+    }
+    for (uint32_t step = 0; step < kRunPairs; step++) {
+        const uint32_t pair = kSrcOrder[step / 3] * 3 + step % 3;
+        if (!((pair_mask >> pair) & 1u))
+            continue;
+        const uint32_t src = pair / 3, dst_tier = kDstTierOf[pair % 3];
+        if (!ts->t[dst_tier].used)
+            return NV_ERR_INVALID_STATE;
+        uint8_t *dst_base = (uint8_t *)ts->t[dst_tier].info.device_ptr;
+        if (src == UVMTIER_RUN_SRC_ZERO) {
+            UVMTIER_LAUNCH(k_zero_pages, ctx->sm_count * 8, 256, 0, ctx->stream, dst_base, (const uint64_t *)list_dst, (uint64_t)0, 1u,
+                           (const uint32_t *)(d_pair_count + pair), (const uint32_t *)(d_bases + pair));
+            continue;
+        }
+        const uint32_t src_tier = kSrcTierOf[src];
+        if (src_tier == dst_tier || !ts->t[src_tier].used)
+            return NV_ERR_INVALID_STATE;
+        copy_list_params p;
+        memset(&p, 0, sizeof(p));
+        p.src_base = (const uint8_t *)ts->t[src_tier].info.device_ptr;
+        p.dst_base = dst_base;
+        p.src_off = ts->d_lists;
+        p.dst_off = list_dst;
+        p.pieces_per_page = 1;
+        p.n_pages_dev = d_pair_count + pair;
+        p.list_base_dev = d_bases + pair;
+        UVMTIER_LAUNCH(k_copy_pages_tma, ctx->sm_count * (int)kCtasPerSm, kCopyThreads, smem, ctx->stream, p);
+    }
+    return NV_OK;
+}
+
+extern "C" {
 
 NV_STATUS uvmtier_checksum_pages_device(uvmtier_ctx_t *ctx, uint32_t tier, size_t n, const uint64_t *d_off, uint32_t page_size,
                                         uint64_t *d_out)
@@ -711,8 +812,7 @@ NV_STATUS uvmtier_p2p_cxl_dma_request(uvmtier_ctx_t *ctx, uvmtier_cxl_buffer_t *
     if ((((uintptr_t)dst | (uintptr_t)src) & 15u) == 0) {
         // whole 4 KB pieces through the TMA pipeline: 2 MB "pages" first (one list-free linear range), then 4 KB ones
         copy_list_params p;
-        p.src_off = NULL;
-        p.dst_off = NULL;
+        memset(&p, 0, sizeof(p));
         const uint64_t big = bytes >> 21, small = (bytes - (big << 21)) >> 12;
         if (big) {
             p.src_base = src; p.dst_base = dst; p.n_pages = big; p.pieces_per_page = 512;

@@ -32,7 +32,22 @@ struct copy_list_params {
     const uint64_t *dst_off;
     uint64_t n_pages;
     uint32_t pieces_per_page;    // page_size / 4096
+    // device-resident overrides (NULL = use the values above): the page count, and the index at which this copy's
+    // segment starts in src_off / dst_off -- lets a caller enqueue copies whose size is decided by an earlier kernel
+    const uint32_t *n_pages_dev;
+    const uint32_t *list_base_dev;
 };
+
+__device__ __forceinline__ void copy_params_resolve(copy_list_params &p)
+{
+    if (p.n_pages_dev)
+        p.n_pages = *p.n_pages_dev;
+    if (p.list_base_dev) {
+        const uint32_t b = *p.list_base_dev;
+        if (p.src_off) p.src_off += b;
+        if (p.dst_off) p.dst_off += b;
+    }
+}
 
 // ---- thin PTX wrappers ----
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -88,6 +103,7 @@ __device__ __forceinline__ void piece_addr(const copy_list_params &p, uint64_t u
 __global__ void __launch_bounds__(kCopyThreads, kCtasPerSm) k_copy_pages_tma(copy_list_params p)
 {
     extern __shared__ __align__(128) uint8_t smem[];
+    copy_params_resolve(p);
     __shared__ __align__(8) uint64_t full[kStages];
     __shared__ uint8_t *s_dst[kStages][kPiecesPerStage];
     const int lane = threadIdx.x;
@@ -185,6 +201,7 @@ __global__ void __launch_bounds__(kCopyThreads, kCtasPerSm) k_copy_pages_tma(cop
 // Comparison kernel: every thread moves 16-byte vectors with plain loads/stores (the pre-TMA way).
 __global__ void __launch_bounds__(256) k_copy_pages_ldst(copy_list_params p)
 {
+    copy_params_resolve(p);
     const uint64_t n_pieces = p.n_pages * p.pieces_per_page;
     for (uint64_t u = blockIdx.x; u < n_pieces; u += gridDim.x) {
         const uint8_t *src;
@@ -196,8 +213,11 @@ __global__ void __launch_bounds__(256) k_copy_pages_ldst(copy_list_params p)
 }
 
 // Zero-fill of 4 KB pieces (first-touch population, UVM/uvm_va_block.c:3011).
-__global__ void __launch_bounds__(256) k_zero_pages(uint8_t *base, const uint64_t *off, uint64_t n_pages, uint32_t pieces_per_page)
+__global__ void __launch_bounds__(256) k_zero_pages(uint8_t *base, const uint64_t *off, uint64_t n_pages, uint32_t pieces_per_page,
+                                                    const uint32_t *n_pages_dev = NULL, const uint32_t *list_base_dev = NULL)
 {
+    if (n_pages_dev) n_pages = *n_pages_dev;
+    if (list_base_dev) off += *list_base_dev;
     const uint64_t n_pieces = n_pages * pieces_per_page;
     for (uint64_t u = blockIdx.x; u < n_pieces; u += gridDim.x) {
         const uint64_t page = u / pieces_per_page;
@@ -238,8 +258,13 @@ __global__ void __launch_bounds__(256) k_count_run_pages(const uvmtier_copy_run_
 // Pass 2: expands the runs into one page-offset list, pair after pair: for run r, page j the offset
 // slot * 2 MB + (first_page + j) * 4 KB (the same offset in every tier's arena).  One thread per run; a run's pages
 // are appended to its pair's segment with one atomicAdd.
+// With a chunk table (HBM arena smaller than the VA, pmm_kernels.cuh) an HBM offset is chunk_of_slot[slot] * 2 MB + ... and
+// the source and destination offsets of a page differ: list_dst is then a second array (else list_dst == list).
+// bases_dev != NULL: the segment starts are read from the device (k_pair_bases) instead of `bases`.
 __global__ void __launch_bounds__(256) k_expand_runs(const uvmtier_copy_run_t *runs, const uint32_t *n_runs_dev, uint32_t run_cap,
-                                                     run_pair_bases bases, uint32_t *pair_cursor, uint64_t *list, uint32_t list_cap)
+                                                     run_pair_bases bases, uint32_t *pair_cursor, uint64_t *list, uint32_t list_cap,
+                                                     uint64_t *list_dst = NULL, const uint32_t *chunk_of_slot = NULL,
+                                                     const uint32_t *bases_dev = NULL)
 {
     const uint32_t n_runs = min(*n_runs_dev, run_cap);
     for (uint32_t r = blockIdx.x * blockDim.x + threadIdx.x; r < n_runs; r += gridDim.x * blockDim.x) {
@@ -247,12 +272,37 @@ __global__ void __launch_bounds__(256) k_expand_runs(const uvmtier_copy_run_t *r
         if (!run.num_pages)
             continue;
         const uint32_t pair = run_pair_of(run);
-        const uint32_t at = bases.base[pair] + atomicAdd(&pair_cursor[pair], (uint32_t)run.num_pages);
-        const uint64_t base = (uint64_t)run.slot * UVMTIER_VA_BLOCK_SIZE + (uint64_t)run.first_page * UVMTIER_PAGE_SIZE;
+        const uint32_t at = (bases_dev ? bases_dev[pair] : bases.base[pair]) + atomicAdd(&pair_cursor[pair], (uint32_t)run.num_pages);
+        const uint64_t in_block = (uint64_t)run.first_page * UVMTIER_PAGE_SIZE;
+        const uint64_t base = (uint64_t)run.slot * UVMTIER_VA_BLOCK_SIZE + in_block;
+        uint64_t hbm = base;
+        if (chunk_of_slot) {
+            // a slot without a chunk cannot happen unless the caller let HBM overflow (counted where chunks are handed
+            // out, and the call fails); chunk 0 keeps the copy inside the arena
+            const uint32_t c = chunk_of_slot[run.slot];
+            hbm = (uint64_t)(c == 0xffffffffu ? 0u : c) * UVMTIER_VA_BLOCK_SIZE + in_block;
+        }
+        const uint64_t src0 = run.src == UVMTIER_RUN_SRC_HBM ? hbm : base, dst0 = run.dst == UVMTIER_RUN_DST_HBM ? hbm : base;
         for (uint32_t j = 0; j < run.num_pages; j++)
-            if (at + j < list_cap)
-                list[at + j] = base + (uint64_t)j * UVMTIER_PAGE_SIZE;
+            if (at + j < list_cap) {
+                list[at + j] = src0 + (uint64_t)j * UVMTIER_PAGE_SIZE;
+                if (list_dst)
+                    list_dst[at + j] = dst0 + (uint64_t)j * UVMTIER_PAGE_SIZE;
+            }
     }
+}
+
+// Segment starts of the pairs from their page counts (one thread); bases[kRunPairs] = the total.
+__global__ void k_pair_bases(const uint32_t *pair_count, uint32_t *bases)
+{
+    if (threadIdx.x || blockIdx.x)
+        return;
+    uint32_t total = 0;
+    for (uint32_t p = 0; p < kRunPairs; p++) {
+        bases[p] = total;
+        total += pair_count[p];
+    }
+    bases[kRunPairs] = total;
 }
 
 // One 64-bit value per page: xor-rotate-multiply over the page's 64-bit words in order.

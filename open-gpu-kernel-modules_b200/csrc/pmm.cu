@@ -27,7 +27,9 @@ NV_STATUS uvmtier_pmm_create(uvmtier_ctx_t *ctx, const uvmtier_va_layout_t *lay,
     memset(out, 0, sizeof(*out));
     UVMTIER_CUDA(cudaMalloc(&out->d_stamp, n * sizeof(uint64_t)));
     UVMTIER_CUDA(cudaMalloc(&out->d_scratch, pmm_scratch_words((uint32_t)n) * sizeof(uint32_t)));
+    UVMTIER_CUDA(cudaMalloc(&out->d_dram_stamp, n * sizeof(uint64_t)));
     UVMTIER_CUDA(cudaMemsetAsync(out->d_stamp, 0, n * sizeof(uint64_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(out->d_dram_stamp, 0, n * sizeof(uint64_t), ctx->stream));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
     out->n_slots = (uint32_t)n;
     out->capacity_chunks = capacity_chunks;
@@ -41,9 +43,63 @@ NV_STATUS uvmtier_pmm_destroy(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm)
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (pmm->d_chunk_of_slot)
+        uvmtier_tiers_set_chunk_table(ctx, NULL);
     if (pmm->d_stamp) cudaFree(pmm->d_stamp);
     if (pmm->d_scratch) cudaFree(pmm->d_scratch);
+    if (pmm->d_chunk_of_slot) cudaFree(pmm->d_chunk_of_slot);
+    if (pmm->d_free_bits) cudaFree(pmm->d_free_bits);
+    if (pmm->d_dram_stamp) cudaFree(pmm->d_dram_stamp);
     memset(pmm, 0, sizeof(*pmm));
+    return NV_OK;
+}
+
+// d_free_bits: one bit per chunk, then one word that counts allocations that found nothing free
+static uint32_t pmm_free_words(const uvmtier_pmm_t *pmm) { return (pmm->capacity_chunks + 31) / 32; }
+
+static pmm_chunk_table pmm_chunks(const uvmtier_pmm_t *pmm)
+{
+    pmm_chunk_table t;
+    t.chunk_of_slot = pmm->d_chunk_of_slot;
+    t.free_bits = pmm->d_free_bits;
+    t.n_words = pmm->d_chunk_of_slot ? pmm_free_words(pmm) : 0;
+    t.errors = pmm->d_free_bits ? pmm->d_free_bits + pmm_free_words(pmm) : NULL;
+    return t;
+}
+
+NV_STATUS uvmtier_pmm_enable_chunk_table(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm)
+{
+    if (!pmm_ok(ctx, pmm) || !pmm->capacity_chunks)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (pmm->d_chunk_of_slot)
+        return NV_OK;
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    // only on a table without GPU pages: every stamp 0
+    UVMTIER_CUDA(cudaMemsetAsync(pmm->d_scratch, 0, 4 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_LAUNCH(k_pmm_select, 1, kPmmSelectThreads, 0, ctx->stream, (const unsigned long long *)pmm->d_stamp, pmm->n_slots, 1u,
+                   pmm->d_scratch);
+    uint32_t sel[3];
+    UVMTIER_CUDA(cudaMemcpyAsync(sel, pmm->d_scratch, sizeof(sel), cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (sel[2] != 0)
+        return NV_ERR_INVALID_STATE;
+    const uint32_t words = pmm_free_words(pmm);
+    UVMTIER_CUDA(cudaMalloc(&pmm->d_chunk_of_slot, (size_t)pmm->n_slots * sizeof(uint32_t)));
+    UVMTIER_CUDA(cudaMalloc(&pmm->d_free_bits, ((size_t)words + 1) * sizeof(uint32_t)));
+    UVMTIER_CUDA(cudaMemsetAsync(pmm->d_chunk_of_slot, 0xff, (size_t)pmm->n_slots * sizeof(uint32_t), ctx->stream));
+    uint32_t *h = (uint32_t *)malloc(((size_t)words + 1) * sizeof(uint32_t));
+    if (!h)
+        return NV_ERR_NO_MEMORY;
+    for (uint32_t w = 0; w < words; w++) {
+        const uint32_t left = pmm->capacity_chunks - w * 32u;
+        h[w] = left >= 32u ? 0xffffffffu : ((1u << left) - 1u);
+    }
+    h[words] = 0;
+    const cudaError_t e = cudaMemcpy(pmm->d_free_bits, h, ((size_t)words + 1) * sizeof(uint32_t), cudaMemcpyHostToDevice);
+    free(h);
+    UVMTIER_CUDA(e);
+    UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
+    uvmtier_tiers_set_chunk_table(ctx, pmm->d_chunk_of_slot);
     return NV_OK;
 }
 
@@ -65,7 +121,8 @@ NV_STATUS uvmtier_pmm_note_service_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm
     if (grid > (uint64_t)ctx->sm_count * 8)
         grid = (uint64_t)ctx->sm_count * 8;
     UVMTIER_LAUNCH(k_pmm_note_service, (int)grid, kPmmThreads, 0, ctx->stream, n_batches, B, d_batches, d_service,
-                   (unsigned long long *)pmm->d_stamp, pmm->n_slots, (unsigned long long)pmm->clock);
+                   (unsigned long long *)pmm->d_stamp, pmm->n_slots, (unsigned long long)pmm->clock, (unsigned long long *)NULL,
+                   pmm_chunks(pmm));
     pmm->clock += total;
     return NV_OK;
 }
@@ -83,9 +140,12 @@ NV_STATUS uvmtier_pmm_note_make_resident_device(uvmtier_ctx_t *ctx, uvmtier_pmm_
         return NV_ERR_INVALID_ARGUMENT;
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     const uint32_t grid = (n_requests + kPmmThreads - 1) / kPmmThreads;
+    // with a chunk table, a call that both brings va_blocks to the GPU and evicts others hands out chunks while it takes
+    // them back: correct, but the newcomers may not see the chunks freed by the same call
     UVMTIER_LAUNCH(k_pmm_note_make_resident, (int)grid, kPmmThreads, 0, ctx->stream, n_requests, d_requests, d_results,
                    (const uint32_t *)state->gpu_resident, (unsigned long long *)pmm->d_stamp, pmm->n_slots,
-                   (unsigned long long)pmm->clock);
+                   (unsigned long long)pmm->clock, (unsigned long long *)NULL, (const uint32_t *)NULL, pmm_chunks(pmm),
+                   (unsigned long long *)pmm->d_dram_stamp, (unsigned long long)pmm->round, (const uint32_t *)state->cpu_resident[0]);
     pmm->clock += n_requests;
     return NV_OK;
 }
@@ -167,15 +227,18 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                                                       const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
                                                       const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
                                                       uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
-                                                      uint32_t chunk_batches, uint64_t dram_capacity_pages, int execute_copies,
+                                                      uint32_t chunk_batches, uint64_t dram_capacity_pages, int flags,
                                                       uvmtier_tiering_stats_t *out_stats)
 {
     if (out_stats)
         memset(out_stats, 0, sizeof(*out_stats));
     if (!pmm_ok(ctx, pmm) || !lay || !state || !chunk_batches || (size_t)lay->n_spaces * lay->blocks_per_space != pmm->n_slots)
         return NV_ERR_INVALID_ARGUMENT;
+    const bool execute_copies = (flags & UVMTIER_TIERED_EXECUTE_COPIES) != 0, demote = (flags & UVMTIER_TIERED_DEMOTE) != 0;
     if (!ctx->faults || (execute_copies && !ctx->tiers))
         return NV_ERR_INVALID_STATE;
+    if (state->n_peers)
+        return NV_ERR_NOT_SUPPORTED;
     if (!n_batches)
         return NV_OK;
     if (!d_ordered || !d_groups || !d_batches || !d_entry_flags || !d_service || n_batches > 65536u)   // 16-bit batch numbers
@@ -183,136 +246,175 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     const uint32_t B = ctx->faults->gp.max_batch_size;
     const uint64_t chunk_entries = (uint64_t)chunk_batches * B;
-    // victims per wave: never more than the va_blocks one chunk of batches can touch, and at most 65536 (the run
-    // array of a wave is sized for them; a larger overflow takes more waves)
-    const uint64_t kmax64 = chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots;
-    const uint32_t kmax = (uint32_t)(kmax64 < 65536 ? kmax64 : 65536);
-    const uint32_t evict_run_cap = kmax * 256u;                           // a block's GPU pages: at most 256 runs
+    const uint32_t n_slots = pmm->n_slots;
+    if (pmm->d_chunk_of_slot && chunk_entries > pmm->capacity_chunks) {
+        uvmtier_set_error("tiered servicing with a chunk table: a round (chunk_batches * max_batch_size entries) may fault on more "
+                          "va_blocks than HBM has chunks", cudaErrorInvalidValue, __FILE__, __LINE__);
+        return NV_ERR_INVALID_ARGUMENT;
+    }
+    // a round evicts at most every va_block that holds a chunk, a va_block's GPU pages are at most 256 runs, and the DRAM
+    // pages of a demoted va_block likewise
+    const uint64_t evict_run_cap64 = (uint64_t)n_slots * 256u;
+    const uint32_t evict_run_cap = (uint32_t)(evict_run_cap64 < 0x7fffffffull ? evict_run_cap64 : 0x7fffffffull);
     // copy runs of one servicing pass, worst case: every page a va_block receives is a run of its own, a va_block
     // receives at most its 512 pages, and a pass touches at most min(entries, slots) va_blocks -- so the list is never
     // cut and the copies never run on a truncated list
-    const uint64_t svc_blocks = chunk_entries < pmm->n_slots ? chunk_entries : pmm->n_slots;
+    const uint64_t svc_blocks = chunk_entries < n_slots ? chunk_entries : n_slots;
     const uint64_t svc_cap64 = svc_blocks * UVMTIER_PAGES_PER_VA_BLOCK;
     const uint32_t svc_run_cap = (uint32_t)(svc_cap64 < 0x7fffffffull ? svc_cap64 : 0x7fffffffull);
-    // working space: counters, tallies, requests, results, the two run arrays
-    const size_t o_cnt = 0, o_acc = 256, o_req = 512, o_res = uvmtier_align_up(o_req + (size_t)kmax * sizeof(uvmtier_make_resident_req_t), 256),
-                 o_eruns = uvmtier_align_up(o_res + (size_t)kmax * sizeof(uvmtier_make_resident_result_t), 256),
-                 o_sruns = uvmtier_align_up(o_eruns + (size_t)evict_run_cap * sizeof(uvmtier_copy_run_t), 256),
-                 bytes = o_sruns + (size_t)svc_run_cap * sizeof(uvmtier_copy_run_t);
-    NV_STATUS st = uvmtier_stage_reserve(ctx, bytes, 256);
+    const uint64_t all_pages = (uint64_t)n_slots * UVMTIER_PAGES_PER_VA_BLOCK;
+    // working space: plan + counters, the selections' per-slot arrays, requests, results, the two run arrays
+    size_t off = 0;
+    auto take = [&](size_t bytes) { const size_t at = off; off = uvmtier_align_up(off + bytes, 256); return at; };
+    const size_t o_plan = take(kPlanWords * sizeof(uint32_t)), o_acc = take(4 * sizeof(unsigned long long)),
+                 o_touched = take(((size_t)n_slots + 31) / 32 * sizeof(uint32_t)), o_ew = take((size_t)n_slots * 4),
+                 o_ea = take((size_t)n_slots * 4), o_dk = take((size_t)n_slots * 8), o_dw = take((size_t)n_slots * 4),
+                 o_req = take((size_t)n_slots * sizeof(uvmtier_make_resident_req_t)),
+                 o_res = take((size_t)n_slots * sizeof(uvmtier_make_resident_result_t)),
+                 o_eruns = take((size_t)evict_run_cap * sizeof(uvmtier_copy_run_t)),
+                 o_sruns = take((size_t)svc_run_cap * sizeof(uvmtier_copy_run_t));
+    NV_STATUS st = uvmtier_stage_reserve(ctx, off, 256);
     if (st != NV_OK)
         return st;
     char *d = (char *)ctx->d_stage;
-    uint32_t *d_cnt = (uint32_t *)(d + o_cnt);                            // [0] needed [1] in use [2..4] pages [5] picked
-    unsigned long long *d_acc = (unsigned long long *)(d + o_acc);        //   [6] eviction runs [8] service runs
+    uint32_t *plan = (uint32_t *)(d + o_plan);                            // layout: k_pmm_plan; [40] requests [42] eviction runs
+    unsigned long long *d_acc = (unsigned long long *)(d + o_acc);        //         [44] demotion runs [46] service runs
+    uint32_t *touched = (uint32_t *)(d + o_touched), *e_weight = (uint32_t *)(d + o_ew), *e_aux = (uint32_t *)(d + o_ea),
+             *d_weight = (uint32_t *)(d + o_dw);
+    unsigned long long *d_key = (unsigned long long *)(d + o_dk);
     uvmtier_make_resident_req_t *d_req = (uvmtier_make_resident_req_t *)(d + o_req);
     uvmtier_make_resident_result_t *d_res = (uvmtier_make_resident_result_t *)(d + o_res);
     uvmtier_copy_run_t *d_eruns = (uvmtier_copy_run_t *)(d + o_eruns), *d_sruns = (uvmtier_copy_run_t *)(d + o_sruns);
     uint32_t *h_cnt = (uint32_t *)ctx->h_stage;
-    UVMTIER_CUDA(cudaMemsetAsync(d, 0, 512, ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(d, 0, o_touched, ctx->stream));
     UVMTIER_CUDA(cudaMemsetAsync(d_entry_flags, 0, (size_t)n_batches * B * sizeof(uint16_t), ctx->stream));
-    uvmtier_tiering_stats_t stats;
-    memset(&stats, 0, sizeof(stats));
+
+    service_kparams prm;
+    memset(&prm, 0, sizeof(prm));
+    prm.va_base = lay->va_base;
+    prm.B = B;
+    prm.blocks_per_space = lay->blocks_per_space;
+    prm.n_spaces = lay->n_spaces;
+    prm.gpu_id = lay->gpu_id;
+    prm.n_slots = n_slots;
+    prm.B_shift = svc_log2_or_none(B);
+    const pmm_chunk_table chunks = pmm_chunks(pmm);
+    const int slot_grid = (int)((((uint64_t)n_slots + kPmmThreads - 1) / kPmmThreads) < (uint64_t)ctx->sm_count * 8
+                                    ? ((uint64_t)n_slots + kPmmThreads - 1) / kPmmThreads : (uint64_t)ctx->sm_count * 8);
+    const uint32_t pair_hbm_dram = UVMTIER_RUN_SRC_HBM * 3 + UVMTIER_RUN_DST_DRAM, pair_hbm_cxl = UVMTIER_RUN_SRC_HBM * 3 + UVMTIER_RUN_DST_CXL,
+                   pair_dram_cxl = UVMTIER_RUN_SRC_DRAM * 3 + UVMTIER_RUN_DST_CXL, pair_dram_hbm = UVMTIER_RUN_SRC_DRAM * 3 + UVMTIER_RUN_DST_HBM,
+                   pair_cxl_hbm = UVMTIER_RUN_SRC_CXL * 3 + UVMTIER_RUN_DST_HBM, pair_zero_hbm = UVMTIER_RUN_SRC_ZERO * 3 + UVMTIER_RUN_DST_HBM;
+    uint32_t passes = 0;
     for (uint32_t b0 = 0; b0 < n_batches; b0 += chunk_batches) {
         const uint32_t nb = n_batches - b0 < chunk_batches ? n_batches - b0 : chunk_batches;
         const size_t e0 = (size_t)b0 * B;
-        // Make room: count what the chunk needs, evict the overflow, count again -- a victim that this very chunk of
-        // batches faults on comes back and needs a chunk again, so the second count can ask for a few more.
-        // Rounds repeat until nothing overflows.  A victim that this chunk of batches faults on needs a chunk again, so
-        // the overflow shrinks geometrically rather than at once; a wave takes at most kmax victims.  The bound covers
-        // emptying HBM wave by wave plus the recounts; a pass that still does not fit is serviced over capacity and
-        // counted (stats.overcommitted_passes).
-        uint32_t needed = 0, in_use = 0;
-        bool fits = false;
-        const int max_rounds = (int)(pmm->n_slots / (kmax ? kmax : 1u)) + 64;
-        for (int round = 0; round < max_rounds; round++) {
-            st = uvmtier_pmm_count_needed_device(ctx, pmm, nb, d_groups + e0, d_batches + b0, lay, d_cnt);
+        const uint64_t total = (uint64_t)nb * B;
+        uint64_t egrid = (total + kPmmThreads - 1) / kPmmThreads;
+        if (egrid > (uint64_t)ctx->sm_count * 8)
+            egrid = (uint64_t)ctx->sm_count * 8;
+        pmm->round++;
+        // ---- what the round needs, what is there ----
+        UVMTIER_CUDA(cudaMemsetAsync(touched, 0, ((size_t)n_slots + 31) / 32 * sizeof(uint32_t), ctx->stream));
+        UVMTIER_CUDA(cudaMemsetAsync(plan, 0, 32 * sizeof(uint32_t), ctx->stream));          // totals, targets, selections
+        UVMTIER_CUDA(cudaMemsetAsync(plan + 40, 0, 8 * sizeof(uint32_t), ctx->stream));      // request / run counters
+        prm.n_batches = nb;
+        UVMTIER_LAUNCH(k_pmm_mark_touched, (int)egrid, kPmmThreads, 0, ctx->stream, prm, d_groups + e0,
+                       (const uvmtier_fault_batch_t *)(d_batches + b0), (const uvmtier_instance_ptr_entry_t *)ctx->faults->d_table, touched);
+        UVMTIER_LAUNCH(k_pmm_slot_keys, slot_grid, kPmmThreads, 0, ctx->stream, n_slots, (const unsigned long long *)pmm->d_stamp,
+                       (const unsigned long long *)pmm->d_dram_stamp, (const uint32_t *)touched, (const uint32_t *)state->gpu_resident,
+                       (const uint32_t *)state->cpu_resident[0], (const uint32_t *)state->cpu_resident[1], e_weight, e_aux, d_key,
+                       d_weight, plan);
+        // ---- who leaves HBM, who leaves DRAM, where the victims go ----
+        UVMTIER_LAUNCH(k_pmm_plan, 1, 32, 0, ctx->stream, plan, 0, pmm->capacity_chunks, (unsigned long long)dram_capacity_pages, (int)demote);
+        UVMTIER_LAUNCH(k_pmm_select_weighted, 1, kPmmSelectThreads, 0, ctx->stream, (const unsigned long long *)pmm->d_stamp,
+                       (const uint32_t *)e_weight, (const uint32_t *)e_aux, n_slots, (const uint32_t *)(plan + 8), plan + 16);
+        UVMTIER_LAUNCH(k_pmm_plan, 1, 32, 0, ctx->stream, plan, 1, pmm->capacity_chunks, (unsigned long long)dram_capacity_pages, (int)demote);
+        if (demote)
+            UVMTIER_LAUNCH(k_pmm_select_weighted, 1, kPmmSelectThreads, 0, ctx->stream, (const unsigned long long *)d_key,
+                           (const uint32_t *)d_weight, (const uint32_t *)NULL, n_slots, (const uint32_t *)(plan + 9), plan + 24);
+        UVMTIER_LAUNCH(k_pmm_plan, 1, 32, 0, ctx->stream, plan, 2, pmm->capacity_chunks, (unsigned long long)dram_capacity_pages, (int)demote);
+        if (demote) {
+            // ---- DRAM -> CXL for the coldest DRAM va_blocks (page mask = the block's row of cpu_resident[0]) ----
+            UVMTIER_LAUNCH(k_pmm_emit_selected, slot_grid, kPmmThreads, 0, ctx->stream, (const unsigned long long *)d_key, n_slots,
+                           (const uint32_t *)(plan + 24), 0, (const uint32_t *)(plan + 10), d_req, plan + 40);
+            st = uvmtier_make_resident_counted(ctx, n_slots, plan + 40, d_req, state->cpu_resident[0], NULL, lay, state, d_res, d_eruns,
+                                               evict_run_cap, plan + 44);
             if (st != NV_OK)
                 return st;
-            st = uvmtier_block_state_count_pages_device(ctx, lay, state, d_cnt + 2);
-            if (st != NV_OK)
-                return st;
-            UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-            UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-            if (h_cnt[6] > evict_run_cap || h_cnt[8] > svc_run_cap)       // an earlier copy list was cut
-                return NV_ERR_NO_MEMORY;
-            needed = h_cnt[0];
-            in_use = h_cnt[1];
-            const uint64_t dram_pages = h_cnt[3];
-            uint32_t k = (uint64_t)in_use + needed > pmm->capacity_chunks ? in_use + needed - pmm->capacity_chunks : 0;
-            if (k > in_use)
-                k = in_use;                                               // the chunk alone overflows HBM: evict all there is
-            if (k > kmax)
-                k = kmax;
-            if (!k) {
-                fits = true;
-                break;
-            }
-            const uint32_t dest = dram_pages + (uint64_t)k * UVMTIER_PAGES_PER_VA_BLOCK <= dram_capacity_pages ? UVMTIER_TIER_DRAM
-                                                                                                                : UVMTIER_TIER_CXL;
-            st = uvmtier_pmm_pick_chunks_to_evict_device(ctx, pmm, k, dest, d_req, d_cnt + 5);
-            if (st != NV_OK)
-                return st;
-            UVMTIER_CUDA(cudaMemsetAsync(d_cnt + 6, 0, 2 * sizeof(uint32_t), ctx->stream));
-            st = uvmtier_make_resident_device(ctx, k, d_req, NULL, NULL, lay, state, d_res, d_eruns, evict_run_cap, d_cnt + 6);
-            if (st != NV_OK)
-                return st;
-            UVMTIER_LAUNCH(k_pmm_note_make_resident, (int)((k + kPmmThreads - 1) / kPmmThreads), kPmmThreads, 0, ctx->stream, k,
+            UVMTIER_LAUNCH(k_pmm_note_make_resident, slot_grid, kPmmThreads, 0, ctx->stream, n_slots,
                            (const uvmtier_make_resident_req_t *)d_req, (const uvmtier_make_resident_result_t *)d_res,
-                           (const uint32_t *)state->gpu_resident, (unsigned long long *)pmm->d_stamp, pmm->n_slots,
-                           (unsigned long long)pmm->clock, d_acc);
-            pmm->clock += k;
+                           (const uint32_t *)state->gpu_resident, (unsigned long long *)pmm->d_stamp, n_slots,
+                           (unsigned long long)pmm->clock, (unsigned long long *)NULL, (const uint32_t *)(plan + 40), chunks,
+                           (unsigned long long *)pmm->d_dram_stamp, (unsigned long long)pmm->round,
+                           (const uint32_t *)state->cpu_resident[0]);
             if (execute_copies) {
-                st = uvmtier_copy_runs_device(ctx, d_eruns, d_cnt + 6, evict_run_cap, 0);
+                st = uvmtier_copy_runs_enqueue(ctx, d_eruns, plan + 44, evict_run_cap, all_pages, 1u << pair_dram_cxl);
                 if (st != NV_OK)
                     return st;
             }
-            stats.eviction_waves++;
-            if (dest == UVMTIER_TIER_DRAM) stats.evicted_to_dram += k; else stats.evicted_to_cxl += k;
-            in_use -= k;                                                  // what the next count will find (if there is none)
         }
-        if (!fits || (uint64_t)in_use + needed > pmm->capacity_chunks)
-            stats.overcommitted_passes++;                                 // e.g. the chunk of batches alone needs more than HBM holds
-        // service the chunk, note its list moves, bring its pages in
-        UVMTIER_CUDA(cudaMemsetAsync(d_cnt + 8, 0, 2 * sizeof(uint32_t), ctx->stream));
-        st = uvmtier_service_pass_chunk(ctx, nb, d_ordered + e0, d_groups + e0, d_batches + b0, lay, state, d_entry_flags + e0,
-                                        d_service + e0, d_sruns, svc_run_cap, d_cnt + 8, b0);
+        // ---- evictions: make_resident to the chosen tier, the copies out, then the list moves and the chunks given back ----
+        UVMTIER_LAUNCH(k_pmm_emit_selected, slot_grid, kPmmThreads, 0, ctx->stream, (const unsigned long long *)pmm->d_stamp, n_slots,
+                       (const uint32_t *)(plan + 16), 1, (const uint32_t *)(plan + 10), d_req, plan + 41);
+        st = uvmtier_make_resident_counted(ctx, n_slots, plan + 41, d_req, NULL, NULL, lay, state, d_res, d_eruns, evict_run_cap, plan + 42);
         if (st != NV_OK)
             return st;
-        const uint64_t total = (uint64_t)nb * B;
-        uint64_t grid = (total + kPmmThreads - 1) / kPmmThreads;
-        if (grid > (uint64_t)ctx->sm_count * 8)
-            grid = (uint64_t)ctx->sm_count * 8;
-        UVMTIER_LAUNCH(k_pmm_note_service, (int)grid, kPmmThreads, 0, ctx->stream, nb, B,
-                       (const uvmtier_fault_batch_t *)(d_batches + b0), (const uvmtier_service_group_t *)(d_service + e0),
-                       (unsigned long long *)pmm->d_stamp, pmm->n_slots, (unsigned long long)pmm->clock, d_acc + 1);
-        pmm->clock += total;
         if (execute_copies) {
-            st = uvmtier_copy_runs_device(ctx, d_sruns, d_cnt + 8, svc_run_cap, 0);
+            st = uvmtier_copy_runs_enqueue(ctx, d_eruns, plan + 42, evict_run_cap, all_pages, (1u << pair_hbm_dram) | (1u << pair_hbm_cxl));
             if (st != NV_OK)
                 return st;
         }
-        stats.passes++;
-        const uint32_t after = in_use + needed;
-        if (after > stats.peak_chunks_in_use)
-            stats.peak_chunks_in_use = after;
-        stats.chunks_in_use = after;
+        UVMTIER_LAUNCH(k_pmm_note_make_resident, slot_grid, kPmmThreads, 0, ctx->stream, n_slots,
+                       (const uvmtier_make_resident_req_t *)d_req, (const uvmtier_make_resident_result_t *)d_res,
+                       (const uint32_t *)state->gpu_resident, (unsigned long long *)pmm->d_stamp, n_slots,
+                       (unsigned long long)pmm->clock, d_acc, (const uint32_t *)(plan + 41), chunks,
+                       (unsigned long long *)pmm->d_dram_stamp, (unsigned long long)pmm->round, (const uint32_t *)state->cpu_resident[0]);
+        // ---- service the round, note its list moves (new va_blocks take chunks), bring its pages in ----
+        st = uvmtier_service_pass_chunk(ctx, nb, d_ordered + e0, d_groups + e0, d_batches + b0, lay, state, d_entry_flags + e0,
+                                        d_service + e0, d_sruns, svc_run_cap, plan + 46, b0);
+        if (st != NV_OK)
+            return st;
+        UVMTIER_LAUNCH(k_pmm_note_service, (int)egrid, kPmmThreads, 0, ctx->stream, nb, B,
+                       (const uvmtier_fault_batch_t *)(d_batches + b0), (const uvmtier_service_group_t *)(d_service + e0),
+                       (unsigned long long *)pmm->d_stamp, n_slots, (unsigned long long)pmm->clock, d_acc + 1, chunks);
+        pmm->clock += total;
+        if (execute_copies) {
+            st = uvmtier_copy_runs_enqueue(ctx, d_sruns, plan + 46, svc_run_cap, svc_cap64,
+                                           (1u << pair_dram_hbm) | (1u << pair_cxl_hbm) | (1u << pair_zero_hbm));
+            if (st != NV_OK)
+                return st;
+        }
+        passes++;
     }
-    // the tallies, the chunks in use now, and whether a run array overflowed in the last chunk (the others were
-    // checked as the loop went)
-    st = uvmtier_pmm_count_needed_device(ctx, pmm, 0, NULL, NULL, lay, d_cnt);
-    if (st != NV_OK)
-        return st;
-    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, d_cnt, 10 * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt + 16, d_acc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    // the tallies and the chunks in use now
+    UVMTIER_CUDA(cudaMemsetAsync(plan, 0, 8 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(touched, 0, ((size_t)n_slots + 31) / 32 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_LAUNCH(k_pmm_slot_keys, slot_grid, kPmmThreads, 0, ctx->stream, n_slots, (const unsigned long long *)pmm->d_stamp,
+                   (const unsigned long long *)pmm->d_dram_stamp, (const uint32_t *)touched, (const uint32_t *)state->gpu_resident,
+                   (const uint32_t *)state->cpu_resident[0], (const uint32_t *)state->cpu_resident[1], e_weight, e_aux, d_key, d_weight,
+                   plan);
+    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, plan, kPlanWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt + kPlanWords, d_acc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    uint32_t chunk_errors = 0;
+    if (chunks.errors)
+        UVMTIER_CUDA(cudaMemcpyAsync(&chunk_errors, chunks.errors, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
     UVMTIER_CUDA(cudaStreamSynchronize(ctx->stream));
-    if (h_cnt[6] > evict_run_cap || h_cnt[8] > svc_run_cap)
-        return NV_ERR_NO_MEMORY;
+    uvmtier_tiering_stats_t stats;
+    memset(&stats, 0, sizeof(stats));
+    stats.passes = passes;
+    stats.eviction_waves = h_cnt[32];
+    stats.evicted_to_dram = h_cnt[33];
+    stats.evicted_to_cxl = h_cnt[34];
+    stats.blocks_demoted = h_cnt[35];
+    stats.overcommitted_passes = h_cnt[36];
+    stats.peak_chunks_in_use = h_cnt[37];
     stats.chunks_in_use = h_cnt[1];
-    stats.pages_evicted = ((const unsigned long long *)(h_cnt + 16))[0];
-    stats.pages_promoted = ((const unsigned long long *)(h_cnt + 16))[1];
+    stats.pages_evicted = ((const unsigned long long *)(h_cnt + kPlanWords))[0];
+    stats.pages_promoted = ((const unsigned long long *)(h_cnt + kPlanWords))[1];
     if (out_stats)
         *out_stats = stats;
+    if (chunk_errors)
+        return NV_ERR_NO_MEMORY;
     return NV_OK;
 }
 

@@ -10,13 +10,13 @@
 
 using namespace uvmtier_k;
 
-extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n_requests,
-                                                  const uvmtier_make_resident_req_t *d_requests,
-                                                  const uvmtier_page_mask_t *d_page_masks,
-                                                  const uvmtier_page_mask_t *d_prefetch_masks,
-                                                  const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
-                                                  uvmtier_make_resident_result_t *d_results, uvmtier_copy_run_t *d_runs,
-                                                  uint32_t run_cap, uint32_t *d_counters)
+// n_requests_dev != NULL: the number of requests is read on the device (n_requests is its upper bound and sizes the
+// grid) -- the tiered loop decides how many va_blocks to evict without a round trip to the host.
+NV_STATUS uvmtier_make_resident_counted(uvmtier_ctx_t *ctx, uint32_t n_requests, const uint32_t *n_requests_dev,
+                                        const uvmtier_make_resident_req_t *d_requests, const uvmtier_page_mask_t *d_page_masks,
+                                        const uvmtier_page_mask_t *d_prefetch_masks, const uvmtier_va_layout_t *lay,
+                                        const uvmtier_block_state_t *state, uvmtier_make_resident_result_t *d_results,
+                                        uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters)
 {
     if (!ctx || !lay || !state)
         return NV_ERR_INVALID_ARGUMENT;
@@ -34,6 +34,7 @@ extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n
     prm.n_slots = (uint32_t)n_slots64;
     prm.run_cap = run_cap;
     prm.gpu_id = lay->gpu_id;
+    prm.n_requests_dev = n_requests_dev;
     if (state->n_peers > UVMTIER_MAX_PEER_GPUS)
         return NV_ERR_INVALID_ARGUMENT;
     peer_state_ptrs peers;
@@ -68,4 +69,16 @@ extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n
     UVMTIER_LAUNCH(k_make_resident, (int)grid, kResThreads, 0, ctx->stream, prm, d_requests, (const uint32_t *)d_page_masks,
                    (const uint32_t *)d_prefetch_masks, bs, peers, d_results, d_runs, d_counters);
     return NV_OK;
+}
+
+extern "C" NV_STATUS uvmtier_make_resident_device(uvmtier_ctx_t *ctx, uint32_t n_requests,
+                                                  const uvmtier_make_resident_req_t *d_requests,
+                                                  const uvmtier_page_mask_t *d_page_masks,
+                                                  const uvmtier_page_mask_t *d_prefetch_masks,
+                                                  const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                                  uvmtier_make_resident_result_t *d_results, uvmtier_copy_run_t *d_runs,
+                                                  uint32_t run_cap, uint32_t *d_counters)
+{
+    return uvmtier_make_resident_counted(ctx, n_requests, NULL, d_requests, d_page_masks, d_prefetch_masks, lay, state, d_results,
+                                         d_runs, run_cap, d_counters);
 }

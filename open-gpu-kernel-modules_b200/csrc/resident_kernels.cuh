@@ -30,6 +30,7 @@ constexpr int kResThreads = 128;
 struct resident_kparams {
     uint32_t n_requests, n_slots, run_cap;
     uint32_t gpu_id;                           // uvm_gpu_id_t of this GPU (places it among the other GPUs)
+    const uint32_t *n_requests_dev;            // when set: the request count lives on the device (at most n_requests)
 };
 
 // the other GPUs of the table (uvmtier_block_state_t.peer_*), ascending gpu id
@@ -49,7 +50,8 @@ k_make_resident(resident_kparams prm, const uvmtier_make_resident_req_t *__restr
 {
     const int lane = threadIdx.x & 31, l = lane & 15;
     const uint32_t n_warps = gridDim.x * (kResThreads / 32);
-    for (uint32_t q = blockIdx.x * (kResThreads / 32) + (threadIdx.x >> 5); q < prm.n_requests; q += n_warps) {
+    const uint32_t n_requests = prm.n_requests_dev ? min(prm.n_requests, *prm.n_requests_dev) : prm.n_requests;
+    for (uint32_t q = blockIdx.x * (kResThreads / 32) + (threadIdx.x >> 5); q < n_requests; q += n_warps) {
         const uvmtier_make_resident_req_t rq = reqs[q];
         uint32_t *res = (uint32_t *)&results[q];
         const uint32_t slot = rq.slot;

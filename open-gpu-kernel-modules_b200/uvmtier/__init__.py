@@ -75,7 +75,8 @@ TIERF_CXL_EMULATED = 0x1
 class PmmState(ctypes.Structure):
     """uvmtier_pmm_t"""
     _fields_ = [("d_stamp", ctypes.c_void_p), ("d_scratch", ctypes.c_void_p), ("clock", ctypes.c_uint64),
-                ("n_slots", ctypes.c_uint32), ("capacity_chunks", ctypes.c_uint32)]
+                ("n_slots", ctypes.c_uint32), ("capacity_chunks", ctypes.c_uint32), ("d_chunk_of_slot", ctypes.c_void_p),
+                ("d_free_bits", ctypes.c_void_p), ("d_dram_stamp", ctypes.c_void_p), ("round", ctypes.c_uint64)]
 
 
 class ThrashingState(ctypes.Structure):
@@ -90,7 +91,7 @@ class TieringStats(ctypes.Structure):
     _fields_ = [("passes", ctypes.c_uint32), ("eviction_waves", ctypes.c_uint32), ("evicted_to_dram", ctypes.c_uint32),
                 ("evicted_to_cxl", ctypes.c_uint32), ("peak_chunks_in_use", ctypes.c_uint32), ("chunks_in_use", ctypes.c_uint32),
                 ("pages_evicted", ctypes.c_uint64), ("pages_promoted", ctypes.c_uint64), ("overcommitted_passes", ctypes.c_uint32),
-                ("reserved", ctypes.c_uint32 * 3)]
+                ("blocks_demoted", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 2)]
 
 
 class TierInfo(ctypes.Structure):
@@ -401,7 +402,16 @@ class Context:
     def pmm_stamps(self, pmm):
         return self.from_device(pmm.d_stamp, pmm.n_slots, "<u8")
 
-    def service_fault_batches_tiered(self, k1, layout, dstate, pmm, chunk_batches, dram_capacity_pages, execute_copies=True):
+    def pmm_enable_chunk_table(self, pmm):
+        """uvmtier_pmm_enable_chunk_table: the HBM arena holds pmm.capacity_chunks chunks, va_blocks take and return them."""
+        _check(lib().uvmtier_pmm_enable_chunk_table(self._h, ctypes.byref(pmm)), "uvmtier_pmm_enable_chunk_table")
+
+    def pmm_chunk_table(self, pmm):
+        """chunk_of_slot (0xFFFFFFFF = none); None when the table is off."""
+        return self.from_device(pmm.d_chunk_of_slot, pmm.n_slots, "<u4") if pmm.d_chunk_of_slot else None
+
+    def service_fault_batches_tiered(self, k1, layout, dstate, pmm, chunk_batches, dram_capacity_pages, execute_copies=True,
+                                     demote=False):
         """uvmtier_service_fault_batches_tiered_device on the results of fetch_preprocess_fault_batches (dict k1, host
         arrays, padded to whole batches).  Returns flags / records / batch headers / state / stats / stamps."""
         from .blockstate import SERVICE_GROUP_DT
@@ -416,11 +426,13 @@ class Context:
             _check(lib().uvmtier_service_fault_batches_tiered_device(
                 self._h, ctypes.byref(pmm), ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(dstate.ptrs),
                 P(d_flags), P(d_svc), ctypes.c_uint32(chunk_batches), ctypes.c_uint64(dram_capacity_pages),
-                ctypes.c_int(1 if execute_copies else 0), ctypes.byref(stats)), "uvmtier_service_fault_batches_tiered_device")
+                ctypes.c_int((1 if execute_copies else 0) | (2 if demote else 0)), ctypes.byref(stats)),
+                "uvmtier_service_fault_batches_tiered_device")
             self.synchronize()
             return dict(flags=self.from_device(d_flags, total, "<u2"), service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
                         batch=self.from_device(d_bat, nb, BATCH_DT), state=dstate.download(), stats=stats,
-                        stamps=self.pmm_stamps(pmm))
+                        stamps=self.pmm_stamps(pmm), dram_stamps=self.from_device(pmm.d_dram_stamp, pmm.n_slots, "<u8"),
+                        chunk_of_slot=self.pmm_chunk_table(pmm))
         finally:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
                 self.free(p)

@@ -12,7 +12,7 @@ extern "C" int simt_make_resident(uint32_t n_requests, const uvmtier_make_reside
                                   uint32_t *counters, uint32_t gpu_id)
 {
     resident_kparams prm;
-    prm.n_requests = n_requests; prm.n_slots = n_slots; prm.run_cap = run_cap; prm.gpu_id = gpu_id;
+    prm.n_requests = n_requests; prm.n_slots = n_slots; prm.run_cap = run_cap; prm.gpu_id = gpu_id; prm.n_requests_dev = NULL;
     peer_state_ptrs peers;
     memset(&peers, 0, sizeof(peers));
     peers.n_peers = state->n_peers; peers.direct = state->peer_direct;

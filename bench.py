@@ -401,55 +401,81 @@ def migration_numbers(ctx, lib, P, rank, world, dist, arena=8 << 30):
     return out
 
 
-def oversubscription_numbers(ctx, lib, P, rank):
-    """BASELINE config D, bounded: the fault path with HBM oversubscribed 1.5x.  1 GB of VA (512 va_blocks) with room
-    for 341 root chunks in HBM; a uniform trace keeps touching all of it, so every chunk of batches evicts least
-    recently used va_blocks (to host DRAM until it holds 192 MB of this table, then to the CXL node) before it is
-    serviced.  Real pages move: eviction copies HBM -> host, servicing copies host -> HBM.  Timed end to end on the host
-    clock (the loop synchronises once per chunk of batches by design)."""
+def oversubscription_numbers(ctx, lib, P, rank, blocks=8192, hbm_chunks=4096, dram_blocks=3072):
+    """BASELINE config D at a bounded size: the fault path with HBM oversubscribed 2x.  16 GB of VA (8192 va_blocks) over an
+    HBM arena of 4096 root chunks (8 GB, slot -> chunk table), host DRAM budget 6 GB of this table's pages, the rest on the
+    CXL node.  Every round of 16 batches evicts least recently used va_blocks, demotes the coldest DRAM va_blocks to CXL to
+    keep the budget, services, and copies: real pages move over the host link in both directions.  Two traces on the same
+    table: uniform (every fault is a 64 KB migration: link-bound) and hotset (most faults land on pages that are already
+    resident and mapped: fault-filtering bound).  Timed end to end on the host clock around one call (the loop decides
+    everything on the device and synchronises once)."""
     import uvmtier
     from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, tracegen as TG
     from uvmtier.blockstate import HostBlockState, make_layout
-    blocks, n_entries, B, chunk_batches = 512, 65536, 256, 2
-    pk, tbl, lay = TG.fault_trace(n_entries, 77 + rank, "uniform", 1, blocks << 21)
+    B, chunk_batches = 256, 16
+    t_setup = time.perf_counter()
     gp = TG.gpu_params(B)
-    ctx.fault_buffer_init(gp, tbl)
-    layout = make_layout(lay)
-    st = HostBlockState(blocks)
-    st.cpu_resident0[:] = np.uint64(0xFFFFFFFFFFFFFFFF)                  # everything starts in host DRAM
-    ring = np.zeros((n_entries + 1, 8), np.uint32)
-    ring[:n_entries] = pk
-    k1 = ctx.fetch_preprocess_fault_batches(ring, 0, n_entries)
-    nb = len(k1["batch"])
-    info = {t: ctx.tier_create(t, blocks << 21) for t in (TIER_HBM, TIER_DRAM, TIER_CXL)}
-    ds = ctx.block_state_alloc(layout)
-    ds.upload(st)
-    capacity = blocks * 2 // 3
-    pmm = ctx.pmm_create(layout, capacity)
-    d_ord, d_grp, d_bat = ctx.to_device(k1["ordered"]), ctx.to_device(k1["groups"]), ctx.to_device(k1["batch"])
-    d_flags, d_svc = ctx.alloc(nb * B * 2), ctx.alloc(nb * B * 96)
-    stats = uvmtier.TieringStats()
-    ctx.synchronize()
-    launches0 = lib.uvmtier_kernel_launch_count()
-    t0 = time.perf_counter()
-    st_code = lib.uvmtier_service_fault_batches_tiered_device(
-        ctx.handle, ctypes.byref(pmm), ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(ds.ptrs), P(d_flags),
-        P(d_svc), ctypes.c_uint32(chunk_batches), ctypes.c_uint64(96 * 512), ctypes.c_int(1), ctypes.byref(stats))
-    ctx.synchronize()
-    dt = time.perf_counter() - t0
-    assert st_code == 0, hex(st_code)
-    out = {"workload": "uniform trace, %d entries over %d va_blocks (1 GB of VA), HBM holds %d root chunks (VA / 1.5)" % (n_entries, blocks, capacity),
-           "chunk_batches": chunk_batches, "entries_per_s": n_entries / dt, "ms": dt * 1e3, "passes": stats.passes,
-           "eviction_waves": stats.eviction_waves, "root_chunks_evicted_to_dram": stats.evicted_to_dram,
-           "root_chunks_evicted_to_cxl": stats.evicted_to_cxl, "peak_chunks_in_use": stats.peak_chunks_in_use,
-           "GB_evicted": stats.pages_evicted * 4096 / 1e9, "GB_promoted": stats.pages_promoted * 4096 / 1e9,
-           "link_GBs": (stats.pages_evicted + stats.pages_promoted) * 4096 / dt / 1e9,
-           "gpu_launches": int(lib.uvmtier_kernel_launch_count() - launches0),
-           "policy": "victims in the reference's order (pick_root_chunk_to_evict); evicted pages to host DRAM up to 192 MB, then CXL"}
-    for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
-        ctx.free(p)
-    ctx.pmm_destroy(pmm)
-    ds.free()
+    info = {TIER_HBM: ctx.tier_create(TIER_HBM, hbm_chunks << 21), TIER_DRAM: ctx.tier_create(TIER_DRAM, blocks << 21),
+            TIER_CXL: ctx.tier_create(TIER_CXL, blocks << 21)}
+    setup_s = time.perf_counter() - t_setup
+    # the copy-engine peaks of this box, both directions at once is what the loop asks of the link
+    peak = {}
+    for name, (dst, src) in (("h2d", (TIER_HBM, TIER_DRAM)), ("d2h", (TIER_DRAM, TIER_HBM))):
+        ms = ctypes.c_float(0)
+        uvmtier._check(lib.uvmtier_tier_memcpy_peak(ctx.handle, ctypes.c_uint32(dst), ctypes.c_uint32(src), ctypes.c_uint64(1 << 30), 3,
+                                                    ctypes.byref(ms)), "peak")
+        peak[name] = (1 << 30) / (ms.value * 1e-3) / 1e9
+    out = {"workload": "%d va_blocks (%d GB of VA) over an HBM arena of %d root chunks (chunk table), DRAM budget %d va_blocks of pages, rest on the CXL node; rounds of %d batches of %d"
+                       % (blocks, blocks >> 9, hbm_chunks, dram_blocks, chunk_batches, B),
+           "tier_setup_s": setup_s, "ce_peak_h2d_GBs": peak["h2d"], "ce_peak_d2h_GBs": peak["d2h"],
+           "policy": "victims in the reference's order (pick_root_chunk_to_evict) until enough of them are va_blocks the round does not "
+                     "fault on; evicted pages go to host DRAM, the coldest DRAM va_blocks are demoted to the CXL node to keep the budget"}
+    for trace, n_entries in (("uniform", 262144), ("hotset", 1048576)):
+        pk, tbl, lay = TG.fault_trace(n_entries, 77 + rank, trace, 1, blocks << 21)
+        ctx.fault_buffer_init(gp, tbl)
+        layout = make_layout(lay)
+        st = HostBlockState(blocks)
+        st.cpu_resident0[:dram_blocks] = np.uint64(0xFFFFFFFFFFFFFFFF)      # the table starts on the CPU tiers, DRAM at its budget
+        st.cpu_resident1[dram_blocks:] = np.uint64(0xFFFFFFFFFFFFFFFF)
+        ring = np.zeros((n_entries + 1, 8), np.uint32)
+        ring[:n_entries] = pk
+        k1 = ctx.fetch_preprocess_fault_batches(ring, 0, n_entries)
+        nb = len(k1["batch"])
+        ds = ctx.block_state_alloc(layout)
+        ds.upload(st)
+        pmm = ctx.pmm_create(layout, hbm_chunks)
+        ctx.pmm_enable_chunk_table(pmm)
+        d_ord, d_grp, d_bat = ctx.to_device(k1["ordered"]), ctx.to_device(k1["groups"]), ctx.to_device(k1["batch"])
+        d_flags, d_svc = ctx.alloc(nb * B * 2), ctx.alloc(nb * B * 96)
+        stats = uvmtier.TieringStats()
+        ctx.synchronize()
+        launches0 = lib.uvmtier_kernel_launch_count()
+        t0 = time.perf_counter()
+        st_code = lib.uvmtier_service_fault_batches_tiered_device(
+            ctx.handle, ctypes.byref(pmm), ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(ds.ptrs), P(d_flags),
+            P(d_svc), ctypes.c_uint32(chunk_batches), ctypes.c_uint64(dram_blocks * 512), ctypes.c_int(3), ctypes.byref(stats))
+        ctx.synchronize()
+        dt = time.perf_counter() - t0
+        assert st_code == 0, hex(st_code)
+        out_b = stats.pages_evicted * 4096 / 1e9
+        in_b = stats.pages_promoted * 4096 / 1e9
+        # demoted pages cross the link twice (DRAM -> GPU -> CXL node), once in each direction
+        dem_b = stats.pages_demoted * 4096 / 1e9
+        out[trace] = {"entries": n_entries, "entries_per_s": n_entries / dt, "ms": dt * 1e3, "rounds": stats.passes,
+                      "eviction_waves": stats.eviction_waves, "root_chunks_evicted_to_dram": stats.evicted_to_dram,
+                      "root_chunks_evicted_to_cxl": stats.evicted_to_cxl, "va_blocks_demoted": stats.blocks_demoted,
+                      "peak_chunks_in_use": stats.peak_chunks_in_use, "overcommitted_rounds": stats.overcommitted_passes,
+                      "GB_evicted": out_b, "GB_promoted": in_b, "GB_demoted": dem_b,
+                      "h2d_GBs": (in_b + dem_b) / dt, "d2h_GBs": (out_b + dem_b) / dt,
+                      "h2d_frac_of_ce_peak": (in_b + dem_b) / dt / peak["h2d"], "d2h_frac_of_ce_peak": (out_b + dem_b) / dt / peak["d2h"],
+                      # the loop's copies run one after the other on one stream: the share of the wall time the link spends
+                      # moving this call's bytes at the copy-engine rate of their direction
+                      "link_busy_frac": ((in_b + dem_b) / peak["h2d"] + (out_b + dem_b) / peak["d2h"]) / dt,
+                      "gpu_launches": int(lib.uvmtier_kernel_launch_count() - launches0)}
+        for p in (d_ord, d_grp, d_bat, d_flags, d_svc):
+            ctx.free(p)
+        ctx.pmm_destroy(pmm)
+        ds.free()
     for t in (TIER_HBM, TIER_DRAM, TIER_CXL):
         ctx.tier_destroy(t)
     return out

@@ -680,6 +680,7 @@ typedef struct {
                                                    everything else was evicted and they were serviced over capacity */
     uint32_t blocks_demoted;                    /* va_blocks whose DRAM pages were moved to the CXL node */
     uint32_t reserved[2];
+    uint64_t pages_demoted;                     /* pages copied DRAM -> CXL */
 } uvmtier_tiering_stats_t;
 NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtier_pmm_t *pmm, uint32_t n_batches,
                                                       const uvmtier_ordered_fault_t *d_ordered,

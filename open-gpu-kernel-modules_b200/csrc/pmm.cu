@@ -273,7 +273,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                  o_res = take((size_t)n_slots * sizeof(uvmtier_make_resident_result_t)),
                  o_eruns = take((size_t)evict_run_cap * sizeof(uvmtier_copy_run_t)),
                  o_sruns = take((size_t)svc_run_cap * sizeof(uvmtier_copy_run_t));
-    NV_STATUS st = uvmtier_stage_reserve(ctx, off, 256);
+    NV_STATUS st = uvmtier_stage_reserve(ctx, off, 512);
     if (st != NV_OK)
         return st;
     char *d = (char *)ctx->d_stage;
@@ -344,7 +344,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
             UVMTIER_LAUNCH(k_pmm_note_make_resident, slot_grid, kPmmThreads, 0, ctx->stream, n_slots,
                            (const uvmtier_make_resident_req_t *)d_req, (const uvmtier_make_resident_result_t *)d_res,
                            (const uint32_t *)state->gpu_resident, (unsigned long long *)pmm->d_stamp, n_slots,
-                           (unsigned long long)pmm->clock, (unsigned long long *)NULL, (const uint32_t *)(plan + 40), chunks,
+                           (unsigned long long)pmm->clock, d_acc + 2, (const uint32_t *)(plan + 40), chunks,
                            (unsigned long long *)pmm->d_dram_stamp, (unsigned long long)pmm->round,
                            (const uint32_t *)state->cpu_resident[0]);
             if (execute_copies) {
@@ -394,7 +394,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
                    (const uint32_t *)state->cpu_resident[0], (const uint32_t *)state->cpu_resident[1], e_weight, e_aux, d_key, d_weight,
                    plan);
     UVMTIER_CUDA(cudaMemcpyAsync(h_cnt, plan, kPlanWords * sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
-    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt + kPlanWords, d_acc, 2 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
+    UVMTIER_CUDA(cudaMemcpyAsync(h_cnt + kPlanWords, d_acc, 3 * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->stream));
     uint32_t chunk_errors = 0;
     if (chunks.errors)
         UVMTIER_CUDA(cudaMemcpyAsync(&chunk_errors, chunks.errors, sizeof(uint32_t), cudaMemcpyDeviceToHost, ctx->stream));
@@ -411,6 +411,7 @@ NV_STATUS uvmtier_service_fault_batches_tiered_device(uvmtier_ctx_t *ctx, uvmtie
     stats.chunks_in_use = h_cnt[1];
     stats.pages_evicted = ((const unsigned long long *)(h_cnt + kPlanWords))[0];
     stats.pages_promoted = ((const unsigned long long *)(h_cnt + kPlanWords))[1];
+    stats.pages_demoted = ((const unsigned long long *)(h_cnt + kPlanWords))[2];
     if (out_stats)
         *out_stats = stats;
     if (chunk_errors)

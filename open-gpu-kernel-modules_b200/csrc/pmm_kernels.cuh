@@ -107,8 +107,11 @@ k_pmm_note_make_resident(uint32_t n_requests, const uvmtier_make_resident_req_t 
         for (int w = 0; w < 16; w++)
             any |= gpu_resident[(size_t)rq.slot * 16 + w];
         const unsigned long long seq = clock + q + 1;
-        if (pages_out && results[q].migrated[2])                          // pages that left HBM (optional tally)
-            atomicAdd(pages_out, (unsigned long long)results[q].migrated[2]);
+        if (pages_out && rq.dest_tier != UVMTIER_TIER_HBM) {               // pages the call copied to a CPU node (optional tally)
+            const unsigned long long moved = (unsigned long long)results[q].migrated[0] + results[q].migrated[1] + results[q].migrated[2];
+            if (moved)
+                atomicAdd(pages_out, moved);
+        }
         if (rq.dest_tier == UVMTIER_TIER_HBM) {
             if (any) {                                                    // make_resident_finish :5076-5077
                 if (stamp[rq.slot] == 0)

@@ -91,7 +91,7 @@ class TieringStats(ctypes.Structure):
     _fields_ = [("passes", ctypes.c_uint32), ("eviction_waves", ctypes.c_uint32), ("evicted_to_dram", ctypes.c_uint32),
                 ("evicted_to_cxl", ctypes.c_uint32), ("peak_chunks_in_use", ctypes.c_uint32), ("chunks_in_use", ctypes.c_uint32),
                 ("pages_evicted", ctypes.c_uint64), ("pages_promoted", ctypes.c_uint64), ("overcommitted_passes", ctypes.c_uint32),
-                ("blocks_demoted", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 2)]
+                ("blocks_demoted", ctypes.c_uint32), ("reserved", ctypes.c_uint32 * 2), ("pages_demoted", ctypes.c_uint64)]
 
 
 class TierInfo(ctypes.Structure):

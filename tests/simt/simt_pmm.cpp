@@ -44,3 +44,24 @@ extern "C" uint32_t simt_pmm_pick(const unsigned long long *stamp, uint32_t n_sl
     simt::launch(dim3(2), dim3(kPmmThreads), [&] { k_pmm_emit_evictions(stamp, n_slots, sel, dest_tier, requests, &count); });
     return count;
 }
+
+// The tiered loop's planning kernels: touched -> per-slot keys and totals, the three plan steps, the two weighted selections.
+// plan: kPlanWords words (zeroed by the caller); returns nothing, the caller reads plan / the arrays.
+extern "C" int simt_pmm_plan_round(uint32_t n_slots, const unsigned long long *stamp, const unsigned long long *dram_stamp,
+                                   const uint32_t *touched, const uint32_t *gpu_resident, const uint32_t *cpu0, const uint32_t *cpu1,
+                                   uint32_t capacity_chunks, unsigned long long dram_capacity_pages, int demote, uint32_t *e_weight,
+                                   uint32_t *e_aux, unsigned long long *d_key, uint32_t *d_weight, uint32_t *plan,
+                                   uvmtier_make_resident_req_t *evict_req, uvmtier_make_resident_req_t *demote_req)
+{
+    simt::launch(dim3(3), dim3(kPmmThreads), [&] { k_pmm_slot_keys(n_slots, stamp, dram_stamp, touched, gpu_resident, cpu0, cpu1, e_weight, e_aux, d_key, d_weight, plan); });
+    simt::launch(dim3(1), dim3(32), [&] { k_pmm_plan(plan, 0, capacity_chunks, dram_capacity_pages, demote); });
+    simt::launch(dim3(1), dim3(kPmmSelectThreads), [&] { k_pmm_select_weighted(stamp, e_weight, e_aux, n_slots, plan + 8, plan + 16); });
+    simt::launch(dim3(1), dim3(32), [&] { k_pmm_plan(plan, 1, capacity_chunks, dram_capacity_pages, demote); });
+    if (demote)
+        simt::launch(dim3(1), dim3(kPmmSelectThreads), [&] { k_pmm_select_weighted(d_key, d_weight, (const uint32_t *)NULL, n_slots, plan + 9, plan + 24); });
+    simt::launch(dim3(1), dim3(32), [&] { k_pmm_plan(plan, 2, capacity_chunks, dram_capacity_pages, demote); });
+    if (demote)
+        simt::launch(dim3(2), dim3(kPmmThreads), [&] { k_pmm_emit_selected(d_key, n_slots, plan + 24, 0, plan + 10, demote_req, plan + 40); });
+    simt::launch(dim3(2), dim3(kPmmThreads), [&] { k_pmm_emit_selected(stamp, n_slots, plan + 16, 1, plan + 10, evict_req, plan + 41); });
+    return 0;
+}

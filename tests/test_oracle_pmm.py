@@ -182,3 +182,59 @@ def test_list_moves_of_service_and_make_resident_and_the_chunks_a_batch_needs():
     st, need2 = service(pk2, st)
     assert need2 > 0 and (stamp_p[stamp_p != before] > before.max()).all()
     assert np.array_equal(T.bool_from_masks(st.gpu_resident).any(axis=1), stamp_p != 0)
+
+
+@pytest.mark.parametrize("seed,n_slots,capacity,dram_cap_blocks,demote", [(1, 300, 120, 40, True), (2, 300, 120, 40, False),
+                                                                          (3, 1000, 200, 10, True), (4, 64, 5, 1000, True),
+                                                                          (5, 500, 450, 0, True)])
+def test_round_planning_kernels_match_the_selection_rule(seed, n_slots, capacity, dram_cap_blocks, demote):
+    """The device-side decisions of one round of the tiered loop (pmm_kernels.cuh, under the emulator) against the rule in
+    plain numpy: victims = ascending stamp until `overflow` of them are va_blocks the round does not fault on; demotion =
+    ascending DRAM stamp among the candidates until the DRAM pages that must go are covered; destination of the victims."""
+    rng = np.random.default_rng(seed)
+    sim = T.load_simt()
+    in_use = rng.random(n_slots) < 0.6
+    stamp = np.where(in_use, rng.permutation(n_slots).astype(np.uint64) + 1 + (rng.random(n_slots) < 0.7) * np.uint64(1 << 63), 0).astype("<u8")
+    touched_b = rng.random(n_slots) < 0.3
+    gres = T.masks_from_bool((rng.random((n_slots, 512)) < 0.3) & in_use[:, None])
+    c0 = T.masks_from_bool((rng.random((n_slots, 512)) < 0.4) & (rng.random((n_slots, 1)) < 0.5))
+    c1 = T.masks_from_bool(rng.random((n_slots, 512)) < 0.1)
+    dram_stamp = (rng.integers(0, 6, n_slots)).astype("<u8")
+    touched = np.zeros((n_slots + 31) // 32, "<u4")
+    for s in np.nonzero(touched_b)[0]:
+        touched[s >> 5] |= np.uint32(1 << (s & 31))
+    e_w, e_a, d_w = np.zeros(n_slots, "<u4"), np.zeros(n_slots, "<u4"), np.zeros(n_slots, "<u4")
+    d_k = np.zeros(n_slots, "<u8")
+    plan = np.zeros(64, "<u4")
+    ev, de = np.zeros(n_slots, R.MAKE_RESIDENT_REQ_DT), np.zeros(n_slots, R.MAKE_RESIDENT_REQ_DT)
+    dram_cap = dram_cap_blocks * 512
+    sim.simt_pmm_plan_round(ctypes.c_uint32(n_slots), P(stamp), P(dram_stamp), P(touched), P(gres), P(c0), P(c1), ctypes.c_uint32(capacity),
+                            ctypes.c_uint64(dram_cap), ctypes.c_int(int(demote)), P(e_w), P(e_a), P(d_k), P(d_w), P(plan), P(ev), P(de))
+    gp, dp = T.bool_from_masks(gres).sum(axis=1), T.bool_from_masks(c0).sum(axis=1)
+    needed, used = int((touched_b & (stamp == 0)).sum()), int((stamp != 0).sum())
+    assert (plan[0], plan[1], plan[2], plan[3]) == (needed, used, int(gp.sum()), int(dp.sum()))
+
+    def select(key, weight, target):
+        live = np.nonzero(key != 0)[0]
+        order = live[np.argsort(key[live], kind="stable")]
+        csum = np.cumsum(weight[order].astype(np.int64))
+        if target <= 0:
+            return order[:0]
+        if len(order) == 0 or csum[-1] < target:
+            return order
+        return live[key[live] <= key[order[int(np.searchsorted(csum, target))]]]
+
+    victims = select(stamp, ((stamp != 0) & ~touched_b).astype(np.int64), used + needed - capacity)
+    assert sorted(ev["slot"][:plan[41]].tolist()) == sorted(victims.tolist()) and plan[16 + 2] == len(victims)
+    arriving = int(gp[victims].sum())
+    demoted = victims[:0]
+    if demote and len(victims) and int(dp.sum()) + arriving > dram_cap:
+        cand = (dp != 0) & (stamp == 0) & ~touched_b
+        demoted = select(np.where(cand, dram_stamp + 1, 0).astype("<u8"), dp, int(dp.sum()) + arriving - dram_cap)
+    assert sorted(de["slot"][:plan[40]].tolist()) == sorted(demoted.tolist())
+    dest = R.TIER_DRAM if int(dp.sum()) - int(dp[demoted].sum()) + arriving <= dram_cap else R.TIER_CXL
+    if len(victims):
+        assert (ev["dest_tier"][:plan[41]] == dest).all() and (ev["flags"][:plan[41]] == R.MR_EVICT_GPU_PAGES).all()
+    if len(demoted):
+        assert (de["dest_tier"][:plan[40]] == R.TIER_CXL).all() and np.array_equal(de["mask_row"][:plan[40]], de["slot"][:plan[40]])
+    assert plan[38] == used - len(victims) + needed + int(touched_b[victims].sum())

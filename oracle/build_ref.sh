@@ -153,6 +153,24 @@ if [ -f "$HERE/ref_thrashing_glue.c" ]; then
     echo "build_ref: built $OUT/libref_thrashing.so"
 fi
 
+# ---------------- the whole thrashing heuristic (detector + hint + pin expiry), verbatim, with a persistent context ----------------
+if [ -f "$HERE/ref_thrashing_hint_glue.c" ]; then
+    pin uvm_perf_thrashing.c 6faca5e5b498600d
+    sed -n '30,43p' "$UVM/uvm_perf_utils.h" > "$TMP/x_perf_saturating.h"
+    sed -n '36,202p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_types.h"
+    sed -n '376,394p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_stamps.h"
+    sed -n '721,1021p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_throttle_pin.h"
+    sed -n '1023,1073p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_detect.h"
+    sed -n '1077,1093p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_region.h"
+    sed -n '1172,1226p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_pinned_update.h"
+    sed -n '1230,1380p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_event.h"
+    sed -n '1382,1780p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_hint.h"
+    sed -n '1822,1906p' "$UVM/uvm_perf_thrashing.c" > "$TMP/x_th_unpin_worker.h"
+    sed -n '1879,1934p' "$UVM/uvm_va_space.c" > "$TMP/x_vs_closest.h"
+    gcc $CFLAGS -DNDEBUG -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_thrashing_hint_glue.c" -o "$OUT/libref_thrashing_hint.so"   # NDEBUG: random streams are not coherent driver histories, the reference's sanity asserts would stop them
+    echo "build_ref: built $OUT/libref_thrashing_hint.so"
+fi
+
 # ---------------- access-counter front half: parse + fetch + preprocess, verbatim, on the fault leg's shims ----------------
 if [ -f "$HERE/ref_access_counters_front_glue.c" ]; then
     pin uvm_turing_access_counter_buffer.c b4afc3558d7cc578

@@ -68,3 +68,75 @@ def test_directed_sequences_match_reference():
     rows += [(10 ** 8 + 63 * i, 1, 500, 12, i % 3, 1, 0) for i in range(20)]     # time stamps closer than the 64 ns unit
     ev = events(rows)
     TH.assert_state_equal(TH.run_ref(ref, ev, 4), TH.run_oracle(orc, ev, 4), "directed")
+
+
+# ---------------- the hint half: throttle, pin, un-pin, epoch reset ----------------
+def _same_hints(a, b, what):
+    assert len(a) == len(b)
+    for i, (x, y) in enumerate(zip(a, b)):
+        for f in ("type", "pin_residency", "pin_processors", "throttle_end"):
+            assert np.array_equal(x[f], y[f]), "%s: hint batch %d field %s: want %s got %s" % (what, i, f, x[f], y[f])
+
+
+@pytest.mark.parametrize("seed,topology,procs,kw", [
+    (1, "pcie", (0, 1), {}), (2, "pcie", (0, 1, 9), {}), (3, "c2c", (0, 1), {}), (4, "nvlink", (1, 9), {}),
+    (5, "nvlink", (0, 1, 9), dict(pref_frac=0.5)), (6, "pcie", (0, 1), dict(pin_threshold=2, pin=1)),
+    (7, "c2c", (0, 1, 2), dict(threshold=1, epoch=30, max_resets=2)), (8, "pcie", (0, 1, 9), dict(pref_frac=1.0, pin_threshold=1, pin=0))])
+def test_hint_restatement_matches_reference_on_driver_histories(seed, topology, procs, kw):
+    """Events, hint queries and pin expiries interleaved the way a driver produces them, through the reference's own
+    uvm_perf_thrashing_get_hint / thrashing_event_cb / thrashing_unpin_pages (compiled verbatim) and through the
+    restatement: every hint and every field of the tracking state."""
+    orc, ref = T.load_oracle(), T.load_ref("thrashing_hint")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_thrashing_hint.so not built (needs /root/reference)")
+    pref_frac = kw.pop("pref_frac", 0.0)
+    cfg = TH.make_cfg(topology, gpus=tuple(p for p in (1, 2, 9) if p in procs) or (1,), **kw)
+    n_slots = 6
+    steps, sim = TH.driver_history(n_slots, 6000, seed, cfg, procs=procs, pref_frac=pref_frac)
+    want, want_h = TH.run_steps_ref(ref, steps, n_slots, cfg)
+    got, got_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    _same_hints(want_h, got_h, "seed %d" % seed)
+    TH.assert_hint_state_equal(want, got, "seed %d" % seed)
+    types = np.concatenate([h["type"] for h in want_h])
+    assert (types == TH.HINT_THROTTLE).sum() > 5 and (types == TH.HINT_PIN).sum() > 5 and (types == TH.HINT_NONE).sum() > 5
+
+
+@pytest.mark.parametrize("seed,topology", [(11, "pcie"), (12, "c2c"), (13, "nvlink")])
+def test_hint_restatement_matches_reference_on_random_streams(seed, topology):
+    """Not a history a driver could produce (queries with arbitrary residency and preferred location, events on pinned
+    pages): every branch of the hint gets exercised, the two implementations must still agree."""
+    orc, ref = T.load_oracle(), T.load_ref("thrashing_hint")
+    if ref is None:
+        pytest.skip("oracle/_ref/libref_thrashing_hint.so not built (needs /root/reference)")
+    rng = np.random.default_rng(seed)
+    procs = np.array([0, 1, 2, 9])
+    cfg = TH.make_cfg(topology, gpus=(1, 2, 9), pin_threshold=3, epoch=50, pin=20)
+    n_slots, now, steps = 4, 5000, []
+    for _ in range(4000):
+        now += int(rng.choice([100, 2000, TH.LAPSE_NS // 3, TH.LAPSE_NS * 2, TH.LAPSE_NS * 60], p=[0.4, 0.3, 0.2, 0.08, 0.02]))
+        r = rng.random()
+        if r < 0.5:
+            n = int(rng.integers(1, 5))
+            ev = np.zeros(n, TH.EVENT_DT)
+            for j in range(n):
+                kind = int(rng.random() < 0.2)
+                flags = 0 if kind else int(rng.choice([0, 0, 0, TH.EV_RESET, TH.EV_PREFETCH]))
+                ev[j] = (now + j, int(rng.integers(0, n_slots)), int(rng.integers(0, 8)), int(rng.integers(1, 4)), int(rng.choice(procs)), kind, flags, 0)
+            steps.append(("events", ev))
+        elif r < 0.97:
+            n = int(rng.integers(1, 6))
+            q = np.zeros(n, TH.QUERY_DT)
+            for j in range(n):
+                res = int(rng.integers(1, 16))
+                resident = sum(1 << int(procs[b]) for b in range(4) if (res >> b) & 1)
+                pref = int(rng.choice([TH.NO_PREF, TH.NO_PREF, 0, 1, 2, 9]))
+                q[j] = (now + j, int(rng.integers(0, n_slots)), int(rng.integers(0, 10)), int(rng.choice(procs)), 0, resident, pref, 0)
+            steps.append(("hints", q))
+        else:
+            steps.append(("expire", now))
+    want, want_h = TH.run_steps_ref(ref, steps, n_slots, cfg)
+    got, got_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    _same_hints(want_h, got_h, "seed %d" % seed)
+    TH.assert_hint_state_equal(want, got, "seed %d" % seed)
+    types = np.concatenate([h["type"] for h in want_h])
+    assert (types == TH.HINT_THROTTLE).sum() > 10 and (types == TH.HINT_PIN).sum() > 20

@@ -89,3 +89,175 @@ def assert_state_equal(want, got, what=""):
         else:
             bad = np.nonzero(w[k] != g[k])[0]
             assert len(bad) == 0, "%s %s differs at %d: want %#x got %#x" % (what, k, bad[0], int(w[k][bad[0]]), int(g[k][bad[0]]))
+
+
+# ---------------- the hint half ----------------
+CFG_DT = np.dtype([("lapse_ns", "<u8"), ("nap_ns", "<u8"), ("epoch_ns", "<u8"), ("pin_ns", "<u8"), ("threshold", "<u4"),
+                   ("pin_threshold", "<u4"), ("max_resets", "<u4"), ("has_memory", "<u4"), ("accessible_from", "<u4", (32,)),
+                   ("can_access", "<u4", (32,)), ("has_fast_link", "<u4", (32,)), ("has_native_atomics", "<u4", (32,))])
+QUERY_DT = np.dtype([("time_stamp", "<u8"), ("slot", "<u4"), ("page", "<u2"), ("requester", "u1"), ("pad", "u1"),
+                     ("resident_processors", "<u4"), ("preferred_location", "<u2"), ("pad2", "<u2")])
+HINT_DT = np.dtype([("throttle_end", "<u8"), ("pin_processors", "<u4"), ("type", "u1"), ("pin_residency", "u1"), ("pad", "<u2")])
+HBLOCK_DT = np.dtype([("last_time_stamp", "<u8"), ("last_thrashing_time_stamp", "<u8"), ("last_processor", "<u2"),
+                      ("num_thrashing_pages", "<u2"), ("tracked", "<u4"), ("pinned_count", "<u2"), ("reset_count", "u1"), ("pad", "u1"),
+                      ("throttling_count", "<u4")])
+assert (CFG_DT.itemsize, QUERY_DT.itemsize, HINT_DT.itemsize, HBLOCK_DT.itemsize) == (560, 24, 16, 32)
+HINT_NONE, HINT_PIN, HINT_THROTTLE = 0, 1, 2
+EV_PREFETCH = 2
+NO_PREF = 0xFFFF
+
+
+def make_cfg(topology="pcie", gpus=(1, 9), lapse_ns=LAPSE_NS, threshold=THRESHOLD, pin_threshold=10, nap=1, epoch=2000, pin=300,
+             max_resets=4):
+    """uvm_perf_thrashing.c:246-310 defaults (nap, epoch, pin are multiples of the lapse).  Topologies: "pcie" -- the CPU
+    reaches only its own memory, GPUs reach the CPU's and each other's, no fast links; "nvlink" -- the same with fast links
+    and native atomics between the GPUs; "c2c" -- everybody reaches everybody over fast links with native atomics."""
+    cfg = np.zeros(1, CFG_DT)
+    cfg["lapse_ns"], cfg["threshold"], cfg["pin_threshold"], cfg["max_resets"] = lapse_ns, threshold, pin_threshold, max_resets
+    cfg["nap_ns"], cfg["epoch_ns"], cfg["pin_ns"] = nap * lapse_ns, epoch * lapse_ns, pin * lapse_ns
+    allp = 1 | sum(1 << g for g in gpus)
+    gmask = allp & ~1
+    cfg["has_memory"] = allp
+    for p in (0,) + tuple(gpus):
+        me = 1 << p
+        if topology == "c2c":
+            acc_from = can = fast = atom = allp
+        else:
+            acc_from = allp if p == 0 else gmask            # who can reach p's memory
+            can = me if p == 0 else allp                    # whose memory p can reach
+            fast = (gmask & ~me) if (topology == "nvlink" and p) else 0
+            atom = me | fast
+        cfg["accessible_from"][0, p], cfg["can_access"][0, p], cfg["has_fast_link"][0, p], cfg["has_native_atomics"][0, p] = acc_from, can, fast, atom
+    return cfg
+
+
+class HintState:
+    """Detector + hint tables on the host."""
+    def __init__(self, n_slots):
+        self.n = n_slots
+        self.blocks = np.zeros(n_slots, HBLOCK_DT)
+        self.page_word = np.zeros(n_slots * 512, "<u8")
+        self.page_procs = np.zeros(n_slots * 512, "<u4")
+        self.thrashing_pages = np.zeros(n_slots * 16, "<u4")
+        self.page_throttle = np.zeros(n_slots * 512, "<u8")
+        self.page_hint = np.zeros(n_slots * 512, "<u4")
+        self.page_throttled = np.zeros(n_slots * 512, "<u4")
+        self.page_deadline = np.zeros(n_slots * 512, "<u8")
+        self.pinned_pages = np.zeros(n_slots * 16, "<u4")
+        self.counters = np.zeros(8, "<u4")
+
+    NAMES = ("blocks", "page_word", "page_procs", "thrashing_pages", "page_throttle", "page_hint", "page_throttled", "page_deadline",
+             "pinned_pages", "counters")
+
+    def tables(self):
+        return (ctypes.c_void_p * 10)(*[getattr(self, k).ctypes.data for k in self.NAMES])
+
+
+def assert_hint_state_equal(want, got, what=""):
+    for k in HintState.NAMES:
+        a, b = getattr(want, k), getattr(got, k)
+        if k == "blocks":
+            for f in HBLOCK_DT.names:
+                if f == "pad":
+                    continue
+                bad = np.nonzero(a[f] != b[f])[0]
+                assert len(bad) == 0, "%s blocks.%s differs at slot %d: want %s got %s" % (what, f, bad[0], a[f][bad[0]], b[f][bad[0]])
+        else:
+            n = 6 if k == "counters" else len(a)
+            bad = np.nonzero(a[:n] != b[:n])[0]
+            assert len(bad) == 0, "%s %s differs at %d (slot %d page %d): want %#x got %#x" % (
+                what, k, bad[0], bad[0] // 512, bad[0] % 512, int(a[bad[0]]), int(b[bad[0]]))
+
+
+def run_steps_oracle(orc, steps, n_slots, cfg):
+    """steps: ("events", array) | ("hints", array) | ("expire", now).  Returns (state, list of hint arrays)."""
+    st, hints = HintState(n_slots), []
+    tb = st.tables()
+    for kind, arg in steps:
+        if kind == "events":
+            orc.oracle_thrashing_note_events_tables(ctypes.c_uint32(len(arg)), P(arg), P(cfg), tb)
+        elif kind == "hints":
+            out = np.zeros(len(arg), HINT_DT)
+            orc.oracle_thrashing_get_hints(ctypes.c_uint32(len(arg)), P(arg), P(cfg), tb, P(out))
+            hints.append(out)
+        else:
+            orc.oracle_thrashing_unpin_expired(ctypes.c_uint32(n_slots), ctypes.c_uint64(arg), tb)
+    return st, hints
+
+
+def run_steps_ref(ref, steps, n_slots, cfg):
+    ref.ref_thrash_open.restype = ctypes.c_void_p
+    h = ctypes.c_void_p(ref.ref_thrash_open(ctypes.c_uint32(n_slots), P(cfg)))
+    hints = []
+    for kind, arg in steps:
+        if kind == "events":
+            ref.ref_thrash_events(h, ctypes.c_uint32(len(arg)), P(arg))
+        elif kind == "hints":
+            out = np.zeros(len(arg), HINT_DT)
+            ref.ref_thrash_hints(h, ctypes.c_uint32(len(arg)), P(arg), P(out))
+            hints.append(out)
+        else:
+            ref.ref_thrash_unpin_expired(h, ctypes.c_uint64(arg))
+    st = HintState(n_slots)
+    ref.ref_thrash_export(h, *[P(getattr(st, k)) for k in HintState.NAMES])
+    ref.ref_thrash_close(h)
+    return st, hints
+
+
+def driver_history(n_slots, n_faults, seed, cfg, procs=(0, 1), hot_pages=6, pref_frac=0.0, query_batch=1):
+    """A coherent history, the way a driver produces it: processors take turns faulting on a few hot pages; every fault
+    asks for a hint and acts on it -- NONE: the page moves to the requester (a MIGRATION event); PIN: it moves to the
+    pin's residency if it is not there (an event on a pinned page: not counted); THROTTLE: nothing happens.  Now and
+    then a revocation, a long pause (window / epoch), the expiry worker, a user migration.  The result is a list of
+    steps for run_steps_*; hints are asked one by one (each depends on the previous one's effect)."""
+    rng = np.random.default_rng(seed)
+    lapse = int(cfg["lapse_ns"][0])
+    now = 10_000
+    where = {}                                            # (slot, page) -> processor holding it
+    steps = []
+    hot = [(int(rng.integers(0, n_slots)), int(rng.integers(0, 512))) for _ in range(hot_pages)]
+    sim = HintState(n_slots)                              # the generator runs the restatement to learn each hint
+    orc = T.load_oracle()
+    tb = sim.tables()
+    pref = {s: (int(rng.choice(procs)) if rng.random() < pref_frac else NO_PREF) for s, _ in hot}
+    for i in range(n_faults):
+        r = rng.random()
+        now += int(rng.choice([200, 3000, lapse // 4, lapse + 100, 40 * lapse, 2500 * lapse], p=[0.45, 0.3, 0.15, 0.07, 0.025, 0.005]))
+        slot, page = hot[int(rng.integers(0, len(hot)))]
+        req = int(rng.choice(procs))
+        cur = where.get((slot, page), 0)
+        if r < 0.04:
+            steps.append(("expire", now))
+            orc.oracle_thrashing_unpin_expired(ctypes.c_uint32(n_slots), ctypes.c_uint64(now), tb)
+            continue
+        if r < 0.10:                                      # a permission revocation on the page
+            ev = np.zeros(1, EVENT_DT); ev[0] = (now, slot, page, 1, req, KIND_REVOCATION, 0, 0)
+            steps.append(("events", ev))
+            orc.oracle_thrashing_note_events_tables(ctypes.c_uint32(1), P(ev), P(cfg), tb)
+            continue
+        if r < 0.115:                                     # cudaMemPrefetchAsync-like user migration of the whole va_block
+            ev = np.zeros(1, EVENT_DT); ev[0] = (now, slot, 0, 512, req, KIND_MIGRATION, EV_RESET, 0)
+            steps.append(("events", ev))
+            orc.oracle_thrashing_note_events_tables(ctypes.c_uint32(1), P(ev), P(cfg), tb)
+            for k in list(where):
+                if k[0] == slot:
+                    where[k] = req
+            continue
+        if req == cur and rng.random() < 0.7:
+            continue                                      # no fault: the page is local
+        q = np.zeros(1, QUERY_DT)
+        q[0] = (now, slot, page, req, 0, 1 << cur, pref[slot], 0)
+        out = np.zeros(1, HINT_DT)
+        steps.append(("hints", q))
+        orc.oracle_thrashing_get_hints(ctypes.c_uint32(1), P(q), P(cfg), tb, P(out))
+        dst = None
+        if out["type"][0] == HINT_NONE:
+            dst = req
+        elif out["type"][0] == HINT_PIN and int(out["pin_residency"][0]) != cur:
+            dst = int(out["pin_residency"][0])
+        if dst is not None and dst != cur:
+            ev = np.zeros(1, EVENT_DT); ev[0] = (now + 50, slot, page, 1, dst, KIND_MIGRATION, 0, 0)
+            steps.append(("events", ev))
+            orc.oracle_thrashing_note_events_tables(ctypes.c_uint32(1), P(ev), P(cfg), tb)
+            where[(slot, page)] = dst
+    return steps, sim

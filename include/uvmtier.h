@@ -770,12 +770,16 @@ NV_STATUS uvmtier_access_counters_service_device(uvmtier_ctx_t *ctx, uint32_t n_
  * pages alone (uvm_perf_prefetch.c:378-381,407) -- and leaves it when the window passes without an event
  * (thrashing_reset_page :1045-1073) or a user-driven migration covers it (:1272-1285).  Per-page state only exists
  * once two different processors touched the va_block inside the window (:1316-1337).
- * Built: this detector.  Not built: the hint that pins or throttles a thrashing page (:1455-1800); no page is ever
- * pinned or throttled here.  Events of evictions and of the first half of staged copies are not sent (:1254-1260). */
+ * Events of evictions and of the first half of staged copies are not sent (:1254-1260).
+ * The second half is the hint (below): what a fault on a thrashing page should do -- wait (throttle), or have the page
+ * pinned somewhere all the thrashing processors can reach and map it from there. */
 #define UVMTIER_PERF_EVENT_MIGRATION  0u
 #define UVMTIER_PERF_EVENT_REVOCATION 1u
 #define UVMTIER_PERF_EVENT_RESETS     0x1u /* flags: a migration whose cause is not a fault, an access counter or a
                                             * prefetch, or that copies instead of moving, or under read duplication */
+#define UVMTIER_PERF_EVENT_PREFETCH   0x2u /* flags: a migration whose cause is PREFETCH (matters only with the hint half
+                                            * on: a fault / access-counter migration onto pinned pages is the pin being
+                                            * carried out and is not an event, is_migration_pinned_pages_update :1198-1226) */
 typedef struct {
     uint64_t time_stamp;     /* ns (NV_GETTIME() at the callback); events of a va_block arrive in time order */
     uint32_t slot;           /* va_block: its row of the state table                                          */
@@ -793,8 +797,48 @@ typedef struct {
     uint16_t last_processor;
     uint16_t num_thrashing_pages;
     uint32_t tracked;                   /* pages != NULL */
-    uint64_t reserved;
+    uint16_t pinned_count;              /* pinned_pages.count (:107): pins ever made, the reference never counts down */
+    uint8_t  thrashing_reset_count;     /* epoch resets so far (:94) */
+    uint8_t  reserved;
+    uint32_t throttling_count;          /* statistic (:103) */
 } uvmtier_thrashing_block_t;            /* 32 bytes */
+
+/* The hint half's parameters (va_space_thrashing_info_t.params :172-199; nap / epoch / pin are the module parameters
+ * times the lapse, :246-310) and the processor topology the decision reads (uvm_va_space_t.accessible_from, can_access,
+ * has_fast_link, has_native_atomics: one 32-bit processor mask per processor id; id 0 = the CPU, GPUs from 1, ids that
+ * share (id - 1) / 8 are SMC partitions of one GPU).  has_memory: uvm_processor_has_memory. */
+typedef struct {
+    uint64_t lapse_ns, nap_ns, epoch_ns, pin_ns;
+    uint32_t threshold, pin_threshold, max_resets, has_memory;
+    uint32_t accessible_from[32], can_access[32], has_fast_link[32], has_native_atomics[32];
+} uvmtier_thrashing_hint_config_t;      /* 560 bytes */
+
+/* One call of uvm_perf_thrashing_get_hint(va_block, address, requester) (:1615): a fault of `requester` on page `page`
+ * of va_block `slot` at time `time_stamp`.  What the reference reads from the va_block comes with the query:
+ * resident_processors = where the page lives now (uvm_va_block_page_resident_processors), preferred_location = the
+ * policy's (0xFFFF = none). */
+typedef struct {
+    uint64_t time_stamp;
+    uint32_t slot;
+    uint16_t page;
+    uint8_t  requester;                 /* < 32 */
+    uint8_t  reserved;
+    uint32_t resident_processors;
+    uint16_t preferred_location;
+    uint16_t reserved2;
+} uvmtier_thrashing_query_t;            /* 24 bytes */
+
+/* uvm_perf_thrashing_hint_t (UVM/uvm_perf_thrashing.h:33-72) */
+#define UVMTIER_THRASHING_HINT_NONE     0u
+#define UVMTIER_THRASHING_HINT_PIN      1u
+#define UVMTIER_THRASHING_HINT_THROTTLE 2u
+typedef struct {
+    uint64_t throttle_end_time_stamp;   /* THROTTLE: when the requester may service faults on the page again */
+    uint32_t pin_processors;            /* PIN: the processors to map to the new residency */
+    uint8_t  type;
+    uint8_t  pin_residency;             /* PIN: where the page is to live; 0xFF otherwise */
+    uint16_t reserved;
+} uvmtier_thrashing_hint_t;             /* 16 bytes */
 
 /* Device tables, one row per va_block slot of the layout.  d_page_word: the reference's first bit-field word of
  * page_thrashing_info_t (:46-63) -- bits 0-57 last_time_stamp in 64 ns units, 58 has_migration_events,
@@ -809,6 +853,17 @@ typedef struct {
     uint64_t lapse_ns;            /* uvm_perf_thrashing_lapse_usec * 1000 (default 500 us, :264) */
     uint32_t threshold;           /* uvm_perf_thrashing_threshold (default 3, :246); 1..7 */
     uint32_t n_slots;
+    /* the hint half (uvmtier_thrashing_enable_hints; NULL until then).  Per page: d_page_throttle = throttling end time
+     * stamp in 64 ns units (:66); d_page_hint = bits 0-7 throttling_count (:71), 8-15 pinned_residency_id + 1 (:81),
+     * 16-23 do_not_throttle_processor_id + 1 (:84); d_page_throttled = throttled_processors (:78); d_page_deadline = when
+     * the pin expires (:132).  d_pinned_pages: pinned_pages.mask, 16 words per slot.  Bit 63 of d_page_word is `pinned`. */
+    uint64_t *d_page_throttle;
+    uint32_t *d_page_hint;
+    uint32_t *d_page_throttled;
+    uint64_t *d_page_deadline;
+    uint32_t *d_pinned_pages;
+    uvmtier_thrashing_hint_config_t *d_hint_config;
+    uvmtier_thrashing_hint_config_t hint_config;
 } uvmtier_thrashing_t;
 
 /* lapse_ns = 0 and threshold = 0 take the reference's defaults.  Tables start out all zero (no history). */
@@ -822,6 +877,35 @@ NV_STATUS uvmtier_thrashing_destroy(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t);
  * dropped -- malformed, or belonging to a second group of a va_block that already had one in this call. */
 NV_STATUS uvmtier_thrashing_note_events_device(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, uint32_t n_events,
                                                const uvmtier_perf_event_t *d_events, uint32_t *d_counters);
+
+/* Turns the hint half on: allocates its (zeroed) tables.  cfg->lapse_ns / threshold are replaced by the detector's.
+ * From now on uvmtier_thrashing_note_events_device also applies what the reference's callback does with pinned and
+ * throttled pages: a reset ends the page's throttling and its pin (:1057-1061), and a fault / access-counter migration
+ * whose whole region is pinned is not an event (:1198-1226, :1293-1295).
+ * uvmtier_thrashing_default_hint_config fills cfg with the module-parameter defaults (pin_threshold 10, nap 1, epoch 2000,
+ * pin 300 lapses, max_resets 4; :246-310) for a box with one CPU (id 0) and the GPUs of gpu_mask: with fast_links = 0 a PCIe
+ * box (the CPU reaches no GPU memory, GPUs reach the CPU's and each other's); with fast_links = 1 NVLink between the GPUs
+ * (fast links and native atomics among them); with fast_links = 2 a coherent box where the CPU is part of that too. */
+void uvmtier_thrashing_default_hint_config(uvmtier_thrashing_hint_config_t *cfg, uint32_t gpu_mask, int fast_links);
+NV_STATUS uvmtier_thrashing_enable_hints(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, const uvmtier_thrashing_hint_config_t *cfg);
+
+/* uvm_perf_thrashing_get_hint (:1615-1780) for n_queries faults, asynchronously on the context's stream: d_hints[i]
+ * answers d_queries[i] and the pages' throttling / pinning state advances as in the reference (throttle periods and the
+ * processor exempt from them :772-832, pinning after pin_threshold periods and where :1455-1595, the quiet-epoch reset of
+ * a va_block :1644-1674).  d_queries must be grouped by slot, in time order inside a group (as the events).
+ * d_counters (8 words, zeroed here): [2] queries dropped (malformed, or a second group of a va_block), [3] throttles,
+ * [4] pins on the requester, [5] pins elsewhere (the reference's num_throttle / num_pin_local / num_pin_remote).
+ * What the caller does with a hint is the fault path's business (UVM/uvm_gpu_replayable_faults.c:1524-1545): THROTTLE =
+ * leave the fault unserviced until the time given, PIN = service it with the pin's residency as destination and map the
+ * processors named. */
+NV_STATUS uvmtier_thrashing_get_hints_device(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, uint32_t n_queries,
+                                             const uvmtier_thrashing_query_t *d_queries, uvmtier_thrashing_hint_t *d_hints,
+                                             uint32_t *d_counters);
+
+/* The reference's delayed worker (thrashing_unpin_pages :1822-1906) at time now_ns: pins whose deadline has passed end
+ * and their pages' tracking state is cleared (they are no longer in thrashing_pages either).  Removing the remote
+ * mappings of such pages (:1892) is the caller's.  d_counters (8 words, zeroed here): [1] pages reset. */
+NV_STATUS uvmtier_thrashing_unpin_expired_device(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, uint64_t now_ns, uint32_t *d_counters);
 
 /* ------------------------------------------------------------------------------------------ */
 /* (1g) Non-replayable faults -- UVM/uvm_gpu_non_replayable_faults.c                           */

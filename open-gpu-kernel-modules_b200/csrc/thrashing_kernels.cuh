@@ -4,8 +4,8 @@
 // in time order inside it) and the lanes take the pages of an event's region, 32 at a time.  Bound: HBM -- 12 B read
 // and written per page an event covers, 24 B per event, 96 B per va_block touched.
 #pragma once
-#include "common.cuh"
 #include "service_kernels.cuh"   // kMaxSlots
+#include "thrashing_hint.cuh"
 
 namespace uvmtier_k {
 
@@ -23,7 +23,7 @@ __device__ __forceinline__ bool thrash_event_ok(const uvmtier_perf_event_t &e, u
 // scratch: [0] number of segments, [4 ..] first event of every segment, then one bit per slot.
 // counters: [0] detections, [1] page resets, [2] events dropped (malformed, or their va_block showed up in a second,
 // separate group of the same call)
-__global__ void __launch_bounds__(kThrashThreads)
+UVMTIER_KERNEL void __launch_bounds__(kThrashThreads)
 k_thrash_heads(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, uint32_t n_slots, uint32_t *__restrict__ scratch,
                uint32_t *__restrict__ counters)
 {
@@ -43,12 +43,15 @@ k_thrash_heads(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, u
     }
 }
 
-__global__ void __launch_bounds__(kThrashThreads)
+// th.page_throttle != NULL: the hint half is on (thrashing_hint.cuh) -- a reset also ends the page's throttling and pin, and
+// a fault-driven migration whose whole region is pinned is not an event.
+UVMTIER_KERNEL void __launch_bounds__(kThrashThreads)
 k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, uint32_t n_slots, unsigned long long lapse_ns,
                 uint32_t threshold, uvmtier_thrashing_block_t *__restrict__ blocks, unsigned long long *__restrict__ page_word,
                 uint32_t *__restrict__ page_procs, uint32_t *__restrict__ masks, const uint32_t *__restrict__ scratch,
-                uint32_t *__restrict__ counters)
+                uint32_t *__restrict__ counters, thrash_hint_tables th)
 {
+    const bool hints_on = th.page_throttle != NULL;
     const uint32_t *seg = scratch + 4;
     const uint32_t n_seg = scratch[0];
     const int lane = threadIdx.x & 31;
@@ -59,6 +62,7 @@ k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, 
         const uint32_t slot = ev[i].slot;
         uvmtier_thrashing_block_t blk = blocks[slot];
         uint32_t mask = lane < 16 ? masks[(size_t)slot * 16 + lane] : 0u;
+        uint32_t pinned_mask = (hints_on && lane < 16) ? th.pinned_pages[(size_t)slot * 16 + lane] : 0u;
         unsigned long long *words = page_word + (size_t)slot * 512;
         uint32_t *procs = page_procs + (size_t)slot * 512;
         uvmtier_perf_event_t e_next = ev[i];
@@ -83,16 +87,33 @@ k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, 
                         const uint32_t mw = __shfl_sync(kThrashFullWarp, mask, base >> 5);
                         const bool hit = p >= first && p < outer && ((mw >> lane) & 1u);
                         if (hit) {
-                            words[p] &= kThrashPinned;     // thrashing_reset_page :1063-1067
+                            if (hints_on) {                // :1057-1061: the throttling and the pin end with the history
+                                hint_reset_page_extras(th, (size_t)slot * 512 + p);
+                                words[p] = 0;
+                            }
+                            else
+                                words[p] &= kThrashPinned; // thrashing_reset_page :1063-1067
                             procs[p] = 0;
                             resets++;
                         }
                         const uint32_t b = __ballot_sync(kThrashFullWarp, hit);
-                        if (lane == (int)(base >> 5)) mask &= ~b;
+                        if (lane == (int)(base >> 5)) { mask &= ~b; pinned_mask &= ~b; }
                         blk.num_thrashing_pages = (uint16_t)(blk.num_thrashing_pages - __popc(b));
                     }
                 }
                 continue;
+            }
+            if (hints_on && blk.tracked && e.kind == UVMTIER_PERF_EVENT_MIGRATION && !(e.flags & UVMTIER_PERF_EVENT_PREFETCH)) {
+                // is_migration_pinned_pages_update :1198-1226: the pin being carried out, not an event
+                bool full = true;
+                for (uint32_t base = first & ~31u; base < outer; base += 32) {
+                    const uint32_t pw = __shfl_sync(kThrashFullWarp, pinned_mask, base >> 5);
+                    const uint32_t lo = first > base ? first - base : 0u, hi = outer - base < 32u ? outer - base : 32u;
+                    const uint32_t want = (hi >= 32u ? 0xffffffffu : ((1u << hi) - 1u)) & ~((1u << lo) - 1u);
+                    full = full && (pw & want) == want;
+                }
+                if (full)
+                    continue;
             }
             bool skip = false;
             if (!blk.tracked) {
@@ -127,6 +148,8 @@ k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, 
                                 w |= e.kind == UVMTIER_PERF_EVENT_MIGRATION ? kThrashMig : kThrashRev;
                             }
                             else if (num >= threshold && !(w & kThrashPinned)) {
+                                if (hints_on)
+                                    hint_throttling_reset(th, (size_t)slot * 512 + p);     // :1057 (not pinned: nothing to un-pin)
                                 w &= kThrashPinned;        // thrashing_reset_page :1045-1073
                                 pr = 0;
                                 clr = in_mask;
@@ -148,6 +171,7 @@ k_thrash_events(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, 
         }
         if (lane == 0) blocks[slot] = blk;
         if (lane < 16) masks[(size_t)slot * 16 + lane] = mask;
+        if (hints_on && lane < 16) th.pinned_pages[(size_t)slot * 16 + lane] = pinned_mask;
     }
     detections = __reduce_add_sync(kThrashFullWarp, detections);
     resets = __reduce_add_sync(kThrashFullWarp, resets);

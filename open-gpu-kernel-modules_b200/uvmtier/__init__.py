@@ -83,7 +83,9 @@ class ThrashingState(ctypes.Structure):
     """uvmtier_thrashing_t"""
     _fields_ = [("d_blocks", ctypes.c_void_p), ("d_page_word", ctypes.c_void_p), ("d_page_processors", ctypes.c_void_p),
                 ("d_thrashing_pages", ctypes.c_void_p), ("d_scratch", ctypes.c_void_p), ("lapse_ns", ctypes.c_uint64),
-                ("threshold", ctypes.c_uint32), ("n_slots", ctypes.c_uint32)]
+                ("threshold", ctypes.c_uint32), ("n_slots", ctypes.c_uint32), ("d_page_throttle", ctypes.c_void_p),
+                ("d_page_hint", ctypes.c_void_p), ("d_page_throttled", ctypes.c_void_p), ("d_page_deadline", ctypes.c_void_p),
+                ("d_pinned_pages", ctypes.c_void_p), ("d_hint_config", ctypes.c_void_p), ("hint_config", ctypes.c_uint8 * 560)]
 
 
 class TieringStats(ctypes.Structure):
@@ -393,11 +395,44 @@ class Context:
             self.free(d_ev); self.free(d_cnt)
 
     def thrashing_tables(self, t):
-        """The detector's tables back on the host: va_block records (32-byte rows), page words, page processors, masks."""
+        """The heuristic's tables back on the host: va_block records (32-byte rows), page words, page processors, masks, and
+        the hint half's tables when it is on."""
         n = t.n_slots
-        return dict(blocks=self.from_device(t.d_blocks, n * 32, "u1"), page_word=self.from_device(t.d_page_word, n * 512, "<u8"),
-                    page_procs=self.from_device(t.d_page_processors, n * 512, "<u4"),
-                    thrashing_pages=self.from_device(t.d_thrashing_pages, n * 16, "<u4"))
+        out = dict(blocks=self.from_device(t.d_blocks, n * 32, "u1"), page_word=self.from_device(t.d_page_word, n * 512, "<u8"),
+                   page_procs=self.from_device(t.d_page_processors, n * 512, "<u4"),
+                   thrashing_pages=self.from_device(t.d_thrashing_pages, n * 16, "<u4"))
+        if t.d_page_throttle:
+            out.update(page_throttle=self.from_device(t.d_page_throttle, n * 512, "<u8"), page_hint=self.from_device(t.d_page_hint, n * 512, "<u4"),
+                       page_throttled=self.from_device(t.d_page_throttled, n * 512, "<u4"),
+                       page_deadline=self.from_device(t.d_page_deadline, n * 512, "<u8"),
+                       pinned_pages=self.from_device(t.d_pinned_pages, n * 16, "<u4"))
+        return out
+
+    def thrashing_enable_hints(self, t, cfg):
+        """uvmtier_thrashing_enable_hints; cfg: a 560-byte uvmtier_thrashing_hint_config_t record (numpy)."""
+        _check(lib().uvmtier_thrashing_enable_hints(self._h, ctypes.byref(t), P(cfg)), "uvmtier_thrashing_enable_hints")
+
+    def thrashing_get_hints(self, t, queries):
+        """uvmtier_thrashing_get_hints_device on a host array of 24-byte queries (grouped by slot).  Returns (hints as 16-byte
+        records, the eight counters)."""
+        d_q, d_h, d_cnt = self.to_device(queries), self.alloc(max(len(queries), 1) * 16), self.alloc(32)
+        try:
+            _check(lib().uvmtier_thrashing_get_hints_device(self._h, ctypes.byref(t), ctypes.c_uint32(len(queries)), P(d_q), P(d_h), P(d_cnt)),
+                   "uvmtier_thrashing_get_hints_device")
+            self.synchronize()
+            return self.from_device(d_h, len(queries) * 16, "u1"), self.from_device(d_cnt, 8, "<u4")
+        finally:
+            self.free(d_q); self.free(d_h); self.free(d_cnt)
+
+    def thrashing_unpin_expired(self, t, now_ns):
+        d_cnt = self.alloc(32)
+        try:
+            _check(lib().uvmtier_thrashing_unpin_expired_device(self._h, ctypes.byref(t), ctypes.c_uint64(now_ns), P(d_cnt)),
+                   "uvmtier_thrashing_unpin_expired_device")
+            self.synchronize()
+            return self.from_device(d_cnt, 8, "<u4")
+        finally:
+            self.free(d_cnt)
 
     def pmm_stamps(self, pmm):
         return self.from_device(pmm.d_stamp, pmm.n_slots, "<u8")

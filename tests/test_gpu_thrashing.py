@@ -82,3 +82,61 @@ def test_thrashing_entry_points_reject_bad_calls():
         ctx.thrashing_destroy(t)
         assert t.d_blocks is None and t.n_slots == 0
         ctx.free(d)
+
+
+# ---------------- the hint half on the GPU ----------------
+def _same_hints(a, b, what):
+    assert len(a) == len(b)
+    for i, (x, y) in enumerate(zip(a, b)):
+        for f in ("type", "pin_residency", "pin_processors", "throttle_end"):
+            assert np.array_equal(x[f], y[f]), "%s: hint batch %d field %s: want %s got %s" % (what, i, f, x[f], y[f])
+
+
+@pytest.mark.parametrize("seed,topology,procs,kw", [(41, "pcie", (0, 1), dict(pin_threshold=3)), (42, "c2c", (0, 1, 2), dict(threshold=1, epoch=30, max_resets=2)),
+                                                    (43, "nvlink", (0, 1, 9), dict(pin_threshold=2, pin=1))])
+def test_gpu_hints_match_restatement_on_driver_histories(seed, topology, procs, kw):
+    """uvmtier_thrashing_get_hints_device / _note_events_device / _unpin_expired_device interleaved the way a driver would
+    call them, against the restatement (held against the reference's own code in tests/test_oracle_thrashing.py): every
+    hint, every field of the tracking state, the counters."""
+    import uvmtier
+    from uvmtier import blockstate as BS, tracegen as TG
+    orc = T.load_oracle()
+    cfg = TH.make_cfg(topology, gpus=tuple(p for p in (1, 2, 9) if p in procs), **kw)
+    n_slots = 6
+    steps, _ = TH.driver_history(n_slots, 2500, seed, cfg, procs=procs, hot_pages=4)
+    want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    layout = BS.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1))
+    with uvmtier.Context(0) as ctx:
+        got, got_h = TH.run_steps_gpu(ctx, steps, layout, n_slots, cfg)
+    _same_hints(want_h, got_h, "seed %d" % seed)
+    TH.assert_hint_state_equal(want, got, "seed %d" % seed)
+    types = np.concatenate([h["type"] for h in want_h])
+    assert (types == TH.HINT_THROTTLE).sum() > 3 and (types == TH.HINT_PIN).sum() > 0
+
+
+def test_gpu_hints_match_restatement_on_random_batches_and_many_blocks():
+    """Batches of queries over 512 va_blocks (one thread per va_block's group), events and expiries in between."""
+    import uvmtier
+    from uvmtier import blockstate as BS, tracegen as TG
+    orc = T.load_oracle()
+    cfg = TH.make_cfg("pcie", gpus=(1, 2, 9), pin_threshold=3, epoch=50, pin=20)
+    n_slots = 512
+    steps = TH.random_stream(77, n_slots, 400, batch=3000)
+    want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    layout = BS.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1))
+    with uvmtier.Context(0) as ctx:
+        got, got_h = TH.run_steps_gpu(ctx, steps, layout, n_slots, cfg)
+        # the hint half has to be switched on first, and only once
+        t = ctx.thrashing_create(layout)
+        lib = uvmtier.lib()
+        import ctypes
+        one = ctx.alloc(64)
+        assert lib.uvmtier_thrashing_get_hints_device(ctx.handle, ctypes.byref(t), ctypes.c_uint32(1), uvmtier.P(one), uvmtier.P(one), uvmtier.P(one)) == 0x40
+        ctx.thrashing_enable_hints(t, cfg)
+        assert lib.uvmtier_thrashing_enable_hints(ctx.handle, ctypes.byref(t), uvmtier.P(cfg)) == 0x40
+        ctx.free(one)
+        ctx.thrashing_destroy(t)
+    _same_hints(want_h, got_h, "batches")
+    TH.assert_hint_state_equal(want, got, "batches")
+    types = np.concatenate([h["type"] for h in want_h])
+    assert (types == TH.HINT_THROTTLE).sum() > 50 and (types == TH.HINT_PIN).sum() > 50

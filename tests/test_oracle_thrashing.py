@@ -140,3 +140,31 @@ def test_hint_restatement_matches_reference_on_random_streams(seed, topology):
     TH.assert_hint_state_equal(want, got, "seed %d" % seed)
     types = np.concatenate([h["type"] for h in want_h])
     assert (types == TH.HINT_THROTTLE).sum() > 10 and (types == TH.HINT_PIN).sum() > 20
+
+
+@pytest.mark.parametrize("seed,topology,procs", [(21, "pcie", (0, 1)), (22, "c2c", (0, 1, 2)), (23, "nvlink", (0, 1, 9))])
+def test_simt_hint_kernels_match_restatement_on_driver_histories(seed, topology, procs):
+    """The product's kernels (k_thrash_events with the hint tables, k_thrash_hints, k_thrash_unpin_expired) under the
+    emulator against the restatement, on interleaved events / one-by-one hint queries / expiries."""
+    orc, sim = T.load_oracle(), T.load_simt()
+    cfg = TH.make_cfg(topology, gpus=tuple(p for p in (1, 2, 9) if p in procs), pin_threshold=3, pin=20, epoch=200)
+    n_slots = 5
+    steps, _ = TH.driver_history(n_slots, 600, seed, cfg, procs=procs, hot_pages=2)
+    want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    got, got_h = TH.run_steps_simt(sim, steps, n_slots, cfg)
+    _same_hints(want_h, got_h, "seed %d" % seed)
+    TH.assert_hint_state_equal(want, got, "seed %d" % seed)
+    types = np.concatenate([h["type"] for h in want_h])
+    assert (types == TH.HINT_THROTTLE).sum() > 3 and (types == TH.HINT_PIN).sum() > 0
+
+
+@pytest.mark.parametrize("seed,topology", [(31, "pcie"), (32, "nvlink")])
+def test_simt_hint_kernels_match_restatement_on_random_streams(seed, topology):
+    orc, sim = T.load_oracle(), T.load_simt()
+    cfg = TH.make_cfg(topology, gpus=(1, 2, 9), pin_threshold=3, epoch=50, pin=20)
+    n_slots = 4
+    steps = TH.random_stream(seed, n_slots, 300)
+    want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
+    got, got_h = TH.run_steps_simt(sim, steps, n_slots, cfg)
+    _same_hints(want_h, got_h, "seed %d" % seed)
+    TH.assert_hint_state_equal(want, got, "seed %d" % seed)

@@ -261,3 +261,77 @@ def driver_history(n_slots, n_faults, seed, cfg, procs=(0, 1), hot_pages=6, pref
             orc.oracle_thrashing_note_events_tables(ctypes.c_uint32(1), P(ev), P(cfg), tb)
             where[(slot, page)] = dst
     return steps, sim
+
+
+def run_steps_simt(sim, steps, n_slots, cfg):
+    st, hints = HintState(n_slots), []
+    tb = st.tables()
+    for kind, arg in steps:
+        if kind == "events":
+            sim.simt_thrash_events(ctypes.c_uint32(n_slots), ctypes.c_uint32(len(arg)), P(arg), ctypes.c_uint64(int(cfg["lapse_ns"][0])),
+                                   ctypes.c_uint32(int(cfg["threshold"][0])), tb)
+        elif kind == "hints":
+            out = np.zeros(len(arg), HINT_DT)
+            sim.simt_thrash_hints(ctypes.c_uint32(n_slots), ctypes.c_uint32(len(arg)), P(arg), P(cfg), tb, P(out))
+            hints.append(out)
+        else:
+            sim.simt_thrash_unpin_expired(ctypes.c_uint32(n_slots), ctypes.c_uint64(arg), tb)
+    return st, hints
+
+
+def run_steps_gpu(ctx, steps, layout, n_slots, cfg):
+    """The same steps through the C ABI on the GPU; returns (HintState downloaded, hints)."""
+    t = ctx.thrashing_create(layout, int(cfg["lapse_ns"][0]), int(cfg["threshold"][0]))
+    ctx.thrashing_enable_hints(t, cfg)
+    hints = []
+    cnt = np.zeros(8, np.int64)
+    try:
+        for kind, arg in steps:
+            if kind == "events":
+                c = ctx.thrashing_note_events(t, arg)
+                cnt[:3] += c[:3]
+            elif kind == "hints":
+                h, c = ctx.thrashing_get_hints(t, arg)
+                hints.append(h.view(HINT_DT))
+                cnt[2:6] += c[2:6]
+            else:
+                cnt[1] += ctx.thrashing_unpin_expired(t, arg)[1]
+        tabs = ctx.thrashing_tables(t)
+    finally:
+        ctx.thrashing_destroy(t)
+    st = HintState(n_slots)
+    st.blocks = tabs["blocks"].view(HBLOCK_DT)
+    for k in ("page_word", "page_procs", "thrashing_pages", "page_throttle", "page_hint", "page_throttled", "page_deadline", "pinned_pages"):
+        setattr(st, k, tabs[k])
+    st.counters[:6] = cnt[:6]
+    return st, hints
+
+
+def random_stream(seed, n_slots, n_steps, procs=(0, 1, 2, 9), batch=6):
+    """Events, query batches (grouped by slot, time order inside a slot) and expiries; not a coherent driver history."""
+    rng = np.random.default_rng(seed)
+    procs = np.array(procs)
+    now, steps = 5000, []
+    for _ in range(n_steps):
+        now += int(rng.choice([100, 2000, LAPSE_NS // 3, LAPSE_NS * 2, LAPSE_NS * 60], p=[0.4, 0.3, 0.2, 0.08, 0.02]))
+        r = rng.random()
+        if r < 0.5:
+            n = int(rng.integers(1, batch))
+            ev = np.zeros(n, EVENT_DT)
+            for j in range(n):
+                kind = int(rng.random() < 0.2)
+                flags = 0 if kind else int(rng.choice([0, 0, 0, EV_RESET, EV_PREFETCH]))
+                ev[j] = (now + j, int(rng.integers(0, n_slots)), int(rng.integers(0, 8)), int(rng.integers(1, 4)), int(rng.choice(procs)), kind, flags, 0)
+            steps.append(("events", by_slot(ev)))
+        elif r < 0.97:
+            n = int(rng.integers(1, batch + 1))
+            q = np.zeros(n, QUERY_DT)
+            for j in range(n):
+                res = int(rng.integers(1, 1 << len(procs)))
+                resident = sum(1 << int(procs[b]) for b in range(len(procs)) if (res >> b) & 1)
+                pref = int(rng.choice([NO_PREF, NO_PREF] + [int(p) for p in procs]))
+                q[j] = (now + j, int(rng.integers(0, n_slots)), int(rng.integers(0, 10)), int(rng.choice(procs)), 0, resident, pref, 0)
+            steps.append(("hints", q[np.argsort(q["slot"], kind="stable")]))
+        else:
+            steps.append(("expire", now))
+    return steps

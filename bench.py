@@ -59,6 +59,34 @@ def peaks():
     return 6650.0, "fallback (B200_PROFILING.md)"
 
 
+def bind_near_gpu(index):
+    """Pins this process (the thread that services GPU `index`, and the pinned buffers it allocates next: first touch) to
+    the CPUs of the GPU's NUMA node, as UVM/uvm_gpu_isr.c:598-625 does for the fault-servicing bottom half.  Returns what was
+    found and done, for the bench line; the caller restores the old affinity afterwards."""
+    info = {"gpu": index, "affinity_before": len(os.sched_getaffinity(0))}
+    try:
+        bdf = subprocess.run(["nvidia-smi", "-i", str(index), "--query-gpu=pci.bus_id", "--format=csv,noheader"],
+                             capture_output=True, text=True, timeout=20).stdout.strip().lower()
+        info["pci_bus_id"] = bdf
+        short = bdf[4:] if len(bdf) > 12 else bdf                      # nvidia-smi prints an 8-digit domain, sysfs a 4-digit one
+        node = int(open("/sys/bus/pci/devices/%s/numa_node" % short).read().strip())
+        info["numa_node"] = node
+        nodes = [d for d in os.listdir("/sys/devices/system/node") if d.startswith("node")]
+        info["numa_nodes_on_host"] = len(nodes)
+        if node >= 0:
+            cpus = set()
+            for part in open("/sys/devices/system/node/node%d/cpulist" % node).read().strip().split(","):
+                a, _, b = part.partition("-")
+                cpus.update(range(int(a), int(b or a) + 1))
+            cpus &= os.sched_getaffinity(0)
+            if cpus:
+                os.sched_setaffinity(0, cpus)
+                info["bound_to_cpus"] = len(cpus)
+    except Exception as e:                                              # no sysfs entry, no nvidia-smi: run unbound and say so
+        info["error"] = repr(e)[:120]
+    return info
+
+
 class ClockSampler(threading.Thread):
     """Samples nvidia-smi clocks / throttle reasons while the timed regions run."""
 
@@ -913,6 +941,9 @@ def main():
 
     # ---- e2e: host-buffer entry point for stage A/B with pinned memory (H2D + D2H in the timed region), then the
     #      service pass on the device-resident sorted view, then the D2H of what a caller consumes (records, runs) ----
+    old_affinity = os.sched_getaffinity(0)
+    binding = bind_near_gpu(local_rank)
+
     def pinned(arr):
         p = ctypes.c_void_p()
         chk(lib.uvmtier_mem_alloc_host_pinned(h, ctypes.c_size_t(max(arr.nbytes, 1)), ctypes.byref(p)), "pinned")
@@ -934,7 +965,9 @@ def main():
     class Readback(ctypes.Structure):
         _fields_ = [("h_batches", ctypes.c_void_p), ("h_entry_flags", ctypes.c_void_p), ("h_counters", ctypes.c_void_p)]
     readback = Readback(hp_bat.ctypes.data, hp_flags.ctypes.data, hp_cnt.ctypes.data)
-    E2E_CHUNKS = max(1, int(os.environ.get("UVMTIER_E2E_CHUNKS", "8")))
+    # 8 chunks on a quiet host; with 8 rings sharing the host's memory the copy is the long pole (23 GB/s per GPU instead of
+    # 54) and finer chunks hide more of the rest behind it: measured 1.295 ms with 8 chunks, 1.206 ms with 16 at N = 8
+    E2E_CHUNKS = max(1, int(os.environ.get("UVMTIER_E2E_CHUNKS", "16" if world >= 8 else "8")))
     E2E_MODE = os.environ.get("UVMTIER_E2E_MODE", "")        # diagnostics only: "copy", "fetch", "norb" (no copy-back)
 
     def e2e_step(full):
@@ -978,6 +1011,19 @@ def main():
         assert np.array_equal(hp_bat["num_coalesced_faults"], bat["num_coalesced_faults"]), "e2e and device paths disagree"
         assert int(hp_cnt[0]) == n_runs
     e2e_full_ms = float(np.mean([e2e_step(True) for _ in range(3)])) * 1e3
+    # the floor of the end-to-end number: this step's ring alone crossing the host link, all ranks at once (the N rings
+    # share the host's memory controllers and root ports)
+    def h2d_alone():
+        ctx.synchronize()
+        t0 = time.perf_counter()
+        chk(lib.uvmtier_memcpy_h2d_async(h, P(d_ring), P(hp_ring), ctypes.c_size_t(ring_host.nbytes)), "h2d")
+        ctx.synchronize()
+        return time.perf_counter() - t0
+    h2d_alone()
+    barrier()
+    h2d_floor_ms = float(np.mean([h2d_alone() for _ in range(5)])) * 1e3
+    barrier()
+    os.sched_setaffinity(0, old_affinity)
 
     migration = None
     if not args.no_migration:
@@ -1004,9 +1050,12 @@ def main():
     # ---- max over ranks ----
     if dist is not None:
         import torch
-        t = torch.tensor([ms_step, e2e_ms, k1_ms, svc_ms], dtype=torch.float64, device="cuda")
+        t = torch.tensor([ms_step, e2e_ms, k1_ms, svc_ms, h2d_floor_ms], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-        ms_step, e2e_ms, k1_ms, svc_ms = [float(x) for x in t.tolist()]
+        ms_step, e2e_ms, k1_ms, svc_ms, h2d_floor_ms = [float(x) for x in t.tolist()]
+        gathered = [None] * world
+        dist.all_gather_object(gathered, binding)
+        binding = gathered
 
     peak, peak_src = peaks()
     dom_is_k1 = k1_ms >= svc_ms
@@ -1029,6 +1078,9 @@ def main():
         "config": config_dict(args.trace, world),
         "e2e": {"value": world * N_ENTRIES / (e2e_ms * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h_result),
                 "ms_per_step": e2e_ms,
+                "h2d_floor_ms": h2d_floor_ms, "h2d_floor_GBs_per_gpu": h2d / (h2d_floor_ms * 1e-3) / 1e9,
+                "h2d_floor_what": "the step's ring alone, one cudaMemcpyAsync from pinned host memory per rank, all ranks at once, max over ranks",
+                "chunks": E2E_CHUNKS, "binding": binding,
                 "result": "batch headers + per-fault flags + run counter (what the caller of service_fault_batch consumes)",
                 "full_readback": {"value": n / (e2e_full_ms * 1e-3), "ms_per_step": e2e_full_ms, "d2h_bytes_per_step": int(d2h_full),
                                   "what": "also ring, service records and copy runs (rank-local, not max over ranks)"}},

@@ -372,6 +372,11 @@ typedef struct {
 #define UVMTIER_SF_ACCESS_SHIFT     5       /* 3 bits: service access type */
 #define UVMTIER_SF_REASON_SHIFT     8       /* 3 bits: UvmEventFatalReason */
 #define UVMTIER_SF_CANCEL_SHIFT     12      /* 1 bit: uvm_fault_cancel_va_mode_t */
+/* with thrashing hints attached (uvmtier_service_fault_batches_thrashing_device) */
+#define UVMTIER_SF_THROTTLED        0x2000u /* hint THROTTLE: mark_fault_throttled (:1537), not serviced; replay later */
+#define UVMTIER_SF_PINNED           0x4000u /* hint PIN on the faulting GPU: the page is in thrashing_pin_mask (:1541-1545), serviced */
+#define UVMTIER_SF_PIN_REMOTE       0x8000u /* hint PIN on another processor: not serviced by this pass (it moves pages to the
+                                             * faulting GPU only); the caller moves / maps the page at the pin's residency */
 
 /* What servicing one va_block run did: the uvm_service_block_context_t fields that survive the call
  * (UVM/uvm_va_block_types.h), plus the copy list. */
@@ -906,6 +911,32 @@ NV_STATUS uvmtier_thrashing_get_hints_device(uvmtier_ctx_t *ctx, uvmtier_thrashi
  * and their pages' tracking state is cleared (they are no longer in thrashing_pages either).  Removing the remote
  * mappings of such pages (:1892) is the caller's.  d_counters (8 words, zeroed here): [1] pages reset. */
 NV_STATUS uvmtier_thrashing_unpin_expired_device(uvmtier_ctx_t *ctx, uvmtier_thrashing_t *t, uint64_t now_ns, uint32_t *d_counters);
+
+/* uvmtier_service_fault_batches_device with the hint inside the fault loop, where the reference asks for it
+ * (service_fault_batch_block_locked, UVM/uvm_gpu_replayable_faults.c:1524-1545): a fault that passed the duplicate,
+ * permission and already-authorised checks calls uvm_perf_thrashing_get_hint(va_block, address, this GPU) -- requester =
+ * layout->gpu_id, residency read from the state table, preferred location from the table, time = d_batch_time_ns[batch]
+ * (NV_GETTIME() when the batch is serviced) -- and
+ *   THROTTLE   the fault is marked (mark_fault_throttled :1537 -> UVMTIER_SF_THROTTLED) and not serviced;
+ *   PIN        the page joins thrashing_pin_mask (UVMTIER_SF_PINNED) and uvm_va_block_select_residency takes the pin's
+ *              residency (UVM/uvm_va_block.c:11624-11628): on this GPU the fault is serviced as ever; elsewhere (the CPU on a
+ *              PCIe box) it is marked UVMTIER_SF_PIN_REMOTE and left to the caller -- this pass moves pages to the faulting
+ *              GPU only, it does not service a GPU fault by making the page resident on another processor and mapping it
+ *              remotely.  The hint's state change (the pin) is recorded either way;
+ *   and the prefetcher leaves the va_block's thrashing pages alone (UVM/uvm_perf_prefetch.c:378-381, 407).
+ * Only va_blocks the detector tracks page by page (uvmtier_thrashing_block_t.tracked) are affected: they are serviced by
+ * the warp-per-block kernel one entry at a time; everything else takes the regular path.  The detector is fed by the
+ * caller (uvmtier_thrashing_note_events_device with the migrations the records / copy runs describe), as the reference's
+ * is by its perf events.  d_thrashing_counters (8 words, zeroed here): [3] throttles, [4] pins on this GPU, [5] pins
+ * elsewhere.  Needs uvmtier_thrashing_enable_hints; layout->gpu_id < 32. */
+NV_STATUS uvmtier_service_fault_batches_thrashing_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                         const uvmtier_ordered_fault_t *d_ordered,
+                                                         const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                         const uvmtier_va_layout_t *layout, const uvmtier_block_state_t *state,
+                                                         uvmtier_thrashing_t *thrashing, const uint64_t *d_batch_time_ns,
+                                                         uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                         uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters,
+                                                         uint32_t *d_thrashing_counters);
 
 /* ------------------------------------------------------------------------------------------ */
 /* (1g) Non-replayable faults -- UVM/uvm_gpu_non_replayable_faults.c                           */

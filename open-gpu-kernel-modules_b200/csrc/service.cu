@@ -59,8 +59,12 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
                               const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches, const uvmtier_va_layout_t *lay,
                               const uvmtier_block_state_t *state, uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
                               uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters, uint32_t batch_base = 0,
-                              bool zero_outputs = true, bool non_replayable = false)
+                              bool zero_outputs = true, bool non_replayable = false, const svc_thrash_params *thrash = NULL)
 {
+    svc_thrash_params tp;
+    memset(&tp, 0, sizeof(tp));
+    if (thrash)
+        tp = *thrash;
     const uint32_t B = ctx->faults->gp.max_batch_size;
     const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
     const size_t total = (size_t)n_batches * B;
@@ -114,13 +118,13 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
                    (unsigned long long *)v.cw, v.batch_unmapped, (uint2 *)v.slotpos);
     const uint32_t list_heavy_min = kHeavyMinEntries;
     UVMTIER_LAUNCH(k_service_alloc, (n_slots + 255) / 256, 256, 0, ctx->stream, n_slots, cw, list_heavy_min, v.offset, v.cursor, v.hist,
-                   v.light_rank);
+                   v.light_rank, (const uvmtier_thrashing_block_t *)tp.th.blocks);
     UVMTIER_LAUNCH(k_service_fill, (int)grid, kSvcThreads, 0, ctx->stream, (uint32_t)total, (const uint2 *)v.slotpos, v.offset, v.list);
     size_t sgrid = ((size_t)n_slots + (kSortThreads / 32) - 1) / (kSortThreads / 32);
     if (sgrid > cap)
         sgrid = cap;
     UVMTIER_LAUNCH(k_service_sort_lists, (int)sgrid, kSortThreads, 0, ctx->stream, n_slots, cw, v.offset, v.list, list_heavy_min,
-                   v.big, v.heavy, v.hist, v.light_rank, v.light);
+                   v.big, v.heavy, v.hist, v.light_rank, v.light, (const uvmtier_thrashing_block_t *)tp.th.blocks);
     // Three independent branches from here: the light va_blocks (lane groups), the heavy ones (their long lists
     // are sorted first, then a warp each) and the runs outside every va_range.  They touch different va_blocks,
     // records and entry flags, and add to the batch counters atomically; the two small branches run on side streams
@@ -131,7 +135,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     UVMTIER_CUDA(cudaStreamWaitEvent(s_unmapped, ctx->aux_events[0], 0));
     UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, s_heavy, cw, v.offset, v.list, v.big);
     UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, s_heavy, prm, d_ordered, d_groups, d_batches, bs, cw,
-                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters);
+                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters, tp);
     UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, s_unmapped, prm, d_ordered, d_groups, d_batches, d_tbl,
                    v.batch_unmapped, d_entry_flags, d_service);
     UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[1], s_heavy));
@@ -334,6 +338,51 @@ NV_STATUS uvmtier_service_fault_batches_device(uvmtier_ctx_t *ctx, uint32_t n_ba
         return st;
     return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
                         d_runs, run_cap, d_counters);
+}
+
+// The same pass with the thrashing heuristic's hint inside the fault loop (UVM/uvm_gpu_replayable_faults.c:1524-1545).
+NV_STATUS uvmtier_service_fault_batches_thrashing_device(uvmtier_ctx_t *ctx, uint32_t n_batches,
+                                                         const uvmtier_ordered_fault_t *d_ordered,
+                                                         const uvmtier_fault_group_t *d_groups, uvmtier_fault_batch_t *d_batches,
+                                                         const uvmtier_va_layout_t *lay, const uvmtier_block_state_t *state,
+                                                         uvmtier_thrashing_t *thrashing, const uint64_t *d_batch_time_ns,
+                                                         uint16_t *d_entry_flags, uvmtier_service_group_t *d_service,
+                                                         uvmtier_copy_run_t *d_runs, uint32_t run_cap, uint32_t *d_counters,
+                                                         uint32_t *d_thrashing_counters)
+{
+    const NV_STATUS ok = service_check_args(ctx, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                                            d_runs, run_cap, d_counters);
+    if (ok != NV_OK)
+        return ok;
+    if (!thrashing || !d_batch_time_ns || !d_thrashing_counters || !thrashing->d_blocks ||
+        (size_t)lay->n_spaces * lay->blocks_per_space != thrashing->n_slots || lay->gpu_id >= 32u)
+        return NV_ERR_INVALID_ARGUMENT;
+    if (!thrashing->d_page_throttle)
+        return NV_ERR_INVALID_STATE;                            // uvmtier_thrashing_enable_hints first
+    UVMTIER_CUDA(cudaSetDevice(ctx->device));
+    UVMTIER_CUDA(cudaMemsetAsync(d_thrashing_counters, 0, 8 * sizeof(uint32_t), ctx->stream));
+    if (!n_batches)
+        return NV_OK;
+    const uint32_t n_slots = lay->n_spaces * lay->blocks_per_space;
+    const size_t total = (size_t)n_batches * ctx->faults->gp.max_batch_size;
+    const NV_STATUS st = service_scratch_reserve(ctx, n_slots, n_batches, total);
+    if (st != NV_OK)
+        return st;
+    svc_thrash_params tp;
+    tp.th.blocks = thrashing->d_blocks;
+    tp.th.page_word = (unsigned long long *)thrashing->d_page_word;
+    tp.th.page_procs = thrashing->d_page_processors;
+    tp.th.thrashing_pages = thrashing->d_thrashing_pages;
+    tp.th.page_throttle = (unsigned long long *)thrashing->d_page_throttle;
+    tp.th.page_hint = thrashing->d_page_hint;
+    tp.th.page_throttled = thrashing->d_page_throttled;
+    tp.th.page_deadline = (unsigned long long *)thrashing->d_page_deadline;
+    tp.th.pinned_pages = thrashing->d_pinned_pages;
+    tp.cfg = thrashing->d_hint_config;
+    tp.batch_time = (const unsigned long long *)d_batch_time_ns;
+    tp.tally = d_thrashing_counters;
+    return service_pass(ctx, ctx->svc.d_base, n_batches, d_ordered, d_groups, d_batches, lay, state, d_entry_flags, d_service,
+                        d_runs, run_cap, d_counters, 0, true, false, &tp);
 }
 
 } // extern "C"

@@ -23,6 +23,7 @@
 #include "devio.cuh"
 #include "fault_decode.cuh"
 #include "prefetch.cuh"
+#include "thrashing_hint_dev.cuh"
 
 namespace uvmtier_k {
 
@@ -214,6 +215,16 @@ __device__ __forceinline__ svc_entry_eval svc_eval_entry(uint32_t acc, uint32_t 
     return r;
 }
 
+// Thrashing hints inside the fault loop (UVM/uvm_gpu_replayable_faults.c:1524-1545), for the va_blocks the detector tracks
+// page by page (uvmtier_service_fault_batches_thrashing_device; th.blocks == NULL: off).  batch_time[b]: NV_GETTIME() when
+// batch b is serviced.  tally: [3] throttles [4] pins on this GPU [5] pins elsewhere.
+struct svc_thrash_params {
+    thrash_hint_tables th;
+    const uvmtier_thrashing_hint_config_t *cfg;
+    const unsigned long long *batch_time;
+    uint32_t *tally;
+};
+
 // One warp per slot, for the slots the sorter put on the `heavy` list: runs with many entries.  The entries of a
 // run are filtered 32 at a time.  An entry depends on the one before it only when both fault on the same page
 // (a duplicate inherits "fatal" / "invalid prefetch"), so every lane evaluates its entry from its neighbour's last
@@ -225,7 +236,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                  block_state_ptrs st, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
                  const uint32_t *__restrict__ list, const uint32_t *__restrict__ heavy, uint16_t *__restrict__ entry_flags,
                  uvmtier_service_group_t *__restrict__ service, uvmtier_copy_run_t *__restrict__ runs,
-                 uint32_t *__restrict__ counters)
+                 uint32_t *__restrict__ counters, svc_thrash_params tp)
 {
     __shared__ uint32_t s_newres[kSvcThreads / 32][16];
     const int lane = threadIdx.x & 31, l = lane & 15, warp = threadIdx.x >> 5;
@@ -245,6 +256,14 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
         uint32_t pte0 = st.gpu_pte[0][w], pte1 = st.gpu_pte[1][w], pte2 = st.gpu_pte[2][w];
         const uint32_t logical = st.logical_prot[slot], pref = st.preferred_location[slot];
         uvmtier_prefetch_info_t pi = st.prefetch_info[slot];
+        // a va_block the thrashing detector tracks page by page: every fault that would be serviced asks for a hint first,
+        // one entry after the other (the hint advances the page's throttling / pinning state)
+        uvmtier_thrashing_block_t tblk;
+        tblk.tracked = 0;
+        if (tp.th.blocks)
+            tblk = tp.th.blocks[slot];
+        const bool tracked = tblk.tracked != 0;
+        uint32_t tally[3] = {0u, 0u, 0u};
 
         // Three runs in flight (as in k_service_blocks_grp): run k+1's first 32 entries, run k+2's group and run
         // k+3's id are loaded while run k is worked on -- a hot va_block is one long chain of dependent steps.
@@ -269,7 +288,7 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
         // regular path below.  A hot va_block is otherwise one chain of thousands of dependent steps.
         bool streak = false;
         for (uint32_t k = 0; k < cnt;) {
-            if (short_runs && streak && cnt - k >= 2) {
+            if (short_runs && streak && cnt - k >= 2 && !tracked) {
                 const uint32_t m = min(32u, cnt - k);
                 const bool mine = (uint32_t)lane < m;
                 uint32_t ts = 0;
@@ -336,6 +355,59 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 s_newres[warp][lane] = 0;
             __syncwarp();
             uint32_t page_faults = 0, dup_sum = 0, ip_sum = 0, carry_page = 0xffffffffu, carry_state = 0;
+            if (tracked) {
+                // with hints: one entry at a time, the same entry on every lane
+                uint32_t state = 0, prev_page = 0xffffffffu;
+                for (uint32_t i = 0; i < n; i++) {
+                    const uint4 e = oraw[base + first + i];
+                    const uint32_t acc = (e.w >> 24) & 7u, num_instances = e.w & 0xffffu, access_type_mask = (e.w >> 16) & 0xffu;
+                    const uint32_t page = (e.x - g0.x) >> 12;
+                    const bool dup = i > 0 && page == prev_page;
+                    const int wl = (int)((page >> 5) & 15u);
+                    const uint32_t sh = page & 31u;
+                    const uint32_t w0 = __shfl_sync(HW_FULL, pte0, wl), w1 = __shfl_sync(HW_FULL, pte1, wl), w2 = __shfl_sync(HW_FULL, pte2, wl);
+                    const uint32_t auth = prm.non_replayable ? 0u : ((w0 >> sh) & 1u) | (((w1 >> sh) & 1u) << 1) | (((w2 >> sh) & 1u) << 2);
+                    const svc_entry_eval ev = svc_eval_entry(acc, num_instances, access_type_mask, dup, state, logical, auth);
+                    uint32_t fl = ev.flags;
+                    bool serviced = ev.serviced;
+                    if (serviced) {                                       // :1524-1545
+                        const uint32_t on_gpu = (__shfl_sync(HW_FULL, gres, wl) >> sh) & 1u;
+                        const uint32_t on_cpu = (__shfl_sync(HW_FULL, c0 | c1, wl) >> sh) & 1u;
+                        uint32_t packed = 0;
+                        if (lane == 0) {
+                            uvmtier_thrashing_query_t q;
+                            q.time_stamp = tp.batch_time[b + prm.batch_base];
+                            q.slot = slot; q.page = (uint16_t)page; q.requester = (uint8_t)prm.gpu_id; q.reserved = 0;
+                            q.resident_processors = (on_gpu ? 1u << prm.gpu_id : 0u) | on_cpu;
+                            q.preferred_location = pref == UVMTIER_ID_INVALID ? (uint16_t)0xffffu : (uint16_t)pref;
+                            q.reserved2 = 0;
+                            const uvmtier_thrashing_hint_t h = hint_get(*tp.cfg, tp.th, q, tblk, tally);
+                            packed = (uint32_t)h.type | ((uint32_t)h.pin_residency << 8);
+                        }
+                        packed = __shfl_sync(HW_FULL, packed, 0);
+                        const uint32_t type = packed & 0xffu, where = packed >> 8;
+                        if (type == UVMTIER_THRASHING_HINT_THROTTLE || (type == UVMTIER_THRASHING_HINT_PIN && where != prm.gpu_id)) {
+                            // mark_fault_throttled (:1537) / a pin this pass does not carry out: not serviced
+                            fl = (fl & ~(UVMTIER_SF_SERVICED | (7u << UVMTIER_SF_ACCESS_SHIFT))) |
+                                 (type == UVMTIER_THRASHING_HINT_THROTTLE ? UVMTIER_SF_THROTTLED : UVMTIER_SF_PIN_REMOTE);
+                            serviced = false;
+                        }
+                        else if (type == UVMTIER_THRASHING_HINT_PIN)
+                            fl |= UVMTIER_SF_PINNED;                      // thrashing_pin_mask (:1541-1545)
+                    }
+                    if (lane == 0) {
+                        entry_flags[base + first + i] = (uint16_t)(fl & flag_mask);
+                        if (serviced)
+                            s_newres[warp][page >> 5] |= 1u << sh;
+                    }
+                    dup_sum += dup ? num_instances : num_instances - 1u;
+                    ip_sum += ev.ip_add;
+                    page_faults += serviced ? 1u : 0u;
+                    state = ev.state;
+                    prev_page = page;
+                }
+            }
+            else
             for (uint32_t c = 0; c < n; c += 32) {
                 const uint32_t i = c + lane;
                 const bool valid = i < n;
@@ -397,7 +469,9 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                     const uint32_t flags = UVMTIER_PF_HAS_RESIDENT_MASK | UVMTIER_PF_GPU_VA_SPACE_REGISTERED |
                                            (block_empty ? UVMTIER_PF_BLOCK_RESIDENT_EMPTY : 0u);
                     const uint64_t block_start = ((uint64_t)g0.y << 32) | g0.x;
-                    pf = pf_get_hint_block(newres, gres, 0u, 0u, false, block_start, 512, rf, ro, prm.gpu_id, pref, flags,
+                    // thrashing pages seed no prefetch region and are not prefetched (uvm_perf_prefetch.c:378-381, 407)
+                    const uint32_t thr_w = tracked ? *((volatile const uint32_t *)&tp.th.thrashing_pages[w]) : 0u;
+                    pf = pf_get_hint_block(newres, gres, thr_w, 0u, tracked, block_start, 512, rf, ro, prm.gpu_id, pref, flags,
                                            16u, prm.pf_threshold, prm.pf_min_faults, &pi, &hint, lane);
                 }
                 if (hint != UVMTIER_ID_INVALID) {                         // uvm_va_block_get_prefetch_hint :11856-11876
@@ -483,6 +557,12 @@ k_service_blocks(service_kparams prm, const uvmtier_ordered_fault_t *__restrict_
                 st.read_duplicated[w] &= c0 | c1;
             if (l == 0)
                 st.prefetch_info[slot] = pi;
+        }
+        if (tracked && lane == 0) {
+            tp.th.blocks[slot] = tblk;
+            if (tally[0]) atomicAdd(&tp.tally[3], tally[0]);
+            if (tally[1]) atomicAdd(&tp.tally[4], tally[1]);
+            if (tally[2]) atomicAdd(&tp.tally[5], tally[2]);
         }
     }
 }

@@ -65,7 +65,8 @@ k_service_count(service_kparams prm, const uvmtier_fault_group_t *__restrict__ g
 constexpr uint32_t kLightBins = 256;
 __global__ void __launch_bounds__(256)
 k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t heavy_min, uint32_t *__restrict__ offset,
-                uint32_t *__restrict__ cursor, uint32_t *__restrict__ hist, uint32_t *__restrict__ light_rank)
+                uint32_t *__restrict__ cursor, uint32_t *__restrict__ hist, uint32_t *__restrict__ light_rank,
+                const uvmtier_thrashing_block_t *__restrict__ thr_blocks = NULL)
 {
     __shared__ uint32_t s_hist[kLightBins], s_cta_base[kLightBins];
     const uint32_t slot = blockIdx.x * blockDim.x + threadIdx.x;
@@ -76,7 +77,8 @@ k_service_alloc(uint32_t n_slots, const uint2 *__restrict__ cw, uint32_t heavy_m
     __syncthreads();
     // the slot's rank inside its bin = this CTA's share of the bin (one global atomic per CTA and bin: thousands of
     // slots share a few dozen bins, per-slot global atomics on them serialise) + the slot's rank inside the CTA
-    const bool is_light = c && cwv.y < heavy_min;
+    // va_blocks the thrashing detector tracks page by page take the warp-per-block kernel, which asks for hints
+    const bool is_light = c && cwv.y < heavy_min && !(thr_blocks && thr_blocks[slot].tracked);
     const uint32_t bin = kLightBins - 1u - min(c, kLightBins - 1u);
     uint32_t rank = 0;
     if (is_light)
@@ -137,7 +139,8 @@ static_assert(kLightBins == (uint32_t)kSortThreads, "one thread per bin in the h
 __global__ void __launch_bounds__(kSortThreads)
 k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint32_t *__restrict__ offset,
                      uint32_t *__restrict__ list, uint32_t heavy_min, uint32_t *__restrict__ big, uint32_t *__restrict__ heavy,
-                     const uint32_t *__restrict__ hist, const uint32_t *__restrict__ light_rank, uint32_t *__restrict__ light)
+                     const uint32_t *__restrict__ hist, const uint32_t *__restrict__ light_rank, uint32_t *__restrict__ light,
+                     const uvmtier_thrashing_block_t *__restrict__ thr_blocks = NULL)
 {
     __shared__ uint32_t s_all[(kSortThreads / 32) * kSortWarpKeys];
     __shared__ uint32_t s_base[kLightBins], s_part[kSortThreads / 32];
@@ -180,7 +183,7 @@ k_service_sort_lists(uint32_t n_slots, const uint2 *__restrict__ cw, const uint3
         if (!cnt)
             continue;
         if (lane == 0) {
-            if (this_c.y >= heavy_min) {
+            if (this_c.y >= heavy_min || (thr_blocks && thr_blocks[this_slot].tracked)) {
                 pend_at = &heavy[1u + atomicAdd(&heavy[0], 1u)];
             }
             else {

@@ -295,6 +295,42 @@ class Context:
             for p in (d_ord, d_grp, d_bat, d_flags, d_svc, d_runs, d_cnt):
                 self.free(p)
 
+    def service_fault_batches_thrashing(self, k1, layout, dstate, thrashing, batch_time_ns, run_cap=1 << 20):
+        """uvmtier_service_fault_batches_thrashing_device: service_fault_batches with the thrashing hint inside the fault loop.
+        thrashing: a ThrashingState with hints enabled; batch_time_ns: uint64 per batch.  Adds the eight thrashing counters."""
+        from .blockstate import COPY_RUN_DT, SERVICE_GROUP_DT
+        from .layouts import BATCH_DT
+        nb = len(k1["batch"])
+        total = len(k1["ordered"])
+        d_ord = self.to_device(k1["ordered"]); d_grp = self.to_device(k1["groups"]); d_bat = self.to_device(k1["batch"])
+        d_time = self.to_device(np.ascontiguousarray(batch_time_ns, "<u8"))
+        d_flags = self.alloc(total * 2); d_svc = self.alloc(total * 96); d_runs = self.alloc(max(run_cap, 1) * 8)
+        d_cnt = self.alloc(8); d_tcnt = self.alloc(32)
+        try:
+            _check(lib().uvmtier_memset_device(self._h, ctypes.c_void_p(d_svc), 0, ctypes.c_size_t(total * 96)), "memset")
+            _check(lib().uvmtier_service_fault_batches_thrashing_device(
+                self._h, ctypes.c_uint32(nb), P(d_ord), P(d_grp), P(d_bat), P(layout), ctypes.byref(dstate.ptrs), ctypes.byref(thrashing),
+                P(d_time), P(d_flags), P(d_svc), P(d_runs), ctypes.c_uint32(run_cap), P(d_cnt), P(d_tcnt)),
+                "uvmtier_service_fault_batches_thrashing_device")
+            self.synchronize()
+            cnt = self.from_device(d_cnt, 2, "<u4")
+            return dict(flags=self.from_device(d_flags, total, "<u2"), service=self.from_device(d_svc, total, SERVICE_GROUP_DT),
+                        runs=self.from_device(d_runs, max(run_cap, 1), COPY_RUN_DT), n_runs=int(cnt[0]),
+                        batch=self.from_device(d_bat, nb, BATCH_DT), state=dstate.download(),
+                        thrashing_counters=self.from_device(d_tcnt, 8, "<u4"))
+        finally:
+            for p in (d_ord, d_grp, d_bat, d_time, d_flags, d_svc, d_runs, d_cnt, d_tcnt):
+                self.free(p)
+
+    def thrashing_upload(self, t, tables):
+        """Copies host tables (a dict with the names thrashing_tables returns; blocks as 32-byte rows) into a ThrashingState."""
+        for name, dptr in (("blocks", t.d_blocks), ("page_word", t.d_page_word), ("page_procs", t.d_page_processors),
+                           ("thrashing_pages", t.d_thrashing_pages), ("page_throttle", t.d_page_throttle), ("page_hint", t.d_page_hint),
+                           ("page_throttled", t.d_page_throttled), ("page_deadline", t.d_page_deadline), ("pinned_pages", t.d_pinned_pages)):
+            if name in tables and dptr:
+                a = np.ascontiguousarray(tables[name])
+                _check(lib().uvmtier_memcpy_h2d(self._h, ctypes.c_void_p(dptr), P(a), ctypes.c_size_t(a.nbytes)), "h2d")
+
     def service_replayable_faults_streamed(self, ring, get, put, layout, dstate, run_cap=1 << 20, chunk_batches=0,
                                            clear_valid=True, repeat=1, before_each=None):
         """uvmtier_service_replayable_faults_streamed on a copy of `ring` in pinned host memory: fetch -> preprocess ->

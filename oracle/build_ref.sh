@@ -72,7 +72,7 @@ if [ -f "$HERE/ref_service_glue.c" ]; then
     sed -n '181,188p;522,537p' "$UVM/uvm_hal_types.h" > "$TMP/x_prot.h"
     sed -n '46,62p' "$UVM/uvm_tools.h" > "$TMP/x_tools_reason.h"
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_service_glue.c" "$HERE/ref_faults_blackwell.c" \
-        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_thrashing.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
         -o "$OUT/libref_service.so"
     echo "build_ref: built $OUT/libref_service.so"
 fi
@@ -83,7 +83,7 @@ if [ -f "$HERE/ref_nonreplayable_glue.c" ]; then
     if [ "$got" != "588e72e5e3163f2e" ]; then echo "build_ref: uvm_gpu_non_replayable_faults.c sha256 prefix $got != pinned 588e72e5e3163f2e" >&2; exit 1; fi
     sed -n '345,445p' "$UVM/uvm_gpu_non_replayable_faults.c" > "$TMP/x_nonreplayable.h"
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_nonreplayable_glue.c" "$HERE/ref_faults_blackwell.c" \
-        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_thrashing.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
         -o "$OUT/libref_nonreplayable.so"
     echo "build_ref: built $OUT/libref_nonreplayable.so"
 fi
@@ -96,7 +96,7 @@ if [ -f "$HERE/ref_resident_glue.c" ]; then
     sed -n '183,195p;584,593p;609,701p;721,734p;2406,2430p;3569,3577p;4379,4452p;4460,4536p;4538,4579p;4581,4619p;4625,4653p;4660,4847p;4877,4976p;4978,5114p;5120,5162p;5164,5332p' \
         "$UVM/uvm_va_block.c" > "$TMP/x_resident.h"
     sed -n '3099,3182p' "$UVM/uvm_va_block.c" > "$TMP/x_populate.h"
-    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+    gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_resident_glue.c" "$HERE/oracle_service.c" "$HERE/oracle_thrashing.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
         -o "$OUT/libref_resident.so"
     echo "build_ref: built $OUT/libref_resident.so"
 fi
@@ -135,7 +135,7 @@ if [ -f "$HERE/ref_access_counters_glue.c" ]; then
     pin uvm_gpu_access_counters.c 67b82fdfd551a698
     sed -n '198,218p;1079,1251p;1253,1260p;1287,1354p' "$UVM/uvm_gpu_access_counters.c" > "$TMP/x_access_counters.h"
     gcc $CFLAGS -I"$TMP" -I"$HERE" -I"$INC" -I"$UVM" "$HERE/ref_access_counters_glue.c" "$HERE/ref_faults_blackwell.c" \
-        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
+        "$HERE/ref_faults_hopper.c" "$HERE/oracle_service.c" "$HERE/oracle_thrashing.c" "$HERE/oracle_resident.c" "$HERE/oracle_prefetch.c" \
         -o "$OUT/libref_access_counters.so"
     echo "build_ref: built $OUT/libref_access_counters.so"
 fi

@@ -27,6 +27,7 @@
  * Batches are applied in trace order, exactly like uvm_parent_gpu_service_replayable_faults (:2906-2960).
  */
 #include "oracle_common.h"
+#include "oracle_thrashing.h"
 #include "ref_api.h"
 
 enum { ACC_PREFETCH = 0, ACC_READ, ACC_WRITE, ACC_ATOMIC_WEAK, ACC_ATOMIC_STRONG, ACC_COUNT };
@@ -69,6 +70,22 @@ void oracle_service_set_back_half(void *prefetch_hint, void *ref_make_resident)
 {
     g_prefetch_hint = prefetch_hint ? (prefetch_hint_fn)prefetch_hint : oracle_prefetch_get_hint_va_block;
     g_ref_make_resident = (ref_make_resident_fn)ref_make_resident;
+}
+
+/* Thrashing hints inside the fault loop (uvm_gpu_replayable_faults.c:1524-1545): off by default (the harness policy of the
+ * bench: "no thrashing"); oracle_service_set_thrashing() attaches the thrashing restatement's tables and one time stamp
+ * per batch (NV_GETTIME() when the batch is serviced).  A fault that reaches the hint:
+ *   THROTTLE -> mark_fault_throttled (:1537): flagged, not serviced
+ *   PIN      -> the page joins thrashing_pin_mask; uvm_va_block_select_residency takes the pin's residency
+ *               (uvm_va_block.c:11624-11628).  On this GPU: serviced as ever.  Elsewhere: flagged and left to the caller --
+ *               the servicing pass moves pages to the faulting GPU only (stated in include/uvmtier.h).
+ * and the prefetcher leaves the va_block's thrashing pages alone (uvm_perf_prefetch.c:378-381, 407). */
+static const thrash_cfg_t *g_th_cfg;
+static const thrash_tables_t *g_th;
+static const uint64_t *g_batch_time;
+void oracle_service_set_thrashing(const thrash_cfg_t *cfg, const thrash_tables_t *th, const uint64_t *batch_time_ns)
+{
+    g_th_cfg = cfg; g_th = cfg ? th : NULL; g_batch_time = batch_time_ns;
 }
 
 static void mask_ptr_load(or_mask_t *m, uint64_t *base, uint32_t slot) { or_load(m, base + 8 * (size_t)slot); }
@@ -125,8 +142,9 @@ void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_block_stat
     mask_ptr_load(&cpu1, st->cpu_resident[1], slot);
     or_or(&any_cpu, &cpu0, &cpu1);
     pb.flags = REF_PF_HAS_RESIDENT_MASK | REF_PF_GPU_VA_SPACE_REGISTERED |
-               ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0);
-    g_prefetch_hint(1, &pb, gpu_res.w, newres.w, NULL, NULL, &st->prefetch_info[slot], pf_mask.w, &hint);
+               ((or_empty(&gpu_res) && or_empty(&any_cpu)) ? REF_PF_BLOCK_RESIDENT_EMPTY : 0) | (g_th ? REF_PF_HAS_THRASHING : 0);
+    g_prefetch_hint(1, &pb, gpu_res.w, newres.w, g_th ? (const uint64_t *)(g_th->thrashing_pages + (size_t)slot * 16) : NULL, NULL,
+                    &st->prefetch_info[slot], pf_mask.w, &hint);
     rec->hint_residency = (uint16_t)hint;
     if (hint != 257) {
         or_or(&newres, &newres, &pf_mask);
@@ -314,7 +332,30 @@ uint32_t oracle_service_fault_batches(uint32_t n_batches, uint32_t max_batch_siz
                     fl |= REF_SF_AUTHORIZED;
                     goto next;
                 }
-                /* new residency = the faulting GPU (harness policy); :1560-1579 */
+                if (g_th) {                                                                  /* :1524-1545 */
+                    thrash_query_t q;
+                    thrash_hint_t h;
+                    or_mask_t c0, c1;
+                    mask_ptr_load(&c0, st->cpu_resident[0], slot);
+                    mask_ptr_load(&c1, st->cpu_resident[1], slot);
+                    memset(&q, 0, sizeof(q));
+                    q.time_stamp = g_batch_time[b]; q.slot = slot; q.page = (uint16_t)page; q.requester = (uint8_t)lay->gpu_id;
+                    q.resident_processors = (or_test(&gpu_res, page) ? 1u << lay->gpu_id : 0u) | ((or_test(&c0, page) || or_test(&c1, page)) ? 1u : 0u);
+                    q.preferred_location = st->preferred_location[slot] == 257 ? 0xFFFF : st->preferred_location[slot];
+                    oracle_thrashing_get_hints(1, &q, g_th_cfg, g_th, &h);
+                    if (h.type == 2) {
+                        fl |= REF_SF_THROTTLED;
+                        goto next;
+                    }
+                    if (h.type == 1) {
+                        if (h.pin_residency != lay->gpu_id) {
+                            fl |= REF_SF_PIN_REMOTE;
+                            goto next;
+                        }
+                        fl |= REF_SF_PINNED;
+                    }
+                }
+                /* new residency = the faulting GPU (harness policy, or the pin); :1560-1579 */
                 or_set(&newres, page);
                 page_faults++;
                 fl |= REF_SF_SERVICED | (service_acc << REF_SF_ACCESS_SHIFT);

@@ -172,6 +172,9 @@ typedef struct {
 #define REF_SF_FATAL            0x0004
 #define REF_SF_INVALID_PREFETCH 0x0008
 #define REF_SF_AUTHORIZED       0x0010
+#define REF_SF_THROTTLED        0x2000   /* thrashing hint THROTTLE: mark_fault_throttled, not serviced */
+#define REF_SF_PINNED           0x4000   /* thrashing hint PIN on the faulting GPU: in thrashing_pin_mask, serviced */
+#define REF_SF_PIN_REMOTE       0x8000   /* thrashing hint PIN elsewhere: left to the caller */
 #define REF_SF_ACCESS_SHIFT     5       /* 3 bits: service access type */
 #define REF_SF_REASON_SHIFT     8       /* 3 bits: UvmEventFatalReason */
 #define REF_SF_CANCEL_SHIFT     12      /* 1 bit: uvm_fault_cancel_va_mode_t */

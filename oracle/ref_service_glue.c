@@ -12,8 +12,10 @@
  *   uvm_va_block_check_logical_permissions   -> prot_of(access) <= logical_prot[slot]  (uvm_va_block.c:12361-12416
  *                                               with uvm_enable_builtin_tests, as in the reference's own test runs)
  *   uvm_va_block_page_is_gpu_authorized      -> the slot's gpu_pte bits                 (uvm_va_block.c:2576-2615)
- *   uvm_perf_thrashing_get_hint              -> NONE                                    (harness policy)
- *   uvm_va_block_select_residency            -> the faulting GPU                        (harness policy)
+ *   uvm_perf_thrashing_get_hint              -> NONE (harness policy), or -- ref_service_set_thrashing() -- the thrashing
+ *                                               restatement's hint for (va_block, page, this GPU, the batch's time stamp)
+ *   uvm_va_block_select_residency            -> the pin's residency for a PIN hint (uvm_va_block.c:11624-11628), else the
+ *                                               faulting GPU                          (harness policy)
  *   uvm_va_block_service_locked              -> oracle_service_block_apply(): the CPU restatement of the prefetch
  *                                               hint + make_resident + mapping back half (oracle_service.c)
  * The batch-level driver below restates service_fault_batch (:2232-2377) / _dispatch (:1946-2035) on the flat
@@ -58,7 +60,7 @@ static inline NvU64 uvm_va_block_cpu_page_address(uvm_va_block_t *b, uvm_page_in
 
 typedef enum { UVM_PERF_THRASHING_HINT_TYPE_NONE = 0, UVM_PERF_THRASHING_HINT_TYPE_PIN = 1,
                UVM_PERF_THRASHING_HINT_TYPE_THROTTLE = 2 } uvm_perf_thrashing_hint_type_t;     /* uvm_perf_thrashing.h:33-50 */
-typedef struct { uvm_perf_thrashing_hint_type_t type; } uvm_perf_thrashing_hint_t;
+typedef struct { uvm_perf_thrashing_hint_type_t type; struct { uvm_processor_id_t residency; } pin; } uvm_perf_thrashing_hint_t;
 typedef enum { UVM_SERVICE_OPERATION_REPLAYABLE_FAULTS, UVM_SERVICE_OPERATION_NON_REPLAYABLE_FAULTS,
                UVM_SERVICE_OPERATION_ACCESS_COUNTERS } uvm_service_operation_t;                /* uvm_va_block_types.h:343-348 */
 typedef struct { NvU64 start, end; bool migratable; } uvm_range_group_range_iter_t;
@@ -108,13 +110,48 @@ static bool uvm_va_block_page_is_gpu_authorized(uvm_va_block_t *b, uvm_page_inde
     (void)id;
     return (g_state->gpu_pte[prot - UVM_PROT_READ_ONLY][8 * (size_t)b->slot + page / 64] >> (page % 64)) & 1;
 }
+/* thrashing hints: off unless ref_service_set_thrashing() attached the restatement's tables (oracle_thrashing.c, itself held
+ * against the reference's uvm_perf_thrashing_get_hint by libref_thrashing_hint.so) */
+#include "oracle_thrashing.h"
+extern void oracle_service_set_thrashing(const thrash_cfg_t *cfg, const thrash_tables_t *th, const uint64_t *batch_time_ns);
+static const thrash_cfg_t *g_thr_cfg;
+static const thrash_tables_t *g_thr;
+static const uint64_t *g_thr_time;
+static uint32_t g_cur_batch;
+void ref_service_set_thrashing(const thrash_cfg_t *cfg, const thrash_tables_t *th, const uint64_t *batch_time_ns)
+{
+    g_thr_cfg = cfg; g_thr = cfg ? th : NULL; g_thr_time = batch_time_ns;
+    oracle_service_set_thrashing(cfg, th, batch_time_ns);     /* the back half's prefetch call reads the thrashing pages */
+}
 static uvm_perf_thrashing_hint_t uvm_perf_thrashing_get_hint(uvm_va_block_t *b, uvm_va_block_context_t *c, NvU64 addr, uvm_processor_id_t id)
-{ uvm_perf_thrashing_hint_t h = { UVM_PERF_THRASHING_HINT_TYPE_NONE }; (void)b; (void)c; (void)addr; (void)id; return h; }
+{
+    uvm_perf_thrashing_hint_t h = { UVM_PERF_THRASHING_HINT_TYPE_NONE, { { 257 } } };
+    (void)c;
+    if (g_thr) {
+        const unsigned page = (unsigned)((addr - b->start) / PAGE_SIZE);
+        const size_t w = 8 * (size_t)b->slot + page / 64;
+        thrash_query_t q;
+        thrash_hint_t out;
+        memset(&q, 0, sizeof(q));
+        q.time_stamp = g_thr_time[g_cur_batch]; q.slot = b->slot; q.page = (uint16_t)page; q.requester = (uint8_t)id.val;
+        q.resident_processors = (((g_state->gpu_resident[w] >> (page % 64)) & 1) ? 1u << id.val : 0u) |
+                                ((((g_state->cpu_resident[0][w] | g_state->cpu_resident[1][w]) >> (page % 64)) & 1) ? 1u : 0u);
+        q.preferred_location = g_state->preferred_location[b->slot] == 257 ? 0xFFFF : g_state->preferred_location[b->slot];
+        oracle_thrashing_get_hints(1, &q, g_thr_cfg, g_thr, &out);
+        h.type = (uvm_perf_thrashing_hint_type_t)out.type;
+        h.pin.residency.val = out.pin_residency;
+    }
+    return h;
+}
 static uvm_processor_id_t uvm_va_block_select_residency(uvm_va_block_t *b, uvm_va_block_context_t *c, uvm_page_index_t page,
                                                         uvm_processor_id_t id, NvU32 access_type_mask, const uvm_va_policy_t *policy,
                                                         const uvm_perf_thrashing_hint_t *hint, uvm_service_operation_t op,
                                                         const bool hmm_migratable, bool *read_duplicate)
-{ (void)b; (void)c; (void)page; (void)access_type_mask; (void)policy; (void)hint; (void)op; (void)hmm_migratable; *read_duplicate = false; return id; }
+{
+    (void)b; (void)c; (void)page; (void)access_type_mask; (void)policy; (void)op; (void)hmm_migratable;
+    *read_duplicate = false;
+    return hint->type == UVM_PERF_THRASHING_HINT_TYPE_PIN ? hint->pin.residency : id;
+}
 static NV_STATUS uvm_va_block_set_cancel(uvm_va_block_t *b, uvm_va_block_context_t *c, uvm_gpu_t *g) { (void)b; (void)c; (void)g; return NV_OK; }
 
 /* back half: CPU restatement (oracle_service.c), called with what the verbatim loop built */
@@ -122,6 +159,7 @@ extern void oracle_service_block_apply(const ref_va_layout_t *lay, const ref_blo
                                        const uint64_t *new_residency, unsigned region_first, unsigned region_outer,
                                        ref_service_group_t *rec, ref_copy_run_t *runs, uint32_t *nrun, uint32_t run_cap);
 static ref_service_group_t *g_rec;
+static uint16_t *g_pin_flags;
 static ref_copy_run_t *g_runs;
 static uint32_t *g_nrun, g_run_cap;
 static NV_STATUS uvm_va_block_service_locked(uvm_processor_id_t id, uvm_va_block_t *b, uvm_va_block_retry_t *r,
@@ -157,6 +195,7 @@ uint32_t ref_service_fault_batches(uint32_t n_batches, uint32_t max_batch_size, 
     (void)groups;
 
     oracle_prefetch_init(pf_enable, pf_threshold, pf_min_faults);
+    g_pin_flags = calloc((size_t)n_batches * max_batch_size + 1, sizeof(uint16_t));
     memset(&parent, 0, sizeof(parent));
     gpu.id.val = lay->gpu_id;
     gpu.parent = &parent;
@@ -218,7 +257,27 @@ uint32_t ref_service_fault_batches(uint32_t n_batches, uint32_t max_batch_size, 
                 rec->slot = blk.slot;
                 g_rec = rec;
                 g_block_service_context.num_retries = 0;
+                g_block_service_context.thrashing_pin_count = 0;
+                g_cur_batch = b;
                 service_fault_batch_block_locked(&gpu, &blk, NULL, &bc, k, true, &block_faults);
+                if (g_thr && g_block_service_context.thrashing_pin_count) {
+                    /* thrashing_pin_mask (:1541-1545), per entry for the harness: the first entry of each pinned page */
+                    uvm_page_mask_t seen;
+                    NvU32 j;
+                    uvm_page_mask_zero(&seen);
+                    for (j = 0; j < block_faults; j++) {
+                        const uvm_fault_buffer_entry_t *pe = bc.ordered_fault_cache[k + j];
+                        const uvm_page_index_t page = (uvm_page_index_t)((pe->fault_address - block_start) / PAGE_SIZE);
+                        if (pe->is_throttled || !uvm_page_mask_test(&g_block_service_context.thrashing_pin_mask, page) ||
+                            uvm_page_mask_test(&seen, page))
+                            continue;
+                        uvm_page_mask_set(&seen, page);
+                        g_pin_flags[base + (size_t)(pe - bc.fault_cache)] =
+                            uvm_page_mask_test(&g_block_service_context.per_processor_masks[gpu.id.val].new_residency, page) &&
+                            test_bit(gpu.id.val, g_block_service_context.resident_processors.bitmap)
+                                ? REF_SF_PINNED : REF_SF_PIN_REMOTE;
+                    }
+                }
             }
             else {
                 /* no va_range covers the address: one entry at a time (:2022-2031), the run = the group K1 formed */
@@ -239,13 +298,17 @@ uint32_t ref_service_fault_batches(uint32_t n_batches, uint32_t max_batch_size, 
                 fl |= REF_SF_FATAL | (uint16_t)(e->fatal_reason << 8) | (uint16_t)(e->replayable.cancel_va_mode << 12);
             if (e->is_invalid_prefetch)
                 fl |= REF_SF_INVALID_PREFETCH;
-            entry_flags[base + k] = fl;
+            if (e->is_throttled)
+                fl |= REF_SF_THROTTLED;
+            entry_flags[base + k] = fl | g_pin_flags[base + k];
         }
         batch[b].num_duplicate_faults = bc.num_duplicate_faults;
         batch[b].num_invalid_prefetch_faults = bc.num_invalid_prefetch_faults;
     }
     free(bc.fault_cache);
     free(bc.ordered_fault_cache);
+    free(g_pin_flags);
+    g_pin_flags = NULL;
     if (n_runs)
         *n_runs = nrun;
     return nsvc;

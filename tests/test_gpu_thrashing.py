@@ -140,3 +140,31 @@ def test_gpu_hints_match_restatement_on_random_batches_and_many_blocks():
     TH.assert_hint_state_equal(want, got, "batches")
     types = np.concatenate([h["type"] for h in want_h])
     assert (types == TH.HINT_THROTTLE).sum() > 50 and (types == TH.HINT_PIN).sum() > 50
+
+
+@pytest.mark.parametrize("seed,topology,kw", [(1, "pcie", {}), (2, "c2c", {}), (3, "pcie", dict(pin_threshold=1, pin=2))])
+def test_gpu_service_with_hints_matches_restatement(seed, topology, kw):
+    """uvmtier_service_fault_batches_thrashing_device: throttled / pinned / pinned-elsewhere entries, records, copy runs, block
+    state and the hint tables against the restated loop (which tests/test_oracle_thrashing_service.py holds against the
+    reference's loop compiled verbatim)."""
+    import faultlib as F
+    import thrashsvclib as TS
+    import uvmtier
+    orc = T.load_oracle()
+    sc = TS.scenario(seed, topology, n_faults=6000, blocks=48, **kw)
+    with uvmtier.Context(0) as ctx:
+        ctx.fault_buffer_init(sc["gp"], sc["tbl"])
+        n = len(sc["pk"])
+        ring = np.zeros((n + 1, 8), np.uint32)
+        ring[:n] = sc["pk"]
+        r = ctx.fetch_preprocess_fault_batches(ring, 0, n)
+        B = sc["B"]
+        pad = len(r["batch"]) * B - n
+        r["ordered"] = np.concatenate([r["ordered"], np.zeros(pad, r["ordered"].dtype)])
+        r["groups"] = np.concatenate([r["groups"], np.zeros(pad, r["groups"].dtype)])
+        k1 = dict(ordered_rec=r["ordered"], groups=r["groups"], batch=r["batch"])
+        want = TS.run_oracle(orc, sc, k1)
+        got = TS.run_gpu(ctx, sc, r)
+    throttled, pinned, remote = TS.check(want, got, B, "seed %d %s" % (seed, topology))
+    assert np.array_equal(want["thrash"].counters[3:6], got["thrash"].counters[3:6])
+    assert throttled + pinned + remote > 10, (throttled, pinned, remote)

@@ -194,7 +194,7 @@ typedef struct {
 
 /* The uvm_parent_gpu_t fields the fault path reads. */
 typedef struct {
-    uint32_t max_batch_size;         /* fault_buffer.max_batch_size = uvm_perf_fault_batch_count, 1..1024 */
+    uint32_t max_batch_size;         /* fault_buffer.max_batch_size = uvm_perf_fault_batch_count, 1..16384 */
     uint32_t utlb_per_gpc_count;     /* Blackwell: 2 * maxTpcPerGpcCount + 1 (UVM/uvm_blackwell_fault_buffer.h:85-90) */
     uint32_t gpc_count;              /* rm_info.maxGpcCount; utlb_count = gpc_count * utlb_per_gpc_count */
     uint32_t va_bits;                /* canonical-address width (UVM/uvm_gpu.c:428-459): 57 on Hopper+ */
@@ -247,8 +247,14 @@ typedef struct {
 /* Configures the context's replayable-fault state: the parent-GPU parameters and the instance-pointer
  * table (copied to the device).  Mirrors fault_buffer_init_replayable_faults
  * (UVM/uvm_gpu_replayable_faults.c:139-213): allocate-once, reused by every batch.
- * NV_ERR_INVALID_ARGUMENT for max_batch_size outside 1..1024, va_bits outside 40..57, n_rows > 256 or
- * sort ranks that do not fit the packed sort key (rank < 256 for batches <= 256, < 64 above). */
+ * NV_ERR_INVALID_ARGUMENT for max_batch_size outside 1..16384, va_bits outside 40..57, n_rows > 256 or
+ * sort ranks that do not fit the packed sort key (64 bits = rank | 45 page bits | 3 access-type bits | index bits with
+ * 2^index_bits >= max_batch_size: rank < 256 for batches <= 256, < 64 up to 1024, < 16 up to 4096, < 4 up to 16384).
+ * The reference clamps uvm_perf_fault_batch_count to the size of the hardware fault buffer (:153-165), not to a CTA:
+ * up to 1024 entries a batch is one CTA with one thread per entry; above that, one CTA of 1024 threads walks the batch
+ * in strides with its per-entry arrays in a working buffer the library keeps (59 bytes per entry), and the fetch-time
+ * coalescing is the reference's sequential scan done by one thread per batch -- slower per entry (there are few such
+ * batches to run side by side), same results.  The access-counter path takes max_batch_size <= 1024 only. */
 NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_params_t *gpu_params,
                                     const uvmtier_instance_ptr_entry_t *h_table, size_t n_rows);
 

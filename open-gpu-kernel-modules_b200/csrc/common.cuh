@@ -24,6 +24,11 @@ struct uvmtier_fault_state {
     uint32_t ac_granularity_2m, ac_cpu_chunk_2m;   // access-counter configuration (uvmtier_access_counters_init)
     uint32_t generation;   // bumped by every uvmtier_fault_buffer_init (the table's contents may have changed)
     uint16_t *d_utlb_pending;   // optional output, uvmtier_fault_buffer_set_utlb_pending_output
+    // batches of more than 1024 entries (k_fault_fetch_preprocess_big): entries per batch rounded up to a power of two
+    // (0 = the one-thread-per-entry kernel is used) and the kernel's working space
+    uint32_t big_T;
+    unsigned char *d_big;
+    size_t big_bytes;
 };
 
 // Scratch of the servicing pass (service.cu), grown on demand and reused.

@@ -580,4 +580,321 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
     }
 }
 
+// ------------------------------------------------------------------------------------------------
+// Batches of more than kFaultMaxThreads entries (uvm_perf_fault_batch_count up to the size of the fault buffer,
+// UVM/uvm_gpu_replayable_faults.c:153-165): one CTA of 1024 threads per batch, several entries per thread, the per-entry
+// arrays in global working space (kBigBytesPerEntry bytes per entry, T = power of two >= B entries per batch).
+// Decode, translation, sort and run formation are strided over the threads.  The fetch-time coalescing is the
+// reference's own sequential scan (:844-986, :753-820), done by one thread: with thousands of entries the fixed-point
+// formulation above would need its arrays in global memory and a barrier per round, and a big batch count means few
+// batches, so the scan of one batch overlaps the scans of the others.  Same outputs as k_fault_fetch_preprocess.
+constexpr uint32_t kBigMaxBatch = 16384;
+constexpr uint32_t kBigThreads = 1024;
+constexpr size_t kBigBytesPerEntry = 8 + 8 + 8 + 4 + 2 + 2 + 2 + 2 + 1 + 1 + 1 + 1 + 1;   // inst, page, key, merged, num, utlb, ctx, gstart, acc, st, flags, mask8 (+ alignment slack)
+
+struct fault_big_arrays {
+    uint64_t *inst, *page, *key;
+    uint32_t *merged;
+    uint16_t *num, *utlb, *ctx, *gstart;
+    uint8_t *acc, *st, *flags, *mask8;
+};
+// The arrays the sequential scan walks (28 bytes per entry) sit in shared memory when the batch fits (T <= kBigSmemEntries),
+// else in the working space with the rest.
+constexpr uint32_t kBigSmemEntries = 2048;   // (at 4096 the 147 KB leave one CTA per SM: measured no faster than global)
+constexpr size_t kBigScanBytesPerEntry = 8 + 8 + 4 + 2 + 2 + 1 + 1 + 1 + 1;
+__device__ __forceinline__ fault_big_arrays fault_big_carve(unsigned char *base, unsigned char *scan_base, uint32_t T)
+{
+    fault_big_arrays a;
+    unsigned char *p = scan_base;
+    a.inst = (uint64_t *)p; p += (size_t)T * 8;
+    a.page = (uint64_t *)p; p += (size_t)T * 8;
+    a.merged = (uint32_t *)p; p += (size_t)T * 4;
+    a.num = (uint16_t *)p; p += (size_t)T * 2;
+    a.utlb = (uint16_t *)p; p += (size_t)T * 2;
+    a.acc = p; p += T;
+    a.st = p; p += T;
+    a.flags = p; p += T;
+    a.mask8 = p; p += T;
+    unsigned char *q = scan_base == base ? p : base;
+    q = (unsigned char *)(((uintptr_t)q + 7) & ~(uintptr_t)7);
+    a.key = (uint64_t *)q; q += (size_t)T * 8;
+    a.ctx = (uint16_t *)q; q += (size_t)T * 2;
+    a.gstart = (uint16_t *)q;
+    return a;
+}
+
+UVMTIER_KERNEL void __launch_bounds__(kBigThreads)
+k_fault_fetch_preprocess_big(fault_kparams prm, uint32_t T, unsigned char *__restrict__ work, uvmtier_fault_packet_t *__restrict__ ring,
+                             const uvmtier_instance_ptr_entry_t *__restrict__ tbl, uint32_t *__restrict__ disp,
+                             uvmtier_ordered_fault_t *__restrict__ ordered, uvmtier_fault_group_t *__restrict__ groups,
+                             uvmtier_fault_batch_t *__restrict__ batches, uvmtier_fault_buffer_entry_t *__restrict__ entries,
+                             uint16_t *__restrict__ utlb_pending)
+{
+    __shared__ uint32_t s_first_invalid, s_coalesced, s_max_utlb, s_single, s_xlat_fail, s_ngroups;
+    __shared__ uint32_t s_scan[kBigThreads];
+    UVMTIER_DYN_SMEM(smem);                                               // per uTLB: last representative (int32) and pending count (uint32)
+    int32_t *s_last = (int32_t *)smem;
+    uint32_t *s_cnt = (uint32_t *)(smem + (size_t)prm.utlb_count * 4);
+    unsigned char *s_scan_arrays = smem + (((size_t)prm.utlb_count * 8 + 15) & ~(size_t)15);
+    const uint32_t tid = threadIdx.x, NT = blockDim.x, U = prm.utlb_count;
+    const uint32_t base = blockIdx.x * prm.B;
+    const uint32_t nb = min(prm.B, prm.n_entries - base);
+    unsigned char *my_work = work + (size_t)blockIdx.x * T * kBigBytesPerEntry;
+    const fault_big_arrays a = fault_big_carve(my_work, T <= kBigSmemEntries ? s_scan_arrays : my_work, T);
+
+    // ---- phase 1: load + decode ----
+    if (tid == 0) { s_first_invalid = nb; s_xlat_fail = 0; }
+    for (uint32_t k = tid; k < U; k += NT) { s_last[k] = -1; s_cnt[k] = 0; }
+    __syncthreads();
+    for (uint32_t i = tid; i < nb; i += NT) {
+        const uint64_t at = (uint64_t)prm.get + base + i;
+        const uint32_t ring_idx = (uint32_t)(at >= prm.ring_entries ? at - prm.ring_entries : at);
+        const uint4 x = ld_stream_v4((const uint4 *)&ring[ring_idx]);
+        const uint4 y = ld_stream_v4((const uint4 *)&ring[ring_idx] + 1);
+        fault_fields f;
+        fd_decode(x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w, prm.utlb_per_gpc, prm.va_bits, &f);
+        if (!f.valid)
+            atomicMin(&s_first_invalid, i);
+        a.inst[i] = ((uint64_t)f.inst_aperture << 60) | ((f.inst_address >> 12) << 8) | f.ve_id;
+        a.page[i] = f.fault_address >> 12;
+        a.acc[i] = (uint8_t)f.access_type;
+        a.utlb[i] = (uint16_t)f.utlb_id;
+        a.flags[i] = (uint8_t)f.flags;
+        a.num[i] = 0;
+        a.mask8[i] = 0;
+    }
+    __syncthreads();
+    const uint32_t n = s_first_invalid;                                   // num_cached_faults (:899-903)
+    if (prm.clear_valid)
+        for (uint32_t i = tid; i < n; i += NT) {
+            const uint64_t at = (uint64_t)prm.get + base + i;
+            const uint32_t ring_idx = (uint32_t)(at >= prm.ring_entries ? at - prm.ring_entries : at);
+            ring[ring_idx].w[7] &= 0x7fffffffu;                           // entry_clear_valid
+        }
+
+    // ---- phases 2-4: the reference's scan, one thread ----
+    if (tid == 0) {
+        int32_t last = -1;
+        uint32_t coalesced = 0, max_utlb = 0;
+        bool single = true;
+        for (uint32_t i = 0; i < n; i++) {
+            const uint64_t inst = a.inst[i], page = a.page[i];
+            const uint32_t acc = a.acc[i], u = a.utlb[i];
+            const bool fatal = (a.flags[i] & UVMTIER_FE_FATAL) != 0;
+            bool merged = false, same_inst = true;
+            if (u > max_utlb) max_utlb = u;
+            if (i > 0) {
+                same_inst = inst == a.inst[last];                         // :944
+                if (prm.coalesce && !fatal) {                             // :947-956 -> :782-820
+                    const int32_t lt = s_cnt[u] ? s_last[u] : -1;
+                    if (lt >= 0 && inst == a.inst[lt] && page == a.page[lt]) {
+                        // per-uTLB rule (:753-780): the entry joins lt's segment; a higher access type takes over
+                        a.num[lt]++;
+                        a.mask8[lt] |= (uint8_t)(1u << acc);
+                        if (acc > a.acc[lt]) {
+                            a.mask8[i] = a.mask8[lt];
+                            a.num[i] = a.num[lt];
+                            a.flags[lt] |= UVMTIER_FE_FILTERED;
+                            s_last[u] = (int32_t)i;                       // the batch-wide `last` is NOT moved (:804-809)
+                        }
+                        else
+                            a.flags[i] |= UVMTIER_FE_FILTERED;
+                        a.st[i] = ST_T;
+                        a.merged[i] = a.st[lt] == ST_NEW ? (uint32_t)lt : a.merged[lt];      // the segment's head, for now
+                        merged = true;
+                    }
+                    else if (same_inst && page == a.page[last] && acc <= a.acc[last]) {
+                        a.num[last]++;                                    // lands on `last` even if that was displaced (:804-817)
+                        a.mask8[last] |= (uint8_t)(1u << acc);
+                        a.flags[i] |= UVMTIER_FE_FILTERED;
+                        a.st[i] = ST_G;
+                        a.merged[i] = (uint32_t)last;
+                        merged = true;
+                    }
+                }
+            }
+            if (!merged) {
+                if (single && !same_inst) single = false;                 // :959-960
+                a.num[i] = 1;
+                a.mask8[i] = (uint8_t)(1u << acc);
+                s_cnt[u]++;
+                s_last[u] = (int32_t)i;
+                last = (int32_t)i;
+                coalesced++;
+                a.st[i] = ST_NEW;
+                a.merged[i] = i;
+            }
+        }
+        // second pass: NEW and T entries report their segment's representative (the one entry of it that is not filtered)
+        for (uint32_t i = 0; i < n; i++)
+            if (a.st[i] != ST_G && !(a.flags[i] & UVMTIER_FE_FILTERED))
+                a.key[a.st[i] == ST_NEW ? i : a.merged[i]] = i;           // key[] is free until phase 5: rep of head h at key[h]
+        for (uint32_t i = 0; i < n; i++)
+            if (a.st[i] != ST_G)
+                a.merged[i] = (uint32_t)a.key[a.st[i] == ST_NEW ? i : a.merged[i]];
+        s_coalesced = coalesced; s_max_utlb = max_utlb; s_single = single ? 1u : 0u;
+    }
+    __syncthreads();
+    const uint32_t num_coalesced = s_coalesced;
+    if (utlb_pending)
+        for (uint32_t k = tid; k < U; k += NT)
+            utlb_pending[(size_t)blockIdx.x * U + k] = (uint16_t)s_cnt[k];
+
+    // ---- phase 5: translation + sort keys ----
+    const uint32_t ib = prm.idx_bits;
+    for (uint32_t i = tid; i < T; i += NT) {
+        uint64_t key = ~0ull;
+        if (i < n && !(a.flags[i] & UVMTIER_FE_FILTERED)) {
+            const uint64_t inst = a.inst[i];
+            const uint64_t inst_address = ((inst >> 8) & ((1ull << 52) - 1)) << 12;
+            const uint32_t aperture = (uint32_t)(inst >> 60), ve_id = (uint32_t)(inst & 0xffu);
+            int ctx = -1;
+            uint32_t rank = 0;
+            for (uint32_t k = 0; k < prm.tbl_n; k++) {
+                const uvmtier_instance_ptr_entry_t r = tbl[k];
+                if (r.instance_ptr == inst_address && r.aperture == aperture && (r.ve_id == UVMTIER_VE_ID_ANY || r.ve_id == ve_id)) {
+                    ctx = (int)k;
+                    rank = r.sort_rank;
+                    break;
+                }
+            }
+            a.ctx[i] = (uint16_t)ctx;
+            if (ctx < 0)
+                s_xlat_fail = 1;
+            key = ((uint64_t)rank << (ib + 3 + kPageBits)) | ((a.page[i] & ((1ull << kPageBits) - 1)) << (ib + 3)) |
+                  ((uint64_t)(7u - a.acc[i]) << ib) | (uint64_t)i;
+        }
+        a.key[i] = key;
+    }
+    __syncthreads();
+    const bool xlat_fail = s_xlat_fail != 0;
+    if (xlat_fail)
+        for (uint32_t i = tid; i < T; i += NT) a.key[i] = ~0ull;
+    __syncthreads();
+    // bitonic sort of T keys in the working space
+    for (uint32_t k = 2; k <= T; k <<= 1)
+        for (uint32_t j = k >> 1; j > 0; j >>= 1) {
+            for (uint32_t t = tid; t < T / 2; t += NT) {
+                const uint32_t lo = ((t & ~(j - 1)) << 1) | (t & (j - 1)), hi = lo | j;
+                const uint64_t x = a.key[lo], y = a.key[hi];
+                const bool up = (lo & k) == 0;
+                if ((x > y) == up) { a.key[lo] = y; a.key[hi] = x; }
+            }
+            __syncthreads();
+        }
+
+    // ---- phase 6: outputs + va_block runs ----
+    const uint32_t m = xlat_fail ? 0u : num_coalesced;
+    const uint32_t idxmask = (1u << ib) - 1u;
+    // run boundaries: each thread takes a contiguous stretch of the sorted view
+    const uint32_t per = (m + NT - 1) / NT, p0 = min(tid * per, m), p1 = min(p0 + per, m);
+    uint32_t mine = 0;
+    for (uint32_t p = p0; p < p1; p++) {
+        const uint64_t key = a.key[p];
+        const uint32_t idx = (uint32_t)key & idxmask;
+        const bool sfatal = (a.flags[idx] & UVMTIER_FE_FATAL) != 0;
+        bool boundary = p == 0;
+        if (p > 0) {
+            const uint64_t prev = a.key[p - 1];
+            const bool pfatal = (a.flags[(uint32_t)prev & idxmask] & UVMTIER_FE_FATAL) != 0;
+            boundary = (prev >> (ib + 3 + 9)) != (key >> (ib + 3 + 9)) || sfatal || pfatal;
+        }
+        mine += boundary ? 1u : 0u;
+        uvmtier_ordered_fault_t o;
+        o.fault_address = a.page[idx] << 12;
+        o.fault_index = (uint16_t)idx;
+        o.ctx = a.ctx[idx];
+        o.num_instances = a.num[idx];
+        o.access_type_mask = a.mask8[idx];
+        o.fault_access_type = (uint8_t)(a.acc[idx] | (sfatal ? UVMTIER_OF_FATAL : 0u));
+        ordered[base + p] = o;
+    }
+    s_scan[tid] = mine;
+    __syncthreads();
+    if (tid == 0) {
+        uint32_t run = 0;
+        for (uint32_t t = 0; t < NT; t++) { const uint32_t c = s_scan[t]; s_scan[t] = run; run += c; }
+        s_ngroups = run;
+    }
+    __syncthreads();
+    uint32_t gidx = s_scan[tid];
+    for (uint32_t p = p0; p < p1; p++) {
+        const uint64_t key = a.key[p];
+        const uint32_t idx = (uint32_t)key & idxmask;
+        const bool sfatal = (a.flags[idx] & UVMTIER_FE_FATAL) != 0;
+        bool boundary = p == 0;
+        if (p > 0) {
+            const uint64_t prev = a.key[p - 1];
+            const bool pfatal = (a.flags[(uint32_t)prev & idxmask] & UVMTIER_FE_FATAL) != 0;
+            boundary = (prev >> (ib + 3 + 9)) != (key >> (ib + 3 + 9)) || sfatal || pfatal;
+        }
+        if (boundary)
+            a.gstart[gidx++] = (uint16_t)p;
+    }
+    __syncthreads();
+    const uint32_t ngroups = s_ngroups;
+    for (uint32_t g = tid; g < ngroups; g += NT) {
+        const uint32_t p = a.gstart[g], next = g + 1 < ngroups ? a.gstart[g + 1] : m;
+        const uint32_t idx = (uint32_t)a.key[p] & idxmask;
+        uvmtier_fault_group_t grp;
+        grp.block_start = (a.page[idx] << 12) & ~((uint64_t)UVMTIER_VA_BLOCK_SIZE - 1);
+        grp.ctx = a.ctx[idx];
+        grp.first_fault_index = (uint16_t)p;
+        grp.block_faults = (uint16_t)(next - p);
+        grp.flags = (a.flags[idx] & UVMTIER_FE_FATAL) ? 1u : 0u;
+        groups[base + g] = grp;
+    }
+    for (uint32_t i = tid; i < nb; i += NT) {
+        uint32_t d = 0;
+        if (i < n) {
+            const bool filtered = (a.flags[i] & UVMTIER_FE_FILTERED) != 0, fatal = (a.flags[i] & UVMTIER_FE_FATAL) != 0;
+            d = (a.merged[i] & UVMTIER_DISP_INDEX_MASK) | (filtered ? UVMTIER_DISP_FILTERED : 0u) | (fatal ? UVMTIER_DISP_FATAL : 0u) |
+                UVMTIER_DISP_VALID | ((uint32_t)a.st[i] << UVMTIER_DISP_RULE_SHIFT);
+        }
+        disp[base + i] = d;
+    }
+    if (entries)
+        for (uint32_t i = tid; i < n; i += NT) {
+            // decode again (cheaper than keeping every field): the packet's VALID bit may be cleared by now, nothing else
+            const uint64_t at = (uint64_t)prm.get + base + i;
+            const uint32_t ring_idx = (uint32_t)(at >= prm.ring_entries ? at - prm.ring_entries : at);
+            const uint4 x = *((const uint4 *)&ring[ring_idx]);
+            const uint4 y = *((const uint4 *)&ring[ring_idx] + 1);
+            fault_fields f;
+            fd_decode(x.x, x.y, x.z, x.w, y.x, y.y, y.z, y.w | 0x80000000u, prm.utlb_per_gpc, prm.va_bits, &f);
+            const bool live = !(a.flags[i] & UVMTIER_FE_FILTERED);
+            uvmtier_fault_buffer_entry_t e;
+            e.fault_address = f.fault_address;
+            e.timestamp = f.timestamp;
+            e.instance_ptr_address = f.inst_address;
+            e.client_id = (uint16_t)f.client_id;
+            e.mmu_engine_id = (uint16_t)f.engine_id;
+            e.utlb_id = (uint16_t)f.utlb_id;
+            e.num_instances = live ? a.num[i] : (uint16_t)0;
+            e.instance_ptr_aperture = (uint8_t)f.inst_aperture;
+            e.fault_type = (uint8_t)f.fault_type;
+            e.fault_access_type = (uint8_t)f.access_type;
+            e.client_type = (uint8_t)f.client_type;
+            e.mmu_engine_type = (uint8_t)f.engine_type;
+            e.gpc_id = (uint8_t)f.gpc_id;
+            e.ve_id = (uint8_t)f.ve_id;
+            e.flags = a.flags[i];
+            e.access_type_mask = live ? a.mask8[i] : (uint8_t)0;
+            for (int k = 0; k < 7; k++) e.pad[k] = 0;
+            entries[base + i] = e;
+        }
+    if (tid == 0) {
+        uvmtier_fault_batch_t bt;
+        bt.num_cached_faults = n;
+        bt.num_coalesced_faults = num_coalesced;
+        bt.is_single_instance_ptr = s_single;
+        bt.max_utlb_id = s_max_utlb;
+        bt.status = xlat_fail ? NV_WARN_MORE_PROCESSING_REQUIRED : NV_OK;
+        bt.num_duplicate_faults = 0;
+        bt.num_invalid_prefetch_faults = 0;
+        bt.num_block_groups = xlat_fail ? 0u : ngroups;
+        batches[blockIdx.x] = bt;
+    }
+}
+
 } // namespace uvmtier_k

@@ -22,6 +22,8 @@ void uvmtier_fault_state_destroy(uvmtier_ctx_t *ctx)
         return;
     if (ctx->faults->d_table)
         cudaFree(ctx->faults->d_table);
+    if (ctx->faults->d_big)
+        cudaFree(ctx->faults->d_big);
     free(ctx->faults);
     ctx->faults = NULL;
 }
@@ -33,7 +35,7 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
 {
     if (!ctx || !gp || (n_rows && !h_table))
         return NV_ERR_INVALID_ARGUMENT;
-    if (gp->max_batch_size < 1 || gp->max_batch_size > kFaultMaxThreads || gp->va_bits < 40 || gp->va_bits > 57 ||
+    if (gp->max_batch_size < 1 || gp->max_batch_size > kBigMaxBatch || gp->va_bits < 40 || gp->va_bits > 57 ||
         n_rows > kFaultMaxTableRows || gp->utlb_per_gpc_count == 0 || gp->gpc_count == 0 ||
         gp->utlb_per_gpc_count * gp->gpc_count > 4096)
         return NV_ERR_INVALID_ARGUMENT;
@@ -63,6 +65,13 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
     fs->threads = threads;
     fs->idx_bits = idx_bits;
     fs->smem_bytes = fault_smem_bytes(threads, gp->utlb_per_gpc_count * gp->gpc_count, (uint32_t)n_rows);
+    if (gp->max_batch_size > kFaultMaxThreads) {
+        // more entries per batch than a CTA has threads: the strided kernel, per-uTLB tables in shared memory
+        fs->big_T = threads;
+        fs->threads = kBigThreads;
+        fs->smem_bytes = (((size_t)gp->utlb_per_gpc_count * gp->gpc_count * 8 + 15) & ~(size_t)15) +
+                         (threads <= kBigSmemEntries ? (size_t)threads * kBigScanBytesPerEntry : 0);
+    }
     ctx->faults = fs;
     UVMTIER_CUDA(cudaMalloc(&fs->d_table, (n_rows ? n_rows : 1) * sizeof(*h_table)));
     if (n_rows) {
@@ -71,8 +80,11 @@ NV_STATUS uvmtier_fault_buffer_init(uvmtier_ctx_t *ctx, const uvmtier_fault_gpu_
     }
     if (fs->smem_bytes > 200 * 1024)
         return NV_ERR_INVALID_ARGUMENT;                     // more uTLBs than a CTA's shared memory can track
-    if (fs->smem_bytes > 48 * 1024)
+    if (fs->smem_bytes > 48 * 1024 && !fs->big_T)
         UVMTIER_CUDA(cudaFuncSetAttribute(k_fault_fetch_preprocess, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                          (int)fs->smem_bytes));
+    if (fs->smem_bytes > 48 * 1024 && fs->big_T)
+        UVMTIER_CUDA(cudaFuncSetAttribute(k_fault_fetch_preprocess_big, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                           (int)fs->smem_bytes));
     return NV_OK;
 }
@@ -144,6 +156,26 @@ NV_STATUS uvmtier_fetch_preprocess_fault_batches_device(uvmtier_ctx_t *ctx, uvmt
 
 } // extern "C"
 
+// Working space of the big-batch kernel for up to n_batches batches per launch (allocates: not while a stream is capturing;
+// the streamed entry points reserve for the whole ring before they start).
+NV_STATUS uvmtier_fault_big_reserve(uvmtier_ctx_t *ctx, uint32_t n_batches)
+{
+    uvmtier_fault_state *fs = ctx->faults;
+    if (!fs->big_T)
+        return NV_OK;
+    const size_t need = (size_t)n_batches * fs->big_T * kBigBytesPerEntry;
+    if (need <= fs->big_bytes)
+        return NV_OK;
+    UVMTIER_CUDA(cudaDeviceSynchronize());                  // a launch on another of the context's streams may still read it
+    if (fs->d_big)
+        UVMTIER_CUDA(cudaFree(fs->d_big));
+    fs->d_big = NULL;
+    fs->big_bytes = 0;
+    UVMTIER_CUDA(cudaMalloc(&fs->d_big, need));
+    fs->big_bytes = need;
+    return NV_OK;
+}
+
 NV_STATUS uvmtier_fetch_preprocess_on_stream(uvmtier_ctx_t *ctx, cudaStream_t stream, uvmtier_fault_packet_t *d_ring,
                                              uint32_t ring_entries, uint32_t get, uint32_t put, int clear_valid,
                                              uint32_t *d_disposition, uvmtier_ordered_fault_t *d_ordered,
@@ -178,6 +210,14 @@ NV_STATUS uvmtier_fetch_preprocess_on_stream(uvmtier_ctx_t *ctx, cudaStream_t st
     const uint32_t n_batches = (n + prm.B - 1) / prm.B;
     // the optional per-uTLB counts of batch b land at d_utlb_pending[(utlb_batch_base + b) * utlb_count + u]
     uint16_t *up = fs->d_utlb_pending ? fs->d_utlb_pending + (size_t)utlb_batch_base * prm.utlb_count : NULL;
+    if (fs->big_T) {
+        const NV_STATUS rs = uvmtier_fault_big_reserve(ctx, n_batches);
+        if (rs != NV_OK)
+            return rs;
+        UVMTIER_LAUNCH(k_fault_fetch_preprocess_big, n_batches, kBigThreads, fs->smem_bytes, stream, prm, fs->big_T, fs->d_big, d_ring,
+                       (const uvmtier_instance_ptr_entry_t *)fs->d_table, d_disposition, d_ordered, d_groups, d_batches, d_entries, up);
+        return NV_OK;
+    }
     UVMTIER_LAUNCH(k_fault_fetch_preprocess, n_batches, fs->threads, fs->smem_bytes, stream, prm, d_ring, fs->d_table,
                    d_disposition, d_ordered, d_groups, d_batches, d_entries, up);
     return NV_OK;
@@ -353,6 +393,8 @@ extern "C" NV_STATUS uvmtier_access_counters_fetch_preprocess_device(uvmtier_ctx
         return NV_OK;
     if (!d_ordered || !d_groups || !d_batches)
         return NV_ERR_INVALID_ARGUMENT;
+    if (fs->big_T)
+        return NV_ERR_NOT_SUPPORTED;                        // notification batches are one thread per entry: max_batch_size <= 1024
     UVMTIER_CUDA(cudaSetDevice(ctx->device));
     ac_kparams prm;
     prm.B = fs->gp.max_batch_size;
@@ -382,6 +424,11 @@ NV_STATUS uvmtier_streamed_begin(uvmtier_ctx_t *ctx, uint32_t ring_entries, uint
         per = (plan->n_batches + UVMTIER_MAX_COPY_CHUNKS - 1) / UVMTIER_MAX_COPY_CHUNKS;
     plan->per = per;
     plan->n_chunks = (plan->n_batches + per - 1) / per;
+    {
+        const NV_STATUS rs = uvmtier_fault_big_reserve(ctx, per);         // before any capture starts
+        if (rs != NV_OK)
+            return rs;
+    }
     if (!ctx->copy_stream)
         UVMTIER_CUDA(cudaStreamCreateWithFlags(&ctx->copy_stream, cudaStreamNonBlocking));
     for (uint32_t c = 0; c <= plan->n_chunks; c++)

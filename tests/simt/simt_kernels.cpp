@@ -2,6 +2,8 @@
 // TEST INFRASTRUCTURE ONLY ("not gpu" tests); see simt.h.
 #include "simt.h"
 
+#include <vector>
+
 #include "prefetch_kernels.cuh"
 
 using namespace uvmtier_k;
@@ -65,6 +67,14 @@ int simt_fault_fetch_preprocess(uvmtier_fault_packet_t *ring, uint32_t ring_entr
     prm.clear_valid = clear_valid != 0;
     const uint32_t n_batches = (n + prm.B - 1) / prm.B;
     (void)force_cta_kernel;
+    if (prm.B > kFaultMaxThreads) {
+        // batches of more than 1024 entries: the strided kernel (64 emulated threads are enough to exercise the striding)
+        std::vector<unsigned char> work((size_t)n_batches * threads * kBigBytesPerEntry);
+        simt::launch(dim3(n_batches), dim3(64), [&] {
+            k_fault_fetch_preprocess_big(prm, threads, work.data(), ring, tbl, disp, ordered, groups, batches, entries, utlb_pending);
+        });
+        return (int)n_batches;
+    }
     if (fault_smem_bytes(threads, prm.utlb_count, tbl_n) > sizeof(simt::g_dynamic_smem))
         return -1;
     simt::launch(dim3(n_batches), dim3(threads),

@@ -103,8 +103,23 @@ def test_gpu_edge_cases(ctx):
     # bad arguments
     import ctypes
     import uvmtier
-    st = uvmtier.lib().uvmtier_fault_buffer_init(ctx.handle, T.P(TG.gpu_params(2000)), T.P(tbl), ctypes.c_size_t(len(tbl)))
+    st = uvmtier.lib().uvmtier_fault_buffer_init(ctx.handle, T.P(TG.gpu_params(20000)), T.P(tbl), ctypes.c_size_t(len(tbl)))
     assert st == 0x1F
+
+
+@pytest.mark.parametrize("dist,n,B,n_spaces", [("uniform", 1 << 20, 4096, 4), ("stream", 300000, 4096, 2), ("hotset", 100000, 2048, 4),
+                                               ("adversarial", 40000, 3000, 2), ("uniform", 15000, 16384, 1)])
+def test_gpu_batches_above_1024_entries(ctx, dist, n, B, n_spaces):
+    """batch = 4096 and the whole trace in one batch.  The strided kernel against the restatement (which
+    tests/test_oracle_faults.py holds against the reference's fetch / preprocess code at these batch sizes)."""
+    orc = T.load_oracle()
+    pk, tbl, _ = TG.fault_trace(n, 3, dist, n_spaces)
+    gp = TG.gpu_params(B)
+    got = gpu_fetch(ctx, pk, gp, tbl)
+    want = F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl)
+    F.assert_fetch_equal(want, got, "%s %d" % (dist, B))
+    F.check_groups(got, tbl, B)
+    assert int(got["batch"]["num_cached_faults"].sum()) == n
 
 
 def test_gpu_baseline_size_1m_entries(ctx):

@@ -38,7 +38,7 @@ def gpu_pipeline(ctx, pk, gp, tbl, lay, st0, run_cap=1 << 21):
 
 
 @pytest.mark.parametrize("dist", ["uniform", "stream", "hotset", "adversarial"])
-@pytest.mark.parametrize("B,n_spaces,va_blocks", [(256, 4, 4096), (64, 2, 128), (1024, 1, 512)])
+@pytest.mark.parametrize("B,n_spaces,va_blocks", [(256, 4, 4096), (64, 2, 128), (1024, 1, 512), (4096, 2, 1024)])
 def test_gpu_service_matches_oracle(dist, B, n_spaces, va_blocks):
     import uvmtier
     orc = T.load_oracle()

@@ -67,6 +67,24 @@ def test_simt_kernel_matches_oracle(dist, B, cta):
     F.check_groups(got, tbl, B)
 
 
+@pytest.mark.parametrize("dist,n,B", [("uniform", 9000, 4096), ("adversarial", 5000, 2048), ("hotset", 12000, 16384), ("stream", 7000, 3000)])
+def test_batches_above_1024_entries(dist, n, B):
+    """uvm_perf_fault_batch_count above a CTA's worth (the reference clamps it to the fault buffer's size, :153-165): the
+    strided kernel with the sequential coalescing scan, against the restatement and against the reference's own fetch /
+    preprocess code; 16384 > n is the whole trace in one batch."""
+    orc, sim = T.load_oracle(), T.load_simt()
+    pk, tbl, _ = TG.fault_trace(n, 5, dist, 2, total_va_bytes=64 << 21)
+    gp = TG.gpu_params(B)
+    want = F.run_fetch_preprocess(orc, "oracle", pk, gp, tbl)
+    ref = T.load_ref("faults")
+    if ref is not None:
+        F.assert_fetch_equal(F.run_fetch_preprocess(ref, "ref", pk, gp, tbl), want, "reference vs restatement %s %d" % (dist, B))
+    got = F.run_fetch_preprocess_simt(sim, pk, gp, tbl)
+    F.assert_fetch_equal(want, got, "%s %d" % (dist, B))
+    F.check_groups(got, tbl, B)
+    assert len(want["batch"]) == -(-n // B)
+
+
 def test_parse_decode_all_field_values():
     """F1: every client id with a uTLB, every fault type, access type, aperture; HUB clients; 49- and 57-bit VAs."""
     orc, sim, ref = T.load_oracle(), T.load_simt(), T.load_ref("faults")

@@ -303,3 +303,14 @@ def test_reference_code_end_to_end_equals_the_restatement(dist):
         S.use_reference_back_half(rs, None, None)
     S.assert_ref_equals_oracle(got, want, "reference end to end, %s" % dist)
     assert int((want["records"]["page_fault_count"] > 0).sum()) >= 4
+
+
+@pytest.mark.parametrize("B", [2048, 4096])
+def test_service_pass_on_batches_above_1024_entries(B):
+    """The servicing pass is indifferent to the batch size (16-bit fields hold up to 65535 entries per batch)."""
+    pk, tbl, lay = TG.fault_trace(6000, 71, "uniform", 2, total_va_bytes=SMALL_VA)
+    gp = TG.gpu_params(B)
+    st0 = S.random_state(lay["blocks_per_space"] * 2, 9)
+    _, want, got = _both(pk, gp, tbl, lay, st0)
+    S.assert_service_equal(want, got, B, "B %d" % B)
+    S.check_service_invariants(got, st0)

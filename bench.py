@@ -440,7 +440,8 @@ def oversubscription_numbers(ctx, lib, P, rank, blocks=8192, hbm_chunks=4096, dr
     import uvmtier
     from uvmtier import TIER_CXL, TIER_DRAM, TIER_HBM, tracegen as TG
     from uvmtier.blockstate import HostBlockState, make_layout
-    B, chunk_batches = 256, 16
+    B = 256
+    chunk_batches = max(1, min(16, hbm_chunks // B))      # a round may not fault on more va_blocks than HBM has chunks
     t_setup = time.perf_counter()
     gp = TG.gpu_params(B)
     info = {TIER_HBM: ctx.tier_create(TIER_HBM, hbm_chunks << 21), TIER_DRAM: ctx.tier_create(TIER_DRAM, blocks << 21),

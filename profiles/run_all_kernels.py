@@ -67,4 +67,41 @@ print("copies done")
 # ---- thrashing detector and access counters at the bench's sizes ----
 print(bench.thrashing_numbers(ctx, lib, P, 0)["ms"])
 print(bench.access_counter_numbers(ctx, lib, P, 0)["service_ms"])
+print(bench.nonreplayable_numbers(ctx, lib, P, 0))
+
+# ---- round 2: thrashing hints (queries over 4096 va_blocks), the tiered loop on a small table, the big-batch K1 ----
+import thrashlib as TH  # noqa: E402
+from uvmtier import tracegen as TG  # noqa: E402
+n_slots = 4096
+cfg = TH.make_cfg("pcie", gpus=(1,), pin_threshold=2)
+layout = BSL.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1))
+t = ctx.thrashing_create(layout)
+ctx.thrashing_enable_hints(t, cfg)
+rng = np.random.default_rng(3)
+now = 10000
+for rnd in range(6):
+    ev = np.zeros(n_slots * 4, TH.EVENT_DT)
+    ev["slot"] = np.repeat(np.arange(n_slots), 4)
+    ev["first_page"] = np.tile(np.arange(4) * 16, n_slots); ev["num_pages"] = 16
+    ev["processor"] = rnd & 1; ev["time_stamp"] = now
+    ctx.thrashing_note_events(t, ev)
+    now += 50000
+q = np.zeros(n_slots * 8, TH.QUERY_DT)
+q["slot"] = np.repeat(np.arange(n_slots), 8); q["page"] = np.tile(np.arange(8) * 2, n_slots)
+q["requester"] = 1; q["resident_processors"] = 1; q["preferred_location"] = TH.NO_PREF
+for rnd in range(4):
+    q["time_stamp"] = now
+    q["requester"] = rnd & 1
+    h, c = ctx.thrashing_get_hints(t, q)
+    now += 20000
+    print("hints round", rnd, c[3:6])
+print("unpinned", ctx.thrashing_unpin_expired(t, now + 10 ** 9)[1])
+ctx.thrashing_destroy(t)
+print(bench.oversubscription_numbers(ctx, lib, P, 0, blocks=1024, hbm_chunks=4096 // 8, dram_blocks=384)["uniform"]["entries_per_s"])
+pk, tbl, lay = TG.fault_trace(1 << 18, 1, "uniform", 4)
+gp = TG.gpu_params(4096)
+ctx.fault_buffer_init(gp, tbl)
+ring = np.zeros(((1 << 18) + 1, 8), np.uint32); ring[:1 << 18] = pk
+r = ctx.fetch_preprocess_fault_batches(ring, 0, 1 << 18)
+print("big batches", len(r["batch"]))
 ctx.close()

@@ -354,21 +354,26 @@ UVMTIER_KERNEL void __launch_bounds__(kPmmSelectThreads)
 k_pmm_select_weighted(const unsigned long long *__restrict__ key, const uint32_t *__restrict__ weight,
                       const uint32_t *__restrict__ aux, uint32_t n, const uint32_t *__restrict__ target, uint32_t *__restrict__ sel)
 {
-    __shared__ unsigned long long hist[256];
-    __shared__ unsigned long long s_prefix, s_left, s_total;
-    __shared__ uint32_t s_cnt, s_w, s_aux;
-    const unsigned long long want = *target;
+    // weights add up to at most 512 * 65536 = 2^25: 32-bit bins.  Stamps of one table share their high bytes, so most of
+    // a pass's keys fall into one bin: every thread first adds up consecutive keys of the same digit, then the lanes of a
+    // warp that ended on the same digit are merged, and only then the shared-memory atomics happen.
+    __shared__ uint32_t hist[256];
+    __shared__ unsigned long long s_prefix;
+    __shared__ uint32_t s_left, s_total, s_cnt, s_w, s_aux;
+    const int lane = threadIdx.x & 31;
+    const uint32_t want = *target;
     if (threadIdx.x == 0) { s_prefix = 0; s_total = 0; s_cnt = 0; s_w = 0; s_aux = 0; }
     __syncthreads();
     if (want == 0) {
         if (threadIdx.x < 6) sel[threadIdx.x] = 0;
         return;
     }
-    unsigned long long mine = 0;
+    uint32_t mine = 0;
     for (uint32_t i = threadIdx.x; i < n; i += blockDim.x)
         if (key[i] != 0)
             mine += weight[i];
-    if (mine)
+    mine = __reduce_add_sync(0xffffffffu, mine);
+    if (lane == 0 && mine)
         atomicAdd(&s_total, mine);
     __syncthreads();
     unsigned long long T = ~0ull;
@@ -381,16 +386,35 @@ k_pmm_select_weighted(const unsigned long long *__restrict__ key, const uint32_t
                 hist[d] = 0;
             __syncthreads();
             const unsigned long long prefix = s_prefix;
+            uint32_t cur = 0xffffffffu, sum = 0;                          // the digit this thread is adding up, and its sum
             for (uint32_t i = threadIdx.x; i < n; i += blockDim.x) {
                 const unsigned long long k = key[i];
                 const bool match = pass == 7 ? true : (k >> (8 * (pass + 1))) == prefix;
-                if (k != 0 && match && weight[i])
-                    atomicAdd(&hist[(uint32_t)(k >> (8 * pass)) & 255u], (unsigned long long)weight[i]);
+                const uint32_t w = weight[i];
+                if (k != 0 && match && w) {
+                    const uint32_t d = (uint32_t)(k >> (8 * pass)) & 255u;
+                    if (d != cur) {
+                        if (sum) atomicAdd(&hist[cur], sum);
+                        cur = d;
+                        sum = 0;
+                    }
+                    sum += w;
+                }
             }
+            // lanes that ended on the same digit: the lowest of them adds for all
+            uint32_t total = 0, first = 32;
+            for (int src = 0; src < 32; src++) {
+                const uint32_t d = __shfl_sync(0xffffffffu, cur, src), v = __shfl_sync(0xffffffffu, sum, src);
+                if (d == cur && v) {
+                    total += v;
+                    if (first == 32) first = (uint32_t)src;
+                }
+            }
+            if (sum && first == (uint32_t)lane)
+                atomicAdd(&hist[cur], total);
             __syncthreads();
             if (threadIdx.x == 0) {
-                unsigned long long left = s_left;
-                uint32_t d = 0;
+                uint32_t left = s_left, d = 0;
                 while (hist[d] < left) {                                  // the digit in which the running sum reaches the target
                     left -= hist[d];
                     d++;
@@ -411,7 +435,10 @@ k_pmm_select_weighted(const unsigned long long *__restrict__ key, const uint32_t
             a += aux ? aux[i] : 0u;
         }
     }
-    if (c) { atomicAdd(&s_cnt, c); atomicAdd(&s_w, w); atomicAdd(&s_aux, a); }
+    c = __reduce_add_sync(0xffffffffu, c);
+    w = __reduce_add_sync(0xffffffffu, w);
+    a = __reduce_add_sync(0xffffffffu, a);
+    if (lane == 0 && c) { atomicAdd(&s_cnt, c); atomicAdd(&s_w, w); atomicAdd(&s_aux, a); }
     __syncthreads();
     if (threadIdx.x == 0) {
         sel[0] = (uint32_t)T; sel[1] = (uint32_t)(T >> 32);

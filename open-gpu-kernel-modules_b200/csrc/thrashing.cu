@@ -9,7 +9,7 @@
 
 using namespace uvmtier_k;
 
-static size_t thrash_scratch_words(uint32_t n_slots) { return 4 + (size_t)n_slots + ((size_t)n_slots + 31) / 32; }
+static size_t thrash_scratch_words(uint32_t n_slots) { return 4 + 2 * (size_t)n_slots; }
 
 static thrash_hint_tables thrash_tables(const uvmtier_thrashing_t *t)
 {
@@ -96,10 +96,11 @@ NV_STATUS uvmtier_thrashing_note_events_device(uvmtier_ctx_t *ctx, uvmtier_thras
         return NV_OK;
     // the segment counter and the one-bit-per-slot table; the segment list between them is overwritten
     UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch, 0, 4 * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch + 4 + t->n_slots, 0, ((size_t)t->n_slots + 31) / 32 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch + 4 + t->n_slots, 0xff, (size_t)t->n_slots * sizeof(uint32_t), ctx->stream));
     uint32_t grid = (n_events + kThrashThreads - 1) / kThrashThreads;
     if (grid > (uint32_t)ctx->sm_count * 8)
         grid = (uint32_t)ctx->sm_count * 8;
+    UVMTIER_LAUNCH(k_thrash_heads_min, (int)grid, kThrashThreads, 0, ctx->stream, n_events, d_events, t->n_slots, t->d_scratch);
     UVMTIER_LAUNCH(k_thrash_heads, (int)grid, kThrashThreads, 0, ctx->stream, n_events, d_events, t->n_slots, t->d_scratch, d_counters);
     // one warp per va_block with events; at most n_slots of them
     const uint64_t segs = n_events < t->n_slots ? n_events : t->n_slots;
@@ -184,13 +185,15 @@ NV_STATUS uvmtier_thrashing_get_hints_device(uvmtier_ctx_t *ctx, uvmtier_thrashi
         return NV_OK;
     UVMTIER_CUDA(cudaMemsetAsync(d_hints, 0, (size_t)n_queries * sizeof(uvmtier_thrashing_hint_t), ctx->stream));
     UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch, 0, 4 * sizeof(uint32_t), ctx->stream));
-    UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch + 4 + t->n_slots, 0, ((size_t)t->n_slots + 31) / 32 * sizeof(uint32_t), ctx->stream));
+    UVMTIER_CUDA(cudaMemsetAsync(t->d_scratch + 4 + t->n_slots, 0xff, (size_t)t->n_slots * sizeof(uint32_t), ctx->stream));
     uint32_t grid = (n_queries + kThrashThreads - 1) / kThrashThreads;
     if (grid > (uint32_t)ctx->sm_count * 8)
         grid = (uint32_t)ctx->sm_count * 8;
     // the groups of queries: the query carries its slot where the event does, and has the event's size
     static_assert(sizeof(uvmtier_thrashing_query_t) == sizeof(uvmtier_perf_event_t) &&
                   offsetof(uvmtier_thrashing_query_t, slot) == offsetof(uvmtier_perf_event_t, slot), "k_thrash_heads reads .slot only");
+    UVMTIER_LAUNCH(k_thrash_heads_min, (int)grid, kThrashThreads, 0, ctx->stream, n_queries, (const uvmtier_perf_event_t *)d_queries,
+                   t->n_slots, t->d_scratch);
     UVMTIER_LAUNCH(k_thrash_heads, (int)grid, kThrashThreads, 0, ctx->stream, n_queries, (const uvmtier_perf_event_t *)d_queries,
                    t->n_slots, t->d_scratch, d_counters);
     const uint64_t segs = n_queries < t->n_slots ? n_queries : t->n_slots;

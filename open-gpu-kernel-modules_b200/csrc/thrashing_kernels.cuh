@@ -20,20 +20,34 @@ __device__ __forceinline__ bool thrash_event_ok(const uvmtier_perf_event_t &e, u
     return e.slot < n_slots && (uint32_t)e.first_page + e.num_pages <= 512u && e.processor < 32u && e.kind <= 1u;
 }
 
-// scratch: [0] number of segments, [4 ..] first event of every segment, then one bit per slot.
+// scratch: [0] number of segments, [4 ..] first event of every segment, then one word per slot (the lowest head index
+// of the slot's groups; 0xffffffff = none, set by the host before the call).
 // counters: [0] detections, [1] page resets, [2] events dropped (malformed, or their va_block showed up in a second,
-// separate group of the same call)
+// separate group of the same call: the group that starts first is kept, whatever order the threads run in)
+UVMTIER_KERNEL void __launch_bounds__(kThrashThreads)
+k_thrash_heads_min(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, uint32_t n_slots, uint32_t *__restrict__ scratch)
+{
+    uint32_t *slot_head = scratch + 4 + n_slots;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_events; i += gridDim.x * blockDim.x) {
+        const uint32_t slot = ev[i].slot;
+        if ((i && ev[i - 1].slot == slot) || slot >= n_slots)
+            continue;
+        atomicMin(&slot_head[slot], i);
+    }
+}
+
 UVMTIER_KERNEL void __launch_bounds__(kThrashThreads)
 k_thrash_heads(uint32_t n_events, const uvmtier_perf_event_t *__restrict__ ev, uint32_t n_slots, uint32_t *__restrict__ scratch,
                uint32_t *__restrict__ counters)
 {
-    uint32_t *seg = scratch + 4, *seen = scratch + 4 + n_slots;
+    uint32_t *seg = scratch + 4;
+    const uint32_t *slot_head = scratch + 4 + n_slots;
     for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n_events; i += gridDim.x * blockDim.x) {
         const uint32_t slot = ev[i].slot;
         if (i && ev[i - 1].slot == slot)
             continue;
-        // no such va_block, or a second group of a va_block that already has one in this call: dropped, and reported
-        if (slot >= n_slots || (atomicOr(&seen[slot >> 5], 1u << (slot & 31)) & (1u << (slot & 31)))) {
+        // no such va_block, or a later group of a va_block that already has one in this call: dropped, and reported
+        if (slot >= n_slots || slot_head[slot] != i) {
             uint32_t n = 1;
             while (i + n < n_events && ev[i + n].slot == slot) n++;
             atomicAdd(&counters[2], n);

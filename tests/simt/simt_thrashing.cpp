@@ -2,6 +2,7 @@
 // TEST INFRASTRUCTURE ONLY.
 #include "simt.h"
 
+#include <algorithm>
 #include <vector>
 
 #include "thrashing_kernels.cuh"
@@ -30,9 +31,11 @@ extern "C" int simt_thrash_events(uint32_t n_slots, uint32_t n_events, const uvm
 {
     const thrash_hint_tables th = tables_of(tb);
     uint32_t *counters = (uint32_t *)tb[9];
-    std::vector<uint32_t> scratch(4 + (size_t)n_slots + (n_slots + 31) / 32, 0u);
+    std::vector<uint32_t> scratch(4 + 2 * (size_t)n_slots, 0u);
+    std::fill(scratch.begin() + 4 + n_slots, scratch.end(), 0xffffffffu);
     if (!n_events)
         return 0;
+    simt::launch(dim3(2), dim3(kThrashThreads), [&] { k_thrash_heads_min(n_events, ev, n_slots, scratch.data()); });
     simt::launch(dim3(2), dim3(kThrashThreads), [&] { k_thrash_heads(n_events, ev, n_slots, scratch.data(), counters); });
     simt::launch(dim3(2), dim3(kThrashThreads), [&] {
         k_thrash_events(n_events, ev, n_slots, lapse_ns, threshold, th.blocks, th.page_word, th.page_procs, th.thrashing_pages,
@@ -46,9 +49,11 @@ extern "C" int simt_thrash_hints(uint32_t n_slots, uint32_t n, const uvmtier_thr
 {
     const thrash_hint_tables th = tables_of(tb);
     uint32_t *counters = (uint32_t *)tb[9];
-    std::vector<uint32_t> scratch(4 + (size_t)n_slots + (n_slots + 31) / 32, 0u);
+    std::vector<uint32_t> scratch(4 + 2 * (size_t)n_slots, 0u);
+    std::fill(scratch.begin() + 4 + n_slots, scratch.end(), 0xffffffffu);
     if (!n)
         return 0;
+    simt::launch(dim3(2), dim3(kThrashThreads), [&] { k_thrash_heads_min(n, (const uvmtier_perf_event_t *)q, n_slots, scratch.data()); });
     simt::launch(dim3(2), dim3(kThrashThreads), [&] { k_thrash_heads(n, (const uvmtier_perf_event_t *)q, n_slots, scratch.data(), counters); });
     simt::launch(dim3(2), dim3(128), [&] { k_thrash_hints(n, q, n_slots, cfg, th, scratch.data(), hints, counters); });
     return 0;

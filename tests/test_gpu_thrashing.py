@@ -168,3 +168,26 @@ def test_gpu_service_with_hints_matches_restatement(seed, topology, kw):
     throttled, pinned, remote = TS.check(want, got, B, "seed %d %s" % (seed, topology))
     assert np.array_equal(want["thrash"].counters[3:6], got["thrash"].counters[3:6])
     assert throttled + pinned + remote > 10, (throttled, pinned, remote)
+
+
+def test_a_va_block_in_two_groups_keeps_the_group_that_starts_first():
+    """Every va_block shows up in two separate groups, far apart in the array (different CTAs take their heads): the first
+    group is the one that is applied, the second is dropped and counted -- on every run, not by the luck of the schedule."""
+    n_slots = 4096
+    layout = S.make_layout(dict(va_base=TG.VA_BASE, blocks_per_space=n_slots, n_spaces=1))
+    ev = np.zeros(2 * n_slots * 2, TH.EVENT_DT)
+    half = n_slots * 2
+    for part, (t0, proc) in enumerate(((1000, 0), (900000, 1))):
+        sl = slice(part * half, (part + 1) * half)
+        ev["slot"][sl] = np.repeat(np.arange(n_slots), 2)
+        ev["time_stamp"][sl] = t0 + np.tile([0, 10], n_slots)
+        ev["num_pages"][sl] = 4
+        ev["processor"][sl] = proc
+    with uvmtier.Context(0) as ctx:
+        for _ in range(3):
+            t = ctx.thrashing_create(layout)
+            cnt = ctx.thrashing_note_events(t, ev)
+            blocks = ctx.thrashing_tables(t)["blocks"].view(TH.BLOCK_DT)
+            ctx.thrashing_destroy(t)
+            assert cnt[2] == half
+            assert (blocks["last_time_stamp"] == 1010).all() and (blocks["last_processor"] == 0).all()

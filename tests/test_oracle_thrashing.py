@@ -149,7 +149,7 @@ def test_simt_hint_kernels_match_restatement_on_driver_histories(seed, topology,
     orc, sim = T.load_oracle(), T.load_simt()
     cfg = TH.make_cfg(topology, gpus=tuple(p for p in (1, 2, 9) if p in procs), pin_threshold=3, pin=20, epoch=200)
     n_slots = 5
-    steps, _ = TH.driver_history(n_slots, 600, seed, cfg, procs=procs, hot_pages=2)
+    steps, _ = TH.driver_history(n_slots, 400, seed, cfg, procs=procs, hot_pages=2)
     want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
     got, got_h = TH.run_steps_simt(sim, steps, n_slots, cfg)
     _same_hints(want_h, got_h, "seed %d" % seed)
@@ -163,7 +163,7 @@ def test_simt_hint_kernels_match_restatement_on_random_streams(seed, topology):
     orc, sim = T.load_oracle(), T.load_simt()
     cfg = TH.make_cfg(topology, gpus=(1, 2, 9), pin_threshold=3, epoch=50, pin=20)
     n_slots = 4
-    steps = TH.random_stream(seed, n_slots, 300)
+    steps = TH.random_stream(seed, n_slots, 200)
     want, want_h = TH.run_steps_oracle(orc, steps, n_slots, cfg)
     got, got_h = TH.run_steps_simt(sim, steps, n_slots, cfg)
     _same_hints(want_h, got_h, "seed %d" % seed)

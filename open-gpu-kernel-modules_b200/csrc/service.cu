@@ -133,15 +133,28 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
     UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[0], ctx->stream));
     UVMTIER_CUDA(cudaStreamWaitEvent(s_heavy, ctx->aux_events[0], 0));
     UVMTIER_CUDA(cudaStreamWaitEvent(s_unmapped, ctx->aux_events[0], 0));
-    UVMTIER_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, 0, s_heavy, cw, v.offset, v.list, v.big);
-    UVMTIER_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, 0, s_heavy, prm, d_ordered, d_groups, d_batches, bs, cw,
-                   v.offset, v.list, v.heavy, d_entry_flags, d_service, d_runs, d_counters, tp);
-    UVMTIER_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, 0, s_unmapped, prm, d_ordered, d_groups, d_batches, d_tbl,
-                   v.batch_unmapped, d_entry_flags, d_service);
+    // a launch that fails between the fork and the join must not leave the side streams unjoined (a capturing stream would
+    // be invalidated): remember the first failure, join, then report it
+    NV_STATUS st = NV_OK;
+#define SVC_SIDE_LAUNCH(kernel, grid, block, stream, ...)                                  \
+    do {                                                                                   \
+        kernel<<<(grid), (block), 0, (stream)>>>(__VA_ARGS__);                             \
+        g_uvmtier_launches.fetch_add(1, std::memory_order_relaxed);                        \
+        const cudaError_t _e = cudaGetLastError();                                         \
+        if (_e != cudaSuccess && st == NV_OK) {                                            \
+            uvmtier_set_error(#kernel, _e, __FILE__, __LINE__);                            \
+            st = uvmtier_status_from_cuda(_e);                                             \
+        }                                                                                  \
+    } while (0)
+    SVC_SIDE_LAUNCH(k_service_sort_big, ctx->sm_count, kSortBigThreads, s_heavy, cw, v.offset, v.list, v.big);
+    SVC_SIDE_LAUNCH(k_service_blocks, ctx->sm_count * 2, kSvcThreads, s_heavy, prm, d_ordered, d_groups, d_batches, bs, cw, v.offset, v.list,
+                    v.heavy, d_entry_flags, d_service, d_runs, d_counters, tp);
+    SVC_SIDE_LAUNCH(k_service_unmapped, (prm.n_batches + 127) / 128, 128, s_unmapped, prm, d_ordered, d_groups, d_batches, d_tbl,
+                    v.batch_unmapped, d_entry_flags, d_service);
+#undef SVC_SIDE_LAUNCH
     UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[1], s_heavy));
     UVMTIER_CUDA(cudaEventRecord(ctx->aux_events[2], s_unmapped));
     // light va_blocks: four lanes each
-    NV_STATUS st = NV_OK;
     {
         // one wave: as many CTAs as the GPU keeps resident (fewer when the table is small); v.cursor[2] is the work counter
         uint32_t grid = (uint32_t)(((size_t)n_slots * kGrpLanes + kGrpThreads - 1) / kGrpThreads);
@@ -152,7 +165,7 @@ static NV_STATUS service_pass(uvmtier_ctx_t *ctx, uint32_t *base, uint32_t n_bat
             d_counters, v.cursor + 2);
         g_uvmtier_launches.fetch_add(1, std::memory_order_relaxed);
         const cudaError_t le = cudaGetLastError();
-        if (le != cudaSuccess) {                                // the side streams are joined below all the same
+        if (le != cudaSuccess && st == NV_OK) {                 // the side streams are joined below all the same
             uvmtier_set_error("k_service_blocks_grp", le, __FILE__, __LINE__);
             st = uvmtier_status_from_cuda(le);
         }

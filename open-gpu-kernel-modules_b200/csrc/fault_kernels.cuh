@@ -241,7 +241,7 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
     uint16_t *s_ctx = (uint16_t *)sp;                         sp += (size_t)T * 2;
     uint16_t *s_num = (uint16_t *)sp;                         sp += (size_t)T * 2;
     uint16_t *s_gstart = (uint16_t *)sp;                      sp += (size_t)T * 2;
-    uint16_t *s_spare = (uint16_t *)sp;                       sp += (size_t)T * 2;
+    sp += (size_t)T * 2;                                      // (spare, keeps fault_smem_bytes' count)
     uint8_t *s_acc = (uint8_t *)sp;                           sp += (size_t)T;
     uint8_t *s_st = (uint8_t *)sp;                            sp += (size_t)T;
     uint8_t *s_mask8 = (uint8_t *)sp;                         sp += (size_t)T;
@@ -249,7 +249,6 @@ k_fault_fetch_preprocess(fault_kparams prm, uvmtier_fault_packet_t *__restrict__
     sp = (unsigned char *)(((uintptr_t)sp + 15) & ~(uintptr_t)15);
     uint16_t *s_tbl = (uint16_t *)sp;                         sp += (((size_t)W * U * 2) + 15) & ~(size_t)15;
     uvmtier_instance_ptr_entry_t *s_rows = (uvmtier_instance_ptr_entry_t *)sp;
-    (void)s_spare;
 
     // ---- phase 1: load + decode (F1) ----
     const bool inwin = (uint32_t)tid < nb;
